@@ -1,0 +1,122 @@
+/* roms_b200.h -- C ABI of libromsb200.so: the B200-native drop-in for the explicit
+ * stencil time step of UCLA-ROMS (reference: dafyddstephenson/ucla-roms, src/).
+ *
+ * The reference drives its dynamical kernel through argument-free / (tile) Fortran
+ * subroutines whose state is module globals (main.F:397-479).  Each export below replaces
+ * one of them; a Fortran maintainer binds it with an `interface ... bind(C)` block (see
+ * INTEGRATION.md).  All state lives on the device in the reference's (i,j,k) column-major
+ * layout with a 2-cell halo: a 2-D field is (-1:Lm+2, -1:Mm+2), rho/u/v-type 3-D fields add
+ * k=1:N, w-type fields k=0:N (set_global_definitions.h:146-150).  Host buffers handed to
+ * roms_push/roms_pull use exactly that layout, so `c_loc(array)` of the Fortran module
+ * arrays can be passed unchanged.
+ *
+ * Every function returns 0 on success, <0 on CUDA/NCCL failure, >0 when a non-finite state
+ * was detected.  No function falls back to the CPU.
+ */
+#ifndef ROMS_B200_H
+#define ROMS_B200_H
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct roms_ctx roms_ctx;   /* opaque per-GPU handle */
+
+/* Run-time replacement for the reference's compile-time param.opt + *.in keywords
+ * (param.opt:20-43, read_inp_mod.F:416-446). Sizes are those of THIS subdomain. */
+typedef struct roms_cfg {
+  int Lm, Mm, N, NT;          /* interior points of this subdomain; levels; tracers          */
+  int ew_periodic, ns_periodic;/* cppdefs EW_PERIODIC / NS_PERIODIC                          */
+  int nonlin_eos;             /* 0: linear rho=Tcoef*(T0-T)+Scoef*(S-S0) ; 1: NONLIN+SPLIT_EOS */
+  int salinity;               /* cppdefs SALINITY (tracer 2 is S)                             */
+  int ndtfast;                /* barotropic steps per baroclinic step (time_stepping keyword) */
+  int np_xi, np_eta;          /* process grid (mpi_setup.F:61-70); 1x1 for a single GPU       */
+  int inode, jnode;           /* this rank's position in it                                   */
+  double dt;                  /* baroclinic time step [s]                                     */
+  double rho0, g;
+  double Tcoef, T0, Scoef, S0;/* lin_rho_eos keyword                                          */
+  double rdrg, rdrg2, Zob;    /* bottom_drag keyword                                          */
+  double gamma2;              /* slipperiness                                                 */
+  double theta_s, theta_b, hc;/* S-coord keyword                                              */
+} roms_cfg;
+
+/* Field identifiers for roms_push / roms_pull.  `lvl` selects the time level (1-based, as in
+ * the Fortran: zeta(:,:,1:4), u(:,:,:,1:3), t(:,:,:,1:3,itrc)); `itrc` the tracer (1-based).
+ * Unused selectors are ignored. */
+enum roms_field {
+  /* static 2-D, supplied by the host (grid.F:124-177) */
+  ROMS_H = 0, ROMS_PM, ROMS_PN, ROMS_F, ROMS_RMASK,
+  /* derived 2-D metrics (setup_grid1.F), computed by roms_setup_grid */
+  ROMS_UMASK, ROMS_VMASK, ROMS_DM_U, ROMS_DN_U, ROMS_DM_V, ROMS_DN_V, ROMS_DM_R, ROMS_DN_R,
+  ROMS_FOMN, ROMS_HINV,
+  /* 2-D state (ocean_vars.F:67-69, coupling.F:22-44, surf_flux.F:86-94) */
+  ROMS_ZETA, ROMS_UBAR, ROMS_VBAR,               /* lvl 1..4 */
+  ROMS_RHOA, ROMS_RHOS, ROMS_RUFRC, ROMS_RVFRC,
+  ROMS_ZT_AVG1, ROMS_DU_AVG1, ROMS_DV_AVG1, ROMS_DU_AVG2, ROMS_DV_AVG2,
+  ROMS_DU_AVG_BAK, ROMS_DV_AVG_BAK, ROMS_R_D,
+  ROMS_SUSTR, ROMS_SVSTR, ROMS_SWFLX,
+  ROMS_STFLX,                                    /* itrc 1..NT */
+  /* 3-D state */
+  ROMS_U, ROMS_V,                                /* lvl 1..3, k=1:N */
+  ROMS_T,                                        /* lvl 1..3, itrc 1..NT, k=1:N */
+  ROMS_HZ, ROMS_Z_R,                             /* k=1:N */
+  ROMS_Z_W,                                      /* k=0:N */
+  ROMS_FLXU, ROMS_FLXV,                          /* k=1:N */
+  ROMS_WE, ROMS_WI,                              /* k=0:N */
+  ROMS_RHO1, ROMS_QP1,                           /* k=1:N (linear EOS: RHO1 holds rho) */
+  ROMS_AKV,                                      /* k=0:N */
+  ROMS_AKT,                                      /* itrc 1..2 (iTandS), k=0:N */
+  ROMS_RU, ROMS_RV,                              /* k=1:N; prsgrd -> pre_step3d/step3d_uv1 hand-off
+                                                    (the reference's A3d(1,1:2), prsgrd.F:12) */
+  ROMS_NFIELDS
+};
+
+/* ---- lifetime, data movement ------------------------------------------------------------ */
+int  roms_create(const roms_cfg* cfg, int device, roms_ctx** out);
+int  roms_destroy(roms_ctx* h);
+int  roms_push(roms_ctx* h, int field, int lvl, int itrc, const double* host);   /* H2D */
+int  roms_pull(roms_ctx* h, int field, int lvl, int itrc, double* host);         /* D2H, blocking */
+long roms_field_count(roms_ctx* h, int field);  /* doubles per (lvl,itrc) slab */
+int  roms_sync(roms_ctx* h);
+const char* roms_last_error(void);
+
+/* ---- host-side constants (set_scoord.F:4-66, set_weights.F:7-246, setup_grid1.F:13-210) -- */
+int  roms_setup_grid(roms_ctx* h);      /* after H,PM,PN,F,RMASK are pushed                  */
+int  roms_get_nfast(roms_ctx* h);       /* executed barotropic substeps (82 for ndtfast=60)   */
+int  roms_get_weights(roms_ctx* h, double* w1, double* w2, int n); /* weight(1:2,1:n)         */
+int  roms_get_scoord(roms_ctx* h, double* Cs_w, double* Cs_r);     /* Cs_w(0:N), Cs_r(1:N)    */
+
+/* ---- loop-control scalars (scalars.F:28-32): the driver keeps owning the rotation -------- */
+int  roms_set_time_indices(roms_ctx* h, int iic, int iif, int nstp, int nrhs, int nnew,
+                           int kstp, int knew);
+int  roms_get_time_indices(roms_ctx* h, int* iic, int* iif, int* nstp, int* nrhs, int* nnew,
+                           int* kstp, int* knew);
+int  roms_compute_tile_bounds(roms_ctx* h, int tile, int* istr, int* iend, int* jstr, int* jend);
+                                        /* compute_tile_bounds.h:45-79 with NSUB_X=NSUB_E=1  */
+
+/* ---- the tile-subroutine surface (one export per reference subroutine) ------------------- */
+int  roms_set_depth(roms_ctx* h, int tile);   /* set_depth.F:4     */
+int  roms_set_huv(roms_ctx* h);               /* set_depth.F:190   */
+int  roms_set_huv1(roms_ctx* h, int tile);    /* set_depth.F:239   */
+int  roms_omega(roms_ctx* h);                 /* omega.F:4         */
+int  roms_rho_eos(roms_ctx* h, int tidx);     /* rho_eos.F:6       */
+int  roms_prsgrd(roms_ctx* h);                /* prsgrd.F:4        */
+int  roms_pre_step3d(roms_ctx* h, int tile);  /* pre_step3d4S.F:4  */
+int  roms_step3d_uv1(roms_ctx* h, int tile);  /* step3d_uv1.F:5    */
+int  roms_step2d(roms_ctx* h);                /* step2d_FB.F:3     */
+int  roms_step3d_uv2(roms_ctx* h, int tile);  /* step3d_uv2.F:6    */
+int  roms_step3d_t(roms_ctx* h, int tile);    /* step3d_t_ISO.F:20 */
+int  roms_alfabeta(roms_ctx* h, double* alpha_host, double* beta_host); /* alfabeta.F:4 */
+int  roms_exchange(roms_ctx* h, int nfields, const int* fields, const int* lvls, const int* itrcs);
+                                              /* mpi_exchanges.F:34-40 exchange_xxx */
+int  roms_diag(roms_ctx* h, double out[4]);   /* diag.F:50: KE, barotropic KE, max adv CFL, its vertical part */
+
+/* ---- the driver loop body, for hosts without a Fortran main (main.F:86-321, 333-520) ---- */
+int  roms_init_step0(roms_ctx* h);            /* set_depth, set_HUV, omega, rho_eos of roms_init */
+int  roms_step(roms_ctx* h);                  /* one baroclinic step: main.F:397-479            */
+int  roms_run(roms_ctx* h, int nsteps);       /* nsteps x roms_step                             */
+int  roms_kernel_launches(roms_ctx* h, long* n); /* kernels launched so far by this context    */
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,1605 @@
+// roms_oracle.cpp -- CPU restatement of the UCLA-ROMS explicit stencil time step.
+//
+// TEST INFRASTRUCTURE ONLY.  This file is the parity oracle for libromsb200.so and the timed
+// "cpu_baseline" of bench.py.  Nothing under ucla-roms_b200/ may link, import or call it.
+//
+// Parity pin: the restatement reproduces the reference's golden regression log
+// tests/Filament/benchmark.result_github_gnu:146-167 (KINETIC_ENRG, BAROTR_KE, MAX_ADV_CFL,
+// MAX_VERT_CFL for steps 0..20); see tests/test_oracle_golden.py.
+//
+// Each function follows the switch-resolved Fortran that the reference's own pre-processing
+// (cpp -traditional | Tools-Roms/mpc_python/mpc.py) emits for the Filament configuration
+// (tests/Filament/cppdefs.opt) and for the same configuration with NONLIN_EOS+SALINITY.
+// Loop structure (k-outer 2-D sweeps with private scratch planes, j-outer (i,k) slabs) and
+// operation order are the reference's; decimal literals are copied verbatim because the mpc
+// pre-compiler promotes them to double as written.
+// Build: g++ -O2 -ffp-contract=off (no FMA contraction) [-fopenmp for the timed variant].
+//
+// Array layout = the reference's: i fastest, 2-cell halo, (-1:Lm+2,-1:Mm+2[,k]).
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <vector>
+#include <algorithm>
+#include "../include/roms_b200.h"
+
+typedef std::vector<double> vec;
+
+namespace {
+
+struct Orc {
+  roms_cfg c;
+  int Lm, Mm, N, NT, SX, SY;
+  size_t SXY;
+  int nfast;
+  vec weight1, weight2, Cs_w, Cs_r;
+  // 2-D
+  vec h, pm, pn, f, rmask, umask, vmask, dm_u, dn_u, dm_v, dn_v, dm_r, dn_r, fomn, hinv;
+  vec zeta[4], ubar[4], vbar[4];
+  vec rhoA, rhoS, rufrc, rvfrc, Zt_avg1, DU_avg1, DV_avg1, DU_avg2, DV_avg2, DU_avg_bak, DV_avg_bak, r_D;
+  vec sustr, svstr, swflx;
+  std::vector<vec> stflx;
+  // 3-D
+  vec u[3], v[3];
+  std::vector<vec> t[3];
+  vec Hz, z_r, z_w, FlxU, FlxV, We, Wi, rho1, qp1, Akv, Akt[2], ru, rv;
+  vec Hz_bak, Hz_fwd, Pp, rho;  // A3d(1,3:4) of the reference
+  // time indices (scalars.F)
+  int iic, iif, nstp, nrhs, nnew, kstp, knew, ntstart, forw_start;
+  double dtfast, area, volume;
+  vec xr;  // only for the Filament analytic initial condition
+  std::vector<vec> s2d;
+};
+
+#define A2(a, i, j) (a)[(size_t)((i) + 1) + (size_t)((j) + 1) * SX]
+#define A3(a, i, j, k) (a)[(size_t)((i) + 1) + (size_t)((j) + 1) * SX + (size_t)((k)-1) * SXY]
+#define AW(a, i, j, k) (a)[(size_t)((i) + 1) + (size_t)((j) + 1) * SX + (size_t)(k) * SXY]
+#define SL(a, i, k) (a)[(size_t)((i) + 1) + (size_t)(k) * SX]   // (i,k) slab scratch, k=0:N
+
+#define GEOM                                                                                 \
+  const int Lm = o.Lm, Mm = o.Mm, N = o.N, SX = o.SX;                                        \
+  const size_t SXY = o.SXY;                                                                  \
+  const int istr = 1, iend = Lm, jstr = 1, jend = Mm;                                        \
+  (void)N; (void)SXY; (void)istr; (void)iend; (void)jstr; (void)jend; (void)Mm;
+
+// ---------------------------------------------------------------------------------------------
+// exchange_xxx (mpi_exchanges.F:34-40) on a single subdomain: periodic wrap of the 2-cell halo
+// (mpi_setup.F:231-250).  Non-periodic edges are left untouched, as in the reference.
+void exchange(const Orc& o, double* a, int nk) {
+  const int Lm = o.Lm, Mm = o.Mm, SX = o.SX;
+  const size_t SXY = o.SXY;
+  for (int k = 0; k < nk; ++k) {
+    double* p = a + (size_t)k * SXY;
+    if (o.c.ew_periodic)
+      for (int j = 1; j <= Mm; ++j) {
+        A2(p, -1, j) = A2(p, Lm - 1, j);
+        A2(p, 0, j) = A2(p, Lm, j);
+        A2(p, Lm + 1, j) = A2(p, 1, j);
+        A2(p, Lm + 2, j) = A2(p, 2, j);
+      }
+    if (o.c.ns_periodic)
+      for (int i = -1; i <= Lm + 2; ++i) {
+        A2(p, i, -1) = A2(p, i, Mm - 1);
+        A2(p, i, 0) = A2(p, i, Mm);
+        A2(p, i, Mm + 1) = A2(p, i, 1);
+        A2(p, i, Mm + 2) = A2(p, i, 2);
+      }
+  }
+}
+inline void ex2(const Orc& o, vec& a) { exchange(o, a.data(), 1); }
+inline void ex3(const Orc& o, vec& a) { exchange(o, a.data(), o.N); }
+inline void exw(const Orc& o, vec& a) { exchange(o, a.data(), o.N + 1); }
+
+// ---------------------------------------------------------------------------------------------
+// set_scoord.F:4-66
+double CSF(double sc, double theta_s, double theta_b) {
+  double csrf, r;
+  if (theta_s > 0.0) csrf = (1.0 - cosh(theta_s * sc)) / (cosh(theta_s) - 1.0);
+  else csrf = -sc * sc;
+  if (theta_b > 0.0) r = (exp(theta_b * csrf) - 1.0) / (1.0 - exp(-theta_b));
+  else r = csrf;
+  return r;
+}
+void set_scoord(Orc& o) {
+  const int N = o.N;
+  o.Cs_w.assign(N + 1, 0.0);
+  o.Cs_r.assign(N + 1, 0.0);
+  double ds = 1.0 / double(N);
+  o.Cs_w[N] = 0.0;
+  for (int k = N - 1; k >= 1; --k) o.Cs_w[k] = CSF(ds * double(k - N), o.c.theta_s, o.c.theta_b);
+  o.Cs_w[0] = -1.0;
+  for (int k = 1; k <= N; ++k) o.Cs_r[k] = CSF(ds * (double(k - N) - 0.5), o.c.theta_s, o.c.theta_b);
+}
+
+// set_weights.F:7-246 (power-law shape filter p=2,q=4,r=0.25; weight(1:2,1:2*ndtfast))
+void set_weights(Orc& o) {
+  const int ndtfast = o.c.ndtfast;
+  vec& w1 = o.weight1;
+  vec& w2 = o.weight2;
+  w1.assign(2 * ndtfast + 2, 0.0);
+  w2.assign(2 * ndtfast + 2, 0.0);
+  int nfast = 0;
+  double p = 2.0, q = 4.0, r = 0.25;
+  double scale = (p + 1.0) * (p + q + 1.0) / ((p + 2.0) * (p + q + 2.0) * double(ndtfast));
+  double sum, shft, cff;
+  for (int iter = 1; iter <= 16; ++iter) {
+    nfast = 0;
+    for (int i = 1; i <= 2 * ndtfast; ++i) {
+      cff = scale * double(i);
+      w1[i] = pow(cff, p) - pow(cff, p + q) - r * cff;
+      if (w1[i] > 0.0) nfast = i;
+      if (nfast > 0 && w1[i] < 0.0) w1[i] = 0.0;
+    }
+    sum = 0.0; shft = 0.0;
+    for (int i = 1; i <= nfast; ++i) { sum = sum + w1[i]; shft = shft + w1[i] * double(i); }
+    scale = scale * shft / (sum * double(ndtfast));
+  }
+  for (int iter = 1; iter <= ndtfast; ++iter) {
+    sum = 0.0; shft = 0.0;
+    for (int i = 1; i <= nfast; ++i) { sum = sum + w1[i]; shft = shft + double(i) * w1[i]; }
+    shft = shft / sum;
+    cff = double(ndtfast) - shft;
+    if (cff > 1.0) {
+      nfast = nfast + 1;
+      for (int i = nfast; i >= 2; --i) w1[i] = w1[i - 1];
+      w1[1] = 0.0;
+    } else if (cff > 0.0) {
+      sum = 1.0 - cff;
+      for (int i = nfast; i >= 2; --i) w1[i] = sum * w1[i] + cff * w1[i - 1];
+      w1[1] = sum * w1[1];
+    } else if (cff < -1.0) {
+      nfast = nfast - 1;
+      for (int i = 1; i <= nfast; ++i) w1[i] = w1[i + 1];
+      w1[nfast + 1] = 0.0;
+    } else if (cff < 0.0) {
+      sum = 1.0 + cff;
+      for (int i = 1; i <= nfast - 1; ++i) w1[i] = sum * w1[i] - cff * w1[i + 1];
+      w1[nfast] = sum * w1[nfast];
+    }
+  }
+  for (int j = 1; j <= nfast; ++j) {
+    cff = w1[j];
+    for (int i = 1; i <= j; ++i) w2[i] = w2[i] + cff;
+  }
+  sum = 0.0; cff = 0.0;
+  for (int i = 1; i <= nfast; ++i) { sum = sum + w1[i]; cff = cff + w2[i]; }
+  sum = 1.0 / sum; cff = 1.0 / cff;
+  for (int i = 1; i <= nfast; ++i) { w1[i] = sum * w1[i]; w2[i] = cff * w2[i]; }
+  o.nfast = nfast;
+}
+
+// setup_grid1.F:13-210 (setup_Corls_tile + setup_grid1_tile), then area/volume of setup_grid2.F
+void setup_grid(Orc& o) {
+  GEOM
+  for (int j = -1; j <= Mm + 2; ++j)
+    for (int i = -1; i <= Lm + 2; ++i) A2(o.fomn, i, j) = A2(o.f, i, j) / (A2(o.pm, i, j) * A2(o.pn, i, j));
+  for (int j = jstr; j <= jend; ++j)
+    for (int i = istr; i <= iend; ++i) {
+      A2(o.dm_r, i, j) = 1.0 / A2(o.pm, i, j);
+      A2(o.dn_r, i, j) = 1.0 / A2(o.pn, i, j);
+      A2(o.dm_u, i, j) = 2.0 / (A2(o.pm, i, j) + A2(o.pm, i - 1, j));
+      A2(o.dn_u, i, j) = 2.0 / (A2(o.pn, i, j) + A2(o.pn, i - 1, j));
+      A2(o.umask, i, j) = A2(o.rmask, i, j) * A2(o.rmask, i - 1, j);
+      A2(o.dm_v, i, j) = 2.0 / (A2(o.pm, i, j) + A2(o.pm, i, j - 1));
+      A2(o.dn_v, i, j) = 2.0 / (A2(o.pn, i, j) + A2(o.pn, i, j - 1));
+      A2(o.vmask, i, j) = A2(o.rmask, i, j) * A2(o.rmask, i, j - 1);
+    }
+  vec* ex[] = {&o.dm_r, &o.dn_r, &o.dm_u, &o.dn_u, &o.dm_v, &o.dn_v, &o.rmask, &o.umask, &o.vmask};
+  for (vec* a : ex) ex2(o, *a);
+  // setup_grid2.F: area, volume (plain sums here; only used to normalise diag output)
+  double area = 0, vol = 0;
+  for (int j = jstr; j <= jend; ++j)
+    for (int i = istr; i <= iend; ++i) {
+      double dA = A2(o.rmask, i, j) / (A2(o.pm, i, j) * A2(o.pn, i, j));
+      area += dA;
+      vol += dA * A2(o.h, i, j);
+    }
+  o.area = area;
+  o.volume = vol;
+}
+
+// ---------------------------------------------------------------------------------------------
+// set_depth.F:16-186 set_depth_tile
+void set_depth(Orc& o) {
+  GEOM
+  const double hc = o.c.hc;
+  vec& zeta = o.zeta[o.knew - 1];
+  if (o.iic == 0) {
+    for (int j = jstr; j <= jend; ++j)
+      for (int i = istr; i <= iend; ++i) A2(o.hinv, i, j) = 1.0 / (A2(o.h, i, j) + hc);
+    for (int j = jstr; j <= jend; ++j)
+      for (int i = istr; i <= iend; ++i)
+        A2(o.DU_avg1, i, j) = 0.5 * (A2(o.h, i - 1, j) + A2(o.h, i, j) + A2(o.zeta[0], i, j) + A2(o.zeta[0], i - 1, j)) *
+                              A2(o.dn_u, i, j) * (A2(o.ubar[0], i, j));
+    for (int j = jstr; j <= jend; ++j)
+      for (int i = istr; i <= iend; ++i)
+        A2(o.DV_avg1, i, j) = 0.5 * (A2(o.h, i, j) + A2(o.h, i, j - 1) + A2(o.zeta[0], i, j) + A2(o.zeta[0], i, j - 1)) *
+                              A2(o.dm_v, i, j) * (A2(o.vbar[0], i, j));
+  }
+  const double ds = 1.0 / double(N);
+#pragma omp parallel for
+  for (int j = jstr; j <= jend; ++j) {
+    for (int i = istr; i <= iend; ++i) AW(o.z_w, i, j, 0) = -A2(o.h, i, j);
+    for (int k = 1; k <= N; ++k) {
+      double cff_w = hc * ds * double(k - N);
+      double cff_r = hc * ds * (double(k - N) - 0.5);
+      double cff1_w = o.Cs_w[k];
+      double cff1_r = o.Cs_r[k];
+      for (int i = istr; i <= iend; ++i) {
+        AW(o.z_w, i, j, k) = A2(zeta, i, j) + (A2(zeta, i, j) + A2(o.h, i, j)) * (cff_w + cff1_w * A2(o.h, i, j)) * A2(o.hinv, i, j);
+        A3(o.z_r, i, j, k) = A2(zeta, i, j) + (A2(zeta, i, j) + A2(o.h, i, j)) * (cff_r + cff1_r * A2(o.h, i, j)) * A2(o.hinv, i, j);
+        A3(o.Hz, i, j, k) = AW(o.z_w, i, j, k) - AW(o.z_w, i, j, k - 1);
+      }
+    }
+  }
+  if (o.iic == 0) ex2(o, o.hinv);
+  exw(o, o.z_w); ex3(o, o.z_r); ex3(o, o.Hz);
+}
+
+// set_depth.F:201-234 set_HUV_tile
+void set_HUV(Orc& o) {
+  GEOM
+  vec& u = o.u[o.nrhs - 1];
+  vec& v = o.v[o.nrhs - 1];
+#pragma omp parallel for
+  for (int k = 1; k <= N; ++k) {
+    for (int j = jstr; j <= jend; ++j)
+      for (int i = istr; i <= iend; ++i)
+        A3(o.FlxU, i, j, k) = 0.5 * (A3(o.Hz, i, j, k) + A3(o.Hz, i - 1, j, k)) * A2(o.dn_u, i, j) * (A3(u, i, j, k));
+    for (int j = jstr; j <= jend; ++j)
+      for (int i = istr; i <= iend; ++i)
+        A3(o.FlxV, i, j, k) = 0.5 * (A3(o.Hz, i, j, k) + A3(o.Hz, i, j - 1, k)) * A2(o.dm_v, i, j) * (A3(v, i, j, k));
+  }
+  ex3(o, o.FlxU); ex3(o, o.FlxV);
+}
+
+// set_depth.F:252-422 set_HUV1_tile
+void set_HUV1(Orc& o) {
+  GEOM
+  vec& u = o.u[o.nnew - 1];
+  vec& v = o.v[o.nnew - 1];
+  const bool first = (o.iic == o.forw_start);
+#pragma omp parallel
+  {
+    vec DC((size_t)SX * (N + 1)), FC((size_t)SX * (N + 1));
+#pragma omp for
+    for (int j = jstr; j <= jend; ++j) {
+      for (int i = istr; i <= iend; ++i) {
+        SL(DC, i, N) = 0.5 * (A3(o.Hz, i, j, N) + A3(o.Hz, i - 1, j, N)) * A2(o.dn_u, i, j);
+        SL(DC, i, 0) = SL(DC, i, N);
+        SL(FC, i, 0) = SL(DC, i, N) * A3(u, i, j, N);
+      }
+      for (int k = N - 1; k >= 1; --k)
+        for (int i = istr; i <= iend; ++i) {
+          SL(DC, i, k) = 0.5 * (A3(o.Hz, i, j, k) + A3(o.Hz, i - 1, j, k)) * A2(o.dn_u, i, j);
+          SL(DC, i, 0) = SL(DC, i, 0) + SL(DC, i, k);
+          SL(FC, i, 0) = SL(FC, i, 0) + SL(DC, i, k) * A3(u, i, j, k);
+        }
+      if (first) {
+        for (int i = istr; i <= iend; ++i) SL(FC, i, 0) = (SL(FC, i, 0) - A2(o.DU_avg1, i, j)) / SL(DC, i, 0);
+      } else {
+        for (int i = istr; i <= iend; ++i)
+          SL(FC, i, 0) = (SL(FC, i, 0) - 3.63 * A2(o.DU_avg1, i, j) + 4.47 * A2(o.DU_avg2, i, j) - 2.05 * A2(o.DU_avg_bak, i, j)) / SL(DC, i, 0);
+      }
+      for (int k = 1; k <= N; ++k)
+        for (int i = istr; i <= iend; ++i) {
+          A3(u, i, j, k) = (A3(u, i, j, k) - SL(FC, i, 0)) * A2(o.umask, i, j);
+          A3(o.FlxU, i, j, k) = SL(DC, i, k) * (A3(u, i, j, k));
+        }
+      for (int i = istr; i <= iend; ++i) {
+        SL(DC, i, N) = 0.5 * (A3(o.Hz, i, j, N) + A3(o.Hz, i, j - 1, N)) * A2(o.dm_v, i, j);
+        SL(DC, i, 0) = SL(DC, i, N);
+        SL(FC, i, 0) = SL(DC, i, N) * A3(v, i, j, N);
+      }
+      for (int k = N - 1; k >= 1; --k)
+        for (int i = istr; i <= iend; ++i) {
+          SL(DC, i, k) = 0.5 * (A3(o.Hz, i, j, k) + A3(o.Hz, i, j - 1, k)) * A2(o.dm_v, i, j);
+          SL(DC, i, 0) = SL(DC, i, 0) + SL(DC, i, k);
+          SL(FC, i, 0) = SL(FC, i, 0) + SL(DC, i, k) * A3(v, i, j, k);
+        }
+      if (first) {
+        for (int i = istr; i <= iend; ++i) SL(FC, i, 0) = (SL(FC, i, 0) - A2(o.DV_avg1, i, j)) / SL(DC, i, 0);
+      } else {
+        for (int i = istr; i <= iend; ++i)
+          SL(FC, i, 0) = (SL(FC, i, 0) - 3.63 * A2(o.DV_avg1, i, j) + 4.47 * A2(o.DV_avg2, i, j) - 2.05 * A2(o.DV_avg_bak, i, j)) / SL(DC, i, 0);
+      }
+      for (int k = 1; k <= N; ++k)
+        for (int i = istr; i <= iend; ++i) {
+          A3(v, i, j, k) = (A3(v, i, j, k) - SL(FC, i, 0)) * A2(o.vmask, i, j);
+          A3(o.FlxV, i, j, k) = SL(DC, i, k) * (A3(v, i, j, k));
+        }
+    }
+  }
+  ex3(o, o.FlxU); ex3(o, o.FlxV); ex3(o, u); ex3(o, v);
+}
+
+// omega.F:17-236 omega_tile
+void omega(Orc& o) {
+  GEOM
+  const double cu_min = 0.6, cu_max = 1.0, cmnx_ratio = cu_min / cu_max, cutoff = 2.0 - cmnx_ratio,
+               r4cmx = 0.25 / (1.0 - cmnx_ratio);
+  double dtau;
+  if (o.nrhs == 3) dtau = o.c.dt;
+  else if (o.iic == o.forw_start) dtau = 0.5 * o.c.dt;
+  else dtau = 0.6 * o.c.dt;
+#pragma omp parallel
+  {
+    vec CX((size_t)SX * (N + 1)), wrk(SX);
+#pragma omp for
+    for (int j = jstr; j <= jend; ++j) {
+      for (int i = istr; i <= iend; ++i) AW(o.Wi, i, j, 0) = 0.0;
+      for (int k = 1; k <= N; ++k)
+        for (int i = istr; i <= iend; ++i) {
+          AW(o.Wi, i, j, k) = AW(o.Wi, i, j, k - 1) - A3(o.FlxU, i + 1, j, k) + A3(o.FlxU, i, j, k) - A3(o.FlxV, i, j + 1, k) + A3(o.FlxV, i, j, k);
+          SL(CX, i, k) = std::max(A3(o.FlxU, i + 1, j, k), 0.0) - std::min(A3(o.FlxU, i, j, k), 0.0) +
+                         std::max(A3(o.FlxV, i, j + 1, k), 0.0) - std::min(A3(o.FlxV, i, j, k), 0.0);
+        }
+      for (int i = istr; i <= iend; ++i) AW(o.Wi, i, j, N) = AW(o.Wi, i, j, N) + A2(o.swflx, i, j) * A2(o.dm_r, i, j) * A2(o.dn_r, i, j);
+      for (int i = istr; i <= iend; ++i) {
+        wrk[i + 1] = AW(o.Wi, i, j, N) / (AW(o.z_w, i, j, N) - AW(o.z_w, i, j, 0));
+        AW(o.Wi, i, j, N) = 0.0;
+        AW(o.We, i, j, N) = 0.0;
+        AW(o.We, i, j, 0) = 0.0;
+        SL(CX, i, 0) = dtau * A2(o.pm, i, j) * A2(o.pn, i, j);
+      }
+      for (int k = N - 1; k >= 1; --k)
+        for (int i = istr; i <= iend; ++i) {
+          AW(o.Wi, i, j, k) = AW(o.Wi, i, j, k) - wrk[i + 1] * (AW(o.z_w, i, j, k) - AW(o.z_w, i, j, 0));
+          double c2d = std::max(SL(CX, i, k), SL(CX, i, k + 1));
+          double dh = std::min(A3(o.Hz, i, j, k), A3(o.Hz, i, j, k + 1));
+          double cw_max = cu_max * dh - c2d * SL(CX, i, 0);
+          if (cw_max > 0.0) {
+            double cw_max2 = cw_max * cw_max;
+            double cw_min = cw_max * cmnx_ratio;
+            double cw = fabs(AW(o.Wi, i, j, k)) * SL(CX, i, 0);
+            double cff;
+            if (cw < cw_min) cff = cw_max2;
+            else if (cw < cutoff * cw_max) cff = cw_max2 + r4cmx * ((cw - cw_min) * (cw - cw_min));
+            else cff = cw_max * cw;
+            AW(o.We, i, j, k) = cw_max2 * AW(o.Wi, i, j, k) / cff;
+            AW(o.Wi, i, j, k) = AW(o.Wi, i, j, k) - AW(o.We, i, j, k);
+          } else {
+            AW(o.We, i, j, k) = 0.0;
+          }
+        }
+    }
+  }
+  exw(o, o.We); exw(o, o.Wi);
+}
+
+// rho_eos.F:26-409 rho_eos_tile (linear branch :316-339, NONLIN+SPLIT branch :195-260; rhoA/rhoS :364-395)
+void rho_eos(Orc& o, int tidx) {
+  GEOM
+  const double rho0 = o.c.rho0, qp2 = 0.0000172;
+  vec& T = o.t[tidx - 1][0];
+  const double r00 = 999.842594, r01 = 6.793952e-2, r02 = -9.095290e-3, r03 = 1.001685e-4, r04 = -1.120083e-6,
+               r05 = 6.536332e-9, r10 = 0.824493, r11 = -4.08990e-3, r12 = 7.64380e-5, r13 = -8.24670e-7,
+               r14 = 5.38750e-9, rS0 = -5.72466e-3, rS1 = 1.02270e-4, rS2 = -1.65460e-6, r20 = 4.8314e-4,
+               K00 = 19092.56, K01 = 209.8925, K02 = -3.041638, K03 = -1.852732e-3, K04 = -1.361629e-5,
+               K10 = 104.4077, K11 = -6.500517, K12 = 0.1553190, K13 = 2.326469e-4, KS0 = -5.587545,
+               KS1 = +0.7390729, KS2 = -1.909078e-2;
+  double Tt = 3.8, Ts = 34.5, sqrtTs = sqrt(Ts);
+  const double K0_Duk = Tt * (K01 + Tt * (K02 + Tt * (K03 + Tt * K04))) +
+                        Ts * (K10 + Tt * (K11 + Tt * (K12 + Tt * K13)) + sqrtTs * (KS0 + Tt * (KS1 + Tt * KS2)));
+  const double dr00 = r00 - rho0;
+  const int nonlin = o.c.nonlin_eos;
+#pragma omp parallel for
+  for (int j = jstr - 2; j <= jend + 2; ++j) {
+    if (!nonlin) {
+      double cff = o.c.Tcoef * o.c.T0;
+      if (o.c.salinity) cff = o.c.Tcoef * o.c.T0 - o.c.Scoef * o.c.S0;   // rho_eos.F:318-322
+      for (int k = 1; k <= N; ++k)
+        for (int i = istr - 2; i <= iend + 2; ++i) {
+          A3(o.rho1, i, j, k) = cff - o.c.Tcoef * A3(T, i, j, k);
+          if (o.c.salinity) A3(o.rho1, i, j, k) = A3(o.rho1, i, j, k) + o.c.Scoef * A3(o.t[tidx - 1][1], i, j, k);
+          A3(o.rho1, i, j, k) = A3(o.rho1, i, j, k) * A2(o.rmask, i, j);
+        }
+    } else {
+      vec& S = o.t[tidx - 1][1];
+      for (int k = 1; k <= N; ++k)
+        for (int i = istr - 2; i <= iend + 2; ++i) {
+          double Tt = A3(T, i, j, k);
+          double Ts = A3(S, i, j, k);
+          double sqrtTs = sqrt(std::max(0.0, Ts));
+          A3(o.rho1, i, j, k) = (dr00 + Tt * (r01 + Tt * (r02 + Tt * (r03 + Tt * (r04 + Tt * r05)))) +
+                                 Ts * (r10 + Tt * (r11 + Tt * (r12 + Tt * (r13 + Tt * r14))) + sqrtTs * (rS0 + Tt * (rS1 + Tt * rS2)) + Ts * r20)) *
+                                A2(o.rmask, i, j);
+          double K0 = Tt * (K01 + Tt * (K02 + Tt * (K03 + Tt * K04))) +
+                      Ts * (K10 + Tt * (K11 + Tt * (K12 + Tt * K13)) + sqrtTs * (KS0 + Tt * (KS1 + Tt * KS2)));
+          A3(o.qp1, i, j, k) = 0.1 * (rho0 + A3(o.rho1, i, j, k)) * (K0_Duk - K0) / ((K00 + K0) * (K00 + K0_Duk)) * A2(o.rmask, i, j);
+        }
+    }
+    for (int i = istr - 2; i <= iend + 2; ++i) {
+      double cff;
+      if (nonlin) {
+        double dpth = -A3(o.z_r, i, j, N);
+        cff = A3(o.Hz, i, j, N) * (A3(o.rho1, i, j, N) + A3(o.qp1, i, j, N) * dpth * (1.0 - qp2 * dpth));
+      } else cff = A3(o.Hz, i, j, N) * A3(o.rho1, i, j, N);
+      A2(o.rhoS, i, j) = 0.5 * cff * A3(o.Hz, i, j, N);
+      A2(o.rhoA, i, j) = cff;
+    }
+    for (int k = N - 1; k >= 1; --k)
+      for (int i = istr - 2; i <= iend + 2; ++i) {
+        double cff;
+        if (nonlin) {
+          double dpth = -A3(o.z_r, i, j, k);
+          cff = A3(o.Hz, i, j, k) * (A3(o.rho1, i, j, k) + A3(o.qp1, i, j, k) * dpth * (1.0 - qp2 * dpth));
+        } else cff = A3(o.Hz, i, j, k) * A3(o.rho1, i, j, k);
+        A2(o.rhoS, i, j) = A2(o.rhoS, i, j) + A3(o.Hz, i, j, k) * (A2(o.rhoA, i, j) + 0.5 * cff);
+        A2(o.rhoA, i, j) = A2(o.rhoA, i, j) + cff;
+      }
+    double cff1 = 1.0 / rho0;
+    for (int i = istr - 2; i <= iend + 2; ++i) {
+      double cff = 1.0 / (AW(o.z_w, i, j, N) - AW(o.z_w, i, j, 0));
+      A2(o.rhoA, i, j) = cff * cff1 * A2(o.rhoA, i, j);
+      A2(o.rhoS, i, j) = 2.0 * cff * cff * cff1 * A2(o.rhoS, i, j);
+    }
+  }
+}
+
+// prsgrd.F:25-510 prsgrd_tile
+void prsgrd(Orc& o) {
+  GEOM
+  const double g = o.c.g, rho0 = o.c.rho0, qp2 = 0.0000172;
+  const double OneFifth = 0.2, OneTwelfth = 1.0 / 12.0, epsil = 0.0;
+  const int imin = istr - 1, imax = iend + 1, jmin = jstr - 1, jmax = jend + 1;
+  const double grho = g / rho0, HalfGRho = 0.5 * grho;
+  const int nonlin = o.c.nonlin_eos;
+  vec& rho = nonlin ? o.rho : o.rho1;
+  vec& P = o.Pp;
+#pragma omp parallel
+  {
+    vec dR((size_t)SX * (N + 1)), dZ((size_t)SX * (N + 1));
+#pragma omp for
+    for (int j = 0; j <= Mm; ++j) {
+      for (int k = 1; k <= N - 1; ++k)
+        for (int i = 0; i <= Lm; ++i) {
+          SL(dZ, i, k) = A3(o.z_r, i, j, k + 1) - A3(o.z_r, i, j, k);
+          if (nonlin) {
+            double dpth = -0.5 * (A3(o.z_r, i, j, k + 1) + A3(o.z_r, i, j, k));
+            SL(dR, i, k) = A3(o.rho1, i, j, k + 1) - A3(o.rho1, i, j, k) + (A3(o.qp1, i, j, k + 1) - A3(o.qp1, i, j, k)) * dpth * (1.0 - qp2 * dpth);
+          } else
+            SL(dR, i, k) = A3(rho, i, j, k + 1) - A3(rho, i, j, k);
+        }
+      for (int i = 0; i <= Lm; ++i) {
+        SL(dR, i, N) = SL(dR, i, N - 1);
+        SL(dR, i, 0) = SL(dR, i, 1);
+        SL(dZ, i, N) = SL(dZ, i, N - 1);
+        SL(dZ, i, 0) = SL(dZ, i, 1);
+      }
+      for (int k = N; k >= 1; --k)
+        for (int i = 0; i <= Lm; ++i) {
+          double cff = 2.0 * SL(dZ, i, k) * SL(dZ, i, k - 1);
+          SL(dZ, i, k) = cff / (SL(dZ, i, k) + SL(dZ, i, k - 1));
+          double cfr = 2.0 * SL(dR, i, k) * SL(dR, i, k - 1);
+          if (cfr > epsil) SL(dR, i, k) = cfr / (SL(dR, i, k) + SL(dR, i, k - 1));
+          else SL(dR, i, k) = 0.0;
+          if (nonlin) {
+            double dpth = -A3(o.z_r, i, j, k);
+            SL(dR, i, k) = SL(dR, i, k) - A3(o.qp1, i, j, k) * SL(dZ, i, k) * (1.0 - 2.0 * qp2 * dpth);
+            A3(rho, i, j, k) = A3(o.rho1, i, j, k) + A3(o.qp1, i, j, k) * dpth * (1.0 - qp2 * dpth);
+          }
+        }
+      for (int i = istr - 1; i <= iend; ++i)
+        A3(P, i, j, N) = g * AW(o.z_w, i, j, N) +
+                         grho * (A3(rho, i, j, N) + 0.5 * (A3(rho, i, j, N) - A3(rho, i, j, N - 1)) * (AW(o.z_w, i, j, N) - A3(o.z_r, i, j, N)) /
+                                                        (A3(o.z_r, i, j, N) - A3(o.z_r, i, j, N - 1))) *
+                             (AW(o.z_w, i, j, N) - A3(o.z_r, i, j, N));
+      for (int k = N - 1; k >= 1; --k)
+        for (int i = istr - 1; i <= iend; ++i)
+          A3(P, i, j, k) = A3(P, i, j, k + 1) +
+                           HalfGRho * ((A3(rho, i, j, k + 1) + A3(rho, i, j, k)) * (A3(o.z_r, i, j, k + 1) - A3(o.z_r, i, j, k)) -
+                                       OneFifth * ((SL(dR, i, k + 1) - SL(dR, i, k)) * (A3(o.z_r, i, j, k + 1) - A3(o.z_r, i, j, k) - OneTwelfth * (SL(dZ, i, k + 1) + SL(dZ, i, k))) -
+                                                   (SL(dZ, i, k + 1) - SL(dZ, i, k)) * (A3(rho, i, j, k + 1) - A3(rho, i, j, k) - OneTwelfth * (SL(dR, i, k + 1) + SL(dR, i, k)))));
+    }
+  }
+#pragma omp parallel
+  {
+    vec FC(o.SXY), dZx(o.SXY), rx(o.SXY), dRx(o.SXY);
+#pragma omp for
+    for (int k = N; k >= 1; --k) {
+      for (int j = jstr; j <= jend; ++j)
+        for (int i = imin; i <= imax; ++i) {
+          A2(FC, i, j) = (A3(o.z_r, i, j, k) - A3(o.z_r, i - 1, j, k)) * A2(o.umask, i, j);
+          if (nonlin) {
+            double dpth = -0.5 * (A3(o.z_r, i, j, k) + A3(o.z_r, i - 1, j, k));
+            A2(rx, i, j) = (A3(o.rho1, i, j, k) - A3(o.rho1, i - 1, j, k) + (A3(o.qp1, i, j, k) - A3(o.qp1, i - 1, j, k)) * dpth * (1.0 - qp2 * dpth)) * A2(o.umask, i, j);
+          } else
+            A2(rx, i, j) = (A3(rho, i, j, k) - A3(rho, i - 1, j, k)) * A2(o.umask, i, j);
+        }
+      for (int j = jstr; j <= jend; ++j) {
+        for (int i = istr - 1; i <= iend; ++i) {
+          double cff = 2.0 * A2(FC, i, j) * A2(FC, i + 1, j);
+          if (cff > epsil) A2(dZx, i, j) = cff / (A2(FC, i, j) + A2(FC, i + 1, j));
+          else A2(dZx, i, j) = 0.0;
+          double cfr = 2.0 * A2(rx, i, j) * A2(rx, i + 1, j);
+          if (cfr > epsil) A2(dRx, i, j) = cfr / (A2(rx, i, j) + A2(rx, i + 1, j));
+          else A2(dRx, i, j) = 0.0;
+          if (nonlin) A2(dRx, i, j) = A2(dRx, i, j) - A3(o.qp1, i, j, k) * A2(dZx, i, j) * (1.0 + 2.0 * qp2 * A3(o.z_r, i, j, k));
+        }
+        for (int i = istr; i <= iend; ++i)
+          A3(o.ru, i, j, k) = 0.5 * (A3(o.Hz, i, j, k) + A3(o.Hz, i - 1, j, k)) * A2(o.dn_u, i, j) *
+                              (A3(P, i - 1, j, k) - A3(P, i, j, k) -
+                               HalfGRho * ((A3(rho, i, j, k) + A3(rho, i - 1, j, k)) * (A3(o.z_r, i, j, k) - A3(o.z_r, i - 1, j, k)) -
+                                           OneFifth * ((A2(dRx, i, j) - A2(dRx, i - 1, j)) * (A3(o.z_r, i, j, k) - A3(o.z_r, i - 1, j, k) - OneTwelfth * (A2(dZx, i, j) + A2(dZx, i - 1, j))) -
+                                                       (A2(dZx, i, j) - A2(dZx, i - 1, j)) * (A3(rho, i, j, k) - A3(rho, i - 1, j, k) - OneTwelfth * (A2(dRx, i, j) + A2(dRx, i - 1, j))))));
+      }
+      for (int j = jmin; j <= jmax; ++j)
+        for (int i = istr; i <= iend; ++i) {
+          A2(FC, i, j) = (A3(o.z_r, i, j, k) - A3(o.z_r, i, j - 1, k)) * A2(o.vmask, i, j);
+          if (nonlin) {
+            double dpth = -0.5 * (A3(o.z_r, i, j, k) + A3(o.z_r, i, j - 1, k));
+            A2(rx, i, j) = (A3(o.rho1, i, j, k) - A3(o.rho1, i, j - 1, k) + (A3(o.qp1, i, j, k) - A3(o.qp1, i, j - 1, k)) * dpth * (1.0 - qp2 * dpth)) * A2(o.vmask, i, j);
+          } else
+            A2(rx, i, j) = (A3(rho, i, j, k) - A3(rho, i, j - 1, k)) * A2(o.vmask, i, j);
+        }
+      for (int j = jstr - 1; j <= jend; ++j) {
+        for (int i = istr; i <= iend; ++i) {
+          double cff = 2.0 * A2(FC, i, j) * A2(FC, i, j + 1);
+          if (cff > epsil) A2(dZx, i, j) = cff / (A2(FC, i, j) + A2(FC, i, j + 1));
+          else A2(dZx, i, j) = 0.0;
+          double cfr = 2.0 * A2(rx, i, j) * A2(rx, i, j + 1);
+          if (cfr > epsil) A2(dRx, i, j) = cfr / (A2(rx, i, j) + A2(rx, i, j + 1));
+          else A2(dRx, i, j) = 0.0;
+          if (nonlin) A2(dRx, i, j) = A2(dRx, i, j) - A3(o.qp1, i, j, k) * A2(dZx, i, j) * (1.0 + 2.0 * qp2 * A3(o.z_r, i, j, k));
+        }
+        if (j >= jstr)
+          for (int i = istr; i <= iend; ++i)
+            A3(o.rv, i, j, k) = 0.5 * (A3(o.Hz, i, j, k) + A3(o.Hz, i, j - 1, k)) * A2(o.dm_v, i, j) *
+                                (A3(P, i, j - 1, k) - A3(P, i, j, k) -
+                                 HalfGRho * ((A3(rho, i, j, k) + A3(rho, i, j - 1, k)) * (A3(o.z_r, i, j, k) - A3(o.z_r, i, j - 1, k)) -
+                                             OneFifth * ((A2(dRx, i, j) - A2(dRx, i, j - 1)) * (A3(o.z_r, i, j, k) - A3(o.z_r, i, j - 1, k) - OneTwelfth * (A2(dZx, i, j) + A2(dZx, i, j - 1))) -
+                                                         (A2(dZx, i, j) - A2(dZx, i, j - 1)) * (A3(rho, i, j, k) - A3(rho, i, j - 1, k) - OneTwelfth * (A2(dRx, i, j) + A2(dRx, i, j - 1))))));
+      }
+    }
+  }
+}
+
+// compute_horiz_rhs_uv_terms.h:1-291 : Coriolis + horizontal advection of momentum for one k-plane.
+// upstream=false -> 4th-order centred (pre_step3d4S.F:178); true -> UP3 (step3d_uv1.F:124).
+void horiz_rhs_uv(Orc& o, int k, const vec& u, const vec& v, bool upstream, vec& UFx, vec& UFe, vec& VFx, vec& VFe, vec& wrk1, vec& wrk2) {
+  GEOM
+  const double delta = 0.1666666666666667, gamma = 0.3333333333333333;
+  for (int j = jstr - 1; j <= jend; ++j)
+    for (int i = istr - 1; i <= iend; ++i) {
+      double cff = 0.5 * A3(o.Hz, i, j, k) * (A2(o.fomn, i, j));
+      A2(UFx, i, j) = cff * (A3(v, i, j, k) + A3(v, i, j + 1, k));
+      A2(VFe, i, j) = cff * (A3(u, i, j, k) + A3(u, i + 1, j, k));
+    }
+  for (int j = jstr; j <= jend; ++j)
+    for (int i = istr; i <= iend; ++i) A3(o.ru, i, j, k) = A3(o.ru, i, j, k) + 0.5 * (A2(UFx, i, j) + A2(UFx, i - 1, j));
+  for (int j = jstr; j <= jend; ++j)
+    for (int i = istr; i <= iend; ++i) A3(o.rv, i, j, k) = A3(o.rv, i, j, k) - 0.5 * (A2(VFe, i, j) + A2(VFe, i, j - 1));
+  const int imin = istr - 1, imax = iend + 1, jmin = jstr - 1, jmax = jend + 1;
+  for (int j = jstr; j <= jend; ++j)
+    for (int i = imin; i <= imax; ++i) {
+      A2(wrk1, i, j) = A3(u, i - 1, j, k) - 2.0 * A3(u, i, j, k) + A3(u, i + 1, j, k);
+      A2(wrk2, i, j) = A3(o.FlxU, i - 1, j, k) - 2.0 * A3(o.FlxU, i, j, k) + A3(o.FlxU, i + 1, j, k);
+    }
+  for (int j = jstr; j <= jend; ++j)
+    for (int i = istr - 1; i <= iend; ++i) {
+      if (upstream) {
+        double cff = A3(o.FlxU, i, j, k) + A3(o.FlxU, i + 1, j, k) - delta * (A2(wrk2, i, j) + A2(wrk2, i + 1, j));
+        A2(UFx, i, j) = 0.25 * (cff * (A3(u, i, j, k) + A3(u, i + 1, j, k)) - gamma * (std::max(cff, 0.0) * A2(wrk1, i, j) + std::min(cff, 0.0) * A2(wrk1, i + 1, j)));
+      } else
+        A2(UFx, i, j) = 0.25 * (A3(u, i, j, k) + A3(u, i + 1, j, k) - delta * (A2(wrk1, i, j) + A2(wrk1, i + 1, j))) *
+                        (A3(o.FlxU, i, j, k) + A3(o.FlxU, i + 1, j, k) - delta * (A2(wrk2, i, j) + A2(wrk2, i + 1, j)));
+    }
+  for (int j = jmin; j <= jmax; ++j)
+    for (int i = istr; i <= iend; ++i) {
+      A2(wrk1, i, j) = A3(v, i, j - 1, k) - 2.0 * A3(v, i, j, k) + A3(v, i, j + 1, k);
+      A2(wrk2, i, j) = A3(o.FlxV, i, j - 1, k) - 2.0 * A3(o.FlxV, i, j, k) + A3(o.FlxV, i, j + 1, k);
+    }
+  for (int j = jstr - 1; j <= jend; ++j)
+    for (int i = istr; i <= iend; ++i) {
+      if (upstream) {
+        double cff = A3(o.FlxV, i, j, k) + A3(o.FlxV, i, j + 1, k) - delta * (A2(wrk2, i, j) + A2(wrk2, i, j + 1));
+        A2(VFe, i, j) = 0.25 * (cff * (A3(v, i, j, k) + A3(v, i, j + 1, k)) - gamma * (std::max(cff, 0.0) * A2(wrk1, i, j) + std::min(cff, 0.0) * A2(wrk1, i, j + 1)));
+      } else
+        A2(VFe, i, j) = 0.25 * (A3(v, i, j, k) + A3(v, i, j + 1, k) - delta * (A2(wrk1, i, j) + A2(wrk1, i, j + 1))) *
+                        (A3(o.FlxV, i, j, k) + A3(o.FlxV, i, j + 1, k) - delta * (A2(wrk2, i, j) + A2(wrk2, i, j + 1)));
+    }
+  for (int j = jmin; j <= jmax; ++j)
+    for (int i = istr; i <= iend; ++i) A2(wrk1, i, j) = A3(u, i, j - 1, k) - 2.0 * A3(u, i, j, k) + A3(u, i, j + 1, k);
+  for (int j = jstr; j <= jend + 1; ++j)
+    for (int i = istr - 1; i <= iend; ++i) A2(wrk2, i, j) = A3(o.FlxV, i - 1, j, k) - 2.0 * A3(o.FlxV, i, j, k) + A3(o.FlxV, i + 1, j, k);
+  for (int j = jstr; j <= jend + 1; ++j)
+    for (int i = istr; i <= iend; ++i) {
+      if (upstream) {
+        double cff = A3(o.FlxV, i, j, k) + A3(o.FlxV, i - 1, j, k) - delta * (A2(wrk2, i, j) + A2(wrk2, i - 1, j));
+        A2(UFe, i, j) = 0.25 * (cff * (A3(u, i, j, k) + A3(u, i, j - 1, k)) - gamma * (std::max(cff, 0.0) * A2(wrk1, i, j - 1) + std::min(cff, 0.0) * A2(wrk1, i, j)));
+      } else
+        A2(UFe, i, j) = 0.25 * (A3(u, i, j, k) + A3(u, i, j - 1, k) - delta * (A2(wrk1, i, j) + A2(wrk1, i, j - 1))) *
+                        (A3(o.FlxV, i, j, k) + A3(o.FlxV, i - 1, j, k) - delta * (A2(wrk2, i, j) + A2(wrk2, i - 1, j)));
+    }
+  for (int j = jstr; j <= jend; ++j)
+    for (int i = imin; i <= imax; ++i) A2(wrk1, i, j) = A3(v, i - 1, j, k) - 2.0 * A3(v, i, j, k) + A3(v, i + 1, j, k);
+  for (int j = jstr - 1; j <= jend; ++j)
+    for (int i = istr; i <= iend + 1; ++i) A2(wrk2, i, j) = A3(o.FlxU, i, j - 1, k) - 2.0 * A3(o.FlxU, i, j, k) + A3(o.FlxU, i, j + 1, k);
+  for (int j = jstr; j <= jend; ++j)
+    for (int i = istr; i <= iend + 1; ++i) {
+      if (upstream) {
+        double cff = A3(o.FlxU, i, j, k) + A3(o.FlxU, i, j - 1, k) - delta * (A2(wrk2, i, j) + A2(wrk2, i, j - 1));
+        A2(VFx, i, j) = 0.25 * (cff * (A3(v, i, j, k) + A3(v, i - 1, j, k)) - gamma * (std::max(cff, 0.0) * A2(wrk1, i - 1, j) + std::min(cff, 0.0) * A2(wrk1, i, j)));
+      } else
+        A2(VFx, i, j) = 0.25 * (A3(v, i, j, k) + A3(v, i - 1, j, k) - delta * (A2(wrk1, i, j) + A2(wrk1, i - 1, j))) *
+                        (A3(o.FlxU, i, j, k) + A3(o.FlxU, i, j - 1, k) - delta * (A2(wrk2, i, j) + A2(wrk2, i, j - 1)));
+    }
+  for (int j = jstr; j <= jend; ++j)
+    for (int i = istr; i <= iend; ++i)
+      A3(o.ru, i, j, k) = A3(o.ru, i, j, k) - A2(UFx, i, j) + A2(UFx, i - 1, j) - A2(UFe, i, j + 1) + A2(UFe, i, j);
+  for (int j = jstr; j <= jend; ++j)
+    for (int i = istr; i <= iend; ++i)
+      A3(o.rv, i, j, k) = A3(o.rv, i, j, k) - A2(VFx, i + 1, j) + A2(VFx, i, j) - A2(VFe, i, j) + A2(VFe, i, j - 1);
+}
+
+// compute_vert_rhs_uv_terms.h:1-188 (SPLINE_UV) for one j-row: adds vertical advection to ru, rv
+void vert_rhs_uv(Orc& o, int j, const vec& u, const vec& v, vec& FC, vec& CF, vec& DC) {
+  GEOM
+  for (int i = istr; i <= iend; ++i) {
+    SL(DC, i, 1) = 0.5625 * (A3(o.Hz, i, j, 1) + A3(o.Hz, i - 1, j, 1)) - 0.0625 * (A3(o.Hz, i + 1, j, 1) + A3(o.Hz, i - 2, j, 1));
+    SL(CF, i, 1) = 1.0;
+    SL(FC, i, 0) = 2.0 * A3(u, i, j, 1);
+  }
+  for (int k = 1; k <= N - 1; ++k)
+    for (int i = istr; i <= iend; ++i) {
+      SL(DC, i, k + 1) = 0.5625 * (A3(o.Hz, i, j, k + 1) + A3(o.Hz, i - 1, j, k + 1)) - 0.0625 * (A3(o.Hz, i + 1, j, k + 1) + A3(o.Hz, i - 2, j, k + 1));
+      double cff = 1.0 / (2.0 * SL(DC, i, k) + SL(DC, i, k + 1) * (2.0 - SL(CF, i, k)));
+      SL(CF, i, k + 1) = cff * SL(DC, i, k);
+      SL(FC, i, k) = cff * (3.0 * (SL(DC, i, k) * A3(u, i, j, k + 1) + SL(DC, i, k + 1) * A3(u, i, j, k)) - SL(DC, i, k + 1) * SL(FC, i, k - 1));
+    }
+  for (int i = istr; i <= iend; ++i) {
+    SL(FC, i, N) = (2.0 * A3(u, i, j, N) - SL(FC, i, N - 1)) / (1.0 - SL(CF, i, N));
+    SL(DC, i, N) = 0.0;
+  }
+  for (int k = N - 1; k >= 1; --k)
+    for (int i = istr; i <= iend; ++i) {
+      SL(FC, i, k) = SL(FC, i, k) - SL(CF, i, k + 1) * SL(FC, i, k + 1);
+      SL(DC, i, k) = SL(FC, i, k) * 0.5 * (AW(o.We, i, j, k) + AW(o.We, i - 1, j, k) -
+                                           0.125 * ((AW(o.We, i + 1, j, k) - AW(o.We, i, j, k)) * A2(o.umask, i + 1, j) -
+                                                    (AW(o.We, i - 1, j, k) - AW(o.We, i - 2, j, k)) * A2(o.umask, i - 1, j)));
+      A3(o.ru, i, j, k + 1) = A3(o.ru, i, j, k + 1) - SL(DC, i, k + 1) + SL(DC, i, k);
+    }
+  for (int i = istr; i <= iend; ++i) A3(o.ru, i, j, 1) = A3(o.ru, i, j, 1) - SL(DC, i, 1);
+  // v
+  for (int i = istr; i <= iend; ++i) {
+    SL(DC, i, 1) = 0.5625 * (A3(o.Hz, i, j, 1) + A3(o.Hz, i, j - 1, 1)) - 0.0625 * (A3(o.Hz, i, j + 1, 1) + A3(o.Hz, i, j - 2, 1));
+    SL(CF, i, 1) = 1.0;
+    SL(FC, i, 0) = 2.0 * A3(v, i, j, 1);
+  }
+  for (int k = 1; k <= N - 1; ++k)
+    for (int i = istr; i <= iend; ++i) {
+      SL(DC, i, k + 1) = 0.5625 * (A3(o.Hz, i, j, k + 1) + A3(o.Hz, i, j - 1, k + 1)) - 0.0625 * (A3(o.Hz, i, j + 1, k + 1) + A3(o.Hz, i, j - 2, k + 1));
+      double cff = 1.0 / (2.0 * SL(DC, i, k) + SL(DC, i, k + 1) * (2.0 - SL(CF, i, k)));
+      SL(CF, i, k + 1) = cff * SL(DC, i, k);
+      SL(FC, i, k) = cff * (3.0 * (SL(DC, i, k) * A3(v, i, j, k + 1) + SL(DC, i, k + 1) * A3(v, i, j, k)) - SL(DC, i, k + 1) * SL(FC, i, k - 1));
+    }
+  for (int i = istr; i <= iend; ++i) {
+    SL(FC, i, N) = (2.0 * A3(v, i, j, N) - SL(FC, i, N - 1)) / (1.0 - SL(CF, i, N));
+    SL(DC, i, N) = 0.0;
+  }
+  for (int k = N - 1; k >= 1; --k)
+    for (int i = istr; i <= iend; ++i) {
+      SL(FC, i, k) = SL(FC, i, k) - SL(CF, i, k + 1) * SL(FC, i, k + 1);
+      SL(DC, i, k) = SL(FC, i, k) * 0.5 * (AW(o.We, i, j, k) + AW(o.We, i, j - 1, k) -
+                                           0.125 * ((AW(o.We, i, j + 1, k) - AW(o.We, i, j, k)) * A2(o.vmask, i, j + 1) -
+                                                    (AW(o.We, i, j - 1, k) - AW(o.We, i, j - 2, k)) * A2(o.vmask, i, j - 1)));
+      A3(o.rv, i, j, k + 1) = A3(o.rv, i, j, k + 1) - SL(DC, i, k + 1) + SL(DC, i, k);
+    }
+  for (int i = istr; i <= iend; ++i) A3(o.rv, i, j, 1) = A3(o.rv, i, j, 1) - SL(DC, i, 1);
+}
+
+// compute_horiz_tracer_fluxes.h:1-246 for one k-plane. upstream=false: C4 (pre_step3d4S.F:154);
+// true: UP3 (step3d_t_ISO.F:196).
+void horiz_tracer_fluxes(Orc& o, int k, const vec& t, bool upstream, vec& FX, vec& FE, vec& wrk1) {
+  GEOM
+  const int imin = istr - 1, imax = iend + 1, jmin = jstr - 1, jmax = jend + 1;
+  for (int j = jstr; j <= jend; ++j)
+    for (int i = imin; i <= imax + 1; ++i) A2(FX, i, j) = (A3(t, i, j, k) - A3(t, i - 1, j, k)) * A2(o.umask, i, j);
+  if (upstream) {
+    for (int j = jstr; j <= jend; ++j)
+      for (int i = istr - 1; i <= iend + 1; ++i) A2(wrk1, i, j) = A2(FX, i + 1, j) - A2(FX, i, j);
+    for (int j = jstr; j <= jend; ++j)
+      for (int i = istr; i <= iend + 1; ++i)
+        A2(FX, i, j) = 0.5 * (A3(t, i, j, k) + A3(t, i - 1, j, k)) * A3(o.FlxU, i, j, k) -
+                       0.1666666666666666 * (A2(wrk1, i - 1, j) * std::max(A3(o.FlxU, i, j, k), 0.0) + A2(wrk1, i, j) * std::min(A3(o.FlxU, i, j, k), 0.0));
+  } else {
+    for (int j = jstr; j <= jend; ++j)
+      for (int i = istr - 1; i <= iend + 1; ++i) A2(wrk1, i, j) = 0.5 * (A2(FX, i + 1, j) + A2(FX, i, j));
+    for (int j = jstr; j <= jend; ++j)
+      for (int i = istr; i <= iend + 1; ++i)
+        A2(FX, i, j) = 0.5 * (A3(t, i, j, k) + A3(t, i - 1, j, k) - 0.3333333333333333 * (A2(wrk1, i, j) - A2(wrk1, i - 1, j))) * A3(o.FlxU, i, j, k);
+  }
+  for (int j = jmin; j <= jmax + 1; ++j)
+    for (int i = istr; i <= iend; ++i) A2(FE, i, j) = (A3(t, i, j, k) - A3(t, i, j - 1, k)) * A2(o.vmask, i, j);
+  if (upstream) {
+    for (int j = jstr - 1; j <= jend + 1; ++j)
+      for (int i = istr; i <= iend; ++i) A2(wrk1, i, j) = A2(FE, i, j + 1) - A2(FE, i, j);
+    for (int j = jstr; j <= jend + 1; ++j)
+      for (int i = istr; i <= iend; ++i)
+        A2(FE, i, j) = 0.5 * (A3(t, i, j, k) + A3(t, i, j - 1, k)) * A3(o.FlxV, i, j, k) -
+                       0.1666666666666666 * (A2(wrk1, i, j - 1) * std::max(A3(o.FlxV, i, j, k), 0.0) + A2(wrk1, i, j) * std::min(A3(o.FlxV, i, j, k), 0.0));
+  } else {
+    for (int j = jstr - 1; j <= jend + 1; ++j)
+      for (int i = istr; i <= iend; ++i) A2(wrk1, i, j) = 0.5 * (A2(FE, i, j + 1) + A2(FE, i, j));
+    for (int j = jstr; j <= jend + 1; ++j)
+      for (int i = istr; i <= iend; ++i)
+        A2(FE, i, j) = 0.5 * (A3(t, i, j, k) + A3(t, i, j - 1, k) - 0.3333333333333333 * (A2(wrk1, i, j) - A2(wrk1, i, j - 1))) * A3(o.FlxV, i, j, k);
+  }
+}
+
+// compute_vert_tracer_fluxes.h:1-140 (SPLINE_TS) for one j-row: FC(i,k) = vertical flux, k=0:N
+void vert_tracer_flux(Orc& o, int j, const vec& t, vec& FC, vec& CF) {
+  GEOM
+  for (int i = istr; i <= iend; ++i) {
+    SL(CF, i, 1) = 1.0;
+    SL(FC, i, 0) = 2.0 * A3(t, i, j, 1);
+  }
+  for (int k = 1; k <= N - 1; ++k)
+    for (int i = istr; i <= iend; ++i) {
+      double cff = 1.0 / (2.0 * A3(o.Hz, i, j, k) + A3(o.Hz, i, j, k + 1) * (2.0 - SL(CF, i, k)));
+      SL(CF, i, k + 1) = cff * A3(o.Hz, i, j, k);
+      SL(FC, i, k) = cff * (3.0 * (A3(o.Hz, i, j, k) * A3(t, i, j, k + 1) + A3(o.Hz, i, j, k + 1) * A3(t, i, j, k)) - A3(o.Hz, i, j, k + 1) * SL(FC, i, k - 1));
+    }
+  for (int i = istr; i <= iend; ++i) SL(FC, i, N) = (2.0 * A3(t, i, j, N) - SL(FC, i, N - 1)) / (1.0 - SL(CF, i, N));
+  for (int k = N - 1; k >= 0; --k)
+    for (int i = istr; i <= iend; ++i) {
+      SL(FC, i, k) = SL(FC, i, k) - SL(CF, i, k + 1) * SL(FC, i, k + 1);
+      SL(FC, i, k + 1) = SL(FC, i, k + 1) * AW(o.We, i, j, k + 1);
+    }
+  for (int i = istr; i <= iend; ++i) {
+    SL(FC, i, N) = 0.0;
+    SL(FC, i, 0) = 0.0;
+  }
+}
+
+// pre_step3d4S.F:23-742 pre_step3d_tile
+void pre_step3d(Orc& o) {
+  GEOM
+  const int NT = o.NT;
+  const int nstp = o.nstp, nrhs = o.nrhs, nnew = o.nnew;
+  const int indx = 3 - nstp;
+  const double dt = o.c.dt;
+  const double AM3_crv = 1.0 / 6.0;
+  double dtau, cf_stp, cf_bak;
+  if (o.iic == o.forw_start) {
+    dtau = 0.5 * dt; cf_stp = 1.0; cf_bak = 0.0;
+  } else {
+    dtau = dt * (1.0 - AM3_crv); cf_stp = 0.5 + AM3_crv; cf_bak = 0.5 - AM3_crv;
+  }
+  vec& Hz_bak = o.Hz_bak;
+  vec& Hz_fwd = o.Hz_fwd;
+  const vec& u_rhs = o.u[nrhs - 1];
+  const vec& v_rhs = o.v[nrhs - 1];
+  vec r_D_prv(o.SXY, 0.0);
+#pragma omp parallel
+  {
+    vec UFx(o.SXY), UFe(o.SXY), VFx(o.SXY), VFe(o.SXY), wrk1(o.SXY), wrk2(o.SXY);
+#pragma omp for
+    for (int k = 1; k <= N; ++k) {
+      double cff = 0.5 * dtau;
+      for (int j = jstr - 1; j <= jend; ++j)
+        for (int i = istr - 1; i <= iend; ++i) {
+          double FlxDiv = cff * A2(o.pm, i, j) * A2(o.pn, i, j) *
+                          (A3(o.FlxU, i + 1, j, k) - A3(o.FlxU, i, j, k) + A3(o.FlxV, i, j + 1, k) - A3(o.FlxV, i, j, k) +
+                           AW(o.We, i, j, k) + AW(o.Wi, i, j, k) - AW(o.We, i, j, k - 1) - AW(o.Wi, i, j, k - 1));
+          A3(Hz_bak, i, j, k) = A3(o.Hz, i, j, k) + FlxDiv;
+          A3(Hz_fwd, i, j, k) = A3(o.Hz, i, j, k) - FlxDiv;
+        }
+      for (int itrc = 0; itrc < NT; ++itrc) {
+        horiz_tracer_fluxes(o, k, o.t[nrhs - 1][itrc], false, UFx, VFe, wrk1);
+        vec& tn = o.t[nnew - 1][itrc];
+        vec& ts = o.t[nstp - 1][itrc];
+        vec& ti = o.t[indx - 1][itrc];
+        for (int j = jstr; j <= jend; ++j)
+          for (int i = istr; i <= iend; ++i) {
+            A3(tn, i, j, k) = A3(Hz_bak, i, j, k) * (cf_stp * A3(ts, i, j, k) + cf_bak * A3(ti, i, j, k)) -
+                              dtau * A2(o.pm, i, j) * A2(o.pn, i, j) * (A2(UFx, i + 1, j) - A2(UFx, i, j) + A2(VFe, i, j + 1) - A2(VFe, i, j));
+            A3(ti, i, j, k) = A3(o.Hz, i, j, k) * A3(ts, i, j, k);
+          }
+      }
+      horiz_rhs_uv(o, k, u_rhs, v_rhs, false, UFx, UFe, VFx, VFe, wrk1, wrk2);
+    }
+  }
+  // compute_rd_bott_drag.h:1-74
+  {
+    const vec& us = o.u[nstp - 1];
+    const vec& vs = o.v[nstp - 1];
+    const double vonKar = 0.41;
+    if (o.c.Zob > 0.0) {
+      for (int j = jstr - 1; j <= jend; ++j)
+        for (int i = istr - 1; i <= iend; ++i) {
+          double cff = sqrt(0.333333333333 * (A3(us, i, j, 1) * A3(us, i, j, 1) + A3(us, i + 1, j, 1) * A3(us, i + 1, j, 1) + A3(us, i, j, 1) * A3(us, i + 1, j, 1) +
+                                              A3(vs, i, j, 1) * A3(vs, i, j, 1) + A3(vs, i, j + 1, 1) * A3(vs, i, j + 1, 1) + A3(vs, i, j, 1) * A3(vs, i, j + 1, 1)));
+          double lg = vonKar / log(1.0 + 0.5 * A3(o.Hz, i, j, 1) / o.c.Zob);
+          A2(r_D_prv, i, j) = cff * (lg * lg);
+        }
+    } else {
+      for (int j = jstr - 1; j <= jend; ++j)
+        for (int i = istr - 1; i <= iend; ++i) {
+          A2(r_D_prv, i, j) = o.c.rdrg;
+          A2(r_D_prv, i, j) = std::min(A2(r_D_prv, i, j), 0.8 * A3(o.Hz, i, j, 1) / dt);
+        }
+    }
+    for (int j = jstr - 1; j <= jend; ++j)
+      for (int i = istr - 1; i <= iend; ++i) A2(o.r_D, i, j) = A2(r_D_prv, i, j);
+  }
+  const vec& wrk1 = r_D_prv;
+#pragma omp parallel
+  {
+    vec WC((size_t)SX * (N + 1)), FC((size_t)SX * (N + 1)), CF((size_t)SX * (N + 1)), DC((size_t)SX * (N + 1));
+#pragma omp for
+    for (int j = jstr; j <= jend; ++j) {
+      for (int itrc = 0; itrc < NT; ++itrc) {
+        vec& tn = o.t[nnew - 1][itrc];
+        vert_tracer_flux(o, j, o.t[nrhs - 1][itrc], FC, CF);
+        for (int k = 1; k <= N; ++k)
+          for (int i = istr; i <= iend; ++i) A3(tn, i, j, k) = A3(tn, i, j, k) - dtau * A2(o.pm, i, j) * A2(o.pn, i, j) * (SL(FC, i, k) - SL(FC, i, k - 1));
+        const vec& Akt = o.Akt[std::min(itrc, 1)];
+        for (int i = istr; i <= iend; ++i) {
+          SL(FC, i, 1) = 2.0 * dtau * AW(Akt, i, j, 1) / (A3(Hz_fwd, i, j, 2) + A3(Hz_fwd, i, j, 1));
+          SL(DC, i, 0) = dtau * A2(o.pm, i, j) * A2(o.pn, i, j);
+          SL(WC, i, 1) = SL(DC, i, 0) * AW(o.Wi, i, j, 1);
+          double cff = 1.0 / (A3(Hz_fwd, i, j, 1) + SL(FC, i, 1) + std::max(SL(WC, i, 1), 0.0));
+          SL(CF, i, 1) = cff * (SL(FC, i, 1) - std::min(SL(WC, i, 1), 0.0));
+          SL(DC, i, 1) = cff * A3(tn, i, j, 1);
+        }
+        for (int k = 2; k <= N - 1; ++k)
+          for (int i = istr; i <= iend; ++i) {
+            SL(FC, i, k) = 2.0 * dtau * AW(Akt, i, j, k) / (A3(Hz_fwd, i, j, k + 1) + A3(Hz_fwd, i, j, k));
+            SL(WC, i, k) = SL(DC, i, 0) * AW(o.Wi, i, j, k);
+            double cff = 1.0 / (A3(Hz_fwd, i, j, k) + SL(FC, i, k) + std::max(SL(WC, i, k), 0.0) + SL(FC, i, k - 1) - std::min(SL(WC, i, k - 1), 0.0) -
+                                SL(CF, i, k - 1) * (SL(FC, i, k - 1) + std::max(SL(WC, i, k - 1), 0.0)));
+            SL(CF, i, k) = cff * (SL(FC, i, k) - std::min(SL(WC, i, k), 0.0));
+            SL(DC, i, k) = cff * (A3(tn, i, j, k) + SL(DC, i, k - 1) * (SL(FC, i, k - 1) + std::max(SL(WC, i, k - 1), 0.0)));
+          }
+        for (int i = istr; i <= iend; ++i)
+          A3(tn, i, j, N) = (A3(tn, i, j, N) + SL(DC, i, N - 1) * (SL(FC, i, N - 1) + std::max(SL(WC, i, N - 1), 0.0))) /
+                            (A3(Hz_fwd, i, j, N) + SL(FC, i, N - 1) - std::min(SL(WC, i, N - 1), 0.0) - SL(CF, i, N - 1) * (SL(FC, i, N - 1) + std::max(SL(WC, i, N - 1), 0.0)));
+        for (int k = N - 1; k >= 1; --k)
+          for (int i = istr; i <= iend; ++i) A3(tn, i, j, k) = SL(DC, i, k) + SL(CF, i, k) * A3(tn, i, j, k + 1);
+      }
+      vert_rhs_uv(o, j, u_rhs, v_rhs, FC, CF, DC);
+      // u: implicit vertical viscosity/advection, pre_step3d4S.F:362-424
+      for (int dir = 0; dir < 2; ++dir) {
+        const int di = dir == 0 ? 1 : 0, dj = dir == 0 ? 0 : 1;
+        vec& un = dir == 0 ? o.u[nnew - 1] : o.v[nnew - 1];
+        vec& us = dir == 0 ? o.u[nstp - 1] : o.v[nstp - 1];
+        vec& ui = dir == 0 ? o.u[indx - 1] : o.v[indx - 1];
+        vec& r = dir == 0 ? o.ru : o.rv;
+        const vec& strs = dir == 0 ? o.sustr : o.svstr;
+        for (int i = istr; i <= iend; ++i)
+          SL(DC, i, 0) = dtau * 0.25 * (A2(o.pm, i, j) + A2(o.pm, i - di, j - dj)) * (A2(o.pn, i, j) + A2(o.pn, i - di, j - dj));
+        for (int k = 1; k <= N; ++k)
+          for (int i = istr; i <= iend; ++i) {
+            SL(DC, i, k) = 0.5 * (A3(Hz_bak, i, j, k) + A3(Hz_bak, i - di, j - dj, k)) * (cf_stp * A3(us, i, j, k) + cf_bak * A3(ui, i, j, k)) + SL(DC, i, 0) * A3(r, i, j, k);
+            A3(ui, i, j, k) = 0.5 * (A3(o.Hz, i, j, k) + A3(o.Hz, i - di, j - dj, k)) * A3(us, i, j, k);
+          }
+        for (int i = istr; i <= iend; ++i) {
+          SL(FC, i, N - 1) = 2.0 * dtau * (AW(o.Akv, i, j, N - 1) + AW(o.Akv, i - di, j - dj, N - 1)) /
+                             (A3(Hz_fwd, i, j, N) + A3(Hz_fwd, i - di, j - dj, N) + A3(Hz_fwd, i, j, N - 1) + A3(Hz_fwd, i - di, j - dj, N - 1));
+          SL(WC, i, N - 1) = SL(DC, i, 0) * 0.5 * (AW(o.Wi, i, j, N - 1) + AW(o.Wi, i - di, j - dj, N - 1));
+          double cff = 1.0 / (0.5 * (A3(Hz_fwd, i, j, N) + A3(Hz_fwd, i - di, j - dj, N)) + SL(FC, i, N - 1) - std::min(SL(WC, i, N - 1), 0.0));
+          SL(CF, i, N - 1) = cff * (SL(FC, i, N - 1) + std::max(SL(WC, i, N - 1), 0.0));
+          SL(DC, i, N) = cff * (SL(DC, i, N) + dtau * A2(strs, i, j));
+        }
+        for (int k = N - 1; k >= 2; --k)
+          for (int i = istr; i <= iend; ++i) {
+            SL(FC, i, k - 1) = 2.0 * dtau * (AW(o.Akv, i, j, k - 1) + AW(o.Akv, i - di, j - dj, k - 1)) /
+                               (A3(Hz_fwd, i, j, k) + A3(Hz_fwd, i - di, j - dj, k) + A3(Hz_fwd, i, j, k - 1) + A3(Hz_fwd, i - di, j - dj, k - 1));
+            SL(WC, i, k - 1) = SL(DC, i, 0) * 0.5 * (AW(o.Wi, i, j, k - 1) + AW(o.Wi, i - di, j - dj, k - 1));
+            double cff = 1.0 / (0.5 * (A3(Hz_fwd, i, j, k) + A3(Hz_fwd, i - di, j - dj, k)) + SL(FC, i, k - 1) - std::min(SL(WC, i, k - 1), 0.0) + SL(FC, i, k) +
+                                std::max(SL(WC, i, k), 0.0) - SL(CF, i, k) * (SL(FC, i, k) - std::min(SL(WC, i, k), 0.0)));
+            SL(CF, i, k - 1) = cff * (SL(FC, i, k - 1) + std::max(SL(WC, i, k - 1), 0.0));
+            SL(DC, i, k) = cff * (SL(DC, i, k) + SL(DC, i, k + 1) * (SL(FC, i, k) - std::min(SL(WC, i, k), 0.0)));
+          }
+        for (int i = istr; i <= iend; ++i)
+          A3(un, i, j, 1) = (SL(DC, i, 1) + SL(DC, i, 2) * (SL(FC, i, 1) - std::min(SL(WC, i, 1), 0.0))) /
+                            (0.5 * (A3(Hz_fwd, i, j, 1) + A3(Hz_fwd, i - di, j - dj, 1)) + 0.5 * dtau * (A2(wrk1, i, j) + A2(wrk1, i - di, j - dj)) + SL(FC, i, 1) +
+                             std::max(SL(WC, i, 1), 0.0) - SL(CF, i, 1) * (SL(FC, i, 1) - std::min(SL(WC, i, 1), 0.0)));
+        for (int k = 2; k <= N; ++k)
+          for (int i = istr; i <= iend; ++i) A3(un, i, j, k) = SL(DC, i, k) + SL(CF, i, k - 1) * A3(un, i, j, k - 1);
+      }
+    }
+  }
+  for (int itrc = 0; itrc < NT; ++itrc) ex3(o, o.t[nnew - 1][itrc]);
+}
+
+// step3d_uv1.F:23-534 step3d_uv1_tile
+void step3d_uv1(Orc& o) {
+  GEOM
+  const int nrhs = o.nrhs, nnew = o.nnew;
+  const double dt = o.c.dt;
+  const vec& u_rhs = o.u[nrhs - 1];
+  const vec& v_rhs = o.v[nrhs - 1];
+#pragma omp parallel
+  {
+    vec UFx(o.SXY), UFe(o.SXY), VFx(o.SXY), VFe(o.SXY), wrk1(o.SXY), wrk2(o.SXY);
+#pragma omp for
+    for (int k = 1; k <= N; ++k) horiz_rhs_uv(o, k, u_rhs, v_rhs, true, UFx, UFe, VFx, VFe, wrk1, wrk2);
+  }
+#pragma omp parallel
+  {
+    vec WC((size_t)SX * (N + 1)), FC((size_t)SX * (N + 1)), CF((size_t)SX * (N + 1)), DC((size_t)SX * (N + 1));
+#pragma omp for
+    for (int j = jstr; j <= jend; ++j) {
+      vert_rhs_uv(o, j, u_rhs, v_rhs, FC, CF, DC);
+      for (int dir = 0; dir < 2; ++dir) {
+        const int di = dir == 0 ? 1 : 0, dj = dir == 0 ? 0 : 1;
+        vec& un = dir == 0 ? o.u[nnew - 1] : o.v[nnew - 1];
+        vec& r = dir == 0 ? o.ru : o.rv;
+        vec& rfrc = dir == 0 ? o.rufrc : o.rvfrc;
+        const vec& strs = dir == 0 ? o.sustr : o.svstr;
+        const vec& dmx = dir == 0 ? o.dm_u : o.dm_v;
+        const vec& dnx = dir == 0 ? o.dn_u : o.dn_v;
+        for (int i = istr; i <= iend; ++i) {
+          SL(DC, i, 0) = dt * 0.25 * (A2(o.pm, i, j) + A2(o.pm, i - di, j - dj)) * (A2(o.pn, i, j) + A2(o.pn, i - di, j - dj));
+          SL(FC, i, N - 1) = 2.0 * dt * (AW(o.Akv, i, j, N - 1) + AW(o.Akv, i - di, j - dj, N - 1)) /
+                             (A3(o.Hz, i, j, N) + A3(o.Hz, i - di, j - dj, N) + A3(o.Hz, i, j, N - 1) + A3(o.Hz, i - di, j - dj, N - 1));
+          SL(WC, i, N - 1) = SL(DC, i, 0) * 0.5 * (AW(o.Wi, i, j, N - 1) + AW(o.Wi, i - di, j - dj, N - 1));
+          double cff = 1.0 / (0.5 * (A3(o.Hz, i, j, N) + A3(o.Hz, i - di, j - dj, N)) + SL(FC, i, N - 1) - std::min(SL(WC, i, N - 1), 0.0));
+          SL(CF, i, N - 1) = cff * (SL(FC, i, N - 1) + std::max(SL(WC, i, N - 1), 0.0));
+          SL(DC, i, N) = cff * (A3(un, i, j, N) + SL(DC, i, 0) * A3(r, i, j, N) + dt * A2(strs, i, j));
+        }
+        for (int k = N - 1; k >= 2; --k)
+          for (int i = istr; i <= iend; ++i) {
+            SL(FC, i, k - 1) = 2.0 * dt * (AW(o.Akv, i, j, k - 1) + AW(o.Akv, i - di, j - dj, k - 1)) /
+                               (A3(o.Hz, i, j, k) + A3(o.Hz, i - di, j - dj, k) + A3(o.Hz, i, j, k - 1) + A3(o.Hz, i - di, j - dj, k - 1));
+            SL(WC, i, k - 1) = SL(DC, i, 0) * 0.5 * (AW(o.Wi, i, j, k - 1) + AW(o.Wi, i - di, j - dj, k - 1));
+            double cff = 1.0 / (0.5 * (A3(o.Hz, i, j, k) + A3(o.Hz, i - di, j - dj, k)) + SL(FC, i, k - 1) - std::min(SL(WC, i, k - 1), 0.0) + SL(FC, i, k) +
+                                std::max(SL(WC, i, k), 0.0) - SL(CF, i, k) * (SL(FC, i, k) - std::min(SL(WC, i, k), 0.0)));
+            SL(CF, i, k - 1) = cff * (SL(FC, i, k - 1) + std::max(SL(WC, i, k - 1), 0.0));
+            SL(DC, i, k) = cff * (A3(un, i, j, k) + SL(DC, i, 0) * A3(r, i, j, k) + SL(DC, i, k + 1) * (SL(FC, i, k) - std::min(SL(WC, i, k), 0.0)));
+          }
+        for (int i = istr; i <= iend; ++i) {
+          SL(DC, i, 1) = (A3(un, i, j, 1) + SL(DC, i, 0) * A3(r, i, j, 1) + SL(DC, i, 2) * (SL(FC, i, 1) - std::min(SL(WC, i, 1), 0.0))) /
+                         (0.5 * (A3(o.Hz, i, j, 1) + A3(o.Hz, i - di, j - dj, 1)) + 0.5 * dt * (A2(o.r_D, i, j) + A2(o.r_D, i - di, j - dj)) + SL(FC, i, 1) +
+                          std::max(SL(WC, i, 1), 0.0) - SL(CF, i, 1) * (SL(FC, i, 1) - std::min(SL(WC, i, 1), 0.0)));
+          A3(un, i, j, 1) = SL(DC, i, 1) * 0.5 * (A3(o.Hz, i, j, 1) + A3(o.Hz, i - di, j - dj, 1));
+          A2(rfrc, i, j) = A3(r, i, j, 1) + A2(dmx, i, j) * A2(dnx, i, j) * (A2(strs, i, j) - 0.5 * (A2(o.r_D, i - di, j - dj) + A2(o.r_D, i, j)) * SL(DC, i, 1));
+        }
+        for (int k = 2; k <= N; ++k)
+          for (int i = istr; i <= iend; ++i) {
+            SL(DC, i, k) = SL(DC, i, k) + SL(CF, i, k - 1) * SL(DC, i, k - 1);
+            A3(un, i, j, k) = SL(DC, i, k) * 0.5 * (A3(o.Hz, i, j, k) + A3(o.Hz, i - di, j - dj, k));
+            A2(rfrc, i, j) = A2(rfrc, i, j) + A3(r, i, j, k);
+          }
+      }
+    }
+  }
+}
+
+// step2d_FB.F:24-576 step2d_FB_tile
+void step2d(Orc& o) {
+  GEOM
+  const int iif = o.iif, kstp = o.kstp, knew = o.knew;
+  const double dtfast = o.dtfast, g = o.c.g;
+  int kbak, kold;
+  double fwd, fwd1, fwd2, bkw_new, bkw, bkw1, bkw2;
+  if (iif == 1) {
+    kbak = kstp; kold = kstp;
+    fwd = 1.0; fwd1 = 0.0; fwd2 = 0.0;
+    bkw_new = 0.0; bkw = 1.0; bkw1 = 0.0; bkw2 = 0.0;
+  } else if (iif == 1 + 1) {
+    kbak = kstp - 1; if (kbak < 1) kbak = 4;
+    kold = kbak;
+    fwd = 1.0; fwd1 = 0.0; fwd2 = 0.0;
+    bkw_new = 1.0833333333333; bkw = -0.1666666666666; bkw1 = 0.0833333333333; bkw2 = 0.0;
+  } else {
+    kbak = kstp - 1; if (kbak < 1) kbak = 4;
+    kold = kbak - 1; if (kold < 1) kold = 4;
+    fwd = 1.781105; fwd1 = -1.06221; fwd2 = 0.281105;
+    bkw_new = 0.614; bkw = 0.285; bkw1 = 0.088; bkw2 = 0.013;
+  }
+  const vec &zs = o.zeta[kstp - 1], &zb = o.zeta[kbak - 1], &zo = o.zeta[kold - 1];
+  const vec &us = o.ubar[kstp - 1], &ub = o.ubar[kbak - 1], &uo = o.ubar[kold - 1];
+  const vec &vs = o.vbar[kstp - 1], &vb = o.vbar[kbak - 1], &vo = o.vbar[kold - 1];
+  vec &zn = o.zeta[knew - 1], &un = o.ubar[knew - 1], &vn = o.vbar[knew - 1];
+  if (o.s2d.size() != 13) o.s2d.assign(13, vec(o.SXY, 0.0));   // the reference's A2d(1,1:13), step2d_FB.F:18-21
+  vec &zeta_new = o.s2d[0], &Dnew = o.s2d[1], &rubar = o.s2d[2], &rvbar = o.s2d[3], &urhs = o.s2d[4], &vrhs = o.s2d[5], &DUon = o.s2d[6],
+      &DVom = o.s2d[7], &Drhs = o.s2d[8], &UFx = o.s2d[9], &UFe = o.s2d[10], &VFx = o.s2d[11], &VFe = o.s2d[12];
+#pragma omp parallel for
+  for (int j = jstr - 2; j <= jend + 1; ++j)
+    for (int i = istr - 2; i <= iend + 1; ++i) A2(Drhs, i, j) = A2(o.h, i, j) + fwd * A2(zs, i, j) + fwd1 * A2(zb, i, j) + fwd2 * A2(zo, i, j);
+#pragma omp parallel for
+  for (int j = jstr - 1; j <= jend + 1; ++j) {
+    for (int i = istr - 1; i <= iend + 1; ++i) {
+      A2(urhs, i, j) = fwd * A2(us, i, j) + fwd1 * A2(ub, i, j) + fwd2 * A2(uo, i, j);
+      A2(DUon, i, j) = 0.5 * (A2(Drhs, i, j) + A2(Drhs, i - 1, j)) * A2(o.dn_u, i, j) * (A2(urhs, i, j));
+    }
+    for (int i = istr - 1; i <= iend + 1; ++i) {
+      A2(vrhs, i, j) = fwd * A2(vs, i, j) + fwd1 * A2(vb, i, j) + fwd2 * A2(vo, i, j);
+      A2(DVom, i, j) = 0.5 * (A2(Drhs, i, j) + A2(Drhs, i, j - 1)) * A2(o.dm_v, i, j) * (A2(vrhs, i, j));
+    }
+  }
+#pragma omp parallel for
+  for (int j = jstr - 1; j <= jend; ++j)
+    for (int i = istr - 1; i <= iend; ++i) {
+      A2(zeta_new, i, j) = A2(zs, i, j) + dtfast * A2(o.pm, i, j) * A2(o.pn, i, j) * (A2(DUon, i, j) - A2(DUon, i + 1, j) + A2(DVom, i, j) - A2(DVom, i, j + 1)) +
+                           dtfast * A2(o.swflx, i, j);
+      A2(zeta_new, i, j) = A2(zeta_new, i, j) * A2(o.rmask, i, j);
+      A2(Dnew, i, j) = A2(zeta_new, i, j) + A2(o.h, i, j);
+      A2(UFx, i, j) = bkw_new * A2(zeta_new, i, j) + bkw * A2(zs, i, j) + bkw1 * A2(zb, i, j) + bkw2 * A2(zo, i, j);
+      A2(UFe, i, j) = (1.0 + A2(o.rhoS, i, j)) * A2(UFx, i, j);
+      A2(VFx, i, j) = A2(UFx, i, j) * (A2(o.rhoS, i, j) - A2(o.rhoA, i, j));
+      A2(VFe, i, j) = A2(UFe, i, j) * A2(UFx, i, j);
+    }
+  // zetabc_tile: nothing to do on periodic edges (zetabc.F, compiled out)
+  for (int j = jstr; j <= jend; ++j)
+    for (int i = istr; i <= iend; ++i) A2(zn, i, j) = A2(zeta_new, i, j);
+  double cff1 = o.weight1[iif], cff2 = o.weight2[iif];
+  if (iif == 1) {
+    for (int j = jstr; j <= jend; ++j)
+      for (int i = istr; i <= iend; ++i) {
+        A2(o.DU_avg_bak, i, j) = A2(o.DU_avg1, i, j) - 0.1024390243902439 * A2(o.DU_avg2, i, j);
+        A2(o.DV_avg_bak, i, j) = A2(o.DV_avg1, i, j) - 0.1024390243902439 * A2(o.DV_avg2, i, j);
+        A2(o.Zt_avg1, i, j) = cff1 * A2(zn, i, j);
+        A2(o.DU_avg1, i, j) = 0.0;
+        A2(o.DV_avg1, i, j) = 0.0;
+        A2(o.DU_avg2, i, j) = cff2 * A2(DUon, i, j);
+        A2(o.DV_avg2, i, j) = cff2 * A2(DVom, i, j);
+      }
+  } else {
+    for (int j = jstr; j <= jend; ++j)
+      for (int i = istr; i <= iend; ++i) {
+        A2(o.Zt_avg1, i, j) = A2(o.Zt_avg1, i, j) + cff1 * A2(zn, i, j);
+        A2(o.DU_avg2, i, j) = A2(o.DU_avg2, i, j) + cff2 * A2(DUon, i, j);
+        A2(o.DV_avg2, i, j) = A2(o.DV_avg2, i, j) + cff2 * A2(DVom, i, j);
+      }
+  }
+  double cff = 0.5 * g;
+#pragma omp parallel for
+  for (int j = jstr; j <= jend; ++j)
+    for (int i = istr; i <= iend; ++i) {
+      A2(rubar, i, j) = cff * A2(o.dn_u, i, j) *
+                        ((A2(o.h, i - 1, j) + A2(o.h, i, j)) * (A2(UFe, i - 1, j) - A2(UFe, i, j)) + A2(VFe, i - 1, j) - A2(VFe, i, j) +
+                         (A2(o.h, i - 1, j) - A2(o.h, i, j)) * (A2(VFx, i - 1, j) + A2(VFx, i, j) + 0.333333333333 * (A2(o.rhoA, i - 1, j) - A2(o.rhoA, i, j)) * (A2(UFx, i - 1, j) - A2(UFx, i, j))));
+      A2(rvbar, i, j) = cff * A2(o.dm_v, i, j) *
+                        ((A2(o.h, i, j - 1) + A2(o.h, i, j)) * (A2(UFe, i, j - 1) - A2(UFe, i, j)) + A2(VFe, i, j - 1) - A2(VFe, i, j) +
+                         (A2(o.h, i, j - 1) - A2(o.h, i, j)) * (A2(VFx, i, j - 1) + A2(VFx, i, j) + 0.333333333333 * (A2(o.rhoA, i, j - 1) - A2(o.rhoA, i, j)) * (A2(UFx, i, j - 1) - A2(UFx, i, j))));
+    }
+  if (iif == 1) {
+    for (int j = jstr; j <= jend; ++j)
+      for (int i = istr; i <= iend; ++i) {
+        A2(o.rufrc, i, j) = A2(o.rufrc, i, j) - A2(rubar, i, j);
+        A2(o.rvfrc, i, j) = A2(o.rvfrc, i, j) - A2(rvbar, i, j);
+      }
+    for (int j = jstr - 1; j <= jend; ++j)
+      for (int i = istr - 1; i <= iend; ++i) {
+        A2(UFx, i, j) = A2(zeta_new, i, j) - A2(zs, i, j);
+        A2(UFe, i, j) = (1.0 + A2(o.rhoS, i, j)) * A2(UFx, i, j);
+        A2(VFe, i, j) = A2(UFe, i, j) * (A2(zeta_new, i, j) + A2(zs, i, j));
+        A2(VFx, i, j) = A2(UFx, i, j) * (A2(o.rhoS, i, j) - A2(o.rhoA, i, j));
+      }
+    cff = 0.5 * g;
+    for (int j = jstr; j <= jend; ++j)
+      for (int i = istr; i <= iend; ++i) {
+        A2(rubar, i, j) = A2(rubar, i, j) +
+                          cff * A2(o.dn_u, i, j) *
+                              ((A2(o.h, i - 1, j) + A2(o.h, i, j)) * (A2(UFe, i - 1, j) - A2(UFe, i, j)) + A2(VFe, i - 1, j) - A2(VFe, i, j) +
+                               (A2(o.h, i - 1, j) - A2(o.h, i, j)) * (A2(VFx, i - 1, j) + A2(VFx, i, j) + 0.333333333333 * (A2(o.rhoA, i - 1, j) - A2(o.rhoA, i, j)) * (A2(UFx, i - 1, j) - A2(UFx, i, j))));
+        A2(rvbar, i, j) = A2(rvbar, i, j) +
+                          cff * A2(o.dm_v, i, j) *
+                              ((A2(o.h, i, j - 1) + A2(o.h, i, j)) * (A2(UFe, i, j - 1) - A2(UFe, i, j)) + A2(VFe, i, j - 1) - A2(VFe, i, j) +
+                               (A2(o.h, i, j - 1) - A2(o.h, i, j)) * (A2(VFx, i, j - 1) + A2(VFx, i, j) + 0.333333333333 * (A2(o.rhoA, i, j - 1) - A2(o.rhoA, i, j)) * (A2(UFx, i, j - 1) - A2(UFx, i, j))));
+      }
+  }
+  for (int j = jstr - 1; j <= jend; ++j)
+    for (int i = istr - 1; i <= iend; ++i) A2(DUon, i, j) = A2(zs, i, j) + A2(o.h, i, j);
+  cff = 0.5 * dtfast;
+  cff1 = 0.5 * o.weight1[iif];
+#pragma omp parallel for
+  for (int j = jstr; j <= jend; ++j) {
+    for (int i = istr; i <= iend; ++i) {
+      double DUnew = ((A2(DUon, i, j) + A2(DUon, i - 1, j)) * A2(us, i, j) +
+                      cff * (A2(o.pm, i, j) + A2(o.pm, i - 1, j)) * (A2(o.pn, i, j) + A2(o.pn, i - 1, j)) * (A2(rubar, i, j) + A2(o.rufrc, i, j))) *
+                     A2(o.umask, i, j);
+      A2(un, i, j) = DUnew / (A2(Dnew, i, j) + A2(Dnew, i - 1, j));
+      A2(o.DU_avg1, i, j) = A2(o.DU_avg1, i, j) + cff1 * A2(o.dn_u, i, j) * (DUnew);
+    }
+    for (int i = istr; i <= iend; ++i) {
+      double DVnew = ((A2(DUon, i, j) + A2(DUon, i, j - 1)) * A2(vs, i, j) +
+                      cff * (A2(o.pm, i, j) + A2(o.pm, i, j - 1)) * (A2(o.pn, i, j) + A2(o.pn, i, j - 1)) * (A2(rvbar, i, j) + A2(o.rvfrc, i, j))) *
+                     A2(o.vmask, i, j);
+      A2(vn, i, j) = DVnew / (A2(Dnew, i, j) + A2(Dnew, i, j - 1));
+      A2(o.DV_avg1, i, j) = A2(o.DV_avg1, i, j) + cff1 * A2(o.dm_v, i, j) * (DVnew);
+    }
+  }
+  // u2dbc_tile / v2dbc_tile: nothing on periodic edges
+  if (iif == o.nfast) {
+    for (int j = jstr; j <= jend; ++j)
+      for (int i = istr; i <= iend; ++i) A2(zn, i, j) = A2(o.Zt_avg1, i, j);
+    set_depth(o);
+  }
+  ex2(o, zn); ex2(o, un); ex2(o, vn);
+}
+
+// step3d_uv2.F:18-786 step3d_uv2_tile
+void step3d_uv2(Orc& o) {
+  GEOM
+  const int nnew = o.nnew, nstp = o.nstp, knew = o.knew;
+#pragma omp parallel
+  {
+    vec FC((size_t)SX * (N + 1)), CF((size_t)SX * (N + 1)), DC((size_t)SX * (N + 1));
+    for (int pass = 0; pass < 2; ++pass) {
+      // u3dbc_tile / v3dbc_tile between the passes: nothing on periodic edges
+#pragma omp for
+      for (int j = jstr; j <= jend; ++j) {
+        for (int dir = 0; dir < 2; ++dir) {
+          const int di = dir == 0 ? 1 : 0, dj = dir == 0 ? 0 : 1;
+          vec& un = dir == 0 ? o.u[nnew - 1] : o.v[nnew - 1];
+          const vec& us = dir == 0 ? o.u[nstp - 1] : o.v[nstp - 1];
+          const vec& dnx = dir == 0 ? o.dn_u : o.dm_v;
+          const vec& msk = dir == 0 ? o.umask : o.vmask;
+          const vec& Davg1 = dir == 0 ? o.DU_avg1 : o.DV_avg1;
+          const vec& Davg2 = dir == 0 ? o.DU_avg2 : o.DV_avg2;
+          vec& Flx = dir == 0 ? o.FlxU : o.FlxV;
+          vec& bar = dir == 0 ? o.ubar[knew - 1] : o.vbar[knew - 1];
+          if (pass == 0) {
+            for (int i = istr; i <= iend; ++i) {
+              SL(CF, i, 0) = 0.5 * (A3(o.Hz, i, j, N) + A3(o.Hz, i - di, j - dj, N));
+              SL(DC, i, 0) = A3(un, i, j, N);
+              A3(un, i, j, N) = A3(un, i, j, N) / SL(CF, i, 0);
+            }
+            for (int k = N - 1; k >= 1; --k)
+              for (int i = istr; i <= iend; ++i) {
+                double cff = 0.5 * (A3(o.Hz, i, j, k) + A3(o.Hz, i - di, j - dj, k));
+                SL(CF, i, 0) = SL(CF, i, 0) + cff;
+                SL(DC, i, 0) = SL(DC, i, 0) + A3(un, i, j, k);
+                A3(un, i, j, k) = A3(un, i, j, k) / cff;
+              }
+            for (int i = istr; i <= iend; ++i) SL(DC, i, 0) = (SL(DC, i, 0) * A2(dnx, i, j) - A2(Davg1, i, j)) / (SL(CF, i, 0) * A2(dnx, i, j));
+            for (int k = 1; k <= N; ++k)
+              for (int i = istr; i <= iend; ++i) A3(un, i, j, k) = (A3(un, i, j, k) - SL(DC, i, 0)) * A2(msk, i, j);
+          } else {
+            for (int i = istr; i <= iend; ++i) {
+              SL(DC, i, N) = 0.5 * (A3(o.Hz, i, j, N) + A3(o.Hz, i - di, j - dj, N)) * A2(dnx, i, j);
+              SL(DC, i, 0) = SL(DC, i, N);
+              SL(FC, i, 0) = SL(DC, i, N) * A3(un, i, j, N);
+            }
+            for (int k = N - 1; k >= 1; --k)
+              for (int i = istr; i <= iend; ++i) {
+                SL(DC, i, k) = 0.5 * (A3(o.Hz, i, j, k) + A3(o.Hz, i - di, j - dj, k)) * A2(dnx, i, j);
+                SL(DC, i, 0) = SL(DC, i, 0) + SL(DC, i, k);
+                SL(FC, i, 0) = SL(FC, i, 0) + SL(DC, i, k) * A3(un, i, j, k);
+              }
+            for (int i = istr; i <= iend; ++i) {
+              SL(DC, i, 0) = 1.0 / SL(DC, i, 0);
+              A2(bar, i, j) = SL(DC, i, 0) * A2(Davg1, i, j);
+              SL(FC, i, 0) = SL(DC, i, 0) * (SL(FC, i, 0) - A2(Davg1, i, j));
+              SL(CF, i, 0) = 0.0;
+            }
+            for (int k = N; k >= 1; --k)
+              for (int i = istr; i <= iend; ++i) {
+                A3(un, i, j, k) = (A3(un, i, j, k) - SL(FC, i, 0)) * A2(msk, i, j);
+                SL(CF, i, k) = 0.28 * A3(Flx, i, j, k) + 0.36 * SL(DC, i, k) * (A3(us, i, j, k) + A3(un, i, j, k));
+                SL(CF, i, 0) = SL(CF, i, 0) + SL(CF, i, k);
+              }
+            for (int i = istr; i <= iend; ++i) SL(CF, i, 0) = SL(DC, i, 0) * (SL(CF, i, 0) - A2(Davg2, i, j));
+            for (int k = 1; k <= N; ++k)
+              for (int i = istr; i <= iend; ++i) A3(Flx, i, j, k) = SL(CF, i, k) - SL(DC, i, k) * SL(CF, i, 0);
+          }
+        }
+      }
+    }
+  }
+  ex3(o, o.FlxU); ex3(o, o.u[nnew - 1]); ex2(o, o.ubar[knew - 1]);
+  ex3(o, o.FlxV); ex3(o, o.v[nnew - 1]); ex2(o, o.vbar[knew - 1]);
+}
+
+// step3d_t_ISO.F:45-1178 step3d_t_iso_tile (non-isoneutral path)
+void step3d_t(Orc& o) {
+  GEOM
+  const int NT = o.NT, nrhs = o.nrhs, nnew = o.nnew;
+  const double dt = o.c.dt;
+  for (int itrc = 0; itrc < NT; ++itrc) {
+    const vec& tr = o.t[nrhs - 1][itrc];
+    vec& tn = o.t[nnew - 1][itrc];
+#pragma omp parallel
+    {
+      vec FX(o.SXY), FE(o.SXY), wrk1(o.SXY);
+#pragma omp for
+      for (int k = 1; k <= N; ++k) {
+        horiz_tracer_fluxes(o, k, tr, true, FX, FE, wrk1);
+        for (int j = jstr; j <= jend; ++j)
+          for (int i = istr; i <= iend; ++i)
+            A3(tn, i, j, k) = A3(tn, i, j, k) - dt * A2(o.pm, i, j) * A2(o.pn, i, j) * (A2(FX, i + 1, j) - A2(FX, i, j) + A2(FE, i, j + 1) - A2(FE, i, j));
+      }
+    }
+#pragma omp parallel
+    {
+      vec WC((size_t)SX * (N + 1)), FC((size_t)SX * (N + 1)), CF((size_t)SX * (N + 1)), DC((size_t)SX * (N + 1));
+#pragma omp for
+      for (int j = jstr; j <= jend; ++j) {
+        vert_tracer_flux(o, j, tr, FC, CF);
+        for (int k = 1; k <= N; ++k)
+          for (int i = istr; i <= iend; ++i) A3(tn, i, j, k) = A3(tn, i, j, k) - dt * A2(o.pm, i, j) * A2(o.pn, i, j) * (SL(FC, i, k) - SL(FC, i, k - 1));
+        if (itrc == 0)
+          for (int i = istr; i <= iend; ++i) A3(tn, i, j, N) = A3(tn, i, j, N) + dt * A2(o.swflx, i, j) * A3(tn, i, j, N) / A3(o.Hz, i, j, N);
+        for (int i = istr; i <= iend; ++i) A3(tn, i, j, N) = A3(tn, i, j, N) + dt * A2(o.stflx[itrc], i, j);
+        const vec& Akt = o.Akt[std::min(itrc, 1)];
+        for (int i = istr; i <= iend; ++i) {
+          SL(DC, i, 0) = dt * A2(o.pm, i, j) * A2(o.pn, i, j);
+          SL(FC, i, 1) = 2.0 * dt * AW(Akt, i, j, 1) / (A3(o.Hz, i, j, 1) + A3(o.Hz, i, j, 2));
+          SL(WC, i, 1) = SL(DC, i, 0) * AW(o.Wi, i, j, 1);
+          double cff = 1.0 / (A3(o.Hz, i, j, 1) + SL(FC, i, 1) + std::max(SL(WC, i, 1), 0.0));
+          SL(CF, i, 1) = cff * (SL(FC, i, 1) - std::min(SL(WC, i, 1), 0.0));
+          SL(DC, i, 1) = cff * A3(tn, i, j, 1);
+        }
+        for (int k = 2; k <= N - 1; ++k)
+          for (int i = istr; i <= iend; ++i) {
+            SL(FC, i, k) = 2.0 * dt * AW(Akt, i, j, k) / (A3(o.Hz, i, j, k) + A3(o.Hz, i, j, k + 1));
+            SL(WC, i, k) = AW(o.Wi, i, j, k) * SL(DC, i, 0);
+            double cff = 1.0 / (A3(o.Hz, i, j, k) + SL(FC, i, k) + std::max(SL(WC, i, k), 0.0) + SL(FC, i, k - 1) - std::min(SL(WC, i, k - 1), 0.0) -
+                                SL(CF, i, k - 1) * (SL(FC, i, k - 1) + std::max(SL(WC, i, k - 1), 0.0)));
+            SL(CF, i, k) = cff * (SL(FC, i, k) - std::min(SL(WC, i, k), 0.0));
+            SL(DC, i, k) = cff * (A3(tn, i, j, k) + SL(DC, i, k - 1) * (SL(FC, i, k - 1) + std::max(SL(WC, i, k - 1), 0.0)));
+          }
+        for (int i = istr; i <= iend; ++i)
+          A3(tn, i, j, N) = (A3(tn, i, j, N) + SL(DC, i, N - 1) * (SL(FC, i, N - 1) + std::max(SL(WC, i, N - 1), 0.0))) /
+                            (A3(o.Hz, i, j, N) + SL(FC, i, N - 1) - std::min(SL(WC, i, N - 1), 0.0) - SL(CF, i, N - 1) * (SL(FC, i, N - 1) + std::max(SL(WC, i, N - 1), 0.0))) *
+                            A2(o.rmask, i, j);
+        for (int k = N - 1; k >= 1; --k)
+          for (int i = istr; i <= iend; ++i) A3(tn, i, j, k) = (SL(DC, i, k) + SL(CF, i, k) * A3(tn, i, j, k + 1)) * A2(o.rmask, i, j);
+      }
+    }
+  }
+  for (int itrc = 0; itrc < NT; ++itrc) ex3(o, o.t[nnew - 1][itrc]);
+}
+
+// diag.F:50-658 diag_tile: KE, barotropic KE, max advective Courant number and its vertical part.
+// Sums use the reference's split-direction pairwise reduction (diag.F:256-325).
+void pairwise(const Orc& o, vec& a) {
+  const int SX = o.SX;
+  const int istr = 1, jstr = 1;
+  int isize = o.Lm - 1, jsize = o.Mm - 1;
+  while (isize > 0 || jsize > 0) {
+    if (jsize > 0) {
+      int js = (jsize + 1) / 2 - 1;
+      for (int j = 0; j <= js; ++j) {
+        int jtg = jstr + j;
+        for (int i = istr; i <= istr + isize; ++i) A2(a, i, jtg) = A2(a, i, jtg + j) + A2(a, i, jtg + j + 1);
+      }
+      if (2 * js + 1 < jsize) {
+        js = js + 1;
+        int jtg = jstr + js;
+        for (int i = istr; i <= istr + isize; ++i) A2(a, i, jtg) = A2(a, i, jtg + js);
+      }
+      jsize = js;
+    }
+    if (isize > 0) {
+      int is = (isize + 1) / 2 - 1;
+      for (int j = jstr; j <= jstr + jsize; ++j)
+        for (int i = 0; i <= is; ++i) {
+          int itg = istr + i;
+          A2(a, itg, j) = A2(a, itg + i, j) + A2(a, itg + i + 1, j);
+        }
+      if (2 * is + 1 < isize) {
+        is = is + 1;
+        int itg = istr + is;
+        for (int j = jstr; j <= jstr + jsize; ++j) A2(a, itg, j) = A2(a, itg + is, j);
+      }
+      isize = is;
+    }
+  }
+}
+void diag(Orc& o, double out[4]) {
+  GEOM
+  const vec& u = o.u[o.nstp - 1];
+  const vec& v = o.v[o.nstp - 1];
+  vec ub(o.SXY), vb(o.SXY), ke(o.SXY), ke2b(o.SXY), dVol(o.SXY);
+  double my_Cu_Adv = 0, my_Cu_W = 0;
+  for (int j = jstr; j <= jend + 1; ++j) {
+    for (int i = istr; i <= iend + 1; ++i) {
+      A2(ub, i, j) = (A3(o.Hz, i, j, N) + A3(o.Hz, i - 1, j, N)) * A3(u, i, j, N);
+      A2(vb, i, j) = (A3(o.Hz, i, j, N) + A3(o.Hz, i, j - 1, N)) * A3(v, i, j, N);
+    }
+    for (int k = N - 1; k >= 2; --k)
+      for (int i = istr; i <= iend + 1; ++i) {
+        A2(ub, i, j) = A2(ub, i, j) + (A3(o.Hz, i, j, k) + A3(o.Hz, i - 1, j, k)) * A3(u, i, j, k);
+        A2(vb, i, j) = A2(vb, i, j) + (A3(o.Hz, i, j, k) + A3(o.Hz, i, j - 1, k)) * A3(v, i, j, k);
+      }
+    for (int i = istr; i <= iend + 1; ++i) {
+      A2(ub, i, j) = (A2(ub, i, j) + (A3(o.Hz, i, j, 1) + A3(o.Hz, i - 1, j, 1)) * A3(u, i, j, 1)) /
+                     (AW(o.z_w, i, j, N) + AW(o.z_w, i - 1, j, N) - AW(o.z_w, i, j, 0) - AW(o.z_w, i - 1, j, 0));
+      A2(vb, i, j) = (A2(vb, i, j) + (A3(o.Hz, i, j, 1) + A3(o.Hz, i, j - 1, 1)) * A3(v, i, j, 1)) /
+                     (AW(o.z_w, i, j, N) + AW(o.z_w, i, j - 1, N) - AW(o.z_w, i, j, 0) - AW(o.z_w, i, j - 1, 0));
+    }
+  }
+  for (int j = jstr; j <= jend; ++j) {
+    for (int i = istr; i <= iend; ++i) {
+      double v2 = 0.5 * (A2(ub, i, j) * A2(ub, i, j) + A2(ub, i + 1, j) * A2(ub, i + 1, j) + A2(vb, i, j) * A2(vb, i, j) + A2(vb, i, j + 1) * A2(vb, i, j + 1));
+      A2(ke, i, j) = 0.0;
+      A2(ke2b, i, j) = 0.5 * (AW(o.z_w, i, j, N) - AW(o.z_w, i, j, 0)) * v2;
+    }
+    for (int k = N; k >= 1; --k)
+      for (int i = istr; i <= iend; ++i) {
+        double v2 = 0.5 * (A3(u, i, j, k) * A3(u, i, j, k) + A3(u, i + 1, j, k) * A3(u, i + 1, j, k) + A3(v, i, j, k) * A3(v, i, j, k) + A3(v, i, j + 1, k) * A3(v, i, j + 1, k));
+        double ciV = o.c.dt * A2(o.rmask, i, j) * A2(o.pm, i, j) * A2(o.pn, i, j) / A3(o.Hz, i, j, k);
+        double cw = ciV * (std::max(AW(o.We, i, j, k) + AW(o.Wi, i, j, k), 0.0) - std::min(AW(o.We, i, j, k - 1) + AW(o.Wi, i, j, k - 1), 0.0));
+        double cx = cw + ciV * (std::max(A3(o.FlxU, i + 1, j, k), 0.0) - std::min(A3(o.FlxU, i, j, k), 0.0) + std::max(A3(o.FlxV, i, j + 1, k), 0.0) - std::min(A3(o.FlxV, i, j, k), 0.0));
+        if (cx > my_Cu_Adv) { my_Cu_Adv = cx; my_Cu_W = cw; }
+        A2(ke, i, j) = A2(ke, i, j) + 0.5 * v2 * A3(o.Hz, i, j, k);
+      }
+    for (int i = istr; i <= iend; ++i) {
+      double dA = A2(o.rmask, i, j) / (A2(o.pm, i, j) * A2(o.pn, i, j));
+      A2(dVol, i, j) = dA * AW(o.z_w, i, j, N);
+      A2(ke, i, j) = dA * A2(ke, i, j);
+      A2(ke2b, i, j) = dA * A2(ke2b, i, j);
+    }
+  }
+  pairwise(o, dVol); pairwise(o, ke); pairwise(o, ke2b);
+  double avzeta = A2(dVol, istr, jstr), avke = A2(ke, istr, jstr), avke2b = A2(ke2b, istr, jstr);
+  out[0] = avke / (o.volume + avzeta);
+  out[1] = avke2b / (o.volume + avzeta);
+  out[2] = my_Cu_Adv;
+  out[3] = my_Cu_W;
+}
+
+// alfabeta.F:4-79 alfabeta_tile (surface alpha, beta; only caller is lmd_kpp.F:156)
+void alfabeta(Orc& o, double* alpha, double* beta) {
+  GEOM
+  const double Q01 = 6.793952e-2, Q02 = -9.095290e-3, Q03 = +1.001685e-4, Q04 = -1.120083e-6, Q05 = +6.536332e-9, U00 = +0.824493,
+               U01 = -4.08990e-3, U02 = +7.64380e-5, U03 = -8.24670e-7, U04 = +5.38750e-9, V00 = -5.72466e-3, V01 = +1.02270e-4,
+               V02 = -1.65460e-6, W00 = +4.8314e-4;
+  const double cff = 1.0 / o.c.rho0;
+  const vec& T = o.t[o.nstp - 1][0];
+  for (int j = jstr - 2; j <= jend + 2; ++j)
+    for (int i = istr - 2; i <= iend + 2; ++i) {
+      if (o.c.nonlin_eos) {
+        double Tt = A3(T, i, j, N);
+        double Ts = A3(o.t[o.nstp - 1][1], i, j, N);
+        double sqrtTs = sqrt(std::max(0., Ts));
+        A2(alpha, i, j) = -cff * (Q01 + Tt * (2.0 * Q02 + Tt * (3.0 * Q03 + Tt * (4.0 * Q04 + Tt * 5.0 * Q05))) +
+                                  Ts * (U01 + Tt * (2.0 * U02 + Tt * (3.0 * U03 + Tt * 4.0 * U04)) + sqrtTs * (V01 + Tt * 2.0 * V02)));
+        A2(beta, i, j) = cff * (U00 + Tt * (U01 + Tt * (U02 + Tt * (U03 + Tt * U04))) + 1.5 * (V00 + Tt * (V01 + Tt * V02)) * sqrtTs + 2.0 * W00 * Ts);
+      } else {
+        A2(alpha, i, j) = fabs(o.c.Tcoef);
+        A2(beta, i, j) = o.c.salinity ? fabs(o.c.Scoef) : 0.0;
+      }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Filament analytic case: tests/Filament/ana_grid.h, ana_init.h (analytical.F:ana_init)
+void init_filament(Orc& o) {
+  GEOM
+  const double SizeX = 12.8e3, SizeY = 3.2e3;
+  const double f0 = 2 * 7.81e-5;
+  const double dx = SizeX / Lm, dy = SizeY / Mm;
+  const double x_mid = SizeX / 2.;
+  o.xr.assign(o.SXY, 0.0);
+  for (int j = -1; j <= Mm + 2; ++j)
+    for (int i = -1; i <= Lm + 2; ++i) {
+      A2(o.xr, i, j) = 0.0 + dx * (double(i) - 0.5) - x_mid;
+      A2(o.pm, i, j) = 1. / dx;
+      A2(o.pn, i, j) = 1. / dy;
+      A2(o.f, i, j) = f0;
+      A2(o.h, i, j) = 1000;
+      A2(o.rmask, i, j) = 1;
+    }
+  setup_grid(o);
+  o.iic = 0; o.kstp = 1; o.knew = 1; o.iif = 1; o.nstp = 1; o.nnew = 1; o.nrhs = 1;
+  set_depth(o);
+  // ana_init
+  const double g = o.c.g, HD = 1000;
+  const double b0 = 5.0e-2, B_cff = 0.025, lambda_inv = 8.0, Nb = 1.0e-7, N0 = 3.0e-5, h0 = 60.0, dh0 = 15., L = 2000.0;
+  const double alpha = o.c.Tcoef / o.c.rho0;
+  vec& T1 = o.t[0][0];
+  for (int j = -1; j <= Mm + 2; ++j)
+    for (int i = -1; i <= Lm + 2; ++i) {
+      double xl = A2(o.xr, i, j) / L;
+      double h_sbl = h0 + dh0 * exp(-(xl * xl));
+      for (int k = 1; k <= N; ++k) {
+        double zr = A3(o.z_r, i, j, k);
+        double b = b0 + Nb * (zr + HD) + 0.5 * N0 * ((1 + B_cff) * zr - (1 - B_cff) * (h_sbl + lambda_inv * log(cosh((1.0 / lambda_inv) * (zr + h_sbl)))));
+        A3(T1, i, j, k) = b / (g * alpha);
+      }
+    }
+  double bf_int = 0;
+  for (int k = 1; k <= N; ++k) {
+    double zr = A3(o.z_r, 1, 1, k);
+    bf_int = bf_int + A3(o.Hz, 1, 1, k) * (b0 + Nb * (zr + HD) + 0.5 * N0 * ((1 + B_cff) * zr - (1 - B_cff) * (h0 + lambda_inv * log(cosh((1.0 / lambda_inv) * (zr + h0)))))) / g;
+  }
+  o.t[1][0] = T1;
+  vec& zeta = o.zeta[0];
+  std::fill(zeta.begin(), zeta.end(), 0.0);
+  for (int k = 1; k <= N; ++k)
+    for (int j = -1; j <= Mm + 2; ++j)
+      for (int i = -1; i <= Lm + 2; ++i) A2(zeta, i, j) = A2(zeta, i, j) + A3(T1, i, j, k) * alpha * A3(o.Hz, i, j, k);
+  for (size_t n = 0; n < zeta.size(); ++n) zeta[n] = (zeta[n] - bf_int);
+  vec& v1 = o.v[0];
+  for (int j = 0; j <= Mm + 1; ++j)
+    for (int i = 0; i <= Lm + 1; ++i) {
+      double dzdx = 0.5 * A2(o.pm, i, j) * (A2(zeta, i + 1, j) - A2(zeta, i - 1, j));
+      A3(v1, i, j, N) = g * dzdx / A2(o.f, i, j);
+    }
+  for (int k = N - 1; k >= 1; --k)
+    for (int j = 0; j <= Mm + 1; ++j)
+      for (int i = 0; i <= Lm + 1; ++i) {
+        double dbdx = 0.25 * A2(o.pm, i, j) * g * alpha * (A3(T1, i + 1, j, k) - A3(T1, i - 1, j, k) + A3(T1, i + 1, j, k + 1) - A3(T1, i - 1, j, k + 1));
+        A3(v1, i, j, k) = A3(v1, i, j, k + 1) - dbdx * (A3(o.z_r, i, j, k + 1) - A3(o.z_r, i, j, k)) / A2(o.f, i, j);
+      }
+  vec& vbar = o.vbar[0];
+  std::fill(vbar.begin(), vbar.end(), 0.0);
+  for (int k = N - 1; k >= 1; --k)
+    for (int j = 0; j <= Mm + 1; ++j)
+      for (int i = 0; i <= Lm + 1; ++i) A2(vbar, i, j) = A2(vbar, i, j) + A3(v1, i, j, k) * A3(o.Hz, i, j, k) / HD;
+  for (int j = 1; j <= Mm; ++j)
+    for (int i = 1; i <= Lm; ++i) {
+      A2(o.ubar[0], i, j) = 0.0;
+      A2(o.vbar[1], i, j) = A2(vbar, i, j);
+      A2(o.zeta[1], i, j) = A2(zeta, i, j);
+      for (int k = 1; k <= N; ++k) {
+        A3(o.u[0], i, j, k) = 0.0;
+        A3(o.u[1], i, j, k) = A3(o.u[0], i, j, k);
+        A3(o.v[1], i, j, k) = A3(v1, i, j, k);
+      }
+    }
+  ex2(o, o.zeta[0]); ex2(o, o.ubar[0]); ex2(o, o.vbar[0]);
+  ex3(o, o.u[0]); ex3(o, o.v[0]);
+  ex3(o, o.t[0][0]);
+}
+
+// main.F:86-321 roms_init, the part after the initial fields exist
+void init_step0(Orc& o) {
+  o.iic = 0; o.kstp = 1; o.knew = 1; o.iif = 1; o.nstp = 1; o.nnew = 1; o.nrhs = 1;
+  o.forw_start = o.ntstart;
+  set_depth(o);
+  set_HUV(o);
+  omega(o);
+  rho_eos(o, o.nrhs);
+}
+
+// main.F:333-520 roms_step
+void step(Orc& o) {
+  if (o.iic == 0) o.iic = o.ntstart; else o.iic = o.iic + 1;
+  o.nstp = 1 + (o.iic - o.ntstart) % 2;
+  o.nrhs = o.nstp; o.nnew = 3;
+  rho_eos(o, o.nrhs);
+  set_HUV(o);
+  omega(o);
+  prsgrd(o);
+  pre_step3d(o);
+  set_HUV1(o);
+  o.nrhs = 3; o.nnew = 3 - o.nstp;
+  omega(o);
+  rho_eos(o, o.nrhs);
+  prsgrd(o);
+  step3d_uv1(o);
+  for (o.iif = 1; o.iif <= o.nfast; ++o.iif) {
+    o.kstp = o.knew;
+    o.knew = o.kstp + 1;
+    if (o.knew > 4) o.knew = 1;
+    step2d(o);
+  }
+  o.iif = o.nfast + 1;  // Fortran do-loop exit value
+  step3d_uv2(o);
+  omega(o);
+  step3d_t(o);
+  rho_eos(o, o.nnew);
+}
+
+vec* field_ptr(Orc& o, int field, int lvl, int itrc, long* count) {
+  const long n2 = (long)o.SXY, n3 = n2 * o.N, nw = n2 * (o.N + 1);
+  vec* p = nullptr; long n = n2;
+  switch (field) {
+    case ROMS_H: p = &o.h; break; case ROMS_PM: p = &o.pm; break; case ROMS_PN: p = &o.pn; break;
+    case ROMS_F: p = &o.f; break; case ROMS_RMASK: p = &o.rmask; break; case ROMS_UMASK: p = &o.umask; break;
+    case ROMS_VMASK: p = &o.vmask; break; case ROMS_DM_U: p = &o.dm_u; break; case ROMS_DN_U: p = &o.dn_u; break;
+    case ROMS_DM_V: p = &o.dm_v; break; case ROMS_DN_V: p = &o.dn_v; break; case ROMS_DM_R: p = &o.dm_r; break;
+    case ROMS_DN_R: p = &o.dn_r; break; case ROMS_FOMN: p = &o.fomn; break; case ROMS_HINV: p = &o.hinv; break;
+    case ROMS_ZETA: p = &o.zeta[lvl - 1]; break; case ROMS_UBAR: p = &o.ubar[lvl - 1]; break; case ROMS_VBAR: p = &o.vbar[lvl - 1]; break;
+    case ROMS_RHOA: p = &o.rhoA; break; case ROMS_RHOS: p = &o.rhoS; break; case ROMS_RUFRC: p = &o.rufrc; break;
+    case ROMS_RVFRC: p = &o.rvfrc; break; case ROMS_ZT_AVG1: p = &o.Zt_avg1; break; case ROMS_DU_AVG1: p = &o.DU_avg1; break;
+    case ROMS_DV_AVG1: p = &o.DV_avg1; break; case ROMS_DU_AVG2: p = &o.DU_avg2; break; case ROMS_DV_AVG2: p = &o.DV_avg2; break;
+    case ROMS_DU_AVG_BAK: p = &o.DU_avg_bak; break; case ROMS_DV_AVG_BAK: p = &o.DV_avg_bak; break; case ROMS_R_D: p = &o.r_D; break;
+    case ROMS_SUSTR: p = &o.sustr; break; case ROMS_SVSTR: p = &o.svstr; break; case ROMS_SWFLX: p = &o.swflx; break;
+    case ROMS_STFLX: p = &o.stflx[itrc - 1]; break;
+    case ROMS_U: p = &o.u[lvl - 1]; n = n3; break; case ROMS_V: p = &o.v[lvl - 1]; n = n3; break;
+    case ROMS_T: p = &o.t[lvl - 1][itrc - 1]; n = n3; break;
+    case ROMS_HZ: p = &o.Hz; n = n3; break; case ROMS_Z_R: p = &o.z_r; n = n3; break; case ROMS_Z_W: p = &o.z_w; n = nw; break;
+    case ROMS_FLXU: p = &o.FlxU; n = n3; break; case ROMS_FLXV: p = &o.FlxV; n = n3; break;
+    case ROMS_WE: p = &o.We; n = nw; break; case ROMS_WI: p = &o.Wi; n = nw; break;
+    case ROMS_RHO1: p = &o.rho1; n = n3; break; case ROMS_QP1: p = &o.qp1; n = n3; break;
+    case ROMS_AKV: p = &o.Akv; n = nw; break; case ROMS_AKT: p = &o.Akt[itrc - 1]; n = nw; break;
+    case ROMS_RU: p = &o.ru; n = n3; break; case ROMS_RV: p = &o.rv; n = n3; break;
+    default: break;
+  }
+  if (count) *count = n;
+  return p;
+}
+
+}  // namespace
+
+extern "C" {
+typedef struct Orc orc_ctx;
+
+int orc_create(const roms_cfg* cfg, void** out) {
+  Orc* o = new Orc();
+  o->c = *cfg;
+  o->Lm = cfg->Lm; o->Mm = cfg->Mm; o->N = cfg->N; o->NT = cfg->NT;
+  o->SX = cfg->Lm + 4; o->SY = cfg->Mm + 4; o->SXY = (size_t)o->SX * o->SY;
+  const size_t n2 = o->SXY, n3 = n2 * o->N, nw = n2 * (o->N + 1);
+  for (vec* a : {&o->h, &o->pm, &o->pn, &o->f, &o->rmask, &o->umask, &o->vmask, &o->dm_u, &o->dn_u, &o->dm_v, &o->dn_v, &o->dm_r, &o->dn_r, &o->fomn,
+                 &o->hinv, &o->rhoA, &o->rhoS, &o->rufrc, &o->rvfrc, &o->Zt_avg1, &o->DU_avg1, &o->DV_avg1, &o->DU_avg2, &o->DV_avg2, &o->DU_avg_bak,
+                 &o->DV_avg_bak, &o->r_D, &o->sustr, &o->svstr, &o->swflx})
+    a->assign(n2, 0.0);
+  for (int l = 0; l < 4; ++l) { o->zeta[l].assign(n2, 0.0); o->ubar[l].assign(n2, 0.0); o->vbar[l].assign(n2, 0.0); }
+  o->stflx.assign(o->NT, vec(n2, 0.0));
+  for (int l = 0; l < 3; ++l) {
+    o->u[l].assign(n3, 0.0); o->v[l].assign(n3, 0.0);
+    o->t[l].assign(o->NT, vec(n3, 0.0));
+  }
+  for (vec* a : {&o->Hz, &o->z_r, &o->FlxU, &o->FlxV, &o->rho1, &o->qp1, &o->ru, &o->rv, &o->Hz_bak, &o->Hz_fwd, &o->Pp, &o->rho}) a->assign(n3, 0.0);
+  for (vec* a : {&o->z_w, &o->We, &o->Wi, &o->Akv, &o->Akt[0], &o->Akt[1]}) a->assign(nw, 0.0);
+  o->iic = 0; o->iif = 1; o->nstp = 1; o->nrhs = 1; o->nnew = 1; o->kstp = 1; o->knew = 1; o->ntstart = 1; o->forw_start = 1;
+  o->dtfast = cfg->dt / double(cfg->ndtfast);   // read_inp_mod.F:416-446
+  set_scoord(*o);
+  set_weights(*o);
+  *out = o;
+  return 0;
+}
+int orc_destroy(void* h) { delete (Orc*)h; return 0; }
+int orc_push(void* h, int field, int lvl, int itrc, const double* host) {
+  long n; vec* p = field_ptr(*(Orc*)h, field, lvl, itrc, &n);
+  if (!p) return -1;
+  memcpy(p->data(), host, n * sizeof(double));
+  return 0;
+}
+int orc_pull(void* h, int field, int lvl, int itrc, double* host) {
+  long n; vec* p = field_ptr(*(Orc*)h, field, lvl, itrc, &n);
+  if (!p) return -1;
+  memcpy(host, p->data(), n * sizeof(double));
+  return 0;
+}
+long orc_field_count(void* h, int field) { long n = 0; field_ptr(*(Orc*)h, field, 1, 1, &n); return n; }
+int orc_setup_grid(void* h) { setup_grid(*(Orc*)h); return 0; }
+int orc_get_nfast(void* h) { return ((Orc*)h)->nfast; }
+int orc_get_weights(void* h, double* w1, double* w2, int n) {
+  Orc& o = *(Orc*)h;
+  for (int i = 1; i <= n; ++i) { w1[i - 1] = o.weight1[i]; w2[i - 1] = o.weight2[i]; }
+  return 0;
+}
+int orc_get_scoord(void* h, double* Cs_w, double* Cs_r) {
+  Orc& o = *(Orc*)h;
+  for (int k = 0; k <= o.N; ++k) Cs_w[k] = o.Cs_w[k];
+  for (int k = 1; k <= o.N; ++k) Cs_r[k - 1] = o.Cs_r[k];
+  return 0;
+}
+int orc_set_time_indices(void* h, int iic, int iif, int nstp, int nrhs, int nnew, int kstp, int knew) {
+  Orc& o = *(Orc*)h;
+  o.iic = iic; o.iif = iif; o.nstp = nstp; o.nrhs = nrhs; o.nnew = nnew; o.kstp = kstp; o.knew = knew;
+  return 0;
+}
+int orc_get_time_indices(void* h, int* iic, int* iif, int* nstp, int* nrhs, int* nnew, int* kstp, int* knew) {
+  Orc& o = *(Orc*)h;
+  *iic = o.iic; *iif = o.iif; *nstp = o.nstp; *nrhs = o.nrhs; *nnew = o.nnew; *kstp = o.kstp; *knew = o.knew;
+  return 0;
+}
+int orc_set_depth(void* h, int) { set_depth(*(Orc*)h); return 0; }
+int orc_set_huv(void* h) { set_HUV(*(Orc*)h); return 0; }
+int orc_set_huv1(void* h, int) { set_HUV1(*(Orc*)h); return 0; }
+int orc_omega(void* h) { omega(*(Orc*)h); return 0; }
+int orc_rho_eos(void* h, int tidx) { rho_eos(*(Orc*)h, tidx); return 0; }
+int orc_prsgrd(void* h) { prsgrd(*(Orc*)h); return 0; }
+int orc_pre_step3d(void* h, int) { pre_step3d(*(Orc*)h); return 0; }
+int orc_step3d_uv1(void* h, int) { step3d_uv1(*(Orc*)h); return 0; }
+int orc_step2d(void* h) { step2d(*(Orc*)h); return 0; }
+int orc_step3d_uv2(void* h, int) { step3d_uv2(*(Orc*)h); return 0; }
+int orc_step3d_t(void* h, int) { step3d_t(*(Orc*)h); return 0; }
+int orc_alfabeta(void* h, double* a, double* b) { alfabeta(*(Orc*)h, a, b); return 0; }
+int orc_diag(void* h, double out[4]) { diag(*(Orc*)h, out); return 0; }
+int orc_init_filament(void* h) { init_filament(*(Orc*)h); return 0; }
+int orc_init_step0(void* h) { init_step0(*(Orc*)h); return 0; }
+int orc_step(void* h) { step(*(Orc*)h); return 0; }
+int orc_run(void* h, int n) { for (int i = 0; i < n; ++i) step(*(Orc*)h); return 0; }
+int orc_exchange(void* h, int field, int lvl, int itrc) {
+  Orc& o = *(Orc*)h;
+  long n; vec* p = field_ptr(o, field, lvl, itrc, &n);
+  if (!p) return -1;
+  exchange(o, p->data(), (int)(n / (long)o.SXY));
+  return 0;
+}
+}
