@@ -1,0 +1,889 @@
+// kernels.cuh -- fp64 CUDA kernels (sm_100a) for the UCLA-ROMS explicit stencil time step.
+//
+// Design: two kernel shapes only.
+//  * "plane" kernels: one thread per (i,j,k) point, x along i (coalesced, 128-B aligned rows),
+//    every horizontal flux recomputed in registers from the L1/L2-cached neighbourhood, so none
+//    of the reference's 2-D scratch planes (UFx,UFe,VFx,VFe,wrk1,wrk2,FX,FE,...) exist.
+//  * "column" kernels: one thread per (i,j) column, x along i; the k-recurrences (parabolic
+//    splines, Thomas solves, omega integration) run in registers with a sliding window, and the
+//    two per-level coefficients that a back-substitution needs live in shared memory laid out
+//    [k][thread] (conflict-free), falling back to global scratch only when N is too large.
+// Operation order inside each expression follows the reference (file:line cited per kernel) so
+// that results agree with the CPU oracle to rounding of fp64 division/log only.
+#pragma once
+#include "kp.h"
+
+#define DMAX(a, b) fmax((a), (b))
+#define DMIN(a, b) fmin((a), (b))
+
+struct ColScr {
+  double* b;
+  long ks, as;
+};
+__device__ __forceinline__ ColScr col_scratch(const KP& p, long c, double* smem) {
+  ColScr s;
+  if (p.use_smem) {
+    const int nth = blockDim.x * blockDim.y;
+    s.b = smem + threadIdx.y * blockDim.x + threadIdx.x;
+    s.ks = nth;
+    s.as = (long)nth * (p.N + 1);
+  } else {
+    s.b = p.scr + c;
+    s.ks = p.SXY;
+    s.as = p.SXY * (p.N + 1);
+  }
+  return s;
+}
+#define S(n, k) sc.b[(long)(n)*sc.as + (long)(k)*sc.ks]
+
+#define THREAD_IJ(i0, i1, j0, j1)                                   \
+  const int i = blockIdx.x * blockDim.x + threadIdx.x - IOFF;       \
+  const int j = (j0) + blockIdx.y * blockDim.y + threadIdx.y;       \
+  if (i < (i0) || i > (i1) || j > (j1)) return;                     \
+  const long c = CIDX(i, j);                                        \
+  const long SX = p.SX; (void)SX;
+
+// ------------------------------------------------------------------------------------------------
+// exchange_xxx on one subdomain (mpi_exchanges.F:34-40 with the periodic wrap of mpi_setup.F:231-250):
+// every halo cell copies its periodic image from the interior.  Up to 4 fields per launch.
+struct HaloList {
+  double* a[4];
+  int nk[4];
+  int n;
+};
+__global__ void k_halo_periodic(const __grid_constant__ KP p, const __grid_constant__ HaloList hl, int ew, int ns) {
+  const int Lm = p.Lm, Mm = p.Mm;
+  const int SXh = Lm + 4;
+  // halo cells enumerated as: 4 full rows (j=-1,0,Mm+1,Mm+2) then 4 columns x Mm rows
+  const int nrow = 4 * SXh, ncol = 4 * Mm;
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t >= nrow + ncol) return;
+  int i, j;
+  if (t < nrow) {
+    const int r = t / SXh;
+    i = t - r * SXh - 1;
+    j = (r < 2) ? (r - 1) : (Mm + r - 1);
+  } else {
+    const int q = t - nrow;
+    const int r = q / Mm;
+    j = q - r * Mm + 1;
+    i = (r < 2) ? (r - 1) : (Lm + r - 1);
+  }
+  int is = i, js = j;
+  if (ew) { if (i < 1) is = i + Lm; else if (i > Lm) is = i - Lm; }
+  if (ns) { if (j < 1) js = j + Mm; else if (j > Mm) js = j - Mm; }
+  if ((is < 1 || is > Lm) || (js < 1 || js > Mm)) return;   // non-periodic edge: untouched
+  if (is == i && js == j) return;
+  const long cd = CIDX(i, j), cs = CIDX(is, js);
+  const int f = blockIdx.y;
+  double* a = hl.a[f];
+  for (int k = blockIdx.z; k < hl.nk[f]; k += gridDim.z) a[cd + (long)k * p.SXY] = a[cs + (long)k * p.SXY];
+}
+
+// ------------------------------------------------------------------------------------------------
+// set_depth.F:16-186 set_depth_tile: z_w, z_r, Hz from zeta(knew).  Plane kernel over k=0:N.
+__global__ void k_set_depth(const __grid_constant__ KP p, const double* __restrict__ zeta) {
+  THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
+  const int k = blockIdx.z;
+  const int N = p.N;
+  const double h = p.h[c];
+  if (k == 0) { RW(p.z_w, c, 0) = -h; return; }
+  const double ds = 1.0 / double(N);
+  const double z = zeta[c], hinv = p.hinv[c];
+  const double cff_w = p.hc * ds * double(k - N);
+  const double cff_r = p.hc * ds * (double(k - N) - 0.5);
+  const double zw = z + (z + h) * (cff_w + p.Cs_w[k] * h) * hinv;
+  const double zr = z + (z + h) * (cff_r + p.Cs_r[k] * h) * hinv;
+  double zwm;
+  if (k == 1) zwm = -h;
+  else {
+    const double cff_wm = p.hc * ds * double(k - 1 - N);
+    zwm = z + (z + h) * (cff_wm + p.Cs_w[k - 1] * h) * hinv;
+  }
+  RW(p.z_w, c, k) = zw;
+  R3(p.z_r, c, k) = zr;
+  R3(p.Hz, c, k) = zw - zwm;
+}
+// set_depth.F iic==0 branch: hinv, DU_avg1, DV_avg1
+__global__ void k_set_depth_init(const __grid_constant__ KP p, const double* __restrict__ zeta, const double* __restrict__ ubar,
+                                 const double* __restrict__ vbar) {
+  THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
+  p.hinv[c] = 1.0 / (p.h[c] + p.hc);
+  p.DU_avg1[c] = 0.5 * (p.h[c - 1] + p.h[c] + zeta[c] + zeta[c - 1]) * p.dn_u[c] * (ubar[c]);
+  p.DV_avg1[c] = 0.5 * (p.h[c] + p.h[c - SX] + zeta[c] + zeta[c - SX]) * p.dm_v[c] * (vbar[c]);
+}
+
+// set_depth.F:201-234 set_HUV_tile
+__global__ void k_set_huv(const __grid_constant__ KP p, const double* __restrict__ u, const double* __restrict__ v) {
+  THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
+  const int k = blockIdx.z + 1;
+  const double Hz = R3(p.Hz, c, k);
+  R3(p.FlxU, c, k) = 0.5 * (Hz + R3(p.Hz, c - 1, k)) * p.dn_u[c] * (R3(u, c, k));
+  R3(p.FlxV, c, k) = 0.5 * (Hz + R3(p.Hz, c - SX, k)) * p.dm_v[c] * (R3(v, c, k));
+}
+
+// set_depth.F:252-422 set_HUV1_tile.  DIR 0: u/FlxU, 1: v/FlxV.  Column kernel, two sweeps, no scratch.
+template <int DIR>
+__global__ void k_set_huv1(const __grid_constant__ KP p, double* __restrict__ u, int first) {
+  THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
+  const long d = DIR == 0 ? 1 : SX;
+  const double dn = DIR == 0 ? p.dn_u[c] : p.dm_v[c];
+  const double msk = DIR == 0 ? p.umask[c] : p.vmask[c];
+  double* Flx = DIR == 0 ? p.FlxU : p.FlxV;
+  const int N = p.N;
+  double DCN = 0.5 * (R3(p.Hz, c, N) + R3(p.Hz, c - d, N)) * dn;
+  double DC0 = DCN;
+  double FC0 = DCN * R3(u, c, N);
+  for (int k = N - 1; k >= 1; --k) {
+    const double DCk = 0.5 * (R3(p.Hz, c, k) + R3(p.Hz, c - d, k)) * dn;
+    DC0 = DC0 + DCk;
+    FC0 = FC0 + DCk * R3(u, c, k);
+  }
+  const double* a1 = DIR == 0 ? p.DU_avg1 : p.DV_avg1;
+  const double* a2 = DIR == 0 ? p.DU_avg2 : p.DV_avg2;
+  const double* ab = DIR == 0 ? p.DU_avg_bak : p.DV_avg_bak;
+  if (first) FC0 = (FC0 - a1[c]) / DC0;
+  else FC0 = (FC0 - 3.63 * a1[c] + 4.47 * a2[c] - 2.05 * ab[c]) / DC0;
+  for (int k = 1; k <= N; ++k) {
+    const double DCk = 0.5 * (R3(p.Hz, c, k) + R3(p.Hz, c - d, k)) * dn;
+    const double un = (R3(u, c, k) - FC0) * msk;
+    R3(u, c, k) = un;
+    R3(Flx, c, k) = DCk * (un);
+  }
+}
+
+// omega.F:17-236 omega_tile.  Column kernel: up-sweep integrates continuity, down-sweep removes the
+// grid motion and splits W into explicit We and implicit Wi by the local Courant number.
+__global__ void k_omega(const __grid_constant__ KP p, double dtau) {
+  extern __shared__ double smem[];
+  THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
+  ColScr sc = col_scratch(p, c, smem);
+  const int N = p.N;
+  const double cu_min = 0.6, cu_max = 1.0, cmnx_ratio = cu_min / cu_max, cutoff = 2.0 - cmnx_ratio, r4cmx = 0.25 / (1.0 - cmnx_ratio);
+  double W = 0.0;
+  RW(p.Wi, c, 0) = 0.0;
+  for (int k = 1; k <= N; ++k) {
+    const double fu1 = R3(p.FlxU, c + 1, k), fu0 = R3(p.FlxU, c, k), fv1 = R3(p.FlxV, c + SX, k), fv0 = R3(p.FlxV, c, k);
+    W = W - fu1 + fu0 - fv1 + fv0;
+    S(0, k) = DMAX(fu1, 0.0) - DMIN(fu0, 0.0) + DMAX(fv1, 0.0) - DMIN(fv0, 0.0);
+    S(1, k) = W;
+  }
+  W = W + p.swflx[c] * p.dm_r[c] * p.dn_r[c];
+  const double zw0 = RW(p.z_w, c, 0);
+  const double wrk = W / (RW(p.z_w, c, N) - zw0);
+  RW(p.Wi, c, N) = 0.0;
+  RW(p.We, c, N) = 0.0;
+  RW(p.We, c, 0) = 0.0;
+  const double CX0 = dtau * p.pm[c] * p.pn[c];
+  double CXkp = S(0, N), Hzkp = R3(p.Hz, c, N);
+  for (int k = N - 1; k >= 1; --k) {
+    double Wik = S(1, k) - wrk * (RW(p.z_w, c, k) - zw0);
+    const double CXk = S(0, k), Hzk = R3(p.Hz, c, k);
+    const double c2d = DMAX(CXk, CXkp);
+    const double dh = DMIN(Hzk, Hzkp);
+    const double cw_max = cu_max * dh - c2d * CX0;
+    double Wek;
+    if (cw_max > 0.0) {
+      const double cw_max2 = cw_max * cw_max;
+      const double cw_min = cw_max * cmnx_ratio;
+      const double cw = fabs(Wik) * CX0;
+      double cff;
+      if (cw < cw_min) cff = cw_max2;
+      else if (cw < cutoff * cw_max) cff = cw_max2 + r4cmx * ((cw - cw_min) * (cw - cw_min));
+      else cff = cw_max * cw;
+      Wek = cw_max2 * Wik / cff;
+      Wik = Wik - Wek;
+    } else Wek = 0.0;
+    RW(p.We, c, k) = Wek;
+    RW(p.Wi, c, k) = Wik;
+    CXkp = CXk; Hzkp = Hzk;
+  }
+}
+
+// rho_eos.F:26-409 rho_eos_tile over the extended range (whole padded subdomain), one down-sweep:
+// rho1,qp1 per level and the vertical integrals rhoA, rhoS (rho_eos.F:364-395).
+template <bool NONLIN>
+__global__ void k_rho_eos(const __grid_constant__ KP p, const double* __restrict__ T, const double* __restrict__ Sal) {
+  THREAD_IJ(p.istr - 2, p.iend + 2, p.jstr - 2, p.jend + 2)
+  const int N = p.N;
+  const double rho0 = p.rho0, qp2 = 0.0000172;
+  const double r00 = 999.842594, r01 = 6.793952e-2, r02 = -9.095290e-3, r03 = 1.001685e-4, r04 = -1.120083e-6, r05 = 6.536332e-9,
+               r10 = 0.824493, r11 = -4.08990e-3, r12 = 7.64380e-5, r13 = -8.24670e-7, r14 = 5.38750e-9, rS0 = -5.72466e-3,
+               rS1 = 1.02270e-4, rS2 = -1.65460e-6, r20 = 4.8314e-4, K00 = 19092.56, K01 = 209.8925, K02 = -3.041638,
+               K03 = -1.852732e-3, K04 = -1.361629e-5, K10 = 104.4077, K11 = -6.500517, K12 = 0.1553190, K13 = 2.326469e-4,
+               KS0 = -5.587545, KS1 = +0.7390729, KS2 = -1.909078e-2;
+  double K0_Duk = 0, dr00 = 0, cffl = 0;
+  if (NONLIN) {
+    const double Tt = 3.8, Ts = 34.5, sqrtTs = sqrt(Ts);
+    K0_Duk = Tt * (K01 + Tt * (K02 + Tt * (K03 + Tt * K04))) + Ts * (K10 + Tt * (K11 + Tt * (K12 + Tt * K13)) + sqrtTs * (KS0 + Tt * (KS1 + Tt * KS2)));
+    dr00 = r00 - rho0;
+  } else {
+    cffl = p.salinity ? (p.Tcoef * p.T0 - p.Scoef * p.S0) : (p.Tcoef * p.T0);
+  }
+  const double rmask = p.rmask[c];
+  double rhoA = 0, rhoS = 0;
+  for (int k = N; k >= 1; --k) {
+    double r1, cff;
+    const double Hz = R3(p.Hz, c, k);
+    if (NONLIN) {
+      const double Tt = R3(T, c, k), Ts = R3(Sal, c, k), sqrtTs = sqrt(DMAX(0.0, Ts));
+      r1 = (dr00 + Tt * (r01 + Tt * (r02 + Tt * (r03 + Tt * (r04 + Tt * r05)))) +
+            Ts * (r10 + Tt * (r11 + Tt * (r12 + Tt * (r13 + Tt * r14))) + sqrtTs * (rS0 + Tt * (rS1 + Tt * rS2)) + Ts * r20)) * rmask;
+      const double K0 = Tt * (K01 + Tt * (K02 + Tt * (K03 + Tt * K04))) + Ts * (K10 + Tt * (K11 + Tt * (K12 + Tt * K13)) + sqrtTs * (KS0 + Tt * (KS1 + Tt * KS2)));
+      const double q1 = 0.1 * (rho0 + r1) * (K0_Duk - K0) / ((K00 + K0) * (K00 + K0_Duk)) * rmask;
+      R3(p.qp1, c, k) = q1;
+      const double dpth = -R3(p.z_r, c, k);
+      cff = Hz * (r1 + q1 * dpth * (1.0 - qp2 * dpth));
+    } else {
+      r1 = cffl - p.Tcoef * R3(T, c, k);
+      if (p.salinity) r1 = r1 + p.Scoef * R3(Sal, c, k);
+      r1 = r1 * rmask;
+      cff = Hz * r1;
+    }
+    R3(p.rho1, c, k) = r1;
+    if (k == N) { rhoS = 0.5 * cff * Hz; rhoA = cff; }
+    else { rhoS = rhoS + Hz * (rhoA + 0.5 * cff); rhoA = rhoA + cff; }
+  }
+  const double cff1 = 1.0 / rho0;
+  const double cff = 1.0 / (RW(p.z_w, c, N) - RW(p.z_w, c, 0));
+  p.rhoA[c] = cff * cff1 * rhoA;
+  p.rhoS[c] = 2.0 * cff * cff * cff1 * rhoS;
+}
+
+// prsgrd.F:160-226: vertical part.  The harmonic means dZ,dR of the reference depend only on levels
+// k-1,k,k+1, so the whole column is one downward sweep with a 3-level register window: writes the
+// hydrostatic pressure P and (SPLIT_EOS) the in-situ density rho.  Columns i=0:Lm, j=0:Mm.
+template <bool NONLIN>
+__global__ void k_prsgrd_vert(const __grid_constant__ KP p) {
+  THREAD_IJ(0, p.Lm, 0, p.Mm)
+  const int N = p.N;
+  const double qp2 = 0.0000172, OneFifth = 0.2, OneTwelfth = 1.0 / 12.0, epsil = 0.0;
+  const double grho = p.g / p.rho0, HalfGRho = 0.5 * grho;
+  // window: level k+1 ("p"), k ("c"), k-1 ("m")
+  double zr_c = R3(p.z_r, c, N), r1_c = R3(p.rho1, c, N), q1_c = NONLIN ? R3(p.qp1, c, N) : 0.0;
+  double zr_m = R3(p.z_r, c, N - 1), r1_m = R3(p.rho1, c, N - 1), q1_m = NONLIN ? R3(p.qp1, c, N - 1) : 0.0;
+  double zr_p = 0, rho_p = 0, dZh_p = 0, dRh_p = 0, P_p = 0;
+  // raw differences: rawZ_c = dZ(k) (between k and k+1), rawZ_m = dZ(k-1)
+  double rawZ_c, rawR_c, rawZ_m, rawR_m;
+  {
+    rawZ_m = zr_c - zr_m;
+    if (NONLIN) { const double dpth = -0.5 * (zr_c + zr_m); rawR_m = r1_c - r1_m + (q1_c - q1_m) * dpth * (1.0 - qp2 * dpth); }
+    else rawR_m = r1_c - r1_m;
+    rawZ_c = rawZ_m; rawR_c = rawR_m;   // dZ(N)=dZ(N-1), dR(N)=dR(N-1)
+  }
+  for (int k = N; k >= 1; --k) {
+    // harmonic averages at level k from raw(k), raw(k-1)
+    double cff = 2.0 * rawZ_c * rawZ_m;
+    const double dZh = cff / (rawZ_c + rawZ_m);
+    const double cfr = 2.0 * rawR_c * rawR_m;
+    double dRh = (cfr > epsil) ? cfr / (rawR_c + rawR_m) : 0.0;
+    double rho_c;
+    if (NONLIN) {
+      const double dpth = -zr_c;
+      dRh = dRh - q1_c * dZh * (1.0 - 2.0 * qp2 * dpth);
+      rho_c = r1_c + q1_c * dpth * (1.0 - qp2 * dpth);
+      R3(p.rho, c, k) = rho_c;
+    } else rho_c = r1_c;
+    double Pk;
+    if (k == N) {
+      double rho_m;
+      if (NONLIN) { const double dpm = -zr_m; rho_m = r1_m + q1_m * dpm * (1.0 - qp2 * dpm); }
+      else rho_m = r1_m;
+      const double zwN = RW(p.z_w, c, N);
+      Pk = p.g * zwN + grho * (rho_c + 0.5 * (rho_c - rho_m) * (zwN - zr_c) / (zr_c - zr_m)) * (zwN - zr_c);
+    } else {
+      Pk = P_p + HalfGRho * ((rho_p + rho_c) * (zr_p - zr_c) -
+                             OneFifth * ((dRh_p - dRh) * (zr_p - zr_c - OneTwelfth * (dZh_p + dZh)) - (dZh_p - dZh) * (rho_p - rho_c - OneTwelfth * (dRh_p + dRh))));
+    }
+    R3(p.P, c, k) = Pk;
+    // slide the window down
+    zr_p = zr_c; rho_p = rho_c; dZh_p = dZh; dRh_p = dRh; P_p = Pk;
+    rawZ_c = rawZ_m; rawR_c = rawR_m;
+    zr_c = zr_m; r1_c = r1_m; q1_c = q1_m;
+    if (k - 2 >= 1) {
+      zr_m = R3(p.z_r, c, k - 2); r1_m = R3(p.rho1, c, k - 2); if (NONLIN) q1_m = R3(p.qp1, c, k - 2);
+      rawZ_m = zr_c - zr_m;
+      if (NONLIN) { const double dpth = -0.5 * (zr_c + zr_m); rawR_m = r1_c - r1_m + (q1_c - q1_m) * dpth * (1.0 - qp2 * dpth); }
+      else rawR_m = r1_c - r1_m;
+    }  // else dZ(0)=dZ(1): rawZ_m keeps the value just shifted into rawZ_c
+  }
+}
+
+// prsgrd.F:231-421: horizontal part, plane kernel.  ru, rv at (i,j,k) from the density-Jacobian with
+// harmonic-mean reconstruction of the horizontal differences.
+template <bool NONLIN>
+__device__ __forceinline__ double prs_dir(const KP& p, long c, long d, int k, const double* __restrict__ msk, double dn, const double* __restrict__ rho) {
+  const double qp2 = 0.0000172, OneFifth = 0.2, OneTwelfth = 1.0 / 12.0, epsil = 0.0;
+  const double HalfGRho = 0.5 * (p.g / p.rho0);
+  // points c-2d, c-d, c, c+d
+  const double z0 = R3(p.z_r, c - 2 * d, k), z1 = R3(p.z_r, c - d, k), z2 = R3(p.z_r, c, k), z3 = R3(p.z_r, c + d, k);
+  const double m1 = msk[c - d], m2 = msk[c], m3 = msk[c + d];
+  const double FCa = (z1 - z0) * m1, FCb = (z2 - z1) * m2, FCc = (z3 - z2) * m3;   // FC(i-1), FC(i), FC(i+1)
+  double rxa, rxb, rxc;
+  double q1 = 0, q2v = 0;
+  if (NONLIN) {
+    const double a0 = R3(p.rho1, c - 2 * d, k), a1 = R3(p.rho1, c - d, k), a2 = R3(p.rho1, c, k), a3 = R3(p.rho1, c + d, k);
+    const double b0 = R3(p.qp1, c - 2 * d, k), b1 = R3(p.qp1, c - d, k), b2 = R3(p.qp1, c, k), b3 = R3(p.qp1, c + d, k);
+    double dpth = -0.5 * (z1 + z0); rxa = (a1 - a0 + (b1 - b0) * dpth * (1.0 - qp2 * dpth)) * m1;
+    dpth = -0.5 * (z2 + z1); rxb = (a2 - a1 + (b2 - b1) * dpth * (1.0 - qp2 * dpth)) * m2;
+    dpth = -0.5 * (z3 + z2); rxc = (a3 - a2 + (b3 - b2) * dpth * (1.0 - qp2 * dpth)) * m3;
+    q1 = b1; q2v = b2;
+  } else {
+    const double a0 = R3(rho, c - 2 * d, k), a1 = R3(rho, c - d, k), a2 = R3(rho, c, k), a3 = R3(rho, c + d, k);
+    rxa = (a1 - a0) * m1; rxb = (a2 - a1) * m2; rxc = (a3 - a2) * m3;
+  }
+  // dZx, dRx at c-d ("m") and c ("c")
+  double cff = 2.0 * FCa * FCb;
+  const double dZx_m = (cff > epsil) ? cff / (FCa + FCb) : 0.0;
+  cff = 2.0 * FCb * FCc;
+  const double dZx_c = (cff > epsil) ? cff / (FCb + FCc) : 0.0;
+  double cfr = 2.0 * rxa * rxb;
+  double dRx_m = (cfr > epsil) ? cfr / (rxa + rxb) : 0.0;
+  cfr = 2.0 * rxb * rxc;
+  double dRx_c = (cfr > epsil) ? cfr / (rxb + rxc) : 0.0;
+  if (NONLIN) {
+    dRx_m = dRx_m - q1 * dZx_m * (1.0 + 2.0 * qp2 * z1);
+    dRx_c = dRx_c - q2v * dZx_c * (1.0 + 2.0 * qp2 * z2);
+  }
+  const double rho_c = R3(rho, c, k), rho_m = R3(rho, c - d, k);
+  return 0.5 * (R3(p.Hz, c, k) + R3(p.Hz, c - d, k)) * dn *
+         (R3(p.P, c - d, k) - R3(p.P, c, k) -
+          HalfGRho * ((rho_c + rho_m) * (z2 - z1) -
+                      OneFifth * ((dRx_c - dRx_m) * (z2 - z1 - OneTwelfth * (dZx_c + dZx_m)) - (dZx_c - dZx_m) * (rho_c - rho_m - OneTwelfth * (dRx_c + dRx_m)))));
+}
+template <bool NONLIN>
+__global__ void k_prsgrd_horiz(const __grid_constant__ KP p) {
+  THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
+  const int k = blockIdx.z + 1;
+  const double* rho = NONLIN ? p.rho : p.rho1;
+  R3(p.ru, c, k) = prs_dir<NONLIN>(p, c, 1, k, p.umask, p.dn_u[c], rho);
+  R3(p.rv, c, k) = prs_dir<NONLIN>(p, c, SX, k, p.vmask, p.dm_v[c], rho);
+}
+
+// ------------------------------------------------------------------------------------------------
+// compute_horiz_rhs_uv_terms.h:1-291.  Fluxes evaluated in registers at the flux point `c`.
+// UP=false: 4th-order centred (pre_step3d4S.F:178); UP=true: 3rd-order upstream (step3d_uv1.F:124).
+#define HDELTA 0.1666666666666667
+#define HGAMMA 0.3333333333333333
+// along-axis flux of the along-axis velocity: UFx (d=1,u,FlxU) / VFe (d=SX,v,FlxV) at rho point c
+template <bool UP>
+__device__ __forceinline__ double flux_along(const KP& p, const double* __restrict__ u, const double* __restrict__ Flx, long c, long d, int k) {
+  const double um = R3(u, c - d, k), u0 = R3(u, c, k), u1 = R3(u, c + d, k), u2 = R3(u, c + 2 * d, k);
+  const double fm = R3(Flx, c - d, k), f0 = R3(Flx, c, k), f1 = R3(Flx, c + d, k), f2 = R3(Flx, c + 2 * d, k);
+  const double w1a = um - 2.0 * u0 + u1, w1b = u0 - 2.0 * u1 + u2;     // wrk1(c), wrk1(c+d)
+  const double w2a = fm - 2.0 * f0 + f1, w2b = f0 - 2.0 * f1 + f2;     // wrk2(c), wrk2(c+d)
+  if (UP) {
+    const double cff = f0 + f1 - HDELTA * (w2a + w2b);
+    return 0.25 * (cff * (u0 + u1) - HGAMMA * (DMAX(cff, 0.0) * w1a + DMIN(cff, 0.0) * w1b));
+  } else
+    return 0.25 * (u0 + u1 - HDELTA * (w1a + w1b)) * (f0 + f1 - HDELTA * (w2a + w2b));
+}
+// cross-axis flux at psi point c: UFe (u advected by FlxV: du=SX, df=1) / VFx (v advected by FlxU: du=1, df=SX)
+template <bool UP>
+__device__ __forceinline__ double flux_cross(const KP& p, const double* __restrict__ u, const double* __restrict__ Flx, long c, long du, long df, int k) {
+  // u second differences along du at c and c-du; Flx second differences along df at c and c-df
+  const double ua = R3(u, c - 2 * du, k), ub = R3(u, c - du, k), uc = R3(u, c, k), ud = R3(u, c + du, k);
+  const double w1m = ua - 2.0 * ub + uc, w1c = ub - 2.0 * uc + ud;     // wrk1(c-du), wrk1(c)
+  const double fa = R3(Flx, c - 2 * df, k), fb = R3(Flx, c - df, k), fc = R3(Flx, c, k), fd = R3(Flx, c + df, k);
+  const double w2m = fa - 2.0 * fb + fc, w2c = fb - 2.0 * fc + fd;     // wrk2(c-df), wrk2(c)
+  if (UP) {
+    const double cff = fc + fb - HDELTA * (w2c + w2m);
+    return 0.25 * (cff * (uc + ub) - HGAMMA * (DMAX(cff, 0.0) * w1m + DMIN(cff, 0.0) * w1c));
+  } else
+    return 0.25 * (uc + ub - HDELTA * (w1c + w1m)) * (fc + fb - HDELTA * (w2c + w2m));
+}
+template <bool UP>
+__global__ void k_rhs_uv_horiz(const __grid_constant__ KP p, const double* __restrict__ u, const double* __restrict__ v) {
+  THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
+  const int k = blockIdx.z + 1;
+  // Coriolis (no CURVGRID): compute_horiz_rhs_uv_terms.h:4-45
+  const double cf0 = 0.5 * R3(p.Hz, c, k) * (p.fomn[c]);
+  const double cfw = 0.5 * R3(p.Hz, c - 1, k) * (p.fomn[c - 1]);
+  const double cfs = 0.5 * R3(p.Hz, c - SX, k) * (p.fomn[c - SX]);
+  const double v00 = R3(v, c, k), u00 = R3(u, c, k);
+  const double UFx_c = cf0 * (v00 + R3(v, c + SX, k));
+  const double UFx_w = cfw * (R3(v, c - 1, k) + R3(v, c - 1 + SX, k));
+  const double VFe_c = cf0 * (u00 + R3(u, c + 1, k));
+  const double VFe_s = cfs * (R3(u, c - SX, k) + R3(u, c - SX + 1, k));
+  double ru = R3(p.ru, c, k) + 0.5 * (UFx_c + UFx_w);
+  double rv = R3(p.rv, c, k) - 0.5 * (VFe_c + VFe_s);
+  // advection
+  const double UFx_i = flux_along<UP>(p, u, p.FlxU, c, 1, k), UFx_im = flux_along<UP>(p, u, p.FlxU, c - 1, 1, k);
+  const double UFe_jp = flux_cross<UP>(p, u, p.FlxV, c + SX, SX, 1, k), UFe_j = flux_cross<UP>(p, u, p.FlxV, c, SX, 1, k);
+  ru = ru - UFx_i + UFx_im - UFe_jp + UFe_j;
+  const double VFx_ip = flux_cross<UP>(p, v, p.FlxU, c + 1, 1, SX, k), VFx_i = flux_cross<UP>(p, v, p.FlxU, c, 1, SX, k);
+  const double VFe_j = flux_along<UP>(p, v, p.FlxV, c, SX, k), VFe_jm = flux_along<UP>(p, v, p.FlxV, c - SX, SX, k);
+  rv = rv - VFx_ip + VFx_i - VFe_j + VFe_jm;
+  R3(p.ru, c, k) = ru;
+  R3(p.rv, c, k) = rv;
+}
+
+// compute_horiz_tracer_fluxes.h:1-246: FX at u-point c (d=1, FlxU, umask) or FE at v-point c (d=SX)
+template <bool UP>
+__device__ __forceinline__ double tflux(const KP& p, const double* __restrict__ t, const double* __restrict__ Flx, const double* __restrict__ msk, long c, long d, int k) {
+  const double t0 = R3(t, c - 2 * d, k), t1 = R3(t, c - d, k), t2 = R3(t, c, k), t3 = R3(t, c + d, k);
+  const double Fa = (t1 - t0) * msk[c - d], Fb = (t2 - t1) * msk[c], Fc = (t3 - t2) * msk[c + d];  // FX(c-d), FX(c), FX(c+d)
+  const double fl = R3(Flx, c, k);
+  if (UP) {
+    const double wm = Fb - Fa, wc = Fc - Fb;   // wrk1(c-d), wrk1(c)
+    return 0.5 * (t2 + t1) * fl - 0.1666666666666666 * (wm * DMAX(fl, 0.0) + wc * DMIN(fl, 0.0));
+  } else {
+    const double wm = 0.5 * (Fb + Fa), wc = 0.5 * (Fc + Fb);
+    return 0.5 * (t2 + t1 - 0.3333333333333333 * (wc - wm)) * fl;
+  }
+}
+
+// pre_step3d4S.F:138-147: FlxDiv such that Hz_bak = Hz + FlxDiv, Hz_fwd = Hz - FlxDiv
+__global__ void k_pre_flxdiv(const __grid_constant__ KP p, double dtau) {
+  THREAD_IJ(p.istr - 1, p.iend, p.jstr - 1, p.jend)
+  const int k = blockIdx.z + 1;
+  const double cff = 0.5 * dtau;
+  R3(p.FlxDiv, c, k) = cff * p.pm[c] * p.pn[c] *
+                       (R3(p.FlxU, c + 1, k) - R3(p.FlxU, c, k) + R3(p.FlxV, c + SX, k) - R3(p.FlxV, c, k) + RW(p.We, c, k) + RW(p.Wi, c, k) -
+                        RW(p.We, c, k - 1) - RW(p.Wi, c, k - 1));
+}
+// pre_step3d4S.F:152-168: tracer predictor, horizontal part (C4), and t(indx)=Hz*t(nstp)
+__global__ void k_pre_t_horiz(const __grid_constant__ KP p, const double* __restrict__ t_rhs, double* __restrict__ t_new, const double* __restrict__ t_stp,
+                              double* __restrict__ t_indx, double dtau, double cf_stp, double cf_bak) {
+  THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
+  const int k = blockIdx.z + 1;
+  const double FXi = tflux<false>(p, t_rhs, p.FlxU, p.umask, c, 1, k), FXip = tflux<false>(p, t_rhs, p.FlxU, p.umask, c + 1, 1, k);
+  const double FEj = tflux<false>(p, t_rhs, p.FlxV, p.vmask, c, SX, k), FEjp = tflux<false>(p, t_rhs, p.FlxV, p.vmask, c + SX, SX, k);
+  const double Hz = R3(p.Hz, c, k), Hz_bak = Hz + R3(p.FlxDiv, c, k);
+  const double ts = R3(t_stp, c, k);
+  R3(t_new, c, k) = Hz_bak * (cf_stp * ts + cf_bak * R3(t_indx, c, k)) - dtau * p.pm[c] * p.pn[c] * (FXip - FXi + FEjp - FEj);
+  R3(t_indx, c, k) = Hz * ts;
+}
+// step3d_t_ISO.F:196-213: tracer corrector, horizontal part (UP3)
+__global__ void k_t_horiz(const __grid_constant__ KP p, const double* __restrict__ t_rhs, double* __restrict__ t_new) {
+  THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
+  const int k = blockIdx.z + 1;
+  const double FXi = tflux<true>(p, t_rhs, p.FlxU, p.umask, c, 1, k), FXip = tflux<true>(p, t_rhs, p.FlxU, p.umask, c + 1, 1, k);
+  const double FEj = tflux<true>(p, t_rhs, p.FlxV, p.vmask, c, SX, k), FEjp = tflux<true>(p, t_rhs, p.FlxV, p.vmask, c + SX, SX, k);
+  R3(t_new, c, k) = R3(t_new, c, k) - p.dt * p.pm[c] * p.pn[c] * (FXip - FXi + FEjp - FEj);
+}
+
+// compute_rd_bott_drag.h:1-74 (log-layer drag when Zob>0, else linear rdrg capped by 0.8*Hz/dt)
+__global__ void k_rd_bott_drag(const __grid_constant__ KP p, const double* __restrict__ u, const double* __restrict__ v) {
+  THREAD_IJ(p.istr - 1, p.iend, p.jstr - 1, p.jend)
+  const double vonKar = 0.41;
+  if (p.Zob > 0.0) {
+    const double u0 = R3(u, c, 1), u1 = R3(u, c + 1, 1), v0 = R3(v, c, 1), v1 = R3(v, c + SX, 1);
+    const double cff = sqrt(0.333333333333 * (u0 * u0 + u1 * u1 + u0 * u1 + v0 * v0 + v1 * v1 + v0 * v1));
+    const double lg = vonKar / log(1.0 + 0.5 * R3(p.Hz, c, 1) / p.Zob);
+    p.r_D[c] = cff * (lg * lg);
+  } else {
+    p.r_D[c] = DMIN(p.rdrg, 0.8 * R3(p.Hz, c, 1) / p.dt);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Tracer column kernel: compute_vert_tracer_fluxes.h:1-140 (SPLINE_TS) + flux divergence + implicit
+// vertical diffusion/advection Thomas solve.  MODE 0: predictor (pre_step3d4S.F:201-263, dtau, Hz_fwd);
+// MODE 1: corrector (step3d_t_ISO.F:907-1100: dt, Hz, swflx/stflx at the surface, rmask).
+// Four sweeps (up, down, up, down) with two shared-memory arrays per thread:
+//   A: spline CF(2:N)            -> Thomas CF(1:N-1)
+//   B: spline FC(0:N-1) -> rhs(1:N) -> Thomas DC(1:N-1)
+template <int MODE>
+__global__ void k_t_vert(const __grid_constant__ KP p, const double* __restrict__ t_rhs, double* __restrict__ t_new, const double* __restrict__ Akt,
+                         const double* __restrict__ stflx, double dtau, int is_temp) {
+  extern __shared__ double smem[];
+  THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
+  ColScr sc = col_scratch(p, c, smem);
+  const int N = p.N;
+  // spline forward elimination
+  double Hzk = R3(p.Hz, c, 1), tk = R3(t_rhs, c, 1);
+  double CFk = 1.0, FCkm = 2.0 * tk;
+  S(1, 0) = FCkm;
+  for (int k = 1; k <= N - 1; ++k) {
+    const double Hzp = R3(p.Hz, c, k + 1), tp = R3(t_rhs, c, k + 1);
+    const double cff = 1.0 / (2.0 * Hzk + Hzp * (2.0 - CFk));
+    CFk = cff * Hzk;                       // CF(k+1)
+    FCkm = cff * (3.0 * (Hzk * tp + Hzp * tk) - Hzp * FCkm);   // FC(k)
+    S(0, k + 1) = CFk;
+    S(1, k) = FCkm;
+    Hzk = Hzp; tk = tp;
+  }
+  // back-substitution, vertical flux and its divergence -> rhs(k) in B
+  const double cdt = dtau * p.pm[c] * p.pn[c];
+  double FCs_p = (2.0 * tk - FCkm) / (1.0 - CFk);   // FC(N) spline value
+  double flux_p = 0.0;                               // FC(N)=0 after the sweep
+  for (int k = N - 1; k >= 0; --k) {
+    double FCs = 0.0, flux = 0.0;                        // FC(0) of the spline is never used (flux(0)=0)
+    if (k >= 1) { FCs = S(1, k) - S(0, k + 1) * FCs_p; flux = FCs * RW(p.We, c, k); }
+    // rhs(k+1) = t_new(k+1) - cdt*(flux(k+1)-flux(k))
+    double r = R3(t_new, c, k + 1) - cdt * (flux_p - flux);
+    if (MODE == 1 && k + 1 == N) {
+      if (is_temp) r = r + p.dt * p.swflx[c] * r / R3(p.Hz, c, N);
+      r = r + p.dt * stflx[c];
+    }
+    S(1, k + 1) = r;
+    FCs_p = FCs; flux_p = flux;
+  }
+  // Thomas forward elimination (k upward)
+  const double DC0 = cdt;
+  double Hzf1 = R3(p.Hz, c, 1), Hzf2 = R3(p.Hz, c, 2);
+  if (MODE == 0) { Hzf1 -= R3(p.FlxDiv, c, 1); Hzf2 -= R3(p.FlxDiv, c, 2); }
+  double FCt = 2.0 * dtau * RW(Akt, c, 1) / (MODE == 0 ? (Hzf2 + Hzf1) : (Hzf1 + Hzf2));
+  double WC = DC0 * RW(p.Wi, c, 1);
+  double cff = 1.0 / (Hzf1 + FCt + DMAX(WC, 0.0));
+  double CFt = cff * (FCt - DMIN(WC, 0.0));
+  double DCt = cff * S(1, 1);
+  S(0, 1) = CFt; S(1, 1) = DCt;
+  double Hzfk = Hzf2;
+  for (int k = 2; k <= N - 1; ++k) {
+    double Hzfp = R3(p.Hz, c, k + 1);
+    if (MODE == 0) Hzfp -= R3(p.FlxDiv, c, k + 1);
+    const double FCtk = 2.0 * dtau * RW(Akt, c, k) / (MODE == 0 ? (Hzfp + Hzfk) : (Hzfk + Hzfp));
+    const double WCk = DC0 * RW(p.Wi, c, k);
+    cff = 1.0 / (Hzfk + FCtk + DMAX(WCk, 0.0) + FCt - DMIN(WC, 0.0) - CFt * (FCt + DMAX(WC, 0.0)));
+    const double CFtk = cff * (FCtk - DMIN(WCk, 0.0));
+    DCt = cff * (S(1, k) + DCt * (FCt + DMAX(WC, 0.0)));
+    S(0, k) = CFtk; S(1, k) = DCt;
+    CFt = CFtk; FCt = FCtk; WC = WCk; Hzfk = Hzfp;
+  }
+  const double rm = MODE == 1 ? p.rmask[c] : 1.0;
+  double tkp = (S(1, N) + DCt * (FCt + DMAX(WC, 0.0))) / (Hzfk + FCt - DMIN(WC, 0.0) - CFt * (FCt + DMAX(WC, 0.0)));
+  if (MODE == 1) tkp = tkp * rm;
+  R3(t_new, c, N) = tkp;
+  for (int k = N - 1; k >= 1; --k) {
+    tkp = S(1, k) + S(0, k) * tkp;
+    if (MODE == 1) tkp = tkp * rm;
+    R3(t_new, c, k) = tkp;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Momentum column kernel: compute_vert_rhs_uv_terms.h:1-188 (SPLINE_UV vertical advection) fused with
+// the implicit vertical viscosity/advection Thomas solve.  DIR 0: u, 1: v.
+// MODE 0: predictor (pre_step3d4S.F:276-488): rhs from Hz_bak*(cf_stp*u(nstp)+cf_bak*u(indx)), Hz_fwd,
+//         dtau; also u(indx) = Hz_u*u(nstp).
+// MODE 1: corrector (step3d_uv1.F:136-280): rhs = u(nnew) [=Hz_u*u(nstp)] + dt*..*ru, Hz, dt, bottom
+//         drag r_D, output Hz_u*u and the barotropic forcing rufrc/rvfrc.
+// Sweeps: up (spline elimination), down (spline back-substitution + final ru + Thomas elimination),
+// up (Thomas back-substitution).  A: spline CF(2:N) -> Thomas CF(k-1) in slot k; B: spline FC(0:N-1) -> DC(2:N).
+template <int MODE, int DIR>
+__global__ void k_uv_vert(const __grid_constant__ KP p, const double* __restrict__ u_rhs, double* __restrict__ u_new, const double* __restrict__ u_stp,
+                          double* __restrict__ u_indx, double dtau, double cf_stp, double cf_bak) {
+  extern __shared__ double smem[];
+  THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
+  ColScr sc = col_scratch(p, c, smem);
+  const int N = p.N;
+  const long d = DIR == 0 ? 1 : SX;
+  double* r = DIR == 0 ? p.ru : p.rv;
+  const double* msk = DIR == 0 ? p.umask : p.vmask;
+  const double strs = DIR == 0 ? p.sustr[c] : p.svstr[c];
+  // spline elimination (upward)
+#define HZ4(k) (0.5625 * (R3(p.Hz, c, k) + R3(p.Hz, c - d, k)) - 0.0625 * (R3(p.Hz, c + d, k) + R3(p.Hz, c - 2 * d, k)))
+  double DCk = HZ4(1), uk = R3(u_rhs, c, 1);
+  double CFk = 1.0, FCkm = 2.0 * uk;
+  S(1, 0) = FCkm;
+  for (int k = 1; k <= N - 1; ++k) {
+    const double DCp = HZ4(k + 1), up = R3(u_rhs, c, k + 1);
+    const double cff = 1.0 / (2.0 * DCk + DCp * (2.0 - CFk));
+    CFk = cff * DCk;
+    FCkm = cff * (3.0 * (DCk * up + DCp * uk) - DCp * FCkm);
+    S(0, k + 1) = CFk;
+    S(1, k) = FCkm;
+    DCk = DCp; uk = up;
+  }
+#undef HZ4
+  // downward: spline back-substitution -> vertical flux DCf(k) -> ru(k+1) final -> Thomas row k+1
+  const double mp = msk[c + d], mm = msk[c - d];
+  const double DC0 = dtau * 0.25 * (p.pm[c] + p.pm[c - d]) * (p.pn[c] + p.pn[c - d]);
+  double FCs_p = (2.0 * uk - FCkm) / (1.0 - CFk);   // FC(N)
+  double DCf_p = 0.0;                                // DC(N)=0
+  // Thomas state carried downward
+  double FCt_k = 0, WC_k = 0, CFt_k = 0, DCt_kp = 0;   // FC(k), WC(k), CF(k), DC(k+1) of the row above
+#define HZF(cc, k) (MODE == 0 ? (R3(p.Hz, cc, k) - R3(p.FlxDiv, cc, k)) : R3(p.Hz, cc, k))
+  double Hzf_c = HZF(c, N), Hzf_d = HZF(c - d, N);     // level k+1 (row being eliminated)
+  for (int k = N - 1; k >= 0; --k) {
+    double DCf = 0.0;
+    if (k >= 1) {
+      const double FCs = S(1, k) - S(0, k + 1) * FCs_p;
+      const double We0 = RW(p.We, c, k), Wem = RW(p.We, c - d, k);
+      DCf = FCs * 0.5 * (We0 + Wem - 0.125 * ((RW(p.We, c + d, k) - We0) * mp - (Wem - RW(p.We, c - 2 * d, k)) * mm));
+      FCs_p = FCs;
+    }
+    const int kk = k + 1;   // row whose final ru is now known
+    const double ruf = (k >= 1) ? (R3(r, c, kk) - DCf_p + DCf) : (R3(r, c, 1) - DCf_p);
+    if (MODE == 1) R3(r, c, kk) = ruf;   // kept for the ascending rufrc sum (step3d_uv1.F:194-206)
+    DCf_p = DCf;
+    // right-hand side of row kk
+    double rhs;
+    if (MODE == 0) {
+      const double us = R3(u_stp, c, kk);
+      const double Hz_c = R3(p.Hz, c, kk), Hz_d = R3(p.Hz, c - d, kk);
+      const double Hzb = 0.5 * ((Hz_c + R3(p.FlxDiv, c, kk)) + (Hz_d + R3(p.FlxDiv, c - d, kk)));
+      rhs = Hzb * (cf_stp * us + cf_bak * R3(u_indx, c, kk)) + DC0 * ruf;
+      R3(u_indx, c, kk) = 0.5 * (Hz_c + Hz_d) * us;
+    } else {
+      rhs = R3(u_new, c, kk) + DC0 * ruf;
+    }
+    if (kk == 1) {
+      // bottom row: solve for u(1)
+      const double rD = 0.5 * dtau * (p.r_D[c] + p.r_D[c - d]);
+      double u1 = (rhs + DCt_kp * (FCt_k - DMIN(WC_k, 0.0))) /
+                  (0.5 * (Hzf_c + Hzf_d) + rD + FCt_k + DMAX(WC_k, 0.0) - CFt_k * (FCt_k - DMIN(WC_k, 0.0)));
+      S(1, 1) = u1;
+      break;
+    }
+    // coefficients between rows kk-1 and kk
+    const double Hzf_cm = HZF(c, kk - 1), Hzf_dm = HZF(c - d, kk - 1);
+    const double FCt_m = 2.0 * dtau * (RW(p.Akv, c, kk - 1) + RW(p.Akv, c - d, kk - 1)) / (Hzf_c + Hzf_d + Hzf_cm + Hzf_dm);
+    const double WC_m = DC0 * 0.5 * (RW(p.Wi, c, kk - 1) + RW(p.Wi, c - d, kk - 1));
+    double cff, DCt;
+    if (kk == N) {
+      cff = 1.0 / (0.5 * (Hzf_c + Hzf_d) + FCt_m - DMIN(WC_m, 0.0));
+      DCt = cff * (rhs + dtau * strs);
+    } else {
+      cff = 1.0 / (0.5 * (Hzf_c + Hzf_d) + FCt_m - DMIN(WC_m, 0.0) + FCt_k + DMAX(WC_k, 0.0) - CFt_k * (FCt_k - DMIN(WC_k, 0.0)));
+      DCt = cff * (rhs + DCt_kp * (FCt_k - DMIN(WC_k, 0.0)));
+    }
+    const double CFt_m = cff * (FCt_m + DMAX(WC_m, 0.0));
+    S(0, kk) = CFt_m;         // Thomas CF(kk-1) goes to slot A(kk): spline CF(kk) was consumed above, A(kk-1) is still live
+    S(1, kk) = DCt;           // Thomas DC(kk): spline FC(kk) is dead
+    FCt_k = FCt_m; WC_k = WC_m; CFt_k = CFt_m; DCt_kp = DCt;
+    Hzf_c = Hzf_cm; Hzf_d = Hzf_dm;
+  }
+#undef HZF
+  // upward back-substitution
+  double uprev = S(1, 1);
+  if (MODE == 0) {
+    R3(u_new, c, 1) = uprev;
+    for (int k = 2; k <= N; ++k) {
+      uprev = S(1, k) + S(0, k) * uprev;
+      R3(u_new, c, k) = uprev;
+    }
+  } else {
+    const double dmn = DIR == 0 ? p.dm_u[c] * p.dn_u[c] : p.dm_v[c] * p.dn_v[c];
+    double* rfrc = DIR == 0 ? p.rufrc : p.rvfrc;
+    R3(u_new, c, 1) = uprev * 0.5 * (R3(p.Hz, c, 1) + R3(p.Hz, c - d, 1));
+    double rf = R3(r, c, 1) + dmn * (strs - 0.5 * (p.r_D[c - d] + p.r_D[c]) * uprev);
+    for (int k = 2; k <= N; ++k) {
+      uprev = S(1, k) + S(0, k) * uprev;
+      R3(u_new, c, k) = uprev * 0.5 * (R3(p.Hz, c, k) + R3(p.Hz, c - d, k));
+      rf = rf + R3(r, c, k);
+    }
+    rfrc[c] = rf;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// step2d_FB.F:24-576, stage 1: zeta_new over [istr-1:iend]x[jstr-1:jend] (kept in a private plane),
+// zeta(knew) and the fast-time averages Zt_avg1, DU_avg2, DV_avg2 (+ DU_avg_bak on the first substep)
+// on the interior.  DUon/DVom of the reference are recomputed in registers.
+struct S2D {
+  const double *zs, *zb, *zo, *us, *ub, *uo, *vs, *vb, *vo;   // kstp, kbak, kold levels
+  double *zn, *un, *vn;                                       // knew
+  double fwd, fwd1, fwd2, bkw_new, bkw, bkw1, bkw2, w1, w2;
+  int iif, nfast;
+};
+__device__ __forceinline__ double s2d_Drhs(const KP& p, const S2D& s, long c) { return p.h[c] + s.fwd * s.zs[c] + s.fwd1 * s.zb[c] + s.fwd2 * s.zo[c]; }
+__device__ __forceinline__ double s2d_DUon(const KP& p, const S2D& s, long c) {
+  const double urhs = s.fwd * s.us[c] + s.fwd1 * s.ub[c] + s.fwd2 * s.uo[c];
+  return 0.5 * (s2d_Drhs(p, s, c) + s2d_Drhs(p, s, c - 1)) * p.dn_u[c] * (urhs);
+}
+__device__ __forceinline__ double s2d_DVom(const KP& p, const S2D& s, long c) {
+  const double vrhs = s.fwd * s.vs[c] + s.fwd1 * s.vb[c] + s.fwd2 * s.vo[c];
+  return 0.5 * (s2d_Drhs(p, s, c) + s2d_Drhs(p, s, c - p.SX)) * p.dm_v[c] * (vrhs);
+}
+__global__ void k_step2d_zeta(const __grid_constant__ KP p, const __grid_constant__ S2D s) {
+  THREAD_IJ(p.istr - 1, p.iend, p.jstr - 1, p.jend)
+  const double DUon = s2d_DUon(p, s, c), DUon1 = s2d_DUon(p, s, c + 1), DVom = s2d_DVom(p, s, c), DVom1 = s2d_DVom(p, s, c + SX);
+  double zn = s.zs[c] + p.dtfast * p.pm[c] * p.pn[c] * (DUon - DUon1 + DVom - DVom1) + p.dtfast * p.swflx[c];
+  zn = zn * p.rmask[c];
+  p.zeta_new[c] = zn;
+  if (i >= p.istr && j >= p.jstr) {
+    s.zn[c] = zn;
+    if (s.iif == 1) {
+      p.DU_avg_bak[c] = p.DU_avg1[c] - 0.1024390243902439 * p.DU_avg2[c];
+      p.DV_avg_bak[c] = p.DV_avg1[c] - 0.1024390243902439 * p.DV_avg2[c];
+      p.Zt_avg1[c] = s.w1 * zn;
+      p.DU_avg1[c] = 0.0;
+      p.DV_avg1[c] = 0.0;
+      p.DU_avg2[c] = s.w2 * DUon;
+      p.DV_avg2[c] = s.w2 * DVom;
+    } else {
+      p.Zt_avg1[c] = p.Zt_avg1[c] + s.w1 * zn;
+      p.DU_avg2[c] = p.DU_avg2[c] + s.w2 * DUon;
+      p.DV_avg2[c] = p.DV_avg2[c] + s.w2 * DVom;
+    }
+  }
+}
+// stage 2: pressure-gradient terms rubar,rvbar (step2d_FB.F:245-268, first-substep correction :313-384),
+// ubar,vbar(knew), DU_avg1/DV_avg1; on the last substep zeta(knew)=Zt_avg1 (:563).
+struct S2Pt { double UFx, UFe, VFx, VFe; };
+__device__ __forceinline__ S2Pt s2d_pt(const KP& p, const S2D& s, long c, bool corr) {
+  S2Pt r;
+  const double zn = p.zeta_new[c], zs = s.zs[c];
+  if (!corr) {
+    r.UFx = s.bkw_new * zn + s.bkw * zs + s.bkw1 * s.zb[c] + s.bkw2 * s.zo[c];
+    r.UFe = (1.0 + p.rhoS[c]) * r.UFx;
+    r.VFx = r.UFx * (p.rhoS[c] - p.rhoA[c]);
+    r.VFe = r.UFe * r.UFx;
+  } else {
+    r.UFx = zn - zs;
+    r.UFe = (1.0 + p.rhoS[c]) * r.UFx;
+    r.VFe = r.UFe * (zn + zs);
+    r.VFx = r.UFx * (p.rhoS[c] - p.rhoA[c]);
+  }
+  return r;
+}
+__device__ __forceinline__ double s2d_pgf(const KP& p, double cff, double dn, long c, long d, const S2Pt& a, const S2Pt& b) {
+  // a at c-d, b at c
+  return cff * dn *
+         ((p.h[c - d] + p.h[c]) * (a.UFe - b.UFe) + a.VFe - b.VFe +
+          (p.h[c - d] - p.h[c]) * (a.VFx + b.VFx + 0.333333333333 * (p.rhoA[c - d] - p.rhoA[c]) * (a.UFx - b.UFx)));
+}
+__global__ void k_step2d_uv(const __grid_constant__ KP p, const __grid_constant__ S2D s) {
+  THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
+  const double cffg = 0.5 * p.g;
+  const S2Pt a0 = s2d_pt(p, s, c, false), aw = s2d_pt(p, s, c - 1, false), as = s2d_pt(p, s, c - SX, false);
+  double rubar = s2d_pgf(p, cffg, p.dn_u[c], c, 1, aw, a0);
+  double rvbar = s2d_pgf(p, cffg, p.dm_v[c], c, SX, as, a0);
+  double rufrc = p.rufrc[c], rvfrc = p.rvfrc[c];
+  if (s.iif == 1) {
+    rufrc = rufrc - rubar;
+    rvfrc = rvfrc - rvbar;
+    p.rufrc[c] = rufrc;
+    p.rvfrc[c] = rvfrc;
+    const S2Pt b0 = s2d_pt(p, s, c, true), bw = s2d_pt(p, s, c - 1, true), bs = s2d_pt(p, s, c - SX, true);
+    rubar = rubar + s2d_pgf(p, cffg, p.dn_u[c], c, 1, bw, b0);
+    rvbar = rvbar + s2d_pgf(p, cffg, p.dm_v[c], c, SX, bs, b0);
+  }
+  const double D0 = s.zs[c] + p.h[c], Dw = s.zs[c - 1] + p.h[c - 1], Ds = s.zs[c - SX] + p.h[c - SX];
+  const double Dn0 = p.zeta_new[c] + p.h[c], Dnw = p.zeta_new[c - 1] + p.h[c - 1], Dns = p.zeta_new[c - SX] + p.h[c - SX];
+  const double cff = 0.5 * p.dtfast, cff1 = 0.5 * s.w1;
+  const double DUnew = ((D0 + Dw) * s.us[c] + cff * (p.pm[c] + p.pm[c - 1]) * (p.pn[c] + p.pn[c - 1]) * (rubar + rufrc)) * p.umask[c];
+  s.un[c] = DUnew / (Dn0 + Dnw);
+  p.DU_avg1[c] = p.DU_avg1[c] + cff1 * p.dn_u[c] * (DUnew);
+  const double DVnew = ((D0 + Ds) * s.vs[c] + cff * (p.pm[c] + p.pm[c - SX]) * (p.pn[c] + p.pn[c - SX]) * (rvbar + rvfrc)) * p.vmask[c];
+  s.vn[c] = DVnew / (Dn0 + Dns);
+  p.DV_avg1[c] = p.DV_avg1[c] + cff1 * p.dm_v[c] * (DVnew);
+  if (s.iif == s.nfast) s.zn[c] = p.Zt_avg1[c];
+}
+
+// ------------------------------------------------------------------------------------------------
+// step3d_uv2.F:18-786.  PASS 0 (:244-268): u <- (u/Hz_u - vertical-mean mismatch vs DU_avg1)*umask.
+// PASS 1 (:521-577): ubar(knew)=DU_avg1/D, re-correct u, FlxU <- DELTA*FlxU+EPSIL*DC*(u(nstp)+u(nnew))
+// minus its mismatch with DU_avg2.  Column kernels without scratch (re-read through L1/L2).
+template <int DIR>
+__global__ void k_uv2_pass0(const __grid_constant__ KP p, double* __restrict__ u) {
+  THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
+  const long d = DIR == 0 ? 1 : SX;
+  const int N = p.N;
+  const double dn = DIR == 0 ? p.dn_u[c] : p.dm_v[c];
+  const double msk = DIR == 0 ? p.umask[c] : p.vmask[c];
+  const double Davg1 = DIR == 0 ? p.DU_avg1[c] : p.DV_avg1[c];
+  double CF0 = 0.5 * (R3(p.Hz, c, N) + R3(p.Hz, c - d, N));
+  double DC0 = R3(u, c, N);
+  R3(u, c, N) = DC0 / CF0;
+  for (int k = N - 1; k >= 1; --k) {
+    const double cff = 0.5 * (R3(p.Hz, c, k) + R3(p.Hz, c - d, k));
+    CF0 = CF0 + cff;
+    const double uk = R3(u, c, k);
+    DC0 = DC0 + uk;
+    R3(u, c, k) = uk / cff;
+  }
+  DC0 = (DC0 * dn - Davg1) / (CF0 * dn);
+  for (int k = 1; k <= N; ++k) R3(u, c, k) = (R3(u, c, k) - DC0) * msk;
+}
+template <int DIR>
+__global__ void k_uv2_pass1(const __grid_constant__ KP p, double* __restrict__ u, const double* __restrict__ u_stp, double* __restrict__ bar) {
+  THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
+  const long d = DIR == 0 ? 1 : SX;
+  const int N = p.N;
+  const double dn = DIR == 0 ? p.dn_u[c] : p.dm_v[c];
+  const double msk = DIR == 0 ? p.umask[c] : p.vmask[c];
+  const double Davg1 = DIR == 0 ? p.DU_avg1[c] : p.DV_avg1[c];
+  const double Davg2 = DIR == 0 ? p.DU_avg2[c] : p.DV_avg2[c];
+  double* Flx = DIR == 0 ? p.FlxU : p.FlxV;
+  double DCN = 0.5 * (R3(p.Hz, c, N) + R3(p.Hz, c - d, N)) * dn;
+  double DC0 = DCN;
+  double FC0 = DCN * R3(u, c, N);
+  for (int k = N - 1; k >= 1; --k) {
+    const double DCk = 0.5 * (R3(p.Hz, c, k) + R3(p.Hz, c - d, k)) * dn;
+    DC0 = DC0 + DCk;
+    FC0 = FC0 + DCk * R3(u, c, k);
+  }
+  DC0 = 1.0 / DC0;
+  bar[c] = DC0 * Davg1;
+  FC0 = DC0 * (FC0 - Davg1);
+  double CF0 = 0.0;
+  for (int k = N; k >= 1; --k) {
+    const double DCk = 0.5 * (R3(p.Hz, c, k) + R3(p.Hz, c - d, k)) * dn;
+    const double un = (R3(u, c, k) - FC0) * msk;
+    R3(u, c, k) = un;
+    const double CFk = 0.28 * R3(Flx, c, k) + 0.36 * DCk * (R3(u_stp, c, k) + un);
+    R3(Flx, c, k) = CFk;      // parked; corrected in the next loop
+    CF0 = CF0 + CFk;
+  }
+  CF0 = DC0 * (CF0 - Davg2);
+  for (int k = 1; k <= N; ++k) {
+    const double DCk = 0.5 * (R3(p.Hz, c, k) + R3(p.Hz, c - d, k)) * dn;
+    R3(Flx, c, k) = R3(Flx, c, k) - DCk * CF0;
+  }
+}
+
+// ------------------------------------------------------------------------------------------------
+// diag.F:50-658: per-column kinetic energy, barotropic KE, free-surface volume and max advective
+// Courant number.  Stage 1: vertical means ub,vb over [istr:iend+1]; stage 2: per-block partials.
+__global__ void k_diag_bar(const __grid_constant__ KP p, const double* __restrict__ u, const double* __restrict__ v, double* __restrict__ ub, double* __restrict__ vb) {
+  THREAD_IJ(p.istr, p.iend + 1, p.jstr, p.jend + 1)
+  const int N = p.N;
+  double a = (R3(p.Hz, c, N) + R3(p.Hz, c - 1, N)) * R3(u, c, N);
+  double b = (R3(p.Hz, c, N) + R3(p.Hz, c - SX, N)) * R3(v, c, N);
+  for (int k = N - 1; k >= 2; --k) {
+    a = a + (R3(p.Hz, c, k) + R3(p.Hz, c - 1, k)) * R3(u, c, k);
+    b = b + (R3(p.Hz, c, k) + R3(p.Hz, c - SX, k)) * R3(v, c, k);
+  }
+  ub[c] = (a + (R3(p.Hz, c, 1) + R3(p.Hz, c - 1, 1)) * R3(u, c, 1)) / (RW(p.z_w, c, N) + RW(p.z_w, c - 1, N) - RW(p.z_w, c, 0) - RW(p.z_w, c - 1, 0));
+  vb[c] = (b + (R3(p.Hz, c, 1) + R3(p.Hz, c - SX, 1)) * R3(v, c, 1)) / (RW(p.z_w, c, N) + RW(p.z_w, c - SX, N) - RW(p.z_w, c, 0) - RW(p.z_w, c - SX, 0));
+}
+// one thread per column writes its 5 values; the (deterministic) reduction is done on the host side
+// of the C ABI over the pulled planes -- diag runs every ninfo steps, outside the timed hot path.
+__global__ void k_diag_col(const __grid_constant__ KP p, const double* __restrict__ u, const double* __restrict__ v, const double* __restrict__ ub,
+                           const double* __restrict__ vb, double* __restrict__ o_ke, double* __restrict__ o_ke2b, double* __restrict__ o_vol,
+                           double* __restrict__ o_cx, double* __restrict__ o_cw) {
+  THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
+  const int N = p.N;
+  double v2 = 0.5 * (ub[c] * ub[c] + ub[c + 1] * ub[c + 1] + vb[c] * vb[c] + vb[c + SX] * vb[c + SX]);
+  const double ke2b = 0.5 * (RW(p.z_w, c, N) - RW(p.z_w, c, 0)) * v2;
+  double ke = 0.0, cxm = 0.0, cwm = 0.0;
+  for (int k = N; k >= 1; --k) {
+    const double u0 = R3(u, c, k), u1 = R3(u, c + 1, k), v0 = R3(v, c, k), v1 = R3(v, c + SX, k);
+    v2 = 0.5 * (u0 * u0 + u1 * u1 + v0 * v0 + v1 * v1);
+    const double Hz = R3(p.Hz, c, k);
+    const double ciV = p.dt * p.rmask[c] * p.pm[c] * p.pn[c] / Hz;
+    const double cw = ciV * (DMAX(RW(p.We, c, k) + RW(p.Wi, c, k), 0.0) - DMIN(RW(p.We, c, k - 1) + RW(p.Wi, c, k - 1), 0.0));
+    const double cx = cw + ciV * (DMAX(R3(p.FlxU, c + 1, k), 0.0) - DMIN(R3(p.FlxU, c, k), 0.0) + DMAX(R3(p.FlxV, c + SX, k), 0.0) - DMIN(R3(p.FlxV, c, k), 0.0));
+    if (cx > cxm) { cxm = cx; cwm = cw; }
+    ke = ke + 0.5 * v2 * Hz;
+  }
+  const double dA = p.rmask[c] / (p.pm[c] * p.pn[c]);
+  o_vol[c] = dA * RW(p.z_w, c, N);
+  o_ke[c] = dA * ke;
+  o_ke2b[c] = dA * ke2b;
+  o_cx[c] = cxm;
+  o_cw[c] = cwm;
+}
+
+// alfabeta.F:4-79
+__global__ void k_alfabeta(const __grid_constant__ KP p, const double* __restrict__ T, const double* __restrict__ Sal, double* __restrict__ alpha, double* __restrict__ beta) {
+  THREAD_IJ(p.istr - 2, p.iend + 2, p.jstr - 2, p.jend + 2)
+  const int N = p.N;
+  if (p.nonlin) {
+    const double r01 = 6.793952e-2, r02 = -9.095290e-3, r03 = +1.001685e-4, r04 = -1.120083e-6, r05 = +6.536332e-9, r10 = +0.824493,
+                 r11 = -4.08990e-3, r12 = +7.64380e-5, r13 = -8.24670e-7, r14 = +5.38750e-9, rS0 = -5.72466e-3, rS1 = +1.02270e-4,
+                 rS2 = -1.65460e-6, r20 = +4.8314e-4;
+    const double cff = 1.0 / p.rho0;
+    const double Tt = R3(T, c, N), Ts = R3(Sal, c, N), sqrtTs = sqrt(DMAX(0.0, Ts));
+    alpha[c] = -cff * (r01 + Tt * (2.0 * r02 + Tt * (3.0 * r03 + Tt * (4.0 * r04 + Tt * 5.0 * r05))) +
+                       Ts * (r11 + Tt * (2.0 * r12 + Tt * (3.0 * r13 + Tt * 4.0 * r14)) + sqrtTs * (rS1 + Tt * 2.0 * rS2)));
+    beta[c] = cff * (r10 + Tt * (r11 + Tt * (r12 + Tt * (r13 + Tt * r14))) + 1.5 * (rS0 + Tt * (rS1 + Tt * rS2)) * sqrtTs + 2.0 * r20 * Ts);
+  } else {
+    alpha[c] = fabs(p.Tcoef);
+    beta[c] = p.salinity ? fabs(p.Scoef) : 0.0;
+  }
+}

@@ -1,0 +1,41 @@
+// kp.h -- kernel parameter block and device indexing for libromsb200.
+//
+// HBM layout: every field keeps the reference's (i,j,k) order, i fastest, 2-cell halo
+// (set_global_definitions.h:146-150), but rows are padded so that interior point i=1 of every
+// row of every plane sits on a 128-byte boundary: element (i,j[,k]) lives at
+//   base[ (i + IOFF) + (j+1)*SX + kplane*SXY ],   IOFF = 15, SX = roundup(Lm+18, 16), SXY = SX*(Mm+4)
+// so a warp reading 32 consecutive i of one row touches exactly two 128-B lines.
+#pragma once
+#include <cstddef>
+
+#define IOFF 15
+#define MAXNT 40
+
+struct KP {
+  int Lm, Mm, N, NT;
+  int SX;            // padded row pitch (doubles)
+  long SXY;          // padded plane size (doubles)
+  int istr, iend, jstr, jend;   // compute_tile_bounds.h with NSUB_X=NSUB_E=1
+  int nonlin, salinity;
+  // scalars
+  double dt, dtfast, g, rho0, Tcoef, T0, Scoef, S0, rdrg, rdrg2, Zob, gamma2, hc;
+  // static 2-D
+  double *h, *pm, *pn, *f, *rmask, *umask, *vmask, *dm_u, *dn_u, *dm_v, *dn_v, *dm_r, *dn_r, *fomn, *hinv;
+  // 2-D state
+  double *rhoA, *rhoS, *rufrc, *rvfrc, *Zt_avg1, *DU_avg1, *DV_avg1, *DU_avg2, *DV_avg2, *DU_avg_bak, *DV_avg_bak, *r_D;
+  double *sustr, *svstr, *swflx;
+  // 3-D state
+  double *Hz, *z_r, *z_w, *FlxU, *FlxV, *We, *Wi, *rho1, *qp1, *Akv, *Akt[2], *ru, *rv;
+  // device-owned scratch (the reference's A3d(1,3:4) and A2d planes)
+  double *FlxDiv;    // Hz_bak = Hz + FlxDiv, Hz_fwd = Hz - FlxDiv (pre_step3d4S.F:138-147)
+  double *P, *rho;   // prsgrd.F:12 P and in-situ rho
+  double *scr;       // column scratch, 3 arrays of (N+1) planes (global-memory fallback)
+  double *zeta_new;  // step2d_FB.F private zeta_new
+  double *Cs_w, *Cs_r;   // scoord.F:38 (k=0:N, k=1:N at index k)
+  int use_smem;      // column scratch in shared memory ([k][thread]) instead of global
+};
+
+// column base index of (i,j) and relative addressing
+#define CIDX(i, j) ((long)((i) + IOFF) + (long)((j) + 1) * p.SX)
+#define R3(a, c, k) (a)[(c) + (long)((k)-1) * p.SXY]    // rho/u/v-type, k=1:N
+#define RW(a, c, k) (a)[(c) + (long)(k) * p.SXY]        // w-type, k=0:N

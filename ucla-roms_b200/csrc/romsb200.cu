@@ -1,0 +1,663 @@
+// romsb200.cu -- C ABI (include/roms_b200.h) of the B200-native UCLA-ROMS time step.
+//
+// Host side of the drop-in boundary: owns the device arena, moves fields between the Fortran
+// module arrays' layout and the padded HBM layout, keeps the loop-control scalars of scalars.F,
+// and exposes one export per reference tile subroutine (main.F:397-479 call order in roms_step).
+// There is no CPU fallback: every numerical export launches CUDA kernels or fails.
+#include <cuda_runtime.h>
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+#include "../../include/roms_b200.h"
+#include "kernels.cuh"
+#include "comm.h"
+
+static thread_local std::string g_err;
+#define CK(call)                                                                              \
+  do {                                                                                        \
+    cudaError_t e_ = (call);                                                                  \
+    if (e_ != cudaSuccess) {                                                                  \
+      g_err = std::string(#call) + ": " + cudaGetErrorString(e_);                             \
+      return -(int)e_;                                                                        \
+    }                                                                                         \
+  } while (0)
+
+struct FieldSlot {
+  std::vector<double*> ptr;   // [lvl*ntrc + itrc]
+  int nlvl = 1, ntrc = 1, nk = 1;
+};
+
+struct roms_ctx {
+  roms_cfg c;
+  int device;
+  KP kp;
+  cudaStream_t st;
+  FieldSlot f[ROMS_NFIELDS];
+  double* arena = nullptr;
+  size_t arena_doubles = 0;
+  // scratch planes for diag
+  double *d_ub, *d_vb, *d_o[5];
+  // scalars.F
+  int iic = 0, iif = 1, nstp = 1, nrhs = 1, nnew = 1, kstp = 1, knew = 1, ntstart = 1, forw_start = 1;
+  int nfast = 0;
+  std::vector<double> w1, w2, Cs_w, Cs_r;
+  long launches = 0;
+  int col_bx = 32, col_by = 2, pl_bx = 128, pl_by = 2;
+  int use_smem = 1;
+  Comm comm;
+  double* u(int l) { return f[ROMS_U].ptr[l - 1]; }
+  double* v(int l) { return f[ROMS_V].ptr[l - 1]; }
+  double* t(int l, int itrc) { return f[ROMS_T].ptr[(l - 1) * c.NT + (itrc - 1)]; }
+  double* zeta(int l) { return f[ROMS_ZETA].ptr[l - 1]; }
+  double* ubar(int l) { return f[ROMS_UBAR].ptr[l - 1]; }
+  double* vbar(int l) { return f[ROMS_VBAR].ptr[l - 1]; }
+};
+
+// ------------------------------------------------------------------------------------------------
+// launch geometry
+static dim3 grid_plane(const roms_ctx* h, int i1, int j0, int j1, int nk, dim3 b) {
+  return dim3((i1 + IOFF + 1 + b.x - 1) / b.x, (j1 - j0 + 1 + b.y - 1) / b.y, nk);
+}
+#define PLANE(kern, i1, j0, j1, nk, ...)                                                      \
+  do {                                                                                        \
+    dim3 b_(h->pl_bx, h->pl_by, 1);                                                           \
+    kern<<<grid_plane(h, i1, j0, j1, nk, b_), b_, 0, h->st>>>(__VA_ARGS__);                   \
+    h->launches++;                                                                            \
+  } while (0)
+static size_t col_smem(const roms_ctx* h, int narr) {
+  return h->use_smem ? (size_t)narr * (h->c.N + 1) * h->col_bx * h->col_by * sizeof(double) : 0;
+}
+#define COLUMN(kern, narr, i1, j0, j1, ...)                                                   \
+  do {                                                                                        \
+    dim3 b_(h->col_bx, h->col_by, 1);                                                         \
+    size_t sm_ = col_smem(h, narr);                                                           \
+    if (sm_ > 48 * 1024) CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_)); \
+    kern<<<grid_plane(h, i1, j0, j1, 1, b_), b_, sm_, h->st>>>(__VA_ARGS__);                  \
+    h->launches++;                                                                            \
+  } while (0)
+
+// ------------------------------------------------------------------------------------------------
+// set_scoord.F:4-66 and set_weights.F:7-246, evaluated on the host in the reference's operation order
+static double cs_curve(double sc, double theta_s, double theta_b) {
+  const double csrf = theta_s > 0.0 ? (1.0 - cosh(theta_s * sc)) / (cosh(theta_s) - 1.0) : -sc * sc;
+  return theta_b > 0.0 ? (exp(theta_b * csrf) - 1.0) / (1.0 - exp(-theta_b)) : csrf;
+}
+static void host_scoord(roms_ctx* h) {
+  const int N = h->c.N;
+  const double ds = 1.0 / double(N);
+  h->Cs_w.assign(N + 1, 0.0);
+  h->Cs_r.assign(N + 1, 0.0);
+  h->Cs_w[0] = -1.0;
+  for (int k = 1; k < N; ++k) h->Cs_w[k] = cs_curve(ds * double(k - N), h->c.theta_s, h->c.theta_b);
+  for (int k = 1; k <= N; ++k) h->Cs_r[k] = cs_curve(ds * (double(k - N) - 0.5), h->c.theta_s, h->c.theta_b);
+}
+static void host_weights(roms_ctx* h) {
+  const int nd = h->c.ndtfast;
+  std::vector<double>& a = h->w1;
+  std::vector<double>& b = h->w2;
+  a.assign(2 * nd + 2, 0.0);
+  b.assign(2 * nd + 2, 0.0);
+  const double p = 2.0, q = 4.0, r = 0.25;
+  double scale = (p + 1.0) * (p + q + 1.0) / ((p + 2.0) * (p + q + 2.0) * double(nd));
+  int nfast = 0;
+  auto moments = [&](double& sum, double& shft, bool iFirst) {
+    sum = 0.0; shft = 0.0;
+    for (int i = 1; i <= nfast; ++i) {
+      sum = sum + a[i];
+      shft = shft + (iFirst ? double(i) * a[i] : a[i] * double(i));
+    }
+  };
+  for (int iter = 0; iter < 16; ++iter) {            // shape function, 16 centring iterations
+    nfast = 0;
+    for (int i = 1; i <= 2 * nd; ++i) {
+      const double cff = scale * double(i);
+      a[i] = pow(cff, p) - pow(cff, p + q) - r * cff;
+      if (a[i] > 0.0) nfast = i;
+      if (nfast > 0 && a[i] < 0.0) a[i] = 0.0;
+    }
+    double sum, shft;
+    moments(sum, shft, false);
+    scale = scale * shft / (sum * double(nd));
+  }
+  for (int iter = 0; iter < nd; ++iter) {            // shift so that the centroid sits exactly at ndtfast
+    double sum, shft;
+    moments(sum, shft, true);
+    shft = shft / sum;
+    const double cff = double(nd) - shft;
+    if (cff > 1.0) {
+      nfast++;
+      for (int i = nfast; i >= 2; --i) a[i] = a[i - 1];
+      a[1] = 0.0;
+    } else if (cff > 0.0) {
+      const double s1 = 1.0 - cff;
+      for (int i = nfast; i >= 2; --i) a[i] = s1 * a[i] + cff * a[i - 1];
+      a[1] = s1 * a[1];
+    } else if (cff < -1.0) {
+      nfast--;
+      for (int i = 1; i <= nfast; ++i) a[i] = a[i + 1];
+      a[nfast + 1] = 0.0;
+    } else if (cff < 0.0) {
+      const double s1 = 1.0 + cff;
+      for (int i = 1; i <= nfast - 1; ++i) a[i] = s1 * a[i] - cff * a[i + 1];
+      a[nfast] = s1 * a[nfast];
+    }
+  }
+  for (int j = 1; j <= nfast; ++j)                   // secondary weights
+    for (int i = 1; i <= j; ++i) b[i] = b[i] + a[j];
+  double sa = 0.0, sb = 0.0;
+  for (int i = 1; i <= nfast; ++i) { sa = sa + a[i]; sb = sb + b[i]; }
+  sa = 1.0 / sa; sb = 1.0 / sb;
+  for (int i = 1; i <= nfast; ++i) { a[i] = sa * a[i]; b[i] = sb * b[i]; }
+  h->nfast = nfast;
+}
+
+// ------------------------------------------------------------------------------------------------
+static void slot(roms_ctx* h, int id, int nlvl, int ntrc, int nk) {
+  h->f[id].nlvl = nlvl; h->f[id].ntrc = ntrc; h->f[id].nk = nk;
+  h->f[id].ptr.assign((size_t)nlvl * ntrc, nullptr);
+}
+
+extern "C" {
+
+const char* roms_last_error(void) { return g_err.c_str(); }
+
+int roms_create(const roms_cfg* cfg, int device, roms_ctx** out) {
+  if (!cfg || !out) { g_err = "roms_create: null argument"; return -1; }
+  if (cfg->NT > MAXNT || cfg->N < 3 || cfg->Lm < 2 || cfg->Mm < 2) { g_err = "roms_create: unsupported sizes"; return -1; }
+  CK(cudaSetDevice(device));
+  roms_ctx* h = new roms_ctx();
+  h->c = *cfg;
+  h->device = device;
+  CK(cudaStreamCreateWithFlags(&h->st, cudaStreamNonBlocking));
+  const int N = cfg->N, NT = cfg->NT;
+  KP& p = h->kp;
+  memset(&p, 0, sizeof(p));
+  p.Lm = cfg->Lm; p.Mm = cfg->Mm; p.N = N; p.NT = NT;
+  p.SX = ((cfg->Lm + 18 + 15) / 16) * 16;
+  p.SXY = (long)p.SX * (cfg->Mm + 4);
+  p.istr = 1; p.iend = cfg->Lm; p.jstr = 1; p.jend = cfg->Mm;
+  p.nonlin = cfg->nonlin_eos; p.salinity = cfg->salinity;
+  p.dt = cfg->dt; p.dtfast = cfg->dt / double(cfg->ndtfast);
+  p.g = cfg->g; p.rho0 = cfg->rho0; p.Tcoef = cfg->Tcoef; p.T0 = cfg->T0; p.Scoef = cfg->Scoef; p.S0 = cfg->S0;
+  p.rdrg = cfg->rdrg; p.rdrg2 = cfg->rdrg2; p.Zob = cfg->Zob; p.gamma2 = cfg->gamma2; p.hc = cfg->hc;
+  if (const char* e = getenv("ROMS_COL_BX")) h->col_bx = atoi(e);
+  if (const char* e = getenv("ROMS_COL_BY")) h->col_by = atoi(e);
+  if (const char* e = getenv("ROMS_PL_BX")) h->pl_bx = atoi(e);
+  if (const char* e = getenv("ROMS_PL_BY")) h->pl_by = atoi(e);
+  if (const char* e = getenv("ROMS_COL_SMEM")) h->use_smem = atoi(e);
+  if ((size_t)2 * (N + 1) * h->col_bx * h->col_by * sizeof(double) > 200 * 1024) { h->col_by = 1; }
+  if ((size_t)2 * (N + 1) * h->col_bx * h->col_by * sizeof(double) > 200 * 1024) h->use_smem = 0;
+  p.use_smem = h->use_smem;
+
+  // field table
+  for (int id = 0; id < ROMS_NFIELDS; ++id) slot(h, id, 1, 1, 1);
+  slot(h, ROMS_ZETA, 4, 1, 1); slot(h, ROMS_UBAR, 4, 1, 1); slot(h, ROMS_VBAR, 4, 1, 1);
+  slot(h, ROMS_STFLX, 1, NT, 1);
+  slot(h, ROMS_U, 3, 1, N); slot(h, ROMS_V, 3, 1, N); slot(h, ROMS_T, 3, NT, N);
+  for (int id : {ROMS_HZ, ROMS_Z_R, ROMS_FLXU, ROMS_FLXV, ROMS_RHO1, ROMS_QP1, ROMS_RU, ROMS_RV}) slot(h, id, 1, 1, N);
+  for (int id : {ROMS_Z_W, ROMS_WE, ROMS_WI, ROMS_AKV}) slot(h, id, 1, 1, N + 1);
+  slot(h, ROMS_AKT, 1, 2, N + 1);
+  // one arena: all fields + device-owned scratch
+  size_t planes = 0;
+  for (int id = 0; id < ROMS_NFIELDS; ++id) planes += (size_t)h->f[id].nlvl * h->f[id].ntrc * h->f[id].nk;
+  const size_t scratch_planes = (size_t)3 * N            /* FlxDiv, P, rho */
+                                + (h->use_smem ? 0 : (size_t)2 * (N + 1)) /* column scratch fallback */
+                                + 1 /* zeta_new */ + 2 /* ub, vb */ + 5 /* diag planes */;
+  const size_t small = 2 * (size_t)(N + 1) + 64;
+  h->arena_doubles = (planes + scratch_planes) * (size_t)p.SXY + small;
+  CK(cudaMalloc(&h->arena, h->arena_doubles * sizeof(double)));
+  CK(cudaMemset(h->arena, 0, h->arena_doubles * sizeof(double)));   // init=0 (init_scalars.F:31)
+  double* cur = h->arena;
+  auto take = [&](size_t npl) { double* r = cur; cur += npl * (size_t)p.SXY; return r; };
+  for (int id = 0; id < ROMS_NFIELDS; ++id)
+    for (size_t s = 0; s < h->f[id].ptr.size(); ++s) h->f[id].ptr[s] = take(h->f[id].nk);
+  p.FlxDiv = take(N); p.P = take(N); p.rho = take(N);
+  p.scr = h->use_smem ? nullptr : take(2 * (N + 1));
+  p.zeta_new = take(1);
+  h->d_ub = take(1); h->d_vb = take(1);
+  for (int q = 0; q < 5; ++q) h->d_o[q] = take(1);
+  p.Cs_w = cur; cur += (N + 1);
+  p.Cs_r = cur; cur += (N + 1);
+#define P1(name, id) p.name = h->f[id].ptr[0]
+  P1(h, ROMS_H); P1(pm, ROMS_PM); P1(pn, ROMS_PN); P1(f, ROMS_F); P1(rmask, ROMS_RMASK); P1(umask, ROMS_UMASK); P1(vmask, ROMS_VMASK);
+  P1(dm_u, ROMS_DM_U); P1(dn_u, ROMS_DN_U); P1(dm_v, ROMS_DM_V); P1(dn_v, ROMS_DN_V); P1(dm_r, ROMS_DM_R); P1(dn_r, ROMS_DN_R);
+  P1(fomn, ROMS_FOMN); P1(hinv, ROMS_HINV); P1(rhoA, ROMS_RHOA); P1(rhoS, ROMS_RHOS); P1(rufrc, ROMS_RUFRC); P1(rvfrc, ROMS_RVFRC);
+  P1(Zt_avg1, ROMS_ZT_AVG1); P1(DU_avg1, ROMS_DU_AVG1); P1(DV_avg1, ROMS_DV_AVG1); P1(DU_avg2, ROMS_DU_AVG2); P1(DV_avg2, ROMS_DV_AVG2);
+  P1(DU_avg_bak, ROMS_DU_AVG_BAK); P1(DV_avg_bak, ROMS_DV_AVG_BAK); P1(r_D, ROMS_R_D); P1(sustr, ROMS_SUSTR); P1(svstr, ROMS_SVSTR);
+  P1(swflx, ROMS_SWFLX); P1(Hz, ROMS_HZ); P1(z_r, ROMS_Z_R); P1(z_w, ROMS_Z_W); P1(FlxU, ROMS_FLXU); P1(FlxV, ROMS_FLXV); P1(We, ROMS_WE);
+  P1(Wi, ROMS_WI); P1(rho1, ROMS_RHO1); P1(qp1, ROMS_QP1); P1(Akv, ROMS_AKV); P1(ru, ROMS_RU); P1(rv, ROMS_RV);
+#undef P1
+  p.Akt[0] = h->f[ROMS_AKT].ptr[0]; p.Akt[1] = h->f[ROMS_AKT].ptr[1];
+  host_scoord(h);
+  host_weights(h);
+  CK(cudaMemcpy(p.Cs_w, h->Cs_w.data(), (N + 1) * sizeof(double), cudaMemcpyHostToDevice));
+  CK(cudaMemcpy(p.Cs_r, h->Cs_r.data(), (N + 1) * sizeof(double), cudaMemcpyHostToDevice));
+  comm_init(&h->comm, cfg);
+  *out = h;
+  return 0;
+}
+
+int roms_destroy(roms_ctx* h) {
+  if (!h) return 0;
+  cudaSetDevice(h->device);
+  cudaStreamSynchronize(h->st);
+  comm_destroy(&h->comm);
+  cudaFree(h->arena);
+  cudaStreamDestroy(h->st);
+  delete h;
+  return 0;
+}
+
+static int find_slot(roms_ctx* h, int field, int lvl, int itrc, double** ptr, int* nk) {
+  if (field < 0 || field >= ROMS_NFIELDS) { g_err = "bad field id"; return -1; }
+  FieldSlot& s = h->f[field];
+  const int l = s.nlvl > 1 ? lvl : 1, t = s.ntrc > 1 ? itrc : 1;
+  if (l < 1 || l > s.nlvl || t < 1 || t > s.ntrc) { g_err = "bad level/tracer selector"; return -1; }
+  *ptr = s.ptr[(size_t)(l - 1) * s.ntrc + (t - 1)];
+  *nk = s.nk;
+  return 0;
+}
+long roms_field_count(roms_ctx* h, int field) {
+  if (field < 0 || field >= ROMS_NFIELDS) return 0;
+  return (long)(h->c.Lm + 4) * (h->c.Mm + 4) * h->f[field].nk;
+}
+int roms_push(roms_ctx* h, int field, int lvl, int itrc, const double* host) {
+  double* d; int nk;
+  if (find_slot(h, field, lvl, itrc, &d, &nk)) return -1;
+  CK(cudaSetDevice(h->device));
+  const size_t w = (size_t)(h->c.Lm + 4) * sizeof(double);
+  CK(cudaMemcpy2DAsync(d + (IOFF - 1), (size_t)h->kp.SX * sizeof(double), host, w, w, (size_t)(h->c.Mm + 4) * nk, cudaMemcpyHostToDevice, h->st));
+  CK(cudaStreamSynchronize(h->st));
+  return 0;
+}
+int roms_pull(roms_ctx* h, int field, int lvl, int itrc, double* host) {
+  double* d; int nk;
+  if (find_slot(h, field, lvl, itrc, &d, &nk)) return -1;
+  CK(cudaSetDevice(h->device));
+  const size_t w = (size_t)(h->c.Lm + 4) * sizeof(double);
+  CK(cudaMemcpy2DAsync(host, w, d + (IOFF - 1), (size_t)h->kp.SX * sizeof(double), w, (size_t)(h->c.Mm + 4) * nk, cudaMemcpyDeviceToHost, h->st));
+  CK(cudaStreamSynchronize(h->st));
+  return 0;
+}
+int roms_sync(roms_ctx* h) {
+  CK(cudaSetDevice(h->device));
+  CK(cudaStreamSynchronize(h->st));
+  CK(cudaGetLastError());
+  return 0;
+}
+int roms_kernel_launches(roms_ctx* h, long* n) { *n = h->launches; return 0; }
+int roms_get_nfast(roms_ctx* h) { return h->nfast; }
+int roms_get_weights(roms_ctx* h, double* w1, double* w2, int n) {
+  for (int i = 1; i <= n; ++i) { w1[i - 1] = h->w1[i]; w2[i - 1] = h->w2[i]; }
+  return 0;
+}
+int roms_get_scoord(roms_ctx* h, double* Cs_w, double* Cs_r) {
+  for (int k = 0; k <= h->c.N; ++k) Cs_w[k] = h->Cs_w[k];
+  for (int k = 1; k <= h->c.N; ++k) Cs_r[k - 1] = h->Cs_r[k];
+  return 0;
+}
+int roms_set_time_indices(roms_ctx* h, int iic, int iif, int nstp, int nrhs, int nnew, int kstp, int knew) {
+  h->iic = iic; h->iif = iif; h->nstp = nstp; h->nrhs = nrhs; h->nnew = nnew; h->kstp = kstp; h->knew = knew;
+  return 0;
+}
+int roms_get_time_indices(roms_ctx* h, int* iic, int* iif, int* nstp, int* nrhs, int* nnew, int* kstp, int* knew) {
+  *iic = h->iic; *iif = h->iif; *nstp = h->nstp; *nrhs = h->nrhs; *nnew = h->nnew; *kstp = h->kstp; *knew = h->knew;
+  return 0;
+}
+int roms_compute_tile_bounds(roms_ctx* h, int tile, int* istr, int* iend, int* jstr, int* jend) {
+  if (tile != 0) { g_err = "only tile 0 exists (NSUB_X=NSUB_E=1, one tile per GPU subdomain)"; return -1; }
+  *istr = 1; *iend = h->c.Lm; *jstr = 1; *jend = h->c.Mm;
+  return 0;
+}
+
+// ---- exchange_xxx -------------------------------------------------------------------------------
+static int exchange(roms_ctx* h, std::initializer_list<XF> fl) {
+  return comm_exchange(&h->comm, h->kp, h->st, fl.begin(), (int)fl.size(), &h->launches);
+}
+int roms_exchange(roms_ctx* h, int nfields, const int* fields, const int* lvls, const int* itrcs) {
+  CK(cudaSetDevice(h->device));
+  std::vector<XF> v;
+  for (int n = 0; n < nfields; ++n) {
+    double* d; int nk;
+    if (find_slot(h, fields[n], lvls ? lvls[n] : 1, itrcs ? itrcs[n] : 1, &d, &nk)) return -1;
+    v.push_back({d, nk});
+  }
+  return comm_exchange(&h->comm, h->kp, h->st, v.data(), (int)v.size(), &h->launches);
+}
+
+// ---- setup_grid1.F:13-210 (metrics, masks, fomn): host arithmetic on pulled planes, pushed back --
+int roms_setup_grid(roms_ctx* h) {
+  const int Lm = h->c.Lm, Mm = h->c.Mm, SXh = Lm + 4;
+  const size_t n2 = (size_t)SXh * (Mm + 4);
+  std::vector<double> pm(n2), pn(n2), f(n2), rm(n2);
+  if (roms_pull(h, ROMS_PM, 1, 1, pm.data()) || roms_pull(h, ROMS_PN, 1, 1, pn.data()) || roms_pull(h, ROMS_F, 1, 1, f.data()) ||
+      roms_pull(h, ROMS_RMASK, 1, 1, rm.data()))
+    return -1;
+  auto at = [&](int i, int j) { return (size_t)(i + 1) + (size_t)(j + 1) * SXh; };
+  std::vector<double> fomn(n2, 0.0), dm_r(n2, 0.0), dn_r(n2, 0.0), dm_u(n2, 0.0), dn_u(n2, 0.0), dm_v(n2, 0.0), dn_v(n2, 0.0), um(n2, 0.0), vm(n2, 0.0);
+  for (size_t q = 0; q < n2; ++q) fomn[q] = f[q] / (pm[q] * pn[q]);
+  for (int j = 1; j <= Mm; ++j)
+    for (int i = 1; i <= Lm; ++i) {
+      const size_t q = at(i, j), w = at(i - 1, j), s = at(i, j - 1);
+      dm_r[q] = 1.0 / pm[q]; dn_r[q] = 1.0 / pn[q];
+      dm_u[q] = 2.0 / (pm[q] + pm[w]); dn_u[q] = 2.0 / (pn[q] + pn[w]); um[q] = rm[q] * rm[w];
+      dm_v[q] = 2.0 / (pm[q] + pm[s]); dn_v[q] = 2.0 / (pn[q] + pn[s]); vm[q] = rm[q] * rm[s];
+    }
+  struct { int id; std::vector<double>* a; } outv[] = {{ROMS_FOMN, &fomn}, {ROMS_DM_R, &dm_r}, {ROMS_DN_R, &dn_r}, {ROMS_DM_U, &dm_u}, {ROMS_DN_U, &dn_u},
+                                                       {ROMS_DM_V, &dm_v}, {ROMS_DN_V, &dn_v}, {ROMS_UMASK, &um}, {ROMS_VMASK, &vm}};
+  for (auto& o : outv)
+    if (roms_push(h, o.id, 1, 1, o.a->data())) return -1;
+  const KP& p = h->kp;
+  int rc = exchange(h, {{p.dm_r, 1}, {p.dn_r, 1}, {p.dm_u, 1}, {p.dn_u, 1}});
+  if (!rc) rc = exchange(h, {{p.dm_v, 1}, {p.dn_v, 1}, {p.rmask, 1}, {p.umask, 1}});
+  if (!rc) rc = exchange(h, {{p.vmask, 1}});
+  return rc;
+}
+
+// ---- the tile-subroutine surface ----------------------------------------------------------------
+int roms_set_depth(roms_ctx* h, int tile) {
+  (void)tile;
+  CK(cudaSetDevice(h->device));
+  const KP& p = h->kp;
+  if (h->iic == 0) PLANE(k_set_depth_init, p.iend, p.jstr, p.jend, 1, p, h->zeta(1), h->ubar(1), h->vbar(1));
+  PLANE(k_set_depth, p.iend, p.jstr, p.jend, p.N + 1, p, h->zeta(h->knew));
+  if (h->iic == 0) { int rc = exchange(h, {{p.hinv, 1}}); if (rc) return rc; }
+  return exchange(h, {{p.z_w, p.N + 1}, {p.z_r, p.N}, {p.Hz, p.N}});
+}
+int roms_set_huv(roms_ctx* h) {
+  CK(cudaSetDevice(h->device));
+  const KP& p = h->kp;
+  PLANE(k_set_huv, p.iend, p.jstr, p.jend, p.N, p, h->u(h->nrhs), h->v(h->nrhs));
+  return exchange(h, {{p.FlxU, p.N}, {p.FlxV, p.N}});
+}
+int roms_set_huv1(roms_ctx* h, int tile) {
+  (void)tile;
+  CK(cudaSetDevice(h->device));
+  const KP& p = h->kp;
+  const int first = (h->iic == h->forw_start);
+  COLUMN(k_set_huv1<0>, 0, p.iend, p.jstr, p.jend, p, h->u(h->nnew), first);
+  COLUMN(k_set_huv1<1>, 0, p.iend, p.jstr, p.jend, p, h->v(h->nnew), first);
+  return exchange(h, {{p.FlxU, p.N}, {p.FlxV, p.N}, {h->u(h->nnew), p.N}, {h->v(h->nnew), p.N}});
+}
+int roms_omega(roms_ctx* h) {
+  CK(cudaSetDevice(h->device));
+  const KP& p = h->kp;
+  double dtau;
+  if (h->nrhs == 3) dtau = h->c.dt;
+  else if (h->iic == h->forw_start) dtau = 0.5 * h->c.dt;
+  else dtau = 0.6 * h->c.dt;
+  COLUMN(k_omega, 2, p.iend, p.jstr, p.jend, p, dtau);
+  return exchange(h, {{p.We, p.N + 1}, {p.Wi, p.N + 1}});
+}
+int roms_rho_eos(roms_ctx* h, int tidx) {
+  CK(cudaSetDevice(h->device));
+  const KP& p = h->kp;
+  const double* T = h->t(tidx, 1);
+  const double* S = h->c.NT >= 2 ? h->t(tidx, 2) : nullptr;
+  if (h->c.nonlin_eos) {
+    if (!S) { g_err = "NONLIN_EOS needs salinity (NT>=2)"; return -1; }
+    COLUMN(k_rho_eos<true>, 0, p.iend + 2, p.jstr - 2, p.jend + 2, p, T, S);
+  } else COLUMN(k_rho_eos<false>, 0, p.iend + 2, p.jstr - 2, p.jend + 2, p, T, S);
+  return 0;
+}
+int roms_prsgrd(roms_ctx* h) {
+  CK(cudaSetDevice(h->device));
+  const KP& p = h->kp;
+  if (h->c.nonlin_eos) {
+    COLUMN(k_prsgrd_vert<true>, 0, p.Lm, 0, p.Mm, p);
+    PLANE(k_prsgrd_horiz<true>, p.iend, p.jstr, p.jend, p.N, p);
+  } else {
+    COLUMN(k_prsgrd_vert<false>, 0, p.Lm, 0, p.Mm, p);
+    PLANE(k_prsgrd_horiz<false>, p.iend, p.jstr, p.jend, p.N, p);
+  }
+  return 0;
+}
+int roms_pre_step3d(roms_ctx* h, int tile) {
+  (void)tile;
+  CK(cudaSetDevice(h->device));
+  const KP& p = h->kp;
+  const int nstp = h->nstp, nrhs = h->nrhs, nnew = h->nnew, indx = 3 - nstp;
+  const double dt = h->c.dt, AM3_crv = 1.0 / 6.0;
+  double dtau, cf_stp, cf_bak;
+  if (h->iic == h->forw_start) { dtau = 0.5 * dt; cf_stp = 1.0; cf_bak = 0.0; }
+  else { dtau = dt * (1.0 - AM3_crv); cf_stp = 0.5 + AM3_crv; cf_bak = 0.5 - AM3_crv; }
+  PLANE(k_pre_flxdiv, p.iend, p.jstr - 1, p.jend, p.N, p, dtau);
+  for (int it = 1; it <= h->c.NT; ++it)
+    PLANE(k_pre_t_horiz, p.iend, p.jstr, p.jend, p.N, p, h->t(nrhs, it), h->t(nnew, it), h->t(nstp, it), h->t(indx, it), dtau, cf_stp, cf_bak);
+  PLANE(k_rhs_uv_horiz<false>, p.iend, p.jstr, p.jend, p.N, p, h->u(nrhs), h->v(nrhs));
+  PLANE(k_rd_bott_drag, p.iend, p.jstr - 1, p.jend, 1, p, h->u(nstp), h->v(nstp));
+  for (int it = 1; it <= h->c.NT; ++it)
+    COLUMN(k_t_vert<0>, 2, p.iend, p.jstr, p.jend, p, h->t(nrhs, it), h->t(nnew, it), p.Akt[it >= 2 ? 1 : 0], (const double*)nullptr, dtau, 0);
+  COLUMN((k_uv_vert<0, 0>), 2, p.iend, p.jstr, p.jend, p, h->u(nrhs), h->u(nnew), h->u(nstp), h->u(indx), dtau, cf_stp, cf_bak);
+  COLUMN((k_uv_vert<0, 1>), 2, p.iend, p.jstr, p.jend, p, h->v(nrhs), h->v(nnew), h->v(nstp), h->v(indx), dtau, cf_stp, cf_bak);
+  // u3dbc/v3dbc/t3dbc: nothing on periodic edges; one exchange per tracer (pre_step3d4S.F:548)
+  for (int it = 1; it <= h->c.NT; ++it) {
+    int rc = exchange(h, {{h->t(nnew, it), p.N}});
+    if (rc) return rc;
+  }
+  return 0;
+}
+int roms_step3d_uv1(roms_ctx* h, int tile) {
+  (void)tile;
+  CK(cudaSetDevice(h->device));
+  const KP& p = h->kp;
+  const int nrhs = h->nrhs, nnew = h->nnew;
+  PLANE(k_rhs_uv_horiz<true>, p.iend, p.jstr, p.jend, p.N, p, h->u(nrhs), h->v(nrhs));
+  COLUMN((k_uv_vert<1, 0>), 2, p.iend, p.jstr, p.jend, p, h->u(nrhs), h->u(nnew), (const double*)nullptr, (double*)nullptr, h->c.dt, 0.0, 0.0);
+  COLUMN((k_uv_vert<1, 1>), 2, p.iend, p.jstr, p.jend, p, h->v(nrhs), h->v(nnew), (const double*)nullptr, (double*)nullptr, h->c.dt, 0.0, 0.0);
+  return 0;
+}
+int roms_step2d(roms_ctx* h) {
+  CK(cudaSetDevice(h->device));
+  const KP& p = h->kp;
+  const int iif = h->iif, kstp = h->kstp, knew = h->knew;
+  int kbak, kold;
+  S2D s;
+  if (iif == 1) {
+    kbak = kstp; kold = kstp;
+    s.fwd = 1.0; s.fwd1 = 0.0; s.fwd2 = 0.0; s.bkw_new = 0.0; s.bkw = 1.0; s.bkw1 = 0.0; s.bkw2 = 0.0;
+  } else if (iif == 2) {
+    kbak = kstp - 1; if (kbak < 1) kbak = 4;
+    kold = kbak;
+    s.fwd = 1.0; s.fwd1 = 0.0; s.fwd2 = 0.0;
+    s.bkw_new = 1.0833333333333; s.bkw = -0.1666666666666; s.bkw1 = 0.0833333333333; s.bkw2 = 0.0;
+  } else {
+    kbak = kstp - 1; if (kbak < 1) kbak = 4;
+    kold = kbak - 1; if (kold < 1) kold = 4;
+    s.fwd = 1.781105; s.fwd1 = -1.06221; s.fwd2 = 0.281105;
+    s.bkw_new = 0.614; s.bkw = 0.285; s.bkw1 = 0.088; s.bkw2 = 0.013;
+  }
+  s.zs = h->zeta(kstp); s.zb = h->zeta(kbak); s.zo = h->zeta(kold);
+  s.us = h->ubar(kstp); s.ub = h->ubar(kbak); s.uo = h->ubar(kold);
+  s.vs = h->vbar(kstp); s.vb = h->vbar(kbak); s.vo = h->vbar(kold);
+  s.zn = h->zeta(knew); s.un = h->ubar(knew); s.vn = h->vbar(knew);
+  s.w1 = h->w1[iif]; s.w2 = h->w2[iif];
+  s.iif = iif; s.nfast = h->nfast;
+  PLANE(k_step2d_zeta, p.iend, p.jstr - 1, p.jend, 1, p, s);
+  PLANE(k_step2d_uv, p.iend, p.jstr, p.jend, 1, p, s);
+  if (iif == h->nfast) {
+    int rc = roms_set_depth(h, 0);
+    if (rc) return rc;
+  }
+  return exchange(h, {{s.zn, 1}, {s.un, 1}, {s.vn, 1}});
+}
+int roms_step3d_uv2(roms_ctx* h, int tile) {
+  (void)tile;
+  CK(cudaSetDevice(h->device));
+  const KP& p = h->kp;
+  const int nnew = h->nnew, nstp = h->nstp, knew = h->knew;
+  COLUMN(k_uv2_pass0<0>, 0, p.iend, p.jstr, p.jend, p, h->u(nnew));
+  COLUMN(k_uv2_pass0<1>, 0, p.iend, p.jstr, p.jend, p, h->v(nnew));
+  // u3dbc_tile / v3dbc_tile act here on non-periodic edges (step3d_uv2.F:471-472)
+  COLUMN(k_uv2_pass1<0>, 0, p.iend, p.jstr, p.jend, p, h->u(nnew), h->u(nstp), h->ubar(knew));
+  COLUMN(k_uv2_pass1<1>, 0, p.iend, p.jstr, p.jend, p, h->v(nnew), h->v(nstp), h->vbar(knew));
+  int rc = exchange(h, {{p.FlxU, p.N}, {h->u(nnew), p.N}, {h->ubar(knew), 1}});
+  if (rc) return rc;
+  return exchange(h, {{p.FlxV, p.N}, {h->v(nnew), p.N}, {h->vbar(knew), 1}});
+}
+int roms_step3d_t(roms_ctx* h, int tile) {
+  (void)tile;
+  CK(cudaSetDevice(h->device));
+  const KP& p = h->kp;
+  const int nrhs = h->nrhs, nnew = h->nnew, NT = h->c.NT;
+  for (int it = 1; it <= NT; ++it) {
+    PLANE(k_t_horiz, p.iend, p.jstr, p.jend, p.N, p, h->t(nrhs, it), h->t(nnew, it));
+    COLUMN(k_t_vert<1>, 2, p.iend, p.jstr, p.jend, p, h->t(nrhs, it), h->t(nnew, it), p.Akt[it >= 2 ? 1 : 0], h->f[ROMS_STFLX].ptr[it - 1], h->c.dt,
+           it == 1 ? 1 : 0);
+  }
+  for (int it = 1; it + 1 <= NT; it += 2) {
+    int rc = exchange(h, {{h->t(nnew, it), p.N}, {h->t(nnew, it + 1), p.N}});
+    if (rc) return rc;
+  }
+  if (NT % 2 == 1) return exchange(h, {{h->t(nnew, NT), p.N}});
+  return 0;
+}
+int roms_alfabeta(roms_ctx* h, double* alpha_host, double* beta_host) {
+  CK(cudaSetDevice(h->device));
+  const KP& p = h->kp;
+  const double* T = h->t(h->nstp, 1);
+  const double* S = h->c.NT >= 2 ? h->t(h->nstp, 2) : T;
+  COLUMN(k_alfabeta, 0, p.iend + 2, p.jstr - 2, p.jend + 2, p, T, S, h->d_o[0], h->d_o[1]);
+  const size_t w = (size_t)(h->c.Lm + 4) * sizeof(double);
+  CK(cudaMemcpy2DAsync(alpha_host, w, h->d_o[0] + (IOFF - 1), (size_t)p.SX * sizeof(double), w, h->c.Mm + 4, cudaMemcpyDeviceToHost, h->st));
+  CK(cudaMemcpy2DAsync(beta_host, w, h->d_o[1] + (IOFF - 1), (size_t)p.SX * sizeof(double), w, h->c.Mm + 4, cudaMemcpyDeviceToHost, h->st));
+  CK(cudaStreamSynchronize(h->st));
+  return 0;
+}
+
+// diag.F:50-658.  Column values on the device; the sums are formed on the host in a fixed order
+// (row-wise pairwise) so that the result is deterministic.  Multi-GPU: each rank reports its own
+// partial sums; roms_diag combines them through the communicator.
+static double pairsum(const double* a, size_t n) {
+  if (n <= 8) { double s = 0; for (size_t i = 0; i < n; ++i) s += a[i]; return s; }
+  return pairsum(a, n / 2) + pairsum(a + n / 2, n - n / 2);
+}
+int roms_diag(roms_ctx* h, double out[4]) {
+  CK(cudaSetDevice(h->device));
+  const KP& p = h->kp;
+  const int Lm = h->c.Lm, Mm = h->c.Mm, SXh = Lm + 4;
+  COLUMN(k_diag_bar, 0, p.iend + 1, p.jstr, p.jend + 1, p, h->u(h->nstp), h->v(h->nstp), h->d_ub, h->d_vb);
+  COLUMN(k_diag_col, 0, p.iend, p.jstr, p.jend, p, h->u(h->nstp), h->v(h->nstp), h->d_ub, h->d_vb, h->d_o[0], h->d_o[1], h->d_o[2], h->d_o[3], h->d_o[4]);
+  const size_t n2 = (size_t)SXh * (Mm + 4), w = (size_t)SXh * sizeof(double);
+  std::vector<double> pl[5];
+  std::vector<double> pmv(n2), pnv(n2), hv(n2), rmv(n2);
+  for (int q = 0; q < 5; ++q) {
+    pl[q].resize(n2);
+    CK(cudaMemcpy2DAsync(pl[q].data(), w, h->d_o[q] + (IOFF - 1), (size_t)p.SX * sizeof(double), w, Mm + 4, cudaMemcpyDeviceToHost, h->st));
+  }
+  if (roms_pull(h, ROMS_PM, 1, 1, pmv.data()) || roms_pull(h, ROMS_PN, 1, 1, pnv.data()) || roms_pull(h, ROMS_H, 1, 1, hv.data()) ||
+      roms_pull(h, ROMS_RMASK, 1, 1, rmv.data()))
+    return -1;
+  CK(cudaStreamSynchronize(h->st));
+  std::vector<double> rows[5];
+  for (int q = 0; q < 5; ++q) rows[q].resize(Mm);
+  double cx = 0.0, cw = 0.0;
+  for (int j = 1; j <= Mm; ++j) {
+    const size_t o = (size_t)(j + 1) * SXh + 2;
+    rows[0][j - 1] = pairsum(&pl[0][o], Lm);
+    rows[1][j - 1] = pairsum(&pl[1][o], Lm);
+    rows[2][j - 1] = pairsum(&pl[2][o], Lm);
+    double ar = 0, vr = 0;
+    for (int i = 0; i < Lm; ++i) {
+      const double dA = rmv[o + i] / (pmv[o + i] * pnv[o + i]);
+      ar += dA; vr += dA * hv[o + i];
+      if (pl[3][o + i] > cx) { cx = pl[3][o + i]; cw = pl[4][o + i]; }
+    }
+    rows[3][j - 1] = ar; rows[4][j - 1] = vr;
+  }
+  double sums[5];
+  for (int q = 0; q < 5; ++q) sums[q] = pairsum(rows[q].data(), Mm);
+  double red[7] = {sums[0], sums[1], sums[2], sums[3], sums[4], cx, cw};
+  int rc = comm_diag_reduce(&h->comm, red);
+  if (rc) return rc;
+  const double avke = red[0], avke2b = red[1], avzeta = red[2], volume = red[4];
+  out[0] = avke / (volume + avzeta);
+  out[1] = avke2b / (volume + avzeta);
+  out[2] = red[5];
+  out[3] = red[6];
+  for (int q = 0; q < 4; ++q)
+    if (!std::isfinite(out[q])) { g_err = "BLOWUP: non-finite diagnostics (diag.F:622-634)"; return 1; }
+  return 0;
+}
+
+// ---- driver: main.F:86-321 (tail of roms_init) and main.F:333-520 (roms_step) -------------------
+int roms_init_step0(roms_ctx* h) {
+  h->iic = 0; h->kstp = 1; h->knew = 1; h->iif = 1; h->nstp = 1; h->nnew = 1; h->nrhs = 1;
+  h->forw_start = h->ntstart;
+  int rc;
+  if ((rc = roms_set_depth(h, 0))) return rc;
+  if ((rc = roms_set_huv(h))) return rc;
+  if ((rc = roms_omega(h))) return rc;
+  if ((rc = roms_rho_eos(h, h->nrhs))) return rc;
+  return 0;
+}
+int roms_step(roms_ctx* h) {
+  int rc;
+  h->iic = (h->iic == 0) ? h->ntstart : h->iic + 1;
+  h->nstp = 1 + (h->iic - h->ntstart) % 2;
+  h->nrhs = h->nstp; h->nnew = 3;
+#define RUN(x) if ((rc = (x))) return rc
+  RUN(roms_rho_eos(h, h->nrhs));
+  RUN(roms_set_huv(h));
+  RUN(roms_omega(h));
+  RUN(roms_prsgrd(h));
+  RUN(roms_pre_step3d(h, 0));
+  RUN(roms_set_huv1(h, 0));
+  h->nrhs = 3; h->nnew = 3 - h->nstp;
+  RUN(roms_omega(h));
+  RUN(roms_rho_eos(h, h->nrhs));
+  RUN(roms_prsgrd(h));
+  RUN(roms_step3d_uv1(h, 0));
+  for (h->iif = 1; h->iif <= h->nfast; ++h->iif) {
+    h->kstp = h->knew;
+    h->knew = h->kstp + 1;
+    if (h->knew > 4) h->knew = 1;
+    RUN(roms_step2d(h));
+  }
+  RUN(roms_step3d_uv2(h, 0));
+  RUN(roms_omega(h));
+  RUN(roms_step3d_t(h, 0));
+  RUN(roms_rho_eos(h, h->nnew));
+#undef RUN
+  return 0;
+}
+int roms_run(roms_ctx* h, int nsteps) {
+  for (int n = 0; n < nsteps; ++n) {
+    int rc = roms_step(h);
+    if (rc) return rc;
+  }
+  return 0;
+}
+
+}  // extern "C"
+
+// ---- exchange_xxx, single-rank path ----------------------------------------------------------------
+int comm_init(Comm* cm, const roms_cfg* cfg) {
+  cm->np_xi = cfg->np_xi > 0 ? cfg->np_xi : 1;
+  cm->np_eta = cfg->np_eta > 0 ? cfg->np_eta : 1;
+  cm->inode = cfg->inode; cm->jnode = cfg->jnode;
+  cm->ew_periodic = cfg->ew_periodic; cm->ns_periodic = cfg->ns_periodic;
+  return 0;
+}
+int comm_destroy(Comm* cm) { (void)cm; return 0; }
+int comm_exchange(Comm* cm, const KP& p, cudaStream_t st, const XF* f, int nf, long* launches) {
+  if (cm->np_xi * cm->np_eta != 1) { g_err = "multi-rank exchange not built into this library"; return -1; }
+  if (!cm->ew_periodic && !cm->ns_periodic) return 0;
+  for (int n0 = 0; n0 < nf; n0 += 4) {
+    HaloList hl;
+    hl.n = 0;
+    int maxk = 1;
+    for (int n = n0; n < nf && n < n0 + 4; ++n) { hl.a[hl.n] = f[n].a; hl.nk[hl.n] = f[n].nk; if (f[n].nk > maxk) maxk = f[n].nk; hl.n++; }
+    const int ncell = 4 * (p.Lm + 4) + 4 * p.Mm;
+    dim3 b(128, 1, 1), g((ncell + 127) / 128, hl.n, maxk);
+    k_halo_periodic<<<g, b, 0, st>>>(p, hl, cm->ew_periodic, cm->ns_periodic);
+    (*launches)++;
+  }
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { g_err = std::string("halo kernel: ") + cudaGetErrorString(e); return -(int)e; }
+  return 0;
+}
+int comm_diag_reduce(Comm* cm, double red[7]) { (void)cm; (void)red; return 0; }

@@ -1,0 +1,158 @@
+"""Analytic (synthetic, deterministic) cases for the explicit time step: host-side numpy only.
+
+Every case returns (cfg, state) where `state` maps field names of include/roms_b200.h to arrays in
+the reference layout (j, i) / (k, j, i) incl. the 2-cell halo, ready for `push_state`.  The same
+state is pushed into libromsb200 and, in the tests, into the CPU oracle.
+
+  channel(...)   BASELINE.json configs[1]: analytic baroclinic channel, T+S, nonlinear split EOS
+                 (SURVEY.md section 8(d) input (2)).  `ns_walls=False` gives the doubly periodic variant.
+  filament(...)  configs[0]: tests/Filament/{ana_grid.h,ana_init.h,param.opt,benchmark.in}
+"""
+import numpy as np
+from .capi import RomsCfg
+
+
+def _scoord(N, theta_s, theta_b):
+    """set_scoord.F:4-66 (host copy used only to place the analytic T,S profiles)."""
+    def csf(sc):
+        csrf = (1.0 - np.cosh(theta_s * sc)) / (np.cosh(theta_s) - 1.0) if theta_s > 0 else -sc ** 2
+        return (np.exp(theta_b * csrf) - 1.0) / (1.0 - np.exp(-theta_b)) if theta_b > 0 else csrf
+    ds = 1.0 / N
+    k = np.arange(1, N + 1)
+    sc_r = ds * (k - N - 0.5)
+    sc_w = ds * (np.arange(0, N + 1) - N)
+    cs_w = csf(sc_w); cs_w[0] = -1.0; cs_w[-1] = 0.0
+    return sc_r, csf(sc_r), sc_w, cs_w
+
+
+def _depths(h, zeta, N, theta_s, theta_b, hc):
+    sc_r, cs_r, sc_w, cs_w = _scoord(N, theta_s, theta_b)
+    hinv = 1.0 / (h + hc)
+    z_r = zeta[None] + (zeta + h)[None] * (hc * sc_r[:, None, None] + cs_r[:, None, None] * h[None]) * hinv[None]
+    z_w = zeta[None] + (zeta + h)[None] * (hc * sc_w[:, None, None] + cs_w[:, None, None] * h[None]) * hinv[None]
+    z_w[0] = -h
+    return z_r, z_w
+
+
+def _wrap(a, ew, ns):
+    """periodic halo fill of the last two axes (j, i), 2 cells"""
+    if ew:
+        a[..., :, :2] = a[..., :, -4:-2]
+        a[..., :, -2:] = a[..., :, 2:4]
+    if ns:
+        a[..., :2, :] = a[..., -4:-2, :]
+        a[..., -2:, :] = a[..., 2:4, :]
+    return a
+
+
+def channel(Lm=64, Mm=64, N=16, NT=2, ns_walls=False, nonlin_eos=True, dt=120.0, ndtfast=60, dx=1.0e3, dy=1.0e3,
+            depth=4000.0, seed=20260101, perturb=1e-6, amp=None):
+    cfg = RomsCfg(Lm=Lm, Mm=Mm, N=N, NT=NT, ew_periodic=1, ns_periodic=0 if ns_walls else 1,
+                  nonlin_eos=1 if nonlin_eos else 0, salinity=1, ndtfast=ndtfast, np_xi=1, np_eta=1, inode=0, jnode=0,
+                  dt=dt, rho0=1027.0, g=9.81, Tcoef=0.2, T0=10.0, Scoef=0.8, S0=35.0,
+                  rdrg=3.0e-4, rdrg2=0.0, Zob=0.0, gamma2=1.0, theta_s=6.0, theta_b=2.0, hc=25.0)
+    sy, sx = Mm + 4, Lm + 4
+    i = np.arange(-1, Lm + 3)[None, :] + np.zeros((sy, 1))
+    j = np.arange(-1, Mm + 3)[:, None] + np.zeros((1, sx))
+    x = dx * (i - 0.5); y = dy * (j - 0.5)
+    Lx, Ly = dx * Lm, dy * Mm
+    if amp is None:
+        amp = 0.02 * min(Lx, Ly) / 64.0e3 + 0.01   # keeps the thermal-wind shear independent of the grid size
+    st = {}
+    h = np.full((sy, sx), depth)
+    st["H"] = h
+    st["PM"] = np.full((sy, sx), 1.0 / dx); st["PN"] = np.full((sy, sx), 1.0 / dy)
+    st["F"] = np.full((sy, sx), 1.0e-4)
+    st["RMASK"] = np.ones((sy, sx))
+    zeta = 0.01 * np.sin(2 * np.pi * x / Lx) * np.cos(2 * np.pi * y / Ly)
+    z_r, z_w = _depths(h, zeta, N, cfg.theta_s, cfg.theta_b, cfg.hc)
+    Hz = z_w[1:] - z_w[:-1]
+    if ns_walls:
+        front = amp * np.tanh((y - 0.5 * Ly) / (0.15 * Ly))
+    else:
+        front = amp * np.sin(2 * np.pi * y / Ly)
+    T = 4.0 + 10.0 * np.exp(z_r / 50.0) + (front + 0.2 * amp * np.sin(2 * np.pi * x / Lx) * np.cos(2 * np.pi * y / Ly))[None] * np.exp(z_r / 400.0)
+    S = 35.0 + 0.1 * amp * np.cos(2 * np.pi * x / Lx)[None] * np.exp(z_r / 300.0) - 0.5 * np.exp(z_r / 100.0)
+    u = 0.02 * (np.sin(2 * np.pi * y / Ly) * (1 + 0.3 * np.cos(2 * np.pi * x / Lx)))[None] * np.exp(z_r / 500.0)
+    v = 0.01 * (np.sin(2 * np.pi * x / Lx) * np.cos(2 * np.pi * y / Ly))[None] * np.exp(z_r / 500.0)
+    rng = np.random.default_rng(seed)
+    T = T * (1 + perturb * rng.standard_normal(T.shape)); S = S * (1 + perturb * rng.standard_normal(S.shape))
+    u = u + perturb * 0.1 * rng.standard_normal(u.shape); v = v + perturb * 0.1 * rng.standard_normal(v.shape)
+    if ns_walls:
+        v[:, :3, :] = 0.0      # v(:,1)=0 south wall ... j index 1 is array row 2
+        v[:, Mm + 2:, :] = 0.0  # v(:,Mm+1)=0 north wall
+    per_ns = not ns_walls
+    for a in (zeta, T, S, u, v):
+        _wrap(a, True, per_ns)
+    Hz = _wrap(Hz, True, per_ns)
+    Hzu = 0.5 * (Hz + np.roll(Hz, 1, axis=2)); Hzv = 0.5 * (Hz + np.roll(Hz, 1, axis=1))
+    ubar = (Hzu * u).sum(0) / Hzu.sum(0); vbar = (Hzv * v).sum(0) / Hzv.sum(0)
+    _wrap(ubar, True, per_ns); _wrap(vbar, True, per_ns)
+    st["ZETA"] = {(1, 1): zeta, (2, 1): zeta}
+    st["UBAR"] = {(1, 1): ubar, (2, 1): ubar}
+    st["VBAR"] = {(1, 1): vbar, (2, 1): vbar}
+    st["U"] = {(1, 1): u, (2, 1): u}
+    st["V"] = {(1, 1): v, (2, 1): v}
+    tr = {(1, 1): T, (2, 1): T, (1, 2): S, (2, 2): S}
+    for it in range(3, NT + 1):   # passive tracers (SURVEY.md 8(d) input (4))
+        pz = np.sin(2 * np.pi * (it - 2) * x / Lx)[None] * np.cos(2 * np.pi * y / Ly)[None] * np.exp(z_r / 100.0)
+        _wrap(pz, True, per_ns)
+        tr[(1, it)] = pz; tr[(2, it)] = pz
+    st["T"] = tr
+    akv = np.full((N + 1, sy, sx), 1.0e-4)
+    st["AKV"] = akv
+    st["AKT"] = {(1, 1): akv, (1, 2): akv}
+    return cfg, st
+
+
+def filament(Lm=64, Mm=64, N=32):
+    """tests/Filament analytical case (ana_grid.h, ana_init.h) evaluated with numpy."""
+    cfg = RomsCfg(Lm=Lm, Mm=Mm, N=N, NT=1, ew_periodic=1, ns_periodic=1, nonlin_eos=0, salinity=0, ndtfast=60,
+                  np_xi=1, np_eta=1, inode=0, jnode=0, dt=5.0, rho0=1000.0, g=9.81, Tcoef=0.20, T0=1.0, Scoef=0.822, S0=1.0,
+                  rdrg=0.0, rdrg2=1.0e-3, Zob=1.0e-2, gamma2=1.0, theta_s=6.0, theta_b=2.0, hc=25.0)
+    sy, sx = Mm + 4, Lm + 4
+    SizeX, SizeY, HD = 12.8e3, 3.2e3, 1000.0
+    dx, dy = SizeX / Lm, SizeY / Mm
+    i = np.arange(-1, Lm + 3)[None, :] + np.zeros((sy, 1))
+    xr = dx * (i - 0.5) - SizeX / 2.0
+    st = {"H": np.full((sy, sx), HD), "PM": np.full((sy, sx), 1.0 / dx), "PN": np.full((sy, sx), 1.0 / dy),
+          "F": np.full((sy, sx), 2 * 7.81e-5), "RMASK": np.ones((sy, sx))}
+    h = st["H"]
+    z_r, z_w = _depths(h, np.zeros((sy, sx)), N, cfg.theta_s, cfg.theta_b, cfg.hc)
+    Hz = z_w[1:] - z_w[:-1]
+    g, alpha = cfg.g, cfg.Tcoef / cfg.rho0
+    b0, B, lam, Nb, N0, h0, dh0, L = 5.0e-2, 0.025, 8.0, 1.0e-7, 3.0e-5, 60.0, 15.0, 2000.0
+    hs = h0 + dh0 * np.exp(-(xr / L) ** 2)
+    bfun = lambda z, hsbl: b0 + Nb * (z + HD) + 0.5 * N0 * ((1 + B) * z - (1 - B) * (hsbl + lam * np.log(np.cosh((1.0 / lam) * (z + hsbl)))))
+    T = bfun(z_r, hs[None]) / (g * alpha)
+    bf_int = (Hz[:, 2, 2] * bfun(z_r[:, 2, 2], h0) / g).sum()
+    zeta = (T * alpha * Hz).sum(0) - bf_int
+    f = st["F"]; pm = st["PM"]
+    v = np.zeros_like(T)
+    dzdx = np.zeros((sy, sx)); dzdx[:, 1:-1] = 0.5 * pm[:, 1:-1] * (zeta[:, 2:] - zeta[:, :-2])
+    v[N - 1] = g * dzdx / f
+    for k in range(N - 2, -1, -1):
+        dbdx = np.zeros((sy, sx))
+        dbdx[:, 1:-1] = 0.25 * pm[:, 1:-1] * g * alpha * (T[k, :, 2:] - T[k, :, :-2] + T[k + 1, :, 2:] - T[k + 1, :, :-2])
+        v[k] = v[k + 1] - dbdx * (z_r[k + 1] - z_r[k]) / f
+    vbar = (v[:N - 1] * Hz[:N - 1]).sum(0) / HD
+    u = np.zeros_like(v); ubar = np.zeros((sy, sx))
+    for a in (zeta, vbar, v, T):
+        _wrap(a, True, True)
+    st["ZETA"] = {(1, 1): zeta, (2, 1): zeta}
+    st["UBAR"] = {(1, 1): ubar}
+    st["VBAR"] = {(1, 1): vbar, (2, 1): vbar}
+    st["U"] = {(1, 1): u, (2, 1): u}
+    st["V"] = {(1, 1): v, (2, 1): v}
+    st["T"] = {(1, 1): T, (2, 1): T}
+    return cfg, st
+
+
+def initialize(model, state):
+    """roms_init (main.F:86-321) for a host without Fortran: push the analytic fields, derive the
+    grid metrics, then set_depth / set_HUV / omega / rho_eos."""
+    grid = {k: state[k] for k in ("H", "PM", "PN", "F", "RMASK")}
+    model.push_state(grid)
+    model.call("setup_grid")
+    model.push_state({k: v for k, v in state.items() if k not in grid})
+    model.call("init_step0")
