@@ -1,0 +1,284 @@
+#!/usr/bin/env python
+"""bench.py -- baroclinic grid-point updates/s of the B200-native UCLA-ROMS time step.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--size Lm Mm N] [--nt NT]
+
+One "step" = one full baroclinic step (main.F:397-479: rho_eos, set_HUV, omega, prsgrd, pre_step3d,
+set_HUV1, omega, rho_eos, prsgrd, step3d_uv1, nfast x step2d, step3d_uv2, omega, step3d_t, rho_eos)
+of the analytic baroclinic channel (BASELINE.json configs[1]: 1024x1024x64 per GPU, T+S, nonlinear
+split EOS, 82 executed barotropic substeps).  Inputs are far larger than L2 (15 GB of state per GPU),
+so no L2 flush is needed between timed iterations.  Timing: CUDA events on the library's stream,
+barrier + synchronize on both sides, max over ranks.  Prints ONE JSON line on rank 0.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, os.path.join(ROOT, "ucla-roms_b200"))
+
+METRIC = "baroclinic grid-point updates/s"
+UNIT = "grid-point updates/s"
+
+# Algorithmic fp64 words per point per launch (SURVEY.md section 8(a)/(d) rule: every 3-D operand of a
+# kernel read once, every 3-D result written once, 2-D operands ignored in 3-D kernels, scratch = 0).
+# (words, dimensionality)
+KERNEL_WORDS = {
+    "k_rho_eos<true>": (6, 3), "k_rho_eos<false>": (4, 3), "k_set_huv": (5, 3), "k_omega": (6, 3),
+    "k_prsgrd_vert<true>": (5, 3), "k_prsgrd_vert<false>": (3, 3), "k_prsgrd_horiz<true>": (8, 3), "k_prsgrd_horiz<false>": (6, 3),
+    "k_pre_flxdiv": (5, 3), "k_pre_t_horiz": (8, 3), "k_rhs_uv_horiz<false>": (9, 3), "k_rhs_uv_horiz<true>": (9, 3),
+    "k_t_vert<0>": (8, 3), "k_t_vert<1>": (7, 3), "(k_uv_vert<0, 0>)": (10, 3), "(k_uv_vert<0, 1>)": (10, 3),
+    "(k_uv_vert<1, 0>)": (9, 3), "(k_uv_vert<1, 1>)": (9, 3), "k_set_huv1<0>": (4, 3), "k_set_huv1<1>": (4, 3),
+    "k_uv2_pass0<0>": (3, 3), "k_uv2_pass0<1>": (3, 3), "k_uv2_pass1<0>": (6, 3), "k_uv2_pass1<1>": (6, 3),
+    "k_t_horiz": (5, 3), "k_set_depth": (3, 3), "k_step2d_zeta": (24, 2), "k_step2d_uv": (23, 2), "k_rd_bott_drag": (3, 2),
+}
+
+
+def step_bytes_per_update(NT, nfast, N):
+    """B = 8*(113 + 7*NT + 34*nfast/N) bytes per baroclinic grid-point update."""
+    return 8.0 * (113 + 7 * NT + 34.0 * nfast / N)
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return json.load(open(p))["hbm_gbs"], "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler:
+    Q = "index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown," \
+        "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, gpu):
+        self.gpu, self.f, self.p = gpu, None, None
+
+    def start(self):
+        try:
+            self.f = tempfile.NamedTemporaryFile("w+", suffix=".csv", delete=False)
+            self.p = subprocess.Popen(["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "200"],
+                                      stdout=self.f, stderr=subprocess.DEVNULL)
+        except Exception:
+            self.p = None
+
+    def stop(self):
+        if not self.p:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.25)
+        self.p.terminate()
+        self.p.wait()
+        self.f.flush()
+        rows = [l.strip().split(", ") for l in open(self.f.name) if l.strip()]
+        os.unlink(self.f.name)
+        sm = sorted(int(float(r[1])) for r in rows if len(r) >= 9)
+        reasons = set()
+        for r in rows:
+            if len(r) < 9:
+                continue
+            for name, v in zip(["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"], r[5:9]):
+                if v.strip().lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": int(float(rows[0][2])) if rows else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_oracle_rate(cfg_kw, steps, warmup, sample):
+    """Times the CPU restatement of the path (oracle/, OpenMP over the reference's independent j/k loops)
+    on all host cores for a bounded sample of the workload; returns (updates/s, cores, seconds, sample str)."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from orclib import Oracle
+    from romsb200 import cases
+    cores = os.cpu_count() or 1
+    os.environ.setdefault("OMP_NUM_THREADS", str(cores))
+    Lm, Mm, N = sample
+    cfg, st = cases.channel(Lm, Mm, N, **cfg_kw)
+    o = Oracle(cfg, omp=True)
+    cases.initialize(o, st)
+    for _ in range(warmup):
+        o.call("step")
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        o.call("step")
+    dt = time.perf_counter() - t0
+    o.close()
+    return Lm * Mm * N * steps / dt, cores, dt, f"{Lm}x{Mm}x{N} block of the same analytic channel, {steps} baroclinic steps after {warmup} warm-up"
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--size", type=int, nargs=3, default=[1024, 1024, 64], metavar=("Lm", "Mm", "N"))
+    ap.add_argument("--nt", type=int, default=2)
+    ap.add_argument("--cpu-sample", type=int, nargs=3, default=[256, 256, 64])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--kernel-table", default=None, help="write the per-kernel timing table to this file")
+    a = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    Lm, Mm, N = a.size
+    NT = a.nt
+    case_kw = dict(NT=NT, ns_walls=False, nonlin_eos=True)
+    workload = f"analytic baroclinic channel {Lm}x{Mm}x{N} per GPU, T+S" + (f"+{NT - 2} passive" if NT > 2 else "") + \
+               ", nonlinear split EOS, doubly periodic, ndtfast=60 (82 executed barotropic substeps per step)"
+    config = {"workload": workload, "grid_per_gpu": [Lm, Mm, N], "tracers": NT, "l2_policy": "inputs (15 GB of resident state per GPU) larger than L2; no flush",
+              "timing": "CUDA events on the library stream, barrier+sync both sides, max over ranks"}
+
+    if a.impl == "reference":
+        # The reference Fortran cannot be built in this image (no gfortran/MPI/netCDF): the arm times the CPU
+        # restatement of its algorithm (oracle/) with all host threads on a bounded sample of the workload.
+        if rank != 0:
+            return 0
+        steps = max(1, min(a.steps, 3))
+        rate, cores, secs, sample = cpu_oracle_rate(case_kw, steps, min(a.warmup, 1), tuple(a.cpu_sample))
+        line = {"impl": "reference", "metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": a.gpus, "steps": steps, "warmup": min(a.warmup, 1),
+                "ms_per_step": 1e3 * secs / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+                "data": "synthetic", "config": config,
+                "cpu_baseline": {"value": rate, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+                "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+        print(json.dumps(line))
+        return 0
+
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from romsb200 import Roms, cases, FID
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
+    torch.cuda.set_device(local)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    np_xi, np_eta = cases.rank_grid(world)
+    cfg, st = cases.channel(Lm * np_xi, Mm * np_eta, N, sub=(rank % np_xi, rank // np_xi, np_xi, np_eta), **case_kw)
+    g = Roms(cfg, local)
+    if world > 1:
+        g.attach_torch_comm(dist)
+    cases.initialize(g, st)
+    del st
+    lib = g.lib
+    nfast = g.nfast()
+
+    def timed_steps(k):
+        barrier()
+        lib.roms_timer_start(g.h)
+        g.call("run", k)
+        ms = C.c_double()
+        lib.roms_timer_stop(g.h, C.byref(ms))
+        barrier()
+        t = torch.tensor([ms.value], device="cuda", dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    g.call("run", a.warmup)
+    g.sync()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = g.launches()
+    ms = timed_steps(a.steps)
+    launches = g.launches() - l0
+    clocks = sampler.stop() if rank == 0 else None
+    d = g.diag()
+    assert np.isfinite(d).all(), d
+    updates = float(Lm) * Mm * N * world * a.steps
+    value = updates / (ms * 1e-3)
+
+    # ---- e2e: the same steps driven the way the Fortran host drives them: every step the surface forcing comes
+    # from pinned HOST memory (set_forces, main.F:386) and the free surface / barotropic velocities go back to the host.
+    sy, sx = Mm + 4, Lm + 4
+    pin_in = [torch.zeros((sy, sx), dtype=torch.float64).pin_memory() for _ in range(3 + NT)]
+    pin_out = [torch.empty((sy, sx), dtype=torch.float64).pin_memory() for _ in range(3)]
+    in_fields = [("SUSTR", 1, 1), ("SVSTR", 1, 1), ("SWFLX", 1, 1)] + [("STFLX", 1, it) for it in range(1, NT + 1)]
+    dptr = C.POINTER(C.c_double)
+
+    def e2e_step():
+        for t_, (f, l, it) in zip(pin_in, in_fields):
+            lib.roms_push(g.h, FID[f], l, it, C.cast(t_.data_ptr(), dptr))
+        g.call("step")
+        knew = g.get_idx()[6]
+        for t_, f in zip(pin_out, ("ZETA", "UBAR", "VBAR")):
+            lib.roms_pull(g.h, FID[f], knew, 1, C.cast(t_.data_ptr(), dptr))
+    e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    lib.roms_timer_start(g.h)
+    for _ in range(a.steps):
+        e2e_step()
+    ems = C.c_double()
+    lib.roms_timer_stop(g.h, C.byref(ems))
+    barrier()
+    e2e_wall = time.perf_counter() - t0
+    te = torch.tensor([max(ems.value, 0.0), e2e_wall * 1e3], device="cuda", dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e_ms = float(te.max().item())
+    plane = sy * sx * 8
+    e2e = {"value": updates / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": len(pin_in) * plane, "d2h_bytes_per_step": len(pin_out) * plane,
+           "what": "per step: H2D of sustr,svstr,swflx,stflx(1:NT) from pinned host, roms_step, D2H of zeta,ubar,vbar(knew)"}
+
+    # ---- roofline of the dominant kernel: a second pass of the same K steps with every launch bracketed by its own events
+    peak, peak_src = peaks()
+    roof = None
+    table = []
+    if rank == 0:
+        lib.roms_kernel_timing(g.h, 1)
+        g.call("run", a.steps)
+        buf = C.create_string_buffer(1 << 16)
+        lib.roms_kernel_times(g.h, buf, len(buf))
+        lib.roms_kernel_timing(g.h, 0)
+        tot = 0.0
+        for ln in buf.value.decode().splitlines():
+            name, cnt, tms = ln.rsplit(" ", 2)
+            table.append((name, int(cnt), float(tms)))
+            tot += float(tms)
+        table.sort(key=lambda r: -r[2])
+        top = table[0]
+        words, dim = KERNEL_WORDS.get(top[0], (None, 3))
+        npts = Lm * Mm * (N if dim == 3 else 1)
+        avg_ms = top[2] / top[1]
+        if words:
+            ach = words * 8.0 * npts / (avg_ms * 1e-3) / 1e9
+            roof = {"bound": "hbm", "kernel": top[0], "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
+                    "peak_source": peak_src, "algorithmic_bytes_per_launch": words * 8.0 * npts, "avg_launch_ms": avg_ms,
+                    "launches_per_step": top[1] / a.steps, "share_of_step": top[2] / tot}
+        if a.kernel_table:
+            with open(a.kernel_table, "w") as f:
+                f.write(f"# per-kernel CUDA-event times, {a.steps} steps, {workload}\n# kernel launches total_ms avg_ms share algorithmic_GB/s\n")
+                for name, cnt, tms in table:
+                    w, dm = KERNEL_WORDS.get(name, (0, 3))
+                    gbs = w * 8.0 * Lm * Mm * (N if dm == 3 else 1) / (tms / cnt * 1e-3) / 1e9 if w else 0.0
+                    f.write(f"{name} {cnt} {tms:.3f} {tms / cnt:.4f} {tms / tot:.4f} {gbs:.1f}\n")
+    B = step_bytes_per_update(NT, nfast, N)
+    step_roof = {"bytes_per_update": B, "achieved": value * B / 1e9 / world, "peak": peak, "unit": "GB/s per GPU", "frac": value * B / 1e9 / world / peak}
+
+    cpu = None
+    if rank == 0 and world == 1 and not a.no_cpu_baseline:
+        rate, cores, secs, sample = cpu_oracle_rate(case_kw, 2, 1, tuple(a.cpu_sample))
+        cpu = {"value": rate, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}
+    g.close()
+    if rank == 0:
+        line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms / a.steps,
+                "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config,
+                "roofline": roof, "step_roofline": step_roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
+                "diag": {"KE": d[0], "BAROTR_KE": d[1], "MAX_ADV_CFL": d[2], "MAX_VERT_CFL": d[3]}}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

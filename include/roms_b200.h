@@ -116,6 +116,12 @@ int  roms_step(roms_ctx* h);                  /* one baroclinic step: main.F:397
 int  roms_run(roms_ctx* h, int nsteps);       /* nsteps x roms_step                             */
 int  roms_kernel_launches(roms_ctx* h, long* n); /* kernels launched so far by this context    */
 
+/* ---- measurement hooks (the reference's timers.F:35-131 analogue; device-side CUDA events) - */
+int  roms_timer_start(roms_ctx* h);           /* event on the library's stream                  */
+int  roms_timer_stop(roms_ctx* h, double* ms);/* second event + elapsed milliseconds            */
+int  roms_kernel_timing(roms_ctx* h, int on); /* bracket every launch with its own event pair   */
+int  roms_kernel_times(roms_ctx* h, char* buf, int buflen); /* "kernel count total_ms" lines    */
+
 #ifdef __cplusplus
 }
 #endif

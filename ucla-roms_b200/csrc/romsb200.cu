@@ -25,6 +25,10 @@ static thread_local std::string g_err;
     }                                                                                         \
   } while (0)
 
+struct KTimer {
+  const char* name;
+  cudaEvent_t a, b;
+};
 struct FieldSlot {
   std::vector<double*> ptr;   // [lvl*ntrc + itrc]
   int nlvl = 1, ntrc = 1, nk = 1;
@@ -45,6 +49,10 @@ struct roms_ctx {
   int nfast = 0;
   std::vector<double> w1, w2, Cs_w, Cs_r;
   long launches = 0;
+  // optional per-kernel CUDA-event timing (bench.py roofline pass)
+  int ktiming = 0;
+  std::vector<KTimer> ktimers;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   int col_bx = 32, col_by = 2, pl_bx = 128, pl_by = 2;
   int use_smem = 1;
   Comm comm;
@@ -61,10 +69,14 @@ struct roms_ctx {
 static dim3 grid_plane(const roms_ctx* h, int i1, int j0, int j1, int nk, dim3 b) {
   return dim3((i1 + IOFF + 1 + b.x - 1) / b.x, (j1 - j0 + 1 + b.y - 1) / b.y, nk);
 }
+static void kt_begin(roms_ctx* h, const char* name);
+static void kt_end(roms_ctx* h);
 #define PLANE(kern, i1, j0, j1, nk, ...)                                                      \
   do {                                                                                        \
     dim3 b_(h->pl_bx, h->pl_by, 1);                                                           \
+    if (h->ktiming) kt_begin(h, #kern);                                                       \
     kern<<<grid_plane(h, i1, j0, j1, nk, b_), b_, 0, h->st>>>(__VA_ARGS__);                   \
+    if (h->ktiming) kt_end(h);                                                                \
     h->launches++;                                                                            \
   } while (0)
 static size_t col_smem(const roms_ctx* h, int narr) {
@@ -75,9 +87,21 @@ static size_t col_smem(const roms_ctx* h, int narr) {
     dim3 b_(h->col_bx, h->col_by, 1);                                                         \
     size_t sm_ = col_smem(h, narr);                                                           \
     if (sm_ > 48 * 1024) CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_)); \
+    if (h->ktiming) kt_begin(h, #kern);                                                       \
     kern<<<grid_plane(h, i1, j0, j1, 1, b_), b_, sm_, h->st>>>(__VA_ARGS__);                  \
+    if (h->ktiming) kt_end(h);                                                                \
     h->launches++;                                                                            \
   } while (0)
+
+static void kt_begin(roms_ctx* h, const char* name) {
+  KTimer t;
+  t.name = name;
+  cudaEventCreate(&t.a);
+  cudaEventCreate(&t.b);
+  cudaEventRecord(t.a, h->st);
+  h->ktimers.push_back(t);
+}
+static void kt_end(roms_ctx* h) { cudaEventRecord(h->ktimers.back().b, h->st); }
 
 // ------------------------------------------------------------------------------------------------
 // set_scoord.F:4-66 and set_weights.F:7-246, evaluated on the host in the reference's operation order
@@ -289,6 +313,54 @@ int roms_sync(roms_ctx* h) {
   return 0;
 }
 int roms_kernel_launches(roms_ctx* h, long* n) { *n = h->launches; return 0; }
+// device-side timing on the library's own stream (bench.py): events bracket whatever is enqueued between
+int roms_timer_start(roms_ctx* h) {
+  CK(cudaSetDevice(h->device));
+  if (!h->ev0) { CK(cudaEventCreate(&h->ev0)); CK(cudaEventCreate(&h->ev1)); }
+  CK(cudaStreamSynchronize(h->st));
+  CK(cudaEventRecord(h->ev0, h->st));
+  return 0;
+}
+int roms_timer_stop(roms_ctx* h, double* ms) {
+  CK(cudaEventRecord(h->ev1, h->st));
+  CK(cudaEventSynchronize(h->ev1));
+  float f = 0;
+  CK(cudaEventElapsedTime(&f, h->ev0, h->ev1));
+  *ms = f;
+  return 0;
+}
+// per-kernel timing: while on, every launch is bracketed by its own pair of events
+int roms_kernel_timing(roms_ctx* h, int on) {
+  CK(cudaStreamSynchronize(h->st));
+  for (auto& t : h->ktimers) { cudaEventDestroy(t.a); cudaEventDestroy(t.b); }
+  h->ktimers.clear();
+  h->ktiming = on;
+  return 0;
+}
+// writes "name count total_ms\n" lines for every kernel timed since roms_kernel_timing(h,1)
+int roms_kernel_times(roms_ctx* h, char* buf, int buflen) {
+  CK(cudaStreamSynchronize(h->st));
+  std::vector<std::string> names;
+  std::vector<double> tot;
+  std::vector<long> cnt;
+  for (auto& t : h->ktimers) {
+    float f = 0;
+    cudaEventElapsedTime(&f, t.a, t.b);
+    size_t q = 0;
+    for (; q < names.size(); ++q) if (names[q] == t.name) break;
+    if (q == names.size()) { names.push_back(t.name); tot.push_back(0); cnt.push_back(0); }
+    tot[q] += f; cnt[q]++;
+  }
+  std::string out;
+  char line[256];
+  for (size_t q = 0; q < names.size(); ++q) {
+    snprintf(line, sizeof line, "%s %ld %.6f\n", names[q].c_str(), cnt[q], tot[q]);
+    out += line;
+  }
+  if ((int)out.size() + 1 > buflen) { g_err = "roms_kernel_times: buffer too small"; return -1; }
+  memcpy(buf, out.c_str(), out.size() + 1);
+  return 0;
+}
 int roms_get_nfast(roms_ctx* h) { return h->nfast; }
 int roms_get_weights(roms_ctx* h, double* w1, double* w2, int n) {
   for (int i = 1; i <= n; ++i) { w1[i - 1] = h->w1[i]; w2[i - 1] = h->w2[i]; }
@@ -315,7 +387,10 @@ int roms_compute_tile_bounds(roms_ctx* h, int tile, int* istr, int* iend, int* j
 
 // ---- exchange_xxx -------------------------------------------------------------------------------
 static int exchange(roms_ctx* h, std::initializer_list<XF> fl) {
-  return comm_exchange(&h->comm, h->kp, h->st, fl.begin(), (int)fl.size(), &h->launches);
+  if (h->ktiming) kt_begin(h, "exchange_xxx");
+  int rc = comm_exchange(&h->comm, h->kp, h->st, fl.begin(), (int)fl.size(), &h->launches);
+  if (h->ktiming) kt_end(h);
+  return rc;
 }
 int roms_exchange(roms_ctx* h, int nfields, const int* fields, const int* lvls, const int* itrcs) {
   CK(cudaSetDevice(h->device));

@@ -150,6 +150,17 @@ class Roms(CApi):
         f = (C.c_int * 1)(FID[field]); l = (C.c_int * 1)(lvl); t = (C.c_int * 1)(itrc)
         self._check(self.lib.roms_exchange(self.h, 1, f, l, t), "exchange")
 
+    def attach_torch_comm(self, dist):
+        """multi-rank runs: hand the NCCL unique id (broadcast through torch.distributed) to the library"""
+        uid = (C.c_char * 128)()
+        if dist.get_rank() == 0:
+            self._check(self.lib.roms_comm_unique_id(uid, 128), "comm_unique_id")
+        import torch
+        t = torch.frombuffer(bytearray(uid.raw), dtype=torch.uint8).cuda()
+        dist.broadcast(t, 0)
+        raw = bytes(t.cpu().numpy().tobytes())
+        self._check(self.lib.roms_comm_attach(self.h, raw, 128, dist.get_rank(), dist.get_world_size()), "comm_attach")
+
     def alfabeta(self):
         a = np.empty(self.shape2); b = np.empty(self.shape2)
         self._check(self.lib.roms_alfabeta(self.h, a.ctypes.data_as(C.POINTER(C.c_double)), b.ctypes.data_as(C.POINTER(C.c_double))), "alfabeta")

@@ -45,25 +45,48 @@ def _wrap(a, ew, ns):
     return a
 
 
+def rank_grid(world):
+    """NP_XI x NP_ETA for `world` GPUs of one box (1x1, 2x1, 2x2, 4x2)."""
+    return {1: (1, 1), 2: (2, 1), 4: (2, 2), 8: (4, 2)}.get(world, (world, 1))
+
+
+def _noise(ig, jg, k, salt):
+    """deterministic pseudo-random field in [-1,1) as a function of GLOBAL indices (so that every rank of a
+    decomposed run generates exactly the values a single-domain run has)"""
+    x = (ig.astype(np.uint64) * np.uint64(73856093)) ^ (jg.astype(np.uint64) * np.uint64(19349663)) ^ \
+        (k.astype(np.uint64) * np.uint64(83492791)) ^ np.uint64(salt * 2654435761 % (1 << 32))
+    x = (x ^ (x >> np.uint64(15))) * np.uint64(2246822519) % np.uint64(1 << 32)
+    x = (x ^ (x >> np.uint64(13))) * np.uint64(3266489917) % np.uint64(1 << 32)
+    x = x ^ (x >> np.uint64(16))
+    return x.astype(np.float64) / float(1 << 31) - 1.0
+
+
 def channel(Lm=64, Mm=64, N=16, NT=2, ns_walls=False, nonlin_eos=True, dt=120.0, ndtfast=60, dx=1.0e3, dy=1.0e3,
-            depth=4000.0, seed=20260101, perturb=1e-6, amp=None):
+            depth=4000.0, seed=20260101, perturb=1e-6, amp=None, sub=(0, 0, 1, 1)):
+    """Lm, Mm are the GLOBAL interior sizes; sub=(inode, jnode, np_xi, np_eta) selects this rank's block
+    (mpi_setup.F:61-70; sizes must divide evenly).  Returns the cfg and state of that block."""
+    inode, jnode, np_xi, np_eta = sub
+    LmG, MmG = Lm, Mm
+    assert LmG % np_xi == 0 and MmG % np_eta == 0
+    Lm, Mm = LmG // np_xi, MmG // np_eta
+    i0, j0 = inode * Lm, jnode * Mm
     cfg = RomsCfg(Lm=Lm, Mm=Mm, N=N, NT=NT, ew_periodic=1, ns_periodic=0 if ns_walls else 1,
-                  nonlin_eos=1 if nonlin_eos else 0, salinity=1, ndtfast=ndtfast, np_xi=1, np_eta=1, inode=0, jnode=0,
+                  nonlin_eos=1 if nonlin_eos else 0, salinity=1, ndtfast=ndtfast, np_xi=np_xi, np_eta=np_eta, inode=inode, jnode=jnode,
                   dt=dt, rho0=1027.0, g=9.81, Tcoef=0.2, T0=10.0, Scoef=0.8, S0=35.0,
                   rdrg=3.0e-4, rdrg2=0.0, Zob=0.0, gamma2=1.0, theta_s=6.0, theta_b=2.0, hc=25.0)
-    sy, sx = Mm + 4, Lm + 4
-    i = np.arange(-1, Lm + 3)[None, :] + np.zeros((sy, 1))
-    j = np.arange(-1, Mm + 3)[:, None] + np.zeros((1, sx))
-    x = dx * (i - 0.5); y = dy * (j - 0.5)
-    Lx, Ly = dx * Lm, dy * Mm
+    # work on a 3-cell halo so that u/v-point averages exist on the whole 2-cell halo, trim at the end
+    sy, sx = Mm + 6, Lm + 6
+    ig = (np.arange(-2, Lm + 4) + i0)[None, :] + np.zeros((sy, 1), dtype=np.int64)
+    jg = (np.arange(-2, Mm + 4) + j0)[:, None] + np.zeros((1, sx), dtype=np.int64)
+    ig = (ig - 1) % LmG + 1                      # E-W periodic images
+    if not ns_walls:
+        jg = (jg - 1) % MmG + 1
+    x = dx * (ig - 0.5); y = dy * (jg - 0.5)
+    Lx, Ly = dx * LmG, dy * MmG
     if amp is None:
         amp = 0.02 * min(Lx, Ly) / 64.0e3 + 0.01   # keeps the thermal-wind shear independent of the grid size
     st = {}
     h = np.full((sy, sx), depth)
-    st["H"] = h
-    st["PM"] = np.full((sy, sx), 1.0 / dx); st["PN"] = np.full((sy, sx), 1.0 / dy)
-    st["F"] = np.full((sy, sx), 1.0e-4)
-    st["RMASK"] = np.ones((sy, sx))
     zeta = 0.01 * np.sin(2 * np.pi * x / Lx) * np.cos(2 * np.pi * y / Ly)
     z_r, z_w = _depths(h, zeta, N, cfg.theta_s, cfg.theta_b, cfg.hc)
     Hz = z_w[1:] - z_w[:-1]
@@ -71,23 +94,27 @@ def channel(Lm=64, Mm=64, N=16, NT=2, ns_walls=False, nonlin_eos=True, dt=120.0,
         front = amp * np.tanh((y - 0.5 * Ly) / (0.15 * Ly))
     else:
         front = amp * np.sin(2 * np.pi * y / Ly)
+    kk = np.arange(1, N + 1)[:, None, None]
+    nz = lambda salt: _noise(ig[None] + 0 * kk, jg[None] + 0 * kk, kk + 0 * ig[None], salt + seed % 1000)
     T = 4.0 + 10.0 * np.exp(z_r / 50.0) + (front + 0.2 * amp * np.sin(2 * np.pi * x / Lx) * np.cos(2 * np.pi * y / Ly))[None] * np.exp(z_r / 400.0)
     S = 35.0 + 0.1 * amp * np.cos(2 * np.pi * x / Lx)[None] * np.exp(z_r / 300.0) - 0.5 * np.exp(z_r / 100.0)
     u = 0.02 * (np.sin(2 * np.pi * y / Ly) * (1 + 0.3 * np.cos(2 * np.pi * x / Lx)))[None] * np.exp(z_r / 500.0)
     v = 0.01 * (np.sin(2 * np.pi * x / Lx) * np.cos(2 * np.pi * y / Ly))[None] * np.exp(z_r / 500.0)
-    rng = np.random.default_rng(seed)
-    T = T * (1 + perturb * rng.standard_normal(T.shape)); S = S * (1 + perturb * rng.standard_normal(S.shape))
-    u = u + perturb * 0.1 * rng.standard_normal(u.shape); v = v + perturb * 0.1 * rng.standard_normal(v.shape)
+    T = T * (1 + perturb * nz(1)); S = S * (1 + perturb * nz(2))
+    u = u + perturb * 0.1 * nz(3); v = v + perturb * 0.1 * nz(4)
     if ns_walls:
-        v[:, :3, :] = 0.0      # v(:,1)=0 south wall ... j index 1 is array row 2
-        v[:, Mm + 2:, :] = 0.0  # v(:,Mm+1)=0 north wall
-    per_ns = not ns_walls
-    for a in (zeta, T, S, u, v):
-        _wrap(a, True, per_ns)
-    Hz = _wrap(Hz, True, per_ns)
-    Hzu = 0.5 * (Hz + np.roll(Hz, 1, axis=2)); Hzv = 0.5 * (Hz + np.roll(Hz, 1, axis=1))
+        jl = (np.arange(-2, Mm + 4) + j0)
+        v[:, (jl <= 1) | (jl >= MmG + 1), :] = 0.0     # closed south (j=1) and north (j=Mm+1) walls
+    Hzu = np.empty_like(Hz); Hzv = np.empty_like(Hz)
+    Hzu[:, :, 1:] = 0.5 * (Hz[:, :, 1:] + Hz[:, :, :-1]); Hzu[:, :, 0] = Hz[:, :, 0]
+    Hzv[:, 1:, :] = 0.5 * (Hz[:, 1:, :] + Hz[:, :-1, :]); Hzv[:, 0, :] = Hz[:, 0, :]
     ubar = (Hzu * u).sum(0) / Hzu.sum(0); vbar = (Hzv * v).sum(0) / Hzv.sum(0)
-    _wrap(ubar, True, per_ns); _wrap(vbar, True, per_ns)
+    t2 = lambda a: np.ascontiguousarray(a[..., 1:-1, 1:-1])
+    st["H"] = t2(h)
+    st["PM"] = np.full((Mm + 4, Lm + 4), 1.0 / dx); st["PN"] = np.full((Mm + 4, Lm + 4), 1.0 / dy)
+    st["F"] = np.full((Mm + 4, Lm + 4), 1.0e-4)
+    st["RMASK"] = np.ones((Mm + 4, Lm + 4))
+    zeta, ubar, vbar, u, v, T, S = (t2(a) for a in (zeta, ubar, vbar, u, v, T, S))
     st["ZETA"] = {(1, 1): zeta, (2, 1): zeta}
     st["UBAR"] = {(1, 1): ubar, (2, 1): ubar}
     st["VBAR"] = {(1, 1): vbar, (2, 1): vbar}
@@ -95,11 +122,10 @@ def channel(Lm=64, Mm=64, N=16, NT=2, ns_walls=False, nonlin_eos=True, dt=120.0,
     st["V"] = {(1, 1): v, (2, 1): v}
     tr = {(1, 1): T, (2, 1): T, (1, 2): S, (2, 2): S}
     for it in range(3, NT + 1):   # passive tracers (SURVEY.md 8(d) input (4))
-        pz = np.sin(2 * np.pi * (it - 2) * x / Lx)[None] * np.cos(2 * np.pi * y / Ly)[None] * np.exp(z_r / 100.0)
-        _wrap(pz, True, per_ns)
+        pz = t2(np.sin(2 * np.pi * (it - 2) * x / Lx)[None] * np.cos(2 * np.pi * y / Ly)[None] * np.exp(z_r / 100.0))
         tr[(1, it)] = pz; tr[(2, it)] = pz
     st["T"] = tr
-    akv = np.full((N + 1, sy, sx), 1.0e-4)
+    akv = np.full((N + 1, Mm + 4, Lm + 4), 1.0e-4)
     st["AKV"] = akv
     st["AKT"] = {(1, 1): akv, (1, 2): akv}
     return cfg, st
