@@ -54,7 +54,7 @@ struct roms_ctx {
   std::vector<KTimer> ktimers;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   int col_bx = 32, col_by = 2, pl_bx = 128, pl_by = 2;
-  int use_smem = 1;
+  int use_smem = 0;   // measured on B200 (profiles/r1_scratch_policy.txt): occupancy beats shared-memory scratch
   Comm comm;
   double* u(int l) { return f[ROMS_U].ptr[l - 1]; }
   double* v(int l) { return f[ROMS_V].ptr[l - 1]; }
