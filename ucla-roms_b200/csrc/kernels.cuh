@@ -484,72 +484,128 @@ __global__ void k_rd_bott_drag(const __grid_constant__ KP p, const double* __res
 // Four sweeps (up, down, up, down) with two shared-memory arrays per thread:
 //   A: spline CF(2:N)            -> Thomas CF(1:N-1)
 //   B: spline FC(0:N-1) -> rhs(1:N) -> Thomas DC(1:N-1)
+#define KC 4   // levels per register chunk: all global/scratch loads of a chunk are issued before its arithmetic
 template <int MODE>
-__global__ void k_t_vert(const __grid_constant__ KP p, const double* __restrict__ t_rhs, double* __restrict__ t_new, const double* __restrict__ Akt,
-                         const double* __restrict__ stflx, double dtau, int is_temp) {
+__global__ void __launch_bounds__(64, 12)
+k_t_vert(const __grid_constant__ KP p, const double* __restrict__ t_rhs, double* __restrict__ t_new, const double* __restrict__ Akt,
+         const double* __restrict__ stflx, double dtau, int is_temp) {
   extern __shared__ double smem[];
   THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
   ColScr sc = col_scratch(p, c, smem);
   const int N = p.N;
-  // spline forward elimination
-  double Hzk = R3(p.Hz, c, 1), tk = R3(t_rhs, c, 1);
+  const double* __restrict__ gHz = p.Hz;
+  const double* __restrict__ gWe = p.We;
+  const double* __restrict__ gWi = p.Wi;
+  const double* __restrict__ gFd = p.FlxDiv;
+  // ---- sweep 1 (up): spline forward elimination
+  double Hzk = R3(gHz, c, 1), tk = R3(t_rhs, c, 1);
   double CFk = 1.0, FCkm = 2.0 * tk;
   S(1, 0) = FCkm;
-  for (int k = 1; k <= N - 1; ++k) {
-    const double Hzp = R3(p.Hz, c, k + 1), tp = R3(t_rhs, c, k + 1);
-    const double cff = 1.0 / (2.0 * Hzk + Hzp * (2.0 - CFk));
-    CFk = cff * Hzk;                       // CF(k+1)
-    FCkm = cff * (3.0 * (Hzk * tp + Hzp * tk) - Hzp * FCkm);   // FC(k)
-    S(0, k + 1) = CFk;
-    S(1, k) = FCkm;
-    Hzk = Hzp; tk = tp;
+  for (int k0 = 1; k0 <= N - 1; k0 += KC) {
+    double hz[KC], tt[KC];
+#pragma unroll
+    for (int q = 0; q < KC; ++q)
+      if (k0 + q <= N - 1) { hz[q] = R3(gHz, c, k0 + q + 1); tt[q] = R3(t_rhs, c, k0 + q + 1); }
+#pragma unroll
+    for (int q = 0; q < KC; ++q) {
+      const int k = k0 + q;
+      if (k <= N - 1) {
+        const double Hzp = hz[q], tp = tt[q];
+        const double cff = 1.0 / (2.0 * Hzk + Hzp * (2.0 - CFk));
+        CFk = cff * Hzk;                                            // CF(k+1)
+        FCkm = cff * (3.0 * (Hzk * tp + Hzp * tk) - Hzp * FCkm);   // FC(k)
+        S(0, k + 1) = CFk;
+        S(1, k) = FCkm;
+        Hzk = Hzp; tk = tp;
+      }
+    }
   }
-  // back-substitution, vertical flux and its divergence -> rhs(k) in B
+  // ---- sweep 2 (down): back-substitution, vertical flux and its divergence -> rhs(k) in B
   const double cdt = dtau * p.pm[c] * p.pn[c];
   double FCs_p = (2.0 * tk - FCkm) / (1.0 - CFk);   // FC(N) spline value
   double flux_p = 0.0;                               // FC(N)=0 after the sweep
-  for (int k = N - 1; k >= 0; --k) {
-    double FCs = 0.0, flux = 0.0;                        // FC(0) of the spline is never used (flux(0)=0)
-    if (k >= 1) { FCs = S(1, k) - S(0, k + 1) * FCs_p; flux = FCs * RW(p.We, c, k); }
-    // rhs(k+1) = t_new(k+1) - cdt*(flux(k+1)-flux(k))
-    double r = R3(t_new, c, k + 1) - cdt * (flux_p - flux);
-    if (MODE == 1 && k + 1 == N) {
-      if (is_temp) r = r + p.dt * p.swflx[c] * r / R3(p.Hz, c, N);
-      r = r + p.dt * stflx[c];
+  for (int k0 = N - 1; k0 >= 0; k0 -= KC) {
+    double b1[KC], a0[KC], we[KC], tn[KC];
+#pragma unroll
+    for (int q = 0; q < KC; ++q) {
+      const int k = k0 - q;
+      if (k >= 0) {
+        tn[q] = R3(t_new, c, k + 1);
+        if (k >= 1) { b1[q] = S(1, k); a0[q] = S(0, k + 1); we[q] = RW(gWe, c, k); }
+      }
     }
-    S(1, k + 1) = r;
-    FCs_p = FCs; flux_p = flux;
+#pragma unroll
+    for (int q = 0; q < KC; ++q) {
+      const int k = k0 - q;
+      if (k >= 0) {
+        double FCs = 0.0, flux = 0.0;                        // FC(0) of the spline is never used (flux(0)=0)
+        if (k >= 1) { FCs = b1[q] - a0[q] * FCs_p; flux = FCs * we[q]; }
+        double r = tn[q] - cdt * (flux_p - flux);            // rhs(k+1) = t_new(k+1) - cdt*(flux(k+1)-flux(k))
+        if (MODE == 1 && k + 1 == N) {
+          if (is_temp) r = r + p.dt * p.swflx[c] * r / R3(gHz, c, N);
+          r = r + p.dt * stflx[c];
+        }
+        S(1, k + 1) = r;
+        FCs_p = FCs; flux_p = flux;
+      }
+    }
   }
-  // Thomas forward elimination (k upward)
+  // ---- sweep 3 (up): Thomas forward elimination
   const double DC0 = cdt;
-  double Hzf1 = R3(p.Hz, c, 1), Hzf2 = R3(p.Hz, c, 2);
-  if (MODE == 0) { Hzf1 -= R3(p.FlxDiv, c, 1); Hzf2 -= R3(p.FlxDiv, c, 2); }
+  double Hzf1 = R3(gHz, c, 1), Hzf2 = R3(gHz, c, 2);
+  if (MODE == 0) { Hzf1 -= R3(gFd, c, 1); Hzf2 -= R3(gFd, c, 2); }
   double FCt = 2.0 * dtau * RW(Akt, c, 1) / (MODE == 0 ? (Hzf2 + Hzf1) : (Hzf1 + Hzf2));
-  double WC = DC0 * RW(p.Wi, c, 1);
+  double WC = DC0 * RW(gWi, c, 1);
   double cff = 1.0 / (Hzf1 + FCt + DMAX(WC, 0.0));
   double CFt = cff * (FCt - DMIN(WC, 0.0));
   double DCt = cff * S(1, 1);
   S(0, 1) = CFt; S(1, 1) = DCt;
   double Hzfk = Hzf2;
-  for (int k = 2; k <= N - 1; ++k) {
-    double Hzfp = R3(p.Hz, c, k + 1);
-    if (MODE == 0) Hzfp -= R3(p.FlxDiv, c, k + 1);
-    const double FCtk = 2.0 * dtau * RW(Akt, c, k) / (MODE == 0 ? (Hzfp + Hzfk) : (Hzfk + Hzfp));
-    const double WCk = DC0 * RW(p.Wi, c, k);
-    cff = 1.0 / (Hzfk + FCtk + DMAX(WCk, 0.0) + FCt - DMIN(WC, 0.0) - CFt * (FCt + DMAX(WC, 0.0)));
-    const double CFtk = cff * (FCtk - DMIN(WCk, 0.0));
-    DCt = cff * (S(1, k) + DCt * (FCt + DMAX(WC, 0.0)));
-    S(0, k) = CFtk; S(1, k) = DCt;
-    CFt = CFtk; FCt = FCtk; WC = WCk; Hzfk = Hzfp;
+  for (int k0 = 2; k0 <= N - 1; k0 += KC) {
+    double hz[KC], ak[KC], wi[KC], rh[KC];
+#pragma unroll
+    for (int q = 0; q < KC; ++q) {
+      const int k = k0 + q;
+      if (k <= N - 1) {
+        hz[q] = R3(gHz, c, k + 1);
+        if (MODE == 0) hz[q] -= R3(gFd, c, k + 1);
+        ak[q] = RW(Akt, c, k); wi[q] = RW(gWi, c, k); rh[q] = S(1, k);
+      }
+    }
+#pragma unroll
+    for (int q = 0; q < KC; ++q) {
+      const int k = k0 + q;
+      if (k <= N - 1) {
+        const double Hzfp = hz[q];
+        const double FCtk = 2.0 * dtau * ak[q] / (MODE == 0 ? (Hzfp + Hzfk) : (Hzfk + Hzfp));
+        const double WCk = DC0 * wi[q];
+        cff = 1.0 / (Hzfk + FCtk + DMAX(WCk, 0.0) + FCt - DMIN(WC, 0.0) - CFt * (FCt + DMAX(WC, 0.0)));
+        const double CFtk = cff * (FCtk - DMIN(WCk, 0.0));
+        DCt = cff * (rh[q] + DCt * (FCt + DMAX(WC, 0.0)));
+        S(0, k) = CFtk; S(1, k) = DCt;
+        CFt = CFtk; FCt = FCtk; WC = WCk; Hzfk = Hzfp;
+      }
+    }
   }
+  // ---- sweep 4 (down): back-substitution
   const double rm = MODE == 1 ? p.rmask[c] : 1.0;
   double tkp = (S(1, N) + DCt * (FCt + DMAX(WC, 0.0))) / (Hzfk + FCt - DMIN(WC, 0.0) - CFt * (FCt + DMAX(WC, 0.0)));
   if (MODE == 1) tkp = tkp * rm;
   R3(t_new, c, N) = tkp;
-  for (int k = N - 1; k >= 1; --k) {
-    tkp = S(1, k) + S(0, k) * tkp;
-    if (MODE == 1) tkp = tkp * rm;
-    R3(t_new, c, k) = tkp;
+  for (int k0 = N - 1; k0 >= 1; k0 -= KC) {
+    double dc[KC], cf[KC];
+#pragma unroll
+    for (int q = 0; q < KC; ++q)
+      if (k0 - q >= 1) { dc[q] = S(1, k0 - q); cf[q] = S(0, k0 - q); }
+#pragma unroll
+    for (int q = 0; q < KC; ++q) {
+      const int k = k0 - q;
+      if (k >= 1) {
+        tkp = dc[q] + cf[q] * tkp;
+        if (MODE == 1) tkp = tkp * rm;
+        R3(t_new, c, k) = tkp;
+      }
+    }
   }
 }
 
