@@ -618,108 +618,164 @@ k_t_vert(const __grid_constant__ KP p, const double* __restrict__ t_rhs, double*
 //         drag r_D, output Hz_u*u and the barotropic forcing rufrc/rvfrc.
 // Sweeps: up (spline elimination), down (spline back-substitution + final ru + Thomas elimination),
 // up (Thomas back-substitution).  A: spline CF(2:N) -> Thomas CF(k-1) in slot k; B: spline FC(0:N-1) -> DC(2:N).
+#define KC2 2
 template <int MODE, int DIR>
-__global__ void k_uv_vert(const __grid_constant__ KP p, const double* __restrict__ u_rhs, double* __restrict__ u_new, const double* __restrict__ u_stp,
-                          double* __restrict__ u_indx, double dtau, double cf_stp, double cf_bak) {
+__global__ void __launch_bounds__(64, 8)
+k_uv_vert(const __grid_constant__ KP p, const double* __restrict__ u_rhs, double* __restrict__ u_new, const double* __restrict__ u_stp,
+          double* __restrict__ u_indx, double dtau, double cf_stp, double cf_bak) {
   extern __shared__ double smem[];
   THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
   ColScr sc = col_scratch(p, c, smem);
   const int N = p.N;
   const long d = DIR == 0 ? 1 : SX;
-  double* r = DIR == 0 ? p.ru : p.rv;
+  double* __restrict__ r = DIR == 0 ? p.ru : p.rv;
   const double* msk = DIR == 0 ? p.umask : p.vmask;
   const double strs = DIR == 0 ? p.sustr[c] : p.svstr[c];
-  // spline elimination (upward)
-#define HZ4(k) (0.5625 * (R3(p.Hz, c, k) + R3(p.Hz, c - d, k)) - 0.0625 * (R3(p.Hz, c + d, k) + R3(p.Hz, c - 2 * d, k)))
+  const double* __restrict__ gHz = p.Hz;
+  const double* __restrict__ gWe = p.We;
+  const double* __restrict__ gWi = p.Wi;
+  const double* __restrict__ gFd = p.FlxDiv;
+  const double* __restrict__ gAkv = p.Akv;
+  // ---- sweep 1 (up): spline elimination
+#define HZ4(k) (0.5625 * (R3(gHz, c, k) + R3(gHz, c - d, k)) - 0.0625 * (R3(gHz, c + d, k) + R3(gHz, c - 2 * d, k)))
   double DCk = HZ4(1), uk = R3(u_rhs, c, 1);
   double CFk = 1.0, FCkm = 2.0 * uk;
   S(1, 0) = FCkm;
-  for (int k = 1; k <= N - 1; ++k) {
-    const double DCp = HZ4(k + 1), up = R3(u_rhs, c, k + 1);
-    const double cff = 1.0 / (2.0 * DCk + DCp * (2.0 - CFk));
-    CFk = cff * DCk;
-    FCkm = cff * (3.0 * (DCk * up + DCp * uk) - DCp * FCkm);
-    S(0, k + 1) = CFk;
-    S(1, k) = FCkm;
-    DCk = DCp; uk = up;
+  for (int k0 = 1; k0 <= N - 1; k0 += KC) {
+    double h0[KC], h1[KC], h2[KC], h3[KC], uu[KC];
+#pragma unroll
+    for (int q = 0; q < KC; ++q)
+      if (k0 + q <= N - 1) {
+        const int k = k0 + q + 1;
+        h0[q] = R3(gHz, c, k); h1[q] = R3(gHz, c - d, k); h2[q] = R3(gHz, c + d, k); h3[q] = R3(gHz, c - 2 * d, k);
+        uu[q] = R3(u_rhs, c, k);
+      }
+#pragma unroll
+    for (int q = 0; q < KC; ++q) {
+      const int k = k0 + q;
+      if (k <= N - 1) {
+        const double DCp = 0.5625 * (h0[q] + h1[q]) - 0.0625 * (h2[q] + h3[q]), up = uu[q];
+        const double cff = 1.0 / (2.0 * DCk + DCp * (2.0 - CFk));
+        CFk = cff * DCk;
+        FCkm = cff * (3.0 * (DCk * up + DCp * uk) - DCp * FCkm);
+        S(0, k + 1) = CFk;
+        S(1, k) = FCkm;
+        DCk = DCp; uk = up;
+      }
+    }
   }
 #undef HZ4
-  // downward: spline back-substitution -> vertical flux DCf(k) -> ru(k+1) final -> Thomas row k+1
+  // ---- sweep 2 (down): spline back-substitution -> vertical flux DCf(k) -> ru(k+1) final -> Thomas row k+1
   const double mp = msk[c + d], mm = msk[c - d];
   const double DC0 = dtau * 0.25 * (p.pm[c] + p.pm[c - d]) * (p.pn[c] + p.pn[c - d]);
+  const double rD = 0.5 * dtau * (p.r_D[c] + p.r_D[c - d]);
   double FCs_p = (2.0 * uk - FCkm) / (1.0 - CFk);   // FC(N)
   double DCf_p = 0.0;                                // DC(N)=0
-  // Thomas state carried downward
-  double FCt_k = 0, WC_k = 0, CFt_k = 0, DCt_kp = 0;   // FC(k), WC(k), CF(k), DC(k+1) of the row above
-#define HZF(cc, k) (MODE == 0 ? (R3(p.Hz, cc, k) - R3(p.FlxDiv, cc, k)) : R3(p.Hz, cc, k))
-  double Hzf_c = HZF(c, N), Hzf_d = HZF(c - d, N);     // level k+1 (row being eliminated)
-  for (int k = N - 1; k >= 0; --k) {
-    double DCf = 0.0;
-    if (k >= 1) {
-      const double FCs = S(1, k) - S(0, k + 1) * FCs_p;
-      const double We0 = RW(p.We, c, k), Wem = RW(p.We, c - d, k);
-      DCf = FCs * 0.5 * (We0 + Wem - 0.125 * ((RW(p.We, c + d, k) - We0) * mp - (Wem - RW(p.We, c - 2 * d, k)) * mm));
-      FCs_p = FCs;
+  double FCt_k = 0, WC_k = 0, CFt_k = 0, DCt_kp = 0;   // Thomas FC(k), WC(k), CF(k), DC(k+1) of the row above
+  // raw thicknesses of the row being eliminated (level kk), carried from the previous iteration's loads
+  double Hz_c = R3(gHz, c, N), Hz_d = R3(gHz, c - d, N), Fd_c = 0.0, Fd_d = 0.0;
+  if (MODE == 0) { Fd_c = R3(gFd, c, N); Fd_d = R3(gFd, c - d, N); }
+  for (int k0 = N - 1; k0 >= 0; k0 -= KC2) {
+    double sB[KC2], sA[KC2], w0[KC2], w1[KC2], w2[KC2], w3[KC2], rr[KC2], us[KC2], ui[KC2];
+    double hcm[KC2], hdm[KC2], fcm[KC2], fdm[KC2], akc[KC2], akd[KC2], wic[KC2], wid[KC2];
+#pragma unroll
+    for (int q = 0; q < KC2; ++q) {
+      const int k = k0 - q, kk = k + 1;
+      if (k >= 0) {
+        if (k >= 1) {
+          sB[q] = S(1, k); sA[q] = S(0, k + 1);
+          w0[q] = RW(gWe, c, k); w1[q] = RW(gWe, c - d, k); w2[q] = RW(gWe, c + d, k); w3[q] = RW(gWe, c - 2 * d, k);
+          hcm[q] = R3(gHz, c, kk - 1); hdm[q] = R3(gHz, c - d, kk - 1);
+          if (MODE == 0) { fcm[q] = R3(gFd, c, kk - 1); fdm[q] = R3(gFd, c - d, kk - 1); }
+          akc[q] = RW(gAkv, c, kk - 1); akd[q] = RW(gAkv, c - d, kk - 1);
+          wic[q] = RW(gWi, c, kk - 1); wid[q] = RW(gWi, c - d, kk - 1);
+        }
+        rr[q] = R3(r, c, kk);
+        if (MODE == 0) { us[q] = R3(u_stp, c, kk); ui[q] = R3(u_indx, c, kk); }
+        else us[q] = R3(u_new, c, kk);
+      }
     }
-    const int kk = k + 1;   // row whose final ru is now known
-    const double ruf = (k >= 1) ? (R3(r, c, kk) - DCf_p + DCf) : (R3(r, c, 1) - DCf_p);
-    if (MODE == 1) R3(r, c, kk) = ruf;   // kept for the ascending rufrc sum (step3d_uv1.F:194-206)
-    DCf_p = DCf;
-    // right-hand side of row kk
-    double rhs;
-    if (MODE == 0) {
-      const double us = R3(u_stp, c, kk);
-      const double Hz_c = R3(p.Hz, c, kk), Hz_d = R3(p.Hz, c - d, kk);
-      const double Hzb = 0.5 * ((Hz_c + R3(p.FlxDiv, c, kk)) + (Hz_d + R3(p.FlxDiv, c - d, kk)));
-      rhs = Hzb * (cf_stp * us + cf_bak * R3(u_indx, c, kk)) + DC0 * ruf;
-      R3(u_indx, c, kk) = 0.5 * (Hz_c + Hz_d) * us;
-    } else {
-      rhs = R3(u_new, c, kk) + DC0 * ruf;
+#pragma unroll
+    for (int q = 0; q < KC2; ++q) {
+      const int k = k0 - q, kk = k + 1;   // kk: row whose final ru becomes known in this iteration
+      if (k >= 0) {
+        double DCf = 0.0;
+        if (k >= 1) {
+          const double FCs = sB[q] - sA[q] * FCs_p;
+          DCf = FCs * 0.5 * (w0[q] + w1[q] - 0.125 * ((w2[q] - w0[q]) * mp - (w1[q] - w3[q]) * mm));
+          FCs_p = FCs;
+        }
+        const double ruf = (k >= 1) ? (rr[q] - DCf_p + DCf) : (rr[q] - DCf_p);
+        if (MODE == 1) R3(r, c, kk) = ruf;   // kept for the ascending rufrc sum (step3d_uv1.F:194-206)
+        DCf_p = DCf;
+        double rhs;
+        if (MODE == 0) {
+          const double Hzb = 0.5 * ((Hz_c + Fd_c) + (Hz_d + Fd_d));
+          rhs = Hzb * (cf_stp * us[q] + cf_bak * ui[q]) + DC0 * ruf;
+          R3(u_indx, c, kk) = 0.5 * (Hz_c + Hz_d) * us[q];
+        } else {
+          rhs = us[q] + DC0 * ruf;
+        }
+        const double Hzf_c = MODE == 0 ? (Hz_c - Fd_c) : Hz_c, Hzf_d = MODE == 0 ? (Hz_d - Fd_d) : Hz_d;
+        if (kk == 1) {
+          const double u1 = (rhs + DCt_kp * (FCt_k - DMIN(WC_k, 0.0))) /
+                            (0.5 * (Hzf_c + Hzf_d) + rD + FCt_k + DMAX(WC_k, 0.0) - CFt_k * (FCt_k - DMIN(WC_k, 0.0)));
+          S(1, 1) = u1;
+        } else {
+          const double Hzf_cm = MODE == 0 ? (hcm[q] - fcm[q]) : hcm[q], Hzf_dm = MODE == 0 ? (hdm[q] - fdm[q]) : hdm[q];
+          const double FCt_m = 2.0 * dtau * (akc[q] + akd[q]) / (Hzf_c + Hzf_d + Hzf_cm + Hzf_dm);
+          const double WC_m = DC0 * 0.5 * (wic[q] + wid[q]);
+          double cff, DCt;
+          if (kk == N) {
+            cff = 1.0 / (0.5 * (Hzf_c + Hzf_d) + FCt_m - DMIN(WC_m, 0.0));
+            DCt = cff * (rhs + dtau * strs);
+          } else {
+            cff = 1.0 / (0.5 * (Hzf_c + Hzf_d) + FCt_m - DMIN(WC_m, 0.0) + FCt_k + DMAX(WC_k, 0.0) - CFt_k * (FCt_k - DMIN(WC_k, 0.0)));
+            DCt = cff * (rhs + DCt_kp * (FCt_k - DMIN(WC_k, 0.0)));
+          }
+          const double CFt_m = cff * (FCt_m + DMAX(WC_m, 0.0));
+          S(0, kk) = CFt_m;         // Thomas CF(kk-1) goes to slot A(kk): spline CF(kk) was consumed above, A(kk-1) is still live
+          S(1, kk) = DCt;           // Thomas DC(kk): spline FC(kk) is dead
+          FCt_k = FCt_m; WC_k = WC_m; CFt_k = CFt_m; DCt_kp = DCt;
+          Hz_c = hcm[q]; Hz_d = hdm[q];
+          if (MODE == 0) { Fd_c = fcm[q]; Fd_d = fdm[q]; }
+        }
+      }
     }
-    if (kk == 1) {
-      // bottom row: solve for u(1)
-      const double rD = 0.5 * dtau * (p.r_D[c] + p.r_D[c - d]);
-      double u1 = (rhs + DCt_kp * (FCt_k - DMIN(WC_k, 0.0))) /
-                  (0.5 * (Hzf_c + Hzf_d) + rD + FCt_k + DMAX(WC_k, 0.0) - CFt_k * (FCt_k - DMIN(WC_k, 0.0)));
-      S(1, 1) = u1;
-      break;
-    }
-    // coefficients between rows kk-1 and kk
-    const double Hzf_cm = HZF(c, kk - 1), Hzf_dm = HZF(c - d, kk - 1);
-    const double FCt_m = 2.0 * dtau * (RW(p.Akv, c, kk - 1) + RW(p.Akv, c - d, kk - 1)) / (Hzf_c + Hzf_d + Hzf_cm + Hzf_dm);
-    const double WC_m = DC0 * 0.5 * (RW(p.Wi, c, kk - 1) + RW(p.Wi, c - d, kk - 1));
-    double cff, DCt;
-    if (kk == N) {
-      cff = 1.0 / (0.5 * (Hzf_c + Hzf_d) + FCt_m - DMIN(WC_m, 0.0));
-      DCt = cff * (rhs + dtau * strs);
-    } else {
-      cff = 1.0 / (0.5 * (Hzf_c + Hzf_d) + FCt_m - DMIN(WC_m, 0.0) + FCt_k + DMAX(WC_k, 0.0) - CFt_k * (FCt_k - DMIN(WC_k, 0.0)));
-      DCt = cff * (rhs + DCt_kp * (FCt_k - DMIN(WC_k, 0.0)));
-    }
-    const double CFt_m = cff * (FCt_m + DMAX(WC_m, 0.0));
-    S(0, kk) = CFt_m;         // Thomas CF(kk-1) goes to slot A(kk): spline CF(kk) was consumed above, A(kk-1) is still live
-    S(1, kk) = DCt;           // Thomas DC(kk): spline FC(kk) is dead
-    FCt_k = FCt_m; WC_k = WC_m; CFt_k = CFt_m; DCt_kp = DCt;
-    Hzf_c = Hzf_cm; Hzf_d = Hzf_dm;
   }
-#undef HZF
-  // upward back-substitution
+  // ---- sweep 3 (up): back-substitution
   double uprev = S(1, 1);
   if (MODE == 0) {
     R3(u_new, c, 1) = uprev;
-    for (int k = 2; k <= N; ++k) {
-      uprev = S(1, k) + S(0, k) * uprev;
-      R3(u_new, c, k) = uprev;
+    for (int k0 = 2; k0 <= N; k0 += KC) {
+      double dc[KC], cf[KC];
+#pragma unroll
+      for (int q = 0; q < KC; ++q)
+        if (k0 + q <= N) { dc[q] = S(1, k0 + q); cf[q] = S(0, k0 + q); }
+#pragma unroll
+      for (int q = 0; q < KC; ++q)
+        if (k0 + q <= N) { uprev = dc[q] + cf[q] * uprev; R3(u_new, c, k0 + q) = uprev; }
     }
   } else {
     const double dmn = DIR == 0 ? p.dm_u[c] * p.dn_u[c] : p.dm_v[c] * p.dn_v[c];
     double* rfrc = DIR == 0 ? p.rufrc : p.rvfrc;
-    R3(u_new, c, 1) = uprev * 0.5 * (R3(p.Hz, c, 1) + R3(p.Hz, c - d, 1));
+    R3(u_new, c, 1) = uprev * 0.5 * (R3(gHz, c, 1) + R3(gHz, c - d, 1));
     double rf = R3(r, c, 1) + dmn * (strs - 0.5 * (p.r_D[c - d] + p.r_D[c]) * uprev);
-    for (int k = 2; k <= N; ++k) {
-      uprev = S(1, k) + S(0, k) * uprev;
-      R3(u_new, c, k) = uprev * 0.5 * (R3(p.Hz, c, k) + R3(p.Hz, c - d, k));
-      rf = rf + R3(r, c, k);
+    for (int k0 = 2; k0 <= N; k0 += KC) {
+      double dc[KC], cf[KC], ha[KC], hb[KC], rk[KC];
+#pragma unroll
+      for (int q = 0; q < KC; ++q)
+        if (k0 + q <= N) {
+          dc[q] = S(1, k0 + q); cf[q] = S(0, k0 + q);
+          ha[q] = R3(gHz, c, k0 + q); hb[q] = R3(gHz, c - d, k0 + q); rk[q] = R3(r, c, k0 + q);
+        }
+#pragma unroll
+      for (int q = 0; q < KC; ++q)
+        if (k0 + q <= N) {
+          uprev = dc[q] + cf[q] * uprev;
+          R3(u_new, c, k0 + q) = uprev * 0.5 * (ha[q] + hb[q]);
+          rf = rf + rk[q];
+        }
     }
     rfrc[c] = rf;
   }
