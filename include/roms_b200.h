@@ -116,6 +116,15 @@ int  roms_step(roms_ctx* h);                  /* one baroclinic step: main.F:397
 int  roms_run(roms_ctx* h, int nsteps);       /* nsteps x roms_step                             */
 int  roms_kernel_launches(roms_ctx* h, long* n); /* kernels launched so far by this context    */
 
+/* ---- multi-GPU: 2-D subdomain split, one process per GPU (replaces mpi_setup.F / mpi_exchanges.F) ---- */
+int  roms_comm_unique_id(char* out, int len);  /* rank 0: NCCL unique id (>=128 bytes) to broadcast   */
+int  roms_comm_attach(roms_ctx* h, const char* id, int len, int rank, int world);
+                                               /* rank = jnode*np_xi+inode (mpi_setup.F:61-70)        */
+int  roms_decomp_neighbor(int np_xi, int np_eta, int inode, int jnode, int ew_periodic, int ns_periodic, int d);
+                                               /* neighbour rank in direction d=0..7 (W,E,S,N,SW,SE,NW,NE), -1 at a wall */
+int  roms_decomp_box(int Lm, int Mm, int d, int send, int out[4]); /* i0,j0,ni,nj of the message to/from direction d */
+int  roms_decomp_opposite(int d);
+
 /* ---- measurement hooks (the reference's timers.F:35-131 analogue; device-side CUDA events) - */
 int  roms_timer_start(roms_ctx* h);           /* event on the library's stream                  */
 int  roms_timer_stop(roms_ctx* h, double* ms);/* second event + elapsed milliseconds            */

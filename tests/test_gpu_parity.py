@@ -116,3 +116,16 @@ def test_alfabeta():
     o.call("alfabeta", ao.ctypes.data_as(C.POINTER(C.c_double)), bo.ctypes.data_as(C.POINTER(C.c_double)))
     assert parity_walk.rel(a, ao) < 1e-14 and parity_walk.rel(b, bo) < 1e-14
     g.close(); o.close()
+
+
+def test_two_gpu_halo_exchange_parity():
+    """NCCL halo swaps: 2 ranks (2x1 split) against the single-domain oracle; skipped on a 1-GPU box."""
+    import subprocess
+    import sys
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    script = os.path.join(os.path.dirname(__file__), "mgpu_parity.py")
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+                        "--master-port", "29731", script, "3"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]

@@ -1,0 +1,212 @@
+// comm_impl.cuh -- exchange_xxx (mpi_exchanges.F:34-40) implementation; included by romsb200.cu.
+//  * one subdomain (np_xi*np_eta == 1): periodic wrap = one device-side halo-copy kernel per <=4 fields;
+//  * several subdomains: one pack kernel fills the 8 neighbour messages of up to 4 fields (the reference
+//    concatenates up to 4 fields per message too, mpi_exchanges.F:504-506), one grouped
+//    ncclSend/ncclRecv over NVLink/NVSwitch moves them, one unpack kernel scatters the halos.
+//    Everything is enqueued on the library's stream: no host synchronisation inside a step.
+#pragma once
+#include "decomp.h"
+#ifdef ROMS_WITH_NCCL
+#include <nccl.h>
+#endif
+
+struct MsgGeom {
+  DirBox box[8];
+  double* buf[8];
+  int active[8];
+};
+// blockIdx.y = direction; blockIdx.z strides over the concatenated planes of the fields in hl
+template <bool PACK>
+__global__ void k_halo_msg(const __grid_constant__ KP p, const __grid_constant__ HaloList hl, const __grid_constant__ MsgGeom g, int nplanes) {
+  const int d = blockIdx.y;
+  if (!g.active[d]) return;
+  const DirBox b = g.box[d];
+  const int cell = blockIdx.x * blockDim.x + threadIdx.x;
+  if (cell >= b.ni * b.nj) return;
+  const int jj = cell / b.ni, ii = cell - jj * b.ni;
+  const long c = CIDX(b.i0 + ii, b.j0 + jj);
+  for (int pl = blockIdx.z; pl < nplanes; pl += gridDim.z) {
+    int f = 0, k = pl;
+    while (k >= hl.nk[f]) { k -= hl.nk[f]; ++f; }
+    double* a = hl.a[f] + c + (long)k * p.SXY;
+    double* m = g.buf[d] + (long)pl * (b.ni * b.nj) + cell;
+    if (PACK) *m = *a; else *a = *m;
+  }
+}
+
+struct NcclState {
+#ifdef ROMS_WITH_NCCL
+  ncclComm_t comm = nullptr;
+#endif
+  int rank = 0, world = 1;
+  double* sbuf[8] = {nullptr};
+  double* rbuf[8] = {nullptr};
+  double* red = nullptr;
+  int nb[8];
+};
+
+int comm_init(Comm* cm, const roms_cfg* cfg) {
+  cm->np_xi = cfg->np_xi > 0 ? cfg->np_xi : 1;
+  cm->np_eta = cfg->np_eta > 0 ? cfg->np_eta : 1;
+  cm->inode = cfg->inode; cm->jnode = cfg->jnode;
+  cm->ew_periodic = cfg->ew_periodic; cm->ns_periodic = cfg->ns_periodic;
+  return 0;
+}
+int comm_destroy(Comm* cm) {
+  NcclState* ns = (NcclState*)cm->nccl;
+  if (ns) {
+    for (int d = 0; d < 8; ++d) { cudaFree(ns->sbuf[d]); cudaFree(ns->rbuf[d]); }
+    cudaFree(ns->red);
+#ifdef ROMS_WITH_NCCL
+    if (ns->comm) ncclCommDestroy(ns->comm);
+#endif
+    delete ns;
+    cm->nccl = nullptr;
+  }
+  return 0;
+}
+
+static int comm_attach(Comm* cm, const KP& p, const char* id, int len, int rank, int world) {
+#ifdef ROMS_WITH_NCCL
+  if (world != cm->np_xi * cm->np_eta) { g_err = "roms_comm_attach: world size != np_xi*np_eta"; return -1; }
+  if (rank != cm->jnode * cm->np_xi + cm->inode) { g_err = "roms_comm_attach: rank != jnode*np_xi+inode (mpi_setup.F:61-70)"; return -1; }
+  if (len < (int)sizeof(ncclUniqueId)) { g_err = "roms_comm_attach: id too short"; return -1; }
+  NcclState* ns = new NcclState();
+  ns->rank = rank; ns->world = world;
+  ncclUniqueId uid;
+  memcpy(&uid, id, sizeof(uid));
+  ncclResult_t r = ncclCommInitRank(&ns->comm, world, uid, rank);
+  if (r != ncclSuccess) { g_err = std::string("ncclCommInitRank: ") + ncclGetErrorString(r); delete ns; return -1000 - (int)r; }
+  for (int d = 0; d < 8; ++d) {
+    ns->nb[d] = decomp_neighbor(cm->np_xi, cm->np_eta, cm->inode, cm->jnode, cm->ew_periodic, cm->ns_periodic, d);
+    const DirBox b = decomp_send_box(p.Lm, p.Mm, d);
+    const size_t cap = (size_t)4 * (p.N + 1) * b.ni * b.nj * sizeof(double);
+    CK(cudaMalloc(&ns->sbuf[d], cap));
+    CK(cudaMalloc(&ns->rbuf[d], cap));
+  }
+  CK(cudaMalloc(&ns->red, sizeof(double) * 7 * (world + 1)));
+  cm->nccl = ns;
+  return 0;
+#else
+  (void)cm; (void)p; (void)id; (void)len; (void)rank; (void)world;
+  g_err = "library built without NCCL";
+  return -1;
+#endif
+}
+
+static int comm_exchange_local(Comm* cm, const KP& p, cudaStream_t st, const XF* f, int nf, long* launches) {
+  if (!cm->ew_periodic && !cm->ns_periodic) return 0;
+  for (int n0 = 0; n0 < nf; n0 += 4) {
+    HaloList hl;
+    hl.n = 0;
+    int maxk = 1;
+    for (int n = n0; n < nf && n < n0 + 4; ++n) { hl.a[hl.n] = f[n].a; hl.nk[hl.n] = f[n].nk; if (f[n].nk > maxk) maxk = f[n].nk; hl.n++; }
+    const int ncell = 4 * (p.Lm + 4) + 4 * p.Mm;
+    dim3 b(128, 1, 1), g((ncell + 127) / 128, hl.n, maxk);
+    k_halo_periodic<<<g, b, 0, st>>>(p, hl, cm->ew_periodic, cm->ns_periodic);
+    (*launches)++;
+  }
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { g_err = std::string("halo kernel: ") + cudaGetErrorString(e); return -(int)e; }
+  return 0;
+}
+
+int comm_exchange(Comm* cm, const KP& p, cudaStream_t st, const XF* f, int nf, long* launches) {
+  if (cm->np_xi * cm->np_eta == 1) return comm_exchange_local(cm, p, st, f, nf, launches);
+#ifdef ROMS_WITH_NCCL
+  NcclState* ns = (NcclState*)cm->nccl;
+  if (!ns) { g_err = "multi-rank context without communicator: call roms_comm_attach first"; return -1; }
+  for (int n0 = 0; n0 < nf; n0 += 4) {
+    HaloList hl;
+    hl.n = 0;
+    int nplanes = 0;
+    for (int n = n0; n < nf && n < n0 + 4; ++n) { hl.a[hl.n] = f[n].a; hl.nk[hl.n] = f[n].nk; nplanes += f[n].nk; hl.n++; }
+    for (int q = hl.n; q < 4; ++q) { hl.a[q] = nullptr; hl.nk[q] = 1 << 30; }
+    MsgGeom gs, gr;
+    int maxcell = 4;
+    for (int d = 0; d < 8; ++d) {
+      gs.box[d] = decomp_send_box(p.Lm, p.Mm, d); gs.buf[d] = ns->sbuf[d]; gs.active[d] = ns->nb[d] >= 0;
+      gr.box[d] = decomp_recv_box(p.Lm, p.Mm, d); gr.buf[d] = ns->rbuf[d]; gr.active[d] = ns->nb[d] >= 0;
+      if (gs.box[d].ni * gs.box[d].nj > maxcell) maxcell = gs.box[d].ni * gs.box[d].nj;
+    }
+    dim3 b(128, 1, 1), g((maxcell + 127) / 128, 8, nplanes < 32 ? nplanes : 32);
+    k_halo_msg<true><<<g, b, 0, st>>>(p, hl, gs, nplanes);
+    (*launches)++;
+    ncclGroupStart();
+    for (int d = 0; d < 8; ++d) {
+      const int o = decomp_opposite(d);
+      const size_t cnt = (size_t)nplanes * gs.box[d].ni * gs.box[d].nj;
+      if (ns->nb[d] >= 0) {
+        if (ns->nb[d] == ns->rank) cudaMemcpyAsync(ns->rbuf[o], ns->sbuf[d], cnt * sizeof(double), cudaMemcpyDeviceToDevice, st);
+        else ncclSend(ns->sbuf[d], cnt, ncclDouble, ns->nb[d], ns->comm, st);
+      }
+      if (ns->nb[o] >= 0 && ns->nb[o] != ns->rank) ncclRecv(ns->rbuf[o], cnt, ncclDouble, ns->nb[o], ns->comm, st);
+    }
+    ncclResult_t r = ncclGroupEnd();
+    if (r != ncclSuccess) { g_err = std::string("nccl send/recv: ") + ncclGetErrorString(r); return -1000 - (int)r; }
+    k_halo_msg<false><<<g, b, 0, st>>>(p, hl, gr, nplanes);
+    (*launches)++;
+  }
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) { g_err = std::string("halo exchange: ") + cudaGetErrorString(e); return -(int)e; }
+  return 0;
+#else
+  (void)p; (void)st; (void)f; (void)nf; (void)launches;
+  g_err = "library built without NCCL";
+  return -1;
+#endif
+}
+
+// diag.F:434-504 (rank tree over 13 doubles) -> one ncclAllGather of 7 doubles, combined in rank order
+int comm_diag_reduce(Comm* cm, double red[7]) {
+  if (cm->np_xi * cm->np_eta == 1) return 0;
+#ifdef ROMS_WITH_NCCL
+  NcclState* ns = (NcclState*)cm->nccl;
+  if (!ns) { g_err = "no communicator"; return -1; }
+  cudaStream_t st = 0;
+  CK(cudaMemcpy(ns->red, red, 7 * sizeof(double), cudaMemcpyHostToDevice));
+  ncclResult_t r = ncclAllGather(ns->red, ns->red + 7, 7, ncclDouble, ns->comm, st);
+  if (r != ncclSuccess) { g_err = std::string("ncclAllGather: ") + ncclGetErrorString(r); return -1000 - (int)r; }
+  CK(cudaStreamSynchronize(st));
+  std::vector<double> all(7 * ns->world);
+  CK(cudaMemcpy(all.data(), ns->red + 7, all.size() * sizeof(double), cudaMemcpyDeviceToHost));
+  for (int q = 0; q < 7; ++q) red[q] = 0.0;
+  for (int rk = 0; rk < ns->world; ++rk) {
+    for (int q = 0; q < 5; ++q) red[q] += all[7 * rk + q];
+    if (all[7 * rk + 5] > red[5]) { red[5] = all[7 * rk + 5]; red[6] = all[7 * rk + 6]; }
+  }
+  return 0;
+#else
+  return -1;
+#endif
+}
+
+extern "C" {
+int roms_comm_unique_id(char* out, int len) {
+#ifdef ROMS_WITH_NCCL
+  if (len < (int)sizeof(ncclUniqueId)) { g_err = "roms_comm_unique_id: buffer too small"; return -1; }
+  ncclUniqueId uid;
+  ncclResult_t r = ncclGetUniqueId(&uid);
+  if (r != ncclSuccess) { g_err = std::string("ncclGetUniqueId: ") + ncclGetErrorString(r); return -1000 - (int)r; }
+  memset(out, 0, len);
+  memcpy(out, &uid, sizeof(uid));
+  return 0;
+#else
+  (void)out; (void)len; g_err = "library built without NCCL"; return -1;
+#endif
+}
+int roms_comm_attach(roms_ctx* h, const char* id, int len, int rank, int world) {
+  CK(cudaSetDevice(h->device));
+  return comm_attach(&h->comm, h->kp, id, len, rank, world);
+}
+// host-only geometry, exported so that the decomposition logic is testable without a GPU
+int roms_decomp_neighbor(int np_xi, int np_eta, int inode, int jnode, int ew_periodic, int ns_periodic, int d) {
+  return decomp_neighbor(np_xi, np_eta, inode, jnode, ew_periodic, ns_periodic, d);
+}
+int roms_decomp_box(int Lm, int Mm, int d, int send, int out[4]) {
+  const DirBox b = send ? decomp_send_box(Lm, Mm, d) : decomp_recv_box(Lm, Mm, d);
+  out[0] = b.i0; out[1] = b.j0; out[2] = b.ni; out[3] = b.nj;
+  return 0;
+}
+int roms_decomp_opposite(int d) { return decomp_opposite(d); }
+}

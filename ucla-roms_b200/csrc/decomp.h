@@ -1,0 +1,57 @@
+// decomp.h -- 2-D subdomain decomposition and halo-message geometry (host-only, no CUDA).
+//
+// Replaces mpi_setup.F:15-262 (rank grid, neighbour ranks with periodic wrap) and the message
+// geometry of mpi_exchanges.F:528-670 (8 neighbours, halo width 2).  One GPU = one subdomain =
+// one "tile" of the reference (compute_tile_bounds.h with NSUB_X=NSUB_E=1).
+//
+// Directions d=0..7 enumerate (dx,dy) in {-1,0,1}^2 \ (0,0):
+//   0:W(-1,0) 1:E(+1,0) 2:S(0,-1) 3:N(0,+1) 4:SW 5:SE 6:NW 7:NE ; opposite(d) flips both signs.
+#pragma once
+
+struct DirBox { int i0, j0, ni, nj; };   // inclusive start, extents (model indices, halo = -1,0 / L+1,L+2)
+
+static inline void decomp_dir(int d, int* dx, int* dy) {
+  static const int DX[8] = {-1, +1, 0, 0, -1, +1, -1, +1};
+  static const int DY[8] = {0, 0, -1, +1, -1, -1, +1, +1};
+  *dx = DX[d]; *dy = DY[d];
+}
+static inline int decomp_opposite(int d) {
+  static const int OPP[8] = {1, 0, 3, 2, 7, 6, 5, 4};
+  return OPP[d];
+}
+// rank = jnode*np_xi + inode (mpi_setup.F:61-70).  Returns the neighbour rank in direction d or -1 when
+// the subdomain touches a non-periodic physical edge there (mpi_setup.F:231-250 wraps periodic ones).
+static inline int decomp_neighbor(int np_xi, int np_eta, int inode, int jnode, int ew_periodic, int ns_periodic, int d) {
+  int dx, dy;
+  decomp_dir(d, &dx, &dy);
+  int in = inode + dx, jn = jnode + dy;
+  if (in < 0 || in >= np_xi) {
+    if (!ew_periodic) return -1;
+    in = (in + np_xi) % np_xi;
+  }
+  if (jn < 0 || jn >= np_eta) {
+    if (!ns_periodic) return -1;
+    jn = (jn + np_eta) % np_eta;
+  }
+  return jn * np_xi + in;
+}
+// interior cells this subdomain SENDS to its neighbour in direction d
+static inline DirBox decomp_send_box(int Lm, int Mm, int d) {
+  int dx, dy;
+  decomp_dir(d, &dx, &dy);
+  DirBox b;
+  b.ni = dx == 0 ? Lm : 2; b.nj = dy == 0 ? Mm : 2;
+  b.i0 = dx > 0 ? Lm - 1 : 1;
+  b.j0 = dy > 0 ? Mm - 1 : 1;
+  return b;
+}
+// halo cells this subdomain RECEIVES from its neighbour in direction d
+static inline DirBox decomp_recv_box(int Lm, int Mm, int d) {
+  int dx, dy;
+  decomp_dir(d, &dx, &dy);
+  DirBox b;
+  b.ni = dx == 0 ? Lm : 2; b.nj = dy == 0 ? Mm : 2;
+  b.i0 = dx < 0 ? -1 : (dx > 0 ? Lm + 1 : 1);
+  b.j0 = dy < 0 ? -1 : (dy > 0 ? Mm + 1 : 1);
+  return b;
+}

@@ -709,30 +709,4 @@ int roms_run(roms_ctx* h, int nsteps) {
 
 }  // extern "C"
 
-// ---- exchange_xxx, single-rank path ----------------------------------------------------------------
-int comm_init(Comm* cm, const roms_cfg* cfg) {
-  cm->np_xi = cfg->np_xi > 0 ? cfg->np_xi : 1;
-  cm->np_eta = cfg->np_eta > 0 ? cfg->np_eta : 1;
-  cm->inode = cfg->inode; cm->jnode = cfg->jnode;
-  cm->ew_periodic = cfg->ew_periodic; cm->ns_periodic = cfg->ns_periodic;
-  return 0;
-}
-int comm_destroy(Comm* cm) { (void)cm; return 0; }
-int comm_exchange(Comm* cm, const KP& p, cudaStream_t st, const XF* f, int nf, long* launches) {
-  if (cm->np_xi * cm->np_eta != 1) { g_err = "multi-rank exchange not built into this library"; return -1; }
-  if (!cm->ew_periodic && !cm->ns_periodic) return 0;
-  for (int n0 = 0; n0 < nf; n0 += 4) {
-    HaloList hl;
-    hl.n = 0;
-    int maxk = 1;
-    for (int n = n0; n < nf && n < n0 + 4; ++n) { hl.a[hl.n] = f[n].a; hl.nk[hl.n] = f[n].nk; if (f[n].nk > maxk) maxk = f[n].nk; hl.n++; }
-    const int ncell = 4 * (p.Lm + 4) + 4 * p.Mm;
-    dim3 b(128, 1, 1), g((ncell + 127) / 128, hl.n, maxk);
-    k_halo_periodic<<<g, b, 0, st>>>(p, hl, cm->ew_periodic, cm->ns_periodic);
-    (*launches)++;
-  }
-  cudaError_t e = cudaGetLastError();
-  if (e != cudaSuccess) { g_err = std::string("halo kernel: ") + cudaGetErrorString(e); return -(int)e; }
-  return 0;
-}
-int comm_diag_reduce(Comm* cm, double red[7]) { (void)cm; (void)red; return 0; }
+#include "comm_impl.cuh"
