@@ -61,7 +61,9 @@ struct Orc {
   const int Lm = o.Lm, Mm = o.Mm, N = o.N, SX = o.SX;                                        \
   const size_t SXY = o.SXY;                                                                  \
   const int istr = 1, iend = Lm, jstr = 1, jend = Mm;                                        \
-  (void)N; (void)SXY; (void)istr; (void)iend; (void)jstr; (void)jend; (void)Mm;
+  const bool SWALL = !o.c.ns_periodic, NWALL = !o.c.ns_periodic;                             \
+  const int jstrR = SWALL ? jstr - 1 : jstr, jendR = NWALL ? jend + 1 : jend, jstrV = SWALL ? jstr + 1 : jstr; \
+  (void)N; (void)SXY; (void)istr; (void)iend; (void)jstr; (void)jend; (void)Mm; (void)jstrR; (void)jendR; (void)jstrV; (void)SWALL; (void)NWALL;
 
 // ---------------------------------------------------------------------------------------------
 // exchange_xxx (mpi_exchanges.F:34-40) on a single subdomain: periodic wrap of the 2-cell halo
@@ -72,7 +74,7 @@ void exchange(const Orc& o, double* a, int nk) {
   for (int k = 0; k < nk; ++k) {
     double* p = a + (size_t)k * SXY;
     if (o.c.ew_periodic)
-      for (int j = 1; j <= Mm; ++j) {
+      for (int j = (o.c.ns_periodic ? 1 : 0); j <= (o.c.ns_periodic ? Mm : Mm + 1); ++j) {
         A2(p, -1, j) = A2(p, Lm - 1, j);
         A2(p, 0, j) = A2(p, Lm, j);
         A2(p, Lm + 1, j) = A2(p, 1, j);
@@ -172,15 +174,18 @@ void set_weights(Orc& o) {
 // setup_grid1.F:13-210 (setup_Corls_tile + setup_grid1_tile), then area/volume of setup_grid2.F
 void setup_grid(Orc& o) {
   GEOM
-  for (int j = -1; j <= Mm + 2; ++j)
+  for (int j = (SWALL ? jstr - 1 : jstr - 2); j <= (NWALL ? jend + 1 : jend + 2); ++j)
     for (int i = -1; i <= Lm + 2; ++i) A2(o.fomn, i, j) = A2(o.f, i, j) / (A2(o.pm, i, j) * A2(o.pn, i, j));
-  for (int j = jstr; j <= jend; ++j)
+  for (int j = jstrR; j <= jendR; ++j)
     for (int i = istr; i <= iend; ++i) {
       A2(o.dm_r, i, j) = 1.0 / A2(o.pm, i, j);
       A2(o.dn_r, i, j) = 1.0 / A2(o.pn, i, j);
       A2(o.dm_u, i, j) = 2.0 / (A2(o.pm, i, j) + A2(o.pm, i - 1, j));
       A2(o.dn_u, i, j) = 2.0 / (A2(o.pn, i, j) + A2(o.pn, i - 1, j));
       A2(o.umask, i, j) = A2(o.rmask, i, j) * A2(o.rmask, i - 1, j);
+    }
+  for (int j = jstr; j <= jendR; ++j)
+    for (int i = istr; i <= iend; ++i) {
       A2(o.dm_v, i, j) = 2.0 / (A2(o.pm, i, j) + A2(o.pm, i, j - 1));
       A2(o.dn_v, i, j) = 2.0 / (A2(o.pn, i, j) + A2(o.pn, i, j - 1));
       A2(o.vmask, i, j) = A2(o.rmask, i, j) * A2(o.rmask, i, j - 1);
@@ -206,20 +211,20 @@ void set_depth(Orc& o) {
   const double hc = o.c.hc;
   vec& zeta = o.zeta[o.knew - 1];
   if (o.iic == 0) {
-    for (int j = jstr; j <= jend; ++j)
+    for (int j = jstrR; j <= jendR; ++j)
       for (int i = istr; i <= iend; ++i) A2(o.hinv, i, j) = 1.0 / (A2(o.h, i, j) + hc);
-    for (int j = jstr; j <= jend; ++j)
+    for (int j = jstrR; j <= jendR; ++j)
       for (int i = istr; i <= iend; ++i)
         A2(o.DU_avg1, i, j) = 0.5 * (A2(o.h, i - 1, j) + A2(o.h, i, j) + A2(o.zeta[0], i, j) + A2(o.zeta[0], i - 1, j)) *
                               A2(o.dn_u, i, j) * (A2(o.ubar[0], i, j));
-    for (int j = jstr; j <= jend; ++j)
+    for (int j = jstr; j <= jendR; ++j)
       for (int i = istr; i <= iend; ++i)
         A2(o.DV_avg1, i, j) = 0.5 * (A2(o.h, i, j) + A2(o.h, i, j - 1) + A2(o.zeta[0], i, j) + A2(o.zeta[0], i, j - 1)) *
                               A2(o.dm_v, i, j) * (A2(o.vbar[0], i, j));
   }
   const double ds = 1.0 / double(N);
 #pragma omp parallel for
-  for (int j = jstr; j <= jend; ++j) {
+  for (int j = jstrR; j <= jendR; ++j) {
     for (int i = istr; i <= iend; ++i) AW(o.z_w, i, j, 0) = -A2(o.h, i, j);
     for (int k = 1; k <= N; ++k) {
       double cff_w = hc * ds * double(k - N);
@@ -244,10 +249,10 @@ void set_HUV(Orc& o) {
   vec& v = o.v[o.nrhs - 1];
 #pragma omp parallel for
   for (int k = 1; k <= N; ++k) {
-    for (int j = jstr; j <= jend; ++j)
+    for (int j = jstrR; j <= jendR; ++j)
       for (int i = istr; i <= iend; ++i)
         A3(o.FlxU, i, j, k) = 0.5 * (A3(o.Hz, i, j, k) + A3(o.Hz, i - 1, j, k)) * A2(o.dn_u, i, j) * (A3(u, i, j, k));
-    for (int j = jstr; j <= jend; ++j)
+    for (int j = jstr; j <= jendR; ++j)
       for (int i = istr; i <= iend; ++i)
         A3(o.FlxV, i, j, k) = 0.5 * (A3(o.Hz, i, j, k) + A3(o.Hz, i, j - 1, k)) * A2(o.dm_v, i, j) * (A3(v, i, j, k));
   }
@@ -264,7 +269,7 @@ void set_HUV1(Orc& o) {
   {
     vec DC((size_t)SX * (N + 1)), FC((size_t)SX * (N + 1));
 #pragma omp for
-    for (int j = jstr; j <= jend; ++j) {
+    for (int j = jstrR; j <= jendR; ++j) {
       for (int i = istr; i <= iend; ++i) {
         SL(DC, i, N) = 0.5 * (A3(o.Hz, i, j, N) + A3(o.Hz, i - 1, j, N)) * A2(o.dn_u, i, j);
         SL(DC, i, 0) = SL(DC, i, N);
@@ -287,6 +292,7 @@ void set_HUV1(Orc& o) {
           A3(u, i, j, k) = (A3(u, i, j, k) - SL(FC, i, 0)) * A2(o.umask, i, j);
           A3(o.FlxU, i, j, k) = SL(DC, i, k) * (A3(u, i, j, k));
         }
+      if (j < jstr) continue;   // set_depth.F: "if (j >= jstr)" guards the v part
       for (int i = istr; i <= iend; ++i) {
         SL(DC, i, N) = 0.5 * (A3(o.Hz, i, j, N) + A3(o.Hz, i, j - 1, N)) * A2(o.dm_v, i, j);
         SL(DC, i, 0) = SL(DC, i, N);
@@ -365,6 +371,12 @@ void omega(Orc& o) {
         }
     }
   }
+  if (SWALL)
+    for (int k = 0; k <= N; ++k)
+      for (int i = istr; i <= iend; ++i) { AW(o.We, i, jstr - 1, k) = AW(o.We, i, jstr, k); AW(o.Wi, i, jstr - 1, k) = AW(o.Wi, i, jstr, k); }
+  if (NWALL)
+    for (int k = 0; k <= N; ++k)
+      for (int i = istr; i <= iend; ++i) { AW(o.We, i, jend + 1, k) = AW(o.We, i, jend, k); AW(o.Wi, i, jend + 1, k) = AW(o.Wi, i, jend, k); }
   exw(o, o.We); exw(o, o.Wi);
 }
 
@@ -385,7 +397,7 @@ void rho_eos(Orc& o, int tidx) {
   const double dr00 = r00 - rho0;
   const int nonlin = o.c.nonlin_eos;
 #pragma omp parallel for
-  for (int j = jstr - 2; j <= jend + 2; ++j) {
+  for (int j = (SWALL ? jstr - 1 : jstr - 2); j <= (NWALL ? jend + 1 : jend + 2); ++j) {
     if (!nonlin) {
       double cff = o.c.Tcoef * o.c.T0;
       if (o.c.salinity) cff = o.c.Tcoef * o.c.T0 - o.c.Scoef * o.c.S0;   // rho_eos.F:318-322
@@ -443,7 +455,8 @@ void prsgrd(Orc& o) {
   GEOM
   const double g = o.c.g, rho0 = o.c.rho0, qp2 = 0.0000172;
   const double OneFifth = 0.2, OneTwelfth = 1.0 / 12.0, epsil = 0.0;
-  const int imin = istr - 1, imax = iend + 1, jmin = jstr - 1, jmax = jend + 1;
+  const int imin = istr - 1, imax = iend + 1;
+  const int jmin = SWALL ? jstrV : jstrV - 1, jmax = NWALL ? jend : jend + 1;   // prsgrd.F:96-131
   const double grho = g / rho0, HalfGRho = 0.5 * grho;
   const int nonlin = o.c.nonlin_eos;
   vec& rho = nonlin ? o.rho : o.rho1;
@@ -534,7 +547,11 @@ void prsgrd(Orc& o) {
           } else
             A2(rx, i, j) = (A3(rho, i, j, k) - A3(rho, i, j - 1, k)) * A2(o.vmask, i, j);
         }
-      for (int j = jstr - 1; j <= jend; ++j) {
+      if (SWALL)
+        for (int i = istr; i <= iend; ++i) { A2(FC, i, jmin - 1) = A2(FC, i, jmin); A2(rx, i, jmin - 1) = A2(rx, i, jmin); }
+      if (NWALL)
+        for (int i = istr; i <= iend; ++i) { A2(FC, i, jmax + 1) = A2(FC, i, jmax); A2(rx, i, jmax + 1) = A2(rx, i, jmax); }
+      for (int j = jstrV - 1; j <= jend; ++j) {
         for (int i = istr; i <= iend; ++i) {
           double cff = 2.0 * A2(FC, i, j) * A2(FC, i, j + 1);
           if (cff > epsil) A2(dZx, i, j) = cff / (A2(FC, i, j) + A2(FC, i, j + 1));
@@ -544,7 +561,7 @@ void prsgrd(Orc& o) {
           else A2(dRx, i, j) = 0.0;
           if (nonlin) A2(dRx, i, j) = A2(dRx, i, j) - A3(o.qp1, i, j, k) * A2(dZx, i, j) * (1.0 + 2.0 * qp2 * A3(o.z_r, i, j, k));
         }
-        if (j >= jstr)
+        if (j >= jstrV)
           for (int i = istr; i <= iend; ++i)
             A3(o.rv, i, j, k) = 0.5 * (A3(o.Hz, i, j, k) + A3(o.Hz, i, j - 1, k)) * A2(o.dm_v, i, j) *
                                 (A3(P, i, j - 1, k) - A3(P, i, j, k) -
@@ -561,7 +578,7 @@ void prsgrd(Orc& o) {
 void horiz_rhs_uv(Orc& o, int k, const vec& u, const vec& v, bool upstream, vec& UFx, vec& UFe, vec& VFx, vec& VFe, vec& wrk1, vec& wrk2) {
   GEOM
   const double delta = 0.1666666666666667, gamma = 0.3333333333333333;
-  for (int j = jstr - 1; j <= jend; ++j)
+  for (int j = jstrV - 1; j <= jend; ++j)
     for (int i = istr - 1; i <= iend; ++i) {
       double cff = 0.5 * A3(o.Hz, i, j, k) * (A2(o.fomn, i, j));
       A2(UFx, i, j) = cff * (A3(v, i, j, k) + A3(v, i, j + 1, k));
@@ -569,9 +586,10 @@ void horiz_rhs_uv(Orc& o, int k, const vec& u, const vec& v, bool upstream, vec&
     }
   for (int j = jstr; j <= jend; ++j)
     for (int i = istr; i <= iend; ++i) A3(o.ru, i, j, k) = A3(o.ru, i, j, k) + 0.5 * (A2(UFx, i, j) + A2(UFx, i - 1, j));
-  for (int j = jstr; j <= jend; ++j)
+  for (int j = jstrV; j <= jend; ++j)
     for (int i = istr; i <= iend; ++i) A3(o.rv, i, j, k) = A3(o.rv, i, j, k) - 0.5 * (A2(VFe, i, j) + A2(VFe, i, j - 1));
-  const int imin = istr - 1, imax = iend + 1, jmin = jstr - 1, jmax = jend + 1;
+  const int imin = istr - 1, imax = iend + 1;
+  int jmin, jmax;
   for (int j = jstr; j <= jend; ++j)
     for (int i = imin; i <= imax; ++i) {
       A2(wrk1, i, j) = A3(u, i - 1, j, k) - 2.0 * A3(u, i, j, k) + A3(u, i + 1, j, k);
@@ -586,12 +604,17 @@ void horiz_rhs_uv(Orc& o, int k, const vec& u, const vec& v, bool upstream, vec&
         A2(UFx, i, j) = 0.25 * (A3(u, i, j, k) + A3(u, i + 1, j, k) - delta * (A2(wrk1, i, j) + A2(wrk1, i + 1, j))) *
                         (A3(o.FlxU, i, j, k) + A3(o.FlxU, i + 1, j, k) - delta * (A2(wrk2, i, j) + A2(wrk2, i + 1, j)));
     }
+  jmin = SWALL ? jstrV : jstrV - 1; jmax = NWALL ? jend : jend + 1;
   for (int j = jmin; j <= jmax; ++j)
     for (int i = istr; i <= iend; ++i) {
       A2(wrk1, i, j) = A3(v, i, j - 1, k) - 2.0 * A3(v, i, j, k) + A3(v, i, j + 1, k);
       A2(wrk2, i, j) = A3(o.FlxV, i, j - 1, k) - 2.0 * A3(o.FlxV, i, j, k) + A3(o.FlxV, i, j + 1, k);
     }
-  for (int j = jstr - 1; j <= jend; ++j)
+  if (SWALL)
+    for (int i = istr; i <= iend; ++i) { A2(wrk1, i, jstrV - 1) = A2(wrk1, i, jstrV); A2(wrk2, i, jstrV - 1) = A2(wrk2, i, jstrV); }
+  if (NWALL)
+    for (int i = istr; i <= iend; ++i) { A2(wrk1, i, jend + 1) = A2(wrk1, i, jend); A2(wrk2, i, jend + 1) = A2(wrk2, i, jend); }
+  for (int j = jstrV - 1; j <= jend; ++j)
     for (int i = istr; i <= iend; ++i) {
       if (upstream) {
         double cff = A3(o.FlxV, i, j, k) + A3(o.FlxV, i, j + 1, k) - delta * (A2(wrk2, i, j) + A2(wrk2, i, j + 1));
@@ -600,8 +623,13 @@ void horiz_rhs_uv(Orc& o, int k, const vec& u, const vec& v, bool upstream, vec&
         A2(VFe, i, j) = 0.25 * (A3(v, i, j, k) + A3(v, i, j + 1, k) - delta * (A2(wrk1, i, j) + A2(wrk1, i, j + 1))) *
                         (A3(o.FlxV, i, j, k) + A3(o.FlxV, i, j + 1, k) - delta * (A2(wrk2, i, j) + A2(wrk2, i, j + 1)));
     }
+  jmin = SWALL ? jstr : jstr - 1; jmax = NWALL ? jend : jend + 1;
   for (int j = jmin; j <= jmax; ++j)
     for (int i = istr; i <= iend; ++i) A2(wrk1, i, j) = A3(u, i, j - 1, k) - 2.0 * A3(u, i, j, k) + A3(u, i, j + 1, k);
+  if (SWALL)
+    for (int i = istr; i <= iend; ++i) A2(wrk1, i, jstr - 1) = A2(wrk1, i, jstr);
+  if (NWALL)
+    for (int i = istr; i <= iend; ++i) A2(wrk1, i, jend + 1) = A2(wrk1, i, jend);
   for (int j = jstr; j <= jend + 1; ++j)
     for (int i = istr - 1; i <= iend; ++i) A2(wrk2, i, j) = A3(o.FlxV, i - 1, j, k) - 2.0 * A3(o.FlxV, i, j, k) + A3(o.FlxV, i + 1, j, k);
   for (int j = jstr; j <= jend + 1; ++j)
@@ -613,11 +641,11 @@ void horiz_rhs_uv(Orc& o, int k, const vec& u, const vec& v, bool upstream, vec&
         A2(UFe, i, j) = 0.25 * (A3(u, i, j, k) + A3(u, i, j - 1, k) - delta * (A2(wrk1, i, j) + A2(wrk1, i, j - 1))) *
                         (A3(o.FlxV, i, j, k) + A3(o.FlxV, i - 1, j, k) - delta * (A2(wrk2, i, j) + A2(wrk2, i - 1, j)));
     }
-  for (int j = jstr; j <= jend; ++j)
+  for (int j = jstrV; j <= jend; ++j)
     for (int i = imin; i <= imax; ++i) A2(wrk1, i, j) = A3(v, i - 1, j, k) - 2.0 * A3(v, i, j, k) + A3(v, i + 1, j, k);
-  for (int j = jstr - 1; j <= jend; ++j)
+  for (int j = jstrV - 1; j <= jend; ++j)
     for (int i = istr; i <= iend + 1; ++i) A2(wrk2, i, j) = A3(o.FlxU, i, j - 1, k) - 2.0 * A3(o.FlxU, i, j, k) + A3(o.FlxU, i, j + 1, k);
-  for (int j = jstr; j <= jend; ++j)
+  for (int j = jstrV; j <= jend; ++j)
     for (int i = istr; i <= iend + 1; ++i) {
       if (upstream) {
         double cff = A3(o.FlxU, i, j, k) + A3(o.FlxU, i, j - 1, k) - delta * (A2(wrk2, i, j) + A2(wrk2, i, j - 1));
@@ -629,7 +657,7 @@ void horiz_rhs_uv(Orc& o, int k, const vec& u, const vec& v, bool upstream, vec&
   for (int j = jstr; j <= jend; ++j)
     for (int i = istr; i <= iend; ++i)
       A3(o.ru, i, j, k) = A3(o.ru, i, j, k) - A2(UFx, i, j) + A2(UFx, i - 1, j) - A2(UFe, i, j + 1) + A2(UFe, i, j);
-  for (int j = jstr; j <= jend; ++j)
+  for (int j = jstrV; j <= jend; ++j)
     for (int i = istr; i <= iend; ++i)
       A3(o.rv, i, j, k) = A3(o.rv, i, j, k) - A2(VFx, i + 1, j) + A2(VFx, i, j) - A2(VFe, i, j) + A2(VFe, i, j - 1);
 }
@@ -662,6 +690,7 @@ void vert_rhs_uv(Orc& o, int j, const vec& u, const vec& v, vec& FC, vec& CF, ve
       A3(o.ru, i, j, k + 1) = A3(o.ru, i, j, k + 1) - SL(DC, i, k + 1) + SL(DC, i, k);
     }
   for (int i = istr; i <= iend; ++i) A3(o.ru, i, j, 1) = A3(o.ru, i, j, 1) - SL(DC, i, 1);
+  if (j < jstrV) return;   // "if (j >= jstrV)": no v-row on a southern wall
   // v
   for (int i = istr; i <= iend; ++i) {
     SL(DC, i, 1) = 0.5625 * (A3(o.Hz, i, j, 1) + A3(o.Hz, i, j - 1, 1)) - 0.0625 * (A3(o.Hz, i, j + 1, 1) + A3(o.Hz, i, j - 2, 1));
@@ -694,7 +723,8 @@ void vert_rhs_uv(Orc& o, int j, const vec& u, const vec& v, vec& FC, vec& CF, ve
 // true: UP3 (step3d_t_ISO.F:196).
 void horiz_tracer_fluxes(Orc& o, int k, const vec& t, bool upstream, vec& FX, vec& FE, vec& wrk1) {
   GEOM
-  const int imin = istr - 1, imax = iend + 1, jmin = jstr - 1, jmax = jend + 1;
+  const int imin = istr - 1, imax = iend + 1;
+  const int jmin = SWALL ? jstr : jstr - 1, jmax = NWALL ? jend : jend + 1;   // compute_horiz_tracer_fluxes.h:118-160
   for (int j = jstr; j <= jend; ++j)
     for (int i = imin; i <= imax + 1; ++i) A2(FX, i, j) = (A3(t, i, j, k) - A3(t, i - 1, j, k)) * A2(o.umask, i, j);
   if (upstream) {
@@ -713,6 +743,10 @@ void horiz_tracer_fluxes(Orc& o, int k, const vec& t, bool upstream, vec& FX, ve
   }
   for (int j = jmin; j <= jmax + 1; ++j)
     for (int i = istr; i <= iend; ++i) A2(FE, i, j) = (A3(t, i, j, k) - A3(t, i, j - 1, k)) * A2(o.vmask, i, j);
+  if (SWALL)
+    for (int i = istr; i <= iend; ++i) A2(FE, i, jstr - 1) = A2(FE, i, jstr);
+  if (NWALL)
+    for (int i = istr; i <= iend; ++i) A2(FE, i, jend + 2) = A2(FE, i, jend + 1);
   if (upstream) {
     for (int j = jstr - 1; j <= jend + 1; ++j)
       for (int i = istr; i <= iend; ++i) A2(wrk1, i, j) = A2(FE, i, j + 1) - A2(FE, i, j);
@@ -754,6 +788,46 @@ void vert_tracer_flux(Orc& o, int j, const vec& t, vec& FC, vec& CF) {
   }
 }
 
+// Lateral boundary conditions on closed (wall) northern/southern edges; E-W is periodic or decomposed.
+// zetabc.F:3 (gradient), u2dbc_im.F:150-152,359,442 / u3dbc_im.F:293-295 (gamma2 slip), v2dbc_im.F / v3dbc_im.F
+// (no normal flow), t3dbc_im.F:86-96 (gradient).  Nothing happens on periodic edges.
+void zetabc(Orc& o, vec& zeta_new) {
+  GEOM
+  if (SWALL) for (int i = istr - 1; i <= iend; ++i) A2(zeta_new, i, jstr - 1) = A2(zeta_new, i, jstr) * A2(o.rmask, i, jstr - 1);
+  if (NWALL) for (int i = istr - 1; i <= iend; ++i) A2(zeta_new, i, jend + 1) = A2(zeta_new, i, jend) * A2(o.rmask, i, jend + 1);
+}
+void u2dbc(Orc& o, vec& ubar) {
+  GEOM
+  if (SWALL) for (int i = istr; i <= iend; ++i) A2(ubar, i, jstr - 1) = o.c.gamma2 * A2(ubar, i, jstr) * A2(o.umask, i, jstr - 1);
+  if (NWALL) for (int i = istr; i <= iend; ++i) A2(ubar, i, jend + 1) = o.c.gamma2 * A2(ubar, i, jend) * A2(o.umask, i, jend + 1);
+}
+void v2dbc(Orc& o, vec& vbar) {
+  GEOM
+  if (SWALL) for (int i = istr; i <= iend; ++i) A2(vbar, i, jstr) = 0.0;
+  if (NWALL) for (int i = istr; i <= iend; ++i) A2(vbar, i, jend + 1) = 0.0;
+}
+void u3dbc(Orc& o, vec& u) {
+  GEOM
+  for (int k = 1; k <= N; ++k) {
+    if (SWALL) for (int i = istr; i <= iend; ++i) A3(u, i, jstr - 1, k) = o.c.gamma2 * A3(u, i, jstr, k) * A2(o.umask, i, jstr - 1);
+    if (NWALL) for (int i = istr; i <= iend; ++i) A3(u, i, jend + 1, k) = o.c.gamma2 * A3(u, i, jend, k) * A2(o.umask, i, jend + 1);
+  }
+}
+void v3dbc(Orc& o, vec& v) {
+  GEOM
+  for (int k = 1; k <= N; ++k) {
+    if (SWALL) for (int i = istr; i <= iend; ++i) A3(v, i, jstr, k) = 0.0;
+    if (NWALL) for (int i = istr; i <= iend; ++i) A3(v, i, jend + 1, k) = 0.0;
+  }
+}
+void t3dbc(Orc& o, vec& t) {
+  GEOM
+  for (int k = 1; k <= N; ++k) {
+    if (SWALL) for (int i = istr; i <= iend; ++i) A3(t, i, jstr - 1, k) = A3(t, i, jstr, k) * A2(o.rmask, i, jstr - 1);
+    if (NWALL) for (int i = istr; i <= iend; ++i) A3(t, i, jend + 1, k) = A3(t, i, jend, k) * A2(o.rmask, i, jend + 1);
+  }
+}
+
 // pre_step3d4S.F:23-742 pre_step3d_tile
 void pre_step3d(Orc& o) {
   GEOM
@@ -779,7 +853,7 @@ void pre_step3d(Orc& o) {
 #pragma omp for
     for (int k = 1; k <= N; ++k) {
       double cff = 0.5 * dtau;
-      for (int j = jstr - 1; j <= jend; ++j)
+      for (int j = jstrV - 1; j <= jend; ++j)
         for (int i = istr - 1; i <= iend; ++i) {
           double FlxDiv = cff * A2(o.pm, i, j) * A2(o.pn, i, j) *
                           (A3(o.FlxU, i + 1, j, k) - A3(o.FlxU, i, j, k) + A3(o.FlxV, i, j + 1, k) - A3(o.FlxV, i, j, k) +
@@ -808,7 +882,7 @@ void pre_step3d(Orc& o) {
     const vec& vs = o.v[nstp - 1];
     const double vonKar = 0.41;
     if (o.c.Zob > 0.0) {
-      for (int j = jstr - 1; j <= jend; ++j)
+      for (int j = jstrV - 1; j <= jend; ++j)
         for (int i = istr - 1; i <= iend; ++i) {
           double cff = sqrt(0.333333333333 * (A3(us, i, j, 1) * A3(us, i, j, 1) + A3(us, i + 1, j, 1) * A3(us, i + 1, j, 1) + A3(us, i, j, 1) * A3(us, i + 1, j, 1) +
                                               A3(vs, i, j, 1) * A3(vs, i, j, 1) + A3(vs, i, j + 1, 1) * A3(vs, i, j + 1, 1) + A3(vs, i, j, 1) * A3(vs, i, j + 1, 1)));
@@ -816,13 +890,13 @@ void pre_step3d(Orc& o) {
           A2(r_D_prv, i, j) = cff * (lg * lg);
         }
     } else {
-      for (int j = jstr - 1; j <= jend; ++j)
+      for (int j = jstrV - 1; j <= jend; ++j)
         for (int i = istr - 1; i <= iend; ++i) {
           A2(r_D_prv, i, j) = o.c.rdrg;
           A2(r_D_prv, i, j) = std::min(A2(r_D_prv, i, j), 0.8 * A3(o.Hz, i, j, 1) / dt);
         }
     }
-    for (int j = jstr - 1; j <= jend; ++j)
+    for (int j = jstrV - 1; j <= jend; ++j)
       for (int i = istr - 1; i <= iend; ++i) A2(o.r_D, i, j) = A2(r_D_prv, i, j);
   }
   const vec& wrk1 = r_D_prv;
@@ -863,6 +937,7 @@ void pre_step3d(Orc& o) {
       vert_rhs_uv(o, j, u_rhs, v_rhs, FC, CF, DC);
       // u: implicit vertical viscosity/advection, pre_step3d4S.F:362-424
       for (int dir = 0; dir < 2; ++dir) {
+        if (dir == 1 && j < jstrV) continue;
         const int di = dir == 0 ? 1 : 0, dj = dir == 0 ? 0 : 1;
         vec& un = dir == 0 ? o.u[nnew - 1] : o.v[nnew - 1];
         vec& us = dir == 0 ? o.u[nstp - 1] : o.v[nstp - 1];
@@ -903,7 +978,12 @@ void pre_step3d(Orc& o) {
       }
     }
   }
-  for (int itrc = 0; itrc < NT; ++itrc) ex3(o, o.t[nnew - 1][itrc]);
+  u3dbc(o, o.u[nnew - 1]);
+  v3dbc(o, o.v[nnew - 1]);
+  for (int itrc = 0; itrc < NT; ++itrc) {
+    t3dbc(o, o.t[nnew - 1][itrc]);
+    ex3(o, o.t[nnew - 1][itrc]);
+  }
 }
 
 // step3d_uv1.F:23-534 step3d_uv1_tile
@@ -926,6 +1006,7 @@ void step3d_uv1(Orc& o) {
     for (int j = jstr; j <= jend; ++j) {
       vert_rhs_uv(o, j, u_rhs, v_rhs, FC, CF, DC);
       for (int dir = 0; dir < 2; ++dir) {
+        if (dir == 1 && j < jstrV) continue;
         const int di = dir == 0 ? 1 : 0, dj = dir == 0 ? 0 : 1;
         vec& un = dir == 0 ? o.u[nnew - 1] : o.v[nnew - 1];
         vec& r = dir == 0 ? o.ru : o.rv;
@@ -1000,7 +1081,7 @@ void step2d(Orc& o) {
   vec &zeta_new = o.s2d[0], &Dnew = o.s2d[1], &rubar = o.s2d[2], &rvbar = o.s2d[3], &urhs = o.s2d[4], &vrhs = o.s2d[5], &DUon = o.s2d[6],
       &DVom = o.s2d[7], &Drhs = o.s2d[8], &UFx = o.s2d[9], &UFe = o.s2d[10], &VFx = o.s2d[11], &VFe = o.s2d[12];
 #pragma omp parallel for
-  for (int j = jstr - 2; j <= jend + 1; ++j)
+  for (int j = jstrV - 2; j <= jend + 1; ++j)
     for (int i = istr - 2; i <= iend + 1; ++i) A2(Drhs, i, j) = A2(o.h, i, j) + fwd * A2(zs, i, j) + fwd1 * A2(zb, i, j) + fwd2 * A2(zo, i, j);
 #pragma omp parallel for
   for (int j = jstr - 1; j <= jend + 1; ++j) {
@@ -1008,13 +1089,14 @@ void step2d(Orc& o) {
       A2(urhs, i, j) = fwd * A2(us, i, j) + fwd1 * A2(ub, i, j) + fwd2 * A2(uo, i, j);
       A2(DUon, i, j) = 0.5 * (A2(Drhs, i, j) + A2(Drhs, i - 1, j)) * A2(o.dn_u, i, j) * (A2(urhs, i, j));
     }
+    if (j >= jstrV - 1)
     for (int i = istr - 1; i <= iend + 1; ++i) {
       A2(vrhs, i, j) = fwd * A2(vs, i, j) + fwd1 * A2(vb, i, j) + fwd2 * A2(vo, i, j);
       A2(DVom, i, j) = 0.5 * (A2(Drhs, i, j) + A2(Drhs, i, j - 1)) * A2(o.dm_v, i, j) * (A2(vrhs, i, j));
     }
   }
 #pragma omp parallel for
-  for (int j = jstr - 1; j <= jend; ++j)
+  for (int j = jstrV - 1; j <= jend; ++j)
     for (int i = istr - 1; i <= iend; ++i) {
       A2(zeta_new, i, j) = A2(zs, i, j) + dtfast * A2(o.pm, i, j) * A2(o.pn, i, j) * (A2(DUon, i, j) - A2(DUon, i + 1, j) + A2(DVom, i, j) - A2(DVom, i, j + 1)) +
                            dtfast * A2(o.swflx, i, j);
@@ -1025,12 +1107,12 @@ void step2d(Orc& o) {
       A2(VFx, i, j) = A2(UFx, i, j) * (A2(o.rhoS, i, j) - A2(o.rhoA, i, j));
       A2(VFe, i, j) = A2(UFe, i, j) * A2(UFx, i, j);
     }
-  // zetabc_tile: nothing to do on periodic edges (zetabc.F, compiled out)
-  for (int j = jstr; j <= jend; ++j)
+  zetabc(o, zeta_new);
+  for (int j = jstrR; j <= jendR; ++j)
     for (int i = istr; i <= iend; ++i) A2(zn, i, j) = A2(zeta_new, i, j);
   double cff1 = o.weight1[iif], cff2 = o.weight2[iif];
   if (iif == 1) {
-    for (int j = jstr; j <= jend; ++j)
+    for (int j = jstrR; j <= jendR; ++j)
       for (int i = istr; i <= iend; ++i) {
         A2(o.DU_avg_bak, i, j) = A2(o.DU_avg1, i, j) - 0.1024390243902439 * A2(o.DU_avg2, i, j);
         A2(o.DV_avg_bak, i, j) = A2(o.DV_avg1, i, j) - 0.1024390243902439 * A2(o.DV_avg2, i, j);
@@ -1041,7 +1123,7 @@ void step2d(Orc& o) {
         A2(o.DV_avg2, i, j) = cff2 * A2(DVom, i, j);
       }
   } else {
-    for (int j = jstr; j <= jend; ++j)
+    for (int j = jstrR; j <= jendR; ++j)
       for (int i = istr; i <= iend; ++i) {
         A2(o.Zt_avg1, i, j) = A2(o.Zt_avg1, i, j) + cff1 * A2(zn, i, j);
         A2(o.DU_avg2, i, j) = A2(o.DU_avg2, i, j) + cff2 * A2(DUon, i, j);
@@ -1065,7 +1147,7 @@ void step2d(Orc& o) {
         A2(o.rufrc, i, j) = A2(o.rufrc, i, j) - A2(rubar, i, j);
         A2(o.rvfrc, i, j) = A2(o.rvfrc, i, j) - A2(rvbar, i, j);
       }
-    for (int j = jstr - 1; j <= jend; ++j)
+    for (int j = jstrV - 1; j <= jend; ++j)
       for (int i = istr - 1; i <= iend; ++i) {
         A2(UFx, i, j) = A2(zeta_new, i, j) - A2(zs, i, j);
         A2(UFe, i, j) = (1.0 + A2(o.rhoS, i, j)) * A2(UFx, i, j);
@@ -1085,7 +1167,7 @@ void step2d(Orc& o) {
                                (A2(o.h, i, j - 1) - A2(o.h, i, j)) * (A2(VFx, i, j - 1) + A2(VFx, i, j) + 0.333333333333 * (A2(o.rhoA, i, j - 1) - A2(o.rhoA, i, j)) * (A2(UFx, i, j - 1) - A2(UFx, i, j))));
       }
   }
-  for (int j = jstr - 1; j <= jend; ++j)
+  for (int j = jstrV - 1; j <= jend; ++j)
     for (int i = istr - 1; i <= iend; ++i) A2(DUon, i, j) = A2(zs, i, j) + A2(o.h, i, j);
   cff = 0.5 * dtfast;
   cff1 = 0.5 * o.weight1[iif];
@@ -1098,6 +1180,7 @@ void step2d(Orc& o) {
       A2(un, i, j) = DUnew / (A2(Dnew, i, j) + A2(Dnew, i - 1, j));
       A2(o.DU_avg1, i, j) = A2(o.DU_avg1, i, j) + cff1 * A2(o.dn_u, i, j) * (DUnew);
     }
+    if (j >= jstrV)
     for (int i = istr; i <= iend; ++i) {
       double DVnew = ((A2(DUon, i, j) + A2(DUon, i, j - 1)) * A2(vs, i, j) +
                       cff * (A2(o.pm, i, j) + A2(o.pm, i, j - 1)) * (A2(o.pn, i, j) + A2(o.pn, i, j - 1)) * (A2(rvbar, i, j) + A2(o.rvfrc, i, j))) *
@@ -1106,9 +1189,26 @@ void step2d(Orc& o) {
       A2(o.DV_avg1, i, j) = A2(o.DV_avg1, i, j) + cff1 * A2(o.dm_v, i, j) * (DVnew);
     }
   }
-  // u2dbc_tile / v2dbc_tile: nothing on periodic edges
+  u2dbc(o, un);
+  v2dbc(o, vn);
+  // boundary-row contributions to the fast-time averaged fluxes (step2d_FB.F:449-529)
+  if (SWALL) for (int i = istr - 1; i <= iend; ++i) A2(Dnew, i, jstr - 1) = A2(o.h, i, jstr - 1) + A2(zeta_new, i, jstr - 1);
+  if (NWALL) for (int i = istr - 1; i <= iend; ++i) A2(Dnew, i, jend + 1) = A2(o.h, i, jend + 1) + A2(zeta_new, i, jend + 1);
+  cff1 = 0.5 * o.weight1[iif];
+  if (SWALL) {
+    for (int i = istr; i <= iend; ++i)
+      A2(o.DU_avg1, i, jstr - 1) = A2(o.DU_avg1, i, jstr - 1) + cff1 * (A2(Dnew, i, jstr - 1) + A2(Dnew, i - 1, jstr - 1)) * (A2(un, i, jstr - 1)) * A2(o.dn_u, i, jstr - 1);
+    for (int i = istr; i <= iend; ++i)
+      A2(o.DV_avg1, i, jstrV - 1) = A2(o.DV_avg1, i, jstrV - 1) + cff1 * (A2(Dnew, i, jstrV - 1) + A2(Dnew, i, jstrV - 2)) * (A2(vn, i, jstrV - 1)) * A2(o.dm_v, i, jstrV - 1);
+  }
+  if (NWALL) {
+    for (int i = istr; i <= iend; ++i)
+      A2(o.DU_avg1, i, jend + 1) = A2(o.DU_avg1, i, jend + 1) + cff1 * (A2(Dnew, i, jend + 1) + A2(Dnew, i - 1, jend + 1)) * (A2(un, i, jend + 1)) * A2(o.dn_u, i, jend + 1);
+    for (int i = istr; i <= iend; ++i)
+      A2(o.DV_avg1, i, jend + 1) = A2(o.DV_avg1, i, jend + 1) + cff1 * (A2(Dnew, i, jend + 1) + A2(Dnew, i, jend)) * (A2(vn, i, jend + 1)) * A2(o.dm_v, i, jend + 1);
+  }
   if (iif == o.nfast) {
-    for (int j = jstr; j <= jend; ++j)
+    for (int j = jstrR; j <= jendR; ++j)
       for (int i = istr; i <= iend; ++i) A2(zn, i, j) = A2(o.Zt_avg1, i, j);
     set_depth(o);
   }
@@ -1123,10 +1223,14 @@ void step3d_uv2(Orc& o) {
   {
     vec FC((size_t)SX * (N + 1)), CF((size_t)SX * (N + 1)), DC((size_t)SX * (N + 1));
     for (int pass = 0; pass < 2; ++pass) {
-      // u3dbc_tile / v3dbc_tile between the passes: nothing on periodic edges
+      if (pass == 1) {
+#pragma omp single
+        { u3dbc(o, o.u[nnew - 1]); v3dbc(o, o.v[nnew - 1]); }   // step3d_uv2.F:471-472
+      }
 #pragma omp for
-      for (int j = jstr; j <= jend; ++j) {
+      for (int j = (pass == 0 ? jstr : jstrR); j <= (pass == 0 ? jend : jendR); ++j) {
         for (int dir = 0; dir < 2; ++dir) {
+          if (dir == 1 && j < (pass == 0 ? jstrV : jstr)) continue;
           const int di = dir == 0 ? 1 : 0, dj = dir == 0 ? 0 : 1;
           vec& un = dir == 0 ? o.u[nnew - 1] : o.v[nnew - 1];
           const vec& us = dir == 0 ? o.u[nstp - 1] : o.v[nstp - 1];
@@ -1245,6 +1349,7 @@ void step3d_t(Orc& o) {
       }
     }
   }
+  for (int itrc = 0; itrc < NT; ++itrc) t3dbc(o, o.t[nnew - 1][itrc]);
   for (int itrc = 0; itrc < NT; ++itrc) ex3(o, o.t[nnew - 1][itrc]);
 }
 
