@@ -29,14 +29,23 @@ UNIT = "grid-point updates/s"
 # kernel read once, every 3-D result written once, 2-D operands ignored in 3-D kernels, scratch = 0).
 # (words, dimensionality)
 KERNEL_WORDS = {
-    "k_rho_eos<true>": (6, 3), "k_rho_eos<false>": (4, 3), "k_set_huv": (5, 3), "k_omega": (6, 3),
-    "k_prsgrd_vert<true>": (5, 3), "k_prsgrd_vert<false>": (3, 3), "k_prsgrd_horiz<true>": (8, 3), "k_prsgrd_horiz<false>": (6, 3),
-    "k_pre_flxdiv": (5, 3), "k_pre_t_horiz": (8, 3), "k_rhs_uv_horiz<false>": (9, 3), "k_rhs_uv_horiz<true>": (9, 3),
-    "k_t_vert<0>": (8, 3), "k_t_vert<1>": (7, 3), "(k_uv_vert<0, 0>)": (10, 3), "(k_uv_vert<0, 1>)": (10, 3),
-    "(k_uv_vert<1, 0>)": (9, 3), "(k_uv_vert<1, 1>)": (9, 3), "k_set_huv1<0>": (4, 3), "k_set_huv1<1>": (4, 3),
-    "k_uv2_pass0<0>": (3, 3), "k_uv2_pass0<1>": (3, 3), "k_uv2_pass1<0>": (6, 3), "k_uv2_pass1<1>": (6, 3),
+    "k_rho_eos": lambda t: (6 if t[0] == "true" else 4, 3), "k_set_huv": (5, 3), "k_omega": (6, 3),
+    "k_prsgrd_vert": lambda t: (5 if t[0] == "true" else 3, 3), "k_prsgrd_horiz": lambda t: (8 if t[0] == "true" else 6, 3),
+    "k_pre_flxdiv": (5, 3), "k_pre_t_horiz": (8, 3), "k_rhs_uv_horiz": (9, 3),
+    "k_t_vert": lambda t: (8 if t[0] == "0" else 7, 3), "k_uv_vert": lambda t: (10 if t[0] == "0" else 9, 3),
+    "k_set_huv1": (4, 3), "k_uv2_pass0": (3, 3), "k_uv2_pass1": (6, 3),
     "k_t_horiz": (5, 3), "k_set_depth": (3, 3), "k_step2d_zeta": (24, 2), "k_step2d_uv": (23, 2), "k_rd_bott_drag": (3, 2),
 }
+
+
+def kernel_words(name):
+    """(words, dim) of a kernel from its stringified launch name, e.g. '(k_prsgrd_horiz<true, false>)'; None if not a compute kernel."""
+    n = name.replace("(", "").replace(")", "").replace(" ", "")
+    base, _, targs = n.partition("<")
+    w = KERNEL_WORDS.get(base)
+    if w is None:
+        return None
+    return w(targs.rstrip(">").split(",")) if callable(w) else w
 
 
 def step_bytes_per_update(NT, nfast, N):
@@ -249,8 +258,8 @@ def main():
             table.append((name, int(cnt), float(tms)))
             tot += float(tms)
         table.sort(key=lambda r: -r[2])
-        top = next((r for r in table if r[0] in KERNEL_WORDS), table[0])   # dominant compute kernel (exchange_xxx is reported in the table)
-        words, dim = KERNEL_WORDS.get(top[0], (None, 3))
+        top = next((r for r in table if kernel_words(r[0])), table[0])   # dominant compute kernel (exchange_xxx is reported in the table)
+        words, dim = kernel_words(top[0]) or (None, 3)
         npts = Lm * Mm * (N if dim == 3 else 1)
         avg_ms = top[2] / top[1]
         if words:
@@ -262,7 +271,7 @@ def main():
             with open(a.kernel_table, "w") as f:
                 f.write(f"# per-kernel CUDA-event times, {a.steps} steps, {workload}\n# kernel launches total_ms avg_ms share algorithmic_GB/s\n")
                 for name, cnt, tms in table:
-                    w, dm = KERNEL_WORDS.get(name, (0, 3))
+                    w, dm = kernel_words(name) or (0, 3)
                     gbs = w * 8.0 * Lm * Mm * (N if dm == 3 else 1) / (tms / cnt * 1e-3) / 1e9 if w else 0.0
                     f.write(f"{name} {cnt} {tms:.3f} {tms / cnt:.4f} {tms / tot:.4f} {gbs:.1f}\n")
     B = step_bytes_per_update(NT, nfast, N)

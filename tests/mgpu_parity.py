@@ -15,18 +15,19 @@ from romsb200 import Roms  # noqa: E402
 
 def main():
     nsteps = int(sys.argv[1]) if len(sys.argv) > 1 else 3
+    walls = len(sys.argv) > 2 and sys.argv[2] == "walls"
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
     npx, npe = cases.rank_grid(world)
     LG, MG, N = 24 * npx, 20 * npe, 10
-    cfg, st = cases.channel(LG, MG, N, sub=(rank % npx, rank // npx, npx, npe))
+    cfg, st = cases.channel(LG, MG, N, ns_walls=walls, sub=(rank % npx, rank // npx, npx, npe))
     g = Roms(cfg, local)
     g.attach_torch_comm(dist)
     cases.initialize(g, st)
     g.call("run", nsteps)
     dg = g.diag()
-    cfgG, stG = cases.channel(LG, MG, N)
+    cfgG, stG = cases.channel(LG, MG, N, ns_walls=walls)
     o = Oracle(cfgG)
     cases.initialize(o, stG)
     o.call("run", nsteps)
@@ -39,6 +40,9 @@ def main():
                      ("RHO1", 1, 1), ("HZ", 1, 1), ("WE", 1, 1), ("FLXU", 1, 1)]:
         a = g.pull(f, l, it)
         b = o.pull(f, l, it)[..., j0:j0 + Mm + 4, i0:i0 + Lm + 4]
+        if walls:      # rows beyond a closed wall are allocated but undefined
+            ja, jb = (1 if rank // npx == 0 else 0), (-1 if rank // npx == npe - 1 else None)
+            a, b = a[..., ja:jb, :], b[..., ja:jb, :]
         r = np.linalg.norm((a - b).ravel()) / max(np.linalg.norm(b.ravel()), 1e-300)
         worst = max(worst, r)
     ok = worst <= 1e-12 and np.allclose(dg, do, rtol=1e-11, atol=1e-18)

@@ -30,6 +30,11 @@ def rel(a, b):
     return d / n if n > 0 else d
 
 
+def view(a, cfg):
+    """rows that exist in the model: with closed N/S walls rows j=-1 and j=Mm+2 are allocated but never defined"""
+    return a if cfg.ns_periodic else a[..., 1:-1, :]
+
+
 def fetch(m, name, NT):
     iic, iif, nstp, nrhs, nnew, kstp, knew = m.get_idx()
     indx = 3 - nstp
@@ -63,7 +68,7 @@ def walk(cfg, st, nsteps=1, verbose=False, device=0):
         o.call(name, *args)
         g.call(name, *args)
         for f in CHECK[check or name]:
-            a, b = fetch(g, f, NT), fetch(o, f, NT)
+            a, b = view(fetch(g, f, NT), cfg), view(fetch(o, f, NT), cfg)
             assert np.isfinite(b).all(), ("oracle non-finite", name, f)
             r = rel(a, b) if np.isfinite(a).all() else np.inf
             worst[(check or name, f)] = max(worst.get((check or name, f), 0.0), r)
@@ -78,7 +83,7 @@ def walk(cfg, st, nsteps=1, verbose=False, device=0):
 
     # init_step0 outputs
     for f in ["HZ", "Z_R", "Z_W", "FLXU", "FLXV", "WE", "WI", "RHO1", "RHOA", "RHOS", "DU_AVG1", "DV_AVG1", "HINV"]:
-        a, b = g.pull(f), o.pull(f)
+        a, b = view(g.pull(f), cfg), view(o.pull(f), cfg)
         worst[("init_step0", f)] = rel(a, b)
         if verbose:
             print(f"  init_step0   {f:10s} relL2={worst[('init_step0', f)]:.3e}")
@@ -106,7 +111,7 @@ def walk(cfg, st, nsteps=1, verbose=False, device=0):
             both("step2d")
         both("set_depth", 0) if False else None
         for f in CHECK["set_depth"]:
-            a, b = fetch(g, f, NT), fetch(o, f, NT)
+            a, b = view(fetch(g, f, NT), cfg), view(fetch(o, f, NT), cfg)
             worst[("set_depth", f)] = max(worst.get(("set_depth", f), 0.0), rel(a, b))
         setidx(iif=nfast + 1)
         both("step3d_uv2", 0)
@@ -120,7 +125,7 @@ def walk(cfg, st, nsteps=1, verbose=False, device=0):
 
 if __name__ == "__main__":
     dims = [int(x) for x in sys.argv[1:4]] or [48, 40, 12]
-    for tag, (cfg, st) in {"channel(nonlin EOS, T+S)": cases.channel(*dims), "filament(linear EOS, T)": cases.filament(*dims)}.items():
+    for tag, (cfg, st) in {"channel(nonlin EOS, T+S)": cases.channel(*dims), "channel(N/S walls)": cases.channel(*dims, ns_walls=True), "filament(linear EOS, T)": cases.filament(*dims)}.items():
         print(tag)
         w = walk(cfg, st, nsteps=2, verbose=True)
         print(" worst:", max(w.values()), max(w, key=w.get))

@@ -23,12 +23,13 @@ def prognostic(m, NT):
     return out
 
 
-def compare(g, o, NT, tol):
+def compare(g, o, NT, tol, cfg=None):
     a, b = prognostic(g, NT), prognostic(o, NT)
     res = {}
     for k in b:
-        assert np.isfinite(a[k]).all(), k
-        res[k] = parity_walk.rel(a[k], b[k])
+        x, y = (parity_walk.view(a[k], cfg), parity_walk.view(b[k], cfg)) if cfg is not None else (a[k], b[k])
+        assert np.isfinite(x).all(), k
+        res[k] = parity_walk.rel(x, y)
     assert max(res.values()) <= tol, res
     return res
 
@@ -55,10 +56,14 @@ def test_constants_match_oracle():
     g.close(); o.close()
 
 
-@pytest.mark.parametrize("case", ["channel", "filament", "channel_linear_odd"])
+@pytest.mark.parametrize("case", ["channel", "filament", "channel_linear_odd", "channel_walls", "channel_walls_linear_odd"])
 def test_routine_by_routine(case):
     if case == "channel":
         cfg, st = cases.channel(48, 40, 12)
+    elif case == "channel_walls":
+        cfg, st = cases.channel(48, 40, 12, ns_walls=True)             # closed N/S walls (configs[1] geometry)
+    elif case == "channel_walls_linear_odd":
+        cfg, st = cases.channel(37, 29, 9, NT=3, nonlin_eos=False, ns_walls=True)
     elif case == "filament":
         cfg, st = cases.filament(64, 64, 32)
     else:
@@ -68,14 +73,15 @@ def test_routine_by_routine(case):
     assert not bad, bad
 
 
-def test_one_step_and_100_steps_channel():
-    cfg, st = cases.channel(64, 48, 16)
+@pytest.mark.parametrize("walls", [False, True])
+def test_one_step_and_100_steps_channel(walls):
+    cfg, st = cases.channel(64, 48, 16, ns_walls=walls)
     g, o = Roms(cfg), Oracle(cfg)
     cases.initialize(g, st); cases.initialize(o, st)
     g.call("step"); o.call("step")
-    r1 = compare(g, o, cfg.NT, TOL1)
+    r1 = compare(g, o, cfg.NT, TOL1, cfg)
     g.call("run", 99); o.call("run", 99)
-    r100 = compare(g, o, cfg.NT, TOL100)
+    r100 = compare(g, o, cfg.NT, TOL100, cfg)
     print("1 step:", r1, "\n100 steps:", r100)
     d1, d2 = g.diag(), o.diag()
     assert np.allclose(d1, d2, rtol=1e-9)
@@ -128,4 +134,7 @@ def test_two_gpu_halo_exchange_parity():
     script = os.path.join(os.path.dirname(__file__), "mgpu_parity.py")
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
                         "--master-port", "29731", script, "3"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+                        "--master-port", "29732", script, "3", "walls"], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]

@@ -36,22 +36,26 @@ static inline int decomp_neighbor(int np_xi, int np_eta, int inode, int jnode, i
   return jn * np_xi + in;
 }
 // interior cells this subdomain SENDS to its neighbour in direction d
-static inline DirBox decomp_send_box(int Lm, int Mm, int d) {
+// swall/nwall: this subdomain touches a closed southern/northern physical edge; E-W messages then also carry
+// the boundary rows j=0 / j=Mm+1 (mpi_exchanges.F:538-543: "if (jnode==0) jl0=0", "if (jnode==NP_ETA-1) jl1=nyl+1").
+static inline DirBox decomp_send_box(int Lm, int Mm, int d, int swall = 0, int nwall = 0) {
   int dx, dy;
   decomp_dir(d, &dx, &dy);
   DirBox b;
   b.ni = dx == 0 ? Lm : 2; b.nj = dy == 0 ? Mm : 2;
   b.i0 = dx > 0 ? Lm - 1 : 1;
   b.j0 = dy > 0 ? Mm - 1 : 1;
+  if (dx != 0 && dy == 0) { b.j0 -= swall ? 1 : 0; b.nj += (swall ? 1 : 0) + (nwall ? 1 : 0); }
   return b;
 }
 // halo cells this subdomain RECEIVES from its neighbour in direction d
-static inline DirBox decomp_recv_box(int Lm, int Mm, int d) {
+static inline DirBox decomp_recv_box(int Lm, int Mm, int d, int swall = 0, int nwall = 0) {
   int dx, dy;
   decomp_dir(d, &dx, &dy);
   DirBox b;
   b.ni = dx == 0 ? Lm : 2; b.nj = dy == 0 ? Mm : 2;
   b.i0 = dx < 0 ? -1 : (dx > 0 ? Lm + 1 : 1);
   b.j0 = dy < 0 ? -1 : (dy > 0 ? Mm + 1 : 1);
+  if (dx != 0 && dy == 0) { b.j0 -= swall ? 1 : 0; b.nj += (swall ? 1 : 0) + (nwall ? 1 : 0); }
   return b;
 }

@@ -43,6 +43,18 @@ __device__ __forceinline__ ColScr col_scratch(const KP& p, long c, double* smem)
   const long c = CIDX(i, j);                                        \
   const long SX = p.SX; (void)SX;
 
+// Closed N/S walls: the reference extends its one-dimensional difference arrays across a wall by copying
+// the nearest computed row (e.g. "wrk1(i,jstr-1)=wrk1(i,jstr)", compute_horiz_rhs_uv_terms.h:110-140,
+// "FE(i,jstr-1)=FE(i,jstr)", compute_horiz_tracer_fluxes.h:150-160, "FC(i,jmin-1)=FC(i,jmin)", prsgrd.F:300).
+// Kernels that recompute those differences in registers evaluate them at the clamped row instead:
+// element offset that moves row j to clamp(j, lo, hi); lo/hi only bind on a wall.
+__device__ __forceinline__ long jclamp(const KP& p, int j, int lo_wall, int hi_wall) {
+  int jc = j;
+  if (p.swall && jc < lo_wall) jc = lo_wall;
+  if (p.nwall && jc > hi_wall) jc = hi_wall;
+  return (long)(jc - j) * p.SX;
+}
+
 // ------------------------------------------------------------------------------------------------
 // exchange_xxx on one subdomain (mpi_exchanges.F:34-40 with the periodic wrap of mpi_setup.F:231-250):
 // every halo cell copies its periodic image from the interior.  Up to 4 fields per launch.
@@ -72,7 +84,8 @@ __global__ void k_halo_periodic(const __grid_constant__ KP p, const __grid_const
   int is = i, js = j;
   if (ew) { if (i < 1) is = i + Lm; else if (i > Lm) is = i - Lm; }
   if (ns) { if (j < 1) js = j + Mm; else if (j > Mm) js = j - Mm; }
-  if ((is < 1 || is > Lm) || (js < 1 || js > Mm)) return;   // non-periodic edge: untouched
+  const int jlo = p.swall ? 0 : 1, jhi = p.nwall ? Mm + 1 : Mm;
+  if ((is < 1 || is > Lm) || (js < jlo || js > jhi)) return;   // non-periodic edge: untouched
   if (is == i && js == j) return;
   const long cd = CIDX(i, j), cs = CIDX(is, js);
   const int f = blockIdx.y;
@@ -83,7 +96,7 @@ __global__ void k_halo_periodic(const __grid_constant__ KP p, const __grid_const
 // ------------------------------------------------------------------------------------------------
 // set_depth.F:16-186 set_depth_tile: z_w, z_r, Hz from zeta(knew).  Plane kernel over k=0:N.
 __global__ void k_set_depth(const __grid_constant__ KP p, const double* __restrict__ zeta) {
-  THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
+  THREAD_IJ(p.istr, p.iend, p.jstrR, p.jendR)
   const int k = blockIdx.z;
   const int N = p.N;
   const double h = p.h[c];
@@ -107,25 +120,25 @@ __global__ void k_set_depth(const __grid_constant__ KP p, const double* __restri
 // set_depth.F iic==0 branch: hinv, DU_avg1, DV_avg1
 __global__ void k_set_depth_init(const __grid_constant__ KP p, const double* __restrict__ zeta, const double* __restrict__ ubar,
                                  const double* __restrict__ vbar) {
-  THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
+  THREAD_IJ(p.istr, p.iend, p.jstrR, p.jendR)
   p.hinv[c] = 1.0 / (p.h[c] + p.hc);
   p.DU_avg1[c] = 0.5 * (p.h[c - 1] + p.h[c] + zeta[c] + zeta[c - 1]) * p.dn_u[c] * (ubar[c]);
-  p.DV_avg1[c] = 0.5 * (p.h[c] + p.h[c - SX] + zeta[c] + zeta[c - SX]) * p.dm_v[c] * (vbar[c]);
+  if (j >= p.jstr) p.DV_avg1[c] = 0.5 * (p.h[c] + p.h[c - SX] + zeta[c] + zeta[c - SX]) * p.dm_v[c] * (vbar[c]);
 }
 
 // set_depth.F:201-234 set_HUV_tile
 __global__ void k_set_huv(const __grid_constant__ KP p, const double* __restrict__ u, const double* __restrict__ v) {
-  THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
+  THREAD_IJ(p.istr, p.iend, p.jstrR, p.jendR)
   const int k = blockIdx.z + 1;
   const double Hz = R3(p.Hz, c, k);
   R3(p.FlxU, c, k) = 0.5 * (Hz + R3(p.Hz, c - 1, k)) * p.dn_u[c] * (R3(u, c, k));
-  R3(p.FlxV, c, k) = 0.5 * (Hz + R3(p.Hz, c - SX, k)) * p.dm_v[c] * (R3(v, c, k));
+  if (j >= p.jstr) R3(p.FlxV, c, k) = 0.5 * (Hz + R3(p.Hz, c - SX, k)) * p.dm_v[c] * (R3(v, c, k));
 }
 
 // set_depth.F:252-422 set_HUV1_tile.  DIR 0: u/FlxU, 1: v/FlxV.  Column kernel, two sweeps, no scratch.
 template <int DIR>
 __global__ void k_set_huv1(const __grid_constant__ KP p, double* __restrict__ u, int first) {
-  THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
+  THREAD_IJ(p.istr, p.iend, (DIR == 0 ? p.jstrR : p.jstr), p.jendR)
   const long d = DIR == 0 ? 1 : SX;
   const double dn = DIR == 0 ? p.dn_u[c] : p.dm_v[c];
   const double msk = DIR == 0 ? p.umask[c] : p.vmask[c];
@@ -204,7 +217,7 @@ __global__ void k_omega(const __grid_constant__ KP p, double dtau) {
 // rho1,qp1 per level and the vertical integrals rhoA, rhoS (rho_eos.F:364-395).
 template <bool NONLIN>
 __global__ void k_rho_eos(const __grid_constant__ KP p, const double* __restrict__ T, const double* __restrict__ Sal) {
-  THREAD_IJ(p.istr - 2, p.iend + 2, p.jstr - 2, p.jend + 2)
+  THREAD_IJ(p.istr - 2, p.iend + 2, (p.swall ? p.jstr - 1 : p.jstr - 2), (p.nwall ? p.jend + 1 : p.jend + 2))
   const int N = p.N;
   const double rho0 = p.rho0, qp2 = 0.0000172;
   const double r00 = 999.842594, r01 = 6.793952e-2, r02 = -9.095290e-3, r03 = 1.001685e-4, r04 = -1.120083e-6, r05 = 6.536332e-9,
@@ -312,15 +325,35 @@ __global__ void k_prsgrd_vert(const __grid_constant__ KP p) {
 // prsgrd.F:231-421: horizontal part, plane kernel.  ru, rv at (i,j,k) from the density-Jacobian with
 // harmonic-mean reconstruction of the horizontal differences.
 template <bool NONLIN>
-__device__ __forceinline__ double prs_dir(const KP& p, long c, long d, int k, const double* __restrict__ msk, double dn, const double* __restrict__ rho) {
+__device__ __forceinline__ void prs_fc_rx(const KP& p, long X, long d, int k, const double* __restrict__ msk, const double* __restrict__ rho,
+                                          double& FC, double& rx) {
+  const double qp2 = 0.0000172;
+  const double zu = R3(p.z_r, X, k), zl = R3(p.z_r, X - d, k), m = msk[X];
+  FC = (zu - zl) * m;
+  if (NONLIN) {
+    const double dpth = -0.5 * (zu + zl);
+    rx = (R3(p.rho1, X, k) - R3(p.rho1, X - d, k) + (R3(p.qp1, X, k) - R3(p.qp1, X - d, k)) * dpth * (1.0 - qp2 * dpth)) * m;
+  } else rx = (R3(rho, X, k) - R3(rho, X - d, k)) * m;
+}
+// CL: the three difference positions (c-d, c, c+d) are displaced by oA, oB, oC (wall clamping, see jclamp)
+template <bool NONLIN, bool CL>
+__device__ __forceinline__ double prs_dir(const KP& p, long c, long d, int k, const double* __restrict__ msk, double dn, const double* __restrict__ rho,
+                                          long oA = 0, long oB = 0, long oC = 0) {
   const double qp2 = 0.0000172, OneFifth = 0.2, OneTwelfth = 1.0 / 12.0, epsil = 0.0;
   const double HalfGRho = 0.5 * (p.g / p.rho0);
   // points c-2d, c-d, c, c+d
-  const double z0 = R3(p.z_r, c - 2 * d, k), z1 = R3(p.z_r, c - d, k), z2 = R3(p.z_r, c, k), z3 = R3(p.z_r, c + d, k);
-  const double m1 = msk[c - d], m2 = msk[c], m3 = msk[c + d];
-  const double FCa = (z1 - z0) * m1, FCb = (z2 - z1) * m2, FCc = (z3 - z2) * m3;   // FC(i-1), FC(i), FC(i+1)
-  double rxa, rxb, rxc;
+  const double z1 = R3(p.z_r, c - d, k), z2 = R3(p.z_r, c, k);
+  double FCa, FCb, FCc, rxa, rxb, rxc;
   double q1 = 0, q2v = 0;
+  if (CL) {
+    prs_fc_rx<NONLIN>(p, c - d + oA, d, k, msk, rho, FCa, rxa);
+    prs_fc_rx<NONLIN>(p, c + oB, d, k, msk, rho, FCb, rxb);
+    prs_fc_rx<NONLIN>(p, c + d + oC, d, k, msk, rho, FCc, rxc);
+    if (NONLIN) { q1 = R3(p.qp1, c - d, k); q2v = R3(p.qp1, c, k); }
+  } else {
+  const double z0 = R3(p.z_r, c - 2 * d, k), z3 = R3(p.z_r, c + d, k);
+  const double m1 = msk[c - d], m2 = msk[c], m3 = msk[c + d];
+  FCa = (z1 - z0) * m1; FCb = (z2 - z1) * m2; FCc = (z3 - z2) * m3;   // FC(i-1), FC(i), FC(i+1)
   if (NONLIN) {
     const double a0 = R3(p.rho1, c - 2 * d, k), a1 = R3(p.rho1, c - d, k), a2 = R3(p.rho1, c, k), a3 = R3(p.rho1, c + d, k);
     const double b0 = R3(p.qp1, c - 2 * d, k), b1 = R3(p.qp1, c - d, k), b2 = R3(p.qp1, c, k), b3 = R3(p.qp1, c + d, k);
@@ -331,6 +364,7 @@ __device__ __forceinline__ double prs_dir(const KP& p, long c, long d, int k, co
   } else {
     const double a0 = R3(rho, c - 2 * d, k), a1 = R3(rho, c - d, k), a2 = R3(rho, c, k), a3 = R3(rho, c + d, k);
     rxa = (a1 - a0) * m1; rxb = (a2 - a1) * m2; rxc = (a3 - a2) * m3;
+  }
   }
   // dZx, dRx at c-d ("m") and c ("c")
   double cff = 2.0 * FCa * FCb;
@@ -351,13 +385,16 @@ __device__ __forceinline__ double prs_dir(const KP& p, long c, long d, int k, co
           HalfGRho * ((rho_c + rho_m) * (z2 - z1) -
                       OneFifth * ((dRx_c - dRx_m) * (z2 - z1 - OneTwelfth * (dZx_c + dZx_m)) - (dZx_c - dZx_m) * (rho_c - rho_m - OneTwelfth * (dRx_c + dRx_m)))));
 }
-template <bool NONLIN>
+template <bool NONLIN, bool WALL>
 __global__ void k_prsgrd_horiz(const __grid_constant__ KP p) {
   THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
   const int k = blockIdx.z + 1;
   const double* rho = NONLIN ? p.rho : p.rho1;
-  R3(p.ru, c, k) = prs_dir<NONLIN>(p, c, 1, k, p.umask, p.dn_u[c], rho);
-  R3(p.rv, c, k) = prs_dir<NONLIN>(p, c, SX, k, p.vmask, p.dm_v[c], rho);
+  R3(p.ru, c, k) = prs_dir<NONLIN, false>(p, c, 1, k, p.umask, p.dn_u[c], rho);
+  if (!WALL) R3(p.rv, c, k) = prs_dir<NONLIN, false>(p, c, SX, k, p.vmask, p.dm_v[c], rho);
+  else if (j >= p.jstrV)   // prsgrd.F:288-310: FC,rx exist on rows jstrV..jend between walls, copied one row outward
+    R3(p.rv, c, k) = prs_dir<NONLIN, true>(p, c, SX, k, p.vmask, p.dm_v[c], rho, jclamp(p, j - 1, p.jstrV, p.jend), jclamp(p, j, p.jstrV, p.jend),
+                                           jclamp(p, j + 1, p.jstrV, p.jend));
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -366,12 +403,24 @@ __global__ void k_prsgrd_horiz(const __grid_constant__ KP p) {
 #define HDELTA 0.1666666666666667
 #define HGAMMA 0.3333333333333333
 // along-axis flux of the along-axis velocity: UFx (d=1,u,FlxU) / VFe (d=SX,v,FlxV) at rho point c
-template <bool UP>
-__device__ __forceinline__ double flux_along(const KP& p, const double* __restrict__ u, const double* __restrict__ Flx, long c, long d, int k) {
-  const double um = R3(u, c - d, k), u0 = R3(u, c, k), u1 = R3(u, c + d, k), u2 = R3(u, c + 2 * d, k);
-  const double fm = R3(Flx, c - d, k), f0 = R3(Flx, c, k), f1 = R3(Flx, c + d, k), f2 = R3(Flx, c + 2 * d, k);
-  const double w1a = um - 2.0 * u0 + u1, w1b = u0 - 2.0 * u1 + u2;     // wrk1(c), wrk1(c+d)
-  const double w2a = fm - 2.0 * f0 + f1, w2b = f0 - 2.0 * f1 + f2;     // wrk2(c), wrk2(c+d)
+template <bool UP, bool CL>
+__device__ __forceinline__ double flux_along(const KP& p, const double* __restrict__ u, const double* __restrict__ Flx, long c, long d, int k,
+                                             long oa = 0, long ob = 0) {
+  const double u0 = R3(u, c, k), u1 = R3(u, c + d, k);
+  const double f0 = R3(Flx, c, k), f1 = R3(Flx, c + d, k);
+  double w1a, w1b, w2a, w2b;     // wrk1(c), wrk1(c+d), wrk2(c), wrk2(c+d)
+  if (CL) {                      // second differences taken at the wall-clamped rows c+oa, c+d+ob
+    const long ca = c + oa, cb = c + d + ob;
+    w1a = R3(u, ca - d, k) - 2.0 * R3(u, ca, k) + R3(u, ca + d, k);
+    w1b = R3(u, cb - d, k) - 2.0 * R3(u, cb, k) + R3(u, cb + d, k);
+    w2a = R3(Flx, ca - d, k) - 2.0 * R3(Flx, ca, k) + R3(Flx, ca + d, k);
+    w2b = R3(Flx, cb - d, k) - 2.0 * R3(Flx, cb, k) + R3(Flx, cb + d, k);
+  } else {
+    const double um = R3(u, c - d, k), u2 = R3(u, c + 2 * d, k);
+    const double fm = R3(Flx, c - d, k), f2 = R3(Flx, c + 2 * d, k);
+    w1a = um - 2.0 * u0 + u1; w1b = u0 - 2.0 * u1 + u2;
+    w2a = fm - 2.0 * f0 + f1; w2b = f0 - 2.0 * f1 + f2;
+  }
   if (UP) {
     const double cff = f0 + f1 - HDELTA * (w2a + w2b);
     return 0.25 * (cff * (u0 + u1) - HGAMMA * (DMAX(cff, 0.0) * w1a + DMIN(cff, 0.0) * w1b));
@@ -379,11 +428,20 @@ __device__ __forceinline__ double flux_along(const KP& p, const double* __restri
     return 0.25 * (u0 + u1 - HDELTA * (w1a + w1b)) * (f0 + f1 - HDELTA * (w2a + w2b));
 }
 // cross-axis flux at psi point c: UFe (u advected by FlxV: du=SX, df=1) / VFx (v advected by FlxU: du=1, df=SX)
-template <bool UP>
-__device__ __forceinline__ double flux_cross(const KP& p, const double* __restrict__ u, const double* __restrict__ Flx, long c, long du, long df, int k) {
+template <bool UP, bool CL>
+__device__ __forceinline__ double flux_cross(const KP& p, const double* __restrict__ u, const double* __restrict__ Flx, long c, long du, long df, int k,
+                                             long om = 0, long oc = 0) {
   // u second differences along du at c and c-du; Flx second differences along df at c and c-df
-  const double ua = R3(u, c - 2 * du, k), ub = R3(u, c - du, k), uc = R3(u, c, k), ud = R3(u, c + du, k);
-  const double w1m = ua - 2.0 * ub + uc, w1c = ub - 2.0 * uc + ud;     // wrk1(c-du), wrk1(c)
+  const double ub = R3(u, c - du, k), uc = R3(u, c, k);
+  double w1m, w1c;     // wrk1(c-du), wrk1(c)
+  if (CL) {
+    const long cm = c - du + om, cc = c + oc;
+    w1m = R3(u, cm - du, k) - 2.0 * R3(u, cm, k) + R3(u, cm + du, k);
+    w1c = R3(u, cc - du, k) - 2.0 * R3(u, cc, k) + R3(u, cc + du, k);
+  } else {
+    const double ua = R3(u, c - 2 * du, k), ud = R3(u, c + du, k);
+    w1m = ua - 2.0 * ub + uc; w1c = ub - 2.0 * uc + ud;
+  }
   const double fa = R3(Flx, c - 2 * df, k), fb = R3(Flx, c - df, k), fc = R3(Flx, c, k), fd = R3(Flx, c + df, k);
   const double w2m = fa - 2.0 * fb + fc, w2c = fb - 2.0 * fc + fd;     // wrk2(c-df), wrk2(c)
   if (UP) {
@@ -392,37 +450,64 @@ __device__ __forceinline__ double flux_cross(const KP& p, const double* __restri
   } else
     return 0.25 * (uc + ub - HDELTA * (w1c + w1m)) * (fc + fb - HDELTA * (w2c + w2m));
 }
-template <bool UP>
+template <bool UP, bool WALL>
 __global__ void k_rhs_uv_horiz(const __grid_constant__ KP p, const double* __restrict__ u, const double* __restrict__ v) {
   THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
   const int k = blockIdx.z + 1;
+  const bool dov = !WALL || j >= p.jstrV;    // no v-row on a southern wall
   // Coriolis (no CURVGRID): compute_horiz_rhs_uv_terms.h:4-45
   const double cf0 = 0.5 * R3(p.Hz, c, k) * (p.fomn[c]);
   const double cfw = 0.5 * R3(p.Hz, c - 1, k) * (p.fomn[c - 1]);
-  const double cfs = 0.5 * R3(p.Hz, c - SX, k) * (p.fomn[c - SX]);
   const double v00 = R3(v, c, k), u00 = R3(u, c, k);
   const double UFx_c = cf0 * (v00 + R3(v, c + SX, k));
   const double UFx_w = cfw * (R3(v, c - 1, k) + R3(v, c - 1 + SX, k));
-  const double VFe_c = cf0 * (u00 + R3(u, c + 1, k));
-  const double VFe_s = cfs * (R3(u, c - SX, k) + R3(u, c - SX + 1, k));
   double ru = R3(p.ru, c, k) + 0.5 * (UFx_c + UFx_w);
-  double rv = R3(p.rv, c, k) - 0.5 * (VFe_c + VFe_s);
-  // advection
-  const double UFx_i = flux_along<UP>(p, u, p.FlxU, c, 1, k), UFx_im = flux_along<UP>(p, u, p.FlxU, c - 1, 1, k);
-  const double UFe_jp = flux_cross<UP>(p, u, p.FlxV, c + SX, SX, 1, k), UFe_j = flux_cross<UP>(p, u, p.FlxV, c, SX, 1, k);
+  // advection of u
+  const double UFx_i = flux_along<UP, false>(p, u, p.FlxU, c, 1, k), UFx_im = flux_along<UP, false>(p, u, p.FlxU, c - 1, 1, k);
+  double UFe_jp, UFe_j;
+  if (WALL) {   // u second differences in j exist on rows jstr..jend between walls (compute_horiz_rhs_uv_terms.h:186-199)
+    UFe_jp = flux_cross<UP, true>(p, u, p.FlxV, c + SX, SX, 1, k, jclamp(p, j, p.jstr, p.jend), jclamp(p, j + 1, p.jstr, p.jend));
+    UFe_j = flux_cross<UP, true>(p, u, p.FlxV, c, SX, 1, k, jclamp(p, j - 1, p.jstr, p.jend), jclamp(p, j, p.jstr, p.jend));
+  } else {
+    UFe_jp = flux_cross<UP, false>(p, u, p.FlxV, c + SX, SX, 1, k);
+    UFe_j = flux_cross<UP, false>(p, u, p.FlxV, c, SX, 1, k);
+  }
   ru = ru - UFx_i + UFx_im - UFe_jp + UFe_j;
-  const double VFx_ip = flux_cross<UP>(p, v, p.FlxU, c + 1, 1, SX, k), VFx_i = flux_cross<UP>(p, v, p.FlxU, c, 1, SX, k);
-  const double VFe_j = flux_along<UP>(p, v, p.FlxV, c, SX, k), VFe_jm = flux_along<UP>(p, v, p.FlxV, c - SX, SX, k);
-  rv = rv - VFx_ip + VFx_i - VFe_j + VFe_jm;
   R3(p.ru, c, k) = ru;
-  R3(p.rv, c, k) = rv;
+  if (dov) {
+    const double cfs = 0.5 * R3(p.Hz, c - SX, k) * (p.fomn[c - SX]);
+    const double VFe_c = cf0 * (u00 + R3(u, c + 1, k));
+    const double VFe_s = cfs * (R3(u, c - SX, k) + R3(u, c - SX + 1, k));
+    double rv = R3(p.rv, c, k) - 0.5 * (VFe_c + VFe_s);
+    const double VFx_ip = flux_cross<UP, false>(p, v, p.FlxU, c + 1, 1, SX, k), VFx_i = flux_cross<UP, false>(p, v, p.FlxU, c, 1, SX, k);
+    double VFe_j, VFe_jm;
+    if (WALL) {   // v, FlxV second differences exist on rows jstrV..jend between walls (compute_horiz_rhs_uv_terms.h:128-141)
+      VFe_j = flux_along<UP, true>(p, v, p.FlxV, c, SX, k, jclamp(p, j, p.jstrV, p.jend), jclamp(p, j + 1, p.jstrV, p.jend));
+      VFe_jm = flux_along<UP, true>(p, v, p.FlxV, c - SX, SX, k, jclamp(p, j - 1, p.jstrV, p.jend), jclamp(p, j, p.jstrV, p.jend));
+    } else {
+      VFe_j = flux_along<UP, false>(p, v, p.FlxV, c, SX, k);
+      VFe_jm = flux_along<UP, false>(p, v, p.FlxV, c - SX, SX, k);
+    }
+    rv = rv - VFx_ip + VFx_i - VFe_j + VFe_jm;
+    R3(p.rv, c, k) = rv;
+  }
 }
 
 // compute_horiz_tracer_fluxes.h:1-246: FX at u-point c (d=1, FlxU, umask) or FE at v-point c (d=SX)
-template <bool UP>
-__device__ __forceinline__ double tflux(const KP& p, const double* __restrict__ t, const double* __restrict__ Flx, const double* __restrict__ msk, long c, long d, int k) {
-  const double t0 = R3(t, c - 2 * d, k), t1 = R3(t, c - d, k), t2 = R3(t, c, k), t3 = R3(t, c + d, k);
-  const double Fa = (t1 - t0) * msk[c - d], Fb = (t2 - t1) * msk[c], Fc = (t3 - t2) * msk[c + d];  // FX(c-d), FX(c), FX(c+d)
+template <bool UP, bool CL>
+__device__ __forceinline__ double tflux(const KP& p, const double* __restrict__ t, const double* __restrict__ Flx, const double* __restrict__ msk, long c, long d, int k,
+                                        long oA = 0, long oB = 0, long oC = 0) {
+  const double t1 = R3(t, c - d, k), t2 = R3(t, c, k);
+  double Fa, Fb, Fc;   // FX(c-d), FX(c), FX(c+d)
+  if (CL) {            // first differences taken at the wall-clamped rows
+    const long XA = c - d + oA, XB = c + oB, XC = c + d + oC;
+    Fa = (R3(t, XA, k) - R3(t, XA - d, k)) * msk[XA];
+    Fb = (R3(t, XB, k) - R3(t, XB - d, k)) * msk[XB];
+    Fc = (R3(t, XC, k) - R3(t, XC - d, k)) * msk[XC];
+  } else {
+    const double t0 = R3(t, c - 2 * d, k), t3 = R3(t, c + d, k);
+    Fa = (t1 - t0) * msk[c - d]; Fb = (t2 - t1) * msk[c]; Fc = (t3 - t2) * msk[c + d];
+  }
   const double fl = R3(Flx, c, k);
   if (UP) {
     const double wm = Fb - Fa, wc = Fc - Fb;   // wrk1(c-d), wrk1(c)
@@ -435,7 +520,7 @@ __device__ __forceinline__ double tflux(const KP& p, const double* __restrict__ 
 
 // pre_step3d4S.F:138-147: FlxDiv such that Hz_bak = Hz + FlxDiv, Hz_fwd = Hz - FlxDiv
 __global__ void k_pre_flxdiv(const __grid_constant__ KP p, double dtau) {
-  THREAD_IJ(p.istr - 1, p.iend, p.jstr - 1, p.jend)
+  THREAD_IJ(p.istr - 1, p.iend, p.jstrV - 1, p.jend)
   const int k = blockIdx.z + 1;
   const double cff = 0.5 * dtau;
   R3(p.FlxDiv, c, k) = cff * p.pm[c] * p.pn[c] *
@@ -443,29 +528,43 @@ __global__ void k_pre_flxdiv(const __grid_constant__ KP p, double dtau) {
                         RW(p.We, c, k - 1) - RW(p.Wi, c, k - 1));
 }
 // pre_step3d4S.F:152-168: tracer predictor, horizontal part (C4), and t(indx)=Hz*t(nstp)
+// FE at v-rows j and j+1; between walls the first differences exist on rows jstr..jend+1 (compute_horiz_tracer_fluxes.h:118-160)
+#define TFLUX_J(UP, FEj, FEjp)                                                                                                     \
+  double FEj, FEjp;                                                                                                                \
+  if (WALL) {                                                                                                                      \
+    FEj = tflux<UP, true>(p, t_rhs, p.FlxV, p.vmask, c, SX, k, jclamp(p, j - 1, p.jstr, p.jend + 1), jclamp(p, j, p.jstr, p.jend + 1),       \
+                          jclamp(p, j + 1, p.jstr, p.jend + 1));                                                                   \
+    FEjp = tflux<UP, true>(p, t_rhs, p.FlxV, p.vmask, c + SX, SX, k, jclamp(p, j, p.jstr, p.jend + 1), jclamp(p, j + 1, p.jstr, p.jend + 1), \
+                           jclamp(p, j + 2, p.jstr, p.jend + 1));                                                                  \
+  } else {                                                                                                                         \
+    FEj = tflux<UP, false>(p, t_rhs, p.FlxV, p.vmask, c, SX, k);                                                                   \
+    FEjp = tflux<UP, false>(p, t_rhs, p.FlxV, p.vmask, c + SX, SX, k);                                                             \
+  }
+template <bool WALL>
 __global__ void k_pre_t_horiz(const __grid_constant__ KP p, const double* __restrict__ t_rhs, double* __restrict__ t_new, const double* __restrict__ t_stp,
                               double* __restrict__ t_indx, double dtau, double cf_stp, double cf_bak) {
   THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
   const int k = blockIdx.z + 1;
-  const double FXi = tflux<false>(p, t_rhs, p.FlxU, p.umask, c, 1, k), FXip = tflux<false>(p, t_rhs, p.FlxU, p.umask, c + 1, 1, k);
-  const double FEj = tflux<false>(p, t_rhs, p.FlxV, p.vmask, c, SX, k), FEjp = tflux<false>(p, t_rhs, p.FlxV, p.vmask, c + SX, SX, k);
+  const double FXi = tflux<false, false>(p, t_rhs, p.FlxU, p.umask, c, 1, k), FXip = tflux<false, false>(p, t_rhs, p.FlxU, p.umask, c + 1, 1, k);
+  TFLUX_J(false, FEj, FEjp)
   const double Hz = R3(p.Hz, c, k), Hz_bak = Hz + R3(p.FlxDiv, c, k);
   const double ts = R3(t_stp, c, k);
   R3(t_new, c, k) = Hz_bak * (cf_stp * ts + cf_bak * R3(t_indx, c, k)) - dtau * p.pm[c] * p.pn[c] * (FXip - FXi + FEjp - FEj);
   R3(t_indx, c, k) = Hz * ts;
 }
 // step3d_t_ISO.F:196-213: tracer corrector, horizontal part (UP3)
+template <bool WALL>
 __global__ void k_t_horiz(const __grid_constant__ KP p, const double* __restrict__ t_rhs, double* __restrict__ t_new) {
   THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
   const int k = blockIdx.z + 1;
-  const double FXi = tflux<true>(p, t_rhs, p.FlxU, p.umask, c, 1, k), FXip = tflux<true>(p, t_rhs, p.FlxU, p.umask, c + 1, 1, k);
-  const double FEj = tflux<true>(p, t_rhs, p.FlxV, p.vmask, c, SX, k), FEjp = tflux<true>(p, t_rhs, p.FlxV, p.vmask, c + SX, SX, k);
+  const double FXi = tflux<true, false>(p, t_rhs, p.FlxU, p.umask, c, 1, k), FXip = tflux<true, false>(p, t_rhs, p.FlxU, p.umask, c + 1, 1, k);
+  TFLUX_J(true, FEj, FEjp)
   R3(t_new, c, k) = R3(t_new, c, k) - p.dt * p.pm[c] * p.pn[c] * (FXip - FXi + FEjp - FEj);
 }
 
 // compute_rd_bott_drag.h:1-74 (log-layer drag when Zob>0, else linear rdrg capped by 0.8*Hz/dt)
 __global__ void k_rd_bott_drag(const __grid_constant__ KP p, const double* __restrict__ u, const double* __restrict__ v) {
-  THREAD_IJ(p.istr - 1, p.iend, p.jstr - 1, p.jend)
+  THREAD_IJ(p.istr - 1, p.iend, p.jstrV - 1, p.jend)
   const double vonKar = 0.41;
   if (p.Zob > 0.0) {
     const double u0 = R3(u, c, 1), u1 = R3(u, c + 1, 1), v0 = R3(v, c, 1), v1 = R3(v, c + SX, 1);
@@ -624,7 +723,7 @@ __global__ void __launch_bounds__(64, 8)
 k_uv_vert(const __grid_constant__ KP p, const double* __restrict__ u_rhs, double* __restrict__ u_new, const double* __restrict__ u_stp,
           double* __restrict__ u_indx, double dtau, double cf_stp, double cf_bak) {
   extern __shared__ double smem[];
-  THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
+  THREAD_IJ(p.istr, p.iend, (DIR == 0 ? p.jstr : p.jstrV), p.jend)
   ColScr sc = col_scratch(p, c, smem);
   const int N = p.N;
   const long d = DIR == 0 ? 1 : SX;
@@ -800,13 +899,23 @@ __device__ __forceinline__ double s2d_DVom(const KP& p, const S2D& s, long c) {
   const double vrhs = s.fwd * s.vs[c] + s.fwd1 * s.vb[c] + s.fwd2 * s.vo[c];
   return 0.5 * (s2d_Drhs(p, s, c) + s2d_Drhs(p, s, c - p.SX)) * p.dm_v[c] * (vrhs);
 }
-__global__ void k_step2d_zeta(const __grid_constant__ KP p, const __grid_constant__ S2D s) {
-  THREAD_IJ(p.istr - 1, p.iend, p.jstr - 1, p.jend)
-  const double DUon = s2d_DUon(p, s, c), DUon1 = s2d_DUon(p, s, c + 1), DVom = s2d_DVom(p, s, c), DVom1 = s2d_DVom(p, s, c + SX);
+__device__ __forceinline__ double s2d_zeta_new(const KP& p, const S2D& s, long c) {
+  const double DUon = s2d_DUon(p, s, c), DUon1 = s2d_DUon(p, s, c + 1), DVom = s2d_DVom(p, s, c), DVom1 = s2d_DVom(p, s, c + p.SX);
   double zn = s.zs[c] + p.dtfast * p.pm[c] * p.pn[c] * (DUon - DUon1 + DVom - DVom1) + p.dtfast * p.swflx[c];
-  zn = zn * p.rmask[c];
+  return zn * p.rmask[c];
+}
+// rows jstrV-1..jend carry the continuity update; a row just outside a closed wall takes zetabc's gradient
+// condition (zetabc.F:3: zeta_new(i,jstr-1)=zeta_new(i,jstr)*rmask(i,jstr-1)), re-evaluating its neighbour's update.
+__global__ void k_step2d_zeta(const __grid_constant__ KP p, const __grid_constant__ S2D s) {
+  THREAD_IJ(p.istr - 1, p.iend, (p.swall ? p.jstrR : p.jstr - 1), p.jendR)
+  double zn;
+  if (p.swall && j < p.jstr) zn = s2d_zeta_new(p, s, c + SX) * p.rmask[c];
+  else if (p.nwall && j > p.jend) zn = s2d_zeta_new(p, s, c - SX) * p.rmask[c];
+  else zn = s2d_zeta_new(p, s, c);
   p.zeta_new[c] = zn;
-  if (i >= p.istr && j >= p.jstr) {
+  if (i >= p.istr && j >= p.jstrR) {
+    const double DUon = s2d_DUon(p, s, c);
+    const double DVom = (j >= p.jstrV - 1) ? s2d_DVom(p, s, c) : 0.0;   // the reference's DVom scratch is never filled below a southern wall
     s.zn[c] = zn;
     if (s.iif == 1) {
       p.DU_avg_bak[c] = p.DU_avg1[c] - 0.1024390243902439 * p.DU_avg2[c];
@@ -826,8 +935,9 @@ __global__ void k_step2d_zeta(const __grid_constant__ KP p, const __grid_constan
 // stage 2: pressure-gradient terms rubar,rvbar (step2d_FB.F:245-268, first-substep correction :313-384),
 // ubar,vbar(knew), DU_avg1/DV_avg1; on the last substep zeta(knew)=Zt_avg1 (:563).
 struct S2Pt { double UFx, UFe, VFx, VFe; };
-__device__ __forceinline__ S2Pt s2d_pt(const KP& p, const S2D& s, long c, bool corr) {
+__device__ __forceinline__ S2Pt s2d_pt(const KP& p, const S2D& s, long c, bool corr, bool valid = true) {
   S2Pt r;
+  if (!valid) { r.UFx = r.UFe = r.VFx = r.VFe = 0.0; return r; }   // row below a southern wall: zero-initialised scratch in the reference
   const double zn = p.zeta_new[c], zs = s.zs[c];
   if (!corr) {
     r.UFx = s.bkw_new * zn + s.bkw * zs + s.bkw1 * s.zb[c] + s.bkw2 * s.zo[c];
@@ -851,7 +961,9 @@ __device__ __forceinline__ double s2d_pgf(const KP& p, double cff, double dn, lo
 __global__ void k_step2d_uv(const __grid_constant__ KP p, const __grid_constant__ S2D s) {
   THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
   const double cffg = 0.5 * p.g;
-  const S2Pt a0 = s2d_pt(p, s, c, false), aw = s2d_pt(p, s, c - 1, false), as = s2d_pt(p, s, c - SX, false);
+  const bool sv = (j - 1 >= p.jstrV - 1);     // row j-1 carries a zeta_new
+  const bool dov = (j >= p.jstrV);
+  const S2Pt a0 = s2d_pt(p, s, c, false), aw = s2d_pt(p, s, c - 1, false), as = s2d_pt(p, s, c - SX, false, sv);
   double rubar = s2d_pgf(p, cffg, p.dn_u[c], c, 1, aw, a0);
   double rvbar = s2d_pgf(p, cffg, p.dm_v[c], c, SX, as, a0);
   double rufrc = p.rufrc[c], rvfrc = p.rvfrc[c];
@@ -860,7 +972,7 @@ __global__ void k_step2d_uv(const __grid_constant__ KP p, const __grid_constant_
     rvfrc = rvfrc - rvbar;
     p.rufrc[c] = rufrc;
     p.rvfrc[c] = rvfrc;
-    const S2Pt b0 = s2d_pt(p, s, c, true), bw = s2d_pt(p, s, c - 1, true), bs = s2d_pt(p, s, c - SX, true);
+    const S2Pt b0 = s2d_pt(p, s, c, true), bw = s2d_pt(p, s, c - 1, true), bs = s2d_pt(p, s, c - SX, true, sv);
     rubar = rubar + s2d_pgf(p, cffg, p.dn_u[c], c, 1, bw, b0);
     rvbar = rvbar + s2d_pgf(p, cffg, p.dm_v[c], c, SX, bs, b0);
   }
@@ -870,10 +982,65 @@ __global__ void k_step2d_uv(const __grid_constant__ KP p, const __grid_constant_
   const double DUnew = ((D0 + Dw) * s.us[c] + cff * (p.pm[c] + p.pm[c - 1]) * (p.pn[c] + p.pn[c - 1]) * (rubar + rufrc)) * p.umask[c];
   s.un[c] = DUnew / (Dn0 + Dnw);
   p.DU_avg1[c] = p.DU_avg1[c] + cff1 * p.dn_u[c] * (DUnew);
-  const double DVnew = ((D0 + Ds) * s.vs[c] + cff * (p.pm[c] + p.pm[c - SX]) * (p.pn[c] + p.pn[c - SX]) * (rvbar + rvfrc)) * p.vmask[c];
-  s.vn[c] = DVnew / (Dn0 + Dns);
-  p.DV_avg1[c] = p.DV_avg1[c] + cff1 * p.dm_v[c] * (DVnew);
+  if (dov) {
+    const double DVnew = ((D0 + Ds) * s.vs[c] + cff * (p.pm[c] + p.pm[c - SX]) * (p.pn[c] + p.pn[c - SX]) * (rvbar + rvfrc)) * p.vmask[c];
+    s.vn[c] = DVnew / (Dn0 + Dns);
+    p.DV_avg1[c] = p.DV_avg1[c] + cff1 * p.dm_v[c] * (DVnew);
+  }
   if (s.iif == s.nfast) s.zn[c] = p.Zt_avg1[c];
+}
+// Closed-wall rows of the barotropic step: u2dbc_im.F:150-152 (gamma2 slip), v2dbc_im.F (no normal flow), the
+// boundary-row contributions to DU_avg1/DV_avg1 (step2d_FB.F:449-529) and zeta(knew)=Zt_avg1 on the last substep.
+__global__ void k_step2d_bc(const __grid_constant__ KP p, const __grid_constant__ S2D s) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x - IOFF;
+  if (i < p.istr || i > p.iend) return;
+  const long SX = p.SX;
+  const double cff1 = 0.5 * s.w1;
+  if (p.swall) {
+    const long c = CIDX(i, p.jstr - 1), cv = CIDX(i, p.jstrV - 1);
+    s.un[c] = p.gamma2 * s.un[c + SX] * p.umask[c];
+    s.vn[cv] = 0.0;
+    const double Dn = p.h[c] + p.zeta_new[c], Dnw = p.h[c - 1] + p.zeta_new[c - 1];
+    p.DU_avg1[c] = p.DU_avg1[c] + cff1 * (Dn + Dnw) * (s.un[c]) * p.dn_u[c];
+    const double Dv = p.zeta_new[cv] + p.h[cv], Dvs = p.h[cv - SX] + p.zeta_new[cv - SX];
+    p.DV_avg1[cv] = p.DV_avg1[cv] + cff1 * (Dv + Dvs) * (s.vn[cv]) * p.dm_v[cv];
+    if (s.iif == s.nfast) s.zn[c] = p.Zt_avg1[c];
+  }
+  if (p.nwall) {
+    const long c = CIDX(i, p.jend + 1);
+    s.un[c] = p.gamma2 * s.un[c - SX] * p.umask[c];
+    s.vn[c] = 0.0;
+    const double Dn = p.h[c] + p.zeta_new[c], Dnw = p.h[c - 1] + p.zeta_new[c - 1], Ds = p.zeta_new[c - SX] + p.h[c - SX];
+    p.DU_avg1[c] = p.DU_avg1[c] + cff1 * (Dn + Dnw) * (s.un[c]) * p.dn_u[c];
+    p.DV_avg1[c] = p.DV_avg1[c] + cff1 * (Dn + Ds) * (s.vn[c]) * p.dm_v[c];
+    if (s.iif == s.nfast) s.zn[c] = p.Zt_avg1[c];
+  }
+}
+// u3dbc_im.F:293-295 / t3dbc_im.F:86-96 / omega.F:171-231 on closed N/S walls: ghost row = factor * first interior row
+// [* mask(ghost)] for planes k0..k0+nk-1; ZERO: v3dbc_im.F no-normal-flow rows jstr and jend+1.
+template <bool ZERO>
+__global__ void k_bc_rows(const __grid_constant__ KP p, double* __restrict__ a, double factor, const double* __restrict__ msk) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x - IOFF;
+  if (i < p.istr || i > p.iend) return;
+  const long SX = p.SX, ko = (long)blockIdx.z * p.SXY;
+  if (p.swall) {
+    if (ZERO) a[CIDX(i, p.jstr) + ko] = 0.0;
+    else {
+      const long c = CIDX(i, p.jstr - 1);
+      double v = factor * a[c + SX + ko];
+      if (msk) v = v * msk[c];
+      a[c + ko] = v;
+    }
+  }
+  if (p.nwall) {
+    const long c = CIDX(i, p.jend + 1);
+    if (ZERO) a[c + ko] = 0.0;
+    else {
+      double v = factor * a[c - SX + ko];
+      if (msk) v = v * msk[c];
+      a[c + ko] = v;
+    }
+  }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -882,7 +1049,7 @@ __global__ void k_step2d_uv(const __grid_constant__ KP p, const __grid_constant_
 // minus its mismatch with DU_avg2.  Column kernels without scratch (re-read through L1/L2).
 template <int DIR>
 __global__ void k_uv2_pass0(const __grid_constant__ KP p, double* __restrict__ u) {
-  THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
+  THREAD_IJ(p.istr, p.iend, (DIR == 0 ? p.jstr : p.jstrV), p.jend)
   const long d = DIR == 0 ? 1 : SX;
   const int N = p.N;
   const double dn = DIR == 0 ? p.dn_u[c] : p.dm_v[c];
@@ -903,7 +1070,7 @@ __global__ void k_uv2_pass0(const __grid_constant__ KP p, double* __restrict__ u
 }
 template <int DIR>
 __global__ void k_uv2_pass1(const __grid_constant__ KP p, double* __restrict__ u, const double* __restrict__ u_stp, double* __restrict__ bar) {
-  THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
+  THREAD_IJ(p.istr, p.iend, (DIR == 0 ? p.jstrR : p.jstr), p.jendR)
   const long d = DIR == 0 ? 1 : SX;
   const int N = p.N;
   const double dn = DIR == 0 ? p.dn_u[c] : p.dm_v[c];

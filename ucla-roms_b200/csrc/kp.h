@@ -16,6 +16,8 @@ struct KP {
   int SX;            // padded row pitch (doubles)
   long SXY;          // padded plane size (doubles)
   int istr, iend, jstr, jend;   // compute_tile_bounds.h with NSUB_X=NSUB_E=1
+  int swall, nwall;             // this subdomain touches a closed (non-periodic) southern / northern physical edge
+  int jstrR, jendR, jstrV;      // compute_auxiliary_bounds.h: jstr-1 / jend+1 / jstr+1 on such an edge, else jstr / jend / jstr
   int nonlin, salinity;
   // scalars
   double dt, dtfast, g, rho0, Tcoef, T0, Scoef, S0, rdrg, rdrg2, Zob, gamma2, hc;

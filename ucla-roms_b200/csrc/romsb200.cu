@@ -191,6 +191,7 @@ const char* roms_last_error(void) { return g_err.c_str(); }
 int roms_create(const roms_cfg* cfg, int device, roms_ctx** out) {
   if (!cfg || !out) { g_err = "roms_create: null argument"; return -1; }
   if (cfg->NT > MAXNT || cfg->N < 3 || cfg->Lm < 2 || cfg->Mm < 2) { g_err = "roms_create: unsupported sizes"; return -1; }
+  if (!cfg->ew_periodic) { g_err = "roms_create: closed/open western and eastern edges are not implemented yet (EW_PERIODIC only; N/S may be closed walls)"; return -1; }
   CK(cudaSetDevice(device));
   roms_ctx* h = new roms_ctx();
   h->c = *cfg;
@@ -203,6 +204,12 @@ int roms_create(const roms_cfg* cfg, int device, roms_ctx** out) {
   p.SX = ((cfg->Lm + 18 + 15) / 16) * 16;
   p.SXY = (long)p.SX * (cfg->Mm + 4);
   p.istr = 1; p.iend = cfg->Lm; p.jstr = 1; p.jend = cfg->Mm;
+  {
+    const int npe = cfg->np_eta > 0 ? cfg->np_eta : 1;
+    p.swall = (!cfg->ns_periodic && cfg->jnode == 0) ? 1 : 0;          // SOUTHERN_EDGE of set_global_definitions.h
+    p.nwall = (!cfg->ns_periodic && cfg->jnode == npe - 1) ? 1 : 0;    // NORTHERN_EDGE
+    p.jstrR = p.swall ? p.jstr - 1 : p.jstr; p.jendR = p.nwall ? p.jend + 1 : p.jend; p.jstrV = p.swall ? p.jstr + 1 : p.jstr;
+  }
   p.nonlin = cfg->nonlin_eos; p.salinity = cfg->salinity;
   p.dt = cfg->dt; p.dtfast = cfg->dt / double(cfg->ndtfast);
   p.g = cfg->g; p.rho0 = cfg->rho0; p.Tcoef = cfg->Tcoef; p.T0 = cfg->T0; p.Scoef = cfg->Scoef; p.S0 = cfg->S0;
@@ -403,6 +410,20 @@ int roms_exchange(roms_ctx* h, int nfields, const int* fields, const int* lvls, 
   return comm_exchange(&h->comm, h->kp, h->st, v.data(), (int)v.size(), &h->launches);
 }
 
+// closed-wall boundary rows (u3dbc/v3dbc/t3dbc/omega copies): no-ops unless this subdomain touches a wall
+static int bc_rows(roms_ctx* h, double* a, int nk, double factor, const double* msk, bool zero) {
+  const KP& p = h->kp;
+  if (!p.swall && !p.nwall) return 0;
+  dim3 b(128, 1, 1), g((p.iend + IOFF + 1 + 127) / 128, 1, nk);
+  if (h->ktiming) kt_begin(h, "k_bc_rows");
+  if (zero) k_bc_rows<true><<<g, b, 0, h->st>>>(p, a, factor, msk);
+  else k_bc_rows<false><<<g, b, 0, h->st>>>(p, a, factor, msk);
+  if (h->ktiming) kt_end(h);
+  h->launches++;
+  return 0;
+}
+#define WALLED(h) ((h)->kp.swall || (h)->kp.nwall)
+
 // ---- setup_grid1.F:13-210 (metrics, masks, fomn): host arithmetic on pulled planes, pushed back --
 int roms_setup_grid(roms_ctx* h) {
   const int Lm = h->c.Lm, Mm = h->c.Mm, SXh = Lm + 4;
@@ -413,13 +434,18 @@ int roms_setup_grid(roms_ctx* h) {
     return -1;
   auto at = [&](int i, int j) { return (size_t)(i + 1) + (size_t)(j + 1) * SXh; };
   std::vector<double> fomn(n2, 0.0), dm_r(n2, 0.0), dn_r(n2, 0.0), dm_u(n2, 0.0), dn_u(n2, 0.0), dm_v(n2, 0.0), dn_v(n2, 0.0), um(n2, 0.0), vm(n2, 0.0);
-  for (size_t q = 0; q < n2; ++q) fomn[q] = f[q] / (pm[q] * pn[q]);
-  for (int j = 1; j <= Mm; ++j)
+  const KP& pp = h->kp;
+  for (int j = (pp.swall ? 0 : -1); j <= (pp.nwall ? Mm + 1 : Mm + 2); ++j)     // extended bounds stop one row outside a wall
+    for (int i = -1; i <= Lm + 2; ++i) fomn[at(i, j)] = f[at(i, j)] / (pm[at(i, j)] * pn[at(i, j)]);
+  for (int j = pp.jstrR; j <= pp.jendR; ++j)
     for (int i = 1; i <= Lm; ++i) {
-      const size_t q = at(i, j), w = at(i - 1, j), s = at(i, j - 1);
+      const size_t q = at(i, j), w = at(i - 1, j);
       dm_r[q] = 1.0 / pm[q]; dn_r[q] = 1.0 / pn[q];
       dm_u[q] = 2.0 / (pm[q] + pm[w]); dn_u[q] = 2.0 / (pn[q] + pn[w]); um[q] = rm[q] * rm[w];
-      dm_v[q] = 2.0 / (pm[q] + pm[s]); dn_v[q] = 2.0 / (pn[q] + pn[s]); vm[q] = rm[q] * rm[s];
+      if (j >= 1) {
+        const size_t s = at(i, j - 1);
+        dm_v[q] = 2.0 / (pm[q] + pm[s]); dn_v[q] = 2.0 / (pn[q] + pn[s]); vm[q] = rm[q] * rm[s];
+      }
     }
   struct { int id; std::vector<double>* a; } outv[] = {{ROMS_FOMN, &fomn}, {ROMS_DM_R, &dm_r}, {ROMS_DN_R, &dn_r}, {ROMS_DM_U, &dm_u}, {ROMS_DN_U, &dn_u},
                                                        {ROMS_DM_V, &dm_v}, {ROMS_DN_V, &dn_v}, {ROMS_UMASK, &um}, {ROMS_VMASK, &vm}};
@@ -437,15 +463,15 @@ int roms_set_depth(roms_ctx* h, int tile) {
   (void)tile;
   CK(cudaSetDevice(h->device));
   const KP& p = h->kp;
-  if (h->iic == 0) PLANE(k_set_depth_init, p.iend, p.jstr, p.jend, 1, p, h->zeta(1), h->ubar(1), h->vbar(1));
-  PLANE(k_set_depth, p.iend, p.jstr, p.jend, p.N + 1, p, h->zeta(h->knew));
+  if (h->iic == 0) PLANE(k_set_depth_init, p.iend, p.jstrR, p.jendR, 1, p, h->zeta(1), h->ubar(1), h->vbar(1));
+  PLANE(k_set_depth, p.iend, p.jstrR, p.jendR, p.N + 1, p, h->zeta(h->knew));
   if (h->iic == 0) { int rc = exchange(h, {{p.hinv, 1}}); if (rc) return rc; }
   return exchange(h, {{p.z_w, p.N + 1}, {p.z_r, p.N}, {p.Hz, p.N}});
 }
 int roms_set_huv(roms_ctx* h) {
   CK(cudaSetDevice(h->device));
   const KP& p = h->kp;
-  PLANE(k_set_huv, p.iend, p.jstr, p.jend, p.N, p, h->u(h->nrhs), h->v(h->nrhs));
+  PLANE(k_set_huv, p.iend, p.jstrR, p.jendR, p.N, p, h->u(h->nrhs), h->v(h->nrhs));
   return exchange(h, {{p.FlxU, p.N}, {p.FlxV, p.N}});
 }
 int roms_set_huv1(roms_ctx* h, int tile) {
@@ -453,8 +479,8 @@ int roms_set_huv1(roms_ctx* h, int tile) {
   CK(cudaSetDevice(h->device));
   const KP& p = h->kp;
   const int first = (h->iic == h->forw_start);
-  COLUMN(k_set_huv1<0>, 0, p.iend, p.jstr, p.jend, p, h->u(h->nnew), first);
-  COLUMN(k_set_huv1<1>, 0, p.iend, p.jstr, p.jend, p, h->v(h->nnew), first);
+  COLUMN(k_set_huv1<0>, 0, p.iend, p.jstrR, p.jendR, p, h->u(h->nnew), first);
+  COLUMN(k_set_huv1<1>, 0, p.iend, p.jstr, p.jendR, p, h->v(h->nnew), first);
   return exchange(h, {{p.FlxU, p.N}, {p.FlxV, p.N}, {h->u(h->nnew), p.N}, {h->v(h->nnew), p.N}});
 }
 int roms_omega(roms_ctx* h) {
@@ -465,6 +491,8 @@ int roms_omega(roms_ctx* h) {
   else if (h->iic == h->forw_start) dtau = 0.5 * h->c.dt;
   else dtau = 0.6 * h->c.dt;
   COLUMN(k_omega, 2, p.iend, p.jstr, p.jend, p, dtau);
+  bc_rows(h, p.We, p.N + 1, 1.0, nullptr, false);      // omega.F:171-231 edge copies
+  bc_rows(h, p.Wi, p.N + 1, 1.0, nullptr, false);
   return exchange(h, {{p.We, p.N + 1}, {p.Wi, p.N + 1}});
 }
 int roms_rho_eos(roms_ctx* h, int tidx) {
@@ -474,8 +502,8 @@ int roms_rho_eos(roms_ctx* h, int tidx) {
   const double* S = h->c.NT >= 2 ? h->t(tidx, 2) : nullptr;
   if (h->c.nonlin_eos) {
     if (!S) { g_err = "NONLIN_EOS needs salinity (NT>=2)"; return -1; }
-    COLUMN(k_rho_eos<true>, 0, p.iend + 2, p.jstr - 2, p.jend + 2, p, T, S);
-  } else COLUMN(k_rho_eos<false>, 0, p.iend + 2, p.jstr - 2, p.jend + 2, p, T, S);
+    COLUMN(k_rho_eos<true>, 0, p.iend + 2, (p.swall ? p.jstr - 1 : p.jstr - 2), p.jend + 2, p, T, S);
+  } else COLUMN(k_rho_eos<false>, 0, p.iend + 2, (p.swall ? p.jstr - 1 : p.jstr - 2), p.jend + 2, p, T, S);
   return 0;
 }
 int roms_prsgrd(roms_ctx* h) {
@@ -483,10 +511,12 @@ int roms_prsgrd(roms_ctx* h) {
   const KP& p = h->kp;
   if (h->c.nonlin_eos) {
     COLUMN(k_prsgrd_vert<true>, 0, p.Lm, 0, p.Mm, p);
-    PLANE(k_prsgrd_horiz<true>, p.iend, p.jstr, p.jend, p.N, p);
+    if (WALLED(h)) PLANE((k_prsgrd_horiz<true, true>), p.iend, p.jstr, p.jend, p.N, p);
+    else PLANE((k_prsgrd_horiz<true, false>), p.iend, p.jstr, p.jend, p.N, p);
   } else {
     COLUMN(k_prsgrd_vert<false>, 0, p.Lm, 0, p.Mm, p);
-    PLANE(k_prsgrd_horiz<false>, p.iend, p.jstr, p.jend, p.N, p);
+    if (WALLED(h)) PLANE((k_prsgrd_horiz<false, true>), p.iend, p.jstr, p.jend, p.N, p);
+    else PLANE((k_prsgrd_horiz<false, false>), p.iend, p.jstr, p.jend, p.N, p);
   }
   return 0;
 }
@@ -499,17 +529,24 @@ int roms_pre_step3d(roms_ctx* h, int tile) {
   double dtau, cf_stp, cf_bak;
   if (h->iic == h->forw_start) { dtau = 0.5 * dt; cf_stp = 1.0; cf_bak = 0.0; }
   else { dtau = dt * (1.0 - AM3_crv); cf_stp = 0.5 + AM3_crv; cf_bak = 0.5 - AM3_crv; }
-  PLANE(k_pre_flxdiv, p.iend, p.jstr - 1, p.jend, p.N, p, dtau);
-  for (int it = 1; it <= h->c.NT; ++it)
-    PLANE(k_pre_t_horiz, p.iend, p.jstr, p.jend, p.N, p, h->t(nrhs, it), h->t(nnew, it), h->t(nstp, it), h->t(indx, it), dtau, cf_stp, cf_bak);
-  PLANE(k_rhs_uv_horiz<false>, p.iend, p.jstr, p.jend, p.N, p, h->u(nrhs), h->v(nrhs));
-  PLANE(k_rd_bott_drag, p.iend, p.jstr - 1, p.jend, 1, p, h->u(nstp), h->v(nstp));
+  const bool wl = WALLED(h);
+  PLANE(k_pre_flxdiv, p.iend, p.jstrV - 1, p.jend, p.N, p, dtau);
+  for (int it = 1; it <= h->c.NT; ++it) {
+    if (wl) PLANE(k_pre_t_horiz<true>, p.iend, p.jstr, p.jend, p.N, p, h->t(nrhs, it), h->t(nnew, it), h->t(nstp, it), h->t(indx, it), dtau, cf_stp, cf_bak);
+    else PLANE(k_pre_t_horiz<false>, p.iend, p.jstr, p.jend, p.N, p, h->t(nrhs, it), h->t(nnew, it), h->t(nstp, it), h->t(indx, it), dtau, cf_stp, cf_bak);
+  }
+  if (wl) PLANE((k_rhs_uv_horiz<false, true>), p.iend, p.jstr, p.jend, p.N, p, h->u(nrhs), h->v(nrhs));
+  else PLANE((k_rhs_uv_horiz<false, false>), p.iend, p.jstr, p.jend, p.N, p, h->u(nrhs), h->v(nrhs));
+  PLANE(k_rd_bott_drag, p.iend, p.jstrV - 1, p.jend, 1, p, h->u(nstp), h->v(nstp));
   for (int it = 1; it <= h->c.NT; ++it)
     COLUMN(k_t_vert<0>, 2, p.iend, p.jstr, p.jend, p, h->t(nrhs, it), h->t(nnew, it), p.Akt[it >= 2 ? 1 : 0], (const double*)nullptr, dtau, 0);
   COLUMN((k_uv_vert<0, 0>), 2, p.iend, p.jstr, p.jend, p, h->u(nrhs), h->u(nnew), h->u(nstp), h->u(indx), dtau, cf_stp, cf_bak);
-  COLUMN((k_uv_vert<0, 1>), 2, p.iend, p.jstr, p.jend, p, h->v(nrhs), h->v(nnew), h->v(nstp), h->v(indx), dtau, cf_stp, cf_bak);
-  // u3dbc/v3dbc/t3dbc: nothing on periodic edges; one exchange per tracer (pre_step3d4S.F:548)
+  COLUMN((k_uv_vert<0, 1>), 2, p.iend, p.jstrV, p.jend, p, h->v(nrhs), h->v(nnew), h->v(nstp), h->v(indx), dtau, cf_stp, cf_bak);
+  // u3dbc/v3dbc/t3dbc (pre_step3d4S.F:533-545), then one exchange per tracer (:548)
+  bc_rows(h, h->u(nnew), p.N, h->c.gamma2, p.umask, false);
+  bc_rows(h, h->v(nnew), p.N, 0.0, nullptr, true);
   for (int it = 1; it <= h->c.NT; ++it) {
+    bc_rows(h, h->t(nnew, it), p.N, 1.0, p.rmask, false);
     int rc = exchange(h, {{h->t(nnew, it), p.N}});
     if (rc) return rc;
   }
@@ -520,9 +557,10 @@ int roms_step3d_uv1(roms_ctx* h, int tile) {
   CK(cudaSetDevice(h->device));
   const KP& p = h->kp;
   const int nrhs = h->nrhs, nnew = h->nnew;
-  PLANE(k_rhs_uv_horiz<true>, p.iend, p.jstr, p.jend, p.N, p, h->u(nrhs), h->v(nrhs));
+  if (WALLED(h)) PLANE((k_rhs_uv_horiz<true, true>), p.iend, p.jstr, p.jend, p.N, p, h->u(nrhs), h->v(nrhs));
+  else PLANE((k_rhs_uv_horiz<true, false>), p.iend, p.jstr, p.jend, p.N, p, h->u(nrhs), h->v(nrhs));
   COLUMN((k_uv_vert<1, 0>), 2, p.iend, p.jstr, p.jend, p, h->u(nrhs), h->u(nnew), (const double*)nullptr, (double*)nullptr, h->c.dt, 0.0, 0.0);
-  COLUMN((k_uv_vert<1, 1>), 2, p.iend, p.jstr, p.jend, p, h->v(nrhs), h->v(nnew), (const double*)nullptr, (double*)nullptr, h->c.dt, 0.0, 0.0);
+  COLUMN((k_uv_vert<1, 1>), 2, p.iend, p.jstrV, p.jend, p, h->v(nrhs), h->v(nnew), (const double*)nullptr, (double*)nullptr, h->c.dt, 0.0, 0.0);
   return 0;
 }
 int roms_step2d(roms_ctx* h) {
@@ -551,8 +589,15 @@ int roms_step2d(roms_ctx* h) {
   s.zn = h->zeta(knew); s.un = h->ubar(knew); s.vn = h->vbar(knew);
   s.w1 = h->w1[iif]; s.w2 = h->w2[iif];
   s.iif = iif; s.nfast = h->nfast;
-  PLANE(k_step2d_zeta, p.iend, p.jstr - 1, p.jend, 1, p, s);
+  PLANE(k_step2d_zeta, p.iend, (p.swall ? p.jstrR : p.jstr - 1), p.jendR, 1, p, s);
   PLANE(k_step2d_uv, p.iend, p.jstr, p.jend, 1, p, s);
+  if (WALLED(h)) {
+    dim3 b_(128, 1, 1), g_((p.iend + IOFF + 1 + 127) / 128, 1, 1);
+    if (h->ktiming) kt_begin(h, "k_step2d_bc");
+    k_step2d_bc<<<g_, b_, 0, h->st>>>(p, s);
+    if (h->ktiming) kt_end(h);
+    h->launches++;
+  }
   if (iif == h->nfast) {
     int rc = roms_set_depth(h, 0);
     if (rc) return rc;
@@ -565,10 +610,11 @@ int roms_step3d_uv2(roms_ctx* h, int tile) {
   const KP& p = h->kp;
   const int nnew = h->nnew, nstp = h->nstp, knew = h->knew;
   COLUMN(k_uv2_pass0<0>, 0, p.iend, p.jstr, p.jend, p, h->u(nnew));
-  COLUMN(k_uv2_pass0<1>, 0, p.iend, p.jstr, p.jend, p, h->v(nnew));
-  // u3dbc_tile / v3dbc_tile act here on non-periodic edges (step3d_uv2.F:471-472)
-  COLUMN(k_uv2_pass1<0>, 0, p.iend, p.jstr, p.jend, p, h->u(nnew), h->u(nstp), h->ubar(knew));
-  COLUMN(k_uv2_pass1<1>, 0, p.iend, p.jstr, p.jend, p, h->v(nnew), h->v(nstp), h->vbar(knew));
+  COLUMN(k_uv2_pass0<1>, 0, p.iend, p.jstrV, p.jend, p, h->v(nnew));
+  bc_rows(h, h->u(nnew), p.N, h->c.gamma2, p.umask, false);     // u3dbc_tile / v3dbc_tile (step3d_uv2.F:471-472)
+  bc_rows(h, h->v(nnew), p.N, 0.0, nullptr, true);
+  COLUMN(k_uv2_pass1<0>, 0, p.iend, p.jstrR, p.jendR, p, h->u(nnew), h->u(nstp), h->ubar(knew));
+  COLUMN(k_uv2_pass1<1>, 0, p.iend, p.jstr, p.jendR, p, h->v(nnew), h->v(nstp), h->vbar(knew));
   int rc = exchange(h, {{p.FlxU, p.N}, {h->u(nnew), p.N}, {h->ubar(knew), 1}});
   if (rc) return rc;
   return exchange(h, {{p.FlxV, p.N}, {h->v(nnew), p.N}, {h->vbar(knew), 1}});
@@ -579,10 +625,12 @@ int roms_step3d_t(roms_ctx* h, int tile) {
   const KP& p = h->kp;
   const int nrhs = h->nrhs, nnew = h->nnew, NT = h->c.NT;
   for (int it = 1; it <= NT; ++it) {
-    PLANE(k_t_horiz, p.iend, p.jstr, p.jend, p.N, p, h->t(nrhs, it), h->t(nnew, it));
+    if (WALLED(h)) PLANE(k_t_horiz<true>, p.iend, p.jstr, p.jend, p.N, p, h->t(nrhs, it), h->t(nnew, it));
+    else PLANE(k_t_horiz<false>, p.iend, p.jstr, p.jend, p.N, p, h->t(nrhs, it), h->t(nnew, it));
     COLUMN(k_t_vert<1>, 2, p.iend, p.jstr, p.jend, p, h->t(nrhs, it), h->t(nnew, it), p.Akt[it >= 2 ? 1 : 0], h->f[ROMS_STFLX].ptr[it - 1], h->c.dt,
            it == 1 ? 1 : 0);
   }
+  for (int it = 1; it <= NT; ++it) bc_rows(h, h->t(nnew, it), p.N, 1.0, p.rmask, false);   // t3dbc_tile (step3d_t_ISO.F:1157-1159)
   for (int it = 1; it + 1 <= NT; it += 2) {
     int rc = exchange(h, {{h->t(nnew, it), p.N}, {h->t(nnew, it + 1), p.N}});
     if (rc) return rc;
