@@ -128,6 +128,7 @@ def main():
     ap.add_argument("--nt", type=int, default=2)
     ap.add_argument("--cpu-sample", type=int, nargs=3, default=[256, 256, 64])
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--periodic", action="store_true", help="doubly periodic variant instead of the closed N/S walls of BASELINE configs[1]")
     ap.add_argument("--kernel-table", default=None, help="write the per-kernel timing table to this file")
     a = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -135,9 +136,9 @@ def main():
     local = int(os.environ.get("LOCAL_RANK", "0"))
     Lm, Mm, N = a.size
     NT = a.nt
-    case_kw = dict(NT=NT, ns_walls=False, nonlin_eos=True)
+    case_kw = dict(NT=NT, ns_walls=not a.periodic, nonlin_eos=True)
     workload = f"analytic baroclinic channel {Lm}x{Mm}x{N} per GPU, T+S" + (f"+{NT - 2} passive" if NT > 2 else "") + \
-               ", nonlinear split EOS, doubly periodic, ndtfast=60 (82 executed barotropic substeps per step)"
+               ", nonlinear split EOS, " + ("doubly periodic" if a.periodic else "E-W periodic, closed free-slip N/S walls") + ", ndtfast=60 (82 executed barotropic substeps per step)"
     config = {"workload": workload, "grid_per_gpu": [Lm, Mm, N], "tracers": NT, "l2_policy": "inputs (15 GB of resident state per GPU) larger than L2; no flush",
               "timing": "CUDA events on the library stream, barrier+sync both sides, max over ranks"}
 
