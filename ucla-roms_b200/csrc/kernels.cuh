@@ -13,6 +13,16 @@
 #pragma once
 #include "kp.h"
 
+// minimum resident 256-thread blocks per SM asked of ptxas for the latency-bound plane kernels (tuned on B200)
+#ifndef LB_PRS
+#define LB_PRS 4
+#endif
+#ifndef LB_RHS
+#define LB_RHS 4
+#endif
+#ifndef LB_S2D
+#define LB_S2D 4
+#endif
 #define DMAX(a, b) fmax((a), (b))
 #define DMIN(a, b) fmin((a), (b))
 
@@ -366,15 +376,16 @@ __device__ __forceinline__ double prs_dir(const KP& p, long c, long d, int k, co
     rxa = (a1 - a0) * m1; rxb = (a2 - a1) * m2; rxc = (a3 - a2) * m3;
   }
   }
-  // dZx, dRx at c-d ("m") and c ("c")
-  double cff = 2.0 * FCa * FCb;
-  const double dZx_m = (cff > epsil) ? cff / (FCa + FCb) : 0.0;
-  cff = 2.0 * FCb * FCc;
-  const double dZx_c = (cff > epsil) ? cff / (FCb + FCc) : 0.0;
-  double cfr = 2.0 * rxa * rxb;
-  double dRx_m = (cfr > epsil) ? cfr / (rxa + rxb) : 0.0;
-  cfr = 2.0 * rxb * rxc;
-  double dRx_c = (cfr > epsil) ? cfr / (rxb + rxc) : 0.0;
+  // dZx, dRx at c-d ("m") and c ("c"): harmonic means (prsgrd.F:330-345).  The quotient is formed unconditionally and
+  // selected afterwards (same value where it is used) so that rows sharing a mean share the division.
+  double cff = 2.0 * FCa * FCb, quo = cff / (FCa + FCb);
+  const double dZx_m = (cff > epsil) ? quo : 0.0;
+  cff = 2.0 * FCb * FCc; quo = cff / (FCb + FCc);
+  const double dZx_c = (cff > epsil) ? quo : 0.0;
+  cff = 2.0 * rxa * rxb; quo = cff / (rxa + rxb);
+  double dRx_m = (cff > epsil) ? quo : 0.0;
+  cff = 2.0 * rxb * rxc; quo = cff / (rxb + rxc);
+  double dRx_c = (cff > epsil) ? quo : 0.0;
   if (NONLIN) {
     dRx_m = dRx_m - q1 * dZx_m * (1.0 + 2.0 * qp2 * z1);
     dRx_c = dRx_c - q2v * dZx_c * (1.0 + 2.0 * qp2 * z2);
@@ -385,16 +396,41 @@ __device__ __forceinline__ double prs_dir(const KP& p, long c, long d, int k, co
           HalfGRho * ((rho_c + rho_m) * (z2 - z1) -
                       OneFifth * ((dRx_c - dRx_m) * (z2 - z1 - OneTwelfth * (dZx_c + dZx_m)) - (dZx_c - dZx_m) * (rho_c - rho_m - OneTwelfth * (dRx_c + dRx_m)))));
 }
-template <bool NONLIN, bool WALL>
-__global__ void k_prsgrd_horiz(const __grid_constant__ KP p) {
-  THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
+template <bool NONLIN, bool WALL, int JB>
+__global__ void __launch_bounds__(256, LB_PRS) k_prsgrd_horiz(const __grid_constant__ KP p) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x - IOFF;
+  const int jb = p.jstr + (blockIdx.y * blockDim.y + threadIdx.y) * JB;
+  if (i < p.istr || i > p.iend || jb > p.jend) return;
+  const long SX = p.SX;
   const int k = blockIdx.z + 1;
-  const double* rho = NONLIN ? p.rho : p.rho1;
-  R3(p.ru, c, k) = prs_dir<NONLIN, false>(p, c, 1, k, p.umask, p.dn_u[c], rho);
-  if (!WALL) R3(p.rv, c, k) = prs_dir<NONLIN, false>(p, c, SX, k, p.vmask, p.dm_v[c], rho);
-  else if (j >= p.jstrV)   // prsgrd.F:288-310: FC,rx exist on rows jstrV..jend between walls, copied one row outward
-    R3(p.rv, c, k) = prs_dir<NONLIN, true>(p, c, SX, k, p.vmask, p.dm_v[c], rho, jclamp(p, j - 1, p.jstrV, p.jend), jclamp(p, j, p.jstrV, p.jend),
-                                           jclamp(p, j + 1, p.jstrV, p.jend));
+  const double* __restrict__ rho = NONLIN ? p.rho : p.rho1;
+  const bool near = WALL && ((p.swall && jb <= p.jstr + 2) || (p.nwall && jb + JB - 1 >= p.jend - 2));
+  const long c0 = CIDX(i, jb);
+  if (near || jb + JB - 1 > p.jend) {   // rows next to a wall / ragged last block: one row at a time
+#pragma unroll 1
+    for (int q = 0; q < JB && jb + q <= p.jend; ++q) {
+      const int j = jb + q;
+      const long c = c0 + q * SX;
+      R3(p.ru, c, k) = prs_dir<NONLIN, false>(p, c, 1, k, p.umask, p.dn_u[c], rho);
+      if (!WALL) R3(p.rv, c, k) = prs_dir<NONLIN, false>(p, c, SX, k, p.vmask, p.dm_v[c], rho);
+      else if (j >= p.jstrV)   // prsgrd.F:288-310: FC,rx exist on rows jstrV..jend between walls, copied one row outward
+        R3(p.rv, c, k) = prs_dir<NONLIN, true>(p, c, SX, k, p.vmask, p.dm_v[c], rho, jclamp(p, j - 1, p.jstrV, p.jend), jclamp(p, j, p.jstrV, p.jend),
+                                               jclamp(p, j + 1, p.jstrV, p.jend));
+    }
+    return;
+  }
+  double ru[JB], rv[JB];
+#pragma unroll
+  for (int q = 0; q < JB; ++q) {
+    const long c = c0 + q * SX;
+    ru[q] = prs_dir<NONLIN, false>(p, c, 1, k, p.umask, p.dn_u[c], rho);
+    rv[q] = prs_dir<NONLIN, false>(p, c, SX, k, p.vmask, p.dm_v[c], rho);
+  }
+#pragma unroll
+  for (int q = 0; q < JB; ++q) {
+    R3(p.ru, c0 + q * SX, k) = ru[q];
+    R3(p.rv, c0 + q * SX, k) = rv[q];
+  }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -450,22 +486,22 @@ __device__ __forceinline__ double flux_cross(const KP& p, const double* __restri
   } else
     return 0.25 * (uc + ub - HDELTA * (w1c + w1m)) * (fc + fb - HDELTA * (w2c + w2m));
 }
-template <bool UP, bool WALL>
-__global__ void k_rhs_uv_horiz(const __grid_constant__ KP p, const double* __restrict__ u, const double* __restrict__ v) {
-  THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
-  const int k = blockIdx.z + 1;
-  const bool dov = !WALL || j >= p.jstrV;    // no v-row on a southern wall
+// one (i,j,k) point of the horizontal momentum RHS; NEAR: a row within two rows of a closed wall (clamped differences)
+template <bool UP, bool NEAR>
+__device__ __forceinline__ void rhs_uv_point(const KP& p, const double* __restrict__ u, const double* __restrict__ v, long c, int j, int k, bool dov,
+                                             double& ru, double& rv) {
+  const long SX = p.SX;
   // Coriolis (no CURVGRID): compute_horiz_rhs_uv_terms.h:4-45
   const double cf0 = 0.5 * R3(p.Hz, c, k) * (p.fomn[c]);
   const double cfw = 0.5 * R3(p.Hz, c - 1, k) * (p.fomn[c - 1]);
   const double v00 = R3(v, c, k), u00 = R3(u, c, k);
   const double UFx_c = cf0 * (v00 + R3(v, c + SX, k));
   const double UFx_w = cfw * (R3(v, c - 1, k) + R3(v, c - 1 + SX, k));
-  double ru = R3(p.ru, c, k) + 0.5 * (UFx_c + UFx_w);
+  ru = R3(p.ru, c, k) + 0.5 * (UFx_c + UFx_w);
   // advection of u
   const double UFx_i = flux_along<UP, false>(p, u, p.FlxU, c, 1, k), UFx_im = flux_along<UP, false>(p, u, p.FlxU, c - 1, 1, k);
   double UFe_jp, UFe_j;
-  if (WALL) {   // u second differences in j exist on rows jstr..jend between walls (compute_horiz_rhs_uv_terms.h:186-199)
+  if (NEAR) {   // u second differences in j exist on rows jstr..jend between walls (compute_horiz_rhs_uv_terms.h:186-199)
     UFe_jp = flux_cross<UP, true>(p, u, p.FlxV, c + SX, SX, 1, k, jclamp(p, j, p.jstr, p.jend), jclamp(p, j + 1, p.jstr, p.jend));
     UFe_j = flux_cross<UP, true>(p, u, p.FlxV, c, SX, 1, k, jclamp(p, j - 1, p.jstr, p.jend), jclamp(p, j, p.jstr, p.jend));
   } else {
@@ -473,15 +509,14 @@ __global__ void k_rhs_uv_horiz(const __grid_constant__ KP p, const double* __res
     UFe_j = flux_cross<UP, false>(p, u, p.FlxV, c, SX, 1, k);
   }
   ru = ru - UFx_i + UFx_im - UFe_jp + UFe_j;
-  R3(p.ru, c, k) = ru;
   if (dov) {
     const double cfs = 0.5 * R3(p.Hz, c - SX, k) * (p.fomn[c - SX]);
     const double VFe_c = cf0 * (u00 + R3(u, c + 1, k));
     const double VFe_s = cfs * (R3(u, c - SX, k) + R3(u, c - SX + 1, k));
-    double rv = R3(p.rv, c, k) - 0.5 * (VFe_c + VFe_s);
+    rv = R3(p.rv, c, k) - 0.5 * (VFe_c + VFe_s);
     const double VFx_ip = flux_cross<UP, false>(p, v, p.FlxU, c + 1, 1, SX, k), VFx_i = flux_cross<UP, false>(p, v, p.FlxU, c, 1, SX, k);
     double VFe_j, VFe_jm;
-    if (WALL) {   // v, FlxV second differences exist on rows jstrV..jend between walls (compute_horiz_rhs_uv_terms.h:128-141)
+    if (NEAR) {   // v, FlxV second differences exist on rows jstrV..jend between walls (compute_horiz_rhs_uv_terms.h:128-141)
       VFe_j = flux_along<UP, true>(p, v, p.FlxV, c, SX, k, jclamp(p, j, p.jstrV, p.jend), jclamp(p, j + 1, p.jstrV, p.jend));
       VFe_jm = flux_along<UP, true>(p, v, p.FlxV, c - SX, SX, k, jclamp(p, j - 1, p.jstrV, p.jend), jclamp(p, j, p.jstrV, p.jend));
     } else {
@@ -489,7 +524,40 @@ __global__ void k_rhs_uv_horiz(const __grid_constant__ KP p, const double* __res
       VFe_jm = flux_along<UP, false>(p, v, p.FlxV, c - SX, SX, k);
     }
     rv = rv - VFx_ip + VFx_i - VFe_j + VFe_jm;
-    R3(p.rv, c, k) = rv;
+  }
+}
+// Each thread computes JB consecutive rows: the neighbour loads and second differences shared by the rows are
+// evaluated once (results are stored only after the last row so that nothing forces a reload).
+// Measured on B200 (1024x1024x64): C4 (UP=false) 1.86 ms at JB=1 -> 1.59 ms at JB=4 with 128 registers; UP3 is best at JB=1.
+template <bool UP, bool WALL, int JB>
+__global__ void __launch_bounds__(256, (JB >= 4 ? 2 : LB_RHS)) k_rhs_uv_horiz(const __grid_constant__ KP p, const double* __restrict__ u, const double* __restrict__ v) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x - IOFF;
+  const int jb = p.jstr + (blockIdx.y * blockDim.y + threadIdx.y) * JB;
+  if (i < p.istr || i > p.iend || jb > p.jend) return;
+  const int k = blockIdx.z + 1;
+  const bool near = WALL && ((p.swall && jb <= p.jstr + 2) || (p.nwall && jb + JB - 1 >= p.jend - 2));
+  const long c0 = CIDX(i, jb), SX = p.SX;
+  if (near || jb + JB - 1 > p.jend) {   // rows next to a wall / ragged last block: one row at a time
+#pragma unroll 1
+    for (int q = 0; q < JB && jb + q <= p.jend; ++q) {
+      const int j = jb + q;
+      const long c = c0 + q * SX;
+      const bool dov = !WALL || j >= p.jstrV;
+      double ru, rv;
+      if (WALL) rhs_uv_point<UP, true>(p, u, v, c, j, k, dov, ru, rv);
+      else rhs_uv_point<UP, false>(p, u, v, c, j, k, dov, ru, rv);
+      R3(p.ru, c, k) = ru;
+      if (dov) R3(p.rv, c, k) = rv;
+    }
+    return;
+  }
+  double ru[JB], rv[JB];
+#pragma unroll
+  for (int q = 0; q < JB; ++q) rhs_uv_point<UP, false>(p, u, v, c0 + q * SX, jb + q, k, true, ru[q], rv[q]);
+#pragma unroll
+  for (int q = 0; q < JB; ++q) {
+    R3(p.ru, c0 + q * SX, k) = ru[q];
+    R3(p.rv, c0 + q * SX, k) = rv[q];
   }
 }
 
@@ -531,7 +599,7 @@ __global__ void k_pre_flxdiv(const __grid_constant__ KP p, double dtau) {
 // FE at v-rows j and j+1; between walls the first differences exist on rows jstr..jend+1 (compute_horiz_tracer_fluxes.h:118-160)
 #define TFLUX_J(UP, FEj, FEjp)                                                                                                     \
   double FEj, FEjp;                                                                                                                \
-  if (WALL) {                                                                                                                      \
+  if (WALL && ((p.swall && j <= p.jstr + 2) || (p.nwall && j >= p.jend - 2))) { /* rows next to a wall only */                     \
     FEj = tflux<UP, true>(p, t_rhs, p.FlxV, p.vmask, c, SX, k, jclamp(p, j - 1, p.jstr, p.jend + 1), jclamp(p, j, p.jstr, p.jend + 1),       \
                           jclamp(p, j + 1, p.jstr, p.jend + 1));                                                                   \
     FEjp = tflux<UP, true>(p, t_rhs, p.FlxV, p.vmask, c + SX, SX, k, jclamp(p, j, p.jstr, p.jend + 1), jclamp(p, j + 1, p.jstr, p.jend + 1), \
@@ -906,7 +974,7 @@ __device__ __forceinline__ double s2d_zeta_new(const KP& p, const S2D& s, long c
 }
 // rows jstrV-1..jend carry the continuity update; a row just outside a closed wall takes zetabc's gradient
 // condition (zetabc.F:3: zeta_new(i,jstr-1)=zeta_new(i,jstr)*rmask(i,jstr-1)), re-evaluating its neighbour's update.
-__global__ void k_step2d_zeta(const __grid_constant__ KP p, const __grid_constant__ S2D s) {
+__global__ void __launch_bounds__(256, LB_S2D) k_step2d_zeta(const __grid_constant__ KP p, const __grid_constant__ S2D s) {
   THREAD_IJ(p.istr - 1, p.iend, (p.swall ? p.jstrR : p.jstr - 1), p.jendR)
   double zn;
   if (p.swall && j < p.jstr) zn = s2d_zeta_new(p, s, c + SX) * p.rmask[c];
@@ -958,7 +1026,7 @@ __device__ __forceinline__ double s2d_pgf(const KP& p, double cff, double dn, lo
          ((p.h[c - d] + p.h[c]) * (a.UFe - b.UFe) + a.VFe - b.VFe +
           (p.h[c - d] - p.h[c]) * (a.VFx + b.VFx + 0.333333333333 * (p.rhoA[c - d] - p.rhoA[c]) * (a.UFx - b.UFx)));
 }
-__global__ void k_step2d_uv(const __grid_constant__ KP p, const __grid_constant__ S2D s) {
+__global__ void __launch_bounds__(256, LB_S2D) k_step2d_uv(const __grid_constant__ KP p, const __grid_constant__ S2D s) {
   THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
   const double cffg = 0.5 * p.g;
   const bool sv = (j - 1 >= p.jstrV - 1);     // row j-1 carries a zeta_new
@@ -988,6 +1056,152 @@ __global__ void k_step2d_uv(const __grid_constant__ KP p, const __grid_constant_
     p.DV_avg1[c] = p.DV_avg1[c] + cff1 * p.dm_v[c] * (DVnew);
   }
   if (s.iif == s.nfast) s.zn[c] = p.Zt_avg1[c];
+}
+// ---- fused barotropic substep ---------------------------------------------------------------------------------
+// One launch per substep: a 32x8 tile first evaluates zeta_new on its points plus the row below and the column to
+// the left (33x9 values in shared memory -- the reference's private zeta_new plane never exists in HBM), then every
+// thread finishes its own point: zeta(knew), the fast-time averages, rubar/rvbar, ubar/vbar(knew).  The thread next
+// to a closed wall also owns the wall point beside it (zetabc / u2dbc / v2dbc, step2d_FB.F:449-529), and on a single
+// subdomain the results are stored to their periodic images as well, so no exchange launch follows.
+#define S2_TX 32
+#define S2_TY 8
+__device__ __forceinline__ double s2d_zn_at(const KP& p, const S2D& s, long c, int j) {
+  if (p.swall && j < p.jstr) return s2d_zeta_new(p, s, c + p.SX) * p.rmask[c];
+  if (p.nwall && j > p.jend) return s2d_zeta_new(p, s, c - p.SX) * p.rmask[c];
+  return s2d_zeta_new(p, s, c);
+}
+__device__ __forceinline__ S2Pt s2d_ptz(const KP& p, const S2D& s, long c, double zn, bool corr) {
+  S2Pt r;
+  const double zs = s.zs[c];
+  if (!corr) {
+    r.UFx = s.bkw_new * zn + s.bkw * zs + s.bkw1 * s.zb[c] + s.bkw2 * s.zo[c];
+    r.UFe = (1.0 + p.rhoS[c]) * r.UFx;
+    r.VFx = r.UFx * (p.rhoS[c] - p.rhoA[c]);
+    r.VFe = r.UFe * r.UFx;
+  } else {
+    r.UFx = zn - zs;
+    r.UFe = (1.0 + p.rhoS[c]) * r.UFx;
+    r.VFe = r.UFe * (zn + zs);
+    r.VFx = r.UFx * (p.rhoS[c] - p.rhoA[c]);
+  }
+  return r;
+}
+// store to (i,j) and, on a single periodic subdomain, to its images in the halo (mpi_setup.F:231-250 wrap)
+__device__ __forceinline__ void s2d_store(const KP& p, double* __restrict__ a, int i, int j, long c, double v) {
+  a[c] = v;
+  if (p.wrap_x | p.wrap_y) {
+    const long ox = !p.wrap_x ? 0 : (i <= 2 ? (long)p.Lm : (i >= p.Lm - 1 ? -(long)p.Lm : 0));
+    const long oy = !p.wrap_y ? 0 : (j <= 2 ? (long)p.Mm * p.SX : (j >= p.Mm - 1 ? -(long)p.Mm * p.SX : 0));
+    if (ox) a[c + ox] = v;
+    if (oy) a[c + oy] = v;
+    if (ox && oy) a[c + ox + oy] = v;
+  }
+}
+// zeta(knew), Zt_avg1, DU_avg2, DV_avg2 (and the first-substep resets) at one point; returns the running DU_avg1/DV_avg1
+__device__ __forceinline__ void s2d_avg_out(const KP& p, const S2D& s, int i, int j, long c, double zn, double DUon, double DVom, double& DU1, double& DV1,
+                                            double& Zt) {
+  s2d_store(p, s.zn, i, j, c, zn);
+  if (s.iif == 1) {
+    p.DU_avg_bak[c] = p.DU_avg1[c] - 0.1024390243902439 * p.DU_avg2[c];
+    p.DV_avg_bak[c] = p.DV_avg1[c] - 0.1024390243902439 * p.DV_avg2[c];
+    Zt = s.w1 * zn;
+    DU1 = 0.0;
+    DV1 = 0.0;
+    p.DU_avg2[c] = s.w2 * DUon;
+    p.DV_avg2[c] = s.w2 * DVom;
+  } else {
+    Zt = p.Zt_avg1[c] + s.w1 * zn;
+    DU1 = p.DU_avg1[c];
+    DV1 = p.DV_avg1[c];
+    p.DU_avg2[c] = p.DU_avg2[c] + s.w2 * DUon;
+    p.DV_avg2[c] = p.DV_avg2[c] + s.w2 * DVom;
+  }
+  p.Zt_avg1[c] = Zt;
+}
+__global__ void __launch_bounds__(S2_TX * S2_TY, LB_S2D) k_step2d(const __grid_constant__ KP p, const __grid_constant__ S2D s) {
+  __shared__ double zt[S2_TY + 1][S2_TX + 1];
+  const int tx = threadIdx.x, ty = threadIdx.y;
+  const int i0 = blockIdx.x * S2_TX - IOFF, j0 = p.jstr + blockIdx.y * S2_TY;
+  const int i = i0 + tx, j = j0 + ty;
+  const long SX = p.SX;
+  // ---- phase 1: zeta_new (step2d_FB.F:151-216) on the tile, the row below it and the column to its left
+  if (i >= p.istr - 1 && i <= p.iend && j <= p.jend) zt[ty + 1][tx + 1] = s2d_zeta_new(p, s, CIDX(i, j));
+  {
+    const int t = ty * S2_TX + tx;
+    if (t < S2_TX + 1) {
+      const int ii = i0 - 1 + t, jj = j0 - 1;
+      if (ii >= p.istr - 1 && ii <= p.iend) zt[0][t] = s2d_zn_at(p, s, CIDX(ii, jj), jj);
+    } else if (t < S2_TX + 1 + S2_TY) {
+      const int r = t - (S2_TX + 1), ii = i0 - 1, jj = j0 + r;
+      if (ii >= p.istr - 1 && jj <= p.jend) zt[r + 1][0] = s2d_zeta_new(p, s, CIDX(ii, jj));
+    }
+  }
+  __syncthreads();
+  if (i < p.istr || i > p.iend || j > p.jend) return;
+  // ---- phase 2: own point
+  const long c = CIDX(i, j);
+  const double zn = zt[ty + 1][tx + 1], znw = zt[ty + 1][tx], zns = zt[ty][tx + 1];
+  double DU1, DV1, Zt;
+  s2d_avg_out(p, s, i, j, c, zn, s2d_DUon(p, s, c), s2d_DVom(p, s, c), DU1, DV1, Zt);
+  const double cffg = 0.5 * p.g;
+  const bool sv = (j - 1 >= p.jstrV - 1);     // row j-1 carries a zeta_new
+  const bool dov = (j >= p.jstrV);
+  const S2Pt zero = {0.0, 0.0, 0.0, 0.0};     // row below a southern wall: zero-initialised scratch in the reference
+  const S2Pt a0 = s2d_ptz(p, s, c, zn, false), aw = s2d_ptz(p, s, c - 1, znw, false), as = sv ? s2d_ptz(p, s, c - SX, zns, false) : zero;
+  double rubar = s2d_pgf(p, cffg, p.dn_u[c], c, 1, aw, a0);
+  double rvbar = s2d_pgf(p, cffg, p.dm_v[c], c, SX, as, a0);
+  double rufrc = p.rufrc[c], rvfrc = p.rvfrc[c];
+  if (s.iif == 1) {
+    rufrc = rufrc - rubar;
+    rvfrc = rvfrc - rvbar;
+    p.rufrc[c] = rufrc;
+    p.rvfrc[c] = rvfrc;
+    const S2Pt b0 = s2d_ptz(p, s, c, zn, true), bw = s2d_ptz(p, s, c - 1, znw, true), bs = sv ? s2d_ptz(p, s, c - SX, zns, true) : zero;
+    rubar = rubar + s2d_pgf(p, cffg, p.dn_u[c], c, 1, bw, b0);
+    rvbar = rvbar + s2d_pgf(p, cffg, p.dm_v[c], c, SX, bs, b0);
+  }
+  const double D0 = s.zs[c] + p.h[c], Dw = s.zs[c - 1] + p.h[c - 1], Ds = s.zs[c - SX] + p.h[c - SX];
+  const double Dn0 = zn + p.h[c], Dnw = znw + p.h[c - 1], Dns = zns + p.h[c - SX];
+  const double cff = 0.5 * p.dtfast, cff1 = 0.5 * s.w1;
+  const double DUnew = ((D0 + Dw) * s.us[c] + cff * (p.pm[c] + p.pm[c - 1]) * (p.pn[c] + p.pn[c - 1]) * (rubar + rufrc)) * p.umask[c];
+  const double un = DUnew / (Dn0 + Dnw);
+  s2d_store(p, s.un, i, j, c, un);
+  p.DU_avg1[c] = DU1 + cff1 * p.dn_u[c] * (DUnew);
+  if (dov) {
+    const double DVnew = ((D0 + Ds) * s.vs[c] + cff * (p.pm[c] + p.pm[c - SX]) * (p.pn[c] + p.pn[c - SX]) * (rvbar + rvfrc)) * p.vmask[c];
+    s2d_store(p, s.vn, i, j, c, DVnew / (Dn0 + Dns));
+    p.DV_avg1[c] = DV1 + cff1 * p.dm_v[c] * (DVnew);
+  } else {   // row jstr on a southern wall: v2dbc (no normal flow) and its DV_avg1 term (step2d_FB.F:449-529)
+    const double vn = 0.0;
+    s2d_store(p, s.vn, i, j, c, vn);
+    p.DV_avg1[c] = DV1 + cff1 * (Dn0 + Dns) * (vn) * p.dm_v[c];
+  }
+  if (s.iif == s.nfast) s2d_store(p, s.zn, i, j, c, Zt);
+  // ---- wall point beside this one
+  const bool sw = p.swall && j == p.jstr, nw = p.nwall && j == p.jend;
+  if (sw | nw) {
+#pragma unroll 1
+    for (int side = 0; side < 2; ++side) {
+      if (side == 0 ? !sw : !nw) continue;
+      const int jw = side == 0 ? j - 1 : j + 1;
+      const long w = side == 0 ? c - SX : c + SX;
+      // zetabc.F:3: gradient condition; the neighbour in -i likewise (needed for D at the u-point)
+      const double znb = side == 0 ? zns : zn * p.rmask[w];
+      const double znbw = side == 0 ? zt[ty][tx] : znw * p.rmask[w - 1];
+      double DU1w, DV1w, Ztw;
+      // DVom below a southern wall is never filled by the reference (zero scratch)
+      s2d_avg_out(p, s, i, jw, w, znb, s2d_DUon(p, s, w), side == 0 ? 0.0 : s2d_DVom(p, s, w), DU1w, DV1w, Ztw);
+      const double unw = p.gamma2 * un * p.umask[w];          // u2dbc_im.F:150-152
+      s2d_store(p, s.un, i, jw, w, unw);
+      p.DU_avg1[w] = DU1w + cff1 * ((p.h[w] + znb) + (p.h[w - 1] + znbw)) * (unw)*p.dn_u[w];
+      if (side == 1) {                                        // v2dbc_im.F: no normal flow through the northern wall
+        const double vnw = 0.0;
+        s2d_store(p, s.vn, i, jw, w, vnw);
+        p.DV_avg1[w] = DV1w + cff1 * ((znb + p.h[w]) + (zn + p.h[c])) * (vnw)*p.dm_v[w];
+      } else if (s.iif == 1) p.DV_avg1[w] = DV1w;
+      if (s.iif == s.nfast) s2d_store(p, s.zn, i, jw, w, Ztw);
+    }
+  }
 }
 // Closed-wall rows of the barotropic step: u2dbc_im.F:150-152 (gamma2 slip), v2dbc_im.F (no normal flow), the
 // boundary-row contributions to DU_avg1/DV_avg1 (step2d_FB.F:449-529) and zeta(knew)=Zt_avg1 on the last substep.

@@ -19,6 +19,7 @@ struct KP {
   int swall, nwall;             // this subdomain touches a closed (non-periodic) southern / northern physical edge
   int jstrR, jendR, jstrV;      // compute_auxiliary_bounds.h: jstr-1 / jend+1 / jstr+1 on such an edge, else jstr / jend / jstr
   int nonlin, salinity;
+  int wrap_x, wrap_y;           // single subdomain along a periodic direction: the fused 2-D kernel stores the halo images itself
   // scalars
   double dt, dtfast, g, rho0, Tcoef, T0, Scoef, S0, rdrg, rdrg2, Zob, gamma2, hc;
   // static 2-D

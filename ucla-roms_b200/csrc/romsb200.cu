@@ -54,6 +54,7 @@ struct roms_ctx {
   std::vector<KTimer> ktimers;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   int col_bx = 32, col_by = 2, pl_bx = 128, pl_by = 2;
+  int s2d_fused = 1;   // ROMS_S2D_FUSED=0 selects the three-launch barotropic substep (zeta, uv, wall rows)
   int use_smem = 0;   // measured on B200 (profiles/r1_scratch_policy.txt): occupancy beats shared-memory scratch
   Comm comm;
   double* u(int l) { return f[ROMS_U].ptr[l - 1]; }
@@ -71,6 +72,15 @@ static dim3 grid_plane(const roms_ctx* h, int i1, int j0, int j1, int nk, dim3 b
 }
 static void kt_begin(roms_ctx* h, const char* name);
 static void kt_end(roms_ctx* h);
+// plane kernel whose threads each compute JB consecutive rows
+#define PLANE_JB(kern, JB, i1, j0, j1, nk, ...)                                                  \
+  do {                                                                                        \
+    dim3 b_(h->pl_bx, h->pl_by, 1);                                                           \
+    if (h->ktiming) kt_begin(h, #kern);                                                       \
+    kern<<<grid_plane(h, i1, 0, ((j1) - (j0) + JB) / JB - 1, nk, b_), b_, 0, h->st>>>(__VA_ARGS__); \
+    if (h->ktiming) kt_end(h);                                                                \
+    h->launches++;                                                                            \
+  } while (0)
 #define PLANE(kern, i1, j0, j1, nk, ...)                                                      \
   do {                                                                                        \
     dim3 b_(h->pl_bx, h->pl_by, 1);                                                           \
@@ -218,6 +228,10 @@ int roms_create(const roms_cfg* cfg, int device, roms_ctx** out) {
   if (const char* e = getenv("ROMS_COL_BY")) h->col_by = atoi(e);
   if (const char* e = getenv("ROMS_PL_BX")) h->pl_bx = atoi(e);
   if (const char* e = getenv("ROMS_PL_BY")) h->pl_by = atoi(e);
+  if (const char* e = getenv("ROMS_S2D_FUSED")) h->s2d_fused = atoi(e);
+  const bool single = cfg->np_xi * cfg->np_eta == 1;
+  p.wrap_x = (single && h->s2d_fused && cfg->ew_periodic) ? 1 : 0;
+  p.wrap_y = (single && h->s2d_fused && cfg->ns_periodic) ? 1 : 0;
   if (const char* e = getenv("ROMS_COL_SMEM")) h->use_smem = atoi(e);
   if ((size_t)2 * (N + 1) * h->col_bx * h->col_by * sizeof(double) > 200 * 1024) { h->col_by = 1; }
   if ((size_t)2 * (N + 1) * h->col_bx * h->col_by * sizeof(double) > 200 * 1024) h->use_smem = 0;
@@ -511,12 +525,12 @@ int roms_prsgrd(roms_ctx* h) {
   const KP& p = h->kp;
   if (h->c.nonlin_eos) {
     COLUMN(k_prsgrd_vert<true>, 0, p.Lm, 0, p.Mm, p);
-    if (WALLED(h)) PLANE((k_prsgrd_horiz<true, true>), p.iend, p.jstr, p.jend, p.N, p);
-    else PLANE((k_prsgrd_horiz<true, false>), p.iend, p.jstr, p.jend, p.N, p);
+    if (WALLED(h)) PLANE_JB((k_prsgrd_horiz<true, true, 1>), 1, p.iend, p.jstr, p.jend, p.N, p);
+    else PLANE_JB((k_prsgrd_horiz<true, false, 1>), 1, p.iend, p.jstr, p.jend, p.N, p);
   } else {
     COLUMN(k_prsgrd_vert<false>, 0, p.Lm, 0, p.Mm, p);
-    if (WALLED(h)) PLANE((k_prsgrd_horiz<false, true>), p.iend, p.jstr, p.jend, p.N, p);
-    else PLANE((k_prsgrd_horiz<false, false>), p.iend, p.jstr, p.jend, p.N, p);
+    if (WALLED(h)) PLANE_JB((k_prsgrd_horiz<false, true, 1>), 1, p.iend, p.jstr, p.jend, p.N, p);
+    else PLANE_JB((k_prsgrd_horiz<false, false, 1>), 1, p.iend, p.jstr, p.jend, p.N, p);
   }
   return 0;
 }
@@ -535,8 +549,8 @@ int roms_pre_step3d(roms_ctx* h, int tile) {
     if (wl) PLANE(k_pre_t_horiz<true>, p.iend, p.jstr, p.jend, p.N, p, h->t(nrhs, it), h->t(nnew, it), h->t(nstp, it), h->t(indx, it), dtau, cf_stp, cf_bak);
     else PLANE(k_pre_t_horiz<false>, p.iend, p.jstr, p.jend, p.N, p, h->t(nrhs, it), h->t(nnew, it), h->t(nstp, it), h->t(indx, it), dtau, cf_stp, cf_bak);
   }
-  if (wl) PLANE((k_rhs_uv_horiz<false, true>), p.iend, p.jstr, p.jend, p.N, p, h->u(nrhs), h->v(nrhs));
-  else PLANE((k_rhs_uv_horiz<false, false>), p.iend, p.jstr, p.jend, p.N, p, h->u(nrhs), h->v(nrhs));
+  if (wl) PLANE_JB((k_rhs_uv_horiz<false, true, 4>), 4, p.iend, p.jstr, p.jend, p.N, p, h->u(nrhs), h->v(nrhs));
+  else PLANE_JB((k_rhs_uv_horiz<false, false, 4>), 4, p.iend, p.jstr, p.jend, p.N, p, h->u(nrhs), h->v(nrhs));
   PLANE(k_rd_bott_drag, p.iend, p.jstrV - 1, p.jend, 1, p, h->u(nstp), h->v(nstp));
   for (int it = 1; it <= h->c.NT; ++it)
     COLUMN(k_t_vert<0>, 2, p.iend, p.jstr, p.jend, p, h->t(nrhs, it), h->t(nnew, it), p.Akt[it >= 2 ? 1 : 0], (const double*)nullptr, dtau, 0);
@@ -557,8 +571,8 @@ int roms_step3d_uv1(roms_ctx* h, int tile) {
   CK(cudaSetDevice(h->device));
   const KP& p = h->kp;
   const int nrhs = h->nrhs, nnew = h->nnew;
-  if (WALLED(h)) PLANE((k_rhs_uv_horiz<true, true>), p.iend, p.jstr, p.jend, p.N, p, h->u(nrhs), h->v(nrhs));
-  else PLANE((k_rhs_uv_horiz<true, false>), p.iend, p.jstr, p.jend, p.N, p, h->u(nrhs), h->v(nrhs));
+  if (WALLED(h)) PLANE_JB((k_rhs_uv_horiz<true, true, 1>), 1, p.iend, p.jstr, p.jend, p.N, p, h->u(nrhs), h->v(nrhs));
+  else PLANE_JB((k_rhs_uv_horiz<true, false, 1>), 1, p.iend, p.jstr, p.jend, p.N, p, h->u(nrhs), h->v(nrhs));
   COLUMN((k_uv_vert<1, 0>), 2, p.iend, p.jstr, p.jend, p, h->u(nrhs), h->u(nnew), (const double*)nullptr, (double*)nullptr, h->c.dt, 0.0, 0.0);
   COLUMN((k_uv_vert<1, 1>), 2, p.iend, p.jstrV, p.jend, p, h->v(nrhs), h->v(nnew), (const double*)nullptr, (double*)nullptr, h->c.dt, 0.0, 0.0);
   return 0;
@@ -589,6 +603,19 @@ int roms_step2d(roms_ctx* h) {
   s.zn = h->zeta(knew); s.un = h->ubar(knew); s.vn = h->vbar(knew);
   s.w1 = h->w1[iif]; s.w2 = h->w2[iif];
   s.iif = iif; s.nfast = h->nfast;
+  if (h->s2d_fused) {
+    dim3 b_(S2_TX, S2_TY, 1), g_((p.iend + IOFF + 1 + S2_TX - 1) / S2_TX, (p.jend - p.jstr + 1 + S2_TY - 1) / S2_TY, 1);
+    if (h->ktiming) kt_begin(h, "k_step2d");
+    k_step2d<<<g_, b_, 0, h->st>>>(p, s);
+    if (h->ktiming) kt_end(h);
+    h->launches++;
+    if (iif == h->nfast) {
+      int rc = roms_set_depth(h, 0);
+      if (rc) return rc;
+    }
+    if (h->c.np_xi * h->c.np_eta == 1) return 0;      // periodic images already stored by the kernel
+    return exchange(h, {{s.zn, 1}, {s.un, 1}, {s.vn, 1}});
+  }
   PLANE(k_step2d_zeta, p.iend, (p.swall ? p.jstrR : p.jstr - 1), p.jendR, 1, p, s);
   PLANE(k_step2d_uv, p.iend, p.jstr, p.jend, 1, p, s);
   if (WALLED(h)) {

@@ -27,7 +27,8 @@ FID = {n: i for i, n in enumerate(FIELDS)}
 
 
 def lib_path():
-    return os.path.join(PKG, "libromsb200.so")
+    # ROMS_B200_LIB: developer hook to A/B a differently tuned build of the same library
+    return os.environ.get("ROMS_B200_LIB") or os.path.join(PKG, "libromsb200.so")
 
 
 def load_library():
