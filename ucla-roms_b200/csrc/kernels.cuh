@@ -20,6 +20,9 @@
 #ifndef LB_RHS
 #define LB_RHS 4
 #endif
+#ifndef LB_T
+#define LB_T 8
+#endif
 #ifndef LB_S2D
 #define LB_S2D 4
 #endif
@@ -177,6 +180,9 @@ __global__ void k_set_huv1(const __grid_constant__ KP p, double* __restrict__ u,
 
 // omega.F:17-236 omega_tile.  Column kernel: up-sweep integrates continuity, down-sweep removes the
 // grid motion and splits W into explicit We and implicit Wi by the local Courant number.
+#ifndef KCO
+#define KCO 4
+#endif
 __global__ void k_omega(const __grid_constant__ KP p, double dtau) {
   extern __shared__ double smem[];
   THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
@@ -185,41 +191,65 @@ __global__ void k_omega(const __grid_constant__ KP p, double dtau) {
   const double cu_min = 0.6, cu_max = 1.0, cmnx_ratio = cu_min / cu_max, cutoff = 2.0 - cmnx_ratio, r4cmx = 0.25 / (1.0 - cmnx_ratio);
   double W = 0.0;
   RW(p.Wi, c, 0) = 0.0;
-  for (int k = 1; k <= N; ++k) {
-    const double fu1 = R3(p.FlxU, c + 1, k), fu0 = R3(p.FlxU, c, k), fv1 = R3(p.FlxV, c + SX, k), fv0 = R3(p.FlxV, c, k);
-    W = W - fu1 + fu0 - fv1 + fv0;
-    S(0, k) = DMAX(fu1, 0.0) - DMIN(fu0, 0.0) + DMAX(fv1, 0.0) - DMIN(fv0, 0.0);
-    S(1, k) = W;
+  const double* __restrict__ gFu = p.FlxU;
+  const double* __restrict__ gFv = p.FlxV;
+  const double* __restrict__ gzw = p.z_w;
+  const double* __restrict__ gHz = p.Hz;
+  for (int k0 = 1; k0 <= N; k0 += KCO) {        // chunked: all loads of KCO levels are issued before the recurrence
+    double a1[KCO], a0[KCO], b1[KCO], b0[KCO];
+#pragma unroll
+    for (int q = 0; q < KCO; ++q)
+      if (k0 + q <= N) { a1[q] = R3(gFu, c + 1, k0 + q); a0[q] = R3(gFu, c, k0 + q); b1[q] = R3(gFv, c + SX, k0 + q); b0[q] = R3(gFv, c, k0 + q); }
+#pragma unroll
+    for (int q = 0; q < KCO; ++q) {
+      const int k = k0 + q;
+      if (k <= N) {
+        const double fu1 = a1[q], fu0 = a0[q], fv1 = b1[q], fv0 = b0[q];
+        W = W - fu1 + fu0 - fv1 + fv0;
+        S(0, k) = DMAX(fu1, 0.0) - DMIN(fu0, 0.0) + DMAX(fv1, 0.0) - DMIN(fv0, 0.0);
+        S(1, k) = W;
+      }
+    }
   }
   W = W + p.swflx[c] * p.dm_r[c] * p.dn_r[c];
-  const double zw0 = RW(p.z_w, c, 0);
-  const double wrk = W / (RW(p.z_w, c, N) - zw0);
+  const double zw0 = RW(gzw, c, 0);
+  const double wrk = W / (RW(gzw, c, N) - zw0);
   RW(p.Wi, c, N) = 0.0;
   RW(p.We, c, N) = 0.0;
   RW(p.We, c, 0) = 0.0;
   const double CX0 = dtau * p.pm[c] * p.pn[c];
-  double CXkp = S(0, N), Hzkp = R3(p.Hz, c, N);
-  for (int k = N - 1; k >= 1; --k) {
-    double Wik = S(1, k) - wrk * (RW(p.z_w, c, k) - zw0);
-    const double CXk = S(0, k), Hzk = R3(p.Hz, c, k);
-    const double c2d = DMAX(CXk, CXkp);
-    const double dh = DMIN(Hzk, Hzkp);
-    const double cw_max = cu_max * dh - c2d * CX0;
-    double Wek;
-    if (cw_max > 0.0) {
-      const double cw_max2 = cw_max * cw_max;
-      const double cw_min = cw_max * cmnx_ratio;
-      const double cw = fabs(Wik) * CX0;
-      double cff;
-      if (cw < cw_min) cff = cw_max2;
-      else if (cw < cutoff * cw_max) cff = cw_max2 + r4cmx * ((cw - cw_min) * (cw - cw_min));
-      else cff = cw_max * cw;
-      Wek = cw_max2 * Wik / cff;
-      Wik = Wik - Wek;
-    } else Wek = 0.0;
-    RW(p.We, c, k) = Wek;
-    RW(p.Wi, c, k) = Wik;
-    CXkp = CXk; Hzkp = Hzk;
+  double CXkp = S(0, N), Hzkp = R3(gHz, c, N);
+  for (int k0 = N - 1; k0 >= 1; k0 -= KCO) {
+    double sw[KCO], sx[KCO], zw[KCO], hz[KCO];
+#pragma unroll
+    for (int q = 0; q < KCO; ++q)
+      if (k0 - q >= 1) { sw[q] = S(1, k0 - q); sx[q] = S(0, k0 - q); zw[q] = RW(gzw, c, k0 - q); hz[q] = R3(gHz, c, k0 - q); }
+#pragma unroll
+    for (int q = 0; q < KCO; ++q) {
+      const int k = k0 - q;
+      if (k >= 1) {
+        double Wik = sw[q] - wrk * (zw[q] - zw0);
+        const double CXk = sx[q], Hzk = hz[q];
+        const double c2d = DMAX(CXk, CXkp);
+        const double dh = DMIN(Hzk, Hzkp);
+        const double cw_max = cu_max * dh - c2d * CX0;
+        double Wek;
+        if (cw_max > 0.0) {
+          const double cw_max2 = cw_max * cw_max;
+          const double cw_min = cw_max * cmnx_ratio;
+          const double cw = fabs(Wik) * CX0;
+          double cff;
+          if (cw < cw_min) cff = cw_max2;
+          else if (cw < cutoff * cw_max) cff = cw_max2 + r4cmx * ((cw - cw_min) * (cw - cw_min));
+          else cff = cw_max * cw;
+          Wek = cw_max2 * Wik / cff;
+          Wik = Wik - Wek;
+        } else Wek = 0.0;
+        RW(p.We, c, k) = Wek;
+        RW(p.Wi, c, k) = Wik;
+        CXkp = CXk; Hzkp = Hzk;
+      }
+    }
   }
 }
 
@@ -609,7 +639,7 @@ __global__ void k_pre_flxdiv(const __grid_constant__ KP p, double dtau) {
     FEjp = tflux<UP, false>(p, t_rhs, p.FlxV, p.vmask, c + SX, SX, k);                                                             \
   }
 template <bool WALL>
-__global__ void k_pre_t_horiz(const __grid_constant__ KP p, const double* __restrict__ t_rhs, double* __restrict__ t_new, const double* __restrict__ t_stp,
+__global__ void __launch_bounds__(256, LB_T) k_pre_t_horiz(const __grid_constant__ KP p, const double* __restrict__ t_rhs, double* __restrict__ t_new, const double* __restrict__ t_stp,
                               double* __restrict__ t_indx, double dtau, double cf_stp, double cf_bak) {
   THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
   const int k = blockIdx.z + 1;
@@ -622,7 +652,7 @@ __global__ void k_pre_t_horiz(const __grid_constant__ KP p, const double* __rest
 }
 // step3d_t_ISO.F:196-213: tracer corrector, horizontal part (UP3)
 template <bool WALL>
-__global__ void k_t_horiz(const __grid_constant__ KP p, const double* __restrict__ t_rhs, double* __restrict__ t_new) {
+__global__ void __launch_bounds__(256, LB_T) k_t_horiz(const __grid_constant__ KP p, const double* __restrict__ t_rhs, double* __restrict__ t_new) {
   THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
   const int k = blockIdx.z + 1;
   const double FXi = tflux<true, false>(p, t_rhs, p.FlxU, p.umask, c, 1, k), FXip = tflux<true, false>(p, t_rhs, p.FlxU, p.umask, c + 1, 1, k);
