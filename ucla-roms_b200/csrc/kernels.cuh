@@ -31,15 +31,15 @@
 
 struct ColScr {
   double* b;
-  long ks, as;
+  ix_t ks, as;
 };
-__device__ __forceinline__ ColScr col_scratch(const KP& p, long c, double* smem) {
+__device__ __forceinline__ ColScr col_scratch(const KP& p, ix_t c, double* smem) {
   ColScr s;
   if (p.use_smem) {
     const int nth = blockDim.x * blockDim.y;
     s.b = smem + threadIdx.y * blockDim.x + threadIdx.x;
     s.ks = nth;
-    s.as = (long)nth * (p.N + 1);
+    s.as = (ix_t)nth * (p.N + 1);
   } else {
     s.b = p.scr + c;
     s.ks = p.SXY;
@@ -47,25 +47,41 @@ __device__ __forceinline__ ColScr col_scratch(const KP& p, long c, double* smem)
   }
   return s;
 }
-#define S(n, k) sc.b[(long)(n)*sc.as + (long)(k)*sc.ks]
+#define S(n, k) sc.b[(ix_t)(n)*sc.as + (ix_t)(k)*sc.ks]
 
-#define THREAD_IJ(i0, i1, j0, j1)                                   \
+// Element-index width per kernel group, chosen by measurement on B200 (profiles/r1_tuning_log.txt): 32-bit indices
+// cut the integer address arithmetic of the column and pressure-gradient kernels, while the momentum-RHS, barotropic
+// and uv2/set_HUV1 kernels schedule their loads better with 64-bit indices.
+#ifndef IXR_T
+#define IXR_T long
+#endif
+#ifndef IX2_T
+#define IX2_T long
+#endif
+#ifndef IXC_T
+#define IXC_T long
+#endif
+typedef IXR_T ixr_t;
+typedef IX2_T ix2_t;
+typedef IXC_T ixc_t;
+#define THREAD_IJT(T, i0, i1, j0, j1)                               \
   const int i = blockIdx.x * blockDim.x + threadIdx.x - IOFF;       \
   const int j = (j0) + blockIdx.y * blockDim.y + threadIdx.y;       \
   if (i < (i0) || i > (i1) || j > (j1)) return;                     \
-  const long c = CIDX(i, j);                                        \
-  const long SX = p.SX; (void)SX;
+  const T c = CIDX(i, j);                                           \
+  const T SX = p.SX; (void)SX;
+#define THREAD_IJ(i0, i1, j0, j1) THREAD_IJT(ix_t, i0, i1, j0, j1)
 
 // Closed N/S walls: the reference extends its one-dimensional difference arrays across a wall by copying
 // the nearest computed row (e.g. "wrk1(i,jstr-1)=wrk1(i,jstr)", compute_horiz_rhs_uv_terms.h:110-140,
 // "FE(i,jstr-1)=FE(i,jstr)", compute_horiz_tracer_fluxes.h:150-160, "FC(i,jmin-1)=FC(i,jmin)", prsgrd.F:300).
 // Kernels that recompute those differences in registers evaluate them at the clamped row instead:
 // element offset that moves row j to clamp(j, lo, hi); lo/hi only bind on a wall.
-__device__ __forceinline__ long jclamp(const KP& p, int j, int lo_wall, int hi_wall) {
+__device__ __forceinline__ ix_t jclamp(const KP& p, int j, int lo_wall, int hi_wall) {
   int jc = j;
   if (p.swall && jc < lo_wall) jc = lo_wall;
   if (p.nwall && jc > hi_wall) jc = hi_wall;
-  return (long)(jc - j) * p.SX;
+  return (ix_t)(jc - j) * p.SX;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -100,10 +116,10 @@ __global__ void k_halo_periodic(const __grid_constant__ KP p, const __grid_const
   const int jlo = p.swall ? 0 : 1, jhi = p.nwall ? Mm + 1 : Mm;
   if ((is < 1 || is > Lm) || (js < jlo || js > jhi)) return;   // non-periodic edge: untouched
   if (is == i && js == j) return;
-  const long cd = CIDX(i, j), cs = CIDX(is, js);
+  const ix_t cd = CIDX(i, j), cs = CIDX(is, js);
   const int f = blockIdx.y;
   double* a = hl.a[f];
-  for (int k = blockIdx.z; k < hl.nk[f]; k += gridDim.z) a[cd + (long)k * p.SXY] = a[cs + (long)k * p.SXY];
+  for (int k = blockIdx.z; k < hl.nk[f]; k += gridDim.z) a[cd + (ix_t)k * p.SXY] = a[cs + (ix_t)k * p.SXY];
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -151,8 +167,8 @@ __global__ void k_set_huv(const __grid_constant__ KP p, const double* __restrict
 // set_depth.F:252-422 set_HUV1_tile.  DIR 0: u/FlxU, 1: v/FlxV.  Column kernel, two sweeps, no scratch.
 template <int DIR>
 __global__ void k_set_huv1(const __grid_constant__ KP p, double* __restrict__ u, int first) {
-  THREAD_IJ(p.istr, p.iend, (DIR == 0 ? p.jstrR : p.jstr), p.jendR)
-  const long d = DIR == 0 ? 1 : SX;
+  THREAD_IJT(ixc_t, p.istr, p.iend, (DIR == 0 ? p.jstrR : p.jstr), p.jendR)
+  const ixc_t d = DIR == 0 ? 1 : SX;
   const double dn = DIR == 0 ? p.dn_u[c] : p.dm_v[c];
   const double msk = DIR == 0 ? p.umask[c] : p.vmask[c];
   double* Flx = DIR == 0 ? p.FlxU : p.FlxV;
@@ -365,7 +381,7 @@ __global__ void k_prsgrd_vert(const __grid_constant__ KP p) {
 // prsgrd.F:231-421: horizontal part, plane kernel.  ru, rv at (i,j,k) from the density-Jacobian with
 // harmonic-mean reconstruction of the horizontal differences.
 template <bool NONLIN>
-__device__ __forceinline__ void prs_fc_rx(const KP& p, long X, long d, int k, const double* __restrict__ msk, const double* __restrict__ rho,
+__device__ __forceinline__ void prs_fc_rx(const KP& p, ix_t X, ix_t d, int k, const double* __restrict__ msk, const double* __restrict__ rho,
                                           double& FC, double& rx) {
   const double qp2 = 0.0000172;
   const double zu = R3(p.z_r, X, k), zl = R3(p.z_r, X - d, k), m = msk[X];
@@ -377,8 +393,8 @@ __device__ __forceinline__ void prs_fc_rx(const KP& p, long X, long d, int k, co
 }
 // CL: the three difference positions (c-d, c, c+d) are displaced by oA, oB, oC (wall clamping, see jclamp)
 template <bool NONLIN, bool CL>
-__device__ __forceinline__ double prs_dir(const KP& p, long c, long d, int k, const double* __restrict__ msk, double dn, const double* __restrict__ rho,
-                                          long oA = 0, long oB = 0, long oC = 0) {
+__device__ __forceinline__ double prs_dir(const KP& p, ix_t c, ix_t d, int k, const double* __restrict__ msk, double dn, const double* __restrict__ rho,
+                                          ix_t oA = 0, ix_t oB = 0, ix_t oC = 0) {
   const double qp2 = 0.0000172, OneFifth = 0.2, OneTwelfth = 1.0 / 12.0, epsil = 0.0;
   const double HalfGRho = 0.5 * (p.g / p.rho0);
   // points c-2d, c-d, c, c+d
@@ -431,16 +447,16 @@ __global__ void __launch_bounds__(256, LB_PRS) k_prsgrd_horiz(const __grid_const
   const int i = blockIdx.x * blockDim.x + threadIdx.x - IOFF;
   const int jb = p.jstr + (blockIdx.y * blockDim.y + threadIdx.y) * JB;
   if (i < p.istr || i > p.iend || jb > p.jend) return;
-  const long SX = p.SX;
+  const ix_t SX = p.SX;
   const int k = blockIdx.z + 1;
   const double* __restrict__ rho = NONLIN ? p.rho : p.rho1;
   const bool near = WALL && ((p.swall && jb <= p.jstr + 2) || (p.nwall && jb + JB - 1 >= p.jend - 2));
-  const long c0 = CIDX(i, jb);
+  const ix_t c0 = CIDX(i, jb);
   if (near || jb + JB - 1 > p.jend) {   // rows next to a wall / ragged last block: one row at a time
 #pragma unroll 1
     for (int q = 0; q < JB && jb + q <= p.jend; ++q) {
       const int j = jb + q;
-      const long c = c0 + q * SX;
+      const ix_t c = c0 + q * SX;
       R3(p.ru, c, k) = prs_dir<NONLIN, false>(p, c, 1, k, p.umask, p.dn_u[c], rho);
       if (!WALL) R3(p.rv, c, k) = prs_dir<NONLIN, false>(p, c, SX, k, p.vmask, p.dm_v[c], rho);
       else if (j >= p.jstrV)   // prsgrd.F:288-310: FC,rx exist on rows jstrV..jend between walls, copied one row outward
@@ -452,7 +468,7 @@ __global__ void __launch_bounds__(256, LB_PRS) k_prsgrd_horiz(const __grid_const
   double ru[JB], rv[JB];
 #pragma unroll
   for (int q = 0; q < JB; ++q) {
-    const long c = c0 + q * SX;
+    const ix_t c = c0 + q * SX;
     ru[q] = prs_dir<NONLIN, false>(p, c, 1, k, p.umask, p.dn_u[c], rho);
     rv[q] = prs_dir<NONLIN, false>(p, c, SX, k, p.vmask, p.dm_v[c], rho);
   }
@@ -470,13 +486,13 @@ __global__ void __launch_bounds__(256, LB_PRS) k_prsgrd_horiz(const __grid_const
 #define HGAMMA 0.3333333333333333
 // along-axis flux of the along-axis velocity: UFx (d=1,u,FlxU) / VFe (d=SX,v,FlxV) at rho point c
 template <bool UP, bool CL>
-__device__ __forceinline__ double flux_along(const KP& p, const double* __restrict__ u, const double* __restrict__ Flx, long c, long d, int k,
-                                             long oa = 0, long ob = 0) {
+__device__ __forceinline__ double flux_along(const KP& p, const double* __restrict__ u, const double* __restrict__ Flx, ixr_t c, ixr_t d, int k,
+                                             ixr_t oa = 0, ixr_t ob = 0) {
   const double u0 = R3(u, c, k), u1 = R3(u, c + d, k);
   const double f0 = R3(Flx, c, k), f1 = R3(Flx, c + d, k);
   double w1a, w1b, w2a, w2b;     // wrk1(c), wrk1(c+d), wrk2(c), wrk2(c+d)
   if (CL) {                      // second differences taken at the wall-clamped rows c+oa, c+d+ob
-    const long ca = c + oa, cb = c + d + ob;
+    const ixr_t ca = c + oa, cb = c + d + ob;
     w1a = R3(u, ca - d, k) - 2.0 * R3(u, ca, k) + R3(u, ca + d, k);
     w1b = R3(u, cb - d, k) - 2.0 * R3(u, cb, k) + R3(u, cb + d, k);
     w2a = R3(Flx, ca - d, k) - 2.0 * R3(Flx, ca, k) + R3(Flx, ca + d, k);
@@ -495,13 +511,13 @@ __device__ __forceinline__ double flux_along(const KP& p, const double* __restri
 }
 // cross-axis flux at psi point c: UFe (u advected by FlxV: du=SX, df=1) / VFx (v advected by FlxU: du=1, df=SX)
 template <bool UP, bool CL>
-__device__ __forceinline__ double flux_cross(const KP& p, const double* __restrict__ u, const double* __restrict__ Flx, long c, long du, long df, int k,
-                                             long om = 0, long oc = 0) {
+__device__ __forceinline__ double flux_cross(const KP& p, const double* __restrict__ u, const double* __restrict__ Flx, ixr_t c, ixr_t du, ixr_t df, int k,
+                                             ixr_t om = 0, ixr_t oc = 0) {
   // u second differences along du at c and c-du; Flx second differences along df at c and c-df
   const double ub = R3(u, c - du, k), uc = R3(u, c, k);
   double w1m, w1c;     // wrk1(c-du), wrk1(c)
   if (CL) {
-    const long cm = c - du + om, cc = c + oc;
+    const ixr_t cm = c - du + om, cc = c + oc;
     w1m = R3(u, cm - du, k) - 2.0 * R3(u, cm, k) + R3(u, cm + du, k);
     w1c = R3(u, cc - du, k) - 2.0 * R3(u, cc, k) + R3(u, cc + du, k);
   } else {
@@ -518,9 +534,9 @@ __device__ __forceinline__ double flux_cross(const KP& p, const double* __restri
 }
 // one (i,j,k) point of the horizontal momentum RHS; NEAR: a row within two rows of a closed wall (clamped differences)
 template <bool UP, bool NEAR>
-__device__ __forceinline__ void rhs_uv_point(const KP& p, const double* __restrict__ u, const double* __restrict__ v, long c, int j, int k, bool dov,
+__device__ __forceinline__ void rhs_uv_point(const KP& p, const double* __restrict__ u, const double* __restrict__ v, ixr_t c, int j, int k, bool dov,
                                              double& ru, double& rv) {
-  const long SX = p.SX;
+  const ixr_t SX = p.SX;
   // Coriolis (no CURVGRID): compute_horiz_rhs_uv_terms.h:4-45
   const double cf0 = 0.5 * R3(p.Hz, c, k) * (p.fomn[c]);
   const double cfw = 0.5 * R3(p.Hz, c - 1, k) * (p.fomn[c - 1]);
@@ -566,12 +582,12 @@ __global__ void __launch_bounds__(256, (JB >= 4 ? 2 : LB_RHS)) k_rhs_uv_horiz(co
   if (i < p.istr || i > p.iend || jb > p.jend) return;
   const int k = blockIdx.z + 1;
   const bool near = WALL && ((p.swall && jb <= p.jstr + 2) || (p.nwall && jb + JB - 1 >= p.jend - 2));
-  const long c0 = CIDX(i, jb), SX = p.SX;
+  const ixr_t c0 = CIDX(i, jb), SX = p.SX;
   if (near || jb + JB - 1 > p.jend) {   // rows next to a wall / ragged last block: one row at a time
 #pragma unroll 1
     for (int q = 0; q < JB && jb + q <= p.jend; ++q) {
       const int j = jb + q;
-      const long c = c0 + q * SX;
+      const ixr_t c = c0 + q * SX;
       const bool dov = !WALL || j >= p.jstrV;
       double ru, rv;
       if (WALL) rhs_uv_point<UP, true>(p, u, v, c, j, k, dov, ru, rv);
@@ -593,12 +609,12 @@ __global__ void __launch_bounds__(256, (JB >= 4 ? 2 : LB_RHS)) k_rhs_uv_horiz(co
 
 // compute_horiz_tracer_fluxes.h:1-246: FX at u-point c (d=1, FlxU, umask) or FE at v-point c (d=SX)
 template <bool UP, bool CL>
-__device__ __forceinline__ double tflux(const KP& p, const double* __restrict__ t, const double* __restrict__ Flx, const double* __restrict__ msk, long c, long d, int k,
-                                        long oA = 0, long oB = 0, long oC = 0) {
+__device__ __forceinline__ double tflux(const KP& p, const double* __restrict__ t, const double* __restrict__ Flx, const double* __restrict__ msk, ix_t c, ix_t d, int k,
+                                        ix_t oA = 0, ix_t oB = 0, ix_t oC = 0) {
   const double t1 = R3(t, c - d, k), t2 = R3(t, c, k);
   double Fa, Fb, Fc;   // FX(c-d), FX(c), FX(c+d)
   if (CL) {            // first differences taken at the wall-clamped rows
-    const long XA = c - d + oA, XB = c + oB, XC = c + d + oC;
+    const ix_t XA = c - d + oA, XB = c + oB, XC = c + d + oC;
     Fa = (R3(t, XA, k) - R3(t, XA - d, k)) * msk[XA];
     Fb = (R3(t, XB, k) - R3(t, XB - d, k)) * msk[XB];
     Fc = (R3(t, XC, k) - R3(t, XC - d, k)) * msk[XC];
@@ -824,7 +840,7 @@ k_uv_vert(const __grid_constant__ KP p, const double* __restrict__ u_rhs, double
   THREAD_IJ(p.istr, p.iend, (DIR == 0 ? p.jstr : p.jstrV), p.jend)
   ColScr sc = col_scratch(p, c, smem);
   const int N = p.N;
-  const long d = DIR == 0 ? 1 : SX;
+  const ix_t d = DIR == 0 ? 1 : SX;
   double* __restrict__ r = DIR == 0 ? p.ru : p.rv;
   const double* msk = DIR == 0 ? p.umask : p.vmask;
   const double strs = DIR == 0 ? p.sustr[c] : p.svstr[c];
@@ -988,16 +1004,16 @@ struct S2D {
   double fwd, fwd1, fwd2, bkw_new, bkw, bkw1, bkw2, w1, w2;
   int iif, nfast;
 };
-__device__ __forceinline__ double s2d_Drhs(const KP& p, const S2D& s, long c) { return p.h[c] + s.fwd * s.zs[c] + s.fwd1 * s.zb[c] + s.fwd2 * s.zo[c]; }
-__device__ __forceinline__ double s2d_DUon(const KP& p, const S2D& s, long c) {
+__device__ __forceinline__ double s2d_Drhs(const KP& p, const S2D& s, ix2_t c) { return p.h[c] + s.fwd * s.zs[c] + s.fwd1 * s.zb[c] + s.fwd2 * s.zo[c]; }
+__device__ __forceinline__ double s2d_DUon(const KP& p, const S2D& s, ix2_t c) {
   const double urhs = s.fwd * s.us[c] + s.fwd1 * s.ub[c] + s.fwd2 * s.uo[c];
   return 0.5 * (s2d_Drhs(p, s, c) + s2d_Drhs(p, s, c - 1)) * p.dn_u[c] * (urhs);
 }
-__device__ __forceinline__ double s2d_DVom(const KP& p, const S2D& s, long c) {
+__device__ __forceinline__ double s2d_DVom(const KP& p, const S2D& s, ix2_t c) {
   const double vrhs = s.fwd * s.vs[c] + s.fwd1 * s.vb[c] + s.fwd2 * s.vo[c];
   return 0.5 * (s2d_Drhs(p, s, c) + s2d_Drhs(p, s, c - p.SX)) * p.dm_v[c] * (vrhs);
 }
-__device__ __forceinline__ double s2d_zeta_new(const KP& p, const S2D& s, long c) {
+__device__ __forceinline__ double s2d_zeta_new(const KP& p, const S2D& s, ix2_t c) {
   const double DUon = s2d_DUon(p, s, c), DUon1 = s2d_DUon(p, s, c + 1), DVom = s2d_DVom(p, s, c), DVom1 = s2d_DVom(p, s, c + p.SX);
   double zn = s.zs[c] + p.dtfast * p.pm[c] * p.pn[c] * (DUon - DUon1 + DVom - DVom1) + p.dtfast * p.swflx[c];
   return zn * p.rmask[c];
@@ -1005,7 +1021,7 @@ __device__ __forceinline__ double s2d_zeta_new(const KP& p, const S2D& s, long c
 // rows jstrV-1..jend carry the continuity update; a row just outside a closed wall takes zetabc's gradient
 // condition (zetabc.F:3: zeta_new(i,jstr-1)=zeta_new(i,jstr)*rmask(i,jstr-1)), re-evaluating its neighbour's update.
 __global__ void __launch_bounds__(256, LB_S2D) k_step2d_zeta(const __grid_constant__ KP p, const __grid_constant__ S2D s) {
-  THREAD_IJ(p.istr - 1, p.iend, (p.swall ? p.jstrR : p.jstr - 1), p.jendR)
+  THREAD_IJT(ix2_t, p.istr - 1, p.iend, (p.swall ? p.jstrR : p.jstr - 1), p.jendR)
   double zn;
   if (p.swall && j < p.jstr) zn = s2d_zeta_new(p, s, c + SX) * p.rmask[c];
   else if (p.nwall && j > p.jend) zn = s2d_zeta_new(p, s, c - SX) * p.rmask[c];
@@ -1033,7 +1049,7 @@ __global__ void __launch_bounds__(256, LB_S2D) k_step2d_zeta(const __grid_consta
 // stage 2: pressure-gradient terms rubar,rvbar (step2d_FB.F:245-268, first-substep correction :313-384),
 // ubar,vbar(knew), DU_avg1/DV_avg1; on the last substep zeta(knew)=Zt_avg1 (:563).
 struct S2Pt { double UFx, UFe, VFx, VFe; };
-__device__ __forceinline__ S2Pt s2d_pt(const KP& p, const S2D& s, long c, bool corr, bool valid = true) {
+__device__ __forceinline__ S2Pt s2d_pt(const KP& p, const S2D& s, ix2_t c, bool corr, bool valid = true) {
   S2Pt r;
   if (!valid) { r.UFx = r.UFe = r.VFx = r.VFe = 0.0; return r; }   // row below a southern wall: zero-initialised scratch in the reference
   const double zn = p.zeta_new[c], zs = s.zs[c];
@@ -1050,14 +1066,14 @@ __device__ __forceinline__ S2Pt s2d_pt(const KP& p, const S2D& s, long c, bool c
   }
   return r;
 }
-__device__ __forceinline__ double s2d_pgf(const KP& p, double cff, double dn, long c, long d, const S2Pt& a, const S2Pt& b) {
+__device__ __forceinline__ double s2d_pgf(const KP& p, double cff, double dn, ix2_t c, ix2_t d, const S2Pt& a, const S2Pt& b) {
   // a at c-d, b at c
   return cff * dn *
          ((p.h[c - d] + p.h[c]) * (a.UFe - b.UFe) + a.VFe - b.VFe +
           (p.h[c - d] - p.h[c]) * (a.VFx + b.VFx + 0.333333333333 * (p.rhoA[c - d] - p.rhoA[c]) * (a.UFx - b.UFx)));
 }
 __global__ void __launch_bounds__(256, LB_S2D) k_step2d_uv(const __grid_constant__ KP p, const __grid_constant__ S2D s) {
-  THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
+  THREAD_IJT(ix2_t, p.istr, p.iend, p.jstr, p.jend)
   const double cffg = 0.5 * p.g;
   const bool sv = (j - 1 >= p.jstrV - 1);     // row j-1 carries a zeta_new
   const bool dov = (j >= p.jstrV);
@@ -1095,12 +1111,12 @@ __global__ void __launch_bounds__(256, LB_S2D) k_step2d_uv(const __grid_constant
 // subdomain the results are stored to their periodic images as well, so no exchange launch follows.
 #define S2_TX 32
 #define S2_TY 8
-__device__ __forceinline__ double s2d_zn_at(const KP& p, const S2D& s, long c, int j) {
+__device__ __forceinline__ double s2d_zn_at(const KP& p, const S2D& s, ix2_t c, int j) {
   if (p.swall && j < p.jstr) return s2d_zeta_new(p, s, c + p.SX) * p.rmask[c];
   if (p.nwall && j > p.jend) return s2d_zeta_new(p, s, c - p.SX) * p.rmask[c];
   return s2d_zeta_new(p, s, c);
 }
-__device__ __forceinline__ S2Pt s2d_ptz(const KP& p, const S2D& s, long c, double zn, bool corr) {
+__device__ __forceinline__ S2Pt s2d_ptz(const KP& p, const S2D& s, ix2_t c, double zn, bool corr) {
   S2Pt r;
   const double zs = s.zs[c];
   if (!corr) {
@@ -1117,18 +1133,18 @@ __device__ __forceinline__ S2Pt s2d_ptz(const KP& p, const S2D& s, long c, doubl
   return r;
 }
 // store to (i,j) and, on a single periodic subdomain, to its images in the halo (mpi_setup.F:231-250 wrap)
-__device__ __forceinline__ void s2d_store(const KP& p, double* __restrict__ a, int i, int j, long c, double v) {
+__device__ __forceinline__ void s2d_store(const KP& p, double* __restrict__ a, int i, int j, ix2_t c, double v) {
   a[c] = v;
   if (p.wrap_x | p.wrap_y) {
-    const long ox = !p.wrap_x ? 0 : (i <= 2 ? (long)p.Lm : (i >= p.Lm - 1 ? -(long)p.Lm : 0));
-    const long oy = !p.wrap_y ? 0 : (j <= 2 ? (long)p.Mm * p.SX : (j >= p.Mm - 1 ? -(long)p.Mm * p.SX : 0));
+    const ix2_t ox = !p.wrap_x ? 0 : (i <= 2 ? (ix2_t)p.Lm : (i >= p.Lm - 1 ? -(ix2_t)p.Lm : 0));
+    const ix2_t oy = !p.wrap_y ? 0 : (j <= 2 ? (ix2_t)p.Mm * p.SX : (j >= p.Mm - 1 ? -(ix2_t)p.Mm * p.SX : 0));
     if (ox) a[c + ox] = v;
     if (oy) a[c + oy] = v;
     if (ox && oy) a[c + ox + oy] = v;
   }
 }
 // zeta(knew), Zt_avg1, DU_avg2, DV_avg2 (and the first-substep resets) at one point; returns the running DU_avg1/DV_avg1
-__device__ __forceinline__ void s2d_avg_out(const KP& p, const S2D& s, int i, int j, long c, double zn, double DUon, double DVom, double& DU1, double& DV1,
+__device__ __forceinline__ void s2d_avg_out(const KP& p, const S2D& s, int i, int j, ix2_t c, double zn, double DUon, double DVom, double& DU1, double& DV1,
                                             double& Zt) {
   s2d_store(p, s.zn, i, j, c, zn);
   if (s.iif == 1) {
@@ -1153,7 +1169,7 @@ __global__ void __launch_bounds__(S2_TX * S2_TY, LB_S2D) k_step2d(const __grid_c
   const int tx = threadIdx.x, ty = threadIdx.y;
   const int i0 = blockIdx.x * S2_TX - IOFF, j0 = p.jstr + blockIdx.y * S2_TY;
   const int i = i0 + tx, j = j0 + ty;
-  const long SX = p.SX;
+  const ix2_t SX = p.SX;
   // ---- phase 1: zeta_new (step2d_FB.F:151-216) on the tile, the row below it and the column to its left
   if (i >= p.istr - 1 && i <= p.iend && j <= p.jend) zt[ty + 1][tx + 1] = s2d_zeta_new(p, s, CIDX(i, j));
   {
@@ -1169,7 +1185,7 @@ __global__ void __launch_bounds__(S2_TX * S2_TY, LB_S2D) k_step2d(const __grid_c
   __syncthreads();
   if (i < p.istr || i > p.iend || j > p.jend) return;
   // ---- phase 2: own point
-  const long c = CIDX(i, j);
+  const ix2_t c = CIDX(i, j);
   const double zn = zt[ty + 1][tx + 1], znw = zt[ty + 1][tx], zns = zt[ty][tx + 1];
   double DU1, DV1, Zt;
   s2d_avg_out(p, s, i, j, c, zn, s2d_DUon(p, s, c), s2d_DVom(p, s, c), DU1, DV1, Zt);
@@ -1214,7 +1230,7 @@ __global__ void __launch_bounds__(S2_TX * S2_TY, LB_S2D) k_step2d(const __grid_c
     for (int side = 0; side < 2; ++side) {
       if (side == 0 ? !sw : !nw) continue;
       const int jw = side == 0 ? j - 1 : j + 1;
-      const long w = side == 0 ? c - SX : c + SX;
+      const ix2_t w = side == 0 ? c - SX : c + SX;
       // zetabc.F:3: gradient condition; the neighbour in -i likewise (needed for D at the u-point)
       const double znb = side == 0 ? zns : zn * p.rmask[w];
       const double znbw = side == 0 ? zt[ty][tx] : znw * p.rmask[w - 1];
@@ -1238,10 +1254,10 @@ __global__ void __launch_bounds__(S2_TX * S2_TY, LB_S2D) k_step2d(const __grid_c
 __global__ void k_step2d_bc(const __grid_constant__ KP p, const __grid_constant__ S2D s) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x - IOFF;
   if (i < p.istr || i > p.iend) return;
-  const long SX = p.SX;
+  const ix2_t SX = p.SX;
   const double cff1 = 0.5 * s.w1;
   if (p.swall) {
-    const long c = CIDX(i, p.jstr - 1), cv = CIDX(i, p.jstrV - 1);
+    const ix2_t c = CIDX(i, p.jstr - 1), cv = CIDX(i, p.jstrV - 1);
     s.un[c] = p.gamma2 * s.un[c + SX] * p.umask[c];
     s.vn[cv] = 0.0;
     const double Dn = p.h[c] + p.zeta_new[c], Dnw = p.h[c - 1] + p.zeta_new[c - 1];
@@ -1251,7 +1267,7 @@ __global__ void k_step2d_bc(const __grid_constant__ KP p, const __grid_constant_
     if (s.iif == s.nfast) s.zn[c] = p.Zt_avg1[c];
   }
   if (p.nwall) {
-    const long c = CIDX(i, p.jend + 1);
+    const ix2_t c = CIDX(i, p.jend + 1);
     s.un[c] = p.gamma2 * s.un[c - SX] * p.umask[c];
     s.vn[c] = 0.0;
     const double Dn = p.h[c] + p.zeta_new[c], Dnw = p.h[c - 1] + p.zeta_new[c - 1], Ds = p.zeta_new[c - SX] + p.h[c - SX];
@@ -1266,18 +1282,18 @@ template <bool ZERO>
 __global__ void k_bc_rows(const __grid_constant__ KP p, double* __restrict__ a, double factor, const double* __restrict__ msk) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x - IOFF;
   if (i < p.istr || i > p.iend) return;
-  const long SX = p.SX, ko = (long)blockIdx.z * p.SXY;
+  const ix_t SX = p.SX, ko = (ix_t)blockIdx.z * p.SXY;
   if (p.swall) {
     if (ZERO) a[CIDX(i, p.jstr) + ko] = 0.0;
     else {
-      const long c = CIDX(i, p.jstr - 1);
+      const ix_t c = CIDX(i, p.jstr - 1);
       double v = factor * a[c + SX + ko];
       if (msk) v = v * msk[c];
       a[c + ko] = v;
     }
   }
   if (p.nwall) {
-    const long c = CIDX(i, p.jend + 1);
+    const ix_t c = CIDX(i, p.jend + 1);
     if (ZERO) a[c + ko] = 0.0;
     else {
       double v = factor * a[c - SX + ko];
@@ -1293,8 +1309,8 @@ __global__ void k_bc_rows(const __grid_constant__ KP p, double* __restrict__ a, 
 // minus its mismatch with DU_avg2.  Column kernels without scratch (re-read through L1/L2).
 template <int DIR>
 __global__ void k_uv2_pass0(const __grid_constant__ KP p, double* __restrict__ u) {
-  THREAD_IJ(p.istr, p.iend, (DIR == 0 ? p.jstr : p.jstrV), p.jend)
-  const long d = DIR == 0 ? 1 : SX;
+  THREAD_IJT(ixc_t, p.istr, p.iend, (DIR == 0 ? p.jstr : p.jstrV), p.jend)
+  const ixc_t d = DIR == 0 ? 1 : SX;
   const int N = p.N;
   const double dn = DIR == 0 ? p.dn_u[c] : p.dm_v[c];
   const double msk = DIR == 0 ? p.umask[c] : p.vmask[c];
@@ -1314,8 +1330,8 @@ __global__ void k_uv2_pass0(const __grid_constant__ KP p, double* __restrict__ u
 }
 template <int DIR>
 __global__ void k_uv2_pass1(const __grid_constant__ KP p, double* __restrict__ u, const double* __restrict__ u_stp, double* __restrict__ bar) {
-  THREAD_IJ(p.istr, p.iend, (DIR == 0 ? p.jstrR : p.jstr), p.jendR)
-  const long d = DIR == 0 ? 1 : SX;
+  THREAD_IJT(ixc_t, p.istr, p.iend, (DIR == 0 ? p.jstrR : p.jstr), p.jendR)
+  const ixc_t d = DIR == 0 ? 1 : SX;
   const int N = p.N;
   const double dn = DIR == 0 ? p.dn_u[c] : p.dm_v[c];
   const double msk = DIR == 0 ? p.umask[c] : p.vmask[c];

@@ -8,13 +8,17 @@
 #pragma once
 #include <cstddef>
 
+// element index inside one field: 32-bit is always enough on one GPU (a field of 2^31 doubles would need 16 GiB per 3-D
+// array and the step keeps 22+3*NT of them resident); roms_create checks it.  Halves the integer address arithmetic.
+typedef int ix_t;
+
 #define IOFF 15
 #define MAXNT 40
 
 struct KP {
   int Lm, Mm, N, NT;
   int SX;            // padded row pitch (doubles)
-  long SXY;          // padded plane size (doubles)
+  ix_t SXY;          // padded plane size (doubles)
   int istr, iend, jstr, jend;   // compute_tile_bounds.h with NSUB_X=NSUB_E=1
   int swall, nwall;             // this subdomain touches a closed (non-periodic) southern / northern physical edge
   int jstrR, jendR, jstrV;      // compute_auxiliary_bounds.h: jstr-1 / jend+1 / jstr+1 on such an edge, else jstr / jend / jstr
@@ -39,6 +43,6 @@ struct KP {
 };
 
 // column base index of (i,j) and relative addressing
-#define CIDX(i, j) ((long)((i) + IOFF) + (long)((j) + 1) * p.SX)
-#define R3(a, c, k) (a)[(c) + (long)((k)-1) * p.SXY]    // rho/u/v-type, k=1:N
-#define RW(a, c, k) (a)[(c) + (long)(k) * p.SXY]        // w-type, k=0:N
+#define CIDX(i, j) ((ix_t)((i) + IOFF) + (ix_t)((j) + 1) * p.SX)
+#define R3(a, c, k) (a)[(c) + (ix_t)((k)-1) * p.SXY]    // rho/u/v-type, k=1:N
+#define RW(a, c, k) (a)[(c) + (ix_t)(k) * p.SXY]        // w-type, k=0:N

@@ -53,7 +53,7 @@ struct roms_ctx {
   int ktiming = 0;
   std::vector<KTimer> ktimers;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
-  int col_bx = 32, col_by = 2, pl_bx = 128, pl_by = 2;
+  int col_bx = 32, col_by = 2, pl_bx = 32, pl_by = 8;   // plane tiles 32x8: fewest halo-row re-reads through L2 (profiles/r1_tuning_log.txt)
   int s2d_fused = 1;   // ROMS_S2D_FUSED=0 selects the three-launch barotropic substep (zeta, uv, wall rows)
   int use_smem = 0;   // measured on B200 (profiles/r1_scratch_policy.txt): occupancy beats shared-memory scratch
   Comm comm;
@@ -212,7 +212,8 @@ int roms_create(const roms_cfg* cfg, int device, roms_ctx** out) {
   memset(&p, 0, sizeof(p));
   p.Lm = cfg->Lm; p.Mm = cfg->Mm; p.N = N; p.NT = NT;
   p.SX = ((cfg->Lm + 18 + 15) / 16) * 16;
-  p.SXY = (long)p.SX * (cfg->Mm + 4);
+  if ((double)p.SX * (cfg->Mm + 4) * (N + 2) >= 2147483647.0) { g_err = "roms_create: subdomain too large for one GPU (a 3-D field must stay below 2^31 elements); split it over more GPUs"; return -1; }
+  p.SXY = (ix_t)(p.SX * (cfg->Mm + 4));
   p.istr = 1; p.iend = cfg->Lm; p.jstr = 1; p.jend = cfg->Mm;
   {
     const int npe = cfg->np_eta > 0 ? cfg->np_eta : 1;
