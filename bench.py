@@ -118,7 +118,27 @@ def cpu_oracle_rate(cfg_kw, steps, warmup, sample):
     return Lm * Mm * N * steps / dt, cores, dt, f"{Lm}x{Mm}x{N} block of the same analytic channel, {steps} baroclinic steps after {warmup} warm-up"
 
 
+_STDOUT_FD = None
+
+
+def _quiet_stdout():
+    """Libraries (NCCL's version banner) write to fd 1; the contract is ONE JSON line there.  Everything but the final
+    line goes to stderr."""
+    global _STDOUT_FD
+    sys.stdout.flush()
+    _STDOUT_FD = os.dup(1)
+    os.dup2(2, 1)
+
+
+def _emit(line):
+    sys.stdout.flush()
+    if _STDOUT_FD is not None:
+        os.dup2(_STDOUT_FD, 1)
+    print(json.dumps(line), flush=True)
+
+
 def main():
+    _quiet_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=5)
@@ -154,7 +174,7 @@ def main():
                 "data": "synthetic", "config": config,
                 "cpu_baseline": {"value": rate, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
                 "e2e": {"value": rate, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-        print(json.dumps(line))
+        _emit(line)
         return 0
 
     import numpy as np
@@ -288,7 +308,7 @@ def main():
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config,
                 "roofline": roof, "step_roofline": step_roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
                 "diag": {"KE": d[0], "BAROTR_KE": d[1], "MAX_ADV_CFL": d[2], "MAX_VERT_CFL": d[3]}}
-        print(json.dumps(line))
+        _emit(line)
     if world > 1:
         dist.destroy_process_group()
     return 0
