@@ -15,19 +15,20 @@ from romsb200 import Roms  # noqa: E402
 
 def main():
     nsteps = int(sys.argv[1]) if len(sys.argv) > 1 else 3
-    walls = len(sys.argv) > 2 and sys.argv[2] == "walls"
+    walls = len(sys.argv) > 2 and sys.argv[2] in ("walls", "seamount")
+    topo = len(sys.argv) > 2 and sys.argv[2] == "seamount"      # + bottom topography and a land mask
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
     npx, npe = cases.rank_grid(world)
     LG, MG, N = 24 * npx, 20 * npe, 10
-    cfg, st = cases.channel(LG, MG, N, ns_walls=walls, sub=(rank % npx, rank // npx, npx, npe))
+    cfg, st = cases.channel(LG, MG, N, ns_walls=walls, seamount=topo, island=topo, sub=(rank % npx, rank // npx, npx, npe))
     g = Roms(cfg, local)
     g.attach_torch_comm(dist)
     cases.initialize(g, st)
     g.call("run", nsteps)
     dg = g.diag()
-    cfgG, stG = cases.channel(LG, MG, N, ns_walls=walls)
+    cfgG, stG = cases.channel(LG, MG, N, ns_walls=walls, seamount=topo, island=topo)
     o = Oracle(cfgG)
     cases.initialize(o, stG)
     o.call("run", nsteps)

@@ -56,12 +56,17 @@ def test_constants_match_oracle():
     g.close(); o.close()
 
 
-@pytest.mark.parametrize("case", ["channel", "filament", "channel_linear_odd", "channel_walls", "channel_walls_linear_odd"])
+@pytest.mark.parametrize("case", ["channel", "filament", "channel_linear_odd", "channel_walls", "channel_walls_linear_odd",
+                                  "seamount_island_walls", "seamount_island_periodic"])
 def test_routine_by_routine(case):
     if case == "channel":
         cfg, st = cases.channel(48, 40, 12)
     elif case == "channel_walls":
         cfg, st = cases.channel(48, 40, 12, ns_walls=True)             # closed N/S walls (configs[1] geometry)
+    elif case == "seamount_island_walls":                              # bottom topography + land mask + closed N/S walls
+        cfg, st = cases.channel(48, 40, 12, ns_walls=True, seamount=True, island=True)
+    elif case == "seamount_island_periodic":
+        cfg, st = cases.channel(45, 38, 11, seamount=True, island=True)
     elif case == "channel_walls_linear_odd":
         cfg, st = cases.channel(37, 29, 9, NT=3, nonlin_eos=False, ns_walls=True)
     elif case == "filament":
@@ -73,9 +78,9 @@ def test_routine_by_routine(case):
     assert not bad, bad
 
 
-@pytest.mark.parametrize("walls", [False, True])
-def test_one_step_and_100_steps_channel(walls):
-    cfg, st = cases.channel(64, 48, 16, ns_walls=walls)
+@pytest.mark.parametrize("walls,topo", [(False, False), (True, False), (True, True)])
+def test_one_step_and_100_steps_channel(walls, topo):
+    cfg, st = cases.channel(64, 48, 16, ns_walls=walls, seamount=topo, island=topo)
     g, o = Roms(cfg), Oracle(cfg)
     cases.initialize(g, st); cases.initialize(o, st)
     g.call("step"); o.call("step")
@@ -137,4 +142,7 @@ def test_two_gpu_halo_exchange_parity():
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
                         "--master-port", "29732", script, "3", "walls"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+                        "--master-port", "29733", script, "3", "seamount"], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]

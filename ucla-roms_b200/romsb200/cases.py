@@ -62,9 +62,12 @@ def _noise(ig, jg, k, salt):
 
 
 def channel(Lm=64, Mm=64, N=16, NT=2, ns_walls=False, nonlin_eos=True, dt=120.0, ndtfast=60, dx=1.0e3, dy=1.0e3,
-            depth=4000.0, seed=20260101, perturb=1e-6, amp=None, sub=(0, 0, 1, 1)):
+            depth=4000.0, seed=20260101, perturb=1e-6, amp=None, sub=(0, 0, 1, 1), seamount=False, island=False):
     """Lm, Mm are the GLOBAL interior sizes; sub=(inode, jnode, np_xi, np_eta) selects this rank's block
-    (mpi_setup.F:61-70; sizes must divide evenly).  Returns the cfg and state of that block."""
+    (mpi_setup.F:61-70; sizes must divide evenly).  Returns the cfg and state of that block.
+    seamount: Gaussian seamount h = depth*(1 - 0.5*exp(-r^2/(L/5)^2)) (SURVEY.md 8(d) input (3), form of
+    NHMG/tests/mg_setup_tests.f90:150); island: a circular land mask (rmask=0) north-east of it, so that the
+    rmask/umask/vmask factors of every routine are exercised."""
     inode, jnode, np_xi, np_eta = sub
     LmG, MmG = Lm, Mm
     assert LmG % np_xi == 0 and MmG % np_eta == 0
@@ -87,6 +90,12 @@ def channel(Lm=64, Mm=64, N=16, NT=2, ns_walls=False, nonlin_eos=True, dt=120.0,
         amp = 0.02 * min(Lx, Ly) / 64.0e3 + 0.01   # keeps the thermal-wind shear independent of the grid size
     st = {}
     h = np.full((sy, sx), depth)
+    if seamount:
+        r2 = (x - 0.5 * Lx) ** 2 + (y - 0.5 * Ly) ** 2
+        h = depth * (1.0 - 0.5 * np.exp(-r2 / (min(Lx, Ly) / 5.0) ** 2))
+    rmask = np.ones((sy, sx))
+    if island:
+        rmask[(x - 0.72 * Lx) ** 2 + (y - 0.70 * Ly) ** 2 < (0.09 * min(Lx, Ly)) ** 2] = 0.0
     zeta = 0.01 * np.sin(2 * np.pi * x / Lx) * np.cos(2 * np.pi * y / Ly)
     z_r, z_w = _depths(h, zeta, N, cfg.theta_s, cfg.theta_b, cfg.hc)
     Hz = z_w[1:] - z_w[:-1]
@@ -105,6 +114,10 @@ def channel(Lm=64, Mm=64, N=16, NT=2, ns_walls=False, nonlin_eos=True, dt=120.0,
     if ns_walls:
         jl = (np.arange(-2, Mm + 4) + j0)
         v[:, (jl <= 1) | (jl >= MmG + 1), :] = 0.0     # closed south (j=1) and north (j=Mm+1) walls
+    if island:
+        um = np.ones_like(rmask); vm = np.ones_like(rmask)
+        um[:, 1:] = rmask[:, 1:] * rmask[:, :-1]; vm[1:, :] = rmask[1:, :] * rmask[:-1, :]
+        u = u * um[None]; v = v * vm[None]; zeta = zeta * rmask
     Hzu = np.empty_like(Hz); Hzv = np.empty_like(Hz)
     Hzu[:, :, 1:] = 0.5 * (Hz[:, :, 1:] + Hz[:, :, :-1]); Hzu[:, :, 0] = Hz[:, :, 0]
     Hzv[:, 1:, :] = 0.5 * (Hz[:, 1:, :] + Hz[:, :-1, :]); Hzv[:, 0, :] = Hz[:, 0, :]
@@ -113,7 +126,7 @@ def channel(Lm=64, Mm=64, N=16, NT=2, ns_walls=False, nonlin_eos=True, dt=120.0,
     st["H"] = t2(h)
     st["PM"] = np.full((Mm + 4, Lm + 4), 1.0 / dx); st["PN"] = np.full((Mm + 4, Lm + 4), 1.0 / dy)
     st["F"] = np.full((Mm + 4, Lm + 4), 1.0e-4)
-    st["RMASK"] = np.ones((Mm + 4, Lm + 4))
+    st["RMASK"] = t2(rmask)
     zeta, ubar, vbar, u, v, T, S = (t2(a) for a in (zeta, ubar, vbar, u, v, T, S))
     st["ZETA"] = {(1, 1): zeta, (2, 1): zeta}
     st["UBAR"] = {(1, 1): ubar, (2, 1): ubar}
