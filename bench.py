@@ -35,6 +35,7 @@ KERNEL_WORDS = {
     "k_t_vert": lambda t: (8 if t[0] == "0" else 7, 3), "k_uv_vert": lambda t: (10 if t[0] == "0" else 9, 3),
     "k_set_huv1": (4, 3), "k_uv2_pass0": (3, 3), "k_uv2_pass1": (6, 3),
     "k_t_horiz": (5, 3), "k_set_depth": (3, 3), "k_step2d_zeta": (24, 2), "k_step2d_uv": (23, 2), "k_rd_bott_drag": (3, 2),
+    "k_step2d": (34, 2),     # 9 state R + 3 W + 12 static R + 10 averages RW per 2-D point and substep
 }
 
 
