@@ -20,8 +20,18 @@
 #ifndef LB_RHS
 #define LB_RHS 4
 #endif
-#ifndef LB_T
-#define LB_T 8
+// levels per thread (2-D operands stay in registers across them) and resident blocks of the k-blocked plane kernels
+#ifndef KB_T
+#define KB_T 8
+#endif
+#ifndef KB_PRS
+#define KB_PRS 1
+#endif
+#ifndef LB_TP
+#define LB_TP 5
+#endif
+#ifndef LB_TC
+#define LB_TC 4
 #endif
 #ifndef LB_S2D
 #define LB_S2D 4
@@ -391,39 +401,14 @@ __device__ __forceinline__ void prs_fc_rx(const KP& p, ix_t X, ix_t d, int k, co
     rx = (R3(p.rho1, X, k) - R3(p.rho1, X - d, k) + (R3(p.qp1, X, k) - R3(p.qp1, X - d, k)) * dpth * (1.0 - qp2 * dpth)) * m;
   } else rx = (R3(rho, X, k) - R3(rho, X - d, k)) * m;
 }
-// CL: the three difference positions (c-d, c, c+d) are displaced by oA, oB, oC (wall clamping, see jclamp)
-template <bool NONLIN, bool CL>
-__device__ __forceinline__ double prs_dir(const KP& p, ix_t c, ix_t d, int k, const double* __restrict__ msk, double dn, const double* __restrict__ rho,
-                                          ix_t oA = 0, ix_t oB = 0, ix_t oC = 0) {
+// second half of prsgrd.F:330-421 for one direction: harmonic means of the three first differences -> ru / rv
+template <bool NONLIN>
+__device__ __forceinline__ double prs_tail(const KP& p, ix_t c, ix_t d, int k, double dn, const double* __restrict__ rho, double FCa, double FCb, double FCc,
+                                           double rxa, double rxb, double rxc, double q1, double q2v, double z1, double z2) {
   const double qp2 = 0.0000172, OneFifth = 0.2, OneTwelfth = 1.0 / 12.0, epsil = 0.0;
   const double HalfGRho = 0.5 * (p.g / p.rho0);
-  // points c-2d, c-d, c, c+d
-  const double z1 = R3(p.z_r, c - d, k), z2 = R3(p.z_r, c, k);
-  double FCa, FCb, FCc, rxa, rxb, rxc;
-  double q1 = 0, q2v = 0;
-  if (CL) {
-    prs_fc_rx<NONLIN>(p, c - d + oA, d, k, msk, rho, FCa, rxa);
-    prs_fc_rx<NONLIN>(p, c + oB, d, k, msk, rho, FCb, rxb);
-    prs_fc_rx<NONLIN>(p, c + d + oC, d, k, msk, rho, FCc, rxc);
-    if (NONLIN) { q1 = R3(p.qp1, c - d, k); q2v = R3(p.qp1, c, k); }
-  } else {
-  const double z0 = R3(p.z_r, c - 2 * d, k), z3 = R3(p.z_r, c + d, k);
-  const double m1 = msk[c - d], m2 = msk[c], m3 = msk[c + d];
-  FCa = (z1 - z0) * m1; FCb = (z2 - z1) * m2; FCc = (z3 - z2) * m3;   // FC(i-1), FC(i), FC(i+1)
-  if (NONLIN) {
-    const double a0 = R3(p.rho1, c - 2 * d, k), a1 = R3(p.rho1, c - d, k), a2 = R3(p.rho1, c, k), a3 = R3(p.rho1, c + d, k);
-    const double b0 = R3(p.qp1, c - 2 * d, k), b1 = R3(p.qp1, c - d, k), b2 = R3(p.qp1, c, k), b3 = R3(p.qp1, c + d, k);
-    double dpth = -0.5 * (z1 + z0); rxa = (a1 - a0 + (b1 - b0) * dpth * (1.0 - qp2 * dpth)) * m1;
-    dpth = -0.5 * (z2 + z1); rxb = (a2 - a1 + (b2 - b1) * dpth * (1.0 - qp2 * dpth)) * m2;
-    dpth = -0.5 * (z3 + z2); rxc = (a3 - a2 + (b3 - b2) * dpth * (1.0 - qp2 * dpth)) * m3;
-    q1 = b1; q2v = b2;
-  } else {
-    const double a0 = R3(rho, c - 2 * d, k), a1 = R3(rho, c - d, k), a2 = R3(rho, c, k), a3 = R3(rho, c + d, k);
-    rxa = (a1 - a0) * m1; rxb = (a2 - a1) * m2; rxc = (a3 - a2) * m3;
-  }
-  }
   // dZx, dRx at c-d ("m") and c ("c"): harmonic means (prsgrd.F:330-345).  The quotient is formed unconditionally and
-  // selected afterwards (same value where it is used) so that rows sharing a mean share the division.
+  // selected afterwards (same value where it is used): no divergent branch around the fp64 division.
   double cff = 2.0 * FCa * FCb, quo = cff / (FCa + FCb);
   const double dZx_m = (cff > epsil) ? quo : 0.0;
   cff = 2.0 * FCb * FCc; quo = cff / (FCb + FCc);
@@ -442,40 +427,66 @@ __device__ __forceinline__ double prs_dir(const KP& p, ix_t c, ix_t d, int k, co
           HalfGRho * ((rho_c + rho_m) * (z2 - z1) -
                       OneFifth * ((dRx_c - dRx_m) * (z2 - z1 - OneTwelfth * (dZx_c + dZx_m)) - (dZx_c - dZx_m) * (rho_c - rho_m - OneTwelfth * (dRx_c + dRx_m)))));
 }
-template <bool NONLIN, bool WALL, int JB>
+// rows next to a closed wall: the three difference positions (c-d, c, c+d) are displaced by oA, oB, oC (see jclamp)
+template <bool NONLIN>
+__device__ __forceinline__ double prs_dir_cl(const KP& p, ix_t c, ix_t d, int k, const double* __restrict__ msk, double dn, const double* __restrict__ rho,
+                                             ix_t oA, ix_t oB, ix_t oC) {
+  const double z1 = R3(p.z_r, c - d, k), z2 = R3(p.z_r, c, k);
+  double FCa, FCb, FCc, rxa, rxb, rxc, q1 = 0, q2v = 0;
+  prs_fc_rx<NONLIN>(p, c - d + oA, d, k, msk, rho, FCa, rxa);
+  prs_fc_rx<NONLIN>(p, c + oB, d, k, msk, rho, FCb, rxb);
+  prs_fc_rx<NONLIN>(p, c + d + oC, d, k, msk, rho, FCc, rxc);
+  if (NONLIN) { q1 = R3(p.qp1, c - d, k); q2v = R3(p.qp1, c, k); }
+  return prs_tail<NONLIN>(p, c, d, k, dn, rho, FCa, FCb, FCc, rxa, rxb, rxc, q1, q2v, z1, z2);
+}
+// interior: points c-2d, c-d, c, c+d; the masks m1..m3 = msk(c-d), msk(c), msk(c+d) are level-independent and come in registers
+template <bool NONLIN>
+__device__ __forceinline__ double prs_dir(const KP& p, ix_t c, ix_t d, int k, double m1, double m2, double m3, double dn, const double* __restrict__ rho) {
+  const double qp2 = 0.0000172;
+  const double z0 = R3(p.z_r, c - 2 * d, k), z1 = R3(p.z_r, c - d, k), z2 = R3(p.z_r, c, k), z3 = R3(p.z_r, c + d, k);
+  const double FCa = (z1 - z0) * m1, FCb = (z2 - z1) * m2, FCc = (z3 - z2) * m3;   // FC(i-1), FC(i), FC(i+1)
+  double rxa, rxb, rxc, q1 = 0, q2v = 0;
+  if (NONLIN) {
+    const double a0 = R3(p.rho1, c - 2 * d, k), a1 = R3(p.rho1, c - d, k), a2 = R3(p.rho1, c, k), a3 = R3(p.rho1, c + d, k);
+    const double b0 = R3(p.qp1, c - 2 * d, k), b1 = R3(p.qp1, c - d, k), b2 = R3(p.qp1, c, k), b3 = R3(p.qp1, c + d, k);
+    double dpth = -0.5 * (z1 + z0); rxa = (a1 - a0 + (b1 - b0) * dpth * (1.0 - qp2 * dpth)) * m1;
+    dpth = -0.5 * (z2 + z1); rxb = (a2 - a1 + (b2 - b1) * dpth * (1.0 - qp2 * dpth)) * m2;
+    dpth = -0.5 * (z3 + z2); rxc = (a3 - a2 + (b3 - b2) * dpth * (1.0 - qp2 * dpth)) * m3;
+    q1 = b1; q2v = b2;
+  } else {
+    const double a0 = R3(rho, c - 2 * d, k), a1 = R3(rho, c - d, k), a2 = R3(rho, c, k), a3 = R3(rho, c + d, k);
+    rxa = (a1 - a0) * m1; rxb = (a2 - a1) * m2; rxc = (a3 - a2) * m3;
+  }
+  return prs_tail<NONLIN>(p, c, d, k, dn, rho, FCa, FCb, FCc, rxa, rxb, rxc, q1, q2v, z1, z2);
+}
+// Each thread computes KB consecutive levels of one (i,j): the six masks and two metric factors of the point stay in
+// registers across the levels (as 2-D operands re-fetched per level they cost up to 3.6 words/point of HBM traffic).
+template <bool NONLIN, bool WALL, int KB>
 __global__ void __launch_bounds__(256, LB_PRS) k_prsgrd_horiz(const __grid_constant__ KP p) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x - IOFF;
-  const int jb = p.jstr + (blockIdx.y * blockDim.y + threadIdx.y) * JB;
-  if (i < p.istr || i > p.iend || jb > p.jend) return;
-  const ix_t SX = p.SX;
-  const int k = blockIdx.z + 1;
+  THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
+  const int k0 = blockIdx.z * KB + 1;
   const double* __restrict__ rho = NONLIN ? p.rho : p.rho1;
-  const bool near = WALL && ((p.swall && jb <= p.jstr + 2) || (p.nwall && jb + JB - 1 >= p.jend - 2));
-  const ix_t c0 = CIDX(i, jb);
-  if (near || jb + JB - 1 > p.jend) {   // rows next to a wall / ragged last block: one row at a time
+  const double dnu = p.dn_u[c], dmv = p.dm_v[c];
+  if (WALL && ((p.swall && j <= p.jstr + 2) || (p.nwall && j >= p.jend - 2))) {   // prsgrd.F:288-310: FC,rx exist on rows jstrV..jend, copied outward
+    const ix_t oA = jclamp(p, j - 1, p.jstrV, p.jend), oB = jclamp(p, j, p.jstrV, p.jend), oC = jclamp(p, j + 1, p.jstrV, p.jend);
 #pragma unroll 1
-    for (int q = 0; q < JB && jb + q <= p.jend; ++q) {
-      const int j = jb + q;
-      const ix_t c = c0 + q * SX;
-      R3(p.ru, c, k) = prs_dir<NONLIN, false>(p, c, 1, k, p.umask, p.dn_u[c], rho);
-      if (!WALL) R3(p.rv, c, k) = prs_dir<NONLIN, false>(p, c, SX, k, p.vmask, p.dm_v[c], rho);
-      else if (j >= p.jstrV)   // prsgrd.F:288-310: FC,rx exist on rows jstrV..jend between walls, copied one row outward
-        R3(p.rv, c, k) = prs_dir<NONLIN, true>(p, c, SX, k, p.vmask, p.dm_v[c], rho, jclamp(p, j - 1, p.jstrV, p.jend), jclamp(p, j, p.jstrV, p.jend),
-                                               jclamp(p, j + 1, p.jstrV, p.jend));
+    for (int k = k0; k < k0 + KB && k <= p.N; ++k) {
+      R3(p.ru, c, k) = prs_dir_cl<NONLIN>(p, c, 1, k, p.umask, dnu, rho, 0, 0, 0);
+      if (j >= p.jstrV) R3(p.rv, c, k) = prs_dir_cl<NONLIN>(p, c, SX, k, p.vmask, dmv, rho, oA, oB, oC);
     }
     return;
   }
-  double ru[JB], rv[JB];
+  const double mu1 = p.umask[c - 1], mu2 = p.umask[c], mu3 = p.umask[c + 1];
+  const double mv1 = p.vmask[c - SX], mv2 = p.vmask[c], mv3 = p.vmask[c + SX];
 #pragma unroll
-  for (int q = 0; q < JB; ++q) {
-    const ix_t c = c0 + q * SX;
-    ru[q] = prs_dir<NONLIN, false>(p, c, 1, k, p.umask, p.dn_u[c], rho);
-    rv[q] = prs_dir<NONLIN, false>(p, c, SX, k, p.vmask, p.dm_v[c], rho);
-  }
-#pragma unroll
-  for (int q = 0; q < JB; ++q) {
-    R3(p.ru, c0 + q * SX, k) = ru[q];
-    R3(p.rv, c0 + q * SX, k) = rv[q];
+  for (int q = 0; q < KB; ++q) {
+    const int k = k0 + q;
+    if (k <= p.N) {
+      const double ru = prs_dir<NONLIN>(p, c, 1, k, mu1, mu2, mu3, dnu, rho);
+      const double rv = prs_dir<NONLIN>(p, c, SX, k, mv1, mv2, mv3, dmv, rho);
+      R3(p.ru, c, k) = ru;
+      R3(p.rv, c, k) = rv;
+    }
   }
 }
 
@@ -608,21 +619,8 @@ __global__ void __launch_bounds__(256, (JB >= 4 ? 2 : LB_RHS)) k_rhs_uv_horiz(co
 }
 
 // compute_horiz_tracer_fluxes.h:1-246: FX at u-point c (d=1, FlxU, umask) or FE at v-point c (d=SX)
-template <bool UP, bool CL>
-__device__ __forceinline__ double tflux(const KP& p, const double* __restrict__ t, const double* __restrict__ Flx, const double* __restrict__ msk, ix_t c, ix_t d, int k,
-                                        ix_t oA = 0, ix_t oB = 0, ix_t oC = 0) {
-  const double t1 = R3(t, c - d, k), t2 = R3(t, c, k);
-  double Fa, Fb, Fc;   // FX(c-d), FX(c), FX(c+d)
-  if (CL) {            // first differences taken at the wall-clamped rows
-    const ix_t XA = c - d + oA, XB = c + oB, XC = c + d + oC;
-    Fa = (R3(t, XA, k) - R3(t, XA - d, k)) * msk[XA];
-    Fb = (R3(t, XB, k) - R3(t, XB - d, k)) * msk[XB];
-    Fc = (R3(t, XC, k) - R3(t, XC - d, k)) * msk[XC];
-  } else {
-    const double t0 = R3(t, c - 2 * d, k), t3 = R3(t, c + d, k);
-    Fa = (t1 - t0) * msk[c - d]; Fb = (t2 - t1) * msk[c]; Fc = (t3 - t2) * msk[c + d];
-  }
-  const double fl = R3(Flx, c, k);
+template <bool UP>
+__device__ __forceinline__ double tflux_fin(double t1, double t2, double Fa, double Fb, double Fc, double fl) {
   if (UP) {
     const double wm = Fb - Fa, wc = Fc - Fb;   // wrk1(c-d), wrk1(c)
     return 0.5 * (t2 + t1) * fl - 0.1666666666666666 * (wm * DMAX(fl, 0.0) + wc * DMIN(fl, 0.0));
@@ -630,6 +628,24 @@ __device__ __forceinline__ double tflux(const KP& p, const double* __restrict__ 
     const double wm = 0.5 * (Fb + Fa), wc = 0.5 * (Fc + Fb);
     return 0.5 * (t2 + t1 - 0.3333333333333333 * (wc - wm)) * fl;
   }
+}
+// rows next to a closed wall: first differences taken at the wall-clamped rows (offsets oA, oB, oC, see jclamp)
+template <bool UP>
+__device__ __forceinline__ double tflux_cl(const KP& p, const double* __restrict__ t, const double* __restrict__ Flx, const double* __restrict__ msk, ix_t c, ix_t d,
+                                           int k, ix_t oA, ix_t oB, ix_t oC) {
+  const double t1 = R3(t, c - d, k), t2 = R3(t, c, k);
+  const ix_t XA = c - d + oA, XB = c + oB, XC = c + d + oC;
+  const double Fa = (R3(t, XA, k) - R3(t, XA - d, k)) * msk[XA];
+  const double Fb = (R3(t, XB, k) - R3(t, XB - d, k)) * msk[XB];
+  const double Fc = (R3(t, XC, k) - R3(t, XC - d, k)) * msk[XC];
+  return tflux_fin<UP>(t1, t2, Fa, Fb, Fc, R3(Flx, c, k));
+}
+// interior: masks mA..mC = msk(c-d), msk(c), msk(c+d) are level-independent and come in registers
+template <bool UP>
+__device__ __forceinline__ double tflux(const double* __restrict__ t, const double* __restrict__ Flx, const KP& p, ix_t c, ix_t d, int k, double mA, double mB,
+                                        double mC) {
+  const double t0 = R3(t, c - 2 * d, k), t1 = R3(t, c - d, k), t2 = R3(t, c, k), t3 = R3(t, c + d, k);
+  return tflux_fin<UP>(t1, t2, (t1 - t0) * mA, (t2 - t1) * mB, (t3 - t2) * mC, R3(Flx, c, k));
 }
 
 // pre_step3d4S.F:138-147: FlxDiv such that Hz_bak = Hz + FlxDiv, Hz_fwd = Hz - FlxDiv
@@ -642,38 +658,68 @@ __global__ void k_pre_flxdiv(const __grid_constant__ KP p, double dtau) {
                         RW(p.We, c, k - 1) - RW(p.Wi, c, k - 1));
 }
 // pre_step3d4S.F:152-168: tracer predictor, horizontal part (C4), and t(indx)=Hz*t(nstp)
-// FE at v-rows j and j+1; between walls the first differences exist on rows jstr..jend+1 (compute_horiz_tracer_fluxes.h:118-160)
-#define TFLUX_J(UP, FEj, FEjp)                                                                                                     \
-  double FEj, FEjp;                                                                                                                \
-  if (WALL && ((p.swall && j <= p.jstr + 2) || (p.nwall && j >= p.jend - 2))) { /* rows next to a wall only */                     \
-    FEj = tflux<UP, true>(p, t_rhs, p.FlxV, p.vmask, c, SX, k, jclamp(p, j - 1, p.jstr, p.jend + 1), jclamp(p, j, p.jstr, p.jend + 1),       \
-                          jclamp(p, j + 1, p.jstr, p.jend + 1));                                                                   \
-    FEjp = tflux<UP, true>(p, t_rhs, p.FlxV, p.vmask, c + SX, SX, k, jclamp(p, j, p.jstr, p.jend + 1), jclamp(p, j + 1, p.jstr, p.jend + 1), \
-                           jclamp(p, j + 2, p.jstr, p.jend + 1));                                                                  \
-  } else {                                                                                                                         \
-    FEj = tflux<UP, false>(p, t_rhs, p.FlxV, p.vmask, c, SX, k);                                                                   \
-    FEjp = tflux<UP, false>(p, t_rhs, p.FlxV, p.vmask, c + SX, SX, k);                                                             \
-  }
-template <bool WALL>
-__global__ void __launch_bounds__(256, LB_T) k_pre_t_horiz(const __grid_constant__ KP p, const double* __restrict__ t_rhs, double* __restrict__ t_new, const double* __restrict__ t_stp,
-                              double* __restrict__ t_indx, double dtau, double cf_stp, double cf_bak) {
-  THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
-  const int k = blockIdx.z + 1;
-  const double FXi = tflux<false, false>(p, t_rhs, p.FlxU, p.umask, c, 1, k), FXip = tflux<false, false>(p, t_rhs, p.FlxU, p.umask, c + 1, 1, k);
-  TFLUX_J(false, FEj, FEjp)
-  const double Hz = R3(p.Hz, c, k), Hz_bak = Hz + R3(p.FlxDiv, c, k);
-  const double ts = R3(t_stp, c, k);
-  R3(t_new, c, k) = Hz_bak * (cf_stp * ts + cf_bak * R3(t_indx, c, k)) - dtau * p.pm[c] * p.pn[c] * (FXip - FXi + FEjp - FEj);
-  R3(t_indx, c, k) = Hz * ts;
-}
 // step3d_t_ISO.F:196-213: tracer corrector, horizontal part (UP3)
-template <bool WALL>
-__global__ void __launch_bounds__(256, LB_T) k_t_horiz(const __grid_constant__ KP p, const double* __restrict__ t_rhs, double* __restrict__ t_new) {
+// Horizontal flux divergence  FX(i+1)-FX(i)+FE(j+1)-FE(j)  at (i,j,k).  Between walls the first differences in j exist on
+// rows jstr..jend+1 only (compute_horiz_tracer_fluxes.h:118-160); NEAR rows take the clamped form.  The eight mask values
+// of the point are level-independent and are passed in registers.
+struct TMask { double u0, u1, u2, u3, v0, v1, v2, v3; };   // umask(c-1..c+2), vmask(c-SX..c+2SX)
+__device__ __forceinline__ TMask tmask_load(const KP& p, ix_t c) {
+  const ix_t SX = p.SX;
+  TMask m;
+  m.u0 = p.umask[c - 1]; m.u1 = p.umask[c]; m.u2 = p.umask[c + 1]; m.u3 = p.umask[c + 2];
+  m.v0 = p.vmask[c - SX]; m.v1 = p.vmask[c]; m.v2 = p.vmask[c + SX]; m.v3 = p.vmask[c + 2 * SX];
+  return m;
+}
+template <bool UP, bool NEAR>
+__device__ __forceinline__ double tdiv(const KP& p, const double* __restrict__ t, ix_t c, int j, int k, const TMask& m) {
+  const ix_t SX = p.SX;
+  const double FXi = tflux<UP>(t, p.FlxU, p, c, 1, k, m.u0, m.u1, m.u2), FXip = tflux<UP>(t, p.FlxU, p, c + 1, 1, k, m.u1, m.u2, m.u3);
+  double FEj, FEjp;
+  if (NEAR) {
+    FEj = tflux_cl<UP>(p, t, p.FlxV, p.vmask, c, SX, k, jclamp(p, j - 1, p.jstr, p.jend + 1), jclamp(p, j, p.jstr, p.jend + 1), jclamp(p, j + 1, p.jstr, p.jend + 1));
+    FEjp = tflux_cl<UP>(p, t, p.FlxV, p.vmask, c + SX, SX, k, jclamp(p, j, p.jstr, p.jend + 1), jclamp(p, j + 1, p.jstr, p.jend + 1),
+                        jclamp(p, j + 2, p.jstr, p.jend + 1));
+  } else {
+    FEj = tflux<UP>(t, p.FlxV, p, c, SX, k, m.v0, m.v1, m.v2);
+    FEjp = tflux<UP>(t, p.FlxV, p, c + SX, SX, k, m.v1, m.v2, m.v3);
+  }
+  return FXip - FXi + FEjp - FEj;
+}
+template <bool WALL, int KB>
+__global__ void __launch_bounds__(256, LB_TP) k_pre_t_horiz(const __grid_constant__ KP p, const double* __restrict__ t_rhs, double* __restrict__ t_new,
+                                                            const double* __restrict__ t_stp, double* __restrict__ t_indx, double dtau, double cf_stp, double cf_bak) {
   THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
-  const int k = blockIdx.z + 1;
-  const double FXi = tflux<true, false>(p, t_rhs, p.FlxU, p.umask, c, 1, k), FXip = tflux<true, false>(p, t_rhs, p.FlxU, p.umask, c + 1, 1, k);
-  TFLUX_J(true, FEj, FEjp)
-  R3(t_new, c, k) = R3(t_new, c, k) - p.dt * p.pm[c] * p.pn[c] * (FXip - FXi + FEjp - FEj);
+  const int k0 = blockIdx.z * KB + 1;
+  const TMask m = tmask_load(p, c);
+  const double cdt = dtau * p.pm[c] * p.pn[c];
+  const bool near = WALL && ((p.swall && j <= p.jstr + 2) || (p.nwall && j >= p.jend - 2));
+#pragma unroll
+  for (int q = 0; q < KB; ++q) {
+    const int k = k0 + q;
+    if (k <= p.N) {
+      const double dv = near ? tdiv<false, true>(p, t_rhs, c, j, k, m) : tdiv<false, false>(p, t_rhs, c, j, k, m);
+      const double Hz = R3(p.Hz, c, k), Hz_bak = Hz + R3(p.FlxDiv, c, k);
+      const double ts = R3(t_stp, c, k);
+      R3(t_new, c, k) = Hz_bak * (cf_stp * ts + cf_bak * R3(t_indx, c, k)) - cdt * (dv);
+      R3(t_indx, c, k) = Hz * ts;
+    }
+  }
+}
+template <bool WALL, int KB>
+__global__ void __launch_bounds__(256, LB_TC) k_t_horiz(const __grid_constant__ KP p, const double* __restrict__ t_rhs, double* __restrict__ t_new) {
+  THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
+  const int k0 = blockIdx.z * KB + 1;
+  const TMask m = tmask_load(p, c);
+  const double cdt = p.dt * p.pm[c] * p.pn[c];
+  const bool near = WALL && ((p.swall && j <= p.jstr + 2) || (p.nwall && j >= p.jend - 2));
+#pragma unroll
+  for (int q = 0; q < KB; ++q) {
+    const int k = k0 + q;
+    if (k <= p.N) {
+      const double dv = near ? tdiv<true, true>(p, t_rhs, c, j, k, m) : tdiv<true, false>(p, t_rhs, c, j, k, m);
+      R3(t_new, c, k) = R3(t_new, c, k) - cdt * (dv);
+    }
+  }
 }
 
 // compute_rd_bott_drag.h:1-74 (log-layer drag when Zob>0, else linear rdrg capped by 0.8*Hz/dt)

@@ -526,12 +526,12 @@ int roms_prsgrd(roms_ctx* h) {
   const KP& p = h->kp;
   if (h->c.nonlin_eos) {
     COLUMN(k_prsgrd_vert<true>, 0, p.Lm, 0, p.Mm, p);
-    if (WALLED(h)) PLANE_JB((k_prsgrd_horiz<true, true, 1>), 1, p.iend, p.jstr, p.jend, p.N, p);
-    else PLANE_JB((k_prsgrd_horiz<true, false, 1>), 1, p.iend, p.jstr, p.jend, p.N, p);
+    if (WALLED(h)) PLANE((k_prsgrd_horiz<true, true, KB_PRS>), p.iend, p.jstr, p.jend, (p.N + KB_PRS - 1) / KB_PRS, p);
+    else PLANE((k_prsgrd_horiz<true, false, KB_PRS>), p.iend, p.jstr, p.jend, (p.N + KB_PRS - 1) / KB_PRS, p);
   } else {
     COLUMN(k_prsgrd_vert<false>, 0, p.Lm, 0, p.Mm, p);
-    if (WALLED(h)) PLANE_JB((k_prsgrd_horiz<false, true, 1>), 1, p.iend, p.jstr, p.jend, p.N, p);
-    else PLANE_JB((k_prsgrd_horiz<false, false, 1>), 1, p.iend, p.jstr, p.jend, p.N, p);
+    if (WALLED(h)) PLANE((k_prsgrd_horiz<false, true, KB_PRS>), p.iend, p.jstr, p.jend, (p.N + KB_PRS - 1) / KB_PRS, p);
+    else PLANE((k_prsgrd_horiz<false, false, KB_PRS>), p.iend, p.jstr, p.jend, (p.N + KB_PRS - 1) / KB_PRS, p);
   }
   return 0;
 }
@@ -547,8 +547,8 @@ int roms_pre_step3d(roms_ctx* h, int tile) {
   const bool wl = WALLED(h);
   PLANE(k_pre_flxdiv, p.iend, p.jstrV - 1, p.jend, p.N, p, dtau);
   for (int it = 1; it <= h->c.NT; ++it) {
-    if (wl) PLANE(k_pre_t_horiz<true>, p.iend, p.jstr, p.jend, p.N, p, h->t(nrhs, it), h->t(nnew, it), h->t(nstp, it), h->t(indx, it), dtau, cf_stp, cf_bak);
-    else PLANE(k_pre_t_horiz<false>, p.iend, p.jstr, p.jend, p.N, p, h->t(nrhs, it), h->t(nnew, it), h->t(nstp, it), h->t(indx, it), dtau, cf_stp, cf_bak);
+    if (wl) PLANE((k_pre_t_horiz<true, KB_T>), p.iend, p.jstr, p.jend, (p.N + KB_T - 1) / KB_T, p, h->t(nrhs, it), h->t(nnew, it), h->t(nstp, it), h->t(indx, it), dtau, cf_stp, cf_bak);
+    else PLANE((k_pre_t_horiz<false, KB_T>), p.iend, p.jstr, p.jend, (p.N + KB_T - 1) / KB_T, p, h->t(nrhs, it), h->t(nnew, it), h->t(nstp, it), h->t(indx, it), dtau, cf_stp, cf_bak);
   }
   if (wl) PLANE_JB((k_rhs_uv_horiz<false, true, 4>), 4, p.iend, p.jstr, p.jend, p.N, p, h->u(nrhs), h->v(nrhs));
   else PLANE_JB((k_rhs_uv_horiz<false, false, 4>), 4, p.iend, p.jstr, p.jend, p.N, p, h->u(nrhs), h->v(nrhs));
@@ -653,8 +653,8 @@ int roms_step3d_t(roms_ctx* h, int tile) {
   const KP& p = h->kp;
   const int nrhs = h->nrhs, nnew = h->nnew, NT = h->c.NT;
   for (int it = 1; it <= NT; ++it) {
-    if (WALLED(h)) PLANE(k_t_horiz<true>, p.iend, p.jstr, p.jend, p.N, p, h->t(nrhs, it), h->t(nnew, it));
-    else PLANE(k_t_horiz<false>, p.iend, p.jstr, p.jend, p.N, p, h->t(nrhs, it), h->t(nnew, it));
+    if (WALLED(h)) PLANE((k_t_horiz<true, KB_T>), p.iend, p.jstr, p.jend, (p.N + KB_T - 1) / KB_T, p, h->t(nrhs, it), h->t(nnew, it));
+    else PLANE((k_t_horiz<false, KB_T>), p.iend, p.jstr, p.jend, (p.N + KB_T - 1) / KB_T, p, h->t(nrhs, it), h->t(nnew, it));
     COLUMN(k_t_vert<1>, 2, p.iend, p.jstr, p.jend, p, h->t(nrhs, it), h->t(nnew, it), p.Akt[it >= 2 ? 1 : 0], h->f[ROMS_STFLX].ptr[it - 1], h->c.dt,
            it == 1 ? 1 : 0);
   }
