@@ -62,8 +62,11 @@ struct Orc {
   const size_t SXY = o.SXY;                                                                  \
   const int istr = 1, iend = Lm, jstr = 1, jend = Mm;                                        \
   const bool SWALL = !o.c.ns_periodic, NWALL = !o.c.ns_periodic;                             \
+  const bool WWALL = !o.c.ew_periodic, EWALL = !o.c.ew_periodic;                             \
   const int jstrR = SWALL ? jstr - 1 : jstr, jendR = NWALL ? jend + 1 : jend, jstrV = SWALL ? jstr + 1 : jstr; \
-  (void)N; (void)SXY; (void)istr; (void)iend; (void)jstr; (void)jend; (void)Mm; (void)jstrR; (void)jendR; (void)jstrV; (void)SWALL; (void)NWALL;
+  const int istrR = WWALL ? istr - 1 : istr, iendR = EWALL ? iend + 1 : iend, istrU = WWALL ? istr + 1 : istr; \
+  (void)N; (void)SXY; (void)istr; (void)iend; (void)jstr; (void)jend; (void)Mm; (void)jstrR; (void)jendR; (void)jstrV; (void)SWALL; (void)NWALL; \
+  (void)istrR; (void)iendR; (void)istrU; (void)WWALL; (void)EWALL;
 
 // ---------------------------------------------------------------------------------------------
 // exchange_xxx (mpi_exchanges.F:34-40) on a single subdomain: periodic wrap of the 2-cell halo
@@ -81,7 +84,7 @@ void exchange(const Orc& o, double* a, int nk) {
         A2(p, Lm + 2, j) = A2(p, 2, j);
       }
     if (o.c.ns_periodic)
-      for (int i = -1; i <= Lm + 2; ++i) {
+      for (int i = (o.c.ew_periodic ? -1 : 0); i <= (o.c.ew_periodic ? Lm + 2 : Lm + 1); ++i) {
         A2(p, i, -1) = A2(p, i, Mm - 1);
         A2(p, i, 0) = A2(p, i, Mm);
         A2(p, i, Mm + 1) = A2(p, i, 1);
@@ -175,17 +178,21 @@ void set_weights(Orc& o) {
 void setup_grid(Orc& o) {
   GEOM
   for (int j = (SWALL ? jstr - 1 : jstr - 2); j <= (NWALL ? jend + 1 : jend + 2); ++j)
-    for (int i = -1; i <= Lm + 2; ++i) A2(o.fomn, i, j) = A2(o.f, i, j) / (A2(o.pm, i, j) * A2(o.pn, i, j));
-  for (int j = jstrR; j <= jendR; ++j)
-    for (int i = istr; i <= iend; ++i) {
+    for (int i = (WWALL ? istr - 1 : istr - 2); i <= (EWALL ? iend + 1 : iend + 2); ++i)
+      A2(o.fomn, i, j) = A2(o.f, i, j) / (A2(o.pm, i, j) * A2(o.pn, i, j));
+  for (int j = jstrR; j <= jendR; ++j) {
+    for (int i = istrR; i <= iendR; ++i) {
       A2(o.dm_r, i, j) = 1.0 / A2(o.pm, i, j);
       A2(o.dn_r, i, j) = 1.0 / A2(o.pn, i, j);
+    }
+    for (int i = istr; i <= iendR; ++i) {
       A2(o.dm_u, i, j) = 2.0 / (A2(o.pm, i, j) + A2(o.pm, i - 1, j));
       A2(o.dn_u, i, j) = 2.0 / (A2(o.pn, i, j) + A2(o.pn, i - 1, j));
       A2(o.umask, i, j) = A2(o.rmask, i, j) * A2(o.rmask, i - 1, j);
     }
+  }
   for (int j = jstr; j <= jendR; ++j)
-    for (int i = istr; i <= iend; ++i) {
+    for (int i = istrR; i <= iendR; ++i) {
       A2(o.dm_v, i, j) = 2.0 / (A2(o.pm, i, j) + A2(o.pm, i, j - 1));
       A2(o.dn_v, i, j) = 2.0 / (A2(o.pn, i, j) + A2(o.pn, i, j - 1));
       A2(o.vmask, i, j) = A2(o.rmask, i, j) * A2(o.rmask, i, j - 1);
@@ -212,26 +219,26 @@ void set_depth(Orc& o) {
   vec& zeta = o.zeta[o.knew - 1];
   if (o.iic == 0) {
     for (int j = jstrR; j <= jendR; ++j)
-      for (int i = istr; i <= iend; ++i) A2(o.hinv, i, j) = 1.0 / (A2(o.h, i, j) + hc);
+      for (int i = istrR; i <= iendR; ++i) A2(o.hinv, i, j) = 1.0 / (A2(o.h, i, j) + hc);
     for (int j = jstrR; j <= jendR; ++j)
-      for (int i = istr; i <= iend; ++i)
+      for (int i = istr; i <= iendR; ++i)
         A2(o.DU_avg1, i, j) = 0.5 * (A2(o.h, i - 1, j) + A2(o.h, i, j) + A2(o.zeta[0], i, j) + A2(o.zeta[0], i - 1, j)) *
                               A2(o.dn_u, i, j) * (A2(o.ubar[0], i, j));
     for (int j = jstr; j <= jendR; ++j)
-      for (int i = istr; i <= iend; ++i)
+      for (int i = istrR; i <= iendR; ++i)
         A2(o.DV_avg1, i, j) = 0.5 * (A2(o.h, i, j) + A2(o.h, i, j - 1) + A2(o.zeta[0], i, j) + A2(o.zeta[0], i, j - 1)) *
                               A2(o.dm_v, i, j) * (A2(o.vbar[0], i, j));
   }
   const double ds = 1.0 / double(N);
 #pragma omp parallel for
   for (int j = jstrR; j <= jendR; ++j) {
-    for (int i = istr; i <= iend; ++i) AW(o.z_w, i, j, 0) = -A2(o.h, i, j);
+    for (int i = istrR; i <= iendR; ++i) AW(o.z_w, i, j, 0) = -A2(o.h, i, j);
     for (int k = 1; k <= N; ++k) {
       double cff_w = hc * ds * double(k - N);
       double cff_r = hc * ds * (double(k - N) - 0.5);
       double cff1_w = o.Cs_w[k];
       double cff1_r = o.Cs_r[k];
-      for (int i = istr; i <= iend; ++i) {
+      for (int i = istrR; i <= iendR; ++i) {
         AW(o.z_w, i, j, k) = A2(zeta, i, j) + (A2(zeta, i, j) + A2(o.h, i, j)) * (cff_w + cff1_w * A2(o.h, i, j)) * A2(o.hinv, i, j);
         A3(o.z_r, i, j, k) = A2(zeta, i, j) + (A2(zeta, i, j) + A2(o.h, i, j)) * (cff_r + cff1_r * A2(o.h, i, j)) * A2(o.hinv, i, j);
         A3(o.Hz, i, j, k) = AW(o.z_w, i, j, k) - AW(o.z_w, i, j, k - 1);
@@ -250,10 +257,10 @@ void set_HUV(Orc& o) {
 #pragma omp parallel for
   for (int k = 1; k <= N; ++k) {
     for (int j = jstrR; j <= jendR; ++j)
-      for (int i = istr; i <= iend; ++i)
+      for (int i = istr; i <= iendR; ++i)
         A3(o.FlxU, i, j, k) = 0.5 * (A3(o.Hz, i, j, k) + A3(o.Hz, i - 1, j, k)) * A2(o.dn_u, i, j) * (A3(u, i, j, k));
     for (int j = jstr; j <= jendR; ++j)
-      for (int i = istr; i <= iend; ++i)
+      for (int i = istrR; i <= iendR; ++i)
         A3(o.FlxV, i, j, k) = 0.5 * (A3(o.Hz, i, j, k) + A3(o.Hz, i, j - 1, k)) * A2(o.dm_v, i, j) * (A3(v, i, j, k));
   }
   ex3(o, o.FlxU); ex3(o, o.FlxV);
@@ -270,48 +277,48 @@ void set_HUV1(Orc& o) {
     vec DC((size_t)SX * (N + 1)), FC((size_t)SX * (N + 1));
 #pragma omp for
     for (int j = jstrR; j <= jendR; ++j) {
-      for (int i = istr; i <= iend; ++i) {
+      for (int i = istr; i <= iendR; ++i) {
         SL(DC, i, N) = 0.5 * (A3(o.Hz, i, j, N) + A3(o.Hz, i - 1, j, N)) * A2(o.dn_u, i, j);
         SL(DC, i, 0) = SL(DC, i, N);
         SL(FC, i, 0) = SL(DC, i, N) * A3(u, i, j, N);
       }
       for (int k = N - 1; k >= 1; --k)
-        for (int i = istr; i <= iend; ++i) {
+        for (int i = istr; i <= iendR; ++i) {
           SL(DC, i, k) = 0.5 * (A3(o.Hz, i, j, k) + A3(o.Hz, i - 1, j, k)) * A2(o.dn_u, i, j);
           SL(DC, i, 0) = SL(DC, i, 0) + SL(DC, i, k);
           SL(FC, i, 0) = SL(FC, i, 0) + SL(DC, i, k) * A3(u, i, j, k);
         }
       if (first) {
-        for (int i = istr; i <= iend; ++i) SL(FC, i, 0) = (SL(FC, i, 0) - A2(o.DU_avg1, i, j)) / SL(DC, i, 0);
+        for (int i = istr; i <= iendR; ++i) SL(FC, i, 0) = (SL(FC, i, 0) - A2(o.DU_avg1, i, j)) / SL(DC, i, 0);
       } else {
-        for (int i = istr; i <= iend; ++i)
+        for (int i = istr; i <= iendR; ++i)
           SL(FC, i, 0) = (SL(FC, i, 0) - 3.63 * A2(o.DU_avg1, i, j) + 4.47 * A2(o.DU_avg2, i, j) - 2.05 * A2(o.DU_avg_bak, i, j)) / SL(DC, i, 0);
       }
       for (int k = 1; k <= N; ++k)
-        for (int i = istr; i <= iend; ++i) {
+        for (int i = istr; i <= iendR; ++i) {
           A3(u, i, j, k) = (A3(u, i, j, k) - SL(FC, i, 0)) * A2(o.umask, i, j);
           A3(o.FlxU, i, j, k) = SL(DC, i, k) * (A3(u, i, j, k));
         }
       if (j < jstr) continue;   // set_depth.F: "if (j >= jstr)" guards the v part
-      for (int i = istr; i <= iend; ++i) {
+      for (int i = istrR; i <= iendR; ++i) {
         SL(DC, i, N) = 0.5 * (A3(o.Hz, i, j, N) + A3(o.Hz, i, j - 1, N)) * A2(o.dm_v, i, j);
         SL(DC, i, 0) = SL(DC, i, N);
         SL(FC, i, 0) = SL(DC, i, N) * A3(v, i, j, N);
       }
       for (int k = N - 1; k >= 1; --k)
-        for (int i = istr; i <= iend; ++i) {
+        for (int i = istrR; i <= iendR; ++i) {
           SL(DC, i, k) = 0.5 * (A3(o.Hz, i, j, k) + A3(o.Hz, i, j - 1, k)) * A2(o.dm_v, i, j);
           SL(DC, i, 0) = SL(DC, i, 0) + SL(DC, i, k);
           SL(FC, i, 0) = SL(FC, i, 0) + SL(DC, i, k) * A3(v, i, j, k);
         }
       if (first) {
-        for (int i = istr; i <= iend; ++i) SL(FC, i, 0) = (SL(FC, i, 0) - A2(o.DV_avg1, i, j)) / SL(DC, i, 0);
+        for (int i = istrR; i <= iendR; ++i) SL(FC, i, 0) = (SL(FC, i, 0) - A2(o.DV_avg1, i, j)) / SL(DC, i, 0);
       } else {
-        for (int i = istr; i <= iend; ++i)
+        for (int i = istrR; i <= iendR; ++i)
           SL(FC, i, 0) = (SL(FC, i, 0) - 3.63 * A2(o.DV_avg1, i, j) + 4.47 * A2(o.DV_avg2, i, j) - 2.05 * A2(o.DV_avg_bak, i, j)) / SL(DC, i, 0);
       }
       for (int k = 1; k <= N; ++k)
-        for (int i = istr; i <= iend; ++i) {
+        for (int i = istrR; i <= iendR; ++i) {
           A3(v, i, j, k) = (A3(v, i, j, k) - SL(FC, i, 0)) * A2(o.vmask, i, j);
           A3(o.FlxV, i, j, k) = SL(DC, i, k) * (A3(v, i, j, k));
         }
@@ -377,12 +384,25 @@ void omega(Orc& o) {
   if (NWALL)
     for (int k = 0; k <= N; ++k)
       for (int i = istr; i <= iend; ++i) { AW(o.We, i, jend + 1, k) = AW(o.We, i, jend, k); AW(o.Wi, i, jend + 1, k) = AW(o.Wi, i, jend, k); }
+  if (WWALL)
+    for (int k = 0; k <= N; ++k)
+      for (int j = jstr; j <= jend; ++j) { AW(o.We, istr - 1, j, k) = AW(o.We, istr, j, k); AW(o.Wi, istr - 1, j, k) = AW(o.Wi, istr, j, k); }
+  if (EWALL)
+    for (int k = 0; k <= N; ++k)
+      for (int j = jstr; j <= jend; ++j) { AW(o.We, iend + 1, j, k) = AW(o.We, iend, j, k); AW(o.Wi, iend + 1, j, k) = AW(o.Wi, iend, j, k); }
+  for (int k = 0; k <= N; ++k) {      // corners (omega.F:205-231)
+    if (WWALL && SWALL) { AW(o.We, istr - 1, jstr - 1, k) = AW(o.We, istr, jstr, k); AW(o.Wi, istr - 1, jstr - 1, k) = AW(o.Wi, istr, jstr, k); }
+    if (WWALL && NWALL) { AW(o.We, istr - 1, jend + 1, k) = AW(o.We, istr, jend, k); AW(o.Wi, istr - 1, jend + 1, k) = AW(o.Wi, istr, jend, k); }
+    if (EWALL && SWALL) { AW(o.We, iend + 1, jstr - 1, k) = AW(o.We, iend, jstr, k); AW(o.Wi, iend + 1, jstr - 1, k) = AW(o.Wi, iend, jstr, k); }
+    if (EWALL && NWALL) { AW(o.We, iend + 1, jend + 1, k) = AW(o.We, iend, jend, k); AW(o.Wi, iend + 1, jend + 1, k) = AW(o.Wi, iend, jend, k); }
+  }
   exw(o, o.We); exw(o, o.Wi);
 }
 
 // rho_eos.F:26-409 rho_eos_tile (linear branch :316-339, NONLIN+SPLIT branch :195-260; rhoA/rhoS :364-395)
 void rho_eos(Orc& o, int tidx) {
   GEOM
+  const int iX0 = WWALL ? istr - 1 : istr - 2, iX1 = EWALL ? iend + 1 : iend + 2;   // extended bounds (compute_extended_bounds.h)
   const double rho0 = o.c.rho0, qp2 = 0.0000172;
   vec& T = o.t[tidx - 1][0];
   const double r00 = 999.842594, r01 = 6.793952e-2, r02 = -9.095290e-3, r03 = 1.001685e-4, r04 = -1.120083e-6,
@@ -402,7 +422,7 @@ void rho_eos(Orc& o, int tidx) {
       double cff = o.c.Tcoef * o.c.T0;
       if (o.c.salinity) cff = o.c.Tcoef * o.c.T0 - o.c.Scoef * o.c.S0;   // rho_eos.F:318-322
       for (int k = 1; k <= N; ++k)
-        for (int i = istr - 2; i <= iend + 2; ++i) {
+        for (int i = iX0; i <= iX1; ++i) {
           A3(o.rho1, i, j, k) = cff - o.c.Tcoef * A3(T, i, j, k);
           if (o.c.salinity) A3(o.rho1, i, j, k) = A3(o.rho1, i, j, k) + o.c.Scoef * A3(o.t[tidx - 1][1], i, j, k);
           A3(o.rho1, i, j, k) = A3(o.rho1, i, j, k) * A2(o.rmask, i, j);
@@ -410,7 +430,7 @@ void rho_eos(Orc& o, int tidx) {
     } else {
       vec& S = o.t[tidx - 1][1];
       for (int k = 1; k <= N; ++k)
-        for (int i = istr - 2; i <= iend + 2; ++i) {
+        for (int i = iX0; i <= iX1; ++i) {
           double Tt = A3(T, i, j, k);
           double Ts = A3(S, i, j, k);
           double sqrtTs = sqrt(std::max(0.0, Ts));
@@ -422,7 +442,7 @@ void rho_eos(Orc& o, int tidx) {
           A3(o.qp1, i, j, k) = 0.1 * (rho0 + A3(o.rho1, i, j, k)) * (K0_Duk - K0) / ((K00 + K0) * (K00 + K0_Duk)) * A2(o.rmask, i, j);
         }
     }
-    for (int i = istr - 2; i <= iend + 2; ++i) {
+    for (int i = iX0; i <= iX1; ++i) {
       double cff;
       if (nonlin) {
         double dpth = -A3(o.z_r, i, j, N);
@@ -432,7 +452,7 @@ void rho_eos(Orc& o, int tidx) {
       A2(o.rhoA, i, j) = cff;
     }
     for (int k = N - 1; k >= 1; --k)
-      for (int i = istr - 2; i <= iend + 2; ++i) {
+      for (int i = iX0; i <= iX1; ++i) {
         double cff;
         if (nonlin) {
           double dpth = -A3(o.z_r, i, j, k);
@@ -442,7 +462,7 @@ void rho_eos(Orc& o, int tidx) {
         A2(o.rhoA, i, j) = A2(o.rhoA, i, j) + cff;
       }
     double cff1 = 1.0 / rho0;
-    for (int i = istr - 2; i <= iend + 2; ++i) {
+    for (int i = iX0; i <= iX1; ++i) {
       double cff = 1.0 / (AW(o.z_w, i, j, N) - AW(o.z_w, i, j, 0));
       A2(o.rhoA, i, j) = cff * cff1 * A2(o.rhoA, i, j);
       A2(o.rhoS, i, j) = 2.0 * cff * cff * cff1 * A2(o.rhoS, i, j);
@@ -455,7 +475,7 @@ void prsgrd(Orc& o) {
   GEOM
   const double g = o.c.g, rho0 = o.c.rho0, qp2 = 0.0000172;
   const double OneFifth = 0.2, OneTwelfth = 1.0 / 12.0, epsil = 0.0;
-  const int imin = istr - 1, imax = iend + 1;
+  const int imin = WWALL ? istrU : istrU - 1, imax = EWALL ? iend : iend + 1;
   const int jmin = SWALL ? jstrV : jstrV - 1, jmax = NWALL ? jend : jend + 1;   // prsgrd.F:96-131
   const double grho = g / rho0, HalfGRho = 0.5 * grho;
   const int nonlin = o.c.nonlin_eos;
@@ -521,8 +541,12 @@ void prsgrd(Orc& o) {
           } else
             A2(rx, i, j) = (A3(rho, i, j, k) - A3(rho, i - 1, j, k)) * A2(o.umask, i, j);
         }
+      if (WWALL)
+        for (int j = jstr; j <= jend; ++j) { A2(FC, imin - 1, j) = A2(FC, imin, j); A2(rx, imin - 1, j) = A2(rx, imin, j); }
+      if (EWALL)
+        for (int j = jstr; j <= jend; ++j) { A2(FC, imax + 1, j) = A2(FC, imax, j); A2(rx, imax + 1, j) = A2(rx, imax, j); }
       for (int j = jstr; j <= jend; ++j) {
-        for (int i = istr - 1; i <= iend; ++i) {
+        for (int i = istrU - 1; i <= iend; ++i) {
           double cff = 2.0 * A2(FC, i, j) * A2(FC, i + 1, j);
           if (cff > epsil) A2(dZx, i, j) = cff / (A2(FC, i, j) + A2(FC, i + 1, j));
           else A2(dZx, i, j) = 0.0;
@@ -531,7 +555,7 @@ void prsgrd(Orc& o) {
           else A2(dRx, i, j) = 0.0;
           if (nonlin) A2(dRx, i, j) = A2(dRx, i, j) - A3(o.qp1, i, j, k) * A2(dZx, i, j) * (1.0 + 2.0 * qp2 * A3(o.z_r, i, j, k));
         }
-        for (int i = istr; i <= iend; ++i)
+        for (int i = istrU; i <= iend; ++i)
           A3(o.ru, i, j, k) = 0.5 * (A3(o.Hz, i, j, k) + A3(o.Hz, i - 1, j, k)) * A2(o.dn_u, i, j) *
                               (A3(P, i - 1, j, k) - A3(P, i, j, k) -
                                HalfGRho * ((A3(rho, i, j, k) + A3(rho, i - 1, j, k)) * (A3(o.z_r, i, j, k) - A3(o.z_r, i - 1, j, k)) -
@@ -579,24 +603,28 @@ void horiz_rhs_uv(Orc& o, int k, const vec& u, const vec& v, bool upstream, vec&
   GEOM
   const double delta = 0.1666666666666667, gamma = 0.3333333333333333;
   for (int j = jstrV - 1; j <= jend; ++j)
-    for (int i = istr - 1; i <= iend; ++i) {
+    for (int i = istrU - 1; i <= iend; ++i) {
       double cff = 0.5 * A3(o.Hz, i, j, k) * (A2(o.fomn, i, j));
       A2(UFx, i, j) = cff * (A3(v, i, j, k) + A3(v, i, j + 1, k));
       A2(VFe, i, j) = cff * (A3(u, i, j, k) + A3(u, i + 1, j, k));
     }
   for (int j = jstr; j <= jend; ++j)
-    for (int i = istr; i <= iend; ++i) A3(o.ru, i, j, k) = A3(o.ru, i, j, k) + 0.5 * (A2(UFx, i, j) + A2(UFx, i - 1, j));
+    for (int i = istrU; i <= iend; ++i) A3(o.ru, i, j, k) = A3(o.ru, i, j, k) + 0.5 * (A2(UFx, i, j) + A2(UFx, i - 1, j));
   for (int j = jstrV; j <= jend; ++j)
     for (int i = istr; i <= iend; ++i) A3(o.rv, i, j, k) = A3(o.rv, i, j, k) - 0.5 * (A2(VFe, i, j) + A2(VFe, i, j - 1));
-  const int imin = istr - 1, imax = iend + 1;
+  int imin = WWALL ? istrU : istrU - 1, imax = EWALL ? iend : iend + 1;
   int jmin, jmax;
   for (int j = jstr; j <= jend; ++j)
     for (int i = imin; i <= imax; ++i) {
       A2(wrk1, i, j) = A3(u, i - 1, j, k) - 2.0 * A3(u, i, j, k) + A3(u, i + 1, j, k);
       A2(wrk2, i, j) = A3(o.FlxU, i - 1, j, k) - 2.0 * A3(o.FlxU, i, j, k) + A3(o.FlxU, i + 1, j, k);
     }
+  if (WWALL)
+    for (int j = jstr; j <= jend; ++j) { A2(wrk1, istrU - 1, j) = A2(wrk1, istrU, j); A2(wrk2, istrU - 1, j) = A2(wrk2, istrU, j); }
+  if (EWALL)
+    for (int j = jstr; j <= jend; ++j) { A2(wrk1, iend + 1, j) = A2(wrk1, iend, j); A2(wrk2, iend + 1, j) = A2(wrk2, iend, j); }
   for (int j = jstr; j <= jend; ++j)
-    for (int i = istr - 1; i <= iend; ++i) {
+    for (int i = istrU - 1; i <= iend; ++i) {
       if (upstream) {
         double cff = A3(o.FlxU, i, j, k) + A3(o.FlxU, i + 1, j, k) - delta * (A2(wrk2, i, j) + A2(wrk2, i + 1, j));
         A2(UFx, i, j) = 0.25 * (cff * (A3(u, i, j, k) + A3(u, i + 1, j, k)) - gamma * (std::max(cff, 0.0) * A2(wrk1, i, j) + std::min(cff, 0.0) * A2(wrk1, i + 1, j)));
@@ -625,15 +653,15 @@ void horiz_rhs_uv(Orc& o, int k, const vec& u, const vec& v, bool upstream, vec&
     }
   jmin = SWALL ? jstr : jstr - 1; jmax = NWALL ? jend : jend + 1;
   for (int j = jmin; j <= jmax; ++j)
-    for (int i = istr; i <= iend; ++i) A2(wrk1, i, j) = A3(u, i, j - 1, k) - 2.0 * A3(u, i, j, k) + A3(u, i, j + 1, k);
+    for (int i = istrU; i <= iend; ++i) A2(wrk1, i, j) = A3(u, i, j - 1, k) - 2.0 * A3(u, i, j, k) + A3(u, i, j + 1, k);
   if (SWALL)
-    for (int i = istr; i <= iend; ++i) A2(wrk1, i, jstr - 1) = A2(wrk1, i, jstr);
+    for (int i = istrU; i <= iend; ++i) A2(wrk1, i, jstr - 1) = A2(wrk1, i, jstr);
   if (NWALL)
-    for (int i = istr; i <= iend; ++i) A2(wrk1, i, jend + 1) = A2(wrk1, i, jend);
+    for (int i = istrU; i <= iend; ++i) A2(wrk1, i, jend + 1) = A2(wrk1, i, jend);
   for (int j = jstr; j <= jend + 1; ++j)
-    for (int i = istr - 1; i <= iend; ++i) A2(wrk2, i, j) = A3(o.FlxV, i - 1, j, k) - 2.0 * A3(o.FlxV, i, j, k) + A3(o.FlxV, i + 1, j, k);
+    for (int i = istrU - 1; i <= iend; ++i) A2(wrk2, i, j) = A3(o.FlxV, i - 1, j, k) - 2.0 * A3(o.FlxV, i, j, k) + A3(o.FlxV, i + 1, j, k);
   for (int j = jstr; j <= jend + 1; ++j)
-    for (int i = istr; i <= iend; ++i) {
+    for (int i = istrU; i <= iend; ++i) {
       if (upstream) {
         double cff = A3(o.FlxV, i, j, k) + A3(o.FlxV, i - 1, j, k) - delta * (A2(wrk2, i, j) + A2(wrk2, i - 1, j));
         A2(UFe, i, j) = 0.25 * (cff * (A3(u, i, j, k) + A3(u, i, j - 1, k)) - gamma * (std::max(cff, 0.0) * A2(wrk1, i, j - 1) + std::min(cff, 0.0) * A2(wrk1, i, j)));
@@ -641,8 +669,13 @@ void horiz_rhs_uv(Orc& o, int k, const vec& u, const vec& v, bool upstream, vec&
         A2(UFe, i, j) = 0.25 * (A3(u, i, j, k) + A3(u, i, j - 1, k) - delta * (A2(wrk1, i, j) + A2(wrk1, i, j - 1))) *
                         (A3(o.FlxV, i, j, k) + A3(o.FlxV, i - 1, j, k) - delta * (A2(wrk2, i, j) + A2(wrk2, i - 1, j)));
     }
+  imin = WWALL ? istr : istr - 1; imax = EWALL ? iend : iend + 1;
   for (int j = jstrV; j <= jend; ++j)
     for (int i = imin; i <= imax; ++i) A2(wrk1, i, j) = A3(v, i - 1, j, k) - 2.0 * A3(v, i, j, k) + A3(v, i + 1, j, k);
+  if (WWALL)
+    for (int j = jstrV; j <= jend; ++j) A2(wrk1, istr - 1, j) = A2(wrk1, istr, j);
+  if (EWALL)
+    for (int j = jstrV; j <= jend; ++j) A2(wrk1, iend + 1, j) = A2(wrk1, iend, j);
   for (int j = jstrV - 1; j <= jend; ++j)
     for (int i = istr; i <= iend + 1; ++i) A2(wrk2, i, j) = A3(o.FlxU, i, j - 1, k) - 2.0 * A3(o.FlxU, i, j, k) + A3(o.FlxU, i, j + 1, k);
   for (int j = jstrV; j <= jend; ++j)
@@ -655,7 +688,7 @@ void horiz_rhs_uv(Orc& o, int k, const vec& u, const vec& v, bool upstream, vec&
                         (A3(o.FlxU, i, j, k) + A3(o.FlxU, i, j - 1, k) - delta * (A2(wrk2, i, j) + A2(wrk2, i, j - 1)));
     }
   for (int j = jstr; j <= jend; ++j)
-    for (int i = istr; i <= iend; ++i)
+    for (int i = istrU; i <= iend; ++i)
       A3(o.ru, i, j, k) = A3(o.ru, i, j, k) - A2(UFx, i, j) + A2(UFx, i - 1, j) - A2(UFe, i, j + 1) + A2(UFe, i, j);
   for (int j = jstrV; j <= jend; ++j)
     for (int i = istr; i <= iend; ++i)
@@ -665,31 +698,31 @@ void horiz_rhs_uv(Orc& o, int k, const vec& u, const vec& v, bool upstream, vec&
 // compute_vert_rhs_uv_terms.h:1-188 (SPLINE_UV) for one j-row: adds vertical advection to ru, rv
 void vert_rhs_uv(Orc& o, int j, const vec& u, const vec& v, vec& FC, vec& CF, vec& DC) {
   GEOM
-  for (int i = istr; i <= iend; ++i) {
+  for (int i = istrU; i <= iend; ++i) {
     SL(DC, i, 1) = 0.5625 * (A3(o.Hz, i, j, 1) + A3(o.Hz, i - 1, j, 1)) - 0.0625 * (A3(o.Hz, i + 1, j, 1) + A3(o.Hz, i - 2, j, 1));
     SL(CF, i, 1) = 1.0;
     SL(FC, i, 0) = 2.0 * A3(u, i, j, 1);
   }
   for (int k = 1; k <= N - 1; ++k)
-    for (int i = istr; i <= iend; ++i) {
+    for (int i = istrU; i <= iend; ++i) {
       SL(DC, i, k + 1) = 0.5625 * (A3(o.Hz, i, j, k + 1) + A3(o.Hz, i - 1, j, k + 1)) - 0.0625 * (A3(o.Hz, i + 1, j, k + 1) + A3(o.Hz, i - 2, j, k + 1));
       double cff = 1.0 / (2.0 * SL(DC, i, k) + SL(DC, i, k + 1) * (2.0 - SL(CF, i, k)));
       SL(CF, i, k + 1) = cff * SL(DC, i, k);
       SL(FC, i, k) = cff * (3.0 * (SL(DC, i, k) * A3(u, i, j, k + 1) + SL(DC, i, k + 1) * A3(u, i, j, k)) - SL(DC, i, k + 1) * SL(FC, i, k - 1));
     }
-  for (int i = istr; i <= iend; ++i) {
+  for (int i = istrU; i <= iend; ++i) {
     SL(FC, i, N) = (2.0 * A3(u, i, j, N) - SL(FC, i, N - 1)) / (1.0 - SL(CF, i, N));
     SL(DC, i, N) = 0.0;
   }
   for (int k = N - 1; k >= 1; --k)
-    for (int i = istr; i <= iend; ++i) {
+    for (int i = istrU; i <= iend; ++i) {
       SL(FC, i, k) = SL(FC, i, k) - SL(CF, i, k + 1) * SL(FC, i, k + 1);
       SL(DC, i, k) = SL(FC, i, k) * 0.5 * (AW(o.We, i, j, k) + AW(o.We, i - 1, j, k) -
                                            0.125 * ((AW(o.We, i + 1, j, k) - AW(o.We, i, j, k)) * A2(o.umask, i + 1, j) -
                                                     (AW(o.We, i - 1, j, k) - AW(o.We, i - 2, j, k)) * A2(o.umask, i - 1, j)));
       A3(o.ru, i, j, k + 1) = A3(o.ru, i, j, k + 1) - SL(DC, i, k + 1) + SL(DC, i, k);
     }
-  for (int i = istr; i <= iend; ++i) A3(o.ru, i, j, 1) = A3(o.ru, i, j, 1) - SL(DC, i, 1);
+  for (int i = istrU; i <= iend; ++i) A3(o.ru, i, j, 1) = A3(o.ru, i, j, 1) - SL(DC, i, 1);
   if (j < jstrV) return;   // "if (j >= jstrV)": no v-row on a southern wall
   // v
   for (int i = istr; i <= iend; ++i) {
@@ -723,10 +756,14 @@ void vert_rhs_uv(Orc& o, int j, const vec& u, const vec& v, vec& FC, vec& CF, ve
 // true: UP3 (step3d_t_ISO.F:196).
 void horiz_tracer_fluxes(Orc& o, int k, const vec& t, bool upstream, vec& FX, vec& FE, vec& wrk1) {
   GEOM
-  const int imin = istr - 1, imax = iend + 1;
+  const int imin = WWALL ? istr : istr - 1, imax = EWALL ? iend : iend + 1;
   const int jmin = SWALL ? jstr : jstr - 1, jmax = NWALL ? jend : jend + 1;   // compute_horiz_tracer_fluxes.h:118-160
   for (int j = jstr; j <= jend; ++j)
     for (int i = imin; i <= imax + 1; ++i) A2(FX, i, j) = (A3(t, i, j, k) - A3(t, i - 1, j, k)) * A2(o.umask, i, j);
+  if (WWALL)
+    for (int j = jstr; j <= jend; ++j) A2(FX, istr - 1, j) = A2(FX, istr, j);
+  if (EWALL)
+    for (int j = jstr; j <= jend; ++j) A2(FX, iend + 2, j) = A2(FX, iend + 1, j);
   if (upstream) {
     for (int j = jstr; j <= jend; ++j)
       for (int i = istr - 1; i <= iend + 1; ++i) A2(wrk1, i, j) = A2(FX, i + 1, j) - A2(FX, i, j);
@@ -788,29 +825,41 @@ void vert_tracer_flux(Orc& o, int j, const vec& t, vec& FC, vec& CF) {
   }
 }
 
-// Lateral boundary conditions on closed (wall) northern/southern edges; E-W is periodic or decomposed.
+// Lateral boundary conditions on closed (wall) edges, incl. the corner rules of a fully closed basin.
 // zetabc.F:3 (gradient), u2dbc_im.F:150-152,359,442 / u3dbc_im.F:293-295 (gamma2 slip), v2dbc_im.F / v3dbc_im.F
 // (no normal flow), t3dbc_im.F:86-96 (gradient).  Nothing happens on periodic edges.
 void zetabc(Orc& o, vec& zeta_new) {
   GEOM
-  if (SWALL) for (int i = istr - 1; i <= iend; ++i) A2(zeta_new, i, jstr - 1) = A2(zeta_new, i, jstr) * A2(o.rmask, i, jstr - 1);
-  if (NWALL) for (int i = istr - 1; i <= iend; ++i) A2(zeta_new, i, jend + 1) = A2(zeta_new, i, jend) * A2(o.rmask, i, jend + 1);
+  if (WWALL) for (int j = jstrV - 1; j <= jend; ++j) A2(zeta_new, istr - 1, j) = A2(zeta_new, istr, j) * A2(o.rmask, istr - 1, j);
+  if (EWALL) for (int j = jstrV - 1; j <= jend; ++j) A2(zeta_new, iend + 1, j) = A2(zeta_new, iend, j) * A2(o.rmask, iend + 1, j);
+  if (SWALL) for (int i = istrU - 1; i <= iend; ++i) A2(zeta_new, i, jstr - 1) = A2(zeta_new, i, jstr) * A2(o.rmask, i, jstr - 1);
+  if (NWALL) for (int i = istrU - 1; i <= iend; ++i) A2(zeta_new, i, jend + 1) = A2(zeta_new, i, jend) * A2(o.rmask, i, jend + 1);
+  if (SWALL && WWALL) A2(zeta_new, istr - 1, jstr - 1) = 0.5 * (A2(zeta_new, istr, jstr - 1) + A2(zeta_new, istr - 1, jstr));
+  if (SWALL && EWALL) A2(zeta_new, iend + 1, jstr - 1) = 0.5 * (A2(zeta_new, iend, jstr - 1) + A2(zeta_new, iend + 1, jstr));
+  if (NWALL && WWALL) A2(zeta_new, istr - 1, jend + 1) = 0.5 * (A2(zeta_new, istr, jend + 1) + A2(zeta_new, istr - 1, jend));
+  if (NWALL && EWALL) A2(zeta_new, iend + 1, jend + 1) = 0.5 * (A2(zeta_new, iend, jend + 1) + A2(zeta_new, iend + 1, jend));
 }
 void u2dbc(Orc& o, vec& ubar) {
   GEOM
-  if (SWALL) for (int i = istr; i <= iend; ++i) A2(ubar, i, jstr - 1) = o.c.gamma2 * A2(ubar, i, jstr) * A2(o.umask, i, jstr - 1);
-  if (NWALL) for (int i = istr; i <= iend; ++i) A2(ubar, i, jend + 1) = o.c.gamma2 * A2(ubar, i, jend) * A2(o.umask, i, jend + 1);
+  if (WWALL) for (int j = jstr; j <= jend; ++j) A2(ubar, istr, j) = 0.0;
+  if (EWALL) for (int j = jstr; j <= jend; ++j) A2(ubar, iend + 1, j) = 0.0;
+  if (SWALL) for (int i = istr; i <= iendR; ++i) A2(ubar, i, jstr - 1) = o.c.gamma2 * A2(ubar, i, jstr) * A2(o.umask, i, jstr - 1);
+  if (NWALL) for (int i = istr; i <= iendR; ++i) A2(ubar, i, jend + 1) = o.c.gamma2 * A2(ubar, i, jend) * A2(o.umask, i, jend + 1);
 }
 void v2dbc(Orc& o, vec& vbar) {
   GEOM
   if (SWALL) for (int i = istr; i <= iend; ++i) A2(vbar, i, jstr) = 0.0;
   if (NWALL) for (int i = istr; i <= iend; ++i) A2(vbar, i, jend + 1) = 0.0;
+  if (WWALL) for (int j = jstr; j <= jendR; ++j) A2(vbar, istr - 1, j) = o.c.gamma2 * A2(vbar, istr, j) * A2(o.vmask, istr - 1, j);
+  if (EWALL) for (int j = jstr; j <= jendR; ++j) A2(vbar, iend + 1, j) = o.c.gamma2 * A2(vbar, iend, j) * A2(o.vmask, iend + 1, j);
 }
 void u3dbc(Orc& o, vec& u) {
   GEOM
   for (int k = 1; k <= N; ++k) {
-    if (SWALL) for (int i = istr; i <= iend; ++i) A3(u, i, jstr - 1, k) = o.c.gamma2 * A3(u, i, jstr, k) * A2(o.umask, i, jstr - 1);
-    if (NWALL) for (int i = istr; i <= iend; ++i) A3(u, i, jend + 1, k) = o.c.gamma2 * A3(u, i, jend, k) * A2(o.umask, i, jend + 1);
+    if (WWALL) for (int j = jstr; j <= jend; ++j) A3(u, istr, j, k) = 0.0;
+    if (EWALL) for (int j = jstr; j <= jend; ++j) A3(u, iend + 1, j, k) = 0.0;
+    if (SWALL) for (int i = istr; i <= iendR; ++i) A3(u, i, jstr - 1, k) = o.c.gamma2 * A3(u, i, jstr, k) * A2(o.umask, i, jstr - 1);
+    if (NWALL) for (int i = istr; i <= iendR; ++i) A3(u, i, jend + 1, k) = o.c.gamma2 * A3(u, i, jend, k) * A2(o.umask, i, jend + 1);
   }
 }
 void v3dbc(Orc& o, vec& v) {
@@ -818,14 +867,31 @@ void v3dbc(Orc& o, vec& v) {
   for (int k = 1; k <= N; ++k) {
     if (SWALL) for (int i = istr; i <= iend; ++i) A3(v, i, jstr, k) = 0.0;
     if (NWALL) for (int i = istr; i <= iend; ++i) A3(v, i, jend + 1, k) = 0.0;
+    if (WWALL) for (int j = jstr; j <= jendR; ++j) A3(v, istr - 1, j, k) = o.c.gamma2 * A3(v, istr, j, k) * A2(o.vmask, istr - 1, j);
+    if (EWALL) for (int j = jstr; j <= jendR; ++j) A3(v, iend + 1, j, k) = o.c.gamma2 * A3(v, iend, j, k) * A2(o.vmask, iend + 1, j);
   }
 }
 void t3dbc(Orc& o, vec& t) {
   GEOM
   for (int k = 1; k <= N; ++k) {
+    if (WWALL) for (int j = jstr; j <= jend; ++j) A3(t, istr - 1, j, k) = A3(t, istr, j, k) * A2(o.rmask, istr - 1, j);
+    if (EWALL) for (int j = jstr; j <= jend; ++j) A3(t, iend + 1, j, k) = A3(t, iend, j, k) * A2(o.rmask, iend + 1, j);
     if (SWALL) for (int i = istr; i <= iend; ++i) A3(t, i, jstr - 1, k) = A3(t, i, jstr, k) * A2(o.rmask, i, jstr - 1);
     if (NWALL) for (int i = istr; i <= iend; ++i) A3(t, i, jend + 1, k) = A3(t, i, jend, k) * A2(o.rmask, i, jend + 1);
   }
+  // corners: mask-weighted mean of the two neighbouring edge values (t3dbc_im.F:81-144)
+  auto corner = [&](int ic, int jc, int ia, int ja, int ib, int jb) {   // (ic,jc) from (ia,ja) and (ib,jb)
+    double cff = A2(o.rmask, ia, ja) + A2(o.rmask, ib, jb);
+    if (cff > 0.0) {
+      cff = 1.0 / cff;
+      for (int k = 1; k <= N; ++k) A3(t, ic, jc, k) = cff * (A2(o.rmask, ia, ja) * A3(t, ia, ja, k) + A2(o.rmask, ib, jb) * A3(t, ib, jb, k));
+    } else
+      for (int k = 1; k <= N; ++k) A3(t, ic, jc, k) = 0.0;
+  };
+  if (SWALL && WWALL) corner(istr - 1, jstr - 1, istr, jstr - 1, istr - 1, jstr);
+  if (SWALL && EWALL) corner(iend + 1, jstr - 1, iend, jstr - 1, iend + 1, jstr);
+  if (NWALL && WWALL) corner(istr - 1, jend + 1, istr, jend + 1, istr - 1, jend);
+  if (NWALL && EWALL) corner(iend + 1, jend + 1, iend, jend + 1, iend + 1, jend);
 }
 
 // pre_step3d4S.F:23-742 pre_step3d_tile
@@ -854,7 +920,7 @@ void pre_step3d(Orc& o) {
     for (int k = 1; k <= N; ++k) {
       double cff = 0.5 * dtau;
       for (int j = jstrV - 1; j <= jend; ++j)
-        for (int i = istr - 1; i <= iend; ++i) {
+        for (int i = istrU - 1; i <= iend; ++i) {
           double FlxDiv = cff * A2(o.pm, i, j) * A2(o.pn, i, j) *
                           (A3(o.FlxU, i + 1, j, k) - A3(o.FlxU, i, j, k) + A3(o.FlxV, i, j + 1, k) - A3(o.FlxV, i, j, k) +
                            AW(o.We, i, j, k) + AW(o.Wi, i, j, k) - AW(o.We, i, j, k - 1) - AW(o.Wi, i, j, k - 1));
@@ -883,7 +949,7 @@ void pre_step3d(Orc& o) {
     const double vonKar = 0.41;
     if (o.c.Zob > 0.0) {
       for (int j = jstrV - 1; j <= jend; ++j)
-        for (int i = istr - 1; i <= iend; ++i) {
+        for (int i = istrU - 1; i <= iend; ++i) {
           double cff = sqrt(0.333333333333 * (A3(us, i, j, 1) * A3(us, i, j, 1) + A3(us, i + 1, j, 1) * A3(us, i + 1, j, 1) + A3(us, i, j, 1) * A3(us, i + 1, j, 1) +
                                               A3(vs, i, j, 1) * A3(vs, i, j, 1) + A3(vs, i, j + 1, 1) * A3(vs, i, j + 1, 1) + A3(vs, i, j, 1) * A3(vs, i, j + 1, 1)));
           double lg = vonKar / log(1.0 + 0.5 * A3(o.Hz, i, j, 1) / o.c.Zob);
@@ -891,13 +957,13 @@ void pre_step3d(Orc& o) {
         }
     } else {
       for (int j = jstrV - 1; j <= jend; ++j)
-        for (int i = istr - 1; i <= iend; ++i) {
+        for (int i = istrU - 1; i <= iend; ++i) {
           A2(r_D_prv, i, j) = o.c.rdrg;
           A2(r_D_prv, i, j) = std::min(A2(r_D_prv, i, j), 0.8 * A3(o.Hz, i, j, 1) / dt);
         }
     }
     for (int j = jstrV - 1; j <= jend; ++j)
-      for (int i = istr - 1; i <= iend; ++i) A2(o.r_D, i, j) = A2(r_D_prv, i, j);
+      for (int i = istrU - 1; i <= iend; ++i) A2(o.r_D, i, j) = A2(r_D_prv, i, j);
   }
   const vec& wrk1 = r_D_prv;
 #pragma omp parallel
@@ -938,20 +1004,20 @@ void pre_step3d(Orc& o) {
       // u: implicit vertical viscosity/advection, pre_step3d4S.F:362-424
       for (int dir = 0; dir < 2; ++dir) {
         if (dir == 1 && j < jstrV) continue;
-        const int di = dir == 0 ? 1 : 0, dj = dir == 0 ? 0 : 1;
+        const int di = dir == 0 ? 1 : 0, dj = dir == 0 ? 0 : 1, i0 = dir == 0 ? istrU : istr;
         vec& un = dir == 0 ? o.u[nnew - 1] : o.v[nnew - 1];
         vec& us = dir == 0 ? o.u[nstp - 1] : o.v[nstp - 1];
         vec& ui = dir == 0 ? o.u[indx - 1] : o.v[indx - 1];
         vec& r = dir == 0 ? o.ru : o.rv;
         const vec& strs = dir == 0 ? o.sustr : o.svstr;
-        for (int i = istr; i <= iend; ++i)
+        for (int i = i0; i <= iend; ++i)
           SL(DC, i, 0) = dtau * 0.25 * (A2(o.pm, i, j) + A2(o.pm, i - di, j - dj)) * (A2(o.pn, i, j) + A2(o.pn, i - di, j - dj));
         for (int k = 1; k <= N; ++k)
-          for (int i = istr; i <= iend; ++i) {
+          for (int i = i0; i <= iend; ++i) {
             SL(DC, i, k) = 0.5 * (A3(Hz_bak, i, j, k) + A3(Hz_bak, i - di, j - dj, k)) * (cf_stp * A3(us, i, j, k) + cf_bak * A3(ui, i, j, k)) + SL(DC, i, 0) * A3(r, i, j, k);
             A3(ui, i, j, k) = 0.5 * (A3(o.Hz, i, j, k) + A3(o.Hz, i - di, j - dj, k)) * A3(us, i, j, k);
           }
-        for (int i = istr; i <= iend; ++i) {
+        for (int i = i0; i <= iend; ++i) {
           SL(FC, i, N - 1) = 2.0 * dtau * (AW(o.Akv, i, j, N - 1) + AW(o.Akv, i - di, j - dj, N - 1)) /
                              (A3(Hz_fwd, i, j, N) + A3(Hz_fwd, i - di, j - dj, N) + A3(Hz_fwd, i, j, N - 1) + A3(Hz_fwd, i - di, j - dj, N - 1));
           SL(WC, i, N - 1) = SL(DC, i, 0) * 0.5 * (AW(o.Wi, i, j, N - 1) + AW(o.Wi, i - di, j - dj, N - 1));
@@ -960,7 +1026,7 @@ void pre_step3d(Orc& o) {
           SL(DC, i, N) = cff * (SL(DC, i, N) + dtau * A2(strs, i, j));
         }
         for (int k = N - 1; k >= 2; --k)
-          for (int i = istr; i <= iend; ++i) {
+          for (int i = i0; i <= iend; ++i) {
             SL(FC, i, k - 1) = 2.0 * dtau * (AW(o.Akv, i, j, k - 1) + AW(o.Akv, i - di, j - dj, k - 1)) /
                                (A3(Hz_fwd, i, j, k) + A3(Hz_fwd, i - di, j - dj, k) + A3(Hz_fwd, i, j, k - 1) + A3(Hz_fwd, i - di, j - dj, k - 1));
             SL(WC, i, k - 1) = SL(DC, i, 0) * 0.5 * (AW(o.Wi, i, j, k - 1) + AW(o.Wi, i - di, j - dj, k - 1));
@@ -969,12 +1035,12 @@ void pre_step3d(Orc& o) {
             SL(CF, i, k - 1) = cff * (SL(FC, i, k - 1) + std::max(SL(WC, i, k - 1), 0.0));
             SL(DC, i, k) = cff * (SL(DC, i, k) + SL(DC, i, k + 1) * (SL(FC, i, k) - std::min(SL(WC, i, k), 0.0)));
           }
-        for (int i = istr; i <= iend; ++i)
+        for (int i = i0; i <= iend; ++i)
           A3(un, i, j, 1) = (SL(DC, i, 1) + SL(DC, i, 2) * (SL(FC, i, 1) - std::min(SL(WC, i, 1), 0.0))) /
                             (0.5 * (A3(Hz_fwd, i, j, 1) + A3(Hz_fwd, i - di, j - dj, 1)) + 0.5 * dtau * (A2(wrk1, i, j) + A2(wrk1, i - di, j - dj)) + SL(FC, i, 1) +
                              std::max(SL(WC, i, 1), 0.0) - SL(CF, i, 1) * (SL(FC, i, 1) - std::min(SL(WC, i, 1), 0.0)));
         for (int k = 2; k <= N; ++k)
-          for (int i = istr; i <= iend; ++i) A3(un, i, j, k) = SL(DC, i, k) + SL(CF, i, k - 1) * A3(un, i, j, k - 1);
+          for (int i = i0; i <= iend; ++i) A3(un, i, j, k) = SL(DC, i, k) + SL(CF, i, k - 1) * A3(un, i, j, k - 1);
       }
     }
   }
@@ -1007,14 +1073,14 @@ void step3d_uv1(Orc& o) {
       vert_rhs_uv(o, j, u_rhs, v_rhs, FC, CF, DC);
       for (int dir = 0; dir < 2; ++dir) {
         if (dir == 1 && j < jstrV) continue;
-        const int di = dir == 0 ? 1 : 0, dj = dir == 0 ? 0 : 1;
+        const int di = dir == 0 ? 1 : 0, dj = dir == 0 ? 0 : 1, i0 = dir == 0 ? istrU : istr;
         vec& un = dir == 0 ? o.u[nnew - 1] : o.v[nnew - 1];
         vec& r = dir == 0 ? o.ru : o.rv;
         vec& rfrc = dir == 0 ? o.rufrc : o.rvfrc;
         const vec& strs = dir == 0 ? o.sustr : o.svstr;
         const vec& dmx = dir == 0 ? o.dm_u : o.dm_v;
         const vec& dnx = dir == 0 ? o.dn_u : o.dn_v;
-        for (int i = istr; i <= iend; ++i) {
+        for (int i = i0; i <= iend; ++i) {
           SL(DC, i, 0) = dt * 0.25 * (A2(o.pm, i, j) + A2(o.pm, i - di, j - dj)) * (A2(o.pn, i, j) + A2(o.pn, i - di, j - dj));
           SL(FC, i, N - 1) = 2.0 * dt * (AW(o.Akv, i, j, N - 1) + AW(o.Akv, i - di, j - dj, N - 1)) /
                              (A3(o.Hz, i, j, N) + A3(o.Hz, i - di, j - dj, N) + A3(o.Hz, i, j, N - 1) + A3(o.Hz, i - di, j - dj, N - 1));
@@ -1024,7 +1090,7 @@ void step3d_uv1(Orc& o) {
           SL(DC, i, N) = cff * (A3(un, i, j, N) + SL(DC, i, 0) * A3(r, i, j, N) + dt * A2(strs, i, j));
         }
         for (int k = N - 1; k >= 2; --k)
-          for (int i = istr; i <= iend; ++i) {
+          for (int i = i0; i <= iend; ++i) {
             SL(FC, i, k - 1) = 2.0 * dt * (AW(o.Akv, i, j, k - 1) + AW(o.Akv, i - di, j - dj, k - 1)) /
                                (A3(o.Hz, i, j, k) + A3(o.Hz, i - di, j - dj, k) + A3(o.Hz, i, j, k - 1) + A3(o.Hz, i - di, j - dj, k - 1));
             SL(WC, i, k - 1) = SL(DC, i, 0) * 0.5 * (AW(o.Wi, i, j, k - 1) + AW(o.Wi, i - di, j - dj, k - 1));
@@ -1033,7 +1099,7 @@ void step3d_uv1(Orc& o) {
             SL(CF, i, k - 1) = cff * (SL(FC, i, k - 1) + std::max(SL(WC, i, k - 1), 0.0));
             SL(DC, i, k) = cff * (A3(un, i, j, k) + SL(DC, i, 0) * A3(r, i, j, k) + SL(DC, i, k + 1) * (SL(FC, i, k) - std::min(SL(WC, i, k), 0.0)));
           }
-        for (int i = istr; i <= iend; ++i) {
+        for (int i = i0; i <= iend; ++i) {
           SL(DC, i, 1) = (A3(un, i, j, 1) + SL(DC, i, 0) * A3(r, i, j, 1) + SL(DC, i, 2) * (SL(FC, i, 1) - std::min(SL(WC, i, 1), 0.0))) /
                          (0.5 * (A3(o.Hz, i, j, 1) + A3(o.Hz, i - di, j - dj, 1)) + 0.5 * dt * (A2(o.r_D, i, j) + A2(o.r_D, i - di, j - dj)) + SL(FC, i, 1) +
                           std::max(SL(WC, i, 1), 0.0) - SL(CF, i, 1) * (SL(FC, i, 1) - std::min(SL(WC, i, 1), 0.0)));
@@ -1041,7 +1107,7 @@ void step3d_uv1(Orc& o) {
           A2(rfrc, i, j) = A3(r, i, j, 1) + A2(dmx, i, j) * A2(dnx, i, j) * (A2(strs, i, j) - 0.5 * (A2(o.r_D, i - di, j - dj) + A2(o.r_D, i, j)) * SL(DC, i, 1));
         }
         for (int k = 2; k <= N; ++k)
-          for (int i = istr; i <= iend; ++i) {
+          for (int i = i0; i <= iend; ++i) {
             SL(DC, i, k) = SL(DC, i, k) + SL(CF, i, k - 1) * SL(DC, i, k - 1);
             A3(un, i, j, k) = SL(DC, i, k) * 0.5 * (A3(o.Hz, i, j, k) + A3(o.Hz, i - di, j - dj, k));
             A2(rfrc, i, j) = A2(rfrc, i, j) + A3(r, i, j, k);
@@ -1082,10 +1148,10 @@ void step2d(Orc& o) {
       &DVom = o.s2d[7], &Drhs = o.s2d[8], &UFx = o.s2d[9], &UFe = o.s2d[10], &VFx = o.s2d[11], &VFe = o.s2d[12];
 #pragma omp parallel for
   for (int j = jstrV - 2; j <= jend + 1; ++j)
-    for (int i = istr - 2; i <= iend + 1; ++i) A2(Drhs, i, j) = A2(o.h, i, j) + fwd * A2(zs, i, j) + fwd1 * A2(zb, i, j) + fwd2 * A2(zo, i, j);
+    for (int i = istrU - 2; i <= iend + 1; ++i) A2(Drhs, i, j) = A2(o.h, i, j) + fwd * A2(zs, i, j) + fwd1 * A2(zb, i, j) + fwd2 * A2(zo, i, j);
 #pragma omp parallel for
   for (int j = jstr - 1; j <= jend + 1; ++j) {
-    for (int i = istr - 1; i <= iend + 1; ++i) {
+    for (int i = istrU - 1; i <= iend + 1; ++i) {
       A2(urhs, i, j) = fwd * A2(us, i, j) + fwd1 * A2(ub, i, j) + fwd2 * A2(uo, i, j);
       A2(DUon, i, j) = 0.5 * (A2(Drhs, i, j) + A2(Drhs, i - 1, j)) * A2(o.dn_u, i, j) * (A2(urhs, i, j));
     }
@@ -1097,7 +1163,7 @@ void step2d(Orc& o) {
   }
 #pragma omp parallel for
   for (int j = jstrV - 1; j <= jend; ++j)
-    for (int i = istr - 1; i <= iend; ++i) {
+    for (int i = istrU - 1; i <= iend; ++i) {
       A2(zeta_new, i, j) = A2(zs, i, j) + dtfast * A2(o.pm, i, j) * A2(o.pn, i, j) * (A2(DUon, i, j) - A2(DUon, i + 1, j) + A2(DVom, i, j) - A2(DVom, i, j + 1)) +
                            dtfast * A2(o.swflx, i, j);
       A2(zeta_new, i, j) = A2(zeta_new, i, j) * A2(o.rmask, i, j);
@@ -1109,11 +1175,11 @@ void step2d(Orc& o) {
     }
   zetabc(o, zeta_new);
   for (int j = jstrR; j <= jendR; ++j)
-    for (int i = istr; i <= iend; ++i) A2(zn, i, j) = A2(zeta_new, i, j);
+    for (int i = istrR; i <= iendR; ++i) A2(zn, i, j) = A2(zeta_new, i, j);
   double cff1 = o.weight1[iif], cff2 = o.weight2[iif];
   if (iif == 1) {
     for (int j = jstrR; j <= jendR; ++j)
-      for (int i = istr; i <= iend; ++i) {
+      for (int i = istrR; i <= iendR; ++i) {
         A2(o.DU_avg_bak, i, j) = A2(o.DU_avg1, i, j) - 0.1024390243902439 * A2(o.DU_avg2, i, j);
         A2(o.DV_avg_bak, i, j) = A2(o.DV_avg1, i, j) - 0.1024390243902439 * A2(o.DV_avg2, i, j);
         A2(o.Zt_avg1, i, j) = cff1 * A2(zn, i, j);
@@ -1124,7 +1190,7 @@ void step2d(Orc& o) {
       }
   } else {
     for (int j = jstrR; j <= jendR; ++j)
-      for (int i = istr; i <= iend; ++i) {
+      for (int i = istrR; i <= iendR; ++i) {
         A2(o.Zt_avg1, i, j) = A2(o.Zt_avg1, i, j) + cff1 * A2(zn, i, j);
         A2(o.DU_avg2, i, j) = A2(o.DU_avg2, i, j) + cff2 * A2(DUon, i, j);
         A2(o.DV_avg2, i, j) = A2(o.DV_avg2, i, j) + cff2 * A2(DVom, i, j);
@@ -1148,7 +1214,7 @@ void step2d(Orc& o) {
         A2(o.rvfrc, i, j) = A2(o.rvfrc, i, j) - A2(rvbar, i, j);
       }
     for (int j = jstrV - 1; j <= jend; ++j)
-      for (int i = istr - 1; i <= iend; ++i) {
+      for (int i = istrU - 1; i <= iend; ++i) {
         A2(UFx, i, j) = A2(zeta_new, i, j) - A2(zs, i, j);
         A2(UFe, i, j) = (1.0 + A2(o.rhoS, i, j)) * A2(UFx, i, j);
         A2(VFe, i, j) = A2(UFe, i, j) * (A2(zeta_new, i, j) + A2(zs, i, j));
@@ -1168,12 +1234,12 @@ void step2d(Orc& o) {
       }
   }
   for (int j = jstrV - 1; j <= jend; ++j)
-    for (int i = istr - 1; i <= iend; ++i) A2(DUon, i, j) = A2(zs, i, j) + A2(o.h, i, j);
+    for (int i = istrU - 1; i <= iend; ++i) A2(DUon, i, j) = A2(zs, i, j) + A2(o.h, i, j);
   cff = 0.5 * dtfast;
   cff1 = 0.5 * o.weight1[iif];
 #pragma omp parallel for
   for (int j = jstr; j <= jend; ++j) {
-    for (int i = istr; i <= iend; ++i) {
+    for (int i = istrU; i <= iend; ++i) {
       double DUnew = ((A2(DUon, i, j) + A2(DUon, i - 1, j)) * A2(us, i, j) +
                       cff * (A2(o.pm, i, j) + A2(o.pm, i - 1, j)) * (A2(o.pn, i, j) + A2(o.pn, i - 1, j)) * (A2(rubar, i, j) + A2(o.rufrc, i, j))) *
                      A2(o.umask, i, j);
@@ -1192,24 +1258,38 @@ void step2d(Orc& o) {
   u2dbc(o, un);
   v2dbc(o, vn);
   // boundary-row contributions to the fast-time averaged fluxes (step2d_FB.F:449-529)
-  if (SWALL) for (int i = istr - 1; i <= iend; ++i) A2(Dnew, i, jstr - 1) = A2(o.h, i, jstr - 1) + A2(zeta_new, i, jstr - 1);
-  if (NWALL) for (int i = istr - 1; i <= iend; ++i) A2(Dnew, i, jend + 1) = A2(o.h, i, jend + 1) + A2(zeta_new, i, jend + 1);
+  if (WWALL) for (int j = jstr - 1; j <= jendR; ++j) A2(Dnew, istr - 1, j) = A2(o.h, istr - 1, j) + A2(zeta_new, istr - 1, j);
+  if (EWALL) for (int j = jstr - 1; j <= jendR; ++j) A2(Dnew, iend + 1, j) = A2(o.h, iend + 1, j) + A2(zeta_new, iend + 1, j);
+  if (SWALL) for (int i = istr - 1; i <= iendR; ++i) A2(Dnew, i, jstr - 1) = A2(o.h, i, jstr - 1) + A2(zeta_new, i, jstr - 1);
+  if (NWALL) for (int i = istr - 1; i <= iendR; ++i) A2(Dnew, i, jend + 1) = A2(o.h, i, jend + 1) + A2(zeta_new, i, jend + 1);
   cff1 = 0.5 * o.weight1[iif];
+  if (WWALL) {
+    for (int j = jstrR; j <= jendR; ++j)
+      A2(o.DU_avg1, istrU - 1, j) = A2(o.DU_avg1, istrU - 1, j) + cff1 * (A2(Dnew, istrU - 1, j) + A2(Dnew, istrU - 2, j)) * (A2(un, istrU - 1, j)) * A2(o.dn_u, istrU - 1, j);
+    for (int j = jstrV; j <= jend; ++j)
+      A2(o.DV_avg1, istr - 1, j) = A2(o.DV_avg1, istr - 1, j) + cff1 * (A2(Dnew, istr - 1, j) + A2(Dnew, istr - 1, j - 1)) * (A2(vn, istr - 1, j)) * A2(o.dm_v, istr - 1, j);
+  }
+  if (EWALL) {
+    for (int j = jstrR; j <= jendR; ++j)
+      A2(o.DU_avg1, iend + 1, j) = A2(o.DU_avg1, iend + 1, j) + cff1 * (A2(Dnew, iend + 1, j) + A2(Dnew, iend, j)) * (A2(un, iend + 1, j)) * A2(o.dn_u, iend + 1, j);
+    for (int j = jstrV; j <= jend; ++j)
+      A2(o.DV_avg1, iend + 1, j) = A2(o.DV_avg1, iend + 1, j) + cff1 * (A2(Dnew, iend + 1, j) + A2(Dnew, iend + 1, j - 1)) * (A2(vn, iend + 1, j)) * A2(o.dm_v, iend + 1, j);
+  }
   if (SWALL) {
-    for (int i = istr; i <= iend; ++i)
+    for (int i = istrU; i <= iend; ++i)
       A2(o.DU_avg1, i, jstr - 1) = A2(o.DU_avg1, i, jstr - 1) + cff1 * (A2(Dnew, i, jstr - 1) + A2(Dnew, i - 1, jstr - 1)) * (A2(un, i, jstr - 1)) * A2(o.dn_u, i, jstr - 1);
-    for (int i = istr; i <= iend; ++i)
+    for (int i = istrR; i <= iendR; ++i)
       A2(o.DV_avg1, i, jstrV - 1) = A2(o.DV_avg1, i, jstrV - 1) + cff1 * (A2(Dnew, i, jstrV - 1) + A2(Dnew, i, jstrV - 2)) * (A2(vn, i, jstrV - 1)) * A2(o.dm_v, i, jstrV - 1);
   }
   if (NWALL) {
-    for (int i = istr; i <= iend; ++i)
+    for (int i = istrU; i <= iend; ++i)
       A2(o.DU_avg1, i, jend + 1) = A2(o.DU_avg1, i, jend + 1) + cff1 * (A2(Dnew, i, jend + 1) + A2(Dnew, i - 1, jend + 1)) * (A2(un, i, jend + 1)) * A2(o.dn_u, i, jend + 1);
-    for (int i = istr; i <= iend; ++i)
+    for (int i = istrR; i <= iendR; ++i)
       A2(o.DV_avg1, i, jend + 1) = A2(o.DV_avg1, i, jend + 1) + cff1 * (A2(Dnew, i, jend + 1) + A2(Dnew, i, jend)) * (A2(vn, i, jend + 1)) * A2(o.dm_v, i, jend + 1);
   }
   if (iif == o.nfast) {
     for (int j = jstrR; j <= jendR; ++j)
-      for (int i = istr; i <= iend; ++i) A2(zn, i, j) = A2(o.Zt_avg1, i, j);
+      for (int i = istrR; i <= iendR; ++i) A2(zn, i, j) = A2(o.Zt_avg1, i, j);
     set_depth(o);
   }
   ex2(o, zn); ex2(o, un); ex2(o, vn);
@@ -1232,6 +1312,7 @@ void step3d_uv2(Orc& o) {
         for (int dir = 0; dir < 2; ++dir) {
           if (dir == 1 && j < (pass == 0 ? jstrV : jstr)) continue;
           const int di = dir == 0 ? 1 : 0, dj = dir == 0 ? 0 : 1;
+          const int i0 = pass == 0 ? (dir == 0 ? istrU : istr) : (dir == 0 ? istr : istrR), i1 = pass == 0 ? iend : iendR;
           vec& un = dir == 0 ? o.u[nnew - 1] : o.v[nnew - 1];
           const vec& us = dir == 0 ? o.u[nstp - 1] : o.v[nstp - 1];
           const vec& dnx = dir == 0 ? o.dn_u : o.dm_v;
@@ -1241,48 +1322,48 @@ void step3d_uv2(Orc& o) {
           vec& Flx = dir == 0 ? o.FlxU : o.FlxV;
           vec& bar = dir == 0 ? o.ubar[knew - 1] : o.vbar[knew - 1];
           if (pass == 0) {
-            for (int i = istr; i <= iend; ++i) {
+            for (int i = i0; i <= i1; ++i) {
               SL(CF, i, 0) = 0.5 * (A3(o.Hz, i, j, N) + A3(o.Hz, i - di, j - dj, N));
               SL(DC, i, 0) = A3(un, i, j, N);
               A3(un, i, j, N) = A3(un, i, j, N) / SL(CF, i, 0);
             }
             for (int k = N - 1; k >= 1; --k)
-              for (int i = istr; i <= iend; ++i) {
+              for (int i = i0; i <= i1; ++i) {
                 double cff = 0.5 * (A3(o.Hz, i, j, k) + A3(o.Hz, i - di, j - dj, k));
                 SL(CF, i, 0) = SL(CF, i, 0) + cff;
                 SL(DC, i, 0) = SL(DC, i, 0) + A3(un, i, j, k);
                 A3(un, i, j, k) = A3(un, i, j, k) / cff;
               }
-            for (int i = istr; i <= iend; ++i) SL(DC, i, 0) = (SL(DC, i, 0) * A2(dnx, i, j) - A2(Davg1, i, j)) / (SL(CF, i, 0) * A2(dnx, i, j));
+            for (int i = i0; i <= i1; ++i) SL(DC, i, 0) = (SL(DC, i, 0) * A2(dnx, i, j) - A2(Davg1, i, j)) / (SL(CF, i, 0) * A2(dnx, i, j));
             for (int k = 1; k <= N; ++k)
-              for (int i = istr; i <= iend; ++i) A3(un, i, j, k) = (A3(un, i, j, k) - SL(DC, i, 0)) * A2(msk, i, j);
+              for (int i = i0; i <= i1; ++i) A3(un, i, j, k) = (A3(un, i, j, k) - SL(DC, i, 0)) * A2(msk, i, j);
           } else {
-            for (int i = istr; i <= iend; ++i) {
+            for (int i = i0; i <= i1; ++i) {
               SL(DC, i, N) = 0.5 * (A3(o.Hz, i, j, N) + A3(o.Hz, i - di, j - dj, N)) * A2(dnx, i, j);
               SL(DC, i, 0) = SL(DC, i, N);
               SL(FC, i, 0) = SL(DC, i, N) * A3(un, i, j, N);
             }
             for (int k = N - 1; k >= 1; --k)
-              for (int i = istr; i <= iend; ++i) {
+              for (int i = i0; i <= i1; ++i) {
                 SL(DC, i, k) = 0.5 * (A3(o.Hz, i, j, k) + A3(o.Hz, i - di, j - dj, k)) * A2(dnx, i, j);
                 SL(DC, i, 0) = SL(DC, i, 0) + SL(DC, i, k);
                 SL(FC, i, 0) = SL(FC, i, 0) + SL(DC, i, k) * A3(un, i, j, k);
               }
-            for (int i = istr; i <= iend; ++i) {
+            for (int i = i0; i <= i1; ++i) {
               SL(DC, i, 0) = 1.0 / SL(DC, i, 0);
               A2(bar, i, j) = SL(DC, i, 0) * A2(Davg1, i, j);
               SL(FC, i, 0) = SL(DC, i, 0) * (SL(FC, i, 0) - A2(Davg1, i, j));
               SL(CF, i, 0) = 0.0;
             }
             for (int k = N; k >= 1; --k)
-              for (int i = istr; i <= iend; ++i) {
+              for (int i = i0; i <= i1; ++i) {
                 A3(un, i, j, k) = (A3(un, i, j, k) - SL(FC, i, 0)) * A2(msk, i, j);
                 SL(CF, i, k) = 0.28 * A3(Flx, i, j, k) + 0.36 * SL(DC, i, k) * (A3(us, i, j, k) + A3(un, i, j, k));
                 SL(CF, i, 0) = SL(CF, i, 0) + SL(CF, i, k);
               }
-            for (int i = istr; i <= iend; ++i) SL(CF, i, 0) = SL(DC, i, 0) * (SL(CF, i, 0) - A2(Davg2, i, j));
+            for (int i = i0; i <= i1; ++i) SL(CF, i, 0) = SL(DC, i, 0) * (SL(CF, i, 0) - A2(Davg2, i, j));
             for (int k = 1; k <= N; ++k)
-              for (int i = istr; i <= iend; ++i) A3(Flx, i, j, k) = SL(CF, i, k) - SL(DC, i, k) * SL(CF, i, 0);
+              for (int i = i0; i <= i1; ++i) A3(Flx, i, j, k) = SL(CF, i, k) - SL(DC, i, k) * SL(CF, i, 0);
           }
         }
       }

@@ -62,18 +62,19 @@ def _noise(ig, jg, k, salt):
 
 
 def channel(Lm=64, Mm=64, N=16, NT=2, ns_walls=False, nonlin_eos=True, dt=120.0, ndtfast=60, dx=1.0e3, dy=1.0e3,
-            depth=4000.0, seed=20260101, perturb=1e-6, amp=None, sub=(0, 0, 1, 1), seamount=False, island=False):
+            depth=4000.0, seed=20260101, perturb=1e-6, amp=None, sub=(0, 0, 1, 1), seamount=False, island=False, ew_walls=False):
     """Lm, Mm are the GLOBAL interior sizes; sub=(inode, jnode, np_xi, np_eta) selects this rank's block
     (mpi_setup.F:61-70; sizes must divide evenly).  Returns the cfg and state of that block.
     seamount: Gaussian seamount h = depth*(1 - 0.5*exp(-r^2/(L/5)^2)) (SURVEY.md 8(d) input (3), form of
     NHMG/tests/mg_setup_tests.f90:150); island: a circular land mask (rmask=0) north-east of it, so that the
-    rmask/umask/vmask factors of every routine are exercised."""
+    rmask/umask/vmask factors of every routine are exercised.  ew_walls: closed western/eastern walls as well (with
+    ns_walls: a fully closed basin, BASELINE configs[2] geometry)."""
     inode, jnode, np_xi, np_eta = sub
     LmG, MmG = Lm, Mm
     assert LmG % np_xi == 0 and MmG % np_eta == 0
     Lm, Mm = LmG // np_xi, MmG // np_eta
     i0, j0 = inode * Lm, jnode * Mm
-    cfg = RomsCfg(Lm=Lm, Mm=Mm, N=N, NT=NT, ew_periodic=1, ns_periodic=0 if ns_walls else 1,
+    cfg = RomsCfg(Lm=Lm, Mm=Mm, N=N, NT=NT, ew_periodic=0 if ew_walls else 1, ns_periodic=0 if ns_walls else 1,
                   nonlin_eos=1 if nonlin_eos else 0, salinity=1, ndtfast=ndtfast, np_xi=np_xi, np_eta=np_eta, inode=inode, jnode=jnode,
                   dt=dt, rho0=1027.0, g=9.81, Tcoef=0.2, T0=10.0, Scoef=0.8, S0=35.0,
                   rdrg=3.0e-4, rdrg2=0.0, Zob=0.0, gamma2=1.0, theta_s=6.0, theta_b=2.0, hc=25.0)
@@ -81,7 +82,8 @@ def channel(Lm=64, Mm=64, N=16, NT=2, ns_walls=False, nonlin_eos=True, dt=120.0,
     sy, sx = Mm + 6, Lm + 6
     ig = (np.arange(-2, Lm + 4) + i0)[None, :] + np.zeros((sy, 1), dtype=np.int64)
     jg = (np.arange(-2, Mm + 4) + j0)[:, None] + np.zeros((1, sx), dtype=np.int64)
-    ig = (ig - 1) % LmG + 1                      # E-W periodic images
+    if not ew_walls:
+        ig = (ig - 1) % LmG + 1                  # E-W periodic images
     if not ns_walls:
         jg = (jg - 1) % MmG + 1
     x = dx * (ig - 0.5); y = dy * (jg - 0.5)
@@ -114,6 +116,9 @@ def channel(Lm=64, Mm=64, N=16, NT=2, ns_walls=False, nonlin_eos=True, dt=120.0,
     if ns_walls:
         jl = (np.arange(-2, Mm + 4) + j0)
         v[:, (jl <= 1) | (jl >= MmG + 1), :] = 0.0     # closed south (j=1) and north (j=Mm+1) walls
+    if ew_walls:
+        il = (np.arange(-2, Lm + 4) + i0)
+        u[:, :, (il <= 1) | (il >= LmG + 1)] = 0.0     # closed west (i=1) and east (i=Lm+1) walls
     if island:
         um = np.ones_like(rmask); vm = np.ones_like(rmask)
         um[:, 1:] = rmask[:, 1:] * rmask[:, :-1]; vm[1:, :] = rmask[1:, :] * rmask[:-1, :]
