@@ -122,8 +122,9 @@ int  roms_comm_attach(roms_ctx* h, const char* id, int len, int rank, int world)
                                                /* rank = jnode*np_xi+inode (mpi_setup.F:61-70)        */
 int  roms_decomp_neighbor(int np_xi, int np_eta, int inode, int jnode, int ew_periodic, int ns_periodic, int d);
                                                /* neighbour rank in direction d=0..7 (W,E,S,N,SW,SE,NW,NE), -1 at a wall */
-int  roms_decomp_box(int Lm, int Mm, int d, int send, int swall, int nwall, int out[4]);
-                                               /* i0,j0,ni,nj of the message to/from direction d; swall/nwall: closed S/N edge */
+int  roms_decomp_box(int Lm, int Mm, int d, int send, const int walls[4], int out[4]);
+                                               /* i0,j0,ni,nj of the message to/from direction d; walls = {S,N,W,E} closed physical
+                                                  edges of this subdomain (NULL: none): messages along a wall carry the boundary row/column */
 int  roms_decomp_opposite(int d);
 
 /* ---- measurement hooks (the reference's timers.F:35-131 analogue; device-side CUDA events) - */

@@ -31,8 +31,9 @@ def rel(a, b):
 
 
 def view(a, cfg):
-    """rows that exist in the model: with closed N/S walls rows j=-1 and j=Mm+2 are allocated but never defined"""
-    return a if cfg.ns_periodic else a[..., 1:-1, :]
+    """rows/columns that exist in the model: beyond a closed wall the outermost halo line is allocated but never defined"""
+    a = a if cfg.ns_periodic else a[..., 1:-1, :]
+    return a if cfg.ew_periodic else a[..., :, 1:-1]
 
 
 def fetch(m, name, NT):
@@ -125,7 +126,8 @@ def walk(cfg, st, nsteps=1, verbose=False, device=0):
 
 if __name__ == "__main__":
     dims = [int(x) for x in sys.argv[1:4]] or [48, 40, 12]
-    for tag, (cfg, st) in {"channel(nonlin EOS, T+S)": cases.channel(*dims), "channel(N/S walls)": cases.channel(*dims, ns_walls=True), "filament(linear EOS, T)": cases.filament(*dims)}.items():
+    for tag, (cfg, st) in {"channel(nonlin EOS, T+S)": cases.channel(*dims), "channel(N/S walls)": cases.channel(*dims, ns_walls=True),
+                             "closed basin": cases.channel(*dims, ns_walls=True, ew_walls=True), "filament(linear EOS, T)": cases.filament(*dims)}.items():
         print(tag)
         w = walk(cfg, st, nsteps=2, verbose=True)
         print(" worst:", max(w.values()), max(w, key=w.get))

@@ -59,12 +59,12 @@ def test_decomp_geometry():
                         # my neighbour in direction d sees me in the opposite direction
                         assert lib.roms_decomp_neighbor(npx, npe, nb % npx, nb // npx, ew, ns, o) == me
                     sb = (C.c_int * 4)(); rb = (C.c_int * 4)()
-                    lib.roms_decomp_box(16, 12, d, 1, 0, 0, sb); lib.roms_decomp_box(16, 12, o, 0, 0, 0, rb)
+                    lib.roms_decomp_box(16, 12, d, 1, None, sb); lib.roms_decomp_box(16, 12, o, 0, None, rb)
                     assert sb[2] == rb[2] and sb[3] == rb[3]      # message extents agree
     # the 8 receive boxes tile the halo exactly once
     Lm, Mm = 10, 7
     cover = np.zeros((Mm + 4, Lm + 4), int)
     for d in range(8):
-        b = (C.c_int * 4)(); lib.roms_decomp_box(Lm, Mm, d, 0, 0, 0, b)
+        b = (C.c_int * 4)(); lib.roms_decomp_box(Lm, Mm, d, 0, None, b)
         cover[b[1] + 1:b[1] + 1 + b[3], b[0] + 1:b[0] + 1 + b[2]] += 1
     assert (cover[2:-2, 2:-2] == 0).all() and cover.sum() == cover.size - Lm * Mm and cover.max() == 1

@@ -27,10 +27,10 @@ def _worker(rank, world, port, npx, npe):
     for d in range(8):
         o = lib.roms_decomp_opposite(d)
         nb = lib.roms_decomp_neighbor(npx, npe, i_n, jn, 1, 1, d)
-        sb = (C.c_int * 4)(); lib.roms_decomp_box(Lm, Mm, d, 1, 0, 0, sb)
+        sb = (C.c_int * 4)(); lib.roms_decomp_box(Lm, Mm, d, 1, None, sb)
         msg = torch.from_numpy(np.ascontiguousarray(loc[sb[1] + 1:sb[1] + 1 + sb[3], sb[0] + 1:sb[0] + 1 + sb[2]]))
         src = lib.roms_decomp_neighbor(npx, npe, i_n, jn, 1, 1, o)
-        rb = (C.c_int * 4)(); lib.roms_decomp_box(Lm, Mm, o, 0, 0, 0, rb)
+        rb = (C.c_int * 4)(); lib.roms_decomp_box(Lm, Mm, o, 0, None, rb)
         buf = torch.empty((rb[3], rb[2]), dtype=torch.float64)
         if nb == rank:
             buf.copy_(msg)

@@ -57,7 +57,8 @@ def test_constants_match_oracle():
 
 
 @pytest.mark.parametrize("case", ["channel", "filament", "channel_linear_odd", "channel_walls", "channel_walls_linear_odd",
-                                  "seamount_island_walls", "seamount_island_periodic"])
+                                  "seamount_island_walls", "seamount_island_periodic", "closed_basin", "closed_basin_seamount_odd",
+                                  "ew_walls_ns_periodic"])
 def test_routine_by_routine(case):
     if case == "channel":
         cfg, st = cases.channel(48, 40, 12)
@@ -67,6 +68,12 @@ def test_routine_by_routine(case):
         cfg, st = cases.channel(48, 40, 12, ns_walls=True, seamount=True, island=True)
     elif case == "seamount_island_periodic":
         cfg, st = cases.channel(45, 38, 11, seamount=True, island=True)
+    elif case == "closed_basin":                                        # walls on all four sides (corner rules)
+        cfg, st = cases.channel(48, 40, 12, ns_walls=True, ew_walls=True)
+    elif case == "closed_basin_seamount_odd":                           # BASELINE configs[2] geometry, ragged sizes, land mask
+        cfg, st = cases.channel(37, 29, 9, ns_walls=True, ew_walls=True, seamount=True, island=True)
+    elif case == "ew_walls_ns_periodic":
+        cfg, st = cases.channel(40, 36, 10, ew_walls=True)
     elif case == "channel_walls_linear_odd":
         cfg, st = cases.channel(37, 29, 9, NT=3, nonlin_eos=False, ns_walls=True)
     elif case == "filament":
@@ -78,9 +85,9 @@ def test_routine_by_routine(case):
     assert not bad, bad
 
 
-@pytest.mark.parametrize("walls,topo", [(False, False), (True, False), (True, True)])
-def test_one_step_and_100_steps_channel(walls, topo):
-    cfg, st = cases.channel(64, 48, 16, ns_walls=walls, seamount=topo, island=topo)
+@pytest.mark.parametrize("walls,topo,ew", [(False, False, False), (True, False, False), (True, True, False), (True, True, True)])
+def test_one_step_and_100_steps_channel(walls, topo, ew):
+    cfg, st = cases.channel(64, 48, 16, ns_walls=walls, seamount=topo, island=topo, ew_walls=ew)
     g, o = Roms(cfg), Oracle(cfg)
     cases.initialize(g, st); cases.initialize(o, st)
     g.call("step"); o.call("step")

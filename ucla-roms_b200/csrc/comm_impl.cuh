@@ -79,7 +79,7 @@ static int comm_attach(Comm* cm, const KP& p, const char* id, int len, int rank,
   if (r != ncclSuccess) { g_err = std::string("ncclCommInitRank: ") + ncclGetErrorString(r); delete ns; return -1000 - (int)r; }
   for (int d = 0; d < 8; ++d) {
     ns->nb[d] = decomp_neighbor(cm->np_xi, cm->np_eta, cm->inode, cm->jnode, cm->ew_periodic, cm->ns_periodic, d);
-    const DirBox b = decomp_send_box(p.Lm, p.Mm, d, p.swall, p.nwall);
+    const DirBox b = decomp_send_box(p.Lm, p.Mm, d, p.swall, p.nwall, p.wwall, p.ewall);
     const size_t cap = (size_t)4 * (p.N + 1) * b.ni * b.nj * sizeof(double);
     CK(cudaMalloc(&ns->sbuf[d], cap));
     CK(cudaMalloc(&ns->rbuf[d], cap));
@@ -125,8 +125,8 @@ int comm_exchange(Comm* cm, const KP& p, cudaStream_t st, const XF* f, int nf, l
     MsgGeom gs, gr;
     int maxcell = 4;
     for (int d = 0; d < 8; ++d) {
-      gs.box[d] = decomp_send_box(p.Lm, p.Mm, d, p.swall, p.nwall); gs.buf[d] = ns->sbuf[d]; gs.active[d] = ns->nb[d] >= 0;
-      gr.box[d] = decomp_recv_box(p.Lm, p.Mm, d, p.swall, p.nwall); gr.buf[d] = ns->rbuf[d]; gr.active[d] = ns->nb[d] >= 0;
+      gs.box[d] = decomp_send_box(p.Lm, p.Mm, d, p.swall, p.nwall, p.wwall, p.ewall); gs.buf[d] = ns->sbuf[d]; gs.active[d] = ns->nb[d] >= 0;
+      gr.box[d] = decomp_recv_box(p.Lm, p.Mm, d, p.swall, p.nwall, p.wwall, p.ewall); gr.buf[d] = ns->rbuf[d]; gr.active[d] = ns->nb[d] >= 0;
       if (gs.box[d].ni * gs.box[d].nj > maxcell) maxcell = gs.box[d].ni * gs.box[d].nj;
     }
     dim3 b(128, 1, 1), g((maxcell + 127) / 128, 8, nplanes < 32 ? nplanes : 32);
@@ -203,8 +203,9 @@ int roms_comm_attach(roms_ctx* h, const char* id, int len, int rank, int world) 
 int roms_decomp_neighbor(int np_xi, int np_eta, int inode, int jnode, int ew_periodic, int ns_periodic, int d) {
   return decomp_neighbor(np_xi, np_eta, inode, jnode, ew_periodic, ns_periodic, d);
 }
-int roms_decomp_box(int Lm, int Mm, int d, int send, int swall, int nwall, int out[4]) {
-  const DirBox b = send ? decomp_send_box(Lm, Mm, d, swall, nwall) : decomp_recv_box(Lm, Mm, d, swall, nwall);
+int roms_decomp_box(int Lm, int Mm, int d, int send, const int walls[4], int out[4]) {
+  const int sw = walls ? walls[0] : 0, nw = walls ? walls[1] : 0, ww = walls ? walls[2] : 0, ew = walls ? walls[3] : 0;
+  const DirBox b = send ? decomp_send_box(Lm, Mm, d, sw, nw, ww, ew) : decomp_recv_box(Lm, Mm, d, sw, nw, ww, ew);
   out[0] = b.i0; out[1] = b.j0; out[2] = b.ni; out[3] = b.nj;
   return 0;
 }

@@ -37,8 +37,9 @@ static inline int decomp_neighbor(int np_xi, int np_eta, int inode, int jnode, i
 }
 // interior cells this subdomain SENDS to its neighbour in direction d
 // swall/nwall: this subdomain touches a closed southern/northern physical edge; E-W messages then also carry
-// the boundary rows j=0 / j=Mm+1 (mpi_exchanges.F:538-543: "if (jnode==0) jl0=0", "if (jnode==NP_ETA-1) jl1=nyl+1").
-static inline DirBox decomp_send_box(int Lm, int Mm, int d, int swall = 0, int nwall = 0) {
+// the boundary rows j=0 / j=Mm+1 (mpi_exchanges.F:538-543: "if (jnode==0) jl0=0", "if (jnode==NP_ETA-1) jl1=nyl+1");
+// wwall/ewall: likewise N-S messages carry the boundary columns i=0 / i=Lm+1.
+static inline DirBox decomp_send_box(int Lm, int Mm, int d, int swall = 0, int nwall = 0, int wwall = 0, int ewall = 0) {
   int dx, dy;
   decomp_dir(d, &dx, &dy);
   DirBox b;
@@ -46,10 +47,11 @@ static inline DirBox decomp_send_box(int Lm, int Mm, int d, int swall = 0, int n
   b.i0 = dx > 0 ? Lm - 1 : 1;
   b.j0 = dy > 0 ? Mm - 1 : 1;
   if (dx != 0 && dy == 0) { b.j0 -= swall ? 1 : 0; b.nj += (swall ? 1 : 0) + (nwall ? 1 : 0); }
+  if (dy != 0 && dx == 0) { b.i0 -= wwall ? 1 : 0; b.ni += (wwall ? 1 : 0) + (ewall ? 1 : 0); }
   return b;
 }
 // halo cells this subdomain RECEIVES from its neighbour in direction d
-static inline DirBox decomp_recv_box(int Lm, int Mm, int d, int swall = 0, int nwall = 0) {
+static inline DirBox decomp_recv_box(int Lm, int Mm, int d, int swall = 0, int nwall = 0, int wwall = 0, int ewall = 0) {
   int dx, dy;
   decomp_dir(d, &dx, &dy);
   DirBox b;
@@ -57,5 +59,6 @@ static inline DirBox decomp_recv_box(int Lm, int Mm, int d, int swall = 0, int n
   b.i0 = dx < 0 ? -1 : (dx > 0 ? Lm + 1 : 1);
   b.j0 = dy < 0 ? -1 : (dy > 0 ? Mm + 1 : 1);
   if (dx != 0 && dy == 0) { b.j0 -= swall ? 1 : 0; b.nj += (swall ? 1 : 0) + (nwall ? 1 : 0); }
+  if (dy != 0 && dx == 0) { b.i0 -= wwall ? 1 : 0; b.ni += (wwall ? 1 : 0) + (ewall ? 1 : 0); }
   return b;
 }

@@ -93,6 +93,17 @@ __device__ __forceinline__ ix_t jclamp(const KP& p, int j, int lo_wall, int hi_w
   if (p.nwall && jc > hi_wall) jc = hi_wall;
   return (ix_t)(jc - j) * p.SX;
 }
+// the same along i on closed western/eastern walls ("wrk1(istrU-1,j)=wrk1(istrU,j)", "FX(istr-1,j)=FX(istr,j)", "FC(imin-1,j)=FC(imin,j)")
+__device__ __forceinline__ ix_t iclamp(const KP& p, int i, int lo_wall, int hi_wall) {
+  int ic = i;
+  if (p.wwall && ic < lo_wall) ic = lo_wall;
+  if (p.ewall && ic > hi_wall) ic = hi_wall;
+  return (ix_t)(ic - i);
+}
+// a point within two cells of a closed wall: its difference stencils need the clamped forms
+__device__ __forceinline__ bool near_wall(const KP& p, int i, int j) {
+  return (p.swall && j <= p.jstr + 2) || (p.nwall && j >= p.jend - 2) || (p.wwall && i <= p.istr + 2) || (p.ewall && i >= p.iend - 2);
+}
 
 // ------------------------------------------------------------------------------------------------
 // exchange_xxx on one subdomain (mpi_exchanges.F:34-40 with the periodic wrap of mpi_setup.F:231-250):
@@ -123,8 +134,8 @@ __global__ void k_halo_periodic(const __grid_constant__ KP p, const __grid_const
   int is = i, js = j;
   if (ew) { if (i < 1) is = i + Lm; else if (i > Lm) is = i - Lm; }
   if (ns) { if (j < 1) js = j + Mm; else if (j > Mm) js = j - Mm; }
-  const int jlo = p.swall ? 0 : 1, jhi = p.nwall ? Mm + 1 : Mm;
-  if ((is < 1 || is > Lm) || (js < jlo || js > jhi)) return;   // non-periodic edge: untouched
+  const int jlo = p.swall ? 0 : 1, jhi = p.nwall ? Mm + 1 : Mm, ilo = p.wwall ? 0 : 1, ihi = p.ewall ? Lm + 1 : Lm;
+  if ((is < ilo || is > ihi) || (js < jlo || js > jhi)) return;   // non-periodic edge: untouched
   if (is == i && js == j) return;
   const ix_t cd = CIDX(i, j), cs = CIDX(is, js);
   const int f = blockIdx.y;
@@ -135,7 +146,7 @@ __global__ void k_halo_periodic(const __grid_constant__ KP p, const __grid_const
 // ------------------------------------------------------------------------------------------------
 // set_depth.F:16-186 set_depth_tile: z_w, z_r, Hz from zeta(knew).  Plane kernel over k=0:N.
 __global__ void k_set_depth(const __grid_constant__ KP p, const double* __restrict__ zeta) {
-  THREAD_IJ(p.istr, p.iend, p.jstrR, p.jendR)
+  THREAD_IJ(p.istrR, p.iendR, p.jstrR, p.jendR)
   const int k = blockIdx.z;
   const int N = p.N;
   const double h = p.h[c];
@@ -159,25 +170,25 @@ __global__ void k_set_depth(const __grid_constant__ KP p, const double* __restri
 // set_depth.F iic==0 branch: hinv, DU_avg1, DV_avg1
 __global__ void k_set_depth_init(const __grid_constant__ KP p, const double* __restrict__ zeta, const double* __restrict__ ubar,
                                  const double* __restrict__ vbar) {
-  THREAD_IJ(p.istr, p.iend, p.jstrR, p.jendR)
+  THREAD_IJ(p.istrR, p.iendR, p.jstrR, p.jendR)
   p.hinv[c] = 1.0 / (p.h[c] + p.hc);
-  p.DU_avg1[c] = 0.5 * (p.h[c - 1] + p.h[c] + zeta[c] + zeta[c - 1]) * p.dn_u[c] * (ubar[c]);
+  if (i >= p.istr) p.DU_avg1[c] = 0.5 * (p.h[c - 1] + p.h[c] + zeta[c] + zeta[c - 1]) * p.dn_u[c] * (ubar[c]);
   if (j >= p.jstr) p.DV_avg1[c] = 0.5 * (p.h[c] + p.h[c - SX] + zeta[c] + zeta[c - SX]) * p.dm_v[c] * (vbar[c]);
 }
 
 // set_depth.F:201-234 set_HUV_tile
 __global__ void k_set_huv(const __grid_constant__ KP p, const double* __restrict__ u, const double* __restrict__ v) {
-  THREAD_IJ(p.istr, p.iend, p.jstrR, p.jendR)
+  THREAD_IJ(p.istrR, p.iendR, p.jstrR, p.jendR)
   const int k = blockIdx.z + 1;
   const double Hz = R3(p.Hz, c, k);
-  R3(p.FlxU, c, k) = 0.5 * (Hz + R3(p.Hz, c - 1, k)) * p.dn_u[c] * (R3(u, c, k));
+  if (i >= p.istr) R3(p.FlxU, c, k) = 0.5 * (Hz + R3(p.Hz, c - 1, k)) * p.dn_u[c] * (R3(u, c, k));
   if (j >= p.jstr) R3(p.FlxV, c, k) = 0.5 * (Hz + R3(p.Hz, c - SX, k)) * p.dm_v[c] * (R3(v, c, k));
 }
 
 // set_depth.F:252-422 set_HUV1_tile.  DIR 0: u/FlxU, 1: v/FlxV.  Column kernel, two sweeps, no scratch.
 template <int DIR>
 __global__ void k_set_huv1(const __grid_constant__ KP p, double* __restrict__ u, int first) {
-  THREAD_IJT(ixc_t, p.istr, p.iend, (DIR == 0 ? p.jstrR : p.jstr), p.jendR)
+  THREAD_IJT(ixc_t, (DIR == 0 ? p.istr : p.istrR), p.iendR, (DIR == 0 ? p.jstrR : p.jstr), p.jendR)
   const ixc_t d = DIR == 0 ? 1 : SX;
   const double dn = DIR == 0 ? p.dn_u[c] : p.dm_v[c];
   const double msk = DIR == 0 ? p.umask[c] : p.vmask[c];
@@ -283,7 +294,7 @@ __global__ void k_omega(const __grid_constant__ KP p, double dtau) {
 // rho1,qp1 per level and the vertical integrals rhoA, rhoS (rho_eos.F:364-395).
 template <bool NONLIN>
 __global__ void k_rho_eos(const __grid_constant__ KP p, const double* __restrict__ T, const double* __restrict__ Sal) {
-  THREAD_IJ(p.istr - 2, p.iend + 2, (p.swall ? p.jstr - 1 : p.jstr - 2), (p.nwall ? p.jend + 1 : p.jend + 2))
+  THREAD_IJ((p.wwall ? p.istr - 1 : p.istr - 2), (p.ewall ? p.iend + 1 : p.iend + 2), (p.swall ? p.jstr - 1 : p.jstr - 2), (p.nwall ? p.jend + 1 : p.jend + 2))
   const int N = p.N;
   const double rho0 = p.rho0, qp2 = 0.0000172;
   const double r00 = 999.842594, r01 = 6.793952e-2, r02 = -9.095290e-3, r03 = 1.001685e-4, r04 = -1.120083e-6, r05 = 6.536332e-9,
@@ -467,11 +478,12 @@ __global__ void __launch_bounds__(256, LB_PRS) k_prsgrd_horiz(const __grid_const
   const int k0 = blockIdx.z * KB + 1;
   const double* __restrict__ rho = NONLIN ? p.rho : p.rho1;
   const double dnu = p.dn_u[c], dmv = p.dm_v[c];
-  if (WALL && ((p.swall && j <= p.jstr + 2) || (p.nwall && j >= p.jend - 2))) {   // prsgrd.F:288-310: FC,rx exist on rows jstrV..jend, copied outward
+  if (WALL && near_wall(p, i, j)) {   // prsgrd.F:288-310: FC,rx exist on rows jstrV..jend / columns istrU..iend between walls, copied outward
     const ix_t oA = jclamp(p, j - 1, p.jstrV, p.jend), oB = jclamp(p, j, p.jstrV, p.jend), oC = jclamp(p, j + 1, p.jstrV, p.jend);
+    const ix_t iA = iclamp(p, i - 1, p.istrU, p.iend), iB = iclamp(p, i, p.istrU, p.iend), iC = iclamp(p, i + 1, p.istrU, p.iend);
 #pragma unroll 1
     for (int k = k0; k < k0 + KB && k <= p.N; ++k) {
-      R3(p.ru, c, k) = prs_dir_cl<NONLIN>(p, c, 1, k, p.umask, dnu, rho, 0, 0, 0);
+      if (i >= p.istrU) R3(p.ru, c, k) = prs_dir_cl<NONLIN>(p, c, 1, k, p.umask, dnu, rho, iA, iB, iC);
       if (j >= p.jstrV) R3(p.rv, c, k) = prs_dir_cl<NONLIN>(p, c, SX, k, p.vmask, dmv, rho, oA, oB, oC);
     }
     return;
@@ -545,7 +557,7 @@ __device__ __forceinline__ double flux_cross(const KP& p, const double* __restri
 }
 // one (i,j,k) point of the horizontal momentum RHS; NEAR: a row within two rows of a closed wall (clamped differences)
 template <bool UP, bool NEAR>
-__device__ __forceinline__ void rhs_uv_point(const KP& p, const double* __restrict__ u, const double* __restrict__ v, ixr_t c, int j, int k, bool dov,
+__device__ __forceinline__ void rhs_uv_point(const KP& p, const double* __restrict__ u, const double* __restrict__ v, ixr_t c, int i, int j, int k, bool dov,
                                              double& ru, double& rv) {
   const ixr_t SX = p.SX;
   // Coriolis (no CURVGRID): compute_horiz_rhs_uv_terms.h:4-45
@@ -556,7 +568,14 @@ __device__ __forceinline__ void rhs_uv_point(const KP& p, const double* __restri
   const double UFx_w = cfw * (R3(v, c - 1, k) + R3(v, c - 1 + SX, k));
   ru = R3(p.ru, c, k) + 0.5 * (UFx_c + UFx_w);
   // advection of u
-  const double UFx_i = flux_along<UP, false>(p, u, p.FlxU, c, 1, k), UFx_im = flux_along<UP, false>(p, u, p.FlxU, c - 1, 1, k);
+  double UFx_i, UFx_im;
+  if (NEAR) {   // u, FlxU second differences in i exist on columns istrU..iend between walls (compute_horiz_rhs_uv_terms.h:60-83)
+    UFx_i = flux_along<UP, true>(p, u, p.FlxU, c, 1, k, iclamp(p, i, p.istrU, p.iend), iclamp(p, i + 1, p.istrU, p.iend));
+    UFx_im = flux_along<UP, true>(p, u, p.FlxU, c - 1, 1, k, iclamp(p, i - 1, p.istrU, p.iend), iclamp(p, i, p.istrU, p.iend));
+  } else {
+    UFx_i = flux_along<UP, false>(p, u, p.FlxU, c, 1, k);
+    UFx_im = flux_along<UP, false>(p, u, p.FlxU, c - 1, 1, k);
+  }
   double UFe_jp, UFe_j;
   if (NEAR) {   // u second differences in j exist on rows jstr..jend between walls (compute_horiz_rhs_uv_terms.h:186-199)
     UFe_jp = flux_cross<UP, true>(p, u, p.FlxV, c + SX, SX, 1, k, jclamp(p, j, p.jstr, p.jend), jclamp(p, j + 1, p.jstr, p.jend));
@@ -571,7 +590,14 @@ __device__ __forceinline__ void rhs_uv_point(const KP& p, const double* __restri
     const double VFe_c = cf0 * (u00 + R3(u, c + 1, k));
     const double VFe_s = cfs * (R3(u, c - SX, k) + R3(u, c - SX + 1, k));
     rv = R3(p.rv, c, k) - 0.5 * (VFe_c + VFe_s);
-    const double VFx_ip = flux_cross<UP, false>(p, v, p.FlxU, c + 1, 1, SX, k), VFx_i = flux_cross<UP, false>(p, v, p.FlxU, c, 1, SX, k);
+    double VFx_ip, VFx_i;
+    if (NEAR) {   // v second differences in i exist on columns istr..iend between walls (compute_horiz_rhs_uv_terms.h:225-250)
+      VFx_ip = flux_cross<UP, true>(p, v, p.FlxU, c + 1, 1, SX, k, iclamp(p, i, p.istr, p.iend), iclamp(p, i + 1, p.istr, p.iend));
+      VFx_i = flux_cross<UP, true>(p, v, p.FlxU, c, 1, SX, k, iclamp(p, i - 1, p.istr, p.iend), iclamp(p, i, p.istr, p.iend));
+    } else {
+      VFx_ip = flux_cross<UP, false>(p, v, p.FlxU, c + 1, 1, SX, k);
+      VFx_i = flux_cross<UP, false>(p, v, p.FlxU, c, 1, SX, k);
+    }
     double VFe_j, VFe_jm;
     if (NEAR) {   // v, FlxV second differences exist on rows jstrV..jend between walls (compute_horiz_rhs_uv_terms.h:128-141)
       VFe_j = flux_along<UP, true>(p, v, p.FlxV, c, SX, k, jclamp(p, j, p.jstrV, p.jend), jclamp(p, j + 1, p.jstrV, p.jend));
@@ -592,25 +618,25 @@ __global__ void __launch_bounds__(256, (JB >= 4 ? 2 : LB_RHS)) k_rhs_uv_horiz(co
   const int jb = p.jstr + (blockIdx.y * blockDim.y + threadIdx.y) * JB;
   if (i < p.istr || i > p.iend || jb > p.jend) return;
   const int k = blockIdx.z + 1;
-  const bool near = WALL && ((p.swall && jb <= p.jstr + 2) || (p.nwall && jb + JB - 1 >= p.jend - 2));
+  const bool near = WALL && ((p.swall && jb <= p.jstr + 2) || (p.nwall && jb + JB - 1 >= p.jend - 2) || (p.wwall && i <= p.istr + 2) || (p.ewall && i >= p.iend - 2));
   const ixr_t c0 = CIDX(i, jb), SX = p.SX;
-  if (near || jb + JB - 1 > p.jend) {   // rows next to a wall / ragged last block: one row at a time
+  if (near || jb + JB - 1 > p.jend) {   // points next to a wall / ragged last block: one row at a time
 #pragma unroll 1
     for (int q = 0; q < JB && jb + q <= p.jend; ++q) {
       const int j = jb + q;
       const ixr_t c = c0 + q * SX;
-      const bool dov = !WALL || j >= p.jstrV;
+      const bool dov = !WALL || j >= p.jstrV, dou = !WALL || i >= p.istrU;
       double ru, rv;
-      if (WALL) rhs_uv_point<UP, true>(p, u, v, c, j, k, dov, ru, rv);
-      else rhs_uv_point<UP, false>(p, u, v, c, j, k, dov, ru, rv);
-      R3(p.ru, c, k) = ru;
+      if (WALL) rhs_uv_point<UP, true>(p, u, v, c, i, j, k, dov, ru, rv);
+      else rhs_uv_point<UP, false>(p, u, v, c, i, j, k, dov, ru, rv);
+      if (dou) R3(p.ru, c, k) = ru;
       if (dov) R3(p.rv, c, k) = rv;
     }
     return;
   }
   double ru[JB], rv[JB];
 #pragma unroll
-  for (int q = 0; q < JB; ++q) rhs_uv_point<UP, false>(p, u, v, c0 + q * SX, jb + q, k, true, ru[q], rv[q]);
+  for (int q = 0; q < JB; ++q) rhs_uv_point<UP, false>(p, u, v, c0 + q * SX, i, jb + q, k, true, ru[q], rv[q]);
 #pragma unroll
   for (int q = 0; q < JB; ++q) {
     R3(p.ru, c0 + q * SX, k) = ru[q];
@@ -650,7 +676,7 @@ __device__ __forceinline__ double tflux(const double* __restrict__ t, const doub
 
 // pre_step3d4S.F:138-147: FlxDiv such that Hz_bak = Hz + FlxDiv, Hz_fwd = Hz - FlxDiv
 __global__ void k_pre_flxdiv(const __grid_constant__ KP p, double dtau) {
-  THREAD_IJ(p.istr - 1, p.iend, p.jstrV - 1, p.jend)
+  THREAD_IJ(p.istrU - 1, p.iend, p.jstrV - 1, p.jend)
   const int k = blockIdx.z + 1;
   const double cff = 0.5 * dtau;
   R3(p.FlxDiv, c, k) = cff * p.pm[c] * p.pn[c] *
@@ -671,10 +697,17 @@ __device__ __forceinline__ TMask tmask_load(const KP& p, ix_t c) {
   return m;
 }
 template <bool UP, bool NEAR>
-__device__ __forceinline__ double tdiv(const KP& p, const double* __restrict__ t, ix_t c, int j, int k, const TMask& m) {
+__device__ __forceinline__ double tdiv(const KP& p, const double* __restrict__ t, ix_t c, int i, int j, int k, const TMask& m) {
   const ix_t SX = p.SX;
-  const double FXi = tflux<UP>(t, p.FlxU, p, c, 1, k, m.u0, m.u1, m.u2), FXip = tflux<UP>(t, p.FlxU, p, c + 1, 1, k, m.u1, m.u2, m.u3);
-  double FEj, FEjp;
+  double FXi, FXip, FEj, FEjp;
+  if (NEAR) {   // first differences in i exist on columns istr..iend+1 between walls (compute_horiz_tracer_fluxes.h:50-84)
+    FXi = tflux_cl<UP>(p, t, p.FlxU, p.umask, c, 1, k, iclamp(p, i - 1, p.istr, p.iend + 1), iclamp(p, i, p.istr, p.iend + 1), iclamp(p, i + 1, p.istr, p.iend + 1));
+    FXip = tflux_cl<UP>(p, t, p.FlxU, p.umask, c + 1, 1, k, iclamp(p, i, p.istr, p.iend + 1), iclamp(p, i + 1, p.istr, p.iend + 1),
+                        iclamp(p, i + 2, p.istr, p.iend + 1));
+  } else {
+    FXi = tflux<UP>(t, p.FlxU, p, c, 1, k, m.u0, m.u1, m.u2);
+    FXip = tflux<UP>(t, p.FlxU, p, c + 1, 1, k, m.u1, m.u2, m.u3);
+  }
   if (NEAR) {
     FEj = tflux_cl<UP>(p, t, p.FlxV, p.vmask, c, SX, k, jclamp(p, j - 1, p.jstr, p.jend + 1), jclamp(p, j, p.jstr, p.jend + 1), jclamp(p, j + 1, p.jstr, p.jend + 1));
     FEjp = tflux_cl<UP>(p, t, p.FlxV, p.vmask, c + SX, SX, k, jclamp(p, j, p.jstr, p.jend + 1), jclamp(p, j + 1, p.jstr, p.jend + 1),
@@ -692,12 +725,12 @@ __global__ void __launch_bounds__(256, LB_TP) k_pre_t_horiz(const __grid_constan
   const int k0 = blockIdx.z * KB + 1;
   const TMask m = tmask_load(p, c);
   const double cdt = dtau * p.pm[c] * p.pn[c];
-  const bool near = WALL && ((p.swall && j <= p.jstr + 2) || (p.nwall && j >= p.jend - 2));
+  const bool near = WALL && near_wall(p, i, j);
 #pragma unroll
   for (int q = 0; q < KB; ++q) {
     const int k = k0 + q;
     if (k <= p.N) {
-      const double dv = near ? tdiv<false, true>(p, t_rhs, c, j, k, m) : tdiv<false, false>(p, t_rhs, c, j, k, m);
+      const double dv = near ? tdiv<false, true>(p, t_rhs, c, i, j, k, m) : tdiv<false, false>(p, t_rhs, c, i, j, k, m);
       const double Hz = R3(p.Hz, c, k), Hz_bak = Hz + R3(p.FlxDiv, c, k);
       const double ts = R3(t_stp, c, k);
       R3(t_new, c, k) = Hz_bak * (cf_stp * ts + cf_bak * R3(t_indx, c, k)) - cdt * (dv);
@@ -711,12 +744,12 @@ __global__ void __launch_bounds__(256, LB_TC) k_t_horiz(const __grid_constant__ 
   const int k0 = blockIdx.z * KB + 1;
   const TMask m = tmask_load(p, c);
   const double cdt = p.dt * p.pm[c] * p.pn[c];
-  const bool near = WALL && ((p.swall && j <= p.jstr + 2) || (p.nwall && j >= p.jend - 2));
+  const bool near = WALL && near_wall(p, i, j);
 #pragma unroll
   for (int q = 0; q < KB; ++q) {
     const int k = k0 + q;
     if (k <= p.N) {
-      const double dv = near ? tdiv<true, true>(p, t_rhs, c, j, k, m) : tdiv<true, false>(p, t_rhs, c, j, k, m);
+      const double dv = near ? tdiv<true, true>(p, t_rhs, c, i, j, k, m) : tdiv<true, false>(p, t_rhs, c, i, j, k, m);
       R3(t_new, c, k) = R3(t_new, c, k) - cdt * (dv);
     }
   }
@@ -724,7 +757,7 @@ __global__ void __launch_bounds__(256, LB_TC) k_t_horiz(const __grid_constant__ 
 
 // compute_rd_bott_drag.h:1-74 (log-layer drag when Zob>0, else linear rdrg capped by 0.8*Hz/dt)
 __global__ void k_rd_bott_drag(const __grid_constant__ KP p, const double* __restrict__ u, const double* __restrict__ v) {
-  THREAD_IJ(p.istr - 1, p.iend, p.jstrV - 1, p.jend)
+  THREAD_IJ(p.istrU - 1, p.iend, p.jstrV - 1, p.jend)
   const double vonKar = 0.41;
   if (p.Zob > 0.0) {
     const double u0 = R3(u, c, 1), u1 = R3(u, c + 1, 1), v0 = R3(v, c, 1), v1 = R3(v, c + SX, 1);
@@ -883,7 +916,7 @@ __global__ void __launch_bounds__(64, 8)
 k_uv_vert(const __grid_constant__ KP p, const double* __restrict__ u_rhs, double* __restrict__ u_new, const double* __restrict__ u_stp,
           double* __restrict__ u_indx, double dtau, double cf_stp, double cf_bak) {
   extern __shared__ double smem[];
-  THREAD_IJ(p.istr, p.iend, (DIR == 0 ? p.jstr : p.jstrV), p.jend)
+  THREAD_IJ((DIR == 0 ? p.istrU : p.istr), p.iend, (DIR == 0 ? p.jstr : p.jstrV), p.jend)
   ColScr sc = col_scratch(p, c, smem);
   const int N = p.N;
   const ix_t d = DIR == 0 ? 1 : SX;
@@ -1064,90 +1097,13 @@ __device__ __forceinline__ double s2d_zeta_new(const KP& p, const S2D& s, ix2_t 
   double zn = s.zs[c] + p.dtfast * p.pm[c] * p.pn[c] * (DUon - DUon1 + DVom - DVom1) + p.dtfast * p.swflx[c];
   return zn * p.rmask[c];
 }
-// rows jstrV-1..jend carry the continuity update; a row just outside a closed wall takes zetabc's gradient
-// condition (zetabc.F:3: zeta_new(i,jstr-1)=zeta_new(i,jstr)*rmask(i,jstr-1)), re-evaluating its neighbour's update.
-__global__ void __launch_bounds__(256, LB_S2D) k_step2d_zeta(const __grid_constant__ KP p, const __grid_constant__ S2D s) {
-  THREAD_IJT(ix2_t, p.istr - 1, p.iend, (p.swall ? p.jstrR : p.jstr - 1), p.jendR)
-  double zn;
-  if (p.swall && j < p.jstr) zn = s2d_zeta_new(p, s, c + SX) * p.rmask[c];
-  else if (p.nwall && j > p.jend) zn = s2d_zeta_new(p, s, c - SX) * p.rmask[c];
-  else zn = s2d_zeta_new(p, s, c);
-  p.zeta_new[c] = zn;
-  if (i >= p.istr && j >= p.jstrR) {
-    const double DUon = s2d_DUon(p, s, c);
-    const double DVom = (j >= p.jstrV - 1) ? s2d_DVom(p, s, c) : 0.0;   // the reference's DVom scratch is never filled below a southern wall
-    s.zn[c] = zn;
-    if (s.iif == 1) {
-      p.DU_avg_bak[c] = p.DU_avg1[c] - 0.1024390243902439 * p.DU_avg2[c];
-      p.DV_avg_bak[c] = p.DV_avg1[c] - 0.1024390243902439 * p.DV_avg2[c];
-      p.Zt_avg1[c] = s.w1 * zn;
-      p.DU_avg1[c] = 0.0;
-      p.DV_avg1[c] = 0.0;
-      p.DU_avg2[c] = s.w2 * DUon;
-      p.DV_avg2[c] = s.w2 * DVom;
-    } else {
-      p.Zt_avg1[c] = p.Zt_avg1[c] + s.w1 * zn;
-      p.DU_avg2[c] = p.DU_avg2[c] + s.w2 * DUon;
-      p.DV_avg2[c] = p.DV_avg2[c] + s.w2 * DVom;
-    }
-  }
-}
-// stage 2: pressure-gradient terms rubar,rvbar (step2d_FB.F:245-268, first-substep correction :313-384),
-// ubar,vbar(knew), DU_avg1/DV_avg1; on the last substep zeta(knew)=Zt_avg1 (:563).
+// pressure-gradient terms rubar,rvbar (step2d_FB.F:245-268, first-substep correction :313-384)
 struct S2Pt { double UFx, UFe, VFx, VFe; };
-__device__ __forceinline__ S2Pt s2d_pt(const KP& p, const S2D& s, ix2_t c, bool corr, bool valid = true) {
-  S2Pt r;
-  if (!valid) { r.UFx = r.UFe = r.VFx = r.VFe = 0.0; return r; }   // row below a southern wall: zero-initialised scratch in the reference
-  const double zn = p.zeta_new[c], zs = s.zs[c];
-  if (!corr) {
-    r.UFx = s.bkw_new * zn + s.bkw * zs + s.bkw1 * s.zb[c] + s.bkw2 * s.zo[c];
-    r.UFe = (1.0 + p.rhoS[c]) * r.UFx;
-    r.VFx = r.UFx * (p.rhoS[c] - p.rhoA[c]);
-    r.VFe = r.UFe * r.UFx;
-  } else {
-    r.UFx = zn - zs;
-    r.UFe = (1.0 + p.rhoS[c]) * r.UFx;
-    r.VFe = r.UFe * (zn + zs);
-    r.VFx = r.UFx * (p.rhoS[c] - p.rhoA[c]);
-  }
-  return r;
-}
 __device__ __forceinline__ double s2d_pgf(const KP& p, double cff, double dn, ix2_t c, ix2_t d, const S2Pt& a, const S2Pt& b) {
   // a at c-d, b at c
   return cff * dn *
          ((p.h[c - d] + p.h[c]) * (a.UFe - b.UFe) + a.VFe - b.VFe +
           (p.h[c - d] - p.h[c]) * (a.VFx + b.VFx + 0.333333333333 * (p.rhoA[c - d] - p.rhoA[c]) * (a.UFx - b.UFx)));
-}
-__global__ void __launch_bounds__(256, LB_S2D) k_step2d_uv(const __grid_constant__ KP p, const __grid_constant__ S2D s) {
-  THREAD_IJT(ix2_t, p.istr, p.iend, p.jstr, p.jend)
-  const double cffg = 0.5 * p.g;
-  const bool sv = (j - 1 >= p.jstrV - 1);     // row j-1 carries a zeta_new
-  const bool dov = (j >= p.jstrV);
-  const S2Pt a0 = s2d_pt(p, s, c, false), aw = s2d_pt(p, s, c - 1, false), as = s2d_pt(p, s, c - SX, false, sv);
-  double rubar = s2d_pgf(p, cffg, p.dn_u[c], c, 1, aw, a0);
-  double rvbar = s2d_pgf(p, cffg, p.dm_v[c], c, SX, as, a0);
-  double rufrc = p.rufrc[c], rvfrc = p.rvfrc[c];
-  if (s.iif == 1) {
-    rufrc = rufrc - rubar;
-    rvfrc = rvfrc - rvbar;
-    p.rufrc[c] = rufrc;
-    p.rvfrc[c] = rvfrc;
-    const S2Pt b0 = s2d_pt(p, s, c, true), bw = s2d_pt(p, s, c - 1, true), bs = s2d_pt(p, s, c - SX, true, sv);
-    rubar = rubar + s2d_pgf(p, cffg, p.dn_u[c], c, 1, bw, b0);
-    rvbar = rvbar + s2d_pgf(p, cffg, p.dm_v[c], c, SX, bs, b0);
-  }
-  const double D0 = s.zs[c] + p.h[c], Dw = s.zs[c - 1] + p.h[c - 1], Ds = s.zs[c - SX] + p.h[c - SX];
-  const double Dn0 = p.zeta_new[c] + p.h[c], Dnw = p.zeta_new[c - 1] + p.h[c - 1], Dns = p.zeta_new[c - SX] + p.h[c - SX];
-  const double cff = 0.5 * p.dtfast, cff1 = 0.5 * s.w1;
-  const double DUnew = ((D0 + Dw) * s.us[c] + cff * (p.pm[c] + p.pm[c - 1]) * (p.pn[c] + p.pn[c - 1]) * (rubar + rufrc)) * p.umask[c];
-  s.un[c] = DUnew / (Dn0 + Dnw);
-  p.DU_avg1[c] = p.DU_avg1[c] + cff1 * p.dn_u[c] * (DUnew);
-  if (dov) {
-    const double DVnew = ((D0 + Ds) * s.vs[c] + cff * (p.pm[c] + p.pm[c - SX]) * (p.pn[c] + p.pn[c - SX]) * (rvbar + rvfrc)) * p.vmask[c];
-    s.vn[c] = DVnew / (Dn0 + Dns);
-    p.DV_avg1[c] = p.DV_avg1[c] + cff1 * p.dm_v[c] * (DVnew);
-  }
-  if (s.iif == s.nfast) s.zn[c] = p.Zt_avg1[c];
 }
 // ---- fused barotropic substep ---------------------------------------------------------------------------------
 // One launch per substep: a 32x8 tile first evaluates zeta_new on its points plus the row below and the column to
@@ -1217,15 +1173,15 @@ __global__ void __launch_bounds__(S2_TX * S2_TY, LB_S2D) k_step2d(const __grid_c
   const int i = i0 + tx, j = j0 + ty;
   const ix2_t SX = p.SX;
   // ---- phase 1: zeta_new (step2d_FB.F:151-216) on the tile, the row below it and the column to its left
-  if (i >= p.istr - 1 && i <= p.iend && j <= p.jend) zt[ty + 1][tx + 1] = s2d_zeta_new(p, s, CIDX(i, j));
+  if (i >= p.istrU - 1 && i <= p.iend && j <= p.jend) zt[ty + 1][tx + 1] = s2d_zeta_new(p, s, CIDX(i, j));
   {
     const int t = ty * S2_TX + tx;
     if (t < S2_TX + 1) {
       const int ii = i0 - 1 + t, jj = j0 - 1;
-      if (ii >= p.istr - 1 && ii <= p.iend) zt[0][t] = s2d_zn_at(p, s, CIDX(ii, jj), jj);
+      if (ii >= p.istrU - 1 && ii <= p.iend) zt[0][t] = s2d_zn_at(p, s, CIDX(ii, jj), jj);
     } else if (t < S2_TX + 1 + S2_TY) {
       const int r = t - (S2_TX + 1), ii = i0 - 1, jj = j0 + r;
-      if (ii >= p.istr - 1 && jj <= p.jend) zt[r + 1][0] = s2d_zeta_new(p, s, CIDX(ii, jj));
+      if (ii >= p.istrU - 1 && jj <= p.jend) zt[r + 1][0] = s2d_zeta_new(p, s, CIDX(ii, jj));
     }
   }
   __syncthreads();
@@ -1238,8 +1194,9 @@ __global__ void __launch_bounds__(S2_TX * S2_TY, LB_S2D) k_step2d(const __grid_c
   const double cffg = 0.5 * p.g;
   const bool sv = (j - 1 >= p.jstrV - 1);     // row j-1 carries a zeta_new
   const bool dov = (j >= p.jstrV);
+  const bool dou = (i >= p.istrU);            // u(istr) sits on a closed western wall: u2dbc, not the momentum update
   const S2Pt zero = {0.0, 0.0, 0.0, 0.0};     // row below a southern wall: zero-initialised scratch in the reference
-  const S2Pt a0 = s2d_ptz(p, s, c, zn, false), aw = s2d_ptz(p, s, c - 1, znw, false), as = sv ? s2d_ptz(p, s, c - SX, zns, false) : zero;
+  const S2Pt a0 = s2d_ptz(p, s, c, zn, false), aw = dou ? s2d_ptz(p, s, c - 1, znw, false) : zero, as = sv ? s2d_ptz(p, s, c - SX, zns, false) : zero;
   double rubar = s2d_pgf(p, cffg, p.dn_u[c], c, 1, aw, a0);
   double rvbar = s2d_pgf(p, cffg, p.dm_v[c], c, SX, as, a0);
   double rufrc = p.rufrc[c], rvfrc = p.rvfrc[c];
@@ -1248,17 +1205,20 @@ __global__ void __launch_bounds__(S2_TX * S2_TY, LB_S2D) k_step2d(const __grid_c
     rvfrc = rvfrc - rvbar;
     p.rufrc[c] = rufrc;
     p.rvfrc[c] = rvfrc;
-    const S2Pt b0 = s2d_ptz(p, s, c, zn, true), bw = s2d_ptz(p, s, c - 1, znw, true), bs = sv ? s2d_ptz(p, s, c - SX, zns, true) : zero;
+    const S2Pt b0 = s2d_ptz(p, s, c, zn, true), bw = dou ? s2d_ptz(p, s, c - 1, znw, true) : zero, bs = sv ? s2d_ptz(p, s, c - SX, zns, true) : zero;
     rubar = rubar + s2d_pgf(p, cffg, p.dn_u[c], c, 1, bw, b0);
     rvbar = rvbar + s2d_pgf(p, cffg, p.dm_v[c], c, SX, bs, b0);
   }
   const double D0 = s.zs[c] + p.h[c], Dw = s.zs[c - 1] + p.h[c - 1], Ds = s.zs[c - SX] + p.h[c - SX];
   const double Dn0 = zn + p.h[c], Dnw = znw + p.h[c - 1], Dns = zns + p.h[c - SX];
   const double cff = 0.5 * p.dtfast, cff1 = 0.5 * s.w1;
-  const double DUnew = ((D0 + Dw) * s.us[c] + cff * (p.pm[c] + p.pm[c - 1]) * (p.pn[c] + p.pn[c - 1]) * (rubar + rufrc)) * p.umask[c];
-  const double un = DUnew / (Dn0 + Dnw);
+  double un = 0.0;      // u2dbc_im.F on a closed western wall: ubar(istr)=0 (its DU_avg1 term is identically zero)
+  if (dou) {
+    const double DUnew = ((D0 + Dw) * s.us[c] + cff * (p.pm[c] + p.pm[c - 1]) * (p.pn[c] + p.pn[c - 1]) * (rubar + rufrc)) * p.umask[c];
+    un = DUnew / (Dn0 + Dnw);
+    p.DU_avg1[c] = DU1 + cff1 * p.dn_u[c] * (DUnew);
+  } else if (s.iif == 1) p.DU_avg1[c] = DU1;
   s2d_store(p, s.un, i, j, c, un);
-  p.DU_avg1[c] = DU1 + cff1 * p.dn_u[c] * (DUnew);
   if (dov) {
     const double DVnew = ((D0 + Ds) * s.vs[c] + cff * (p.pm[c] + p.pm[c - SX]) * (p.pn[c] + p.pn[c - SX]) * (rvbar + rvfrc)) * p.vmask[c];
     s2d_store(p, s.vn, i, j, c, DVnew / (Dn0 + Dns));
@@ -1285,7 +1245,8 @@ __global__ void __launch_bounds__(S2_TX * S2_TY, LB_S2D) k_step2d(const __grid_c
       s2d_avg_out(p, s, i, jw, w, znb, s2d_DUon(p, s, w), side == 0 ? 0.0 : s2d_DVom(p, s, w), DU1w, DV1w, Ztw);
       const double unw = p.gamma2 * un * p.umask[w];          // u2dbc_im.F:150-152
       s2d_store(p, s.un, i, jw, w, unw);
-      p.DU_avg1[w] = DU1w + cff1 * ((p.h[w] + znb) + (p.h[w - 1] + znbw)) * (unw)*p.dn_u[w];
+      if (dou) p.DU_avg1[w] = DU1w + cff1 * ((p.h[w] + znb) + (p.h[w - 1] + znbw)) * (unw)*p.dn_u[w];
+      else if (s.iif == 1) p.DU_avg1[w] = DU1w;     // on the western wall the term is identically zero (ubar=0)
       if (side == 1) {                                        // v2dbc_im.F: no normal flow through the northern wall
         const double vnw = 0.0;
         s2d_store(p, s.vn, i, jw, w, vnw);
@@ -1295,56 +1256,110 @@ __global__ void __launch_bounds__(S2_TX * S2_TY, LB_S2D) k_step2d(const __grid_c
     }
   }
 }
-// Closed-wall rows of the barotropic step: u2dbc_im.F:150-152 (gamma2 slip), v2dbc_im.F (no normal flow), the
-// boundary-row contributions to DU_avg1/DV_avg1 (step2d_FB.F:449-529) and zeta(knew)=Zt_avg1 on the last substep.
-__global__ void k_step2d_bc(const __grid_constant__ KP p, const __grid_constant__ S2D s) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x - IOFF;
-  if (i < p.istr || i > p.iend) return;
-  const ix2_t SX = p.SX;
-  const double cff1 = 0.5 * s.w1;
-  if (p.swall) {
-    const ix2_t c = CIDX(i, p.jstr - 1), cv = CIDX(i, p.jstrV - 1);
-    s.un[c] = p.gamma2 * s.un[c + SX] * p.umask[c];
-    s.vn[cv] = 0.0;
-    const double Dn = p.h[c] + p.zeta_new[c], Dnw = p.h[c - 1] + p.zeta_new[c - 1];
-    p.DU_avg1[c] = p.DU_avg1[c] + cff1 * (Dn + Dnw) * (s.un[c]) * p.dn_u[c];
-    const double Dv = p.zeta_new[cv] + p.h[cv], Dvs = p.h[cv - SX] + p.zeta_new[cv - SX];
-    p.DV_avg1[cv] = p.DV_avg1[cv] + cff1 * (Dv + Dvs) * (s.vn[cv]) * p.dm_v[cv];
-    if (s.iif == s.nfast) s.zn[c] = p.Zt_avg1[c];
-  }
-  if (p.nwall) {
-    const ix2_t c = CIDX(i, p.jend + 1);
-    s.un[c] = p.gamma2 * s.un[c - SX] * p.umask[c];
-    s.vn[c] = 0.0;
-    const double Dn = p.h[c] + p.zeta_new[c], Dnw = p.h[c - 1] + p.zeta_new[c - 1], Ds = p.zeta_new[c - SX] + p.h[c - SX];
-    p.DU_avg1[c] = p.DU_avg1[c] + cff1 * (Dn + Dnw) * (s.un[c]) * p.dn_u[c];
-    p.DV_avg1[c] = p.DV_avg1[c] + cff1 * (Dn + Ds) * (s.vn[c]) * p.dm_v[c];
-    if (s.iif == s.nfast) s.zn[c] = p.Zt_avg1[c];
-  }
+// zeta_new at any point of the rho-range incl. wall rows, wall columns and basin corners (zetabc.F:39-81)
+__device__ __forceinline__ double s2d_zn_full(const KP& p, const S2D& s, int i, int j) {
+  const int ii = (p.wwall && i < p.istr) ? p.istr : ((p.ewall && i > p.iend) ? p.iend : i);
+  const int jj = (p.swall && j < p.jstr) ? p.jstr : ((p.nwall && j > p.jend) ? p.jend : j);
+  const double zin = s2d_zeta_new(p, s, CIDX(ii, jj));
+  if (ii == i && jj == j) return zin;
+  if (ii != i && jj != j) return 0.5 * (zin * p.rmask[CIDX(ii, j)] + zin * p.rmask[CIDX(i, jj)]);   // corner: mean of its two edge neighbours
+  return zin * p.rmask[CIDX(i, j)];
 }
-// u3dbc_im.F:293-295 / t3dbc_im.F:86-96 / omega.F:171-231 on closed N/S walls: ghost row = factor * first interior row
-// [* mask(ghost)] for planes k0..k0+nk-1; ZERO: v3dbc_im.F no-normal-flow rows jstr and jend+1.
-template <bool ZERO>
-__global__ void k_bc_rows(const __grid_constant__ KP p, double* __restrict__ a, double factor, const double* __restrict__ msk) {
-  const int i = blockIdx.x * blockDim.x + threadIdx.x - IOFF;
-  if (i < p.istr || i > p.iend) return;
-  const ix_t SX = p.SX, ko = (ix_t)blockIdx.z * p.SXY;
-  if (p.swall) {
-    if (ZERO) a[CIDX(i, p.jstr) + ko] = 0.0;
-    else {
-      const ix_t c = CIDX(i, p.jstr - 1);
-      double v = factor * a[c + SX + ko];
-      if (msk) v = v * msk[c];
-      a[c + ko] = v;
-    }
+// Closed western/eastern walls of the barotropic substep, launched after k_step2d: one thread per wall-column point
+// (x = row index, y = 0 west / 1 east).  zetabc on the column and the corners, the fast-time averages there,
+// v2dbc slip columns and their DV_avg1 term (step2d_FB.F:259-303), u2dbc zero flow through the eastern wall.
+__global__ void k_step2d_ew(const __grid_constant__ KP p, const __grid_constant__ S2D s) {
+  const int west = blockIdx.y == 0;
+  if (west ? !p.wwall : !p.ewall) return;
+  const int j = p.jstrR + blockIdx.x * blockDim.x + threadIdx.x;
+  if (j > p.jendR) return;
+  const int iw = west ? p.istr - 1 : p.iend + 1, ia = west ? p.istr : p.iend;
+  const ix2_t c = CIDX(iw, j), SX = p.SX;
+  const double zn = s2d_zn_full(p, s, iw, j);
+  // DUon at i=istr-1 is never filled by the reference (zero scratch), likewise DVom below a southern wall
+  const double DUon = west ? 0.0 : s2d_DUon(p, s, c);
+  const double DVom = (j >= p.jstrV - 1) ? s2d_DVom(p, s, c) : 0.0;
+  double DU1, DV1, Zt;
+  s2d_avg_out(p, s, iw, j, c, zn, DUon, DVom, DU1, DV1, Zt);
+  if (s.iif == 1) p.DU_avg1[c] = DU1;
+  const double cff1 = 0.5 * s.w1;
+  if (j >= p.jstr) {     // v2dbc_im.F: gamma2 slip; v on the S/N wall rows has just been zeroed
+    const bool zeroed = (p.swall && j == p.jstr) || (p.nwall && j == p.jend + 1);
+    const double vsrc = zeroed ? 0.0 : s.vn[CIDX(ia, j)];
+    const double vn = p.gamma2 * vsrc * p.vmask[c];
+    s.vn[c] = vn;
+    if (j >= p.jstrV && j <= p.jend) {
+      const double Dn = p.h[c] + zn, Dns = p.h[c - SX] + s2d_zn_full(p, s, iw, j - 1);
+      p.DV_avg1[c] = DV1 + cff1 * (Dn + Dns) * (vn)*p.dm_v[c];
+    } else if (s.iif == 1) p.DV_avg1[c] = DV1;
+  } else if (s.iif == 1) p.DV_avg1[c] = DV1;
+  if (!west) {           // u2dbc_im.F: no flow through the eastern wall (u-point iend+1); slip rule on the wall rows gives gamma2*0*umask
+    const bool row = (j < p.jstr) || (j > p.jend);
+    s.un[c] = row ? p.gamma2 * 0.0 * p.umask[c] : 0.0;
   }
-  if (p.nwall) {
-    const ix_t c = CIDX(i, p.jend + 1);
-    if (ZERO) a[c + ko] = 0.0;
-    else {
-      double v = factor * a[c - SX + ko];
-      if (msk) v = v * msk[c];
-      a[c + ko] = v;
+  if (s.iif == s.nfast) s.zn[c] = Zt;
+}
+
+// Lateral boundary conditions of the 3-D fields on closed walls, one launch per field: u3dbc_im.F:293-295 (u: zero on the
+// W/E wall, gamma2 slip rows), v3dbc_im.F (v: zero on the S/N wall, slip columns), t3dbc_im.F:86-144 (gradient + the
+// mask-weighted corner mean), omega.F:171-231 (We/Wi copies + corners).  Every boundary point is written by one thread as a
+// pure function of interior values, so the result does not depend on the order in which the reference applies the edges
+// (where one edge rule reads a value another edge rule has just set, that value is substituted: it is always 0).
+// grid: x = position along the edge, y = side (0 S row, 1 N row, 2 W column, 3 E column), z = level.
+enum { BC_U = 0, BC_V = 1, BC_T = 2, BC_W = 3 };
+template <int KIND>
+__global__ void k_bc3d(const __grid_constant__ KP p, double* __restrict__ a, double gamma2) {
+  const int side = blockIdx.y, q = blockIdx.x * blockDim.x + threadIdx.x;
+  const ix_t ko = (ix_t)blockIdx.z * p.SXY;
+  if (side < 2) {
+    if (side == 0 ? !p.swall : !p.nwall) return;
+    const int i = p.istr - 1 + q;
+    if (i > p.iend + 1) return;
+    const int jw = side == 0 ? p.jstr - 1 : p.jend + 1, ja = side == 0 ? p.jstr : p.jend;
+    const bool wc = i < p.istr, ec = i > p.iend;       // corner columns
+    if (KIND == BC_U) {
+      if (i < p.istr || i > p.iendR) return;
+      const bool onwall = (p.wwall && i == p.istr) || (p.ewall && i == p.iend + 1);      // u there has just been zeroed
+      const double src = onwall ? 0.0 : a[CIDX(i, ja) + ko];
+      a[CIDX(i, jw) + ko] = gamma2 * src * p.umask[CIDX(i, jw)];
+    } else if (KIND == BC_V) {
+      if (wc || ec) return;
+      a[CIDX(i, side == 0 ? p.jstr : p.jend + 1) + ko] = 0.0;
+    } else if (KIND == BC_T) {
+      if (!wc && !ec) a[CIDX(i, jw) + ko] = a[CIDX(i, ja) + ko] * p.rmask[CIDX(i, jw)];
+      else if ((wc && p.wwall) || (ec && p.ewall)) {
+        const int ii = wc ? p.istr : p.iend;
+        const double tin = a[CIDX(ii, ja) + ko];
+        const double ra = p.rmask[CIDX(ii, jw)], rb = p.rmask[CIDX(i, ja)];
+        const double ta = tin * ra, tb = tin * rb;    // the two edge values next to the corner
+        double cff = ra + rb;
+        if (cff > 0.0) {
+          cff = 1.0 / cff;
+          a[CIDX(i, jw) + ko] = cff * (ra * ta + rb * tb);
+        } else a[CIDX(i, jw) + ko] = 0.0;
+      }
+    } else {
+      if (!wc && !ec) a[CIDX(i, jw) + ko] = a[CIDX(i, ja) + ko];
+      else if ((wc && p.wwall) || (ec && p.ewall)) a[CIDX(i, jw) + ko] = a[CIDX(wc ? p.istr : p.iend, ja) + ko];
+    }
+  } else {
+    if (side == 2 ? !p.wwall : !p.ewall) return;
+    const int j = p.jstr + q;
+    const int iw = side == 2 ? p.istr - 1 : p.iend + 1, ia = side == 2 ? p.istr : p.iend;
+    if (KIND == BC_U) {
+      if (j > p.jend) return;
+      a[CIDX(side == 2 ? p.istr : p.iend + 1, j) + ko] = 0.0;
+    } else if (KIND == BC_V) {
+      if (j > p.jendR) return;
+      const bool zeroed = (p.swall && j == p.jstr) || (p.nwall && j == p.jend + 1);       // v there has just been zeroed
+      const double src = zeroed ? 0.0 : a[CIDX(ia, j) + ko];
+      a[CIDX(iw, j) + ko] = gamma2 * src * p.vmask[CIDX(iw, j)];
+    } else if (KIND == BC_T) {
+      if (j > p.jend) return;
+      a[CIDX(iw, j) + ko] = a[CIDX(ia, j) + ko] * p.rmask[CIDX(iw, j)];
+    } else {
+      if (j > p.jend) return;
+      a[CIDX(iw, j) + ko] = a[CIDX(ia, j) + ko];
     }
   }
 }
@@ -1355,7 +1370,7 @@ __global__ void k_bc_rows(const __grid_constant__ KP p, double* __restrict__ a, 
 // minus its mismatch with DU_avg2.  Column kernels without scratch (re-read through L1/L2).
 template <int DIR>
 __global__ void k_uv2_pass0(const __grid_constant__ KP p, double* __restrict__ u) {
-  THREAD_IJT(ixc_t, p.istr, p.iend, (DIR == 0 ? p.jstr : p.jstrV), p.jend)
+  THREAD_IJT(ixc_t, (DIR == 0 ? p.istrU : p.istr), p.iend, (DIR == 0 ? p.jstr : p.jstrV), p.jend)
   const ixc_t d = DIR == 0 ? 1 : SX;
   const int N = p.N;
   const double dn = DIR == 0 ? p.dn_u[c] : p.dm_v[c];
@@ -1376,7 +1391,7 @@ __global__ void k_uv2_pass0(const __grid_constant__ KP p, double* __restrict__ u
 }
 template <int DIR>
 __global__ void k_uv2_pass1(const __grid_constant__ KP p, double* __restrict__ u, const double* __restrict__ u_stp, double* __restrict__ bar) {
-  THREAD_IJT(ixc_t, p.istr, p.iend, (DIR == 0 ? p.jstrR : p.jstr), p.jendR)
+  THREAD_IJT(ixc_t, (DIR == 0 ? p.istr : p.istrR), p.iendR, (DIR == 0 ? p.jstrR : p.jstr), p.jendR)
   const ixc_t d = DIR == 0 ? 1 : SX;
   const int N = p.N;
   const double dn = DIR == 0 ? p.dn_u[c] : p.dm_v[c];

@@ -22,6 +22,8 @@ struct KP {
   int istr, iend, jstr, jend;   // compute_tile_bounds.h with NSUB_X=NSUB_E=1
   int swall, nwall;             // this subdomain touches a closed (non-periodic) southern / northern physical edge
   int jstrR, jendR, jstrV;      // compute_auxiliary_bounds.h: jstr-1 / jend+1 / jstr+1 on such an edge, else jstr / jend / jstr
+  int wwall, ewall;             // likewise a closed western / eastern physical edge
+  int istrR, iendR, istrU;      // istr-1 / iend+1 / istr+1 on such an edge, else istr / iend / istr
   int nonlin, salinity;
   int wrap_x, wrap_y;           // single subdomain along a periodic direction: the fused 2-D kernel stores the halo images itself
   // scalars

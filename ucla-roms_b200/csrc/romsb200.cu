@@ -54,7 +54,6 @@ struct roms_ctx {
   std::vector<KTimer> ktimers;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   int col_bx = 32, col_by = 2, pl_bx = 32, pl_by = 8;   // plane tiles 32x8: fewest halo-row re-reads through L2 (profiles/r1_tuning_log.txt)
-  int s2d_fused = 1;   // ROMS_S2D_FUSED=0 selects the three-launch barotropic substep (zeta, uv, wall rows)
   int use_smem = 0;   // measured on B200 (profiles/r1_scratch_policy.txt): occupancy beats shared-memory scratch
   Comm comm;
   double* u(int l) { return f[ROMS_U].ptr[l - 1]; }
@@ -201,7 +200,6 @@ const char* roms_last_error(void) { return g_err.c_str(); }
 int roms_create(const roms_cfg* cfg, int device, roms_ctx** out) {
   if (!cfg || !out) { g_err = "roms_create: null argument"; return -1; }
   if (cfg->NT > MAXNT || cfg->N < 3 || cfg->Lm < 2 || cfg->Mm < 2) { g_err = "roms_create: unsupported sizes"; return -1; }
-  if (!cfg->ew_periodic) { g_err = "roms_create: closed/open western and eastern edges are not implemented yet (EW_PERIODIC only; N/S may be closed walls)"; return -1; }
   CK(cudaSetDevice(device));
   roms_ctx* h = new roms_ctx();
   h->c = *cfg;
@@ -220,6 +218,10 @@ int roms_create(const roms_cfg* cfg, int device, roms_ctx** out) {
     p.swall = (!cfg->ns_periodic && cfg->jnode == 0) ? 1 : 0;          // SOUTHERN_EDGE of set_global_definitions.h
     p.nwall = (!cfg->ns_periodic && cfg->jnode == npe - 1) ? 1 : 0;    // NORTHERN_EDGE
     p.jstrR = p.swall ? p.jstr - 1 : p.jstr; p.jendR = p.nwall ? p.jend + 1 : p.jend; p.jstrV = p.swall ? p.jstr + 1 : p.jstr;
+    const int npx = cfg->np_xi > 0 ? cfg->np_xi : 1;
+    p.wwall = (!cfg->ew_periodic && cfg->inode == 0) ? 1 : 0;          // WESTERN_EDGE
+    p.ewall = (!cfg->ew_periodic && cfg->inode == npx - 1) ? 1 : 0;    // EASTERN_EDGE
+    p.istrR = p.wwall ? p.istr - 1 : p.istr; p.iendR = p.ewall ? p.iend + 1 : p.iend; p.istrU = p.wwall ? p.istr + 1 : p.istr;
   }
   p.nonlin = cfg->nonlin_eos; p.salinity = cfg->salinity;
   p.dt = cfg->dt; p.dtfast = cfg->dt / double(cfg->ndtfast);
@@ -229,10 +231,9 @@ int roms_create(const roms_cfg* cfg, int device, roms_ctx** out) {
   if (const char* e = getenv("ROMS_COL_BY")) h->col_by = atoi(e);
   if (const char* e = getenv("ROMS_PL_BX")) h->pl_bx = atoi(e);
   if (const char* e = getenv("ROMS_PL_BY")) h->pl_by = atoi(e);
-  if (const char* e = getenv("ROMS_S2D_FUSED")) h->s2d_fused = atoi(e);
   const bool single = cfg->np_xi * cfg->np_eta == 1;
-  p.wrap_x = (single && h->s2d_fused && cfg->ew_periodic) ? 1 : 0;
-  p.wrap_y = (single && h->s2d_fused && cfg->ns_periodic) ? 1 : 0;
+  p.wrap_x = (single && cfg->ew_periodic) ? 1 : 0;
+  p.wrap_y = (single && cfg->ns_periodic) ? 1 : 0;
   if (const char* e = getenv("ROMS_COL_SMEM")) h->use_smem = atoi(e);
   if ((size_t)2 * (N + 1) * h->col_bx * h->col_by * sizeof(double) > 200 * 1024) { h->col_by = 1; }
   if ((size_t)2 * (N + 1) * h->col_bx * h->col_by * sizeof(double) > 200 * 1024) h->use_smem = 0;
@@ -426,18 +427,22 @@ int roms_exchange(roms_ctx* h, int nfields, const int* fields, const int* lvls, 
 }
 
 // closed-wall boundary rows (u3dbc/v3dbc/t3dbc/omega copies): no-ops unless this subdomain touches a wall
-static int bc_rows(roms_ctx* h, double* a, int nk, double factor, const double* msk, bool zero) {
+static int bc3d(roms_ctx* h, double* a, int nk, int kind) {
   const KP& p = h->kp;
-  if (!p.swall && !p.nwall) return 0;
-  dim3 b(128, 1, 1), g((p.iend + IOFF + 1 + 127) / 128, 1, nk);
-  if (h->ktiming) kt_begin(h, "k_bc_rows");
-  if (zero) k_bc_rows<true><<<g, b, 0, h->st>>>(p, a, factor, msk);
-  else k_bc_rows<false><<<g, b, 0, h->st>>>(p, a, factor, msk);
+  if (!p.swall && !p.nwall && !p.wwall && !p.ewall) return 0;
+  const int len = (p.Lm > p.Mm ? p.Lm : p.Mm) + 3;
+  dim3 b(128, 1, 1), g((len + 127) / 128, 4, nk);
+  if (h->ktiming) kt_begin(h, "k_bc3d");
+  const double g2 = h->c.gamma2;
+  if (kind == BC_U) k_bc3d<BC_U><<<g, b, 0, h->st>>>(p, a, g2);
+  else if (kind == BC_V) k_bc3d<BC_V><<<g, b, 0, h->st>>>(p, a, g2);
+  else if (kind == BC_T) k_bc3d<BC_T><<<g, b, 0, h->st>>>(p, a, g2);
+  else k_bc3d<BC_W><<<g, b, 0, h->st>>>(p, a, g2);
   if (h->ktiming) kt_end(h);
   h->launches++;
   return 0;
 }
-#define WALLED(h) ((h)->kp.swall || (h)->kp.nwall)
+#define WALLED(h) ((h)->kp.swall || (h)->kp.nwall || (h)->kp.wwall || (h)->kp.ewall)
 
 // ---- setup_grid1.F:13-210 (metrics, masks, fomn): host arithmetic on pulled planes, pushed back --
 int roms_setup_grid(roms_ctx* h) {
@@ -451,12 +456,15 @@ int roms_setup_grid(roms_ctx* h) {
   std::vector<double> fomn(n2, 0.0), dm_r(n2, 0.0), dn_r(n2, 0.0), dm_u(n2, 0.0), dn_u(n2, 0.0), dm_v(n2, 0.0), dn_v(n2, 0.0), um(n2, 0.0), vm(n2, 0.0);
   const KP& pp = h->kp;
   for (int j = (pp.swall ? 0 : -1); j <= (pp.nwall ? Mm + 1 : Mm + 2); ++j)     // extended bounds stop one row outside a wall
-    for (int i = -1; i <= Lm + 2; ++i) fomn[at(i, j)] = f[at(i, j)] / (pm[at(i, j)] * pn[at(i, j)]);
+    for (int i = (pp.wwall ? 0 : -1); i <= (pp.ewall ? Lm + 1 : Lm + 2); ++i) fomn[at(i, j)] = f[at(i, j)] / (pm[at(i, j)] * pn[at(i, j)]);
   for (int j = pp.jstrR; j <= pp.jendR; ++j)
-    for (int i = 1; i <= Lm; ++i) {
-      const size_t q = at(i, j), w = at(i - 1, j);
+    for (int i = pp.istrR; i <= pp.iendR; ++i) {
+      const size_t q = at(i, j);
       dm_r[q] = 1.0 / pm[q]; dn_r[q] = 1.0 / pn[q];
-      dm_u[q] = 2.0 / (pm[q] + pm[w]); dn_u[q] = 2.0 / (pn[q] + pn[w]); um[q] = rm[q] * rm[w];
+      if (i >= 1) {
+        const size_t w = at(i - 1, j);
+        dm_u[q] = 2.0 / (pm[q] + pm[w]); dn_u[q] = 2.0 / (pn[q] + pn[w]); um[q] = rm[q] * rm[w];
+      }
       if (j >= 1) {
         const size_t s = at(i, j - 1);
         dm_v[q] = 2.0 / (pm[q] + pm[s]); dn_v[q] = 2.0 / (pn[q] + pn[s]); vm[q] = rm[q] * rm[s];
@@ -478,15 +486,15 @@ int roms_set_depth(roms_ctx* h, int tile) {
   (void)tile;
   CK(cudaSetDevice(h->device));
   const KP& p = h->kp;
-  if (h->iic == 0) PLANE(k_set_depth_init, p.iend, p.jstrR, p.jendR, 1, p, h->zeta(1), h->ubar(1), h->vbar(1));
-  PLANE(k_set_depth, p.iend, p.jstrR, p.jendR, p.N + 1, p, h->zeta(h->knew));
+  if (h->iic == 0) PLANE(k_set_depth_init, p.iendR, p.jstrR, p.jendR, 1, p, h->zeta(1), h->ubar(1), h->vbar(1));
+  PLANE(k_set_depth, p.iendR, p.jstrR, p.jendR, p.N + 1, p, h->zeta(h->knew));
   if (h->iic == 0) { int rc = exchange(h, {{p.hinv, 1}}); if (rc) return rc; }
   return exchange(h, {{p.z_w, p.N + 1}, {p.z_r, p.N}, {p.Hz, p.N}});
 }
 int roms_set_huv(roms_ctx* h) {
   CK(cudaSetDevice(h->device));
   const KP& p = h->kp;
-  PLANE(k_set_huv, p.iend, p.jstrR, p.jendR, p.N, p, h->u(h->nrhs), h->v(h->nrhs));
+  PLANE(k_set_huv, p.iendR, p.jstrR, p.jendR, p.N, p, h->u(h->nrhs), h->v(h->nrhs));
   return exchange(h, {{p.FlxU, p.N}, {p.FlxV, p.N}});
 }
 int roms_set_huv1(roms_ctx* h, int tile) {
@@ -494,8 +502,8 @@ int roms_set_huv1(roms_ctx* h, int tile) {
   CK(cudaSetDevice(h->device));
   const KP& p = h->kp;
   const int first = (h->iic == h->forw_start);
-  COLUMN(k_set_huv1<0>, 0, p.iend, p.jstrR, p.jendR, p, h->u(h->nnew), first);
-  COLUMN(k_set_huv1<1>, 0, p.iend, p.jstr, p.jendR, p, h->v(h->nnew), first);
+  COLUMN(k_set_huv1<0>, 0, p.iendR, p.jstrR, p.jendR, p, h->u(h->nnew), first);
+  COLUMN(k_set_huv1<1>, 0, p.iendR, p.jstr, p.jendR, p, h->v(h->nnew), first);
   return exchange(h, {{p.FlxU, p.N}, {p.FlxV, p.N}, {h->u(h->nnew), p.N}, {h->v(h->nnew), p.N}});
 }
 int roms_omega(roms_ctx* h) {
@@ -506,8 +514,8 @@ int roms_omega(roms_ctx* h) {
   else if (h->iic == h->forw_start) dtau = 0.5 * h->c.dt;
   else dtau = 0.6 * h->c.dt;
   COLUMN(k_omega, 2, p.iend, p.jstr, p.jend, p, dtau);
-  bc_rows(h, p.We, p.N + 1, 1.0, nullptr, false);      // omega.F:171-231 edge copies
-  bc_rows(h, p.Wi, p.N + 1, 1.0, nullptr, false);
+  bc3d(h, p.We, p.N + 1, BC_W);      // omega.F:171-231 edge copies
+  bc3d(h, p.Wi, p.N + 1, BC_W);
   return exchange(h, {{p.We, p.N + 1}, {p.Wi, p.N + 1}});
 }
 int roms_rho_eos(roms_ctx* h, int tidx) {
@@ -558,10 +566,10 @@ int roms_pre_step3d(roms_ctx* h, int tile) {
   COLUMN((k_uv_vert<0, 0>), 2, p.iend, p.jstr, p.jend, p, h->u(nrhs), h->u(nnew), h->u(nstp), h->u(indx), dtau, cf_stp, cf_bak);
   COLUMN((k_uv_vert<0, 1>), 2, p.iend, p.jstrV, p.jend, p, h->v(nrhs), h->v(nnew), h->v(nstp), h->v(indx), dtau, cf_stp, cf_bak);
   // u3dbc/v3dbc/t3dbc (pre_step3d4S.F:533-545), then one exchange per tracer (:548)
-  bc_rows(h, h->u(nnew), p.N, h->c.gamma2, p.umask, false);
-  bc_rows(h, h->v(nnew), p.N, 0.0, nullptr, true);
+  bc3d(h, h->u(nnew), p.N, BC_U);
+  bc3d(h, h->v(nnew), p.N, BC_V);
   for (int it = 1; it <= h->c.NT; ++it) {
-    bc_rows(h, h->t(nnew, it), p.N, 1.0, p.rmask, false);
+    bc3d(h, h->t(nnew, it), p.N, BC_T);
     int rc = exchange(h, {{h->t(nnew, it), p.N}});
     if (rc) return rc;
   }
@@ -604,25 +612,17 @@ int roms_step2d(roms_ctx* h) {
   s.zn = h->zeta(knew); s.un = h->ubar(knew); s.vn = h->vbar(knew);
   s.w1 = h->w1[iif]; s.w2 = h->w2[iif];
   s.iif = iif; s.nfast = h->nfast;
-  if (h->s2d_fused) {
+  {
     dim3 b_(S2_TX, S2_TY, 1), g_((p.iend + IOFF + 1 + S2_TX - 1) / S2_TX, (p.jend - p.jstr + 1 + S2_TY - 1) / S2_TY, 1);
     if (h->ktiming) kt_begin(h, "k_step2d");
     k_step2d<<<g_, b_, 0, h->st>>>(p, s);
     if (h->ktiming) kt_end(h);
     h->launches++;
-    if (iif == h->nfast) {
-      int rc = roms_set_depth(h, 0);
-      if (rc) return rc;
-    }
-    if (h->c.np_xi * h->c.np_eta == 1) return 0;      // periodic images already stored by the kernel
-    return exchange(h, {{s.zn, 1}, {s.un, 1}, {s.vn, 1}});
   }
-  PLANE(k_step2d_zeta, p.iend, (p.swall ? p.jstrR : p.jstr - 1), p.jendR, 1, p, s);
-  PLANE(k_step2d_uv, p.iend, p.jstr, p.jend, 1, p, s);
-  if (WALLED(h)) {
-    dim3 b_(128, 1, 1), g_((p.iend + IOFF + 1 + 127) / 128, 1, 1);
-    if (h->ktiming) kt_begin(h, "k_step2d_bc");
-    k_step2d_bc<<<g_, b_, 0, h->st>>>(p, s);
+  if (p.wwall || p.ewall) {
+    dim3 b_(128, 1, 1), g_((p.jendR - p.jstrR + 1 + 127) / 128, 2, 1);
+    if (h->ktiming) kt_begin(h, "k_step2d_ew");
+    k_step2d_ew<<<g_, b_, 0, h->st>>>(p, s);
     if (h->ktiming) kt_end(h);
     h->launches++;
   }
@@ -630,6 +630,7 @@ int roms_step2d(roms_ctx* h) {
     int rc = roms_set_depth(h, 0);
     if (rc) return rc;
   }
+  if (h->c.np_xi * h->c.np_eta == 1 && h->c.ew_periodic) return 0;      // periodic images already stored by the kernel
   return exchange(h, {{s.zn, 1}, {s.un, 1}, {s.vn, 1}});
 }
 int roms_step3d_uv2(roms_ctx* h, int tile) {
@@ -639,10 +640,10 @@ int roms_step3d_uv2(roms_ctx* h, int tile) {
   const int nnew = h->nnew, nstp = h->nstp, knew = h->knew;
   COLUMN(k_uv2_pass0<0>, 0, p.iend, p.jstr, p.jend, p, h->u(nnew));
   COLUMN(k_uv2_pass0<1>, 0, p.iend, p.jstrV, p.jend, p, h->v(nnew));
-  bc_rows(h, h->u(nnew), p.N, h->c.gamma2, p.umask, false);     // u3dbc_tile / v3dbc_tile (step3d_uv2.F:471-472)
-  bc_rows(h, h->v(nnew), p.N, 0.0, nullptr, true);
-  COLUMN(k_uv2_pass1<0>, 0, p.iend, p.jstrR, p.jendR, p, h->u(nnew), h->u(nstp), h->ubar(knew));
-  COLUMN(k_uv2_pass1<1>, 0, p.iend, p.jstr, p.jendR, p, h->v(nnew), h->v(nstp), h->vbar(knew));
+  bc3d(h, h->u(nnew), p.N, BC_U);     // u3dbc_tile / v3dbc_tile (step3d_uv2.F:471-472)
+  bc3d(h, h->v(nnew), p.N, BC_V);
+  COLUMN(k_uv2_pass1<0>, 0, p.iendR, p.jstrR, p.jendR, p, h->u(nnew), h->u(nstp), h->ubar(knew));
+  COLUMN(k_uv2_pass1<1>, 0, p.iendR, p.jstr, p.jendR, p, h->v(nnew), h->v(nstp), h->vbar(knew));
   int rc = exchange(h, {{p.FlxU, p.N}, {h->u(nnew), p.N}, {h->ubar(knew), 1}});
   if (rc) return rc;
   return exchange(h, {{p.FlxV, p.N}, {h->v(nnew), p.N}, {h->vbar(knew), 1}});
@@ -658,7 +659,7 @@ int roms_step3d_t(roms_ctx* h, int tile) {
     COLUMN(k_t_vert<1>, 2, p.iend, p.jstr, p.jend, p, h->t(nrhs, it), h->t(nnew, it), p.Akt[it >= 2 ? 1 : 0], h->f[ROMS_STFLX].ptr[it - 1], h->c.dt,
            it == 1 ? 1 : 0);
   }
-  for (int it = 1; it <= NT; ++it) bc_rows(h, h->t(nnew, it), p.N, 1.0, p.rmask, false);   // t3dbc_tile (step3d_t_ISO.F:1157-1159)
+  for (int it = 1; it <= NT; ++it) bc3d(h, h->t(nnew, it), p.N, BC_T);   // t3dbc_tile (step3d_t_ISO.F:1157-1159)
   for (int it = 1; it + 1 <= NT; it += 2) {
     int rc = exchange(h, {{h->t(nnew, it), p.N}, {h->t(nnew, it + 1), p.N}});
     if (rc) return rc;
