@@ -15,20 +15,22 @@ from romsb200 import Roms  # noqa: E402
 
 def main():
     nsteps = int(sys.argv[1]) if len(sys.argv) > 1 else 3
-    walls = len(sys.argv) > 2 and sys.argv[2] in ("walls", "seamount")
-    topo = len(sys.argv) > 2 and sys.argv[2] == "seamount"      # + bottom topography and a land mask
+    mode = sys.argv[2] if len(sys.argv) > 2 else "periodic"
+    walls = mode in ("walls", "seamount", "closed")
+    topo = mode in ("seamount", "closed")                        # + bottom topography and a land mask
+    ew = mode == "closed"                                        # closed basin: walls on all four sides
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
     npx, npe = cases.rank_grid(world)
     LG, MG, N = 24 * npx, 20 * npe, 10
-    cfg, st = cases.channel(LG, MG, N, ns_walls=walls, seamount=topo, island=topo, sub=(rank % npx, rank // npx, npx, npe))
+    cfg, st = cases.channel(LG, MG, N, ns_walls=walls, ew_walls=ew, seamount=topo, island=topo, sub=(rank % npx, rank // npx, npx, npe))
     g = Roms(cfg, local)
     g.attach_torch_comm(dist)
     cases.initialize(g, st)
     g.call("run", nsteps)
     dg = g.diag()
-    cfgG, stG = cases.channel(LG, MG, N, ns_walls=walls, seamount=topo, island=topo)
+    cfgG, stG = cases.channel(LG, MG, N, ns_walls=walls, ew_walls=ew, seamount=topo, island=topo)
     o = Oracle(cfgG)
     cases.initialize(o, stG)
     o.call("run", nsteps)
@@ -44,6 +46,9 @@ def main():
         if walls:      # rows beyond a closed wall are allocated but undefined
             ja, jb = (1 if rank // npx == 0 else 0), (-1 if rank // npx == npe - 1 else None)
             a, b = a[..., ja:jb, :], b[..., ja:jb, :]
+        if ew:
+            ia, ib = (1 if rank % npx == 0 else 0), (-1 if rank % npx == npx - 1 else None)
+            a, b = a[..., :, ia:ib], b[..., :, ia:ib]
         r = np.linalg.norm((a - b).ravel()) / max(np.linalg.norm(b.ravel()), 1e-300)
         worst = max(worst, r)
     ok = worst <= 1e-12 and np.allclose(dg, do, rtol=1e-11, atol=1e-18)
