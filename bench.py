@@ -35,6 +35,8 @@ KERNEL_WORDS = {
     "k_t_vert": lambda t: (8 if t[0] == "0" else 7, 3), "k_uv_vert": lambda t: (10 if t[0] == "0" else 9, 3),
     "k_set_huv1": (4, 3), "k_uv2_pass0": (3, 3), "k_uv2_pass1": (6, 3),
     "k_t_horiz": (5, 3), "k_set_depth": (3, 3), "k_step2d_zeta": (24, 2), "k_step2d_uv": (23, 2), "k_rd_bott_drag": (3, 2),
+    "k_visc3d": (7, 3),      # row f1: u,v(nstp),Hz read; u,v(3-nstp) read+written
+    "k_t3dmix": (4, 3),      # row f1: t(nrhs),Hz read; t(nnew) read+written
     "k_step2d": (34, 2),     # 9 state R + 3 W + 12 static R + 10 averages RW per 2-D point and substep
 }
 
@@ -59,6 +61,20 @@ def peaks():
     if os.path.exists(p):
         return json.load(open(p))["hbm_gbs"], "measured (MEASURED_PEAKS.json hbm_gbs)"
     return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+def ncu_traffic(kernel):
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel` from the committed `ncu --set full` capture of this
+    workload (profiles/r1_ncu_traffic_v2.json, made from gpurun_out/r1_full_v2_*_raw.csv); None if the kernel is not in it."""
+    p = os.path.join(ROOT, "profiles", "r1_ncu_traffic_v2.json")
+    if not os.path.exists(p):
+        return None
+    norm = lambda n: n.replace("(", "").replace(")", "").replace(" ", "").replace("true", "1").replace("false", "0")
+    want = norm(kernel)
+    for k, v in json.load(open(p)).items():
+        if norm(k) == want or norm(k).split("<")[0] == want:
+            return v["dram_bytes"]
+    return None
 
 
 class ClockSampler:
@@ -150,6 +166,7 @@ def main():
     ap.add_argument("--cpu-sample", type=int, nargs=3, default=[256, 256, 64])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--periodic", action="store_true", help="doubly periodic variant instead of the closed N/S walls of BASELINE configs[1]")
+    ap.add_argument("--mixing", action="store_true", help="also run visc3d / t3dmix (UV_VIS2, TS_DIF2; SURVEY.md 8(f) row f1) inside every step")
     ap.add_argument("--kernel-table", default=None, help="write the per-kernel timing table to this file")
     a = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -158,8 +175,11 @@ def main():
     Lm, Mm, N = a.size
     NT = a.nt
     case_kw = dict(NT=NT, ns_walls=not a.periodic, nonlin_eos=True)
+    if a.mixing:
+        case_kw.update(visc2=100.0, tnu2=50.0)
     workload = f"analytic baroclinic channel {Lm}x{Mm}x{N} per GPU, T+S" + (f"+{NT - 2} passive" if NT > 2 else "") + \
-               ", nonlinear split EOS, " + ("doubly periodic" if a.periodic else "E-W periodic, closed free-slip N/S walls") + ", ndtfast=60 (82 executed barotropic substeps per step)"
+               ", nonlinear split EOS, " + ("doubly periodic" if a.periodic else "E-W periodic, closed free-slip N/S walls") + ", ndtfast=60 (82 executed barotropic substeps per step)" + \
+               (", + harmonic lateral viscosity/diffusion (visc3d, t3dmix)" if a.mixing else "")
     config = {"workload": workload, "grid_per_gpu": [Lm, Mm, N], "tracers": NT, "l2_policy": "inputs (15 GB of resident state per GPU) larger than L2; no flush",
               "timing": "CUDA events on the library stream, barrier+sync both sides, max over ranks"}
 
@@ -286,9 +306,11 @@ def main():
         avg_ms = top[2] / top[1]
         if words:
             ach = words * 8.0 * npts / (avg_ms * 1e-3) / 1e9
-            roof = {"bound": "hbm", "kernel": top[0], "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak, "traffic": None,
+            roof = {"bound": "hbm", "kernel": top[0], "achieved": ach, "peak": peak, "unit": "GB/s", "frac": ach / peak,
+                    "traffic": ncu_traffic(top[0]) if (Lm, Mm, N) == (1024, 1024, 64) else None,
                     "peak_source": peak_src, "algorithmic_bytes_per_launch": words * 8.0 * npts, "avg_launch_ms": avg_ms,
-                    "launches_per_step": top[1] / a.steps, "share_of_step": top[2] / tot}
+                    "launches_per_step": top[1] / a.steps, "share_of_step": top[2] / tot,
+                    "traffic_source": "profiles/r1_ncu_traffic_v2.json (ncu --set full, dram read+write bytes per launch, this workload)"}
         if a.kernel_table:
             with open(a.kernel_table, "w") as f:
                 f.write(f"# per-kernel CUDA-event times, {a.steps} steps, {workload}\n# kernel launches total_ms avg_ms share algorithmic_GB/s\n")

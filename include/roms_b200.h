@@ -20,6 +20,7 @@ extern "C" {
 #endif
 
 typedef struct roms_ctx roms_ctx;   /* opaque per-GPU handle */
+#define ROMS_MAXNT 40                /* most tracers one context carries (bgc configurations: 34) */
 
 /* Run-time replacement for the reference's compile-time param.opt + *.in keywords
  * (param.opt:20-43, read_inp_mod.F:416-446). Sizes are those of THIS subdomain. */
@@ -37,6 +38,11 @@ typedef struct roms_cfg {
   double rdrg, rdrg2, Zob;    /* bottom_drag keyword                                          */
   double gamma2;              /* slipperiness                                                 */
   double theta_s, theta_b, hc;/* S-coord keyword                                              */
+  /* lateral mixing along S-surfaces; zero-initialised = switched off */
+  int uv_vis2;                /* cppdefs UV_VIS2: roms_step calls roms_visc3d after step3d_uv1 (main.F:448-450) */
+  int ts_dif2;                /* cppdefs TS_DIF2: roms_step calls roms_t3dmix after step3d_t (main.F:471-473)   */
+  double visc2;               /* lateral_visc keyword [m2/s] -> visc2_r, visc2_p (mixing.F:156-157)           */
+  double tnu2[ROMS_MAXNT];    /* tracer_diff2 keyword [m2/s] -> diff2(:,:,itrc)  (mixing.F:161-163)           */
 } roms_cfg;
 
 /* Field identifiers for roms_push / roms_pull.  `lvl` selects the time level (1-based, as in
@@ -67,6 +73,12 @@ enum roms_field {
   ROMS_AKT,                                      /* itrc 1..2 (iTandS), k=0:N */
   ROMS_RU, ROMS_RV,                              /* k=1:N; prsgrd -> pre_step3d/step3d_uv1 hand-off
                                                     (the reference's A3d(1,1:2), prsgrd.F:12) */
+  /* lateral mixing (row f1): psi-point metrics and mask computed by roms_setup_grid (setup_grid1.F:107-190);
+     coefficients filled from cfg.visc2 / cfg.tnu2 by roms_setup_grid (mixing.F:156-163) -- a host that adds a
+     sponge (set_nudgcof.F:88-110) pushes its own afterwards */
+  ROMS_PMASK, ROMS_DM_P, ROMS_DN_P, ROMS_PMON_U, ROMS_PNOM_V,
+  ROMS_VISC2_R, ROMS_VISC2_P,
+  ROMS_DIFF2,                                    /* itrc 1..NT */
   ROMS_NFIELDS
 };
 
@@ -105,6 +117,8 @@ int  roms_step3d_uv1(roms_ctx* h, int tile);  /* step3d_uv1.F:5    */
 int  roms_step2d(roms_ctx* h);                /* step2d_FB.F:3     */
 int  roms_step3d_uv2(roms_ctx* h, int tile);  /* step3d_uv2.F:6    */
 int  roms_step3d_t(roms_ctx* h, int tile);    /* step3d_t_ISO.F:20 */
+int  roms_visc3d(roms_ctx* h);                /* visc3d_S.F:4  (UV_VIS2: harmonic viscosity along S-surfaces)  */
+int  roms_t3dmix(roms_ctx* h);                /* t3dmix_S.F:4  (TS_DIF2: Laplacian tracer diffusion, all NT)   */
 int  roms_alfabeta(roms_ctx* h, double* alpha_host, double* beta_host); /* alfabeta.F:4 */
 int  roms_exchange(roms_ctx* h, int nfields, const int* fields, const int* lvls, const int* itrcs);
                                               /* mpi_exchanges.F:34-40 exchange_xxx */

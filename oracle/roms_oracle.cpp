@@ -40,6 +40,9 @@ struct Orc {
   vec rhoA, rhoS, rufrc, rvfrc, Zt_avg1, DU_avg1, DV_avg1, DU_avg2, DV_avg2, DU_avg_bak, DV_avg_bak, r_D;
   vec sustr, svstr, swflx;
   std::vector<vec> stflx;
+  // lateral mixing (visc3d_S.F, t3dmix_S.F): psi-point metrics/mask (grid.F:84-100), coefficients (mixing.F:14-19)
+  vec pmask, dm_p, dn_p, pmon_u, pnom_v, visc2_r, visc2_p;
+  std::vector<vec> diff2;
   // 3-D
   vec u[3], v[3];
   std::vector<vec> t[3];
@@ -197,8 +200,40 @@ void setup_grid(Orc& o) {
       A2(o.dn_v, i, j) = 2.0 / (A2(o.pn, i, j) + A2(o.pn, i, j - 1));
       A2(o.vmask, i, j) = A2(o.rmask, i, j) * A2(o.rmask, i, j - 1);
     }
-  vec* ex[] = {&o.dm_r, &o.dn_r, &o.dm_u, &o.dn_u, &o.dm_v, &o.dn_v, &o.rmask, &o.umask, &o.vmask};
+  // setup_grid1.F:107-127 pmon_u, pnom_v
+  for (int j = jstrR; j <= jendR; ++j)
+    for (int i = istr; i <= iendR; ++i)
+      A2(o.pmon_u, i, j) = (A2(o.pm, i, j) + A2(o.pm, i - 1, j)) / (A2(o.pn, i, j) + A2(o.pn, i - 1, j));
+  for (int j = jstr; j <= jendR; ++j)
+    for (int i = istrR; i <= iendR; ++i)
+      A2(o.pnom_v, i, j) = (A2(o.pn, i, j) + A2(o.pn, i, j - 1)) / (A2(o.pm, i, j) + A2(o.pm, i, j - 1));
+  // setup_grid1.F:139-191 psi points: metrics and the slipperiness mask (no-slip on land-mask boundaries: 1 land
+  // neighbour -> 1, 2 adjacent land neighbours -> 2, else 0)
+  for (int j = jstr; j <= jendR; ++j)
+    for (int i = istr; i <= iendR; ++i) {
+      A2(o.dm_p, i, j) = 4. / (A2(o.pm, i, j) + A2(o.pm, i, j - 1) + A2(o.pm, i - 1, j) + A2(o.pm, i - 1, j - 1));
+      A2(o.dn_p, i, j) = 4. / (A2(o.pn, i, j) + A2(o.pn, i, j - 1) + A2(o.pn, i - 1, j) + A2(o.pn, i - 1, j - 1));
+      const bool a = A2(o.rmask, i - 1, j) > 0.5, b = A2(o.rmask, i, j) > 0.5, c = A2(o.rmask, i - 1, j - 1) > 0.5, d = A2(o.rmask, i, j - 1) > 0.5;
+      const double cff1 = 1., cff2 = 2.;
+      double pmk;
+      if (a && b && c && d) pmk = 1.;
+      else if (!a && b && c && d) pmk = cff1;
+      else if (a && !b && c && d) pmk = cff1;
+      else if (a && b && !c && d) pmk = cff1;
+      else if (a && b && c && !d) pmk = cff1;
+      else if (a && !b && c && !d) pmk = cff2;
+      else if (!a && b && !c && d) pmk = cff2;
+      else if (a && b && !c && !d) pmk = cff2;
+      else if (!a && !b && c && d) pmk = cff2;
+      else pmk = 0.;
+      A2(o.pmask, i, j) = pmk;
+    }
+  vec* ex[] = {&o.dm_r, &o.dn_r, &o.dm_p, &o.dn_p, &o.dm_u, &o.dn_u, &o.dm_v, &o.dn_v, &o.pmon_u, &o.pnom_v, &o.rmask, &o.umask, &o.vmask, &o.pmask};
   for (vec* a : ex) ex2(o, *a);
+  // mixing.F:156-163: whole-array assignment of the background coefficients
+  std::fill(o.visc2_r.begin(), o.visc2_r.end(), o.c.visc2);
+  std::fill(o.visc2_p.begin(), o.visc2_p.end(), o.c.visc2);
+  for (int it = 0; it < o.NT; ++it) std::fill(o.diff2[it].begin(), o.diff2[it].end(), o.c.tnu2[it]);
   // setup_grid2.F: area, volume (plain sums here; only used to normalise diag output)
   double area = 0, vol = 0;
   for (int j = jstr; j <= jend; ++j)
@@ -1434,6 +1469,88 @@ void step3d_t(Orc& o) {
   for (int itrc = 0; itrc < NT; ++itrc) ex3(o, o.t[nnew - 1][itrc]);
 }
 
+// ---------------------------------------------------------------------------------------------
+// visc3d_S.F:18-134 visc3d_tile (UV_VIS2): harmonic viscosity along S-surfaces as the divergence of the
+// horizontal stress tensor; adds dt*cff to u,v(:,:,:,3-nstp) [= Hz*u] and the vertical integral to rufrc, rvfrc.
+void visc3d(Orc& o) {
+  GEOM
+  const int nstp = o.nstp, indx = 3 - nstp;
+  const double dt = o.c.dt;
+  const vec &u = o.u[nstp - 1], &v = o.v[nstp - 1], &pm = o.pm, &pn = o.pn;
+  vec &ui = o.u[indx - 1], &vi = o.v[indx - 1];
+  vec UFx(o.SXY), UFe(o.SXY), VFx(o.SXY), VFe(o.SXY);
+  for (int k = 1; k <= N; ++k) {        // k stays serial: rufrc, rvfrc accumulate level by level
+#pragma omp parallel for
+    for (int j = jstrV - 1; j <= jend; ++j)
+      for (int i = istrU - 1; i <= iend; ++i) {
+        const double cff = 0.5 * A3(o.Hz, i, j, k) * A2(o.visc2_r, i, j) *
+                           (A2(o.dn_r, i, j) * A2(pm, i, j) * ((A2(pn, i, j) + A2(pn, i + 1, j)) * A3(u, i + 1, j, k) - (A2(pn, i - 1, j) + A2(pn, i, j)) * A3(u, i, j, k)) -
+                            A2(o.dm_r, i, j) * A2(pn, i, j) * ((A2(pm, i, j) + A2(pm, i, j + 1)) * A3(v, i, j + 1, k) - (A2(pm, i, j - 1) + A2(pm, i, j)) * A3(v, i, j, k)));
+        A2(UFx, i, j) = cff * A2(o.dn_r, i, j) * A2(o.dn_r, i, j);
+        A2(VFe, i, j) = -cff * A2(o.dm_r, i, j) * A2(o.dm_r, i, j);
+      }
+#pragma omp parallel for
+    for (int j = jstr; j <= jend + 1; ++j)
+      for (int i = istr; i <= iend + 1; ++i) {
+        const double cff = 0.125 * (A3(o.Hz, i - 1, j, k) + A3(o.Hz, i, j, k) + A3(o.Hz, i - 1, j - 1, k) + A3(o.Hz, i, j - 1, k)) * A2(o.visc2_p, i, j) *
+                           (0.25 * (A2(pm, i - 1, j) + A2(pm, i, j) + A2(pm, i - 1, j - 1) + A2(pm, i, j - 1)) * A2(o.dn_p, i, j) *
+                                ((A2(pn, i, j - 1) + A2(pn, i, j)) * A3(v, i, j, k) - (A2(pn, i - 1, j - 1) + A2(pn, i - 1, j)) * A3(v, i - 1, j, k)) +
+                            0.25 * (A2(pn, i - 1, j) + A2(pn, i, j) + A2(pn, i - 1, j - 1) + A2(pn, i, j - 1)) * A2(o.dm_p, i, j) *
+                                ((A2(pm, i - 1, j) + A2(pm, i, j)) * A3(u, i, j, k) - (A2(pm, i - 1, j - 1) + A2(pm, i, j - 1)) * A3(u, i, j - 1, k))) *
+                           A2(o.pmask, i, j);
+        A2(UFe, i, j) = cff * A2(o.dm_p, i, j) * A2(o.dm_p, i, j);
+        A2(VFx, i, j) = cff * A2(o.dn_p, i, j) * A2(o.dn_p, i, j);
+      }
+#pragma omp parallel for
+    for (int j = jstr; j <= jend; ++j)
+      for (int i = istrU; i <= iend; ++i) {
+        const double cff = 0.125 * (A2(pm, i - 1, j) + A2(pm, i, j)) * (A2(pn, i - 1, j) + A2(pn, i, j)) *
+                           ((A2(pn, i - 1, j) + A2(pn, i, j)) * (A2(UFx, i, j) - A2(UFx, i - 1, j)) + (A2(pm, i - 1, j) + A2(pm, i, j)) * (A2(UFe, i, j + 1) - A2(UFe, i, j)));
+        A2(o.rufrc, i, j) = A2(o.rufrc, i, j) + cff;
+        A3(ui, i, j, k) = A3(ui, i, j, k) + dt * cff;
+      }
+#pragma omp parallel for
+    for (int j = jstrV; j <= jend; ++j)
+      for (int i = istr; i <= iend; ++i) {
+        const double cff = 0.125 * (A2(pm, i, j) + A2(pm, i, j - 1)) * (A2(pn, i, j) + A2(pn, i, j - 1)) *
+                           ((A2(pn, i, j - 1) + A2(pn, i, j)) * (A2(VFx, i + 1, j) - A2(VFx, i, j)) + (A2(pm, i, j - 1) + A2(pm, i, j)) * (A2(VFe, i, j) - A2(VFe, i, j - 1)));
+        A2(o.rvfrc, i, j) = A2(o.rvfrc, i, j) + cff;
+        A3(vi, i, j, k) = A3(vi, i, j, k) + dt * cff;
+      }
+  }
+}
+
+// t3dmix_S.F:17-258 t3dmix / t3dmix_tile, TS_DIF2 branch (:54-105; TS_DIF4 is #undef in every shipped cppdefs.opt):
+// Laplacian diffusion of every tracer along S-surfaces added to t(nnew), then the exchange (:254-256).
+void t3dmix(Orc& o) {
+  GEOM
+  const int nrhs = o.nrhs, nnew = o.nnew;
+  const double dt = o.c.dt;
+  for (int itrc = 0; itrc < o.NT; ++itrc) {
+    const vec &tr = o.t[nrhs - 1][itrc], &d2 = o.diff2[itrc];
+    vec& tn = o.t[nnew - 1][itrc];
+#pragma omp parallel
+    {
+      vec FX(o.SXY), FE(o.SXY);
+#pragma omp for
+      for (int k = 1; k <= N; ++k) {
+        for (int j = jstr; j <= jend; ++j)
+          for (int i = istr; i <= iend + 1; ++i)
+            A2(FX, i, j) = 0.25 * (A2(d2, i, j) + A2(d2, i - 1, j)) * A2(o.pmon_u, i, j) * (A3(o.Hz, i, j, k) + A3(o.Hz, i - 1, j, k)) *
+                           (A3(tr, i, j, k) - A3(tr, i - 1, j, k)) * A2(o.umask, i, j);
+        for (int j = jstr; j <= jend + 1; ++j)
+          for (int i = istr; i <= iend; ++i)
+            A2(FE, i, j) = 0.25 * (A2(d2, i, j) + A2(d2, i, j - 1)) * A2(o.pnom_v, i, j) * (A3(o.Hz, i, j, k) + A3(o.Hz, i, j - 1, k)) *
+                           (A3(tr, i, j, k) - A3(tr, i, j - 1, k)) * A2(o.vmask, i, j);
+        for (int j = jstr; j <= jend; ++j)
+          for (int i = istr; i <= iend; ++i)
+            A3(tn, i, j, k) = A3(tn, i, j, k) + dt * A2(o.pm, i, j) * A2(o.pn, i, j) * (A2(FX, i + 1, j) - A2(FX, i, j) + A2(FE, i, j + 1) - A2(FE, i, j)) / A3(o.Hz, i, j, k);
+      }
+    }
+    ex3(o, tn);
+  }
+}
+
 // diag.F:50-658 diag_tile: KE, barotropic KE, max advective Courant number and its vertical part.
 // Sums use the reference's split-direction pairwise reduction (diag.F:256-325).
 void pairwise(const Orc& o, vec& a) {
@@ -1654,6 +1771,7 @@ void step(Orc& o) {
   rho_eos(o, o.nrhs);
   prsgrd(o);
   step3d_uv1(o);
+  if (o.c.uv_vis2) visc3d(o);          // main.F:448-450
   for (o.iif = 1; o.iif <= o.nfast; ++o.iif) {
     o.kstp = o.knew;
     o.knew = o.kstp + 1;
@@ -1664,6 +1782,7 @@ void step(Orc& o) {
   step3d_uv2(o);
   omega(o);
   step3d_t(o);
+  if (o.c.ts_dif2) t3dmix(o);          // main.F:471-473
   rho_eos(o, o.nnew);
 }
 
@@ -1691,6 +1810,9 @@ vec* field_ptr(Orc& o, int field, int lvl, int itrc, long* count) {
     case ROMS_RHO1: p = &o.rho1; n = n3; break; case ROMS_QP1: p = &o.qp1; n = n3; break;
     case ROMS_AKV: p = &o.Akv; n = nw; break; case ROMS_AKT: p = &o.Akt[itrc - 1]; n = nw; break;
     case ROMS_RU: p = &o.ru; n = n3; break; case ROMS_RV: p = &o.rv; n = n3; break;
+    case ROMS_PMASK: p = &o.pmask; break; case ROMS_DM_P: p = &o.dm_p; break; case ROMS_DN_P: p = &o.dn_p; break;
+    case ROMS_PMON_U: p = &o.pmon_u; break; case ROMS_PNOM_V: p = &o.pnom_v; break;
+    case ROMS_VISC2_R: p = &o.visc2_r; break; case ROMS_VISC2_P: p = &o.visc2_p; break; case ROMS_DIFF2: p = &o.diff2[itrc - 1]; break;
     default: break;
   }
   if (count) *count = n;
@@ -1710,10 +1832,12 @@ int orc_create(const roms_cfg* cfg, void** out) {
   const size_t n2 = o->SXY, n3 = n2 * o->N, nw = n2 * (o->N + 1);
   for (vec* a : {&o->h, &o->pm, &o->pn, &o->f, &o->rmask, &o->umask, &o->vmask, &o->dm_u, &o->dn_u, &o->dm_v, &o->dn_v, &o->dm_r, &o->dn_r, &o->fomn,
                  &o->hinv, &o->rhoA, &o->rhoS, &o->rufrc, &o->rvfrc, &o->Zt_avg1, &o->DU_avg1, &o->DV_avg1, &o->DU_avg2, &o->DV_avg2, &o->DU_avg_bak,
-                 &o->DV_avg_bak, &o->r_D, &o->sustr, &o->svstr, &o->swflx})
+                 &o->DV_avg_bak, &o->r_D, &o->sustr, &o->svstr, &o->swflx, &o->pmask, &o->dm_p, &o->dn_p, &o->pmon_u, &o->pnom_v, &o->visc2_r,
+                 &o->visc2_p})
     a->assign(n2, 0.0);
   for (int l = 0; l < 4; ++l) { o->zeta[l].assign(n2, 0.0); o->ubar[l].assign(n2, 0.0); o->vbar[l].assign(n2, 0.0); }
   o->stflx.assign(o->NT, vec(n2, 0.0));
+  o->diff2.assign(o->NT, vec(n2, 0.0));
   for (int l = 0; l < 3; ++l) {
     o->u[l].assign(n3, 0.0); o->v[l].assign(n3, 0.0);
     o->t[l].assign(o->NT, vec(n3, 0.0));
@@ -1775,6 +1899,8 @@ int orc_step3d_uv1(void* h, int) { step3d_uv1(*(Orc*)h); return 0; }
 int orc_step2d(void* h) { step2d(*(Orc*)h); return 0; }
 int orc_step3d_uv2(void* h, int) { step3d_uv2(*(Orc*)h); return 0; }
 int orc_step3d_t(void* h, int) { step3d_t(*(Orc*)h); return 0; }
+int orc_visc3d(void* h) { visc3d(*(Orc*)h); return 0; }
+int orc_t3dmix(void* h) { t3dmix(*(Orc*)h); return 0; }
 int orc_alfabeta(void* h, double* a, double* b) { alfabeta(*(Orc*)h, a, b); return 0; }
 int orc_diag(void* h, double out[4]) { diag(*(Orc*)h, out); return 0; }
 int orc_init_filament(void* h) { init_filament(*(Orc*)h); return 0; }

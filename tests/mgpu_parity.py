@@ -16,21 +16,22 @@ from romsb200 import Roms  # noqa: E402
 def main():
     nsteps = int(sys.argv[1]) if len(sys.argv) > 1 else 3
     mode = sys.argv[2] if len(sys.argv) > 2 else "periodic"
-    walls = mode in ("walls", "seamount", "closed")
-    topo = mode in ("seamount", "closed")                        # + bottom topography and a land mask
-    ew = mode == "closed"                                        # closed basin: walls on all four sides
+    walls = mode in ("walls", "seamount", "closed", "closedmix")
+    topo = mode in ("seamount", "closed", "closedmix")           # + bottom topography and a land mask
+    ew = mode in ("closed", "closedmix")                         # closed basin: walls on all four sides
+    mix = dict(visc2=100.0, tnu2=50.0, sponge=True) if mode == "closedmix" else {}   # + visc3d / t3dmix
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
     npx, npe = cases.rank_grid(world)
     LG, MG, N = 24 * npx, 20 * npe, 10
-    cfg, st = cases.channel(LG, MG, N, ns_walls=walls, ew_walls=ew, seamount=topo, island=topo, sub=(rank % npx, rank // npx, npx, npe))
+    cfg, st = cases.channel(LG, MG, N, ns_walls=walls, ew_walls=ew, seamount=topo, island=topo, sub=(rank % npx, rank // npx, npx, npe), **mix)
     g = Roms(cfg, local)
     g.attach_torch_comm(dist)
     cases.initialize(g, st)
     g.call("run", nsteps)
     dg = g.diag()
-    cfgG, stG = cases.channel(LG, MG, N, ns_walls=walls, ew_walls=ew, seamount=topo, island=topo)
+    cfgG, stG = cases.channel(LG, MG, N, ns_walls=walls, ew_walls=ew, seamount=topo, island=topo, **mix)
     o = Oracle(cfgG)
     cases.initialize(o, stG)
     o.call("run", nsteps)

@@ -21,6 +21,8 @@ CHECK = {
     "set_depth": ["HZ", "Z_R", "Z_W"],
     "step3d_uv2": ["Unew", "Vnew", "FLXU", "FLXV", "UBARk", "VBARk"],
     "step3d_t": ["Tnew"],
+    "visc3d": ["Unew", "Vnew", "RUFRC", "RVFRC"],
+    "t3dmix": ["Tnew"],
 }
 
 
@@ -83,7 +85,8 @@ def walk(cfg, st, nsteps=1, verbose=False, device=0):
             m.set_idx(i["iic"], i["iif"], i["nstp"], i["nrhs"], i["nnew"], i["kstp"], i["knew"])
 
     # init_step0 outputs
-    for f in ["HZ", "Z_R", "Z_W", "FLXU", "FLXV", "WE", "WI", "RHO1", "RHOA", "RHOS", "DU_AVG1", "DV_AVG1", "HINV"]:
+    for f in ["HZ", "Z_R", "Z_W", "FLXU", "FLXV", "WE", "WI", "RHO1", "RHOA", "RHOS", "DU_AVG1", "DV_AVG1", "HINV", "PMASK", "DM_P", "DN_P", "PMON_U", "PNOM_V",
+              "VISC2_R", "VISC2_P"]:
         a, b = view(g.pull(f), cfg), view(o.pull(f), cfg)
         worst[("init_step0", f)] = rel(a, b)
         if verbose:
@@ -105,6 +108,8 @@ def walk(cfg, st, nsteps=1, verbose=False, device=0):
         both("rho_eos", 3)
         both("prsgrd")
         both("step3d_uv1", 0)
+        if cfg.uv_vis2:
+            both("visc3d")
         for iif in range(1, nfast + 1):
             kstp = knew
             knew = kstp + 1 if kstp < 4 else 1
@@ -118,6 +123,8 @@ def walk(cfg, st, nsteps=1, verbose=False, device=0):
         both("step3d_uv2", 0)
         both("omega")
         both("step3d_t", 0)
+        if cfg.ts_dif2:
+            both("t3dmix")
         both("rho_eos", 3 - nstp)
     o.close()
     g.close()

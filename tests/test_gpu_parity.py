@@ -58,7 +58,7 @@ def test_constants_match_oracle():
 
 @pytest.mark.parametrize("case", ["channel", "filament", "channel_linear_odd", "channel_walls", "channel_walls_linear_odd",
                                   "seamount_island_walls", "seamount_island_periodic", "closed_basin", "closed_basin_seamount_odd",
-                                  "ew_walls_ns_periodic"])
+                                  "ew_walls_ns_periodic", "channel_mixing", "closed_basin_seamount_mixing", "filament_mixing_switches"])
 def test_routine_by_routine(case):
     if case == "channel":
         cfg, st = cases.channel(48, 40, 12)
@@ -76,6 +76,13 @@ def test_routine_by_routine(case):
         cfg, st = cases.channel(40, 36, 10, ew_walls=True)
     elif case == "channel_walls_linear_odd":
         cfg, st = cases.channel(37, 29, 9, NT=3, nonlin_eos=False, ns_walls=True)
+    elif case == "channel_mixing":                                      # UV_VIS2 + TS_DIF2, spatially varying coefficients, 3 tracers
+        cfg, st = cases.channel(45, 38, 11, NT=3, visc2=80.0, tnu2=40.0, sponge=True)
+    elif case == "closed_basin_seamount_mixing":                        # + walls on all sides, land mask (pmask = 0/1/2)
+        cfg, st = cases.channel(37, 29, 9, ns_walls=True, ew_walls=True, seamount=True, island=True, visc2=120.0, tnu2=60.0, sponge=True)
+    elif case == "filament_mixing_switches":                            # tests/Filament/cppdefs.opt:34-35 with visc2 = tnu2 = 0
+        cfg, st = cases.filament(64, 64, 32)
+        cfg.uv_vis2, cfg.ts_dif2 = 1, 1
     elif case == "filament":
         cfg, st = cases.filament(64, 64, 32)
     else:
@@ -85,9 +92,10 @@ def test_routine_by_routine(case):
     assert not bad, bad
 
 
-@pytest.mark.parametrize("walls,topo,ew", [(False, False, False), (True, False, False), (True, True, False), (True, True, True)])
-def test_one_step_and_100_steps_channel(walls, topo, ew):
-    cfg, st = cases.channel(64, 48, 16, ns_walls=walls, seamount=topo, island=topo, ew_walls=ew)
+@pytest.mark.parametrize("walls,topo,ew,mix", [(False, False, False, False), (True, False, False, False), (True, True, False, False),
+                                               (True, True, True, False), (True, True, True, True)])
+def test_one_step_and_100_steps_channel(walls, topo, ew, mix):
+    cfg, st = cases.channel(64, 48, 16, ns_walls=walls, seamount=topo, island=topo, ew_walls=ew, **(dict(visc2=100.0, tnu2=50.0, sponge=True) if mix else {}))
     g, o = Roms(cfg), Oracle(cfg)
     cases.initialize(g, st); cases.initialize(o, st)
     g.call("step"); o.call("step")
@@ -103,6 +111,7 @@ def test_one_step_and_100_steps_channel(walls, topo, ew):
 def test_filament_golden_on_gpu():
     """The CUDA path itself against the reference's golden log (tests/Filament/benchmark.result_github_gnu:146-167)."""
     cfg, _ = cases.filament()
+    cfg.uv_vis2, cfg.ts_dif2 = 1, 1     # tests/Filament/cppdefs.opt:34-35 (UV_VIS2, TS_DIF2 compiled in; visc2 = tnu2 = 0 in benchmark.in)
     o = Oracle(cfg)
     o.call("init_filament")            # exact restatement of ana_grid.h / ana_init.h
     g = Roms(cfg)
@@ -155,4 +164,7 @@ def test_two_gpu_halo_exchange_parity():
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
                         "--master-port", "29734", script, "3", "closed"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
+                        "--master-port", "29735", script, "3", "closedmix"], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]

@@ -31,8 +31,17 @@ def test_scoord_table():
     o.close()
 
 
-def test_filament_golden_20_steps():
-    o = Oracle(filament_cfg())
+import pytest
+
+
+@pytest.mark.parametrize("mixing", [False, True])
+def test_filament_golden_20_steps(mixing):
+    """mixing=True: UV_VIS2 and TS_DIF2 switched on with visc2 = tnu2 = 0, exactly as tests/Filament/cppdefs.opt:34-35 and
+    benchmark.in compile and run them -- visc3d / t3dmix are then part of the pinned call sequence."""
+    cfg = filament_cfg()
+    if mixing:
+        cfg.uv_vis2, cfg.ts_dif2 = 1, 1
+    o = Oracle(cfg)
     o.call("init_filament")
     o.call("init_step0")
     gold = np.array([[float(x) for x in r] for r in GOLD["github_gnu"]])
@@ -50,3 +59,47 @@ def test_filament_golden_20_steps():
         assert (np.abs(d[:3] - ifx[s, :3]) / np.abs(ifx[s, :3])).max() < 1e-11
     print("worst relative deviation from golden:", worst)
     o.close()
+
+
+def test_lateral_mixing_properties():
+    """visc3d_S.F / t3dmix_S.F restatement: (1) Laplacian diffusion conserves the volume integral of every tracer on a
+    periodic domain (flux form) and damps its variance; (2) visc3d adds the same vertical integral to rufrc that it adds
+    (times dt) to Hz*u; (3) zero coefficients change nothing."""
+    from orclib import cases
+    cfg, st = cases.channel(24, 20, 6, NT=3, nonlin_eos=False, visc2=80.0, tnu2=40.0, sponge=True)
+    o = Oracle(cfg)
+    cases.initialize(o, st)
+    o.set_idx(1, 1, 1, 3, 2, 1, 1)                   # nstp=1, nrhs=3, nnew=2 as at the call site main.F:471-473
+    rng = np.random.default_rng(20260101)
+    Hz = o.pull("HZ")
+    dA = 1.0 / (o.pull("PM") * o.pull("PN"))
+    inner = (slice(None), slice(2, -2), slice(2, -2))
+    for it in range(1, 4):
+        a = rng.standard_normal(o.shape("T"))
+        o.push("T", a, 3, it); o.exchange("T", 3, it)
+        o.push("T", o.pull("T", 3, it), 2, it)
+    before = [o.pull("T", 2, it) for it in range(1, 4)]
+    o.call("t3dmix")
+    for it in range(1, 4):
+        b, a = before[it - 1], o.pull("T", 2, it)
+        tot = lambda x: (x * Hz * dA[None])[inner].sum()
+        assert abs(tot(a) - tot(b)) <= 1e-12 * np.abs(b * Hz * dA[None])[inner].sum()
+        assert (a[inner] ** 2).sum() < (b[inner] ** 2).sum()
+    # visc3d: rufrc increment == sum_k of the increment of u(indx)/dt
+    for f in ("U", "V"):
+        a = 0.1 * rng.standard_normal(o.shape(f))
+        o.push(f, a, 1); o.exchange(f, 1, 1)
+    u0, v0, r0 = o.pull("U", 2), o.pull("V", 2), o.pull("RUFRC")
+    o.call("visc3d")
+    du = (o.pull("U", 2) - u0).sum(0) / cfg.dt
+    dr = o.pull("RUFRC") - r0
+    assert np.abs(dr).max() > 0 and np.abs(du - dr)[2:-2, 2:-2].max() <= 1e-9 * np.abs(dr).max()
+    o.close()
+    cfg0, st0 = cases.channel(24, 20, 6, NT=2, visc2=0.0, tnu2=0.0)
+    cfgn, _ = cases.channel(24, 20, 6, NT=2)
+    a, b = Oracle(cfg0), Oracle(cfgn)
+    cases.initialize(a, st0); cases.initialize(b, st0)
+    a.call("run", 2); b.call("run", 2)
+    for f, l in (("U", 1), ("T", 1), ("ZETA", a.get_idx()[6])):
+        assert np.array_equal(a.pull(f, l), b.pull(f, l))
+    a.close(); b.close()

@@ -1487,3 +1487,105 @@ __global__ void k_alfabeta(const __grid_constant__ KP p, const double* __restric
     beta[c] = p.salinity ? fabs(p.Scoef) : 0.0;
   }
 }
+
+// ------------------------------------------------------------------------------------------------
+// Lateral mixing along S-surfaces.
+//
+// visc3d_S.F:18-134 visc3d_tile.  The reference sweeps four 2-D scratch planes (UFx,VFe at rho points, UFe,VFx at psi
+// points) per level; here a thread owns the (i,j) column of u- and v-points, keeps every level-independent metric
+// product of its three rho-point and three psi-point stresses in registers and walks k, so that rufrc/rvfrc receive
+// the levels in the reference's order (k=1..N, one rounding per level) without atomics.
+struct VisR { double A1, pnE, pnW, B1, pmN, pmS, nu, dn, dm; };      // rho point: (dn_r*pm), pn(i)+pn(i+1), pn(i-1)+pn(i), (dm_r*pn), ...
+struct VisP { double C1, pnA, pnB, C2, pmA, pmB, nu, msk, dn, dm; }; // psi point
+__device__ __forceinline__ VisR visr_load(const KP& p, ix_t c) {
+  const ix_t SX = p.SX;
+  VisR r;
+  const double pm = p.pm[c], pn = p.pn[c];
+  r.dn = p.dn_r[c]; r.dm = p.dm_r[c];
+  r.A1 = r.dn * pm; r.pnE = pn + p.pn[c + 1]; r.pnW = p.pn[c - 1] + pn;
+  r.B1 = r.dm * pn; r.pmN = pm + p.pm[c + SX]; r.pmS = p.pm[c - SX] + pm;
+  r.nu = p.visc2_r[c];
+  return r;
+}
+__device__ __forceinline__ VisP visp_load(const KP& p, ix_t c) {
+  const ix_t SX = p.SX;
+  VisP q;
+  const double pm00 = p.pm[c], pmw = p.pm[c - 1], pms = p.pm[c - SX], pmsw = p.pm[c - 1 - SX];
+  const double pn00 = p.pn[c], pnw = p.pn[c - 1], pns = p.pn[c - SX], pnsw = p.pn[c - 1 - SX];
+  q.dn = p.dn_p[c]; q.dm = p.dm_p[c];
+  q.C1 = 0.25 * (pmw + pm00 + pmsw + pms) * q.dn; q.pnA = pns + pn00; q.pnB = pnsw + pnw;
+  q.C2 = 0.25 * (pnw + pn00 + pnsw + pns) * q.dm; q.pmA = pmw + pm00; q.pmB = pmsw + pms;
+  q.nu = p.visc2_p[c]; q.msk = p.pmask[c];
+  return q;
+}
+// cff of visc3d_S.F:64-74 at rho point c, level k (UFx = cff*dn*dn, VFe = -cff*dm*dm)
+__device__ __forceinline__ double visr_cff(const KP& p, const double* __restrict__ u, const double* __restrict__ v, ix_t c, int k, const VisR& r) {
+  return 0.5 * R3(p.Hz, c, k) * r.nu * (r.A1 * (r.pnE * R3(u, c + 1, k) - r.pnW * R3(u, c, k)) - r.B1 * (r.pmN * R3(v, c + p.SX, k) - r.pmS * R3(v, c, k)));
+}
+// cff of visc3d_S.F:80-97 at psi point c (UFe = cff*dm_p*dm_p, VFx = cff*dn_p*dn_p)
+__device__ __forceinline__ double visp_cff(const KP& p, const double* __restrict__ u, const double* __restrict__ v, ix_t c, int k, const VisP& q) {
+  const ix_t SX = p.SX;
+  return 0.125 * (R3(p.Hz, c - 1, k) + R3(p.Hz, c, k) + R3(p.Hz, c - 1 - SX, k) + R3(p.Hz, c - SX, k)) * q.nu *
+         (q.C1 * (q.pnA * R3(v, c, k) - q.pnB * R3(v, c - 1, k)) + q.C2 * (q.pmA * R3(u, c, k) - q.pmB * R3(u, c - SX, k))) * q.msk;
+}
+__global__ void __launch_bounds__(256, 2) k_visc3d(const __grid_constant__ KP p, const double* __restrict__ u, const double* __restrict__ v,
+                                                    double* __restrict__ ui, double* __restrict__ vi) {
+  THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
+  const int N = p.N;
+  const bool dou = i >= p.istrU, dov = j >= p.jstrV;
+  const VisR r0 = visr_load(p, c), rw = visr_load(p, c - 1), rs = visr_load(p, c - SX);
+  const VisP q0 = visp_load(p, c), qn = visp_load(p, c + SX), qe = visp_load(p, c + 1);
+  const double pm0 = p.pm[c], pn0 = p.pn[c];
+  const double pmu = p.pm[c - 1] + pm0, pnu = p.pn[c - 1] + pn0;        // u point (i,j)
+  const double pmv = pm0 + p.pm[c - SX], pnv = pn0 + p.pn[c - SX];      // v point (i,j)
+  const double cu = 0.125 * pmu * pnu, cv = 0.125 * pmv * pnv;
+  const double dt = p.dt;
+  double ruf = p.rufrc[c], rvf = p.rvfrc[c];
+#pragma unroll 2
+  for (int k = 1; k <= N; ++k) {
+    const double s0 = visr_cff(p, u, v, c, k, r0), sw = visr_cff(p, u, v, c - 1, k, rw), ss = visr_cff(p, u, v, c - SX, k, rs);
+    const double t0 = visp_cff(p, u, v, c, k, q0), tn = visp_cff(p, u, v, c + SX, k, qn), te = visp_cff(p, u, v, c + 1, k, qe);
+    if (dou) {
+      const double UFx_c = s0 * r0.dn * r0.dn, UFx_w = sw * rw.dn * rw.dn;
+      const double UFe_n = tn * qn.dm * qn.dm, UFe_c = t0 * q0.dm * q0.dm;
+      const double cff = cu * (pnu * (UFx_c - UFx_w) + pmu * (UFe_n - UFe_c));
+      ruf = ruf + cff;
+      R3(ui, c, k) = R3(ui, c, k) + dt * cff;
+    }
+    if (dov) {
+      const double VFx_e = te * qe.dn * qe.dn, VFx_c = t0 * q0.dn * q0.dn;
+      const double VFe_c = -s0 * r0.dm * r0.dm, VFe_s = -ss * rs.dm * rs.dm;
+      const double cff = cv * (pnv * (VFx_e - VFx_c) + pmv * (VFe_c - VFe_s));
+      rvf = rvf + cff;
+      R3(vi, c, k) = R3(vi, c, k) + dt * cff;
+    }
+  }
+  if (dou) p.rufrc[c] = ruf;
+  if (dov) p.rvfrc[c] = rvf;
+}
+
+// t3dmix_S.F:54-105 (TS_DIF2): t(nnew) += dt*pm*pn*(FX(i+1)-FX(i)+FE(j+1)-FE(j))/Hz with the Laplacian fluxes recomputed in
+// registers at the four faces of the point; KB levels per thread share the level-independent face coefficients and masks.
+template <int KB>
+__global__ void __launch_bounds__(256, 4) k_t3dmix(const __grid_constant__ KP p, const double* __restrict__ t_rhs, double* __restrict__ t_new,
+                                                    const double* __restrict__ d2) {
+  THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
+  const int k0 = blockIdx.z * KB + 1;
+  const double dc = d2[c];
+  const double xw = 0.25 * (dc + d2[c - 1]) * p.pmon_u[c], xe = 0.25 * (d2[c + 1] + dc) * p.pmon_u[c + 1];
+  const double ys = 0.25 * (dc + d2[c - SX]) * p.pnom_v[c], yn = 0.25 * (d2[c + SX] + dc) * p.pnom_v[c + SX];
+  const double mw = p.umask[c], me = p.umask[c + 1], ms = p.vmask[c], mn = p.vmask[c + SX];
+  const double cdt = p.dt * p.pm[c] * p.pn[c];
+#pragma unroll
+  for (int q = 0; q < KB; ++q) {
+    const int k = k0 + q;
+    if (k <= p.N) {
+      const double H0 = R3(p.Hz, c, k), t0 = R3(t_rhs, c, k);
+      const double FXw = xw * (H0 + R3(p.Hz, c - 1, k)) * (t0 - R3(t_rhs, c - 1, k)) * mw;
+      const double FXe = xe * (R3(p.Hz, c + 1, k) + H0) * (R3(t_rhs, c + 1, k) - t0) * me;
+      const double FEs = ys * (H0 + R3(p.Hz, c - SX, k)) * (t0 - R3(t_rhs, c - SX, k)) * ms;
+      const double FEn = yn * (R3(p.Hz, c + SX, k) + H0) * (R3(t_rhs, c + SX, k) - t0) * mn;
+      R3(t_new, c, k) = R3(t_new, c, k) + cdt * (FXe - FXw + FEn - FEs) / H0;
+    }
+  }
+}

@@ -30,6 +30,7 @@ struct KP {
   double dt, dtfast, g, rho0, Tcoef, T0, Scoef, S0, rdrg, rdrg2, Zob, gamma2, hc;
   // static 2-D
   double *h, *pm, *pn, *f, *rmask, *umask, *vmask, *dm_u, *dn_u, *dm_v, *dn_v, *dm_r, *dn_r, *fomn, *hinv;
+  double *pmask, *dm_p, *dn_p, *pmon_u, *pnom_v, *visc2_r, *visc2_p;   // lateral mixing (visc3d_S.F, t3dmix_S.F)
   // 2-D state
   double *rhoA, *rhoS, *rufrc, *rvfrc, *Zt_avg1, *DU_avg1, *DV_avg1, *DU_avg2, *DV_avg2, *DU_avg_bak, *DV_avg_bak, *r_D;
   double *sustr, *svstr, *swflx;

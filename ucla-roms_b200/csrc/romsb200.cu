@@ -243,6 +243,7 @@ int roms_create(const roms_cfg* cfg, int device, roms_ctx** out) {
   for (int id = 0; id < ROMS_NFIELDS; ++id) slot(h, id, 1, 1, 1);
   slot(h, ROMS_ZETA, 4, 1, 1); slot(h, ROMS_UBAR, 4, 1, 1); slot(h, ROMS_VBAR, 4, 1, 1);
   slot(h, ROMS_STFLX, 1, NT, 1);
+  slot(h, ROMS_DIFF2, 1, NT, 1);
   slot(h, ROMS_U, 3, 1, N); slot(h, ROMS_V, 3, 1, N); slot(h, ROMS_T, 3, NT, N);
   for (int id : {ROMS_HZ, ROMS_Z_R, ROMS_FLXU, ROMS_FLXV, ROMS_RHO1, ROMS_QP1, ROMS_RU, ROMS_RV}) slot(h, id, 1, 1, N);
   for (int id : {ROMS_Z_W, ROMS_WE, ROMS_WI, ROMS_AKV}) slot(h, id, 1, 1, N + 1);
@@ -276,6 +277,8 @@ int roms_create(const roms_cfg* cfg, int device, roms_ctx** out) {
   P1(DU_avg_bak, ROMS_DU_AVG_BAK); P1(DV_avg_bak, ROMS_DV_AVG_BAK); P1(r_D, ROMS_R_D); P1(sustr, ROMS_SUSTR); P1(svstr, ROMS_SVSTR);
   P1(swflx, ROMS_SWFLX); P1(Hz, ROMS_HZ); P1(z_r, ROMS_Z_R); P1(z_w, ROMS_Z_W); P1(FlxU, ROMS_FLXU); P1(FlxV, ROMS_FLXV); P1(We, ROMS_WE);
   P1(Wi, ROMS_WI); P1(rho1, ROMS_RHO1); P1(qp1, ROMS_QP1); P1(Akv, ROMS_AKV); P1(ru, ROMS_RU); P1(rv, ROMS_RV);
+  P1(pmask, ROMS_PMASK); P1(dm_p, ROMS_DM_P); P1(dn_p, ROMS_DN_P); P1(pmon_u, ROMS_PMON_U); P1(pnom_v, ROMS_PNOM_V);
+  P1(visc2_r, ROMS_VISC2_R); P1(visc2_p, ROMS_VISC2_P);
 #undef P1
   p.Akt[0] = h->f[ROMS_AKT].ptr[0]; p.Akt[1] = h->f[ROMS_AKT].ptr[1];
   host_scoord(h);
@@ -470,14 +473,42 @@ int roms_setup_grid(roms_ctx* h) {
         dm_v[q] = 2.0 / (pm[q] + pm[s]); dn_v[q] = 2.0 / (pn[q] + pn[s]); vm[q] = rm[q] * rm[s];
       }
     }
+  // psi-point metrics and slipperiness mask, pm/pn ratios at u and v points (setup_grid1.F:107-191)
+  std::vector<double> pmon_u(n2, 0.0), pnom_v(n2, 0.0), dm_p(n2, 0.0), dn_p(n2, 0.0), pmk(n2, 0.0);
+  for (int j = pp.jstrR; j <= pp.jendR; ++j)
+    for (int i = pp.istrR; i <= pp.iendR; ++i) {
+      const size_t q = at(i, j);
+      if (i >= 1) pmon_u[q] = (pm[q] + pm[at(i - 1, j)]) / (pn[q] + pn[at(i - 1, j)]);
+      if (j >= 1) pnom_v[q] = (pn[q] + pn[at(i, j - 1)]) / (pm[q] + pm[at(i, j - 1)]);
+      if (i >= 1 && j >= 1) {
+        const size_t w = at(i - 1, j), s = at(i, j - 1), sw = at(i - 1, j - 1);
+        dm_p[q] = 4. / (pm[q] + pm[s] + pm[w] + pm[sw]);
+        dn_p[q] = 4. / (pn[q] + pn[s] + pn[w] + pn[sw]);
+        const int land = (rm[w] < 0.5) + (rm[q] < 0.5) + (rm[sw] < 0.5) + (rm[s] < 0.5);
+        // no-slip on land-mask boundaries: one land corner -> 1, two ADJACENT land corners -> 2, otherwise (diagonal pair, 3, 4) -> 0
+        const bool diagonal = (rm[w] < 0.5 && rm[s] < 0.5 && !(rm[q] < 0.5) && !(rm[sw] < 0.5)) || (rm[q] < 0.5 && rm[sw] < 0.5 && !(rm[w] < 0.5) && !(rm[s] < 0.5));
+        pmk[q] = land == 0 ? 1. : land == 1 ? 1. : (land == 2 && !diagonal) ? 2. : 0.;
+      }
+    }
+  const size_t ncoef = n2;
+  std::vector<double> coef(ncoef);
   struct { int id; std::vector<double>* a; } outv[] = {{ROMS_FOMN, &fomn}, {ROMS_DM_R, &dm_r}, {ROMS_DN_R, &dn_r}, {ROMS_DM_U, &dm_u}, {ROMS_DN_U, &dn_u},
-                                                       {ROMS_DM_V, &dm_v}, {ROMS_DN_V, &dn_v}, {ROMS_UMASK, &um}, {ROMS_VMASK, &vm}};
+                                                       {ROMS_DM_V, &dm_v}, {ROMS_DN_V, &dn_v}, {ROMS_UMASK, &um}, {ROMS_VMASK, &vm},
+                                                       {ROMS_PMON_U, &pmon_u}, {ROMS_PNOM_V, &pnom_v}, {ROMS_DM_P, &dm_p}, {ROMS_DN_P, &dn_p}, {ROMS_PMASK, &pmk}};
   for (auto& o : outv)
     if (roms_push(h, o.id, 1, 1, o.a->data())) return -1;
+  // background mixing coefficients: whole-array assignment (mixing.F:156-163)
+  std::fill(coef.begin(), coef.end(), h->c.visc2);
+  if (roms_push(h, ROMS_VISC2_R, 1, 1, coef.data()) || roms_push(h, ROMS_VISC2_P, 1, 1, coef.data())) return -1;
+  for (int it = 1; it <= h->c.NT; ++it) {
+    std::fill(coef.begin(), coef.end(), h->c.tnu2[it - 1]);
+    if (roms_push(h, ROMS_DIFF2, 1, it, coef.data())) return -1;
+  }
   const KP& p = h->kp;
   int rc = exchange(h, {{p.dm_r, 1}, {p.dn_r, 1}, {p.dm_u, 1}, {p.dn_u, 1}});
   if (!rc) rc = exchange(h, {{p.dm_v, 1}, {p.dn_v, 1}, {p.rmask, 1}, {p.umask, 1}});
-  if (!rc) rc = exchange(h, {{p.vmask, 1}});
+  if (!rc) rc = exchange(h, {{p.vmask, 1}, {p.pmask, 1}, {p.dm_p, 1}, {p.dn_p, 1}});
+  if (!rc) rc = exchange(h, {{p.pmon_u, 1}, {p.pnom_v, 1}});
   return rc;
 }
 
@@ -667,6 +698,26 @@ int roms_step3d_t(roms_ctx* h, int tile) {
   if (NT % 2 == 1) return exchange(h, {{h->t(nnew, NT), p.N}});
   return 0;
 }
+// visc3d_S.F:4-134 (UV_VIS2).  Called between step3d_uv1 and the barotropic loop (main.F:448-450): u,v(3-nstp) hold Hz*u.
+int roms_visc3d(roms_ctx* h) {
+  CK(cudaSetDevice(h->device));
+  const KP& p = h->kp;
+  const int nstp = h->nstp, indx = 3 - nstp;
+  PLANE(k_visc3d, p.iend, p.jstr, p.jend, 1, p, h->u(nstp), h->v(nstp), h->u(indx), h->v(indx));
+  return 0;
+}
+// t3dmix_S.F:4-258 (TS_DIF2 branch), every tracer, each followed by its exchange (:254-256)
+int roms_t3dmix(roms_ctx* h) {
+  CK(cudaSetDevice(h->device));
+  const KP& p = h->kp;
+  const int nrhs = h->nrhs, nnew = h->nnew;
+  for (int it = 1; it <= h->c.NT; ++it) {
+    PLANE((k_t3dmix<KB_T>), p.iend, p.jstr, p.jend, (p.N + KB_T - 1) / KB_T, p, h->t(nrhs, it), h->t(nnew, it), h->f[ROMS_DIFF2].ptr[it - 1]);
+    int rc = exchange(h, {{h->t(nnew, it), p.N}});
+    if (rc) return rc;
+  }
+  return 0;
+}
 int roms_alfabeta(roms_ctx* h, double* alpha_host, double* beta_host) {
   CK(cudaSetDevice(h->device));
   const KP& p = h->kp;
@@ -763,6 +814,7 @@ int roms_step(roms_ctx* h) {
   RUN(roms_rho_eos(h, h->nrhs));
   RUN(roms_prsgrd(h));
   RUN(roms_step3d_uv1(h, 0));
+  if (h->c.uv_vis2) RUN(roms_visc3d(h));
   for (h->iif = 1; h->iif <= h->nfast; ++h->iif) {
     h->kstp = h->knew;
     h->knew = h->kstp + 1;
@@ -772,6 +824,7 @@ int roms_step(roms_ctx* h) {
   RUN(roms_step3d_uv2(h, 0));
   RUN(roms_omega(h));
   RUN(roms_step3d_t(h, 0));
+  if (h->c.ts_dif2) RUN(roms_t3dmix(h));
   RUN(roms_rho_eos(h, h->nnew));
 #undef RUN
   return 0;

@@ -14,7 +14,8 @@ class RomsCfg(C.Structure):
                 ("dt", C.c_double), ("rho0", C.c_double), ("g", C.c_double),
                 ("Tcoef", C.c_double), ("T0", C.c_double), ("Scoef", C.c_double), ("S0", C.c_double),
                 ("rdrg", C.c_double), ("rdrg2", C.c_double), ("Zob", C.c_double), ("gamma2", C.c_double),
-                ("theta_s", C.c_double), ("theta_b", C.c_double), ("hc", C.c_double)]
+                ("theta_s", C.c_double), ("theta_b", C.c_double), ("hc", C.c_double),
+                ("uv_vis2", C.c_int), ("ts_dif2", C.c_int), ("visc2", C.c_double), ("tnu2", C.c_double * 40)]
 
 
 # enum roms_field, in the order of include/roms_b200.h
@@ -22,7 +23,7 @@ FIELDS = ["H", "PM", "PN", "F", "RMASK", "UMASK", "VMASK", "DM_U", "DN_U", "DM_V
           "FOMN", "HINV", "ZETA", "UBAR", "VBAR", "RHOA", "RHOS", "RUFRC", "RVFRC", "ZT_AVG1", "DU_AVG1",
           "DV_AVG1", "DU_AVG2", "DV_AVG2", "DU_AVG_BAK", "DV_AVG_BAK", "R_D", "SUSTR", "SVSTR", "SWFLX",
           "STFLX", "U", "V", "T", "HZ", "Z_R", "Z_W", "FLXU", "FLXV", "WE", "WI", "RHO1", "QP1", "AKV", "AKT",
-          "RU", "RV"]
+          "RU", "RV", "PMASK", "DM_P", "DN_P", "PMON_U", "PNOM_V", "VISC2_R", "VISC2_P", "DIFF2"]
 FID = {n: i for i, n in enumerate(FIELDS)}
 
 

@@ -62,13 +62,17 @@ def _noise(ig, jg, k, salt):
 
 
 def channel(Lm=64, Mm=64, N=16, NT=2, ns_walls=False, nonlin_eos=True, dt=120.0, ndtfast=60, dx=1.0e3, dy=1.0e3,
-            depth=4000.0, seed=20260101, perturb=1e-6, amp=None, sub=(0, 0, 1, 1), seamount=False, island=False, ew_walls=False):
+            depth=4000.0, seed=20260101, perturb=1e-6, amp=None, sub=(0, 0, 1, 1), seamount=False, island=False, ew_walls=False,
+            visc2=None, tnu2=None, sponge=False):
     """Lm, Mm are the GLOBAL interior sizes; sub=(inode, jnode, np_xi, np_eta) selects this rank's block
     (mpi_setup.F:61-70; sizes must divide evenly).  Returns the cfg and state of that block.
     seamount: Gaussian seamount h = depth*(1 - 0.5*exp(-r^2/(L/5)^2)) (SURVEY.md 8(d) input (3), form of
     NHMG/tests/mg_setup_tests.f90:150); island: a circular land mask (rmask=0) north-east of it, so that the
     rmask/umask/vmask factors of every routine are exercised.  ew_walls: closed western/eastern walls as well (with
-    ns_walls: a fully closed basin, BASELINE configs[2] geometry)."""
+    ns_walls: a fully closed basin, BASELINE configs[2] geometry).
+    visc2 / tnu2 [m2/s]: switch on UV_VIS2 / TS_DIF2 lateral mixing (visc3d_S.F, t3dmix_S.F) with these background
+    coefficients; sponge: add a smooth spatially varying part to visc2_r, visc2_p, diff2 (what set_nudgcof.F:88-110 does
+    near open boundaries) so that the coefficient averaging of the flux formulas is exercised."""
     inode, jnode, np_xi, np_eta = sub
     LmG, MmG = Lm, Mm
     assert LmG % np_xi == 0 and MmG % np_eta == 0
@@ -78,6 +82,12 @@ def channel(Lm=64, Mm=64, N=16, NT=2, ns_walls=False, nonlin_eos=True, dt=120.0,
                   nonlin_eos=1 if nonlin_eos else 0, salinity=1, ndtfast=ndtfast, np_xi=np_xi, np_eta=np_eta, inode=inode, jnode=jnode,
                   dt=dt, rho0=1027.0, g=9.81, Tcoef=0.2, T0=10.0, Scoef=0.8, S0=35.0,
                   rdrg=3.0e-4, rdrg2=0.0, Zob=0.0, gamma2=1.0, theta_s=6.0, theta_b=2.0, hc=25.0)
+    if visc2 is not None:
+        cfg.uv_vis2, cfg.visc2 = 1, visc2
+    if tnu2 is not None:
+        cfg.ts_dif2 = 1
+        for it in range(NT):
+            cfg.tnu2[it] = tnu2 * (1.0 + 0.25 * it)
     # work on a 3-cell halo so that u/v-point averages exist on the whole 2-cell halo, trim at the end
     sy, sx = Mm + 6, Lm + 6
     ig = (np.arange(-2, Lm + 4) + i0)[None, :] + np.zeros((sy, 1), dtype=np.int64)
@@ -146,6 +156,14 @@ def channel(Lm=64, Mm=64, N=16, NT=2, ns_walls=False, nonlin_eos=True, dt=120.0,
     akv = np.full((N + 1, Mm + 4, Lm + 4), 1.0e-4)
     st["AKV"] = akv
     st["AKT"] = {(1, 1): akv, (1, 2): akv}
+    if sponge:
+        wr = 0.5 + 0.5 * np.cos(2 * np.pi * x / Lx) * np.sin(2 * np.pi * y / Ly)          # at rho points, 3-cell halo
+        wp = np.zeros_like(wr)
+        wp[1:, 1:] = 0.25 * (wr[1:, 1:] + wr[1:, :-1] + wr[:-1, 1:] + wr[:-1, :-1])      # psi points (set_nudgcof.F:97-98)
+        if visc2 is not None:
+            st["VISC2_R"] = t2(visc2 * (1.0 + wr)); st["VISC2_P"] = t2(visc2 * (1.0 + wp))
+        if tnu2 is not None:
+            st["DIFF2"] = {(1, it + 1): t2(cfg.tnu2[it] * (1.0 + wr)) for it in range(NT)}
     return cfg, st
 
 
