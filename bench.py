@@ -317,7 +317,7 @@ def main():
                 for name, cnt, tms in table:
                     w, dm = kernel_words(name) or (0, 3)
                     gbs = w * 8.0 * Lm * Mm * (N if dm == 3 else 1) / (tms / cnt * 1e-3) / 1e9 if w else 0.0
-                    f.write(f"{name} {cnt} {tms:.3f} {tms / cnt:.4f} {tms / tot:.4f} {gbs:.1f}\n")
+                    f.write(f"{name.replace(' ', '')} {cnt} {tms:.3f} {tms / cnt:.4f} {tms / tot:.4f} {gbs:.1f}\n")
     B = step_bytes_per_update(NT, nfast, N)
     step_roof = {"bytes_per_update": B, "achieved": value * B / 1e9 / world, "peak": peak, "unit": "GB/s per GPU", "frac": value * B / 1e9 / world / peak}
 

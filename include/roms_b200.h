@@ -140,6 +140,10 @@ int  roms_decomp_box(int Lm, int Mm, int d, int send, const int walls[4], int ou
                                                /* i0,j0,ni,nj of the message to/from direction d; walls = {S,N,W,E} closed physical
                                                   edges of this subdomain (NULL: none): messages along a wall carry the boundary row/column */
 int  roms_decomp_opposite(int d);
+int  roms_decomp_extent(int LL, int np, int node, int* L, int* corn);
+                                               /* mpi_setup.F:117-160: interior points L of block `node` of `np` along a direction of
+                                                  LL global points (surplus trimmed from the first/last block) and its global offset
+                                                  (iSW_corn / jSW_corn); non-zero if the block is narrower than the halo */
 
 /* ---- measurement hooks (the reference's timers.F:35-131 analogue; device-side CUDA events) - */
 int  roms_timer_start(roms_ctx* h);           /* event on the library's stream                  */

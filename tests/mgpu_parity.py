@@ -16,15 +16,17 @@ from romsb200 import Roms  # noqa: E402
 def main():
     nsteps = int(sys.argv[1]) if len(sys.argv) > 1 else 3
     mode = sys.argv[2] if len(sys.argv) > 2 else "periodic"
-    walls = mode in ("walls", "seamount", "closed", "closedmix")
-    topo = mode in ("seamount", "closed", "closedmix")           # + bottom topography and a land mask
-    ew = mode in ("closed", "closedmix")                         # closed basin: walls on all four sides
+    walls = mode in ("walls", "seamount", "closed", "closedmix", "unevenclosed")
+    topo = mode in ("seamount", "closed", "closedmix", "unevenclosed")           # + bottom topography and a land mask
+    ew = mode in ("closed", "closedmix", "unevenclosed")                         # closed basin: walls on all four sides
     mix = dict(visc2=100.0, tnu2=50.0, sponge=True) if mode == "closedmix" else {}   # + visc3d / t3dmix
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))
     npx, npe = cases.rank_grid(world)
     LG, MG, N = 24 * npx, 20 * npe, 10
+    if mode.startswith("uneven"):       # blocks of unequal size (mpi_setup.F:117-160): 3 points short in xi, 1 in eta
+        LG, MG = LG - (3 if npx > 1 else 0), MG - (1 if npe > 1 else 0)
     cfg, st = cases.channel(LG, MG, N, ns_walls=walls, ew_walls=ew, seamount=topo, island=topo, sub=(rank % npx, rank // npx, npx, npe), **mix)
     g = Roms(cfg, local)
     g.attach_torch_comm(dist)
@@ -38,7 +40,7 @@ def main():
     do = o.diag()
     iic, iif, nstp, nrhs, nnew, kstp, knew = g.get_idx()
     Lm, Mm = cfg.Lm, cfg.Mm
-    i0, j0 = (rank % npx) * Lm, (rank // npx) * Mm
+    i0, j0 = cases.block_extent(LG, npx, rank % npx)[1], cases.block_extent(MG, npe, rank // npx)[1]
     worst = 0.0
     for f, l, it in [("ZETA", knew, 1), ("UBAR", knew, 1), ("VBAR", knew, 1), ("U", nnew, 1), ("V", nnew, 1), ("T", nnew, 1), ("T", nnew, 2),
                      ("RHO1", 1, 1), ("HZ", 1, 1), ("WE", 1, 1), ("FLXU", 1, 1)]:

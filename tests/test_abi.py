@@ -69,3 +69,25 @@ def test_decomp_geometry():
         b = (C.c_int * 4)(); lib.roms_decomp_box(Lm, Mm, d, 0, None, b)
         cover[b[1] + 1:b[1] + 1 + b[3], b[0] + 1:b[0] + 1 + b[2]] += 1
     assert (cover[2:-2, 2:-2] == 0).all() and cover.sum() == cover.size - Lm * Mm and cover.max() == 1
+
+
+def test_uneven_block_extents():
+    """mpi_setup.F:117-160: blocks of ceil(LL/np) points, surplus trimmed from the first and last block; the C export and the
+    Python mirror used by the analytic cases agree, blocks tile the global range without gaps."""
+    import ctypes as C
+    from romsb200 import load_library, cases
+    lib = load_library()
+    for LL in (7, 45, 64, 100, 1023, 4096):
+        for np_ in (1, 2, 3, 4, 8):
+            nxt = 0
+            for node in range(np_):
+                L, c = C.c_int(), C.c_int()
+                rc = lib.roms_decomp_extent(LL, np_, node, C.byref(L), C.byref(c))
+                assert (L.value, c.value) == cases.block_extent(LL, np_, node)
+                assert rc == (0 if L.value >= 2 else 1)
+                assert c.value == nxt
+                nxt += L.value
+            assert nxt == LL
+    # the reference's example geometry: LLm=45 on 2 ranks -> Lm=23 per block, off=1: first keeps 23, last gets 22
+    assert cases.block_extent(45, 2, 0) == (23, 0) and cases.block_extent(45, 2, 1) == (22, 23)
+    assert lib.roms_decomp_extent(45, 2, 2, None, None) != 0

@@ -10,19 +10,23 @@ import torch.distributed as dist
 import torch.multiprocessing as mp
 
 
-def _worker(rank, world, port, npx, npe):
+def _worker(rank, world, port, npx, npe, uneven=False):
     import ctypes as C
-    from romsb200 import load_library
+    from romsb200 import load_library, cases
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
     lib = load_library()
-    Lm, Mm = 12, 10
-    LG, MG = Lm * npx, Mm * npe
+    LG, MG = 12 * npx - (3 if uneven else 0), 10 * npe - (1 if uneven else 0)
     i_n, jn = rank % npx, rank // npx
+    # mpi_setup.F:117-160: with `uneven` the first/last block of a direction is narrower than the others
+    Lc, ic, Mc, jc = C.c_int(), C.c_int(), C.c_int(), C.c_int()
+    assert lib.roms_decomp_extent(LG, npx, i_n, C.byref(Lc), C.byref(ic)) == 0 and lib.roms_decomp_extent(MG, npe, jn, C.byref(Mc), C.byref(jc)) == 0
+    Lm, Mm, i0, j0 = Lc.value, Mc.value, ic.value, jc.value
+    assert (Lm, i0) == cases.block_extent(LG, npx, i_n) and (Mm, j0) == cases.block_extent(MG, npe, jn)
     glob = np.arange((MG) * (LG), dtype=np.float64).reshape(MG, LG) + 0.5       # interior only, (j,i)
     loc = np.full((Mm + 4, Lm + 4), np.nan)
-    loc[2:-2, 2:-2] = glob[jn * Mm:(jn + 1) * Mm, i_n * Lm:(i_n + 1) * Lm]
+    loc[2:-2, 2:-2] = glob[j0:j0 + Mm, i0:i0 + Lm]
     reqs, recvs = [], []
     for d in range(8):
         o = lib.roms_decomp_opposite(d)
@@ -42,8 +46,8 @@ def _worker(rank, world, port, npx, npe):
         r.wait()
     for rb, buf in recvs:
         loc[rb[1] + 1:rb[1] + 1 + rb[3], rb[0] + 1:rb[0] + 1 + rb[2]] = buf.numpy()
-    jj = (np.arange(-2, Mm + 2) + jn * Mm) % MG
-    ii = (np.arange(-2, Lm + 2) + i_n * Lm) % LG
+    jj = (np.arange(-2, Mm + 2) + j0) % MG
+    ii = (np.arange(-2, Lm + 2) + i0) % LG
     ref = glob[np.ix_(jj, ii)]
     assert np.array_equal(loc, ref), rank
     dist.destroy_process_group()
@@ -115,6 +119,10 @@ def test_halo_messages_world2_gloo():
 
 def test_halo_messages_world4_gloo():
     mp.spawn(_worker, args=(4, _free_port(), 2, 2), nprocs=4, join=True)
+
+
+def test_halo_messages_uneven_blocks_world4_gloo():
+    mp.spawn(_worker, args=(4, _free_port(), 2, 2, True), nprocs=4, join=True)
 
 
 def test_halo_messages_closed_basin_world4_gloo():

@@ -210,4 +210,9 @@ int roms_decomp_box(int Lm, int Mm, int d, int send, const int walls[4], int out
   return 0;
 }
 int roms_decomp_opposite(int d) { return decomp_opposite(d); }
+int roms_decomp_extent(int LL, int np, int node, int* L, int* corn) {
+  if (LL < 1 || np < 1 || node < 0 || node >= np || !L || !corn) return 1;
+  decomp_extent(LL, np, node, L, corn);
+  return *L >= 2 ? 0 : 1;   // a block narrower than the halo cannot be exchanged
+}
 }

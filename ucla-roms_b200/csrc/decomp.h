@@ -35,6 +35,17 @@ static inline int decomp_neighbor(int np_xi, int np_eta, int inode, int jnode, i
   }
   return jn * np_xi + in;
 }
+// Block extent along one direction (mpi_setup.F:117-160): every block gets L0 = ceil(LL/np) interior points, the
+// surplus off = np*L0 - LL is trimmed from the two physical-edge blocks (off/2 from the first, (off+1)/2 from the
+// last); corn = global index offset of the block (iSW_corn / jSW_corn: local i=1 is global corn+1).
+static inline void decomp_extent(int LL, int np, int node, int* L, int* corn) {
+  const int L0 = (LL + np - 1) / np, off = np * L0 - LL;
+  int l = L0;
+  if (node == 0) l -= off / 2;
+  if (node == np - 1) l -= (off + 1) / 2;
+  *L = l;
+  *corn = node == 0 ? 0 : node * L0 - off / 2;
+}
 // interior cells this subdomain SENDS to its neighbour in direction d
 // swall/nwall: this subdomain touches a closed southern/northern physical edge; E-W messages then also carry
 // the boundary rows j=0 / j=Mm+1 (mpi_exchanges.F:538-543: "if (jnode==0) jl0=0", "if (jnode==NP_ETA-1) jl1=nyl+1");

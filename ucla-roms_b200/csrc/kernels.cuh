@@ -1111,8 +1111,12 @@ __device__ __forceinline__ double s2d_pgf(const KP& p, double cff, double dn, ix
 // thread finishes its own point: zeta(knew), the fast-time averages, rubar/rvbar, ubar/vbar(knew).  The thread next
 // to a closed wall also owns the wall point beside it (zetabc / u2dbc / v2dbc, step2d_FB.F:449-529), and on a single
 // subdomain the results are stored to their periodic images as well, so no exchange launch follows.
+#ifndef S2_TX
 #define S2_TX 32
+#endif
+#ifndef S2_TY
 #define S2_TY 8
+#endif
 __device__ __forceinline__ double s2d_zn_at(const KP& p, const S2D& s, ix2_t c, int j) {
   if (p.swall && j < p.jstr) return s2d_zeta_new(p, s, c + p.SX) * p.rmask[c];
   if (p.nwall && j > p.jend) return s2d_zeta_new(p, s, c - p.SX) * p.rmask[c];
@@ -1425,6 +1429,105 @@ __global__ void k_uv2_pass1(const __grid_constant__ KP p, double* __restrict__ u
     R3(Flx, c, k) = R3(Flx, c, k) - DCk * CF0;
   }
 }
+
+// ------------------------------------------------------------------------------------------------
+// k_uv2_pass1 with the column parked in SHARED memory between its three sweeps (one warp-row per block, [k][lane]) and
+// the operands of each sweep fetched one register chunk ahead of the arithmetic: every 3-D operand crosses HBM once
+// (6 words per point instead of ~10.7: Hz and u are not re-read twice, Flx is not written twice), 1.0 -> 0.78 ms on
+// B200.  The sums have short dependency chains, so the 6 resident warps per SM (shared memory holds 2(N+1) doubles per
+// column) are enough here -- unlike the spline/Thomas column kernels, where the same design is 20-80 % SLOWER than the
+// global scratch slab (profiles/r1_scratch_policy.txt, third experiment).  Arithmetic is expression-for-expression
+// that of k_uv2_pass1.
+#ifndef CP_K
+#define CP_K 16
+#endif
+#define COLSM_PROLOGUE                                                                   \
+  const int nth = blockDim.x * blockDim.y;                                               \
+  double* __restrict__ sA = smem + threadIdx.y * blockDim.x + threadIdx.x;               \
+  double* __restrict__ sB = sA + (p.N + 1) * nth;
+#define SA(k) sA[(k)*nth]
+#define SB(k) sB[(k)*nth]
+// summing sweep: A(k) = DC(k) = Hz_u*dn, B(k) = u(k); returns sum DC, sum DC*u
+template <int DIR>
+__device__ __forceinline__ void colsm_sum_sweep(const KP& p, ixc_t c, ixc_t d, double dn, const double* __restrict__ u, double* __restrict__ sA,
+                                                double* __restrict__ sB, int nth, double& DC0, double& FC0) {
+  const int N = p.N;
+  const double* __restrict__ gHz = p.Hz;
+  double na[CP_K], nb[CP_K], nu[CP_K];
+#pragma unroll
+  for (int q = 0; q < CP_K; ++q)
+    if (N - q >= 1) { na[q] = R3(gHz, c, N - q); nb[q] = R3(gHz, c - d, N - q); nu[q] = R3(u, c, N - q); }
+  for (int k0 = N; k0 >= 1; k0 -= CP_K) {
+    double ha[CP_K], hb[CP_K], uu[CP_K];
+#pragma unroll
+    for (int q = 0; q < CP_K; ++q) { ha[q] = na[q]; hb[q] = nb[q]; uu[q] = nu[q]; }
+    const int kn = k0 - CP_K;
+#pragma unroll
+    for (int q = 0; q < CP_K; ++q)
+      if (kn - q >= 1) { na[q] = R3(gHz, c, kn - q); nb[q] = R3(gHz, c - d, kn - q); nu[q] = R3(u, c, kn - q); }
+#pragma unroll
+    for (int q = 0; q < CP_K; ++q) {
+      const int k = k0 - q;
+      if (k >= 1) {
+        const double DCk = 0.5 * (ha[q] + hb[q]) * dn;
+        if (k == N) { DC0 = DCk; FC0 = DCk * uu[q]; }
+        else { DC0 = DC0 + DCk; FC0 = FC0 + DCk * uu[q]; }
+        SA(k) = DCk;
+        SB(k) = uu[q];
+      }
+    }
+  }
+}
+template <int DIR>
+__global__ void __launch_bounds__(64, 3) k_uv2_pass1_sm(const __grid_constant__ KP p, double* __restrict__ u, const double* __restrict__ u_stp, double* __restrict__ bar) {
+  extern __shared__ double smem[];
+  THREAD_IJT(ixc_t, (DIR == 0 ? p.istr : p.istrR), p.iendR, (DIR == 0 ? p.jstrR : p.jstr), p.jendR)
+  COLSM_PROLOGUE
+  const ixc_t d = DIR == 0 ? 1 : SX;
+  const int N = p.N;
+  const double dn = DIR == 0 ? p.dn_u[c] : p.dm_v[c];
+  const double msk = DIR == 0 ? p.umask[c] : p.vmask[c];
+  const double Davg1 = DIR == 0 ? p.DU_avg1[c] : p.DV_avg1[c];
+  const double Davg2 = DIR == 0 ? p.DU_avg2[c] : p.DV_avg2[c];
+  double* __restrict__ Flx = DIR == 0 ? p.FlxU : p.FlxV;
+  double DC0 = 0.0, FC0 = 0.0;
+  colsm_sum_sweep<DIR>(p, c, d, dn, u, sA, sB, nth, DC0, FC0);
+  DC0 = 1.0 / DC0;
+  bar[c] = DC0 * Davg1;
+  FC0 = DC0 * (FC0 - Davg1);
+  double CF0 = 0.0;
+  {
+    double nf[CP_K], ns[CP_K];
+#pragma unroll
+    for (int q = 0; q < CP_K; ++q)
+      if (N - q >= 1) { nf[q] = R3(Flx, c, N - q); ns[q] = R3(u_stp, c, N - q); }
+    for (int k0 = N; k0 >= 1; k0 -= CP_K) {
+      double fl[CP_K], us[CP_K];
+#pragma unroll
+      for (int q = 0; q < CP_K; ++q) { fl[q] = nf[q]; us[q] = ns[q]; }
+      const int kn = k0 - CP_K;
+#pragma unroll
+      for (int q = 0; q < CP_K; ++q)
+        if (kn - q >= 1) { nf[q] = R3(Flx, c, kn - q); ns[q] = R3(u_stp, c, kn - q); }
+#pragma unroll
+      for (int q = 0; q < CP_K; ++q) {
+        const int k = k0 - q;
+        if (k >= 1) {
+          const double DCk = SA(k);
+          const double un = (SB(k) - FC0) * msk;
+          R3(u, c, k) = un;
+          const double CFk = 0.28 * fl[q] + 0.36 * DCk * (us[q] + un);
+          SB(k) = CFk;      // parked; corrected in the next loop
+          CF0 = CF0 + CFk;
+        }
+      }
+    }
+  }
+  CF0 = DC0 * (CF0 - Davg2);
+  for (int k = 1; k <= N; ++k) R3(Flx, c, k) = SB(k) - SA(k) * CF0;
+}
+#undef SA
+#undef SB
 
 // ------------------------------------------------------------------------------------------------
 // diag.F:50-658: per-column kinetic energy, barotropic KE, free-surface volume and max advective

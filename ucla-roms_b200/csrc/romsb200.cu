@@ -54,6 +54,7 @@ struct roms_ctx {
   std::vector<KTimer> ktimers;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   int col_bx = 32, col_by = 2, pl_bx = 32, pl_by = 8;   // plane tiles 32x8: fewest halo-row re-reads through L2 (profiles/r1_tuning_log.txt)
+  int uv2_sm = 1;     // k_uv2_pass1 with the column parked in shared memory (1.0 -> 0.78 ms on B200); off when the column is too tall
   int use_smem = 0;   // measured on B200 (profiles/r1_scratch_policy.txt): occupancy beats shared-memory scratch
   Comm comm;
   double* u(int l) { return f[ROMS_U].ptr[l - 1]; }
@@ -96,6 +97,19 @@ static size_t col_smem(const roms_ctx* h, int narr) {
     dim3 b_(h->col_bx, h->col_by, 1);                                                         \
     size_t sm_ = col_smem(h, narr);                                                           \
     if (sm_ > 48 * 1024) CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_)); \
+    if (h->ktiming) kt_begin(h, #kern);                                                       \
+    kern<<<grid_plane(h, i1, j0, j1, 1, b_), b_, sm_, h->st>>>(__VA_ARGS__);                  \
+    if (h->ktiming) kt_end(h);                                                                \
+    h->launches++;                                                                            \
+  } while (0)
+
+// column kernel that parks its column in shared memory: one warp-row per block, two arrays [k][lane]
+#define COLUMN_SM(kern, i1, j0, j1, ...)                                                      \
+  do {                                                                                        \
+    dim3 b_(32, 1, 1);                                                                        \
+    size_t sm_ = (size_t)2 * (h->c.N + 1) * 32 * sizeof(double);                              \
+    static size_t attr_ = 0;                                                                  \
+    if (attr_ != sm_) { CK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_)); attr_ = sm_; } \
     if (h->ktiming) kt_begin(h, #kern);                                                       \
     kern<<<grid_plane(h, i1, j0, j1, 1, b_), b_, sm_, h->st>>>(__VA_ARGS__);                  \
     if (h->ktiming) kt_end(h);                                                                \
@@ -235,6 +249,8 @@ int roms_create(const roms_cfg* cfg, int device, roms_ctx** out) {
   p.wrap_x = (single && cfg->ew_periodic) ? 1 : 0;
   p.wrap_y = (single && cfg->ns_periodic) ? 1 : 0;
   if (const char* e = getenv("ROMS_COL_SMEM")) h->use_smem = atoi(e);
+  if (const char* e = getenv("ROMS_UV2_SM")) h->uv2_sm = atoi(e);
+  if ((size_t)2 * (N + 1) * 32 * sizeof(double) > 64 * 1024) h->uv2_sm = 0;   // fewer than 3 warps per SM would fit: global re-read version
   if ((size_t)2 * (N + 1) * h->col_bx * h->col_by * sizeof(double) > 200 * 1024) { h->col_by = 1; }
   if ((size_t)2 * (N + 1) * h->col_bx * h->col_by * sizeof(double) > 200 * 1024) h->use_smem = 0;
   p.use_smem = h->use_smem;
@@ -673,8 +689,13 @@ int roms_step3d_uv2(roms_ctx* h, int tile) {
   COLUMN(k_uv2_pass0<1>, 0, p.iend, p.jstrV, p.jend, p, h->v(nnew));
   bc3d(h, h->u(nnew), p.N, BC_U);     // u3dbc_tile / v3dbc_tile (step3d_uv2.F:471-472)
   bc3d(h, h->v(nnew), p.N, BC_V);
-  COLUMN(k_uv2_pass1<0>, 0, p.iendR, p.jstrR, p.jendR, p, h->u(nnew), h->u(nstp), h->ubar(knew));
-  COLUMN(k_uv2_pass1<1>, 0, p.iendR, p.jstr, p.jendR, p, h->v(nnew), h->v(nstp), h->vbar(knew));
+  if (h->uv2_sm) {
+    COLUMN_SM(k_uv2_pass1_sm<0>, p.iendR, p.jstrR, p.jendR, p, h->u(nnew), h->u(nstp), h->ubar(knew));
+    COLUMN_SM(k_uv2_pass1_sm<1>, p.iendR, p.jstr, p.jendR, p, h->v(nnew), h->v(nstp), h->vbar(knew));
+  } else {
+    COLUMN(k_uv2_pass1<0>, 0, p.iendR, p.jstrR, p.jendR, p, h->u(nnew), h->u(nstp), h->ubar(knew));
+    COLUMN(k_uv2_pass1<1>, 0, p.iendR, p.jstr, p.jendR, p, h->v(nnew), h->v(nstp), h->vbar(knew));
+  }
   int rc = exchange(h, {{p.FlxU, p.N}, {h->u(nnew), p.N}, {h->ubar(knew), 1}});
   if (rc) return rc;
   return exchange(h, {{p.FlxV, p.N}, {h->v(nnew), p.N}, {h->vbar(knew), 1}});

@@ -50,6 +50,15 @@ def rank_grid(world):
     return {1: (1, 1), 2: (2, 1), 4: (2, 2), 8: (4, 2)}.get(world, (world, 1))
 
 
+def block_extent(LL, np_, node):
+    """mpi_setup.F:117-160 (mirror of roms_decomp_extent): interior points of block `node` of `np_` along a direction of LL global
+    points and its global offset.  Blocks get ceil(LL/np_) points; the surplus is trimmed from the first and the last block."""
+    L0 = (LL + np_ - 1) // np_
+    off = np_ * L0 - LL
+    L = L0 - (off // 2 if node == 0 else 0) - ((off + 1) // 2 if node == np_ - 1 else 0)
+    return L, (0 if node == 0 else node * L0 - off // 2)
+
+
 def _noise(ig, jg, k, salt):
     """deterministic pseudo-random field in [-1,1) as a function of GLOBAL indices (so that every rank of a
     decomposed run generates exactly the values a single-domain run has)"""
@@ -65,7 +74,7 @@ def channel(Lm=64, Mm=64, N=16, NT=2, ns_walls=False, nonlin_eos=True, dt=120.0,
             depth=4000.0, seed=20260101, perturb=1e-6, amp=None, sub=(0, 0, 1, 1), seamount=False, island=False, ew_walls=False,
             visc2=None, tnu2=None, sponge=False):
     """Lm, Mm are the GLOBAL interior sizes; sub=(inode, jnode, np_xi, np_eta) selects this rank's block
-    (mpi_setup.F:61-70; sizes must divide evenly).  Returns the cfg and state of that block.
+    (mpi_setup.F:61-70; uneven splits as mpi_setup.F:117-160, see block_extent).  Returns the cfg and state of that block.
     seamount: Gaussian seamount h = depth*(1 - 0.5*exp(-r^2/(L/5)^2)) (SURVEY.md 8(d) input (3), form of
     NHMG/tests/mg_setup_tests.f90:150); island: a circular land mask (rmask=0) north-east of it, so that the
     rmask/umask/vmask factors of every routine are exercised.  ew_walls: closed western/eastern walls as well (with
@@ -75,9 +84,7 @@ def channel(Lm=64, Mm=64, N=16, NT=2, ns_walls=False, nonlin_eos=True, dt=120.0,
     near open boundaries) so that the coefficient averaging of the flux formulas is exercised."""
     inode, jnode, np_xi, np_eta = sub
     LmG, MmG = Lm, Mm
-    assert LmG % np_xi == 0 and MmG % np_eta == 0
-    Lm, Mm = LmG // np_xi, MmG // np_eta
-    i0, j0 = inode * Lm, jnode * Mm
+    (Lm, i0), (Mm, j0) = block_extent(LmG, np_xi, inode), block_extent(MmG, np_eta, jnode)
     cfg = RomsCfg(Lm=Lm, Mm=Mm, N=N, NT=NT, ew_periodic=0 if ew_walls else 1, ns_periodic=0 if ns_walls else 1,
                   nonlin_eos=1 if nonlin_eos else 0, salinity=1, ndtfast=ndtfast, np_xi=np_xi, np_eta=np_eta, inode=inode, jnode=jnode,
                   dt=dt, rho0=1027.0, g=9.81, Tcoef=0.2, T0=10.0, Scoef=0.8, S0=35.0,
