@@ -4,8 +4,8 @@
 //    concatenates up to 4 fields per message too, mpi_exchanges.F:504-506) and one unpack kernel scatters the halos.
 //    In between, by default (ROMS_HALO=p2p): the pack kernel has stored the messages DIRECTLY into the neighbours'
 //    receive buffers over NVLink peer memory (CUDA IPC mapping of one buffer block per rank, double-buffered by the
-//    parity of the exchange counter), and one tiny kernel raises a flag in every neighbour and waits for theirs:
-//    no NCCL kernel, no proxy thread, ~4 us instead of ~20 us per exchange.  ROMS_HALO=nccl (or no peer access):
+//    parity of the exchange counter); its last block raises this rank's flag in every neighbour, and the blocks of the
+//    unpack kernel wait for the flag of their direction: two launches per exchange, no NCCL kernel, no proxy thread.  ROMS_HALO=nccl (or no peer access):
 //    one grouped ncclSend/ncclRecv over NVLink/NVSwitch.
 //    Everything is enqueued on the library's stream: no host synchronisation inside a step.
 #pragma once
@@ -19,22 +19,58 @@ struct MsgGeom {
   double* buf[8];
   int active[8];
 };
-// blockIdx.y = direction; blockIdx.z strides over the concatenated planes of the fields in hl
+struct SyncGeom { unsigned long long* to[8]; unsigned long long* from[8]; };
+// blockIdx.y = direction; blockIdx.z strides over the concatenated planes of the fields in hl.
+// Peer-memory path (counter != nullptr / sg.from set): the PACK launch writes into the neighbours' receive buffers and its
+// LAST block to finish raises this rank's flag in every neighbour (slot = the direction this rank is in, seen from
+// there); every block of the UNPACK launch first waits for the flag of the direction it unpacks.  A block never waits
+// for another block of its own GPU, so the pair cannot deadlock whatever the block scheduling order.
 template <bool PACK>
-__global__ void k_halo_msg(const __grid_constant__ KP p, const __grid_constant__ HaloList hl, const __grid_constant__ MsgGeom g, int nplanes) {
+__global__ void k_halo_msg(const __grid_constant__ KP p, const __grid_constant__ HaloList hl, const __grid_constant__ MsgGeom g, int nplanes,
+                           const __grid_constant__ SyncGeom sg, unsigned long long epoch, unsigned* counter, int* fail) {
   const int d = blockIdx.y;
-  if (!g.active[d]) return;
-  const DirBox b = g.box[d];
-  const int cell = blockIdx.x * blockDim.x + threadIdx.x;
-  if (cell >= b.ni * b.nj) return;
-  const int jj = cell / b.ni, ii = cell - jj * b.ni;
-  const long c = CIDX(b.i0 + ii, b.j0 + jj);
-  for (int pl = blockIdx.z; pl < nplanes; pl += gridDim.z) {
-    int f = 0, k = pl;
-    while (k >= hl.nk[f]) { k -= hl.nk[f]; ++f; }
-    double* a = hl.a[f] + c + (long)k * p.SXY;
-    double* m = g.buf[d] + (long)pl * (b.ni * b.nj) + cell;
-    if (PACK) *m = *a; else *a = *m;
+  const bool act = g.active[d];
+  if (!PACK) {
+    if (!act) return;
+    if (sg.from[d]) {
+      if (threadIdx.x == 0) {
+        const long long t0 = clock64();
+        unsigned long long v;
+        do {
+          asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(sg.from[d]) : "memory");
+          if (v < epoch && clock64() - t0 > 20000000000LL) { *fail = 1; break; }     // ~10 s: a neighbour died; do not hang the GPU
+        } while (v < epoch);
+      }
+      __syncthreads();
+    }
+  }
+  if (act) {
+    const DirBox b = g.box[d];
+    const int cell = blockIdx.x * blockDim.x + threadIdx.x;
+    if (cell < b.ni * b.nj) {
+      const int jj = cell / b.ni, ii = cell - jj * b.ni;
+      const long c = CIDX(b.i0 + ii, b.j0 + jj);
+      for (int pl = blockIdx.z; pl < nplanes; pl += gridDim.z) {
+        int f = 0, k = pl;
+        while (k >= hl.nk[f]) { k -= hl.nk[f]; ++f; }
+        double* a = hl.a[f] + c + (long)k * p.SXY;
+        double* m = g.buf[d] + (long)pl * (b.ni * b.nj) + cell;
+        if (PACK) *m = *a; else *a = __ldcg(m);
+      }
+    }
+  }
+  if (PACK && counter) {
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      const unsigned total = gridDim.x * gridDim.y * gridDim.z;
+      if (atomicAdd(counter, 1u) == total - 1) {
+        *counter = 0;
+        __threadfence_system();
+        for (int q = 0; q < 8; ++q)
+          if (sg.to[q]) asm volatile("st.release.sys.global.u64 [%0], %1;" :: "l"(sg.to[q]), "l"(epoch) : "memory");
+      }
+    }
   }
 }
 
@@ -56,27 +92,9 @@ struct NcclState {
   long long peer_off[8][2][8];           // that neighbour's offsets
   std::vector<std::pair<int, void*>> opened;   // rank -> mapped base (cudaIpcOpenMemHandle)
   int* d_fail = nullptr;                 // pinned host flag: a flag wait timed out
+  unsigned* counter = nullptr;           // blocks of the current pack launch that have finished
 };
 struct P2PInfo { cudaIpcMemHandle_t handle; long long off[2][8]; };
-struct SyncGeom { unsigned long long* to[8]; unsigned long long* from[8]; };
-// raise my flag in every neighbour (slot = the direction I am in, seen from there), then wait for theirs
-__global__ void k_halo_sync(const __grid_constant__ SyncGeom g, unsigned long long epoch, int* fail) {
-  const int d = threadIdx.x;
-  if (d >= 8) return;
-  if (g.to[d]) {
-    __threadfence_system();
-    asm volatile("st.release.sys.global.u64 [%0], %1;" :: "l"(g.to[d]), "l"(epoch) : "memory");
-  }
-  if (g.from[d]) {
-    const long long t0 = clock64();
-    unsigned long long v;
-    do {
-      asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(g.from[d]) : "memory");
-      if (v < epoch && clock64() - t0 > 20000000000LL) { *fail = 1; break; }     // ~10 s: a neighbour died; do not hang the GPU
-    } while (v < epoch);
-  }
-}
-
 int comm_init(Comm* cm, const roms_cfg* cfg) {
   cm->np_xi = cfg->np_xi > 0 ? cfg->np_xi : 1;
   cm->np_eta = cfg->np_eta > 0 ? cfg->np_eta : 1;
@@ -91,6 +109,7 @@ int comm_destroy(Comm* cm) {
     cudaFree(ns->red);
     for (auto& o : ns->opened) cudaIpcCloseMemHandle(o.second);
     cudaFree(ns->shm);
+    cudaFree(ns->counter);
     if (ns->d_fail) cudaFreeHost(ns->d_fail);
 #ifdef ROMS_WITH_NCCL
     if (ns->comm) ncclCommDestroy(ns->comm);
@@ -115,6 +134,8 @@ static int p2p_setup(NcclState* ns, const KP& p) {
     }
   CK(cudaMalloc(&ns->shm, cur));
   CK(cudaMemset(ns->shm, 0, cur));
+  CK(cudaMalloc(&ns->counter, sizeof(unsigned)));
+  CK(cudaMemset(ns->counter, 0, sizeof(unsigned)));
   CK(cudaHostAlloc(&ns->d_fail, sizeof(int), cudaHostAllocMapped));
   *ns->d_fail = 0;
   P2PInfo mine;
@@ -239,14 +260,15 @@ int comm_exchange(Comm* cm, const KP& p, cudaStream_t st, const XF* f, int nf, l
           sg.from[d] = (unsigned long long*)ns->shm + d;
         }
       }
-      k_halo_msg<true><<<g, b, 0, st>>>(p, hl, gs, nplanes);
-      k_halo_sync<<<1, 32, 0, st>>>(sg, ns->epoch, ns->d_fail);
-      k_halo_msg<false><<<g, b, 0, st>>>(p, hl, gr, nplanes);
-      (*launches) += 3;
+      k_halo_msg<true><<<g, b, 0, st>>>(p, hl, gs, nplanes, sg, ns->epoch, ns->counter, ns->d_fail);
+      k_halo_msg<false><<<g, b, 0, st>>>(p, hl, gr, nplanes, sg, ns->epoch, nullptr, ns->d_fail);
+      (*launches) += 2;
       if (*ns->d_fail) { g_err = "halo exchange: a neighbour never raised its flag (rank lost?)"; return -2; }
       continue;
     }
-    k_halo_msg<true><<<g, b, 0, st>>>(p, hl, gs, nplanes);
+    SyncGeom none;
+    memset(&none, 0, sizeof(none));
+    k_halo_msg<true><<<g, b, 0, st>>>(p, hl, gs, nplanes, none, 0ull, nullptr, nullptr);
     (*launches)++;
     ncclGroupStart();
     for (int d = 0; d < 8; ++d) {
@@ -260,7 +282,7 @@ int comm_exchange(Comm* cm, const KP& p, cudaStream_t st, const XF* f, int nf, l
     }
     ncclResult_t r = ncclGroupEnd();
     if (r != ncclSuccess) { g_err = std::string("nccl send/recv: ") + ncclGetErrorString(r); return -1000 - (int)r; }
-    k_halo_msg<false><<<g, b, 0, st>>>(p, hl, gr, nplanes);
+    k_halo_msg<false><<<g, b, 0, st>>>(p, hl, gr, nplanes, none, 0ull, nullptr, nullptr);
     (*launches)++;
   }
   cudaError_t e = cudaGetLastError();
