@@ -65,8 +65,8 @@ def peaks():
 
 def ncu_traffic(kernel):
     """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel` from the committed `ncu --set full` capture of this
-    workload (profiles/r1_ncu_traffic_v2.json, made from gpurun_out/r1_full_v2_*_raw.csv); None if the kernel is not in it."""
-    p = os.path.join(ROOT, "profiles", "r1_ncu_traffic_v2.json")
+    workload (profiles/r1_ncu_traffic_v3.json, made from gpurun_out/prof3/full_v3.ncu-rep and the v2 captures); None if the kernel is not in it."""
+    p = os.path.join(ROOT, "profiles", "r1_ncu_traffic_v3.json")
     if not os.path.exists(p):
         return None
     norm = lambda n: n.replace("(", "").replace(")", "").replace(" ", "").replace("true", "1").replace("false", "0")
@@ -310,7 +310,7 @@ def main():
                     "traffic": ncu_traffic(top[0]) if (Lm, Mm, N) == (1024, 1024, 64) else None,
                     "peak_source": peak_src, "algorithmic_bytes_per_launch": words * 8.0 * npts, "avg_launch_ms": avg_ms,
                     "launches_per_step": top[1] / a.steps, "share_of_step": top[2] / tot,
-                    "traffic_source": "profiles/r1_ncu_traffic_v2.json (ncu --set full, dram read+write bytes per launch, this workload)"}
+                    "traffic_source": "profiles/r1_ncu_traffic_v3.json (ncu --set full, dram read+write bytes per launch, this workload)"}
         if a.kernel_table:
             with open(a.kernel_table, "w") as f:
                 f.write(f"# per-kernel CUDA-event times, {a.steps} steps, {workload}\n# kernel launches total_ms avg_ms share algorithmic_GB/s\n")
