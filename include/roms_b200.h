@@ -122,6 +122,8 @@ int  roms_t3dmix(roms_ctx* h);                /* t3dmix_S.F:4  (TS_DIF2: Laplaci
 int  roms_alfabeta(roms_ctx* h, double* alpha_host, double* beta_host); /* alfabeta.F:4 */
 int  roms_exchange(roms_ctx* h, int nfields, const int* fields, const int* lvls, const int* itrcs);
                                               /* mpi_exchanges.F:34-40 exchange_xxx */
+int  roms_grid_stats(roms_ctx* h, double out[9]); /* setup_grid2.F:64-100 start-up report of this subdomain: hmin, hmax, grdmin,
+                                                  grdmax, Cg_min, Cg_max, Cu_Cor, area, volume                                */
 int  roms_diag(roms_ctx* h, double out[4]);   /* diag.F:50: KE, barotropic KE, max adv CFL, its vertical part */
 
 /* ---- the driver loop body, for hosts without a Fortran main (main.F:86-321, 333-520) ---- */

@@ -1866,6 +1866,25 @@ int orc_pull(void* h, int field, int lvl, int itrc, double* host) {
 }
 long orc_field_count(void* h, int field) { long n = 0; field_ptr(*(Orc*)h, field, 1, 1, &n); return n; }
 int orc_setup_grid(void* h) { setup_grid(*(Orc*)h); return 0; }
+// setup_grid2.F:64-100: extrema over the water points of the rho-range incl. boundary rows, unmasked area and volume
+int orc_grid_stats(void* h, double out[9]) {
+  Orc& o = *(Orc*)h;
+  GEOM
+  double hmin = 1e20, hmax = -1e20, gmin = 1e20, gmax = -1e20, cmin = 1e20, cmax = -1e20, ccor = -1e20;
+  for (int j = jstrR; j <= jendR; ++j)
+    for (int i = istrR; i <= iendR; ++i)
+      if (A2(o.rmask, i, j) > 0.5) {
+        hmin = std::min(hmin, A2(o.h, i, j)); hmax = std::max(hmax, A2(o.h, i, j));
+        double cff = 1. / sqrt(A2(o.pm, i, j) * A2(o.pn, i, j));
+        gmin = std::min(gmin, cff); gmax = std::max(gmax, cff);
+        cff = o.dtfast * sqrt(o.c.g * A2(o.h, i, j) * (A2(o.pm, i, j) * A2(o.pm, i, j) + A2(o.pn, i, j) * A2(o.pn, i, j)));
+        cmin = std::min(cmin, cff); cmax = std::max(cmax, cff);
+        cff = o.c.dt * fabs(A2(o.f, i, j));
+        ccor = std::max(ccor, cff);
+      }
+  out[0] = hmin; out[1] = hmax; out[2] = gmin; out[3] = gmax; out[4] = cmin; out[5] = cmax; out[6] = ccor; out[7] = o.area; out[8] = o.volume;
+  return 0;
+}
 int orc_get_nfast(void* h) { return ((Orc*)h)->nfast; }
 int orc_get_weights(void* h, double* w1, double* w2, int n) {
   Orc& o = *(Orc*)h;

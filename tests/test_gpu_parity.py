@@ -56,6 +56,28 @@ def test_constants_match_oracle():
     g.close(); o.close()
 
 
+def test_rivers_ana_startup_on_gpu():
+    """nfast, weights, Cs tables and the setup_grid2 report of the reference's Rivers_ana grid (masked, sloping bottom, closed
+    walls): library == oracle, and both == the reference's log (tests/golden/rivers_ana_startup.json)."""
+    G = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "rivers_ana_startup.json")))
+    cfg, st = cases.rivers_ana_grid()
+    g, o = Roms(cfg), Oracle(cfg)
+    assert g.nfast() == o.nfast() == G["nfast"]
+    for a, b in zip(g.weights(41), o.weights(41)):
+        assert np.array_equal(a, b)
+    for a, b in zip(g.scoord(), o.scoord()):
+        assert np.array_equal(a, b)
+    for m in (g, o):
+        m.push_state(st)
+        m.call("setup_grid")
+    sg, so = g.grid_stats(), o.grid_stats()
+    assert np.array_equal(sg[:7], so[:7]) and np.allclose(sg[7:], so[7:], rtol=1e-14, atol=0)
+    assert sg[0] == G["hmin"] and sg[1] == G["hmax"] and abs(sg[7] / G["area"] - 1) < 1e-13 and abs(sg[8] / G["volume"] - 1) < 1e-13
+    for f in ("UMASK", "VMASK", "PMASK", "DM_U", "DN_V", "PMON_U", "FOMN"):
+        assert np.array_equal(parity_walk.view(g.pull(f), cfg), parity_walk.view(o.pull(f), cfg)), f
+    g.close(); o.close()
+
+
 @pytest.mark.parametrize("case", ["channel", "filament", "channel_linear_odd", "channel_walls", "channel_walls_linear_odd",
                                   "seamount_island_walls", "seamount_island_periodic", "closed_basin", "closed_basin_seamount_odd",
                                   "ew_walls_ns_periodic", "channel_mixing", "closed_basin_seamount_mixing", "filament_mixing_switches"])

@@ -6,7 +6,7 @@ bar here is 1e-14 relative (observed: <= 2e-16), two orders tighter than the gfo
 import json
 import os
 import numpy as np
-from orclib import Oracle, filament_cfg
+from orclib import Oracle, filament_cfg, cases
 
 GOLD = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "filament_diag.json")))
 
@@ -103,3 +103,32 @@ def test_lateral_mixing_properties():
     for f, l in (("U", 1), ("T", 1), ("ZETA", a.get_idx()[6])):
         assert np.array_equal(a.pull(f, l), b.pull(f, l))
     a.close(); b.close()
+
+
+def test_rivers_ana_startup_golden():
+    """Second pin of the start-up arithmetic, from the reference's Rivers_ana log (tests/golden/rivers_ana_startup.json):
+    set_weights with ndtfast=30 -> nfast=41 (benchmark.result_github_gnu:58), the Cs_w table for theta_s=theta_b=6, N=10
+    (:102-112, 8 digits) and the setup_grid2 report of a MASKED grid with a sloping bottom and closed walls (:116-118):
+    hmin/hmax over water points incl. the boundary rows, unmasked area and volume (17 digits), Cg_min/Cg_max."""
+    import json
+    import os
+    G = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "rivers_ana_startup.json")))
+    cfg, st = cases.rivers_ana_grid()
+    o = Oracle(cfg)
+    assert cfg.ndtfast == G["ndtfast"] and o.nfast() == G["nfast"]
+    w1, w2 = o.weights(o.nfast())
+    assert abs(w1.sum() - 1) < 1e-14 and abs(w2.sum() - 1) < 1e-14
+    cw, _ = o.scoord()
+    for k, sc, cs in G["Cs_w"]:
+        tol = 0.51e-7 * 10.0 ** np.floor(np.log10(abs(cs))) if cs != 0 else 0.0      # printed as d.ddddddd E+xx
+        assert abs(cw[k] - cs) <= tol, (k, cw[k], cs)
+    o.push_state(st)
+    o.call("setup_grid")
+    hmin, hmax, gmin, gmax, cgmin, cgmax, cucor, area, vol = o.grid_stats()
+    assert hmin == G["hmin"] and hmax == G["hmax"]
+    assert abs(gmin - G["grdmin"]) < 1e-5 and abs(gmax - G["grdmax"]) < 1e-5
+    assert abs(area / G["area"] - 1) < 1e-13 and abs(vol / G["volume"] - 1) < 1e-13
+    assert abs(cgmax - G["Cg_max"]) < 5.1e-8 and abs(cgmin - G["Cg_min"]) < 5.1e-8 and cucor == G["Cu_Cor"]
+    # land mask of the case: 840 land cells (two all-land rows + 8 rows with a 20-cell river channel)
+    assert int((st["RMASK"][2:-2, 2:-2] == 0).sum()) == 840
+    o.close()

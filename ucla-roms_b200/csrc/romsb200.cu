@@ -5,6 +5,7 @@
 // and exposes one export per reference tile subroutine (main.F:397-479 call order in roms_step).
 // There is no CPU fallback: every numerical export launches CUDA kernels or fails.
 #include <cuda_runtime.h>
+#include <algorithm>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -758,6 +759,41 @@ int roms_alfabeta(roms_ctx* h, double* alpha_host, double* beta_host) {
 static double pairsum(const double* a, size_t n) {
   if (n <= 8) { double s = 0; for (size_t i = 0; i < n; ++i) s += a[i]; return s; }
   return pairsum(a, n / 2) + pairsum(a + n / 2, n - n / 2);
+}
+// setup_grid2.F:64-100 for this subdomain (the reference prints the global values once at start-up): extrema over the water
+// points of the rho-range incl. boundary rows on a physical edge, unmasked area and volume.  A one-off start-up report
+// like the reference's: the five planes are pulled and scanned on the host in index order.
+int roms_grid_stats(roms_ctx* h, double out[9]) {
+  CK(cudaSetDevice(h->device));
+  const KP& p = h->kp;
+  const int Lm = h->c.Lm, Mm = h->c.Mm, SXh = Lm + 4;
+  const size_t n2 = (size_t)SXh * (Mm + 4);
+  std::vector<double> pmv(n2), pnv(n2), hv(n2), rmv(n2), fv(n2);
+  if (roms_pull(h, ROMS_PM, 1, 1, pmv.data()) || roms_pull(h, ROMS_PN, 1, 1, pnv.data()) || roms_pull(h, ROMS_H, 1, 1, hv.data()) ||
+      roms_pull(h, ROMS_RMASK, 1, 1, rmv.data()) || roms_pull(h, ROMS_F, 1, 1, fv.data()))
+    return -1;
+  double hmin = 1e20, hmax = -1e20, gmin = 1e20, gmax = -1e20, cmin = 1e20, cmax = -1e20, ccor = -1e20, area = 0, vol = 0;
+  for (int j = p.jstrR; j <= p.jendR; ++j)
+    for (int i = p.istrR; i <= p.iendR; ++i) {
+      const size_t o = (size_t)(j + 1) * SXh + (i + 1);
+      if (rmv[o] > 0.5) {
+        hmin = std::min(hmin, hv[o]); hmax = std::max(hmax, hv[o]);
+        double cff = 1. / sqrt(pmv[o] * pnv[o]);
+        gmin = std::min(gmin, cff); gmax = std::max(gmax, cff);
+        cff = p.dtfast * sqrt(p.g * hv[o] * (pmv[o] * pmv[o] + pnv[o] * pnv[o]));
+        cmin = std::min(cmin, cff); cmax = std::max(cmax, cff);
+        cff = p.dt * fabs(fv[o]);
+        ccor = std::max(ccor, cff);
+      }
+    }
+  for (int j = p.jstr; j <= p.jend; ++j)
+    for (int i = p.istr; i <= p.iend; ++i) {
+      const size_t o = (size_t)(j + 1) * SXh + (i + 1);
+      const double dA = rmv[o] / (pmv[o] * pnv[o]);
+      area += dA; vol += dA * hv[o];
+    }
+  out[0] = hmin; out[1] = hmax; out[2] = gmin; out[3] = gmax; out[4] = cmin; out[5] = cmax; out[6] = ccor; out[7] = area; out[8] = vol;
+  return 0;
 }
 int roms_diag(roms_ctx* h, double out[4]) {
   CK(cudaSetDevice(h->device));

@@ -96,6 +96,12 @@ class CApi:
         self._check(self._f("diag")(self.h, out), "diag")
         return np.array(out[:])
 
+    def grid_stats(self):
+        """setup_grid2.F:64-100: hmin, hmax, grdmin, grdmax, Cg_min, Cg_max, Cu_Cor, area, volume"""
+        out = (C.c_double * 9)()
+        self._check(self._f("grid_stats")(self.h, out), "grid_stats")
+        return np.array(out[:])
+
     def nfast(self):
         return self._f("get_nfast")(self.h)
 

@@ -217,6 +217,34 @@ def filament(Lm=64, Mm=64, N=32):
     return cfg, st
 
 
+def rivers_ana_grid():
+    """Grid, mask and run parameters of the reference's tests/Rivers_ana (ana_grid.h, param.opt, benchmark.in): 100x100x10,
+    dx=dy=100 m, closed walls, flat 5 m shelf over the southern fifth then a uniform slope to 100 m, land strip with a river
+    channel.  Only the start-up quantities of this case are pinned by the reference's log (nfast, Cs_w table, hmin/hmax,
+    area/volume, Cg_min/Cg_max: benchmark.result_github_gnu:58,101-118): its time stepping needs KPP and river forcing."""
+    Lm = Mm = 100
+    N = 10
+    cfg = RomsCfg(Lm=Lm, Mm=Mm, N=N, NT=2, ew_periodic=0, ns_periodic=0, nonlin_eos=1, salinity=1, ndtfast=30,
+                  np_xi=1, np_eta=1, inode=0, jnode=0, dt=20.0, rho0=1027.5, g=9.81, Tcoef=0.0, T0=0.0, Scoef=0.0, S0=0.0,
+                  rdrg=0.0, rdrg2=1.0e-3, Zob=1.0e-2, gamma2=1.0, theta_s=6.0, theta_b=6.0, hc=25.0)
+    sy, sx = Mm + 4, Lm + 4
+    size_xi = size_eta = 1.0e4
+    depth, max_depth = 5.0, 100.0
+    dx, dy = size_xi / Lm, size_eta / Mm
+    i = np.arange(-1, Lm + 3)[None, :] + np.zeros((sy, 1))
+    j = np.arange(-1, Mm + 3)[:, None] + np.zeros((1, sx))
+    xr, yr = dx * (i - 0.5), dy * (j - 0.5)
+    shelf = size_eta / 5
+    slope = (max_depth - depth) / (size_eta * 4 / 5)
+    h = np.where(yr < shelf, depth, depth + (yr - shelf) * slope)
+    land, coast, riv_west, riv_east = size_eta * 0.1, size_eta * 0.02, size_xi * 0.4, size_xi * 0.6
+    rmask = np.ones((sy, sx))
+    rmask[(yr < land) & ((xr < riv_west) | (xr > riv_east))] = 0.0
+    rmask[yr < coast] = 0.0
+    st = {"H": h, "PM": np.full((sy, sx), 1.0 / dx), "PN": np.full((sy, sx), 1.0 / dy), "F": np.zeros((sy, sx)), "RMASK": rmask}
+    return cfg, st
+
+
 def initialize(model, state):
     """roms_init (main.F:86-321) for a host without Fortran: push the analytic fields, derive the
     grid metrics, then set_depth / set_HUV / omega / rho_eos."""
