@@ -167,6 +167,48 @@ def test_alfabeta():
     g.close(); o.close()
 
 
+def test_full_size_properties():
+    """BASELINE configs[1] at FULL size (1024x1024x64, the bench workload), where the CPU oracle is out of reach: parity through
+    size-independent properties.  (1) Translation: the E-W periodic problem shifted by 37 cells is the roll of the unshifted
+    one, so after two baroclinic steps every prognostic field must be the roll of the unshifted result BIT FOR BIT (any
+    tile-, block- or alignment-dependent arithmetic in a kernel would break this: 37 is coprime to every tile size).
+    (2) Conservation: with closed N/S walls and no surface fluxes the volume (sum zeta*dA) and the heat and salt content
+    (sum Hz*T*dA) are conserved to round-off."""
+    Lm, Mm, N, shift = 1024, 1024, 64, 37
+
+    def run(ishift):
+        cfg, st = cases.channel(Lm, Mm, N, ns_walls=True, ishift=ishift)
+        g = Roms(cfg)
+        cases.initialize(g, st)
+        del st
+        dA = 1.0e6
+        Hz0 = g.pull("HZ")[:, 2:-2, 2:-2]
+        c0 = [float((Hz0 * g.pull("T", 1, it)[:, 2:-2, 2:-2]).sum()) * dA for it in (1, 2)]
+        v0 = float(g.pull("ZETA", 1)[2:-2, 2:-2].sum()) * dA
+        hsum = float(g.pull("H")[2:-2, 2:-2].sum()) * dA
+        del Hz0
+        g.call("run", 2)
+        iic, iif, nstp, nrhs, nnew, kstp, knew = g.get_idx()
+        out = {"zeta": g.pull("ZETA", knew), "ubar": g.pull("UBAR", knew), "vbar": g.pull("VBAR", knew), "u": g.pull("U", nnew),
+               "v": g.pull("V", nnew), "T": g.pull("T", nnew, 1), "S": g.pull("T", nnew, 2), "rho": g.pull("RHO1")}
+        Hz1 = g.pull("HZ")[:, 2:-2, 2:-2]
+        c1 = [float((Hz1 * out[k][:, 2:-2, 2:-2]).sum()) * dA for k in ("T", "S")]
+        v1 = float(out["zeta"][2:-2, 2:-2].sum()) * dA
+        d = g.diag()
+        g.close()
+        cons = {"volume": abs(v1 - v0) / hsum, "heat": abs(c1[0] - c0[0]) / abs(c0[0]), "salt": abs(c1[1] - c0[1]) / abs(c0[1])}
+        return {k: np.ascontiguousarray(a[..., 2:-2, 2:-2]) for k, a in out.items()}, cons, d
+
+    a, cons, da = run(0)
+    print("full-size conservation after 2 steps:", cons)
+    assert cons["volume"] <= 1e-15 and cons["heat"] <= 1e-12 and cons["salt"] <= 1e-12, cons
+    assert all(np.isfinite(x).all() for x in a.values())
+    b, cons_b, db = run(shift)
+    for k in a:
+        assert np.array_equal(np.roll(a[k], -shift, axis=-1), b[k]), k
+    assert np.allclose(da, db, rtol=1e-12)
+
+
 def test_two_gpu_halo_exchange_parity():
     """NCCL halo swaps: 2 ranks (2x1 split) against the single-domain oracle; skipped on a 1-GPU box."""
     import subprocess

@@ -72,7 +72,7 @@ def _noise(ig, jg, k, salt):
 
 def channel(Lm=64, Mm=64, N=16, NT=2, ns_walls=False, nonlin_eos=True, dt=120.0, ndtfast=60, dx=1.0e3, dy=1.0e3,
             depth=4000.0, seed=20260101, perturb=1e-6, amp=None, sub=(0, 0, 1, 1), seamount=False, island=False, ew_walls=False,
-            visc2=None, tnu2=None, sponge=False):
+            visc2=None, tnu2=None, sponge=False, ishift=0):
     """Lm, Mm are the GLOBAL interior sizes; sub=(inode, jnode, np_xi, np_eta) selects this rank's block
     (mpi_setup.F:61-70; uneven splits as mpi_setup.F:117-160, see block_extent).  Returns the cfg and state of that block.
     seamount: Gaussian seamount h = depth*(1 - 0.5*exp(-r^2/(L/5)^2)) (SURVEY.md 8(d) input (3), form of
@@ -81,7 +81,9 @@ def channel(Lm=64, Mm=64, N=16, NT=2, ns_walls=False, nonlin_eos=True, dt=120.0,
     ns_walls: a fully closed basin, BASELINE configs[2] geometry).
     visc2 / tnu2 [m2/s]: switch on UV_VIS2 / TS_DIF2 lateral mixing (visc3d_S.F, t3dmix_S.F) with these background
     coefficients; sponge: add a smooth spatially varying part to visc2_r, visc2_p, diff2 (what set_nudgcof.F:88-110 does
-    near open boundaries) so that the coefficient averaging of the flux formulas is exercised."""
+    near open boundaries) so that the coefficient averaging of the flux formulas is exercised.
+    ishift: translate the whole E-W periodic problem by this many cells in xi (the state is the roll of the unshifted one, so
+    the solution must be the roll of the unshifted solution, bit for bit -- a size-independent parity property)."""
     inode, jnode, np_xi, np_eta = sub
     LmG, MmG = Lm, Mm
     (Lm, i0), (Mm, j0) = block_extent(LmG, np_xi, inode), block_extent(MmG, np_eta, jnode)
@@ -100,7 +102,7 @@ def channel(Lm=64, Mm=64, N=16, NT=2, ns_walls=False, nonlin_eos=True, dt=120.0,
     ig = (np.arange(-2, Lm + 4) + i0)[None, :] + np.zeros((sy, 1), dtype=np.int64)
     jg = (np.arange(-2, Mm + 4) + j0)[:, None] + np.zeros((1, sx), dtype=np.int64)
     if not ew_walls:
-        ig = (ig - 1) % LmG + 1                  # E-W periodic images
+        ig = (ig - 1 + ishift) % LmG + 1         # E-W periodic images
     if not ns_walls:
         jg = (jg - 1) % MmG + 1
     x = dx * (ig - 0.5); y = dy * (jg - 0.5)
