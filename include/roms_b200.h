@@ -79,6 +79,7 @@ enum roms_field {
   ROMS_PMASK, ROMS_DM_P, ROMS_DN_P, ROMS_PMON_U, ROMS_PNOM_V,
   ROMS_VISC2_R, ROMS_VISC2_P,
   ROMS_DIFF2,                                    /* itrc 1..NT */
+  ROMS_RIV_UFLX, ROMS_RIV_VFLX,                  /* river_frc.F: river faces, 10*iriver + fraction of the river's volume flux */
   ROMS_NFIELDS
 };
 
@@ -120,6 +121,12 @@ int  roms_step3d_t(roms_ctx* h, int tile);    /* step3d_t_ISO.F:20 */
 int  roms_visc3d(roms_ctx* h);                /* visc3d_S.F:4  (UV_VIS2: harmonic viscosity along S-surfaces)  */
 int  roms_t3dmix(roms_ctx* h);                /* t3dmix_S.F:4  (TS_DIF2: Laplacian tracer diffusion, all NT)   */
 int  roms_alfabeta(roms_ctx* h, double* alpha_host, double* beta_host); /* alfabeta.F:4 */
+int  roms_set_river(roms_ctx* h, int iriver, double vol, const double* trc);
+                                               /* river_frc.F set_river_frc: volume flux [m3/s] and the NT tracer values of river
+                                                  iriver (1..8) for the coming steps; switches river_source on.  The river faces
+                                                  are the non-zero entries of ROMS_RIV_UFLX / ROMS_RIV_VFLX (init_river_frc).
+                                                  Hooks: step2d_FB.F:531-554, pre_step3d4S.F:493-522, step3d_uv2.F:689-717,
+                                                  compute_horiz_tracer_fluxes.h:217-246 */
 int  roms_exchange(roms_ctx* h, int nfields, const int* fields, const int* lvls, const int* itrcs);
                                               /* mpi_exchanges.F:34-40 exchange_xxx */
 int  roms_grid_stats(roms_ctx* h, double out[9]); /* setup_grid2.F:64-100 start-up report of this subdomain: hmin, hmax, grdmin,

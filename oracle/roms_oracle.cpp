@@ -51,6 +51,12 @@ struct Orc {
   // time indices (scalars.F)
   int iic, iif, nstp, nrhs, nnew, kstp, knew, ntstart, forw_start;
   double dtfast, area, volume;
+  // river_frc.F: river faces coded as 10*iriver + fraction of the river's volume flux through the face (riv_uflx/riv_vflx),
+  // per-river volume flux [m3/s] and tracer values (set_river_frc, ana_frc_river.h)
+  vec riv_uflx, riv_vflx;
+  std::vector<double> riv_vol;
+  std::vector<vec> riv_trc;
+  bool river_source = false;
   vec xr;  // only for the Filament analytic initial condition
   std::vector<vec> s2d;
 };
@@ -59,6 +65,8 @@ struct Orc {
 #define A3(a, i, j, k) (a)[(size_t)((i) + 1) + (size_t)((j) + 1) * SX + (size_t)((k)-1) * SXY]
 #define AW(a, i, j, k) (a)[(size_t)((i) + 1) + (size_t)((j) + 1) * SX + (size_t)(k) * SXY]
 #define SL(a, i, k) (a)[(size_t)((i) + 1) + (size_t)(k) * SX]   // (i,k) slab scratch, k=0:N
+static inline bool riv_on(double code) { return std::fabs(code) > 1e-3; }
+static inline int riv_id(double code) { return (int)std::lround(code / 10); }   // nint(riv_uflx/10)
 
 #define GEOM                                                                                 \
   const int Lm = o.Lm, Mm = o.Mm, N = o.N, SX = o.SX;                                        \
@@ -789,7 +797,7 @@ void vert_rhs_uv(Orc& o, int j, const vec& u, const vec& v, vec& FC, vec& CF, ve
 
 // compute_horiz_tracer_fluxes.h:1-246 for one k-plane. upstream=false: C4 (pre_step3d4S.F:154);
 // true: UP3 (step3d_t_ISO.F:196).
-void horiz_tracer_fluxes(Orc& o, int k, const vec& t, bool upstream, vec& FX, vec& FE, vec& wrk1) {
+void horiz_tracer_fluxes(Orc& o, int k, const vec& t, bool upstream, vec& FX, vec& FE, vec& wrk1, int itrc) {
   GEOM
   const int imin = WWALL ? istr : istr - 1, imax = EWALL ? iend : iend + 1;
   const int jmin = SWALL ? jstr : jstr - 1, jmax = NWALL ? jend : jend + 1;   // compute_horiz_tracer_fluxes.h:118-160
@@ -833,6 +841,45 @@ void horiz_tracer_fluxes(Orc& o, int k, const vec& t, bool upstream, vec& FX, ve
       for (int i = istr; i <= iend; ++i)
         A2(FE, i, j) = 0.5 * (A3(t, i, j, k) + A3(t, i, j - 1, k) - 0.3333333333333333 * (A2(wrk1, i, j) - A2(wrk1, i, j - 1))) * A3(o.FlxV, i, j, k);
   }
+  if (o.river_source) {   // compute_horiz_tracer_fluxes.h:217-246: river faces carry the river's tracer value
+    const int N = o.N;
+    for (int j = jstr; j <= jend; ++j)
+      for (int i = istr; i <= iend + 1; ++i)
+        if (riv_on(A2(o.riv_uflx, i, j))) {
+          const double riv_depth = 0.5 * (AW(o.z_w, i - 1, j, N) - AW(o.z_w, i - 1, j, 0) + AW(o.z_w, i, j, N) - AW(o.z_w, i, j, 0));
+          const int iriver = riv_id(A2(o.riv_uflx, i, j));
+          const double riv_uvel = o.riv_vol[iriver - 1] * (A2(o.riv_uflx, i, j) - 10 * iriver) / riv_depth;
+          A2(FX, i, j) = o.riv_trc[iriver - 1][itrc] * 0.5 * (A3(o.Hz, i - 1, j, k) + A3(o.Hz, i, j, k)) * riv_uvel;
+        }
+    for (int j = jstr; j <= jend + 1; ++j)
+      for (int i = istr; i <= iend; ++i)
+        if (riv_on(A2(o.riv_vflx, i, j))) {
+          const double riv_depth = 0.5 * (AW(o.z_w, i, j - 1, N) - AW(o.z_w, i, j - 1, 0) + AW(o.z_w, i, j, N) - AW(o.z_w, i, j, 0));
+          const int iriver = riv_id(A2(o.riv_vflx, i, j));
+          const double riv_vvel = o.riv_vol[iriver - 1] * (A2(o.riv_vflx, i, j) - 10 * iriver) / riv_depth;
+          A2(FE, i, j) = o.riv_trc[iriver - 1][itrc] * 0.5 * (A3(o.Hz, i, j - 1, k) + A3(o.Hz, i, j, k)) * riv_vvel;
+        }
+  }
+}
+// pre_step3d4S.F:493-522 / step3d_uv2.F:689-717: the velocity through a river face is the river's, uniform over the column
+void river_uv(Orc& o, vec& un, vec& vn, int iu0, int jv0) {
+  GEOM
+  for (int j = jstr; j <= jend; ++j)
+    for (int i = iu0; i <= iend; ++i)
+      if (riv_on(A2(o.riv_uflx, i, j))) {
+        const double riv_depth = 0.5 * (AW(o.z_w, i - 1, j, N) - AW(o.z_w, i - 1, j, 0) + AW(o.z_w, i, j, N) - AW(o.z_w, i, j, 0));
+        const int iriver = riv_id(A2(o.riv_uflx, i, j));
+        const double riv_uvel = o.riv_vol[iriver - 1] * (A2(o.riv_uflx, i, j) - 10 * iriver) / (A2(o.dn_u, i, j) * riv_depth);
+        for (int k = 1; k <= N; ++k) A3(un, i, j, k) = riv_uvel;
+      }
+  for (int j = jv0; j <= jend; ++j)
+    for (int i = istr; i <= iend; ++i)
+      if (riv_on(A2(o.riv_vflx, i, j))) {
+        const double riv_depth = 0.5 * (AW(o.z_w, i, j - 1, N) - AW(o.z_w, i, j - 1, 0) + AW(o.z_w, i, j, N) - AW(o.z_w, i, j, 0));
+        const int iriver = riv_id(A2(o.riv_vflx, i, j));
+        const double riv_vvel = o.riv_vol[iriver - 1] * (A2(o.riv_vflx, i, j) - 10 * iriver) / (A2(o.dm_v, i, j) * riv_depth);
+        for (int k = 1; k <= N; ++k) A3(vn, i, j, k) = riv_vvel;
+      }
 }
 
 // compute_vert_tracer_fluxes.h:1-140 (SPLINE_TS) for one j-row: FC(i,k) = vertical flux, k=0:N
@@ -963,7 +1010,7 @@ void pre_step3d(Orc& o) {
           A3(Hz_fwd, i, j, k) = A3(o.Hz, i, j, k) - FlxDiv;
         }
       for (int itrc = 0; itrc < NT; ++itrc) {
-        horiz_tracer_fluxes(o, k, o.t[nrhs - 1][itrc], false, UFx, VFe, wrk1);
+        horiz_tracer_fluxes(o, k, o.t[nrhs - 1][itrc], false, UFx, VFe, wrk1, itrc);
         vec& tn = o.t[nnew - 1][itrc];
         vec& ts = o.t[nstp - 1][itrc];
         vec& ti = o.t[indx - 1][itrc];
@@ -1079,6 +1126,7 @@ void pre_step3d(Orc& o) {
       }
     }
   }
+  if (o.river_source) river_uv(o, o.u[nnew - 1], o.v[nnew - 1], istrU, jstrV);   // pre_step3d4S.F:493-522
   u3dbc(o, o.u[nnew - 1]);
   v3dbc(o, o.v[nnew - 1]);
   for (int itrc = 0; itrc < NT; ++itrc) {
@@ -1322,6 +1370,24 @@ void step2d(Orc& o) {
     for (int i = istrR; i <= iendR; ++i)
       A2(o.DV_avg1, i, jend + 1) = A2(o.DV_avg1, i, jend + 1) + cff1 * (A2(Dnew, i, jend + 1) + A2(Dnew, i, jend)) * (A2(vn, i, jend + 1)) * A2(o.dm_v, i, jend + 1);
   }
+  if (o.river_source) {   // step2d_FB.F:531-554
+    for (int j = jstr; j <= jend; ++j)
+      for (int i = istrU; i <= iend; ++i)
+        if (riv_on(A2(o.riv_uflx, i, j))) {
+          const int iriver = riv_id(A2(o.riv_uflx, i, j));
+          const double river_flux = o.riv_vol[iriver - 1] * (A2(o.riv_uflx, i, j) - 10 * iriver);
+          A2(un, i, j) = river_flux * 2 / (A2(o.dn_u, i, j) * (A2(Dnew, i - 1, j) + A2(Dnew, i, j)));
+          A2(o.DU_avg1, i, j) = river_flux;
+        }
+    for (int j = jstrV; j <= jend; ++j)
+      for (int i = istr; i <= iend; ++i)
+        if (riv_on(A2(o.riv_vflx, i, j))) {
+          const int iriver = riv_id(A2(o.riv_vflx, i, j));
+          const double river_flux = o.riv_vol[iriver - 1] * (A2(o.riv_vflx, i, j) - 10 * iriver);
+          A2(vn, i, j) = river_flux * 2 / (A2(o.dm_v, i, j) * (A2(Dnew, i, j - 1) + A2(Dnew, i, j)));
+          A2(o.DV_avg1, i, j) = river_flux;
+        }
+  }
   if (iif == o.nfast) {
     for (int j = jstrR; j <= jendR; ++j)
       for (int i = istrR; i <= iendR; ++i) A2(zn, i, j) = A2(o.Zt_avg1, i, j);
@@ -1404,6 +1470,7 @@ void step3d_uv2(Orc& o) {
       }
     }
   }
+  if (o.river_source) river_uv(o, o.u[nnew - 1], o.v[nnew - 1], istr, jstr);   // step3d_uv2.F:689-717
   ex3(o, o.FlxU); ex3(o, o.u[nnew - 1]); ex2(o, o.ubar[knew - 1]);
   ex3(o, o.FlxV); ex3(o, o.v[nnew - 1]); ex2(o, o.vbar[knew - 1]);
 }
@@ -1421,7 +1488,7 @@ void step3d_t(Orc& o) {
       vec FX(o.SXY), FE(o.SXY), wrk1(o.SXY);
 #pragma omp for
       for (int k = 1; k <= N; ++k) {
-        horiz_tracer_fluxes(o, k, tr, true, FX, FE, wrk1);
+        horiz_tracer_fluxes(o, k, tr, true, FX, FE, wrk1, itrc);
         for (int j = jstr; j <= jend; ++j)
           for (int i = istr; i <= iend; ++i)
             A3(tn, i, j, k) = A3(tn, i, j, k) - dt * A2(o.pm, i, j) * A2(o.pn, i, j) * (A2(FX, i + 1, j) - A2(FX, i, j) + A2(FE, i, j + 1) - A2(FE, i, j));
@@ -1813,6 +1880,7 @@ vec* field_ptr(Orc& o, int field, int lvl, int itrc, long* count) {
     case ROMS_PMASK: p = &o.pmask; break; case ROMS_DM_P: p = &o.dm_p; break; case ROMS_DN_P: p = &o.dn_p; break;
     case ROMS_PMON_U: p = &o.pmon_u; break; case ROMS_PNOM_V: p = &o.pnom_v; break;
     case ROMS_VISC2_R: p = &o.visc2_r; break; case ROMS_VISC2_P: p = &o.visc2_p; break; case ROMS_DIFF2: p = &o.diff2[itrc - 1]; break;
+    case ROMS_RIV_UFLX: p = &o.riv_uflx; break; case ROMS_RIV_VFLX: p = &o.riv_vflx; break;
     default: break;
   }
   if (count) *count = n;
@@ -1836,6 +1904,7 @@ int orc_create(const roms_cfg* cfg, void** out) {
                  &o->visc2_p})
     a->assign(n2, 0.0);
   for (int l = 0; l < 4; ++l) { o->zeta[l].assign(n2, 0.0); o->ubar[l].assign(n2, 0.0); o->vbar[l].assign(n2, 0.0); }
+  o->riv_uflx.assign(n2, 0.0); o->riv_vflx.assign(n2, 0.0);
   o->stflx.assign(o->NT, vec(n2, 0.0));
   o->diff2.assign(o->NT, vec(n2, 0.0));
   for (int l = 0; l < 3; ++l) {
@@ -1883,6 +1952,16 @@ int orc_grid_stats(void* h, double out[9]) {
         ccor = std::max(ccor, cff);
       }
   out[0] = hmin; out[1] = hmax; out[2] = gmin; out[3] = gmax; out[4] = cmin; out[5] = cmax; out[6] = ccor; out[7] = o.area; out[8] = o.volume;
+  return 0;
+}
+// set_river_frc (river_frc.F): volume flux and tracer values of river `iriver` (1-based) for the coming steps
+int orc_set_river(void* h, int iriver, double vol, const double* trc) {
+  Orc& o = *(Orc*)h;
+  if (iriver < 1 || iriver > 8) return -1;
+  if ((int)o.riv_vol.size() < iriver) { o.riv_vol.resize(iriver, 0.0); o.riv_trc.resize(iriver, vec(o.NT, 0.0)); }
+  o.riv_vol[iriver - 1] = vol;
+  for (int it = 0; it < o.NT; ++it) o.riv_trc[iriver - 1][it] = trc[it];
+  o.river_source = true;
   return 0;
 }
 int orc_get_nfast(void* h) { return ((Orc*)h)->nfast; }

@@ -16,10 +16,12 @@ from romsb200 import Roms  # noqa: E402
 def main():
     nsteps = int(sys.argv[1]) if len(sys.argv) > 1 else 3
     mode = sys.argv[2] if len(sys.argv) > 2 else "periodic"
-    walls = mode in ("walls", "seamount", "closed", "closedmix", "unevenclosed")
+    walls = mode in ("walls", "seamount", "closed", "closedmix", "unevenclosed", "river")
     topo = mode in ("seamount", "closed", "closedmix", "unevenclosed")           # + bottom topography and a land mask
-    ew = mode in ("closed", "closedmix", "unevenclosed")                         # closed basin: walls on all four sides
+    ew = mode in ("closed", "closedmix", "unevenclosed", "river")                # closed basin: walls on all four sides
     mix = dict(visc2=100.0, tnu2=50.0, sponge=True) if mode == "closedmix" else {}   # + visc3d / t3dmix
+    if mode == "river":                                                              # + a river source whose faces straddle the block boundary
+        mix = dict(river=True, dt=60.0)
     rank, world, local = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"]), int(os.environ["LOCAL_RANK"])
     torch.cuda.set_device(local)
     dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local}"))

@@ -80,7 +80,8 @@ def test_rivers_ana_startup_on_gpu():
 
 @pytest.mark.parametrize("case", ["channel", "filament", "channel_linear_odd", "channel_walls", "channel_walls_linear_odd",
                                   "seamount_island_walls", "seamount_island_periodic", "closed_basin", "closed_basin_seamount_odd",
-                                  "ew_walls_ns_periodic", "channel_mixing", "closed_basin_seamount_mixing", "filament_mixing_switches"])
+                                  "ew_walls_ns_periodic", "channel_mixing", "closed_basin_seamount_mixing", "filament_mixing_switches",
+                                  "closed_basin_river", "walled_channel_river_mixing"])
 def test_routine_by_routine(case):
     if case == "channel":
         cfg, st = cases.channel(48, 40, 12)
@@ -105,6 +106,10 @@ def test_routine_by_routine(case):
     elif case == "filament_mixing_switches":                            # tests/Filament/cppdefs.opt:34-35 with visc2 = tnu2 = 0
         cfg, st = cases.filament(64, 64, 32)
         cfg.uv_vis2, cfg.ts_dif2 = 1, 1
+    elif case == "closed_basin_river":                                  # river source through a land strip (Rivers_ana geometry)
+        cfg, st = cases.channel(40, 36, 8, ns_walls=True, ew_walls=True, river=True, dt=60.0)
+    elif case == "walled_channel_river_mixing":                         # E-W periodic, 3 tracers, seamount, lateral mixing + river
+        cfg, st = cases.channel(45, 38, 9, NT=3, ns_walls=True, seamount=True, river=True, dt=60.0, visc2=60.0, tnu2=30.0)
     elif case == "filament":
         cfg, st = cases.filament(64, 64, 32)
     else:
@@ -164,6 +169,38 @@ def test_alfabeta():
     ao = np.empty(o.shape2); bo = np.empty(o.shape2)
     o.call("alfabeta", ao.ctypes.data_as(C.POINTER(C.c_double)), bo.ctypes.data_as(C.POINTER(C.c_double)))
     assert parity_walk.rel(a, ao) < 1e-14 and parity_walk.rel(b, bo) < 1e-14
+    g.close(); o.close()
+
+
+def test_river_source_budgets_and_100_steps():
+    """River sources (river_frc.F; hooks step2d_FB.F:531-554, pre_step3d4S.F:493-522, step3d_uv2.F:689-717,
+    compute_horiz_tracer_fluxes.h:217-246): no golden log of the reference pins them without KPP, so besides GPU-vs-oracle
+    parity the volume, heat and salt budgets must close: per baroclinic step the basin gains riv_vol*dt of water and
+    riv_vol*dt*riv_trc of each tracer."""
+    cfg, st = cases.channel(40, 36, 8, ns_walls=True, ew_walls=True, river=True, dt=60.0)
+    g, o = Roms(cfg), Oracle(cfg)
+    cases.initialize(g, st); cases.initialize(o, st)
+    vol, trc = st["RIVERS"][0]
+    rm = st["RMASK"][2:-2, 2:-2]
+    dA = 1.0e6
+
+    def budget(m):
+        iic, iif, nstp, nrhs, nnew, kstp, knew = m.get_idx()
+        Hz = m.pull("HZ")[:, 2:-2, 2:-2]
+        return np.array([(m.pull("ZETA", knew)[2:-2, 2:-2] * rm).sum() * dA] +
+                        [(Hz * m.pull("T", nnew, it)[:, 2:-2, 2:-2] * rm).sum() * dA for it in (1, 2)])
+    g.call("step"); o.call("step")
+    compare(g, o, cfg.NT, TOL1, cfg)
+    b0 = budget(g)
+    for n in range(3):
+        g.call("step"); o.call("step")
+        b = budget(g)
+        gain = (b - b0) / (vol * cfg.dt * np.array([1.0, trc[0], trc[1]]))
+        assert np.all(np.abs(gain - 1.0) < 1e-6), gain
+        b0 = b
+    g.call("run", 96); o.call("run", 96)
+    r100 = compare(g, o, cfg.NT, TOL100, cfg)
+    print("river case, 100 steps:", r100)
     g.close(); o.close()
 
 
@@ -232,7 +269,7 @@ def test_two_gpu_halo_exchange_parity():
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
                         "--master-port", "29735", script, "3", "closedmix"], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
-    for port, mode in ((29736, "uneven"), (29737, "unevenclosed")):      # blocks of unequal size (mpi_setup.F:117-160)
+    for port, mode in ((29736, "uneven"), (29737, "unevenclosed"), (29738, "river")):      # blocks of unequal size (mpi_setup.F:117-160); river source
         r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
                             "--master-port", str(port), script, "3", mode], capture_output=True, text=True, timeout=600)
         assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]

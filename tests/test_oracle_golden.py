@@ -132,3 +132,30 @@ def test_rivers_ana_startup_golden():
     # land mask of the case: 840 land cells (two all-land rows + 8 rows with a 20-cell river channel)
     assert int((st["RMASK"][2:-2, 2:-2] == 0).sum()) == 840
     o.close()
+
+
+def test_river_source_budgets_oracle():
+    """River sources in the oracle (no reference log pins them without KPP): the volume, heat and salt budgets of a closed basin
+    with one river must close to round-off of the diagnostics: +riv_vol*dt and +riv_vol*dt*riv_trc per baroclinic step."""
+    cfg, st = cases.channel(40, 36, 8, ns_walls=True, ew_walls=True, river=True, dt=60.0)
+    o = Oracle(cfg)
+    cases.initialize(o, st)
+    vol, trc = st["RIVERS"][0]
+    rm = st["RMASK"][2:-2, 2:-2]
+    assert int((st["RIV_VFLX"] != 0).sum()) == 8 and not (st["RIV_UFLX"] != 0).any()
+    assert abs(sum(c - 10 for c in st["RIV_VFLX"][st["RIV_VFLX"] != 0]) - 1.0) < 1e-12      # the faces carry the whole river
+
+    def budget():
+        iic, iif, nstp, nrhs, nnew, kstp, knew = o.get_idx()
+        Hz = o.pull("HZ")[:, 2:-2, 2:-2]
+        return np.array([(o.pull("ZETA", knew)[2:-2, 2:-2] * rm).sum() * 1.0e6] +
+                        [(Hz * o.pull("T", nnew, it)[:, 2:-2, 2:-2] * rm).sum() * 1.0e6 for it in (1, 2)])
+    o.call("step")
+    b0 = budget()
+    for n in range(3):
+        o.call("step")
+        b = budget()
+        gain = (b - b0) / (vol * cfg.dt * np.array([1.0, trc[0], trc[1]]))
+        assert np.all(np.abs(gain - 1.0) < 1e-6), gain
+        b0 = b
+    o.close()

@@ -697,9 +697,9 @@ __device__ __forceinline__ TMask tmask_load(const KP& p, ix_t c) {
   return m;
 }
 template <bool UP, bool NEAR>
-__device__ __forceinline__ double tdiv(const KP& p, const double* __restrict__ t, ix_t c, int i, int j, int k, const TMask& m) {
+__device__ __forceinline__ void tflux4(const KP& p, const double* __restrict__ t, ix_t c, int i, int j, int k, const TMask& m, double& FXi, double& FXip, double& FEj,
+                                       double& FEjp) {
   const ix_t SX = p.SX;
-  double FXi, FXip, FEj, FEjp;
   if (NEAR) {   // first differences in i exist on columns istr..iend+1 between walls (compute_horiz_tracer_fluxes.h:50-84)
     FXi = tflux_cl<UP>(p, t, p.FlxU, p.umask, c, 1, k, iclamp(p, i - 1, p.istr, p.iend + 1), iclamp(p, i, p.istr, p.iend + 1), iclamp(p, i + 1, p.istr, p.iend + 1));
     FXip = tflux_cl<UP>(p, t, p.FlxU, p.umask, c + 1, 1, k, iclamp(p, i, p.istr, p.iend + 1), iclamp(p, i + 1, p.istr, p.iend + 1),
@@ -716,21 +716,63 @@ __device__ __forceinline__ double tdiv(const KP& p, const double* __restrict__ t
     FEj = tflux<UP>(t, p.FlxV, p, c, SX, k, m.v0, m.v1, m.v2);
     FEjp = tflux<UP>(t, p.FlxV, p, c + SX, SX, k, m.v1, m.v2, m.v3);
   }
+}
+template <bool UP, bool NEAR>
+__device__ __forceinline__ double tdiv(const KP& p, const double* __restrict__ t, ix_t c, int i, int j, int k, const TMask& m) {
+  double FXi, FXip, FEj, FEjp;
+  tflux4<UP, NEAR>(p, t, c, i, j, k, m, FXi, FXip, FEj, FEjp);
   return FXip - FXi + FEjp - FEj;
 }
-template <bool WALL, int KB>
+// compute_horiz_tracer_fluxes.h:217-246: the flux through a river face is the river's tracer value times its volume flux,
+// spread over the column in proportion to the layer thickness.  d = 1: u-face (i,j), d = SX: v-face.
+__device__ __forceinline__ bool riv_on(double code) { return fabs(code) > 1e-3; }
+__device__ __forceinline__ double riv_speed(const KP& p, double code, ix_t c, ix_t d, int& iriver) {   // vol*fraction/riv_depth
+  const double riv_depth = 0.5 * (RW(p.z_w, c - d, p.N) - RW(p.z_w, c - d, 0) + RW(p.z_w, c, p.N) - RW(p.z_w, c, 0));
+  iriver = (int)lround(code / 10);
+  return p.riv_tab[(iriver - 1) * RIVROW] * (code - 10 * iriver) / riv_depth;
+}
+__device__ __forceinline__ double riv_tflux(const KP& p, double code, ix_t c, ix_t d, int k, int itrc) {
+  int iriver;
+  const double vel = riv_speed(p, code, c, d, iriver);
+  return p.riv_tab[(iriver - 1) * RIVROW + itrc] * 0.5 * (R3(p.Hz, c - d, k) + R3(p.Hz, c, k)) * vel;
+}
+struct RivFaces { double u0, u1, v0, v1; bool any; };   // codes of the four faces of a cell
+__device__ __forceinline__ RivFaces riv_faces(const KP& p, ix_t c) {
+  RivFaces r;
+  r.u0 = p.riv_uflx[c]; r.u1 = p.riv_uflx[c + 1]; r.v0 = p.riv_vflx[c]; r.v1 = p.riv_vflx[c + p.SX];
+  r.any = riv_on(r.u0) | riv_on(r.u1) | riv_on(r.v0) | riv_on(r.v1);
+  return r;
+}
+template <bool UP>
+__device__ __forceinline__ double tdiv_riv(const KP& p, const double* __restrict__ t, ix_t c, int i, int j, int k, const TMask& m, bool near, const RivFaces& r,
+                                           int itrc) {
+  double FXi, FXip, FEj, FEjp;
+  if (near) tflux4<UP, true>(p, t, c, i, j, k, m, FXi, FXip, FEj, FEjp);
+  else tflux4<UP, false>(p, t, c, i, j, k, m, FXi, FXip, FEj, FEjp);
+  if (riv_on(r.u0)) FXi = riv_tflux(p, r.u0, c, 1, k, itrc);
+  if (riv_on(r.u1)) FXip = riv_tflux(p, r.u1, c + 1, 1, k, itrc);
+  if (riv_on(r.v0)) FEj = riv_tflux(p, r.v0, c, p.SX, k, itrc);
+  if (riv_on(r.v1)) FEjp = riv_tflux(p, r.v1, c + p.SX, p.SX, k, itrc);
+  return FXip - FXi + FEjp - FEj;
+}
+template <bool WALL, int KB, bool RIV>
 __global__ void __launch_bounds__(256, LB_TP) k_pre_t_horiz(const __grid_constant__ KP p, const double* __restrict__ t_rhs, double* __restrict__ t_new,
-                                                            const double* __restrict__ t_stp, double* __restrict__ t_indx, double dtau, double cf_stp, double cf_bak) {
+                                                            const double* __restrict__ t_stp, double* __restrict__ t_indx, double dtau, double cf_stp, double cf_bak,
+                                                            int itrc) {
   THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
   const int k0 = blockIdx.z * KB + 1;
   const TMask m = tmask_load(p, c);
   const double cdt = dtau * p.pm[c] * p.pn[c];
   const bool near = WALL && near_wall(p, i, j);
+  RivFaces rf;
+  rf.any = false;
+  if (RIV) rf = riv_faces(p, c);
 #pragma unroll
   for (int q = 0; q < KB; ++q) {
     const int k = k0 + q;
     if (k <= p.N) {
-      const double dv = near ? tdiv<false, true>(p, t_rhs, c, i, j, k, m) : tdiv<false, false>(p, t_rhs, c, i, j, k, m);
+      const double dv = (RIV && rf.any) ? tdiv_riv<false>(p, t_rhs, c, i, j, k, m, near, rf, itrc)
+                                        : (near ? tdiv<false, true>(p, t_rhs, c, i, j, k, m) : tdiv<false, false>(p, t_rhs, c, i, j, k, m));
       const double Hz = R3(p.Hz, c, k), Hz_bak = Hz + R3(p.FlxDiv, c, k);
       const double ts = R3(t_stp, c, k);
       R3(t_new, c, k) = Hz_bak * (cf_stp * ts + cf_bak * R3(t_indx, c, k)) - cdt * (dv);
@@ -738,20 +780,44 @@ __global__ void __launch_bounds__(256, LB_TP) k_pre_t_horiz(const __grid_constan
     }
   }
 }
-template <bool WALL, int KB>
-__global__ void __launch_bounds__(256, LB_TC) k_t_horiz(const __grid_constant__ KP p, const double* __restrict__ t_rhs, double* __restrict__ t_new) {
+template <bool WALL, int KB, bool RIV>
+__global__ void __launch_bounds__(256, LB_TC) k_t_horiz(const __grid_constant__ KP p, const double* __restrict__ t_rhs, double* __restrict__ t_new, int itrc) {
   THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
   const int k0 = blockIdx.z * KB + 1;
   const TMask m = tmask_load(p, c);
   const double cdt = p.dt * p.pm[c] * p.pn[c];
   const bool near = WALL && near_wall(p, i, j);
+  RivFaces rf;
+  rf.any = false;
+  if (RIV) rf = riv_faces(p, c);
 #pragma unroll
   for (int q = 0; q < KB; ++q) {
     const int k = k0 + q;
     if (k <= p.N) {
-      const double dv = near ? tdiv<true, true>(p, t_rhs, c, i, j, k, m) : tdiv<true, false>(p, t_rhs, c, i, j, k, m);
+      const double dv = (RIV && rf.any) ? tdiv_riv<true>(p, t_rhs, c, i, j, k, m, near, rf, itrc)
+                                        : (near ? tdiv<true, true>(p, t_rhs, c, i, j, k, m) : tdiv<true, false>(p, t_rhs, c, i, j, k, m));
       R3(t_new, c, k) = R3(t_new, c, k) - cdt * (dv);
     }
+  }
+}
+
+// pre_step3d4S.F:493-522 / step3d_uv2.F:689-717: the velocity through a river face is the river's, uniform over the column.
+// One thread per (i,j); iu0/jv0 = first u-column / v-row of the reference's loops (istrU,jstrV in pre_step3d; istr,jstr in uv2).
+__global__ void k_river_uv(const __grid_constant__ KP p, double* __restrict__ u, double* __restrict__ v, int iu0, int jv0) {
+  THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
+  const double cu = p.riv_uflx[c], cv = p.riv_vflx[c];
+  int iriver;
+  if (i >= iu0 && riv_on(cu)) {
+    const double riv_depth = 0.5 * (RW(p.z_w, c - 1, p.N) - RW(p.z_w, c - 1, 0) + RW(p.z_w, c, p.N) - RW(p.z_w, c, 0));
+    iriver = (int)lround(cu / 10);
+    const double vel = p.riv_tab[(iriver - 1) * RIVROW] * (cu - 10 * iriver) / (p.dn_u[c] * riv_depth);
+    for (int k = 1; k <= p.N; ++k) R3(u, c, k) = vel;
+  }
+  if (j >= jv0 && riv_on(cv)) {
+    const double riv_depth = 0.5 * (RW(p.z_w, c - SX, p.N) - RW(p.z_w, c - SX, 0) + RW(p.z_w, c, p.N) - RW(p.z_w, c, 0));
+    iriver = (int)lround(cv / 10);
+    const double vel = p.riv_tab[(iriver - 1) * RIVROW] * (cv - 10 * iriver) / (p.dm_v[c] * riv_depth);
+    for (int k = 1; k <= p.N; ++k) R3(v, c, k) = vel;
   }
 }
 
@@ -1220,13 +1286,34 @@ __global__ void __launch_bounds__(S2_TX * S2_TY, LB_S2D) k_step2d(const __grid_c
   if (dou) {
     const double DUnew = ((D0 + Dw) * s.us[c] + cff * (p.pm[c] + p.pm[c - 1]) * (p.pn[c] + p.pn[c - 1]) * (rubar + rufrc)) * p.umask[c];
     un = DUnew / (Dn0 + Dnw);
-    p.DU_avg1[c] = DU1 + cff1 * p.dn_u[c] * (DUnew);
+    double DUa = DU1 + cff1 * p.dn_u[c] * (DUnew);
+    if (p.rivers) {        // step2d_FB.F:531-554: a river face carries the river's volume flux
+      const double code = p.riv_uflx[c];
+      if (riv_on(code)) {
+        const int iriver = (int)lround(code / 10);
+        const double river_flux = p.riv_tab[(iriver - 1) * RIVROW] * (code - 10 * iriver);
+        un = river_flux * 2 / (p.dn_u[c] * (Dnw + Dn0));
+        DUa = river_flux;
+      }
+    }
+    p.DU_avg1[c] = DUa;
   } else if (s.iif == 1) p.DU_avg1[c] = DU1;
   s2d_store(p, s.un, i, j, c, un);
   if (dov) {
     const double DVnew = ((D0 + Ds) * s.vs[c] + cff * (p.pm[c] + p.pm[c - SX]) * (p.pn[c] + p.pn[c - SX]) * (rvbar + rvfrc)) * p.vmask[c];
-    s2d_store(p, s.vn, i, j, c, DVnew / (Dn0 + Dns));
-    p.DV_avg1[c] = DV1 + cff1 * p.dm_v[c] * (DVnew);
+    double vn = DVnew / (Dn0 + Dns);
+    double DVa = DV1 + cff1 * p.dm_v[c] * (DVnew);
+    if (p.rivers) {
+      const double code = p.riv_vflx[c];
+      if (riv_on(code)) {
+        const int iriver = (int)lround(code / 10);
+        const double river_flux = p.riv_tab[(iriver - 1) * RIVROW] * (code - 10 * iriver);
+        vn = river_flux * 2 / (p.dm_v[c] * (Dns + Dn0));
+        DVa = river_flux;
+      }
+    }
+    s2d_store(p, s.vn, i, j, c, vn);
+    p.DV_avg1[c] = DVa;
   } else {   // row jstr on a southern wall: v2dbc (no normal flow) and its DV_avg1 term (step2d_FB.F:449-529)
     const double vn = 0.0;
     s2d_store(p, s.vn, i, j, c, vn);

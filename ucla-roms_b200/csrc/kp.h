@@ -14,6 +14,8 @@ typedef int ix_t;
 
 #define IOFF 15
 #define MAXNT 40
+#define MAXRIV 8
+#define RIVROW (1 + MAXNT)
 
 struct KP {
   int Lm, Mm, N, NT;
@@ -43,6 +45,10 @@ struct KP {
   double *zeta_new;  // step2d_FB.F private zeta_new
   double *Cs_w, *Cs_r;   // scoord.F:38 (k=0:N, k=1:N at index k)
   int use_smem;      // column scratch in shared memory ([k][thread]) instead of global
+  // river_frc.F: river faces (10*iriver + fraction of the river's volume flux), per-river table [iriver-1][0]=volume flux,
+  // [iriver-1][1+itrc]=tracer value; rivers = river_source
+  double *riv_uflx, *riv_vflx, *riv_tab;
+  int rivers;
 };
 
 // column base index of (i,j) and relative addressing

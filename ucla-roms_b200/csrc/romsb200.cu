@@ -271,7 +271,7 @@ int roms_create(const roms_cfg* cfg, int device, roms_ctx** out) {
   const size_t scratch_planes = (size_t)3 * N            /* FlxDiv, P, rho */
                                 + (h->use_smem ? 0 : (size_t)2 * (N + 1)) /* column scratch fallback */
                                 + 1 /* zeta_new */ + 2 /* ub, vb */ + 5 /* diag planes */;
-  const size_t small = 2 * (size_t)(N + 1) + 64;
+  const size_t small = 2 * (size_t)(N + 1) + 64 + (size_t)MAXRIV * RIVROW;
   h->arena_doubles = (planes + scratch_planes) * (size_t)p.SXY + small;
   CK(cudaMalloc(&h->arena, h->arena_doubles * sizeof(double)));
   CK(cudaMemset(h->arena, 0, h->arena_doubles * sizeof(double)));   // init=0 (init_scalars.F:31)
@@ -286,6 +286,8 @@ int roms_create(const roms_cfg* cfg, int device, roms_ctx** out) {
   for (int q = 0; q < 5; ++q) h->d_o[q] = take(1);
   p.Cs_w = cur; cur += (N + 1);
   p.Cs_r = cur; cur += (N + 1);
+  p.riv_tab = cur; cur += (size_t)MAXRIV * RIVROW;
+  p.rivers = 0;
 #define P1(name, id) p.name = h->f[id].ptr[0]
   P1(h, ROMS_H); P1(pm, ROMS_PM); P1(pn, ROMS_PN); P1(f, ROMS_F); P1(rmask, ROMS_RMASK); P1(umask, ROMS_UMASK); P1(vmask, ROMS_VMASK);
   P1(dm_u, ROMS_DM_U); P1(dn_u, ROMS_DN_U); P1(dm_v, ROMS_DM_V); P1(dn_v, ROMS_DN_V); P1(dm_r, ROMS_DM_R); P1(dn_r, ROMS_DN_R);
@@ -296,6 +298,7 @@ int roms_create(const roms_cfg* cfg, int device, roms_ctx** out) {
   P1(Wi, ROMS_WI); P1(rho1, ROMS_RHO1); P1(qp1, ROMS_QP1); P1(Akv, ROMS_AKV); P1(ru, ROMS_RU); P1(rv, ROMS_RV);
   P1(pmask, ROMS_PMASK); P1(dm_p, ROMS_DM_P); P1(dn_p, ROMS_DN_P); P1(pmon_u, ROMS_PMON_U); P1(pnom_v, ROMS_PNOM_V);
   P1(visc2_r, ROMS_VISC2_R); P1(visc2_p, ROMS_VISC2_P);
+  P1(riv_uflx, ROMS_RIV_UFLX); P1(riv_vflx, ROMS_RIV_VFLX);
 #undef P1
   p.Akt[0] = h->f[ROMS_AKT].ptr[0]; p.Akt[1] = h->f[ROMS_AKT].ptr[1];
   host_scoord(h);
@@ -603,8 +606,9 @@ int roms_pre_step3d(roms_ctx* h, int tile) {
   const bool wl = WALLED(h);
   PLANE(k_pre_flxdiv, p.iend, p.jstrV - 1, p.jend, p.N, p, dtau);
   for (int it = 1; it <= h->c.NT; ++it) {
-    if (wl) PLANE((k_pre_t_horiz<true, KB_T>), p.iend, p.jstr, p.jend, (p.N + KB_T - 1) / KB_T, p, h->t(nrhs, it), h->t(nnew, it), h->t(nstp, it), h->t(indx, it), dtau, cf_stp, cf_bak);
-    else PLANE((k_pre_t_horiz<false, KB_T>), p.iend, p.jstr, p.jend, (p.N + KB_T - 1) / KB_T, p, h->t(nrhs, it), h->t(nnew, it), h->t(nstp, it), h->t(indx, it), dtau, cf_stp, cf_bak);
+    if (p.rivers) PLANE((k_pre_t_horiz<true, KB_T, true>), p.iend, p.jstr, p.jend, (p.N + KB_T - 1) / KB_T, p, h->t(nrhs, it), h->t(nnew, it), h->t(nstp, it), h->t(indx, it), dtau, cf_stp, cf_bak, it);
+    else if (wl) PLANE((k_pre_t_horiz<true, KB_T, false>), p.iend, p.jstr, p.jend, (p.N + KB_T - 1) / KB_T, p, h->t(nrhs, it), h->t(nnew, it), h->t(nstp, it), h->t(indx, it), dtau, cf_stp, cf_bak, it);
+    else PLANE((k_pre_t_horiz<false, KB_T, false>), p.iend, p.jstr, p.jend, (p.N + KB_T - 1) / KB_T, p, h->t(nrhs, it), h->t(nnew, it), h->t(nstp, it), h->t(indx, it), dtau, cf_stp, cf_bak, it);
   }
   if (wl) PLANE_JB((k_rhs_uv_horiz<false, true, 4>), 4, p.iend, p.jstr, p.jend, p.N, p, h->u(nrhs), h->v(nrhs));
   else PLANE_JB((k_rhs_uv_horiz<false, false, 4>), 4, p.iend, p.jstr, p.jend, p.N, p, h->u(nrhs), h->v(nrhs));
@@ -613,6 +617,7 @@ int roms_pre_step3d(roms_ctx* h, int tile) {
     COLUMN(k_t_vert<0>, 2, p.iend, p.jstr, p.jend, p, h->t(nrhs, it), h->t(nnew, it), p.Akt[it >= 2 ? 1 : 0], (const double*)nullptr, dtau, 0);
   COLUMN((k_uv_vert<0, 0>), 2, p.iend, p.jstr, p.jend, p, h->u(nrhs), h->u(nnew), h->u(nstp), h->u(indx), dtau, cf_stp, cf_bak);
   COLUMN((k_uv_vert<0, 1>), 2, p.iend, p.jstrV, p.jend, p, h->v(nrhs), h->v(nnew), h->v(nstp), h->v(indx), dtau, cf_stp, cf_bak);
+  if (p.rivers) PLANE(k_river_uv, p.iend, p.jstr, p.jend, 1, p, h->u(nnew), h->v(nnew), p.istrU, p.jstrV);   // pre_step3d4S.F:493-522
   // u3dbc/v3dbc/t3dbc (pre_step3d4S.F:533-545), then one exchange per tracer (:548)
   bc3d(h, h->u(nnew), p.N, BC_U);
   bc3d(h, h->v(nnew), p.N, BC_V);
@@ -697,6 +702,7 @@ int roms_step3d_uv2(roms_ctx* h, int tile) {
     COLUMN(k_uv2_pass1<0>, 0, p.iendR, p.jstrR, p.jendR, p, h->u(nnew), h->u(nstp), h->ubar(knew));
     COLUMN(k_uv2_pass1<1>, 0, p.iendR, p.jstr, p.jendR, p, h->v(nnew), h->v(nstp), h->vbar(knew));
   }
+  if (p.rivers) PLANE(k_river_uv, p.iend, p.jstr, p.jend, 1, p, h->u(nnew), h->v(nnew), p.istr, p.jstr);   // step3d_uv2.F:689-717
   int rc = exchange(h, {{p.FlxU, p.N}, {h->u(nnew), p.N}, {h->ubar(knew), 1}});
   if (rc) return rc;
   return exchange(h, {{p.FlxV, p.N}, {h->v(nnew), p.N}, {h->vbar(knew), 1}});
@@ -707,8 +713,9 @@ int roms_step3d_t(roms_ctx* h, int tile) {
   const KP& p = h->kp;
   const int nrhs = h->nrhs, nnew = h->nnew, NT = h->c.NT;
   for (int it = 1; it <= NT; ++it) {
-    if (WALLED(h)) PLANE((k_t_horiz<true, KB_T>), p.iend, p.jstr, p.jend, (p.N + KB_T - 1) / KB_T, p, h->t(nrhs, it), h->t(nnew, it));
-    else PLANE((k_t_horiz<false, KB_T>), p.iend, p.jstr, p.jend, (p.N + KB_T - 1) / KB_T, p, h->t(nrhs, it), h->t(nnew, it));
+    if (p.rivers) PLANE((k_t_horiz<true, KB_T, true>), p.iend, p.jstr, p.jend, (p.N + KB_T - 1) / KB_T, p, h->t(nrhs, it), h->t(nnew, it), it);
+    else if (WALLED(h)) PLANE((k_t_horiz<true, KB_T, false>), p.iend, p.jstr, p.jend, (p.N + KB_T - 1) / KB_T, p, h->t(nrhs, it), h->t(nnew, it), it);
+    else PLANE((k_t_horiz<false, KB_T, false>), p.iend, p.jstr, p.jend, (p.N + KB_T - 1) / KB_T, p, h->t(nrhs, it), h->t(nnew, it), it);
     COLUMN(k_t_vert<1>, 2, p.iend, p.jstr, p.jend, p, h->t(nrhs, it), h->t(nnew, it), p.Akt[it >= 2 ? 1 : 0], h->f[ROMS_STFLX].ptr[it - 1], h->c.dt,
            it == 1 ? 1 : 0);
   }
@@ -759,6 +766,18 @@ int roms_alfabeta(roms_ctx* h, double* alpha_host, double* beta_host) {
 static double pairsum(const double* a, size_t n) {
   if (n <= 8) { double s = 0; for (size_t i = 0; i < n; ++i) s += a[i]; return s; }
   return pairsum(a, n / 2) + pairsum(a + n / 2, n - n / 2);
+}
+// river_frc.F set_river_frc: volume flux and tracer values of one river; the table lives next to the fields in the arena
+int roms_set_river(roms_ctx* h, int iriver, double vol, const double* trc) {
+  CK(cudaSetDevice(h->device));
+  if (iriver < 1 || iriver > MAXRIV || !trc) { g_err = "roms_set_river: river index out of range (1..8)"; return -1; }
+  double row[RIVROW] = {0.0};
+  row[0] = vol;
+  for (int it = 0; it < h->c.NT; ++it) row[1 + it] = trc[it];
+  CK(cudaMemcpyAsync(h->kp.riv_tab + (size_t)(iriver - 1) * RIVROW, row, sizeof(row), cudaMemcpyHostToDevice, h->st));
+  CK(cudaStreamSynchronize(h->st));
+  h->kp.rivers = 1;
+  return 0;
 }
 // setup_grid2.F:64-100 for this subdomain (the reference prints the global values once at start-up): extrema over the water
 // points of the rho-range incl. boundary rows on a physical edge, unmasked area and volume.  A one-off start-up report

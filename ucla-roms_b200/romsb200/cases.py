@@ -59,6 +59,26 @@ def block_extent(LL, np_, node):
     return L, (0 if node == 0 else node * L0 - off // 2)
 
 
+def river_faces(rmask, ridx, rfrc):
+    """river_frc.F:228-277 calc_river_flux: a river cell (a masked cell with index ridx and fraction rfrc of its river's
+    volume flux) feeds every unmasked neighbour through the face between them; faces are coded 10*iriver +- fraction/faces,
+    the sign being the direction of the flow along the axis."""
+    ru = np.zeros_like(rmask); rv = np.zeros_like(rmask)
+    for j, i in zip(*np.nonzero(rfrc[1:-1, 1:-1] > 0)):
+        j += 1; i += 1
+        faces = rmask[j, i - 1] + rmask[j, i + 1] + rmask[j - 1, i] + rmask[j + 1, i]
+        assert faces > 0 and rmask[j, i] == 0, "river grid position error"
+        if rmask[j, i - 1] > 0:
+            ru[j, i] = -rfrc[j, i] / faces + 10 * ridx[j, i]
+        if rmask[j, i + 1] > 0:
+            ru[j, i + 1] = rfrc[j, i] / faces + 10 * ridx[j, i]
+        if rmask[j - 1, i] > 0:
+            rv[j, i] = -rfrc[j, i] / faces + 10 * ridx[j, i]
+        if rmask[j + 1, i] > 0:
+            rv[j + 1, i] = rfrc[j, i] / faces + 10 * ridx[j, i]
+    return ru, rv
+
+
 def _noise(ig, jg, k, salt):
     """deterministic pseudo-random field in [-1,1) as a function of GLOBAL indices (so that every rank of a
     decomposed run generates exactly the values a single-domain run has)"""
@@ -72,7 +92,7 @@ def _noise(ig, jg, k, salt):
 
 def channel(Lm=64, Mm=64, N=16, NT=2, ns_walls=False, nonlin_eos=True, dt=120.0, ndtfast=60, dx=1.0e3, dy=1.0e3,
             depth=4000.0, seed=20260101, perturb=1e-6, amp=None, sub=(0, 0, 1, 1), seamount=False, island=False, ew_walls=False,
-            visc2=None, tnu2=None, sponge=False, ishift=0):
+            visc2=None, tnu2=None, sponge=False, ishift=0, river=False):
     """Lm, Mm are the GLOBAL interior sizes; sub=(inode, jnode, np_xi, np_eta) selects this rank's block
     (mpi_setup.F:61-70; uneven splits as mpi_setup.F:117-160, see block_extent).  Returns the cfg and state of that block.
     seamount: Gaussian seamount h = depth*(1 - 0.5*exp(-r^2/(L/5)^2)) (SURVEY.md 8(d) input (3), form of
@@ -82,6 +102,10 @@ def channel(Lm=64, Mm=64, N=16, NT=2, ns_walls=False, nonlin_eos=True, dt=120.0,
     visc2 / tnu2 [m2/s]: switch on UV_VIS2 / TS_DIF2 lateral mixing (visc3d_S.F, t3dmix_S.F) with these background
     coefficients; sponge: add a smooth spatially varying part to visc2_r, visc2_p, diff2 (what set_nudgcof.F:88-110 does
     near open boundaries) so that the coefficient averaging of the flux formulas is exercised.
+    river: the southern tenth of the domain becomes land cut by a river channel over the middle fifth in xi, the southernmost
+    2 % is all land (the geometry of tests/Rivers_ana/ana_grid.h); the land cells at the head of the channel are the river cells of
+    river 1 (river_frc.F:125-137), its faces are coded by `river_faces` and its volume flux and tracer values are those of
+    tests/Rivers_ana/ana_frc_river.h scaled to the cell size, with a milder T,S contrast (state key "RIVERS").
     ishift: translate the whole E-W periodic problem by this many cells in xi (the state is the roll of the unshifted one, so
     the solution must be the roll of the unshifted solution, bit for bit -- a size-independent parity property)."""
     inode, jnode, np_xi, np_eta = sub
@@ -117,6 +141,9 @@ def channel(Lm=64, Mm=64, N=16, NT=2, ns_walls=False, nonlin_eos=True, dt=120.0,
     rmask = np.ones((sy, sx))
     if island:
         rmask[(x - 0.72 * Lx) ** 2 + (y - 0.70 * Ly) ** 2 < (0.09 * min(Lx, Ly)) ** 2] = 0.0
+    if river:
+        rmask[(y < 0.1 * Ly) & ((x < 0.4 * Lx) | (x > 0.6 * Lx))] = 0.0
+        rmask[y < 0.02 * Ly + 0.75 * dy] = 0.0
     zeta = 0.01 * np.sin(2 * np.pi * x / Lx) * np.cos(2 * np.pi * y / Ly)
     z_r, z_w = _depths(h, zeta, N, cfg.theta_s, cfg.theta_b, cfg.hc)
     Hz = z_w[1:] - z_w[:-1]
@@ -138,7 +165,7 @@ def channel(Lm=64, Mm=64, N=16, NT=2, ns_walls=False, nonlin_eos=True, dt=120.0,
     if ew_walls:
         il = (np.arange(-2, Lm + 4) + i0)
         u[:, :, (il <= 1) | (il >= LmG + 1)] = 0.0     # closed west (i=1) and east (i=Lm+1) walls
-    if island:
+    if island or river:
         um = np.ones_like(rmask); vm = np.ones_like(rmask)
         um[:, 1:] = rmask[:, 1:] * rmask[:, :-1]; vm[1:, :] = rmask[1:, :] * rmask[:-1, :]
         u = u * um[None]; v = v * vm[None]; zeta = zeta * rmask
@@ -165,6 +192,15 @@ def channel(Lm=64, Mm=64, N=16, NT=2, ns_walls=False, nonlin_eos=True, dt=120.0,
     akv = np.full((N + 1, Mm + 4, Lm + 4), 1.0e-4)
     st["AKV"] = akv
     st["AKT"] = {(1, 1): akv, (1, 2): akv}
+    if river:
+        ridx = np.zeros_like(rmask); rfrc = np.zeros_like(rmask)
+        head = np.zeros_like(rmask, dtype=bool)
+        head[:-1, :] = (rmask[:-1, :] == 0) & (rmask[1:, :] == 1) & (x[:-1, :] > 0.4 * Lx) & (x[:-1, :] < 0.6 * Lx)
+        ncell = int(round(0.2 * LmG))
+        ridx[head] = 1.0; rfrc[head] = 1.0 / ncell
+        ru, rv = river_faces(rmask, ridx, rfrc)
+        st["RIV_UFLX"] = t2(ru); st["RIV_VFLX"] = t2(rv)
+        st["RIVERS"] = [(5.0e2 * dx * dy / 1.0e4, [15.0, 34.5] + [0.5] * (NT - 2))]   # Rivers_ana volume flux per unit area; mild T,S contrast (deep basin)
     if sponge:
         wr = 0.5 + 0.5 * np.cos(2 * np.pi * x / Lx) * np.sin(2 * np.pi * y / Ly)          # at rho points, 3-cell halo
         wp = np.zeros_like(wr)
@@ -253,5 +289,7 @@ def initialize(model, state):
     grid = {k: state[k] for k in ("H", "PM", "PN", "F", "RMASK")}
     model.push_state(grid)
     model.call("setup_grid")
-    model.push_state({k: v for k, v in state.items() if k not in grid})
+    model.push_state({k: v for k, v in state.items() if k not in grid and k != "RIVERS"})
+    for n, (vol, trc) in enumerate(state.get("RIVERS", []), 1):
+        model.set_river(n, vol, trc)
     model.call("init_step0")
