@@ -57,6 +57,11 @@ struct Orc {
   std::vector<double> riv_vol;
   std::vector<vec> riv_trc;
   bool river_source = false;
+  // pipe_frc.F: pipe cells (pipe_idx > 0), their volume flux pipe_flx = fraction * pipe_vol [m3/s], per-pipe vertical release
+  // profile pipe_prf(1:N) and tracer values
+  vec pipe_idx, pipe_flx;
+  std::vector<vec> pipe_prf, pipe_trc;
+  bool pipe_source = false;
   vec xr;  // only for the Filament analytic initial condition
   std::vector<vec> s2d;
 };
@@ -388,6 +393,8 @@ void omega(Orc& o) {
       for (int k = 1; k <= N; ++k)
         for (int i = istr; i <= iend; ++i) {
           AW(o.Wi, i, j, k) = AW(o.Wi, i, j, k - 1) - A3(o.FlxU, i + 1, j, k) + A3(o.FlxU, i, j, k) - A3(o.FlxV, i, j + 1, k) + A3(o.FlxV, i, j, k);
+          if (o.pipe_source && A2(o.pipe_idx, i, j) > 0)   // omega.F:102-108
+            AW(o.Wi, i, j, k) = AW(o.Wi, i, j, k) + A2(o.pipe_flx, i, j) * o.pipe_prf[(int)A2(o.pipe_idx, i, j) - 1][k - 1];
           SL(CX, i, k) = std::max(A3(o.FlxU, i + 1, j, k), 0.0) - std::min(A3(o.FlxU, i, j, k), 0.0) +
                          std::max(A3(o.FlxV, i, j + 1, k), 0.0) - std::min(A3(o.FlxV, i, j, k), 0.0);
         }
@@ -1249,6 +1256,8 @@ void step2d(Orc& o) {
     for (int i = istrU - 1; i <= iend; ++i) {
       A2(zeta_new, i, j) = A2(zs, i, j) + dtfast * A2(o.pm, i, j) * A2(o.pn, i, j) * (A2(DUon, i, j) - A2(DUon, i + 1, j) + A2(DVom, i, j) - A2(DVom, i, j + 1)) +
                            dtfast * A2(o.swflx, i, j);
+      if (o.pipe_source && A2(o.pipe_idx, i, j) > 0.)   // step2d_FB.F:155-159
+        A2(zeta_new, i, j) = A2(zeta_new, i, j) + dtfast * A2(o.pm, i, j) * A2(o.pn, i, j) * A2(o.pipe_flx, i, j);
       A2(zeta_new, i, j) = A2(zeta_new, i, j) * A2(o.rmask, i, j);
       A2(Dnew, i, j) = A2(zeta_new, i, j) + A2(o.h, i, j);
       A2(UFx, i, j) = bkw_new * A2(zeta_new, i, j) + bkw * A2(zs, i, j) + bkw1 * A2(zb, i, j) + bkw2 * A2(zo, i, j);
@@ -1501,7 +1510,13 @@ void step3d_t(Orc& o) {
       for (int j = jstr; j <= jend; ++j) {
         vert_tracer_flux(o, j, tr, FC, CF);
         for (int k = 1; k <= N; ++k)
-          for (int i = istr; i <= iend; ++i) A3(tn, i, j, k) = A3(tn, i, j, k) - dt * A2(o.pm, i, j) * A2(o.pn, i, j) * (SL(FC, i, k) - SL(FC, i, k - 1));
+          for (int i = istr; i <= iend; ++i) {
+            A3(tn, i, j, k) = A3(tn, i, j, k) - dt * A2(o.pm, i, j) * A2(o.pn, i, j) * (SL(FC, i, k) - SL(FC, i, k - 1));
+            if (o.pipe_source && A2(o.pipe_idx, i, j) > 0.) {   // step3d_t_ISO.F:927-935
+              const int pidx = (int)A2(o.pipe_idx, i, j);
+              A3(tn, i, j, k) = A3(tn, i, j, k) + dt * A2(o.pm, i, j) * A2(o.pn, i, j) * A2(o.pipe_flx, i, j) * o.pipe_prf[pidx - 1][k - 1] * o.pipe_trc[pidx - 1][itrc];
+            }
+          }
         if (itrc == 0)
           for (int i = istr; i <= iend; ++i) A3(tn, i, j, N) = A3(tn, i, j, N) + dt * A2(o.swflx, i, j) * A3(tn, i, j, N) / A3(o.Hz, i, j, N);
         for (int i = istr; i <= iend; ++i) A3(tn, i, j, N) = A3(tn, i, j, N) + dt * A2(o.stflx[itrc], i, j);
@@ -1881,6 +1896,7 @@ vec* field_ptr(Orc& o, int field, int lvl, int itrc, long* count) {
     case ROMS_PMON_U: p = &o.pmon_u; break; case ROMS_PNOM_V: p = &o.pnom_v; break;
     case ROMS_VISC2_R: p = &o.visc2_r; break; case ROMS_VISC2_P: p = &o.visc2_p; break; case ROMS_DIFF2: p = &o.diff2[itrc - 1]; break;
     case ROMS_RIV_UFLX: p = &o.riv_uflx; break; case ROMS_RIV_VFLX: p = &o.riv_vflx; break;
+    case ROMS_PIPE_IDX: p = &o.pipe_idx; break; case ROMS_PIPE_FLX: p = &o.pipe_flx; break;
     default: break;
   }
   if (count) *count = n;
@@ -1905,6 +1921,7 @@ int orc_create(const roms_cfg* cfg, void** out) {
     a->assign(n2, 0.0);
   for (int l = 0; l < 4; ++l) { o->zeta[l].assign(n2, 0.0); o->ubar[l].assign(n2, 0.0); o->vbar[l].assign(n2, 0.0); }
   o->riv_uflx.assign(n2, 0.0); o->riv_vflx.assign(n2, 0.0);
+  o->pipe_idx.assign(n2, 0.0); o->pipe_flx.assign(n2, 0.0);
   o->stflx.assign(o->NT, vec(n2, 0.0));
   o->diff2.assign(o->NT, vec(n2, 0.0));
   for (int l = 0; l < 3; ++l) {
@@ -1962,6 +1979,16 @@ int orc_set_river(void* h, int iriver, double vol, const double* trc) {
   o.riv_vol[iriver - 1] = vol;
   for (int it = 0; it < o.NT; ++it) o.riv_trc[iriver - 1][it] = trc[it];
   o.river_source = true;
+  return 0;
+}
+// set_pipe_frc / init_arrays_pipes (pipe_frc.F): release profile over the N levels and tracer values of pipe `ipipe` (1-based)
+int orc_set_pipe(void* h, int ipipe, const double* prf, const double* trc) {
+  Orc& o = *(Orc*)h;
+  if (ipipe < 1 || ipipe > 8) return -1;
+  if ((int)o.pipe_prf.size() < ipipe) { o.pipe_prf.resize(ipipe, vec(o.N, 0.0)); o.pipe_trc.resize(ipipe, vec(o.NT, 0.0)); }
+  for (int k = 0; k < o.N; ++k) o.pipe_prf[ipipe - 1][k] = prf[k];
+  for (int it = 0; it < o.NT; ++it) o.pipe_trc[ipipe - 1][it] = trc[it];
+  o.pipe_source = true;
   return 0;
 }
 int orc_get_nfast(void* h) { return ((Orc*)h)->nfast; }

@@ -81,7 +81,7 @@ def test_rivers_ana_startup_on_gpu():
 @pytest.mark.parametrize("case", ["channel", "filament", "channel_linear_odd", "channel_walls", "channel_walls_linear_odd",
                                   "seamount_island_walls", "seamount_island_periodic", "closed_basin", "closed_basin_seamount_odd",
                                   "ew_walls_ns_periodic", "channel_mixing", "closed_basin_seamount_mixing", "filament_mixing_switches",
-                                  "closed_basin_river", "walled_channel_river_mixing"])
+                                  "closed_basin_river", "walled_channel_river_mixing", "walled_channel_pipe", "closed_basin_river_pipe"])
 def test_routine_by_routine(case):
     if case == "channel":
         cfg, st = cases.channel(48, 40, 12)
@@ -110,6 +110,10 @@ def test_routine_by_routine(case):
         cfg, st = cases.channel(40, 36, 8, ns_walls=True, ew_walls=True, river=True, dt=60.0)
     elif case == "walled_channel_river_mixing":                         # E-W periodic, 3 tracers, seamount, lateral mixing + river
         cfg, st = cases.channel(45, 38, 9, NT=3, ns_walls=True, seamount=True, river=True, dt=60.0, visc2=60.0, tnu2=30.0)
+    elif case == "walled_channel_pipe":                                 # pipe outfall (pipe_frc.F) in an E-W periodic channel
+        cfg, st = cases.channel(40, 36, 8, ns_walls=True, pipe=True, dt=60.0)
+    elif case == "closed_basin_river_pipe":                             # both sources, 3 tracers, ragged sizes
+        cfg, st = cases.channel(37, 31, 9, NT=3, ns_walls=True, ew_walls=True, river=True, pipe=True, dt=60.0)
     elif case == "filament":
         cfg, st = cases.filament(64, 64, 32)
     else:
@@ -201,6 +205,33 @@ def test_river_source_budgets_and_100_steps():
     g.call("run", 96); o.call("run", 96)
     r100 = compare(g, o, cfg.NT, TOL100, cfg)
     print("river case, 100 steps:", r100)
+    g.close(); o.close()
+
+
+def test_pipe_source_budgets_and_100_steps():
+    """Pipe outfalls (pipe_frc.F; hooks step2d_FB.F:155-159, omega.F:102-108, step3d_t_ISO.F:927-935): GPU-vs-oracle parity
+    and closed budgets: per baroclinic step the domain gains sum(pipe_flx)*dt of water and sum(pipe_flx)*dt*pipe_trc of each tracer."""
+    cfg, st = cases.channel(40, 36, 8, ns_walls=True, pipe=True, dt=60.0)
+    g, o = Roms(cfg), Oracle(cfg)
+    cases.initialize(g, st); cases.initialize(o, st)
+    vol, trc = st["PIPE_FLX"][2:-2, 2:-2].sum(), st["PIPES"][0][1]
+
+    def budget(m):
+        iic, iif, nstp, nrhs, nnew, kstp, knew = m.get_idx()
+        Hz = m.pull("HZ")[:, 2:-2, 2:-2]
+        return np.array([m.pull("ZETA", knew)[2:-2, 2:-2].sum() * 1.0e6] + [(Hz * m.pull("T", nnew, it)[:, 2:-2, 2:-2]).sum() * 1.0e6 for it in (1, 2)])
+    g.call("step"); o.call("step")
+    compare(g, o, cfg.NT, TOL1, cfg)
+    b0 = budget(g)
+    for n in range(3):
+        g.call("step"); o.call("step")
+        b = budget(g)
+        gain = (b - b0) / (vol * cfg.dt * np.array([1.0, trc[0], trc[1]]))
+        assert np.all(np.abs(gain - 1.0) < 1e-6), gain
+        b0 = b
+    g.call("run", 96); o.call("run", 96)
+    r100 = compare(g, o, cfg.NT, TOL100, cfg)
+    print("pipe case, 100 steps:", r100)
     g.close(); o.close()
 
 

@@ -159,3 +159,26 @@ def test_river_source_budgets_oracle():
         assert np.all(np.abs(gain - 1.0) < 1e-6), gain
         b0 = b
     o.close()
+
+
+def test_pipe_source_budgets_oracle():
+    """Pipe outfalls in the oracle: +sum(pipe_flx)*dt of water and +sum(pipe_flx)*dt*pipe_trc of heat and salt per baroclinic step."""
+    cfg, st = cases.channel(40, 36, 8, ns_walls=True, pipe=True, dt=60.0)
+    o = Oracle(cfg)
+    cases.initialize(o, st)
+    vol, trc = st["PIPE_FLX"][2:-2, 2:-2].sum(), st["PIPES"][0][1]
+    assert int((st["PIPE_IDX"][2:-2, 2:-2] > 0).sum()) == 2 and abs(sum(st["PIPES"][0][0]) - 1.0) < 1e-15
+
+    def budget():
+        iic, iif, nstp, nrhs, nnew, kstp, knew = o.get_idx()
+        Hz = o.pull("HZ")[:, 2:-2, 2:-2]
+        return np.array([o.pull("ZETA", knew)[2:-2, 2:-2].sum() * 1.0e6] + [(Hz * o.pull("T", nnew, it)[:, 2:-2, 2:-2]).sum() * 1.0e6 for it in (1, 2)])
+    o.call("step")
+    b0 = budget()
+    for n in range(3):
+        o.call("step")
+        b = budget()
+        gain = (b - b0) / (vol * cfg.dt * np.array([1.0, trc[0], trc[1]]))
+        assert np.all(np.abs(gain - 1.0) < 1e-6), gain
+        b0 = b
+    o.close()

@@ -228,6 +228,8 @@ __global__ void k_omega(const __grid_constant__ KP p, double dtau) {
   const double cu_min = 0.6, cu_max = 1.0, cmnx_ratio = cu_min / cu_max, cutoff = 2.0 - cmnx_ratio, r4cmx = 0.25 / (1.0 - cmnx_ratio);
   double W = 0.0;
   RW(p.Wi, c, 0) = 0.0;
+  const int pidx = p.pipes ? (int)p.pipe_idx[c] : 0;
+  const double pflx = pidx > 0 ? p.pipe_flx[c] : 0.0;
   const double* __restrict__ gFu = p.FlxU;
   const double* __restrict__ gFv = p.FlxV;
   const double* __restrict__ gzw = p.z_w;
@@ -243,6 +245,7 @@ __global__ void k_omega(const __grid_constant__ KP p, double dtau) {
       if (k <= N) {
         const double fu1 = a1[q], fu0 = a0[q], fv1 = b1[q], fv0 = b0[q];
         W = W - fu1 + fu0 - fv1 + fv0;
+        if (pidx > 0) W = W + pflx * p.pipe_tab[(pidx - 1) * PIPROW(N) + k - 1];   // omega.F:102-108
         S(0, k) = DMAX(fu1, 0.0) - DMIN(fu0, 0.0) + DMAX(fv1, 0.0) - DMIN(fv0, 0.0);
         S(1, k) = W;
       }
@@ -846,7 +849,7 @@ __global__ void k_rd_bott_drag(const __grid_constant__ KP p, const double* __res
 template <int MODE>
 __global__ void __launch_bounds__(64, 12)
 k_t_vert(const __grid_constant__ KP p, const double* __restrict__ t_rhs, double* __restrict__ t_new, const double* __restrict__ Akt,
-         const double* __restrict__ stflx, double dtau, int is_temp) {
+         const double* __restrict__ stflx, double dtau, int is_temp, int itrc) {
   extern __shared__ double smem[];
   THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
   ColScr sc = col_scratch(p, c, smem);
@@ -880,6 +883,8 @@ k_t_vert(const __grid_constant__ KP p, const double* __restrict__ t_rhs, double*
   }
   // ---- sweep 2 (down): back-substitution, vertical flux and its divergence -> rhs(k) in B
   const double cdt = dtau * p.pm[c] * p.pn[c];
+  const int pidx = (MODE == 1 && p.pipes) ? (int)p.pipe_idx[c] : 0;
+  const double pflx = pidx > 0 ? p.pipe_flx[c] : 0.0, ptrc = pidx > 0 ? p.pipe_tab[(pidx - 1) * PIPROW(N) + N + itrc - 1] : 0.0;
   double FCs_p = (2.0 * tk - FCkm) / (1.0 - CFk);   // FC(N) spline value
   double flux_p = 0.0;                               // FC(N)=0 after the sweep
   for (int k0 = N - 1; k0 >= 0; k0 -= KC) {
@@ -899,6 +904,7 @@ k_t_vert(const __grid_constant__ KP p, const double* __restrict__ t_rhs, double*
         double FCs = 0.0, flux = 0.0;                        // FC(0) of the spline is never used (flux(0)=0)
         if (k >= 1) { FCs = b1[q] - a0[q] * FCs_p; flux = FCs * we[q]; }
         double r = tn[q] - cdt * (flux_p - flux);            // rhs(k+1) = t_new(k+1) - cdt*(flux(k+1)-flux(k))
+        if (MODE == 1 && pidx > 0) r = r + cdt * pflx * p.pipe_tab[(pidx - 1) * PIPROW(N) + k] * ptrc;   // step3d_t_ISO.F:927-935 (level k+1)
         if (MODE == 1 && k + 1 == N) {
           if (is_temp) r = r + p.dt * p.swflx[c] * r / R3(gHz, c, N);
           r = r + p.dt * stflx[c];
@@ -1161,6 +1167,7 @@ __device__ __forceinline__ double s2d_DVom(const KP& p, const S2D& s, ix2_t c) {
 __device__ __forceinline__ double s2d_zeta_new(const KP& p, const S2D& s, ix2_t c) {
   const double DUon = s2d_DUon(p, s, c), DUon1 = s2d_DUon(p, s, c + 1), DVom = s2d_DVom(p, s, c), DVom1 = s2d_DVom(p, s, c + p.SX);
   double zn = s.zs[c] + p.dtfast * p.pm[c] * p.pn[c] * (DUon - DUon1 + DVom - DVom1) + p.dtfast * p.swflx[c];
+  if (p.pipes && p.pipe_idx[c] > 0.) zn = zn + p.dtfast * p.pm[c] * p.pn[c] * p.pipe_flx[c];   // step2d_FB.F:155-159
   return zn * p.rmask[c];
 }
 // pressure-gradient terms rubar,rvbar (step2d_FB.F:245-268, first-substep correction :313-384)

@@ -16,6 +16,8 @@ typedef int ix_t;
 #define MAXNT 40
 #define MAXRIV 8
 #define RIVROW (1 + MAXNT)
+#define MAXPIP 8
+#define PIPROW(N) ((N) + MAXNT)
 
 struct KP {
   int Lm, Mm, N, NT;
@@ -49,6 +51,9 @@ struct KP {
   // [iriver-1][1+itrc]=tracer value; rivers = river_source
   double *riv_uflx, *riv_vflx, *riv_tab;
   int rivers;
+  // pipe_frc.F: pipe cells (index > 0) and their volume flux; per-pipe row of pipe_tab: release profile prf(1:N) then NT tracer values
+  double *pipe_idx, *pipe_flx, *pipe_tab;
+  int pipes;
 };
 
 // column base index of (i,j) and relative addressing

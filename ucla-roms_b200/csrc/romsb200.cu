@@ -271,7 +271,7 @@ int roms_create(const roms_cfg* cfg, int device, roms_ctx** out) {
   const size_t scratch_planes = (size_t)3 * N            /* FlxDiv, P, rho */
                                 + (h->use_smem ? 0 : (size_t)2 * (N + 1)) /* column scratch fallback */
                                 + 1 /* zeta_new */ + 2 /* ub, vb */ + 5 /* diag planes */;
-  const size_t small = 2 * (size_t)(N + 1) + 64 + (size_t)MAXRIV * RIVROW;
+  const size_t small = 2 * (size_t)(N + 1) + 64 + (size_t)MAXRIV * RIVROW + (size_t)MAXPIP * PIPROW(N);
   h->arena_doubles = (planes + scratch_planes) * (size_t)p.SXY + small;
   CK(cudaMalloc(&h->arena, h->arena_doubles * sizeof(double)));
   CK(cudaMemset(h->arena, 0, h->arena_doubles * sizeof(double)));   // init=0 (init_scalars.F:31)
@@ -288,6 +288,8 @@ int roms_create(const roms_cfg* cfg, int device, roms_ctx** out) {
   p.Cs_r = cur; cur += (N + 1);
   p.riv_tab = cur; cur += (size_t)MAXRIV * RIVROW;
   p.rivers = 0;
+  p.pipe_tab = cur; cur += (size_t)MAXPIP * PIPROW(N);
+  p.pipes = 0;
 #define P1(name, id) p.name = h->f[id].ptr[0]
   P1(h, ROMS_H); P1(pm, ROMS_PM); P1(pn, ROMS_PN); P1(f, ROMS_F); P1(rmask, ROMS_RMASK); P1(umask, ROMS_UMASK); P1(vmask, ROMS_VMASK);
   P1(dm_u, ROMS_DM_U); P1(dn_u, ROMS_DN_U); P1(dm_v, ROMS_DM_V); P1(dn_v, ROMS_DN_V); P1(dm_r, ROMS_DM_R); P1(dn_r, ROMS_DN_R);
@@ -298,7 +300,7 @@ int roms_create(const roms_cfg* cfg, int device, roms_ctx** out) {
   P1(Wi, ROMS_WI); P1(rho1, ROMS_RHO1); P1(qp1, ROMS_QP1); P1(Akv, ROMS_AKV); P1(ru, ROMS_RU); P1(rv, ROMS_RV);
   P1(pmask, ROMS_PMASK); P1(dm_p, ROMS_DM_P); P1(dn_p, ROMS_DN_P); P1(pmon_u, ROMS_PMON_U); P1(pnom_v, ROMS_PNOM_V);
   P1(visc2_r, ROMS_VISC2_R); P1(visc2_p, ROMS_VISC2_P);
-  P1(riv_uflx, ROMS_RIV_UFLX); P1(riv_vflx, ROMS_RIV_VFLX);
+  P1(riv_uflx, ROMS_RIV_UFLX); P1(riv_vflx, ROMS_RIV_VFLX); P1(pipe_idx, ROMS_PIPE_IDX); P1(pipe_flx, ROMS_PIPE_FLX);
 #undef P1
   p.Akt[0] = h->f[ROMS_AKT].ptr[0]; p.Akt[1] = h->f[ROMS_AKT].ptr[1];
   host_scoord(h);
@@ -614,7 +616,7 @@ int roms_pre_step3d(roms_ctx* h, int tile) {
   else PLANE_JB((k_rhs_uv_horiz<false, false, 4>), 4, p.iend, p.jstr, p.jend, p.N, p, h->u(nrhs), h->v(nrhs));
   PLANE(k_rd_bott_drag, p.iend, p.jstrV - 1, p.jend, 1, p, h->u(nstp), h->v(nstp));
   for (int it = 1; it <= h->c.NT; ++it)
-    COLUMN(k_t_vert<0>, 2, p.iend, p.jstr, p.jend, p, h->t(nrhs, it), h->t(nnew, it), p.Akt[it >= 2 ? 1 : 0], (const double*)nullptr, dtau, 0);
+    COLUMN(k_t_vert<0>, 2, p.iend, p.jstr, p.jend, p, h->t(nrhs, it), h->t(nnew, it), p.Akt[it >= 2 ? 1 : 0], (const double*)nullptr, dtau, 0, it);
   COLUMN((k_uv_vert<0, 0>), 2, p.iend, p.jstr, p.jend, p, h->u(nrhs), h->u(nnew), h->u(nstp), h->u(indx), dtau, cf_stp, cf_bak);
   COLUMN((k_uv_vert<0, 1>), 2, p.iend, p.jstrV, p.jend, p, h->v(nrhs), h->v(nnew), h->v(nstp), h->v(indx), dtau, cf_stp, cf_bak);
   if (p.rivers) PLANE(k_river_uv, p.iend, p.jstr, p.jend, 1, p, h->u(nnew), h->v(nnew), p.istrU, p.jstrV);   // pre_step3d4S.F:493-522
@@ -717,7 +719,7 @@ int roms_step3d_t(roms_ctx* h, int tile) {
     else if (WALLED(h)) PLANE((k_t_horiz<true, KB_T, false>), p.iend, p.jstr, p.jend, (p.N + KB_T - 1) / KB_T, p, h->t(nrhs, it), h->t(nnew, it), it);
     else PLANE((k_t_horiz<false, KB_T, false>), p.iend, p.jstr, p.jend, (p.N + KB_T - 1) / KB_T, p, h->t(nrhs, it), h->t(nnew, it), it);
     COLUMN(k_t_vert<1>, 2, p.iend, p.jstr, p.jend, p, h->t(nrhs, it), h->t(nnew, it), p.Akt[it >= 2 ? 1 : 0], h->f[ROMS_STFLX].ptr[it - 1], h->c.dt,
-           it == 1 ? 1 : 0);
+           it == 1 ? 1 : 0, it);
   }
   for (int it = 1; it <= NT; ++it) bc3d(h, h->t(nnew, it), p.N, BC_T);   // t3dbc_tile (step3d_t_ISO.F:1157-1159)
   for (int it = 1; it + 1 <= NT; it += 2) {
@@ -766,6 +768,19 @@ int roms_alfabeta(roms_ctx* h, double* alpha_host, double* beta_host) {
 static double pairsum(const double* a, size_t n) {
   if (n <= 8) { double s = 0; for (size_t i = 0; i < n; ++i) s += a[i]; return s; }
   return pairsum(a, n / 2) + pairsum(a + n / 2, n - n / 2);
+}
+// pipe_frc.F (init_arrays_pipes, set_pipe_frc): release profile and tracer values of one pipe
+int roms_set_pipe(roms_ctx* h, int ipipe, const double* prf, const double* trc) {
+  CK(cudaSetDevice(h->device));
+  if (ipipe < 1 || ipipe > MAXPIP || !prf || !trc) { g_err = "roms_set_pipe: pipe index out of range (1..8)"; return -1; }
+  const int N = h->c.N;
+  std::vector<double> row(PIPROW(N), 0.0);
+  for (int k = 0; k < N; ++k) row[k] = prf[k];
+  for (int it = 0; it < h->c.NT; ++it) row[N + it] = trc[it];
+  CK(cudaMemcpyAsync(h->kp.pipe_tab + (size_t)(ipipe - 1) * PIPROW(N), row.data(), row.size() * sizeof(double), cudaMemcpyHostToDevice, h->st));
+  CK(cudaStreamSynchronize(h->st));
+  h->kp.pipes = 1;
+  return 0;
 }
 // river_frc.F set_river_frc: volume flux and tracer values of one river; the table lives next to the fields in the arena
 int roms_set_river(roms_ctx* h, int iriver, double vol, const double* trc) {

@@ -23,7 +23,8 @@ FIELDS = ["H", "PM", "PN", "F", "RMASK", "UMASK", "VMASK", "DM_U", "DN_U", "DM_V
           "FOMN", "HINV", "ZETA", "UBAR", "VBAR", "RHOA", "RHOS", "RUFRC", "RVFRC", "ZT_AVG1", "DU_AVG1",
           "DV_AVG1", "DU_AVG2", "DV_AVG2", "DU_AVG_BAK", "DV_AVG_BAK", "R_D", "SUSTR", "SVSTR", "SWFLX",
           "STFLX", "U", "V", "T", "HZ", "Z_R", "Z_W", "FLXU", "FLXV", "WE", "WI", "RHO1", "QP1", "AKV", "AKT",
-          "RU", "RV", "PMASK", "DM_P", "DN_P", "PMON_U", "PNOM_V", "VISC2_R", "VISC2_P", "DIFF2", "RIV_UFLX", "RIV_VFLX"]
+          "RU", "RV", "PMASK", "DM_P", "DN_P", "PMON_U", "PNOM_V", "VISC2_R", "VISC2_P", "DIFF2", "RIV_UFLX", "RIV_VFLX",
+          "PIPE_IDX", "PIPE_FLX"]
 FID = {n: i for i, n in enumerate(FIELDS)}
 
 
@@ -106,6 +107,12 @@ class CApi:
         """river_frc.F set_river_frc: volume flux [m3/s] and tracer values of river `iriver` (1-based)"""
         a = (C.c_double * len(trc))(*trc)
         self._check(self._f("set_river")(self.h, iriver, C.c_double(vol), a), "set_river")
+
+    def set_pipe(self, ipipe, prf, trc):
+        """pipe_frc.F: vertical release profile (N values, bottom first) and tracer values of pipe `ipipe` (1-based)"""
+        a = (C.c_double * len(prf))(*prf)
+        b = (C.c_double * len(trc))(*trc)
+        self._check(self._f("set_pipe")(self.h, ipipe, a, b), "set_pipe")
 
     def nfast(self):
         return self._f("get_nfast")(self.h)
