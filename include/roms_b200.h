@@ -80,6 +80,7 @@ enum roms_field {
   ROMS_VISC2_R, ROMS_VISC2_P,
   ROMS_DIFF2,                                    /* itrc 1..NT */
   ROMS_RIV_UFLX, ROMS_RIV_VFLX,                  /* river_frc.F: river faces, 10*iriver + fraction of the river's volume flux */
+  ROMS_PTIDE,                                    /* tides.F:26 equilibrium tidal potential [m] (pot_tides) */
   ROMS_PIPE_IDX, ROMS_PIPE_FLX,                  /* pipe_frc.F: pipe index of a cell (0: none) and its volume flux fraction*pipe_vol [m3/s] */
   ROMS_NFIELDS
 };
@@ -122,6 +123,8 @@ int  roms_step3d_t(roms_ctx* h, int tile);    /* step3d_t_ISO.F:20 */
 int  roms_visc3d(roms_ctx* h);                /* visc3d_S.F:4  (UV_VIS2: harmonic viscosity along S-surfaces)  */
 int  roms_t3dmix(roms_ctx* h);                /* t3dmix_S.F:4  (TS_DIF2: Laplacian tracer diffusion, all NT)   */
 int  roms_alfabeta(roms_ctx* h, double* alpha_host, double* beta_host); /* alfabeta.F:4 */
+int  roms_set_pot_tides(roms_ctx* h, int on);  /* tides.F pot_tides: prsgrd subtracts g*ptide (ROMS_PTIDE, pushed by the host each
+                                                  step after its harmonic synthesis, tides.F:238-246) from the surface pressure, prsgrd.F:209-211 */
 int  roms_set_pipe(roms_ctx* h, int ipipe, const double* prf, const double* trc);
                                                /* pipe_frc.F: release profile pipe_prf(1:N) and the NT tracer values of pipe ipipe (1..8);
                                                   switches pipe_source on.  Pipe cells and their fluxes: ROMS_PIPE_IDX / ROMS_PIPE_FLX.

@@ -62,6 +62,8 @@ struct Orc {
   vec pipe_idx, pipe_flx;
   std::vector<vec> pipe_prf, pipe_trc;
   bool pipe_source = false;
+  vec ptide;                 // tides.F:26 equilibrium tidal potential [m]
+  bool pot_tides = false;
   vec xr;  // only for the Filament analytic initial condition
   std::vector<vec> s2d;
 };
@@ -569,6 +571,8 @@ void prsgrd(Orc& o) {
                          grho * (A3(rho, i, j, N) + 0.5 * (A3(rho, i, j, N) - A3(rho, i, j, N - 1)) * (AW(o.z_w, i, j, N) - A3(o.z_r, i, j, N)) /
                                                         (A3(o.z_r, i, j, N) - A3(o.z_r, i, j, N - 1))) *
                              (AW(o.z_w, i, j, N) - A3(o.z_r, i, j, N));
+      if (o.pot_tides)   // prsgrd.F:209-211: tidal potential (tides.F:238-246 synthesises ptide each step)
+        for (int i = istr - 1; i <= iend; ++i) A3(P, i, j, N) = A3(P, i, j, N) - g * A2(o.ptide, i, j);
       for (int k = N - 1; k >= 1; --k)
         for (int i = istr - 1; i <= iend; ++i)
           A3(P, i, j, k) = A3(P, i, j, k + 1) +
@@ -1897,6 +1901,7 @@ vec* field_ptr(Orc& o, int field, int lvl, int itrc, long* count) {
     case ROMS_VISC2_R: p = &o.visc2_r; break; case ROMS_VISC2_P: p = &o.visc2_p; break; case ROMS_DIFF2: p = &o.diff2[itrc - 1]; break;
     case ROMS_RIV_UFLX: p = &o.riv_uflx; break; case ROMS_RIV_VFLX: p = &o.riv_vflx; break;
     case ROMS_PIPE_IDX: p = &o.pipe_idx; break; case ROMS_PIPE_FLX: p = &o.pipe_flx; break;
+    case ROMS_PTIDE: p = &o.ptide; break;
     default: break;
   }
   if (count) *count = n;
@@ -1922,6 +1927,7 @@ int orc_create(const roms_cfg* cfg, void** out) {
   for (int l = 0; l < 4; ++l) { o->zeta[l].assign(n2, 0.0); o->ubar[l].assign(n2, 0.0); o->vbar[l].assign(n2, 0.0); }
   o->riv_uflx.assign(n2, 0.0); o->riv_vflx.assign(n2, 0.0);
   o->pipe_idx.assign(n2, 0.0); o->pipe_flx.assign(n2, 0.0);
+  o->ptide.assign(n2, 0.0);
   o->stflx.assign(o->NT, vec(n2, 0.0));
   o->diff2.assign(o->NT, vec(n2, 0.0));
   for (int l = 0; l < 3; ++l) {
@@ -1991,6 +1997,7 @@ int orc_set_pipe(void* h, int ipipe, const double* prf, const double* trc) {
   o.pipe_source = true;
   return 0;
 }
+int orc_set_pot_tides(void* h, int on) { ((Orc*)h)->pot_tides = on != 0; return 0; }
 int orc_get_nfast(void* h) { return ((Orc*)h)->nfast; }
 int orc_get_weights(void* h, double* w1, double* w2, int n) {
   Orc& o = *(Orc*)h;

@@ -81,7 +81,7 @@ def test_rivers_ana_startup_on_gpu():
 @pytest.mark.parametrize("case", ["channel", "filament", "channel_linear_odd", "channel_walls", "channel_walls_linear_odd",
                                   "seamount_island_walls", "seamount_island_periodic", "closed_basin", "closed_basin_seamount_odd",
                                   "ew_walls_ns_periodic", "channel_mixing", "closed_basin_seamount_mixing", "filament_mixing_switches",
-                                  "closed_basin_river", "walled_channel_river_mixing", "walled_channel_pipe", "closed_basin_river_pipe"])
+                                  "closed_basin_river", "walled_channel_river_mixing", "walled_channel_pipe", "closed_basin_river_pipe", "closed_basin_tide"])
 def test_routine_by_routine(case):
     if case == "channel":
         cfg, st = cases.channel(48, 40, 12)
@@ -114,6 +114,8 @@ def test_routine_by_routine(case):
         cfg, st = cases.channel(40, 36, 8, ns_walls=True, pipe=True, dt=60.0)
     elif case == "closed_basin_river_pipe":                             # both sources, 3 tracers, ragged sizes
         cfg, st = cases.channel(37, 31, 9, NT=3, ns_walls=True, ew_walls=True, river=True, pipe=True, dt=60.0)
+    elif case == "closed_basin_tide":                                   # tidal potential in the surface pressure (prsgrd.F:209-211)
+        cfg, st = cases.channel(40, 36, 8, ns_walls=True, ew_walls=True, seamount=True, tide=True)
     elif case == "filament":
         cfg, st = cases.filament(64, 64, 32)
     else:

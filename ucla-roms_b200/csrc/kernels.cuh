@@ -384,6 +384,7 @@ __global__ void k_prsgrd_vert(const __grid_constant__ KP p) {
       else rho_m = r1_m;
       const double zwN = RW(p.z_w, c, N);
       Pk = p.g * zwN + grho * (rho_c + 0.5 * (rho_c - rho_m) * (zwN - zr_c) / (zr_c - zr_m)) * (zwN - zr_c);
+      if (p.pot_tides) Pk = Pk - p.g * p.ptide[c];   // prsgrd.F:209-211
     } else {
       Pk = P_p + HalfGRho * ((rho_p + rho_c) * (zr_p - zr_c) -
                              OneFifth * ((dRh_p - dRh) * (zr_p - zr_c - OneTwelfth * (dZh_p + dZh)) - (dZh_p - dZh) * (rho_p - rho_c - OneTwelfth * (dRh_p + dRh))));

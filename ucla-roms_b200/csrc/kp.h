@@ -54,6 +54,8 @@ struct KP {
   // pipe_frc.F: pipe cells (index > 0) and their volume flux; per-pipe row of pipe_tab: release profile prf(1:N) then NT tracer values
   double *pipe_idx, *pipe_flx, *pipe_tab;
   int pipes;
+  double* ptide;     // tides.F:26 equilibrium tidal potential
+  int pot_tides;
 };
 
 // column base index of (i,j) and relative addressing

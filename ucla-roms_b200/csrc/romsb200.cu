@@ -290,6 +290,7 @@ int roms_create(const roms_cfg* cfg, int device, roms_ctx** out) {
   p.rivers = 0;
   p.pipe_tab = cur; cur += (size_t)MAXPIP * PIPROW(N);
   p.pipes = 0;
+  p.pot_tides = 0;
 #define P1(name, id) p.name = h->f[id].ptr[0]
   P1(h, ROMS_H); P1(pm, ROMS_PM); P1(pn, ROMS_PN); P1(f, ROMS_F); P1(rmask, ROMS_RMASK); P1(umask, ROMS_UMASK); P1(vmask, ROMS_VMASK);
   P1(dm_u, ROMS_DM_U); P1(dn_u, ROMS_DN_U); P1(dm_v, ROMS_DM_V); P1(dn_v, ROMS_DN_V); P1(dm_r, ROMS_DM_R); P1(dn_r, ROMS_DN_R);
@@ -300,7 +301,7 @@ int roms_create(const roms_cfg* cfg, int device, roms_ctx** out) {
   P1(Wi, ROMS_WI); P1(rho1, ROMS_RHO1); P1(qp1, ROMS_QP1); P1(Akv, ROMS_AKV); P1(ru, ROMS_RU); P1(rv, ROMS_RV);
   P1(pmask, ROMS_PMASK); P1(dm_p, ROMS_DM_P); P1(dn_p, ROMS_DN_P); P1(pmon_u, ROMS_PMON_U); P1(pnom_v, ROMS_PNOM_V);
   P1(visc2_r, ROMS_VISC2_R); P1(visc2_p, ROMS_VISC2_P);
-  P1(riv_uflx, ROMS_RIV_UFLX); P1(riv_vflx, ROMS_RIV_VFLX); P1(pipe_idx, ROMS_PIPE_IDX); P1(pipe_flx, ROMS_PIPE_FLX);
+  P1(riv_uflx, ROMS_RIV_UFLX); P1(riv_vflx, ROMS_RIV_VFLX); P1(pipe_idx, ROMS_PIPE_IDX); P1(pipe_flx, ROMS_PIPE_FLX); P1(ptide, ROMS_PTIDE);
 #undef P1
   p.Akt[0] = h->f[ROMS_AKT].ptr[0]; p.Akt[1] = h->f[ROMS_AKT].ptr[1];
   host_scoord(h);
@@ -769,6 +770,7 @@ static double pairsum(const double* a, size_t n) {
   if (n <= 8) { double s = 0; for (size_t i = 0; i < n; ++i) s += a[i]; return s; }
   return pairsum(a, n / 2) + pairsum(a + n / 2, n - n / 2);
 }
+int roms_set_pot_tides(roms_ctx* h, int on) { h->kp.pot_tides = on ? 1 : 0; return 0; }
 // pipe_frc.F (init_arrays_pipes, set_pipe_frc): release profile and tracer values of one pipe
 int roms_set_pipe(roms_ctx* h, int ipipe, const double* prf, const double* trc) {
   CK(cudaSetDevice(h->device));

@@ -92,7 +92,7 @@ def _noise(ig, jg, k, salt):
 
 def channel(Lm=64, Mm=64, N=16, NT=2, ns_walls=False, nonlin_eos=True, dt=120.0, ndtfast=60, dx=1.0e3, dy=1.0e3,
             depth=4000.0, seed=20260101, perturb=1e-6, amp=None, sub=(0, 0, 1, 1), seamount=False, island=False, ew_walls=False,
-            visc2=None, tnu2=None, sponge=False, ishift=0, river=False, pipe=False):
+            visc2=None, tnu2=None, sponge=False, ishift=0, river=False, pipe=False, tide=False):
     """Lm, Mm are the GLOBAL interior sizes; sub=(inode, jnode, np_xi, np_eta) selects this rank's block
     (mpi_setup.F:61-70; uneven splits as mpi_setup.F:117-160, see block_extent).  Returns the cfg and state of that block.
     seamount: Gaussian seamount h = depth*(1 - 0.5*exp(-r^2/(L/5)^2)) (SURVEY.md 8(d) input (3), form of
@@ -108,6 +108,8 @@ def channel(Lm=64, Mm=64, N=16, NT=2, ns_walls=False, nonlin_eos=True, dt=120.0,
     tests/Rivers_ana/ana_frc_river.h scaled to the cell size, with a milder T,S contrast (state key "RIVERS").
     pipe: two neighbouring water cells share the outfall of pipe 1 (pipe_frc.F: index + fraction, pipe_flx = fraction*pipe_vol),
     released over the two bottom levels (the profile of pipe_frc.F:232-234) with its own tracer values (state key "PIPES").
+    tide: an equilibrium tidal potential ptide (tides.F) of 0.3 m amplitude, one wave across the domain (state key "PTIDE";
+    `initialize` switches pot_tides on).
     ishift: translate the whole E-W periodic problem by this many cells in xi (the state is the roll of the unshifted one, so
     the solution must be the roll of the unshifted solution, bit for bit -- a size-independent parity property)."""
     inode, jnode, np_xi, np_eta = sub
@@ -210,6 +212,8 @@ def channel(Lm=64, Mm=64, N=16, NT=2, ns_walls=False, nonlin_eos=True, dt=120.0,
         pidx[sel] = 1.0; pflx[sel] = 0.5 * 2.0e2 * dx * dy / 1.0e4
         st["PIPE_IDX"] = t2(pidx); st["PIPE_FLX"] = t2(pflx)
         st["PIPES"] = [([0.5, 0.5] + [0.0] * (N - 2), [4.5, 34.95] + [1.0] * (NT - 2))]   # close to the ambient bottom water: a gentle plume
+    if tide:
+        st["PTIDE"] = t2(0.3 * np.cos(2 * np.pi * x / Lx) * np.cos(np.pi * y / Ly))
     if sponge:
         wr = 0.5 + 0.5 * np.cos(2 * np.pi * x / Lx) * np.sin(2 * np.pi * y / Ly)          # at rho points, 3-cell halo
         wp = np.zeros_like(wr)
@@ -303,4 +307,6 @@ def initialize(model, state):
         model.set_river(n, vol, trc)
     for n, (prf, trc) in enumerate(state.get("PIPES", []), 1):
         model.set_pipe(n, prf, trc)
+    if "PTIDE" in state:
+        model.call("set_pot_tides", 1)
     model.call("init_step0")
