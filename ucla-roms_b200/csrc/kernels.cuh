@@ -403,6 +403,114 @@ __global__ void k_prsgrd_vert(const __grid_constant__ KP p) {
   }
 }
 
+// rho_eos_tile FUSED with the vertical part of prsgrd_tile (used when prsgrd follows a rho_eos of the same time level, as in
+// main.F:397-413 and :430-445): both are downward sweeps of the same column, so the equation of state feeds the 3-level
+// window of the pressure integration directly and rho1, qp1, z_r are not read back (8 instead of 11 words per point for
+// the pair).  Every value is produced by the expressions of k_rho_eos / k_prsgrd_vert in the same order (the EOS levels
+// are visited N, N-1, ..., 1, so the running integrals rhoA, rhoS round identically).  Runs over the extended range of
+// rho_eos; columns outside prsgrd's range only do the EOS part.
+template <bool NONLIN>
+__global__ void k_rho_prs_vert(const __grid_constant__ KP p, const double* __restrict__ T, const double* __restrict__ Sal) {
+  THREAD_IJ((p.wwall ? p.istr - 1 : p.istr - 2), (p.ewall ? p.iend + 1 : p.iend + 2), (p.swall ? p.jstr - 1 : p.jstr - 2), (p.nwall ? p.jend + 1 : p.jend + 2))
+  const bool doP = i >= 0 && i <= p.Lm && j >= 0 && j <= p.Mm;
+  const int N = p.N;
+  const double rho0 = p.rho0, qp2 = 0.0000172;
+  const double r00 = 999.842594, r01 = 6.793952e-2, r02 = -9.095290e-3, r03 = 1.001685e-4, r04 = -1.120083e-6, r05 = 6.536332e-9,
+               r10 = 0.824493, r11 = -4.08990e-3, r12 = 7.64380e-5, r13 = -8.24670e-7, r14 = 5.38750e-9, rS0 = -5.72466e-3,
+               rS1 = 1.02270e-4, rS2 = -1.65460e-6, r20 = 4.8314e-4, K00 = 19092.56, K01 = 209.8925, K02 = -3.041638,
+               K03 = -1.852732e-3, K04 = -1.361629e-5, K10 = 104.4077, K11 = -6.500517, K12 = 0.1553190, K13 = 2.326469e-4,
+               KS0 = -5.587545, KS1 = +0.7390729, KS2 = -1.909078e-2;
+  double K0_Duk = 0, dr00 = 0, cffl = 0;
+  if (NONLIN) {
+    const double Tt = 3.8, Ts = 34.5, sqrtTs = sqrt(Ts);
+    K0_Duk = Tt * (K01 + Tt * (K02 + Tt * (K03 + Tt * K04))) + Ts * (K10 + Tt * (K11 + Tt * (K12 + Tt * K13)) + sqrtTs * (KS0 + Tt * (KS1 + Tt * KS2)));
+    dr00 = r00 - rho0;
+  } else {
+    cffl = p.salinity ? (p.Tcoef * p.T0 - p.Scoef * p.S0) : (p.Tcoef * p.T0);
+  }
+  const double rmask = p.rmask[c];
+  double rhoA = 0, rhoS = 0;
+  // equation of state at level k (k_rho_eos body): stores rho1, qp1, advances the integrals, returns r1, q1, z_r
+  auto eos = [&](int k, double& r1, double& q1, double& zr) {
+    double cff;
+    const double Hz = R3(p.Hz, c, k);
+    zr = R3(p.z_r, c, k);
+    if (NONLIN) {
+      const double Tt = R3(T, c, k), Ts = R3(Sal, c, k), sqrtTs = sqrt(DMAX(0.0, Ts));
+      r1 = (dr00 + Tt * (r01 + Tt * (r02 + Tt * (r03 + Tt * (r04 + Tt * r05)))) +
+            Ts * (r10 + Tt * (r11 + Tt * (r12 + Tt * (r13 + Tt * r14))) + sqrtTs * (rS0 + Tt * (rS1 + Tt * rS2)) + Ts * r20)) * rmask;
+      const double K0 = Tt * (K01 + Tt * (K02 + Tt * (K03 + Tt * K04))) + Ts * (K10 + Tt * (K11 + Tt * (K12 + Tt * K13)) + sqrtTs * (KS0 + Tt * (KS1 + Tt * KS2)));
+      q1 = 0.1 * (rho0 + r1) * (K0_Duk - K0) / ((K00 + K0) * (K00 + K0_Duk)) * rmask;
+      R3(p.qp1, c, k) = q1;
+      const double dpth = -zr;
+      cff = Hz * (r1 + q1 * dpth * (1.0 - qp2 * dpth));
+    } else {
+      r1 = cffl - p.Tcoef * R3(T, c, k);
+      if (p.salinity) r1 = r1 + p.Scoef * R3(Sal, c, k);
+      r1 = r1 * rmask;
+      q1 = 0.0;
+      cff = Hz * r1;
+    }
+    R3(p.rho1, c, k) = r1;
+    if (k == N) { rhoS = 0.5 * cff * Hz; rhoA = cff; }
+    else { rhoS = rhoS + Hz * (rhoA + 0.5 * cff); rhoA = rhoA + cff; }
+  };
+  const double OneFifth = 0.2, OneTwelfth = 1.0 / 12.0, epsil = 0.0;
+  const double grho = p.g / p.rho0, HalfGRho = 0.5 * grho;
+  double zr_c, r1_c, q1_c, zr_m, r1_m, q1_m;
+  eos(N, r1_c, q1_c, zr_c);
+  eos(N - 1, r1_m, q1_m, zr_m);
+  double zr_p = 0, rho_p = 0, dZh_p = 0, dRh_p = 0, P_p = 0;
+  double rawZ_c, rawR_c, rawZ_m, rawR_m;
+  {
+    rawZ_m = zr_c - zr_m;
+    if (NONLIN) { const double dpth = -0.5 * (zr_c + zr_m); rawR_m = r1_c - r1_m + (q1_c - q1_m) * dpth * (1.0 - qp2 * dpth); }
+    else rawR_m = r1_c - r1_m;
+    rawZ_c = rawZ_m; rawR_c = rawR_m;   // dZ(N)=dZ(N-1), dR(N)=dR(N-1)
+  }
+  for (int k = N; k >= 1; --k) {
+    if (doP) {
+      double cff = 2.0 * rawZ_c * rawZ_m;
+      const double dZh = cff / (rawZ_c + rawZ_m);
+      const double cfr = 2.0 * rawR_c * rawR_m;
+      double dRh = (cfr > epsil) ? cfr / (rawR_c + rawR_m) : 0.0;
+      double rho_c;
+      if (NONLIN) {
+        const double dpth = -zr_c;
+        dRh = dRh - q1_c * dZh * (1.0 - 2.0 * qp2 * dpth);
+        rho_c = r1_c + q1_c * dpth * (1.0 - qp2 * dpth);
+        R3(p.rho, c, k) = rho_c;
+      } else rho_c = r1_c;
+      double Pk;
+      if (k == N) {
+        double rho_m;
+        if (NONLIN) { const double dpm = -zr_m; rho_m = r1_m + q1_m * dpm * (1.0 - qp2 * dpm); }
+        else rho_m = r1_m;
+        const double zwN = RW(p.z_w, c, N);
+        Pk = p.g * zwN + grho * (rho_c + 0.5 * (rho_c - rho_m) * (zwN - zr_c) / (zr_c - zr_m)) * (zwN - zr_c);
+        if (p.pot_tides) Pk = Pk - p.g * p.ptide[c];   // prsgrd.F:209-211
+      } else {
+        Pk = P_p + HalfGRho * ((rho_p + rho_c) * (zr_p - zr_c) -
+                               OneFifth * ((dRh_p - dRh) * (zr_p - zr_c - OneTwelfth * (dZh_p + dZh)) - (dZh_p - dZh) * (rho_p - rho_c - OneTwelfth * (dRh_p + dRh))));
+      }
+      R3(p.P, c, k) = Pk;
+      zr_p = zr_c; rho_p = rho_c; dZh_p = dZh; dRh_p = dRh; P_p = Pk;
+    }
+    rawZ_c = rawZ_m; rawR_c = rawR_m;
+    zr_c = zr_m; r1_c = r1_m; q1_c = q1_m;
+    if (k - 2 >= 1) {
+      eos(k - 2, r1_m, q1_m, zr_m);
+      rawZ_m = zr_c - zr_m;
+      if (NONLIN) { const double dpth = -0.5 * (zr_c + zr_m); rawR_m = r1_c - r1_m + (q1_c - q1_m) * dpth * (1.0 - qp2 * dpth); }
+      else rawR_m = r1_c - r1_m;
+    }
+  }
+  const double cff1 = 1.0 / rho0;
+  const double cff = 1.0 / (RW(p.z_w, c, N) - RW(p.z_w, c, 0));
+  p.rhoA[c] = cff * cff1 * rhoA;
+  p.rhoS[c] = 2.0 * cff * cff * cff1 * rhoS;
+}
+
 // prsgrd.F:231-421: horizontal part, plane kernel.  ru, rv at (i,j,k) from the density-Jacobian with
 // harmonic-mean reconstruction of the horizontal differences.
 template <bool NONLIN>

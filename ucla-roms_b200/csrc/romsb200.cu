@@ -55,6 +55,8 @@ struct roms_ctx {
   std::vector<KTimer> ktimers;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   int col_bx = 32, col_by = 2, pl_bx = 32, pl_by = 8;   // plane tiles 32x8: fewest halo-row re-reads through L2 (profiles/r1_tuning_log.txt)
+  int fuse_rho = 1;       // a rho_eos call is deferred; if prsgrd follows (main.F:397-413, 430-445) both run as one fused column kernel
+  int rho_pending = 0;    // time index of the deferred rho_eos (0: none)
   int uv2_sm = 1;     // k_uv2_pass1 with the column parked in shared memory (1.0 -> 0.78 ms on B200); off when the column is too tall
   int use_smem = 0;   // measured on B200 (profiles/r1_scratch_policy.txt): occupancy beats shared-memory scratch
   Comm comm;
@@ -73,6 +75,8 @@ static dim3 grid_plane(const roms_ctx* h, int i1, int j0, int j1, int nk, dim3 b
 }
 static void kt_begin(roms_ctx* h, const char* name);
 static void kt_end(roms_ctx* h);
+static int flush_rho(roms_ctx* h);
+#define FLUSH_RHO(h) do { int rc_ = flush_rho(h); if (rc_) return rc_; } while (0)
 // plane kernel whose threads each compute JB consecutive rows
 #define PLANE_JB(kern, JB, i1, j0, j1, nk, ...)                                                  \
   do {                                                                                        \
@@ -251,6 +255,7 @@ int roms_create(const roms_cfg* cfg, int device, roms_ctx** out) {
   p.wrap_y = (single && cfg->ns_periodic) ? 1 : 0;
   if (const char* e = getenv("ROMS_COL_SMEM")) h->use_smem = atoi(e);
   if (const char* e = getenv("ROMS_UV2_SM")) h->uv2_sm = atoi(e);
+  if (const char* e = getenv("ROMS_FUSE_RHO")) h->fuse_rho = atoi(e);
   if ((size_t)2 * (N + 1) * 32 * sizeof(double) > 64 * 1024) h->uv2_sm = 0;   // fewer than 3 warps per SM would fit: global re-read version
   if ((size_t)2 * (N + 1) * h->col_bx * h->col_by * sizeof(double) > 200 * 1024) { h->col_by = 1; }
   if ((size_t)2 * (N + 1) * h->col_bx * h->col_by * sizeof(double) > 200 * 1024) h->use_smem = 0;
@@ -338,6 +343,7 @@ long roms_field_count(roms_ctx* h, int field) {
   return (long)(h->c.Lm + 4) * (h->c.Mm + 4) * h->f[field].nk;
 }
 int roms_push(roms_ctx* h, int field, int lvl, int itrc, const double* host) {
+  FLUSH_RHO(h);
   double* d; int nk;
   if (find_slot(h, field, lvl, itrc, &d, &nk)) return -1;
   CK(cudaSetDevice(h->device));
@@ -347,6 +353,7 @@ int roms_push(roms_ctx* h, int field, int lvl, int itrc, const double* host) {
   return 0;
 }
 int roms_pull(roms_ctx* h, int field, int lvl, int itrc, double* host) {
+  FLUSH_RHO(h);
   double* d; int nk;
   if (find_slot(h, field, lvl, itrc, &d, &nk)) return -1;
   CK(cudaSetDevice(h->device));
@@ -356,6 +363,7 @@ int roms_pull(roms_ctx* h, int field, int lvl, int itrc, double* host) {
   return 0;
 }
 int roms_sync(roms_ctx* h) {
+  FLUSH_RHO(h);
   CK(cudaSetDevice(h->device));
   CK(cudaStreamSynchronize(h->st));
   CK(cudaGetLastError());
@@ -364,6 +372,7 @@ int roms_sync(roms_ctx* h) {
 int roms_kernel_launches(roms_ctx* h, long* n) { *n = h->launches; return 0; }
 // device-side timing on the library's own stream (bench.py): events bracket whatever is enqueued between
 int roms_timer_start(roms_ctx* h) {
+  FLUSH_RHO(h);
   CK(cudaSetDevice(h->device));
   if (!h->ev0) { CK(cudaEventCreate(&h->ev0)); CK(cudaEventCreate(&h->ev1)); }
   CK(cudaStreamSynchronize(h->st));
@@ -371,6 +380,7 @@ int roms_timer_start(roms_ctx* h) {
   return 0;
 }
 int roms_timer_stop(roms_ctx* h, double* ms) {
+  FLUSH_RHO(h);
   CK(cudaEventRecord(h->ev1, h->st));
   CK(cudaEventSynchronize(h->ev1));
   float f = 0;
@@ -442,6 +452,7 @@ static int exchange(roms_ctx* h, std::initializer_list<XF> fl) {
   return rc;
 }
 int roms_exchange(roms_ctx* h, int nfields, const int* fields, const int* lvls, const int* itrcs) {
+  FLUSH_RHO(h);
   CK(cudaSetDevice(h->device));
   std::vector<XF> v;
   for (int n = 0; n < nfields; ++n) {
@@ -537,6 +548,7 @@ int roms_setup_grid(roms_ctx* h) {
 
 // ---- the tile-subroutine surface ----------------------------------------------------------------
 int roms_set_depth(roms_ctx* h, int tile) {
+  FLUSH_RHO(h);
   (void)tile;
   CK(cudaSetDevice(h->device));
   const KP& p = h->kp;
@@ -552,6 +564,7 @@ int roms_set_huv(roms_ctx* h) {
   return exchange(h, {{p.FlxU, p.N}, {p.FlxV, p.N}});
 }
 int roms_set_huv1(roms_ctx* h, int tile) {
+  FLUSH_RHO(h);
   (void)tile;
   CK(cudaSetDevice(h->device));
   const KP& p = h->kp;
@@ -572,32 +585,60 @@ int roms_omega(roms_ctx* h) {
   bc3d(h, p.Wi, p.N + 1, BC_W);
   return exchange(h, {{p.We, p.N + 1}, {p.Wi, p.N + 1}});
 }
-int roms_rho_eos(roms_ctx* h, int tidx) {
-  CK(cudaSetDevice(h->device));
+}  // extern "C"
+static int rho_eos_launch(roms_ctx* h, int tidx, bool with_prs_vert) {
   const KP& p = h->kp;
   const double* T = h->t(tidx, 1);
   const double* S = h->c.NT >= 2 ? h->t(tidx, 2) : nullptr;
+  const int j0 = p.swall ? p.jstr - 1 : p.jstr - 2;
   if (h->c.nonlin_eos) {
     if (!S) { g_err = "NONLIN_EOS needs salinity (NT>=2)"; return -1; }
-    COLUMN(k_rho_eos<true>, 0, p.iend + 2, (p.swall ? p.jstr - 1 : p.jstr - 2), p.jend + 2, p, T, S);
-  } else COLUMN(k_rho_eos<false>, 0, p.iend + 2, (p.swall ? p.jstr - 1 : p.jstr - 2), p.jend + 2, p, T, S);
+    if (with_prs_vert) COLUMN(k_rho_prs_vert<true>, 0, p.iend + 2, j0, p.jend + 2, p, T, S);
+    else COLUMN(k_rho_eos<true>, 0, p.iend + 2, j0, p.jend + 2, p, T, S);
+  } else {
+    if (with_prs_vert) COLUMN(k_rho_prs_vert<false>, 0, p.iend + 2, j0, p.jend + 2, p, T, S);
+    else COLUMN(k_rho_eos<false>, 0, p.iend + 2, j0, p.jend + 2, p, T, S);
+  }
   return 0;
+}
+// a deferred rho_eos runs on its own as soon as anything but set_HUV / omega / prsgrd is called
+static int flush_rho(roms_ctx* h) {
+  if (!h->rho_pending) return 0;
+  const int tidx = h->rho_pending;
+  h->rho_pending = 0;
+  return rho_eos_launch(h, tidx, false);
+}
+extern "C" {
+int roms_rho_eos(roms_ctx* h, int tidx) {
+  CK(cudaSetDevice(h->device));
+  FLUSH_RHO(h);
+  if (h->fuse_rho) { h->rho_pending = tidx; return 0; }
+  return rho_eos_launch(h, tidx, false);
 }
 int roms_prsgrd(roms_ctx* h) {
   CK(cudaSetDevice(h->device));
   const KP& p = h->kp;
+  bool fused = false;
+  if (h->rho_pending) {      // rho_eos of this time level is still due: EOS + vertical pressure integration in one sweep
+    const int tidx = h->rho_pending;
+    h->rho_pending = 0;
+    int rc = rho_eos_launch(h, tidx, true);
+    if (rc) return rc;
+    fused = true;
+  }
   if (h->c.nonlin_eos) {
-    COLUMN(k_prsgrd_vert<true>, 0, p.Lm, 0, p.Mm, p);
+    if (!fused) COLUMN(k_prsgrd_vert<true>, 0, p.Lm, 0, p.Mm, p);
     if (WALLED(h)) PLANE((k_prsgrd_horiz<true, true, KB_PRS>), p.iend, p.jstr, p.jend, (p.N + KB_PRS - 1) / KB_PRS, p);
     else PLANE((k_prsgrd_horiz<true, false, KB_PRS>), p.iend, p.jstr, p.jend, (p.N + KB_PRS - 1) / KB_PRS, p);
   } else {
-    COLUMN(k_prsgrd_vert<false>, 0, p.Lm, 0, p.Mm, p);
+    if (!fused) COLUMN(k_prsgrd_vert<false>, 0, p.Lm, 0, p.Mm, p);
     if (WALLED(h)) PLANE((k_prsgrd_horiz<false, true, KB_PRS>), p.iend, p.jstr, p.jend, (p.N + KB_PRS - 1) / KB_PRS, p);
     else PLANE((k_prsgrd_horiz<false, false, KB_PRS>), p.iend, p.jstr, p.jend, (p.N + KB_PRS - 1) / KB_PRS, p);
   }
   return 0;
 }
 int roms_pre_step3d(roms_ctx* h, int tile) {
+  FLUSH_RHO(h);
   (void)tile;
   CK(cudaSetDevice(h->device));
   const KP& p = h->kp;
@@ -632,6 +673,7 @@ int roms_pre_step3d(roms_ctx* h, int tile) {
   return 0;
 }
 int roms_step3d_uv1(roms_ctx* h, int tile) {
+  FLUSH_RHO(h);
   (void)tile;
   CK(cudaSetDevice(h->device));
   const KP& p = h->kp;
@@ -643,6 +685,7 @@ int roms_step3d_uv1(roms_ctx* h, int tile) {
   return 0;
 }
 int roms_step2d(roms_ctx* h) {
+  FLUSH_RHO(h);
   CK(cudaSetDevice(h->device));
   const KP& p = h->kp;
   const int iif = h->iif, kstp = h->kstp, knew = h->knew;
@@ -690,6 +733,7 @@ int roms_step2d(roms_ctx* h) {
   return exchange(h, {{s.zn, 1}, {s.un, 1}, {s.vn, 1}});
 }
 int roms_step3d_uv2(roms_ctx* h, int tile) {
+  FLUSH_RHO(h);
   (void)tile;
   CK(cudaSetDevice(h->device));
   const KP& p = h->kp;
@@ -711,6 +755,7 @@ int roms_step3d_uv2(roms_ctx* h, int tile) {
   return exchange(h, {{p.FlxV, p.N}, {h->v(nnew), p.N}, {h->vbar(knew), 1}});
 }
 int roms_step3d_t(roms_ctx* h, int tile) {
+  FLUSH_RHO(h);
   (void)tile;
   CK(cudaSetDevice(h->device));
   const KP& p = h->kp;
@@ -732,6 +777,7 @@ int roms_step3d_t(roms_ctx* h, int tile) {
 }
 // visc3d_S.F:4-134 (UV_VIS2).  Called between step3d_uv1 and the barotropic loop (main.F:448-450): u,v(3-nstp) hold Hz*u.
 int roms_visc3d(roms_ctx* h) {
+  FLUSH_RHO(h);
   CK(cudaSetDevice(h->device));
   const KP& p = h->kp;
   const int nstp = h->nstp, indx = 3 - nstp;
@@ -740,6 +786,7 @@ int roms_visc3d(roms_ctx* h) {
 }
 // t3dmix_S.F:4-258 (TS_DIF2 branch), every tracer, each followed by its exchange (:254-256)
 int roms_t3dmix(roms_ctx* h) {
+  FLUSH_RHO(h);
   CK(cudaSetDevice(h->device));
   const KP& p = h->kp;
   const int nrhs = h->nrhs, nnew = h->nnew;
@@ -751,6 +798,7 @@ int roms_t3dmix(roms_ctx* h) {
   return 0;
 }
 int roms_alfabeta(roms_ctx* h, double* alpha_host, double* beta_host) {
+  FLUSH_RHO(h);
   CK(cudaSetDevice(h->device));
   const KP& p = h->kp;
   const double* T = h->t(h->nstp, 1);
@@ -832,6 +880,7 @@ int roms_grid_stats(roms_ctx* h, double out[9]) {
   return 0;
 }
 int roms_diag(roms_ctx* h, double out[4]) {
+  FLUSH_RHO(h);
   CK(cudaSetDevice(h->device));
   const KP& p = h->kp;
   const int Lm = h->c.Lm, Mm = h->c.Mm, SXh = Lm + 4;
@@ -881,6 +930,7 @@ int roms_diag(roms_ctx* h, double out[4]) {
 
 // ---- driver: main.F:86-321 (tail of roms_init) and main.F:333-520 (roms_step) -------------------
 int roms_init_step0(roms_ctx* h) {
+  FLUSH_RHO(h);
   h->iic = 0; h->kstp = 1; h->knew = 1; h->iif = 1; h->nstp = 1; h->nnew = 1; h->nrhs = 1;
   h->forw_start = h->ntstart;
   int rc;
