@@ -81,7 +81,7 @@ def test_rivers_ana_startup_on_gpu():
 @pytest.mark.parametrize("case", ["channel", "filament", "channel_linear_odd", "channel_walls", "channel_walls_linear_odd",
                                   "seamount_island_walls", "seamount_island_periodic", "closed_basin", "closed_basin_seamount_odd",
                                   "ew_walls_ns_periodic", "channel_mixing", "closed_basin_seamount_mixing", "filament_mixing_switches",
-                                  "closed_basin_river", "walled_channel_river_mixing", "walled_channel_pipe", "closed_basin_river_pipe", "closed_basin_tide"])
+                                  "closed_basin_river", "walled_channel_river_mixing", "walled_channel_pipe", "closed_basin_river_pipe", "closed_basin_tide", "rivers_ana_without_kpp"])
 def test_routine_by_routine(case):
     if case == "channel":
         cfg, st = cases.channel(48, 40, 12)
@@ -116,6 +116,8 @@ def test_routine_by_routine(case):
         cfg, st = cases.channel(37, 31, 9, NT=3, ns_walls=True, ew_walls=True, river=True, pipe=True, dt=60.0)
     elif case == "closed_basin_tide":                                   # tidal potential in the surface pressure (prsgrd.F:209-211)
         cfg, st = cases.channel(40, 36, 8, ns_walls=True, ew_walls=True, seamount=True, tide=True)
+    elif case == "rivers_ana_without_kpp":                              # the reference's tests/Rivers_ana, uniform Akv/Akt instead of KPP
+        cfg, st = cases.rivers_ana(1.0e-4, 1.0e-5)
     elif case == "filament":
         cfg, st = cases.filament(64, 64, 32)
     else:
@@ -207,6 +209,23 @@ def test_river_source_budgets_and_100_steps():
     g.call("run", 96); o.call("run", 96)
     r100 = compare(g, o, cfg.NT, TOL100, cfg)
     print("river case, 100 steps:", r100)
+    g.close(); o.close()
+
+
+def test_rivers_ana_without_kpp_on_gpu():
+    """tests/Rivers_ana of the reference (closed walls, land mask, sloping bottom, nonlinear EOS, river) with uniform Akv/Akt in
+    place of KPP: 20 steps on the GPU are bit-identical to the oracle, and step 2 of the reference's log is met to 5e-9
+    (see tests/test_oracle_golden.py::test_rivers_ana_golden_without_kpp for what that pins)."""
+    G = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "rivers_ana_diag.json")))["diag"]
+    cfg, st = cases.rivers_ana(1.0e-4, 1.0e-5)
+    g, o = Roms(cfg), Oracle(cfg)
+    cases.initialize(g, st); cases.initialize(o, st)
+    g.call("run", 2); o.call("run", 2)
+    d = g.diag()
+    assert abs(d[0] / G[2]["KE"] - 1) < 5e-9 and abs(d[1] / G[2]["BAROTR_KE"] - 1) < 5e-9, d
+    g.call("run", 18); o.call("run", 18)
+    r = compare(g, o, cfg.NT, 1e-11, cfg)
+    print("Rivers_ana without KPP, 20 steps:", r)
     g.close(); o.close()
 
 

@@ -182,3 +182,34 @@ def test_pipe_source_budgets_oracle():
         assert np.all(np.abs(gain - 1.0) < 1e-6), gain
         b0 = b
     o.close()
+
+
+def test_rivers_ana_golden_without_kpp():
+    """The reference's Rivers_ana log (tests/golden/rivers_ana_diag.json) exercises what Filament does not: closed walls, a land
+    mask, a sloping bottom, the nonlinear split EOS, T+S and a river source -- but also the KPP closure (lmd_vmix/lmd_kpp,
+    SURVEY.md 8f-2), which this path does not have, so the log cannot be reproduced to round-off.  What CAN be checked: with
+    uniform Akv/Akt standing in for KPP the oracle stays within the mixing sensitivity of the log -- kinetic and barotropic
+    kinetic energy of step 2 (the first non-zero ones, driven by the river through step2d and the predictor) agree to 5e-9
+    relative for both Akv = 0 and Akv = 1e-4 m2/s, all four columns of steps 1-6 agree to 2e-3, and the two stand-ins BRACKET
+    the log's Courant numbers (deviations of opposite sign), i.e. the residual is the closure, not the dynamics."""
+    import json
+    import os
+    G = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "rivers_ana_diag.json")))["diag"]
+    dev = {}
+    for akv, akt in ((0.0, 0.0), (1.0e-4, 1.0e-5)):
+        cfg, st = cases.rivers_ana(akv, akt)
+        o = Oracle(cfg)
+        cases.initialize(o, st)
+        assert np.array_equal(o.diag(), np.zeros(4))             # log line 0: a state of rest
+        rows = []
+        for n in range(1, 7):
+            o.call("step")
+            d = o.diag()
+            g = np.array([G[n]["KE"], G[n]["BAROTR_KE"], G[n]["MAX_ADV_CFL"], G[n]["MAX_VERT_CFL"]])
+            rows.append(np.where(g != 0, (d - g) / np.where(g != 0, g, 1.0), d))
+        o.close()
+        dev[akv] = np.array(rows)
+        assert np.all(dev[akv][0, :2] == 0.0)                     # step 1: still at rest, exactly as the log
+        assert np.all(np.abs(dev[akv][1, :2]) < 5e-9), dev[akv][1]
+        assert np.all(np.abs(dev[akv]) < 2e-3), dev[akv]
+    assert np.all(dev[0.0][:, 2:] > 0) and np.all(dev[1.0e-4][:, 2:] < 0)

@@ -296,6 +296,32 @@ def rivers_ana_grid():
     return cfg, st
 
 
+def rivers_ana(akv=0.0, akt=0.0):
+    """The reference's tests/Rivers_ana case without its KPP closure: grid and mask of `rivers_ana_grid`, ana_init.h (rest,
+    T = 4 + 10 exp(z/50), S = 36), zero surface forcing (analytical.F:216-305), the analytic river of river_frc.F:125-137 /
+    ana_frc_river.h (20 coast cells at the head of the channel share 500 m3/s of 24 degC, 1 PSU water).  Akv, Akt are uniform
+    stand-ins for what lmd_vmix/lmd_kpp would compute."""
+    cfg, st = rivers_ana_grid()
+    N = cfg.N
+    sy, sx = cfg.Mm + 4, cfg.Lm + 4
+    h, rmask = st["H"], st["RMASK"]
+    z_r, z_w = _depths(h, np.zeros_like(h), N, cfg.theta_s, cfg.theta_b, cfg.hc)
+    T = 4.0 + 10.0 * np.exp(z_r / 50.0)
+    S = np.full_like(T, 36.0)
+    zero2, zero3 = np.zeros((sy, sx)), np.zeros_like(T)
+    xr = 100.0 * (np.arange(-1, cfg.Lm + 3)[None, :] + np.zeros((sy, 1)) - 0.5)
+    ridx = np.zeros_like(rmask); rfrc = np.zeros_like(rmask)
+    head = np.zeros_like(rmask, dtype=bool)
+    head[:-1, :] = (rmask[:-1, :] == 0) & (rmask[1:, :] == 1) & (xr[:-1, :] > 4000.0) & (xr[:-1, :] < 6000.0)
+    ridx[head] = 1.0; rfrc[head] = 1.0 / 20.0
+    ru, rv = river_faces(rmask, ridx, rfrc)
+    st.update({"ZETA": {(1, 1): zero2}, "UBAR": {(1, 1): zero2}, "VBAR": {(1, 1): zero2}, "U": {(1, 1): zero3, (2, 1): zero3},
+               "V": {(1, 1): zero3, (2, 1): zero3}, "T": {(1, 1): T, (2, 1): T, (1, 2): S, (2, 2): S},
+               "AKV": np.full((N + 1, sy, sx), akv), "AKT": {(1, 1): np.full((N + 1, sy, sx), akt), (1, 2): np.full((N + 1, sy, sx), akt)},
+               "RIV_UFLX": ru, "RIV_VFLX": rv, "RIVERS": [(5.0e2, [24.0, 1.0])]})
+    return cfg, st
+
+
 def initialize(model, state):
     """roms_init (main.F:86-321) for a host without Fortran: push the analytic fields, derive the
     grid metrics, then set_depth / set_HUV / omega / rho_eos."""
