@@ -62,6 +62,12 @@ struct Orc {
   vec pipe_idx, pipe_flx;
   std::vector<vec> pipe_prf, pipe_trc;
   bool pipe_source = false;
+  // LMD/KPP vertical mixing closure (lmd_vmix.F, lmd_kpp.F, lmd_swr_frac.F; cppdefs LMD_MIXING LMD_KPP LMD_BKPP LMD_RIMIX LMD_NONLOCAL)
+  bool lmd_kpp = false;
+  vec bvf, swr_frac, ghat;   // (0:N): Brunt-Vaisala frequency^2 (rho_eos.F), solar penetration fraction, nonlocal transport
+  vec hbls, hbbl;            // surface / bottom boundary layer thickness (mixing.F:143,151, start at 0)
+  vec srflx;                 // shortwave flux (surf_flux.F), zero unless pushed
+  double Akv_bak = 0.0, Akt_bak[2] = {0.0, 0.0};
   vec ptide;                 // tides.F:26 equilibrium tidal potential [m]
   bool pot_tides = false;
   vec xr;  // only for the Filament analytic initial condition
@@ -493,6 +499,19 @@ void rho_eos(Orc& o, int tidx) {
                       Ts * (K10 + Tt * (K11 + Tt * (K12 + Tt * K13)) + sqrtTs * (KS0 + Tt * (KS1 + Tt * KS2)));
           A3(o.qp1, i, j, k) = 0.1 * (rho0 + A3(o.rho1, i, j, k)) * (K0_Duk - K0) / ((K00 + K0) * (K00 + K0_Duk)) * A2(o.rmask, i, j);
         }
+      if (o.lmd_kpp) {   // rho_eos.F (LMD_KPP): Brunt-Vaisala frequency from the adiabatic elementary differences
+        const double cff = o.c.g / rho0;
+        for (int k = 1; k <= N - 1; ++k)
+          for (int i = iX0; i <= iX1; ++i) {
+            const double dpth = -0.5 * (A3(o.z_r, i, j, k + 1) + A3(o.z_r, i, j, k));
+            AW(o.bvf, i, j, k) = -cff * (A3(o.rho1, i, j, k + 1) - A3(o.rho1, i, j, k) + (A3(o.qp1, i, j, k + 1) - A3(o.qp1, i, j, k)) * dpth * (1. - qp2 * dpth)) /
+                                 (A3(o.z_r, i, j, k + 1) - A3(o.z_r, i, j, k)) * A2(o.rmask, i, j);
+          }
+        for (int i = iX0; i <= iX1; ++i) {
+          AW(o.bvf, i, j, N) = AW(o.bvf, i, j, N - 1);
+          AW(o.bvf, i, j, 0) = AW(o.bvf, i, j, 1);
+        }
+      }
     }
     for (int i = iX0; i <= iX1; ++i) {
       double cff;
@@ -1750,6 +1769,309 @@ void alfabeta(Orc& o, double* alpha, double* beta) {
     }
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// lmd_swr_frac.F: fraction of the solar shortwave flux penetrating to each w-level (Jerlov water type 1)
+void lmd_swr_frac(Orc& o) {
+  GEOM
+  const double mu1 = 0.35, mu2 = 23.0, r1 = 0.58;
+  const double attn1 = -1. / mu1, attn2 = -1. / mu2;
+  for (int j = jstr; j <= jend; ++j)
+    for (int i = istr; i <= iend; ++i) {
+      double swdk1 = r1, swdk2 = 1. - swdk1;
+      AW(o.swr_frac, i, j, N) = 1.;
+      for (int k = N; k >= 1; --k) {
+        const double xi1 = attn1 * A3(o.Hz, i, j, k);
+        if (xi1 > -20.) swdk1 = swdk1 * exp(xi1); else swdk1 = 0.;
+        const double xi2 = attn2 * A3(o.Hz, i, j, k);
+        if (xi2 > -20.) swdk2 = swdk2 * exp(xi2); else swdk2 = 0.;
+        AW(o.swr_frac, i, j, k - 1) = swdk1 + swdk2;
+      }
+    }
+  exchange(o, o.swr_frac.data(), N + 1);
+}
+// the masked isotropic smoothing of a 2-D field used by lmd_vmix (Rig) and lmd_kpp (hbl, bbl): boundary copies on closed
+// edges, masked elementary differences, transversal terms, 3/16 Laplacian update (lmd_vmix.F:155-246, lmd_kpp_smooth_hbl.h)
+static void lmd_smooth(Orc& o, double* a, int imin, int imax, int jmin, int jmax, vec& FX, vec& FE, vec& FE1, bool mask_result) {
+  GEOM
+  if (WWALL) for (int j = jmin; j <= jmax; ++j) A2(a, istr - 1, j) = A2(a, istr, j);
+  if (EWALL) for (int j = jmin; j <= jmax; ++j) A2(a, iend + 1, j) = A2(a, iend, j);
+  if (SWALL) for (int i = imin; i <= imax; ++i) A2(a, i, jstr - 1) = A2(a, i, jstr);
+  if (NWALL) for (int i = imin; i <= imax; ++i) A2(a, i, jend + 1) = A2(a, i, jend);
+  if (WWALL && SWALL) A2(a, istr - 1, jstr - 1) = A2(a, istr, jstr);
+  if (WWALL && NWALL) A2(a, istr - 1, jend + 1) = A2(a, istr, jend);
+  if (EWALL && SWALL) A2(a, iend + 1, jstr - 1) = A2(a, iend, jstr);
+  if (EWALL && NWALL) A2(a, iend + 1, jend + 1) = A2(a, iend, jend);
+  const double cff = 1. / 12., cff1 = 3. / 16.;
+  for (int j = jstr - 1; j <= jend + 1; ++j)
+    for (int i = istr; i <= iend + 1; ++i) A2(FX, i, j) = (A2(a, i, j) - A2(a, i - 1, j)) * A2(o.umask, i, j);
+  for (int j = jstr; j <= jend + 1; ++j) {
+    for (int i = istr - 1; i <= iend + 1; ++i) A2(FE1, i, j) = (A2(a, i, j) - A2(a, i, j - 1)) * A2(o.vmask, i, j);
+    for (int i = istr; i <= iend; ++i) A2(FE, i, j) = A2(FE1, i, j) + cff * (A2(FX, i + 1, j) + A2(FX, i, j - 1) - A2(FX, i, j) - A2(FX, i + 1, j - 1));
+  }
+  for (int j = jstr; j <= jend; ++j) {
+    for (int i = istr; i <= iend + 1; ++i) A2(FX, i, j) = A2(FX, i, j) + cff * (A2(FE1, i, j + 1) + A2(FE1, i - 1, j) - A2(FE1, i, j) - A2(FE1, i - 1, j + 1));
+    for (int i = istr; i <= iend; ++i) {
+      A2(a, i, j) = A2(a, i, j) + cff1 * (A2(FX, i + 1, j) - A2(FX, i, j) + A2(FE, i, j + 1) - A2(FE, i, j));
+      if (mask_result) A2(a, i, j) = A2(a, i, j) * A2(o.rmask, i, j);
+    }
+  }
+}
+// lmd_vmix.F:31-433 (LMD_RIMIX; no LMD_DDMIX; the LMD_CONVEC block is swallowed by the traditional cpp of the reference's build:
+// an apostrophe in the comment above it): interior mixing Kv,Kt,Ks(0:N), then lmd_kpp_tile below
+void lmd_kpp(Orc& o, int tind, vec& Kv, vec& Kt, vec& Ks);
+void lmd_vmix(Orc& o, int tind) {
+  GEOM
+  const double Ri0 = 0.7, nu0m = 1.e-2, nu0s = 1.e-2, nuwm = 1.0e-4, nuws = 0.1e-4, Lturb = 10., pi = 3.14159265358979323;
+  const int imin = WWALL ? istr : istr - 1, imax = EWALL ? iend : iend + 1, jmin = SWALL ? jstr : jstr - 1, jmax = NWALL ? jend : jend + 1;
+  const vec &u = o.u[tind - 1], &v = o.v[tind - 1];
+  vec Kv(SXY * (N + 1), 0.0), Kt(SXY * (N + 1), 0.0), Ks(SXY * (N + 1), 0.0), Rig(SXY * (N + 1), 0.0), FX(SXY, 0.0), FE(SXY, 0.0), FE1(SXY, 0.0);
+  for (int k = 1; k <= N - 1; ++k) {
+    for (int j = jmin; j <= jmax; ++j)
+      for (int i = imin; i <= imax; ++i) {
+        const double cff = 0.5 / (A3(o.z_r, i, j, k + 1) - A3(o.z_r, i, j, k));
+        const double dudz = cff * (A3(u, i, j, k + 1) - A3(u, i, j, k) + A3(u, i + 1, j, k + 1) - A3(u, i + 1, j, k));
+        const double dvdz = cff * (A3(v, i, j, k + 1) - A3(v, i, j, k) + A3(v, i, j + 1, k + 1) - A3(v, i, j + 1, k));
+        AW(Rig, i, j, k) = AW(o.bvf, i, j, k) / (Ri0 * std::max(dudz * dudz + dvdz * dvdz, 1.E-10));
+      }
+    lmd_smooth(o, &Rig[(size_t)k * SXY], imin, imax, jmin, jmax, FX, FE, FE1, false);
+    for (int j = jstr; j <= jend; ++j)
+      for (int i = istr; i <= iend; ++i) {
+        const double cff = std::min(1., std::max(0., AW(Rig, i, j, k)));
+        double nu_sx = 1. - cff * cff;
+        nu_sx = nu_sx * nu_sx * nu_sx;
+        AW(Kv, i, j, k) = nuwm + nu0m * nu_sx;
+        AW(Kt, i, j, k) = nuws + nu0s * nu_sx;
+        AW(Ks, i, j, k) = AW(Kt, i, j, k);
+      }
+  }
+  for (int k = 1; k <= N - 1; ++k)       // suppress mixing near the bottom
+    for (int j = jstr; j <= jend; ++j)
+      for (int i = istr; i <= iend; ++i) {
+        const double dist = AW(o.z_w, i, j, k) - AW(o.z_w, i, j, 0);
+        if (dist < Lturb) {
+          const double mult = sin(0.5 * pi * (AW(o.z_w, i, j, k) - AW(o.z_w, i, j, 0)) / Lturb);
+          AW(Kv, i, j, k) = AW(Kv, i, j, k) * mult;
+          AW(Kt, i, j, k) = AW(Kt, i, j, k) * mult;
+          AW(Ks, i, j, k) = AW(Ks, i, j, k) * mult;
+        }
+      }
+  for (int j = jstr; j <= jend; ++j)
+    for (int i = istr; i <= iend; ++i) {
+      AW(Kv, i, j, N) = AW(Kv, i, j, N - 1) + o.Akv_bak;
+      AW(Ks, i, j, N) = AW(Ks, i, j, N - 1) + o.Akt_bak[1];
+      AW(Kt, i, j, N) = AW(Kt, i, j, N - 1) + o.Akt_bak[0];
+      AW(Kv, i, j, 0) = AW(Kv, i, j, 1) + o.Akv_bak;
+      AW(Ks, i, j, 0) = AW(Ks, i, j, 1) + o.Akt_bak[1];
+      AW(Kt, i, j, 0) = AW(Kt, i, j, 1) + o.Akt_bak[0];
+    }
+  for (int k = 1; k <= N - 1; ++k)       // in-place 1-2-1 filter, ascending (uses the already filtered level below)
+    for (int j = jstr; j <= jend; ++j)
+      for (int i = istr; i <= iend; ++i) {
+        AW(Kv, i, j, k) = 0.5 * AW(Kv, i, j, k) + 0.25 * AW(Kv, i, j, k - 1) + 0.25 * AW(Kv, i, j, k + 1) + o.Akv_bak;
+        AW(Kt, i, j, k) = 0.5 * AW(Kt, i, j, k) + 0.25 * AW(Kt, i, j, k - 1) + 0.25 * AW(Kt, i, j, k + 1) + o.Akt_bak[0];
+        AW(Ks, i, j, k) = 0.5 * AW(Ks, i, j, k) + 0.25 * AW(Ks, i, j, k - 1) + 0.25 * AW(Ks, i, j, k + 1) + o.Akt_bak[1];
+      }
+  lmd_kpp(o, tind, Kv, Kt, Ks);
+}
+// lmd_kpp.F (INT_AT_RHO_POINTS, SMOOTH_HBL, LMD_BKPP, LMD_NONLOCAL): surface and bottom boundary layer depths from the
+// integral bulk-Richardson criterion, KPP shape functions blended into Kv,Kt,Ks, result to Akv, Akt, hbls, hbbl, ghat
+void lmd_kpp(Orc& o, int tind, vec& Kv, vec& Kt, vec& Ks) {
+  GEOM
+  const double Ricr = 0.15, Ri_inv = 1. / Ricr, epssfc = 0.1, betaT = -0.2, Cv = 1.8, C_Ek = 258., Cstar = 10., zeta_m = -0.2, a_m = 1.257, c_m = 8.360,
+               zeta_s = -1.0, a_s = -28.86, c_s = 98.96, r2 = 0.5, r3 = 1. / 3., r4 = 0.25, EPS = 1.E-20, vonKar = 0.41;
+  const int imin = WWALL ? istr : istr - 1, imax = EWALL ? iend : iend + 1, jmin = SWALL ? jstr : jstr - 1, jmax = NWALL ? jend : jend + 1;
+  const vec &u = o.u[tind - 1], &v = o.v[tind - 1], &un = o.u[o.nstp - 1], &vn = o.v[o.nstp - 1];
+  const double g = o.c.g, Zob = o.c.Zob;
+  const double Cg = Cstar * vonKar * pow(c_s * vonKar * epssfc, 1. / 3.);
+  const double Vtc = Cv * sqrt(-betaT / (c_s * epssfc)) / (Ricr * (vonKar * vonKar));
+  vec ustar(SXY, 0.0), Bo(SXY, 0.0), Bosol(SXY, 0.0), hbl(SXY, 0.0), bbl(SXY, 0.0), FX(SXY, 0.0), FE(SXY, 0.0), FE1(SXY, 0.0);
+  alfabeta(o, Bosol.data(), Bo.data());       // alpha -> Bosol, beta -> Bo (lmd_kpp.F:156)
+  vec Cr((size_t)SX * (N + 1)), FC((size_t)SX * (N + 1)), wrk1((size_t)SX * (N + 1)), Bfsfc_bl(SX);
+  std::vector<int> kbls(SX), kbbl(SX);
+#define I1(a, i) (a)[(i) + 1]
+  for (int j = jmin; j <= jmax; ++j) {
+    for (int i = imin; i <= imax; ++i) {
+      A2(Bo, i, j) = g * (A2(Bosol, i, j) * (A2(o.stflx[0], i, j) - A2(o.srflx, i, j)) - A2(Bo, i, j) * (o.NT >= 2 ? A2(o.stflx[1], i, j) : 0.0));
+      A2(Bosol, i, j) = g * A2(Bosol, i, j) * A2(o.srflx, i, j);
+      // sustr_r, svstr_r: wind stress at rho points (surf_flux.F); here the mean of the two faces
+      const double sr = 0.5 * (A2(o.sustr, i, j) + A2(o.sustr, i + 1, j)), vr = 0.5 * (A2(o.svstr, i, j) + A2(o.svstr, i, j + 1));
+      A2(ustar, i, j) = sqrt(sqrt(sr * sr + vr * vr));
+      A2(hbl, i, j) = A2(o.hbls, i, j);
+      A2(bbl, i, j) = A2(o.hbbl, i, j);
+      I1(kbls, i) = 0;
+      SL(Cr, i, N) = 0.;
+      SL(Cr, i, 0) = 0.;
+      SL(FC, i, N) = 0.;
+    }
+    for (int k = N - 1; k >= 1; --k)
+      for (int i = imin; i <= imax; ++i) {
+        const double du = AW(o.z_w, i, j, N) - AW(o.z_w, i, j, k), dd = AW(o.z_w, i, j, k) - AW(o.z_w, i, j, 0);
+        const double cff_up = du * du, cff_dn = dd * dd;
+        const double eh = epssfc * A2(hbl, i, j), eb = epssfc * A2(bbl, i, j);
+        const double Kern = cff_up * cff_dn / ((cff_up + eh * eh) * (cff_dn + eb * eb));
+        const double su = A3(u, i, j, k + 1) + A3(u, i + 1, j, k + 1) - A3(u, i, j, k) - A3(u, i + 1, j, k);
+        const double sv = A3(v, i, j, k + 1) + A3(v, i, j + 1, k + 1) - A3(v, i, j, k) - A3(v, i, j + 1, k);
+        SL(FC, i, k) = SL(FC, i, k + 1) +
+                       Kern * (0.5 * (su * su + sv * sv) / (A3(o.Hz, i, j, k) + A3(o.Hz, i, j, k + 1)) -
+                               0.5 * (A3(o.Hz, i, j, k) + A3(o.Hz, i, j, k + 1)) * (Ri_inv * AW(o.bvf, i, j, k) + C_Ek * A2(o.f, i, j) * A2(o.f, i, j)));
+      }
+    for (int i = imin; i <= imax; ++i) {
+      const double z_bl = AW(o.z_w, i, j, 0) + 0.25 * A3(o.Hz, i, j, 1);
+      const double du = AW(o.z_w, i, j, N) - z_bl, dd = z_bl - AW(o.z_w, i, j, 0);
+      const double cff_up = du * du, cff_dn = dd * dd;
+      const double eh = epssfc * A2(hbl, i, j), eb = epssfc * A2(bbl, i, j);
+      const double Kern = cff_up * cff_dn / ((cff_up + eh * eh) * (cff_dn + eb * eb));
+      const double su = A3(u, i, j, 1) + A3(u, i + 1, j, 1), sv = A3(v, i, j, 1) + A3(v, i, j + 1, 1);
+      SL(FC, i, 0) = SL(FC, i, 1) + Kern * (0.5 * (su * su + sv * sv) / A3(o.Hz, i, j, 1) -
+                                            0.5 * A3(o.Hz, i, j, 1) * (Ri_inv * AW(o.bvf, i, j, 1) + C_Ek * A2(o.f, i, j) * A2(o.f, i, j)));
+    }
+    for (int k = N; k >= 1; --k)
+      for (int i = imin; i <= imax; ++i) {
+        SL(wrk1, i, k) = sqrt(AW(o.swr_frac, i, j, k) * AW(o.swr_frac, i, j, k - 1));
+        double zscale = AW(o.z_w, i, j, N) - A3(o.z_r, i, j, k);
+        const double Bfsfc = A2(Bo, i, j) + A2(Bosol, i, j) * (1. - SL(wrk1, i, k));
+        zscale = std::min(zscale, A2(hbl, i, j) * epssfc);
+        zscale = zscale * A2(o.rmask, i, j);
+        const double zetahat = vonKar * zscale * Bfsfc;
+        const double us = A2(ustar, i, j), ustar3 = us * us * us;
+        double ws;
+        if (zetahat >= 0.) ws = vonKar * us * ustar3 / std::max(ustar3 + 5. * zetahat, 1.E-20);
+        else if (zetahat > zeta_s * ustar3) ws = vonKar * pow((ustar3 - 16. * zetahat) / us, r2);
+        else ws = vonKar * pow(a_s * ustar3 - c_s * zetahat, r3);
+        const double Vtsq = 1.8 * Vtc * ws * sqrt(std::max(1.e-5, AW(o.bvf, i, j, k - 1)));
+        SL(Cr, i, k) = SL(FC, i, k) + Vtsq;
+        if (I1(kbls, i) == 0 && SL(Cr, i, k) < 0.) I1(kbls, i) = k;
+      }
+    for (int i = imin; i <= imax; ++i) {
+      if (I1(kbls, i) > 0) {
+        const int k = I1(kbls, i);
+        if (k == N) A2(hbl, i, j) = AW(o.z_w, i, j, N) - A3(o.z_r, i, j, N);
+        else A2(hbl, i, j) = AW(o.z_w, i, j, N) - (A3(o.z_r, i, j, k) * SL(Cr, i, k + 1) - A3(o.z_r, i, j, k + 1) * SL(Cr, i, k)) / (SL(Cr, i, k + 1) - SL(Cr, i, k));
+      } else A2(hbl, i, j) = AW(o.z_w, i, j, N) - AW(o.z_w, i, j, 0);
+      A2(hbl, i, j) = A2(hbl, i, j) * A2(o.rmask, i, j);
+    }
+    for (int i = imin; i <= imax; ++i) { I1(kbbl, i) = 0; SL(Cr, i, 0) = 0.; }
+    for (int k = 1; k <= N; ++k)
+      for (int i = imin; i <= imax; ++i) {
+        SL(Cr, i, k) = SL(FC, i, k) - SL(FC, i, 0);
+        if (I1(kbbl, i) == 0 && SL(Cr, i, k) > 0.) I1(kbbl, i) = k;
+      }
+    for (int i = imin; i <= imax; ++i) {
+      if (I1(kbbl, i) > 0) {
+        const int k = I1(kbbl, i);
+        if (k == 1) A2(bbl, i, j) = A3(o.z_r, i, j, 1) - AW(o.z_w, i, j, 0);
+        else A2(bbl, i, j) = (A3(o.z_r, i, j, k - 1) * SL(Cr, i, k) - A3(o.z_r, i, j, k) * SL(Cr, i, k - 1)) / (SL(Cr, i, k) - SL(Cr, i, k - 1)) - AW(o.z_w, i, j, 0);
+      } else A2(bbl, i, j) = AW(o.z_w, i, j, N) - AW(o.z_w, i, j, 0);
+      A2(bbl, i, j) = A2(bbl, i, j) * A2(o.rmask, i, j);
+    }
+  }
+  lmd_smooth(o, hbl.data(), imin, imax, jmin, jmax, FX, FE, FE1, true);
+  lmd_smooth(o, bbl.data(), imin, imax, jmin, jmax, FX, FE, FE1, true);
+  for (int j = jstr; j <= jend; ++j) {
+    if (!(o.iic == o.forw_start))
+      for (int i = istr; i <= iend; ++i) {
+        A2(hbl, i, j) = 0.5 * (A2(hbl, i, j) + A2(o.hbls, i, j));
+        A2(bbl, i, j) = 0.5 * (A2(bbl, i, j) + A2(o.hbbl, i, j));
+      }
+    for (int i = istr; i <= iend; ++i) I1(kbls, i) = N;
+    for (int k = N - 1; k >= 1; --k)
+      for (int i = istr; i <= iend; ++i)
+        if (AW(o.z_w, i, j, k) > AW(o.z_w, i, j, N) - A2(hbl, i, j)) I1(kbls, i) = k;
+    for (int i = istr; i <= iend; ++i) {
+      const int k = I1(kbls, i);
+      const double z_bl = AW(o.z_w, i, j, N) - A2(hbl, i, j);
+      double Bfsfc;
+      if (AW(o.swr_frac, i, j, k - 1) > 0.)
+        Bfsfc = A2(Bo, i, j) + A2(Bosol, i, j) * (1. - AW(o.swr_frac, i, j, k - 1) * AW(o.swr_frac, i, j, k) * (AW(o.z_w, i, j, k) - AW(o.z_w, i, j, k - 1)) /
+                                                           (AW(o.swr_frac, i, j, k) * (AW(o.z_w, i, j, k) - z_bl) + AW(o.swr_frac, i, j, k - 1) * (z_bl - AW(o.z_w, i, j, k - 1))));
+      else Bfsfc = A2(Bo, i, j) + A2(Bosol, i, j);
+      I1(Bfsfc_bl, i) = Bfsfc;      // (the wm, ws evaluated here by the reference are not used)
+    }
+    for (int i = istr; i <= iend; ++i)
+      for (int k = N; k >= 0; --k) {
+        const double Bfsfc = I1(Bfsfc_bl, i);
+        double zscale = AW(o.z_w, i, j, N) - AW(o.z_w, i, j, k);
+        zscale = std::min(zscale, A2(hbl, i, j) * epssfc);
+        zscale = zscale * A2(o.rmask, i, j);
+        const double zetahat = vonKar * zscale * Bfsfc;
+        const double us = A2(ustar, i, j), ustar3 = us * us * us;
+        double wm, ws;
+        if (zetahat >= 0.) {
+          wm = vonKar * us * ustar3 / std::max(ustar3 + 5. * zetahat, 1.E-20);
+          ws = wm;
+        } else {
+          if (zetahat > zeta_m * ustar3) wm = vonKar * pow(us * (ustar3 - 16. * zetahat), r4);
+          else wm = vonKar * pow(a_m * ustar3 - c_m * zetahat, r3);
+          if (zetahat > zeta_s * ustar3) ws = vonKar * pow((ustar3 - 16. * zetahat) / us, r2);
+          else ws = vonKar * pow(a_s * ustar3 - c_s * zetahat, r3);
+        }
+        const double ssgm = (AW(o.z_w, i, j, N) - AW(o.z_w, i, j, k)) / std::max(A2(hbl, i, j), EPS);
+        if (ssgm < 1.) {
+          double cff;
+          if (ssgm < 0.07) cff = 0.5 * ((ssgm - 0.07) * (ssgm - 0.07)) / 0.07;
+          else cff = 0.;
+          cff = cff + ssgm * ((1. - ssgm) * (1. - ssgm));
+          const double amp = ssgm * ssgm;
+          const double akv = amp * AW(Kv, i, j, k), akt = amp * AW(Kt, i, j, k), aks = amp * AW(Ks, i, j, k);
+          const double bm = wm * A2(hbl, i, j) * cff, bs = ws * A2(hbl, i, j) * cff;
+          AW(Kv, i, j, k) = sqrt(akv * akv + bm * bm);
+          AW(Kt, i, j, k) = sqrt(akt * akt + bs * bs);
+          AW(Ks, i, j, k) = sqrt(aks * aks + bs * bs);
+          if (Bfsfc < 0.) AW(o.ghat, i, j, k) = -Cg * ssgm * ((1. - ssgm) * (1. - ssgm));
+          else AW(o.ghat, i, j, k) = 0.;
+        } else AW(o.ghat, i, j, k) = 0.;
+      }
+    for (int i = istr; i <= iend; ++i) I1(kbbl, i) = N;
+    for (int k = N - 1; k >= 1; --k)
+      for (int i = istr; i <= iend; ++i)
+        if (AW(o.z_w, i, j, k) > AW(o.z_w, i, j, 0) + A2(bbl, i, j)) I1(kbbl, i) = k;
+    for (int i = istr; i <= iend; ++i) {
+      const double u0 = A3(un, i, j, 1), u1 = A3(un, i + 1, j, 1), v0 = A3(vn, i, j, 1), v1 = A3(vn, i, j + 1, 1);
+      const double wmb = vonKar * vonKar * sqrt(0.333333333333 * (u0 * u0 + u1 * u1 + u0 * u1 + v0 * v0 + v1 * v1 + v0 * v1)) / log(1. + 0.5 * A3(o.Hz, i, j, 1) / Zob);
+      const double wsb = wmb;
+      for (int k = 0; k <= N; ++k) {
+        const double sgmb = (AW(o.z_w, i, j, k) - AW(o.z_w, i, j, 0) + Zob) / (A2(bbl, i, j) + Zob);
+        if (sgmb < 1.) {
+          const double cff1 = sgmb * ((1. - sgmb) * (1. - sgmb));
+          const double bm = wmb * A2(bbl, i, j) * cff1, bs = wsb * A2(bbl, i, j) * cff1;
+          AW(Kv, i, j, k) = sqrt(AW(Kv, i, j, k) * AW(Kv, i, j, k) + bm * bm);
+          AW(Kt, i, j, k) = sqrt(AW(Kt, i, j, k) * AW(Kt, i, j, k) + bs * bs);
+          AW(Ks, i, j, k) = sqrt(AW(Ks, i, j, k) * AW(Ks, i, j, k) + bs * bs);
+        }
+      }
+    }
+    for (int i = istr; i <= iend; ++i) {
+      const bool wet = A2(o.rmask, i, j) > 0.5;
+      for (int k = 0; k <= N; ++k) {
+        AW(o.Akv, i, j, k) = wet ? AW(Kv, i, j, k) : 0.;
+        AW(o.Akt[0], i, j, k) = wet ? AW(Kt, i, j, k) : 0.;
+        AW(o.Akt[1], i, j, k) = wet ? AW(Ks, i, j, k) : 0.;
+      }
+    }
+  }
+#undef I1
+  auto share = [&](vec& dst, const vec& src) {      // copy into the shared array and pad the ghost points of closed edges
+    for (int j = jstr; j <= jend; ++j)
+      for (int i = istr; i <= iend; ++i) A2(dst, i, j) = A2(src, i, j);
+    if (WWALL) for (int j = jstr; j <= jend; ++j) A2(dst, istr - 1, j) = A2(dst, istr, j);
+    if (EWALL) for (int j = jstr; j <= jend; ++j) A2(dst, iend + 1, j) = A2(dst, iend, j);
+    if (SWALL) for (int i = istr; i <= iend; ++i) A2(dst, i, jstr - 1) = A2(dst, i, jstr);
+    if (NWALL) for (int i = istr; i <= iend; ++i) A2(dst, i, jend + 1) = A2(dst, i, jend);
+    if (WWALL && SWALL) A2(dst, istr - 1, jstr - 1) = A2(dst, istr, jstr);
+    if (WWALL && NWALL) A2(dst, istr - 1, jend + 1) = A2(dst, istr, jend);
+    if (EWALL && SWALL) A2(dst, iend + 1, jstr - 1) = A2(dst, iend, jstr);
+    if (EWALL && NWALL) A2(dst, iend + 1, jend + 1) = A2(dst, iend, jend);
+  };
+  share(o.hbls, hbl);
+  share(o.hbbl, bbl);
+  exchange(o, o.Akv.data(), N + 1);
+  exchange(o, o.hbls.data(), 1);
+  exchange(o, o.hbbl.data(), 1);
+  exchange(o, o.Akt[0].data(), N + 1);
+  exchange(o, o.Akt[1].data(), N + 1);
+}
+
 // ---------------------------------------------------------------------------------------------
 // Filament analytic case: tests/Filament/ana_grid.h, ana_init.h (analytical.F:ana_init)
 void init_filament(Orc& o) {
@@ -1836,6 +2158,7 @@ void init_step0(Orc& o) {
   o.iic = 0; o.kstp = 1; o.knew = 1; o.iif = 1; o.nstp = 1; o.nnew = 1; o.nrhs = 1;
   o.forw_start = o.ntstart;
   set_depth(o);
+  if (o.lmd_kpp) lmd_swr_frac(o);      // main.F:219
   set_HUV(o);
   omega(o);
   rho_eos(o, o.nrhs);
@@ -1849,12 +2172,14 @@ void step(Orc& o) {
   rho_eos(o, o.nrhs);
   set_HUV(o);
   omega(o);
+  if (o.lmd_kpp) lmd_vmix(o, o.nstp);      // main.F:408-410
   prsgrd(o);
   pre_step3d(o);
   set_HUV1(o);
   o.nrhs = 3; o.nnew = 3 - o.nstp;
   omega(o);
   rho_eos(o, o.nrhs);
+  if (o.lmd_kpp) lmd_vmix(o, o.nrhs);      // main.F:434-436
   prsgrd(o);
   step3d_uv1(o);
   if (o.c.uv_vis2) visc3d(o);          // main.F:448-450
@@ -1928,6 +2253,8 @@ int orc_create(const roms_cfg* cfg, void** out) {
   o->riv_uflx.assign(n2, 0.0); o->riv_vflx.assign(n2, 0.0);
   o->pipe_idx.assign(n2, 0.0); o->pipe_flx.assign(n2, 0.0);
   o->ptide.assign(n2, 0.0);
+  o->hbls.assign(n2, 0.0); o->hbbl.assign(n2, 0.0); o->srflx.assign(n2, 0.0);
+  o->bvf.assign(nw, 0.0); o->swr_frac.assign(nw, 0.0); o->ghat.assign(nw, 0.0);
   o->stflx.assign(o->NT, vec(n2, 0.0));
   o->diff2.assign(o->NT, vec(n2, 0.0));
   for (int l = 0; l < 3; ++l) {
@@ -1995,6 +2322,13 @@ int orc_set_pipe(void* h, int ipipe, const double* prf, const double* trc) {
   for (int k = 0; k < o.N; ++k) o.pipe_prf[ipipe - 1][k] = prf[k];
   for (int it = 0; it < o.NT; ++it) o.pipe_trc[ipipe - 1][it] = trc[it];
   o.pipe_source = true;
+  return 0;
+}
+// cppdefs LMD_MIXING/LMD_KPP/...: switch the vertical mixing closure on (call before init_step0: rho_eos then also fills bvf)
+int orc_set_kpp(void* h, int on) { ((Orc*)h)->lmd_kpp = on != 0; return 0; }
+int orc_get_hbl(void* h, double* hbls, double* hbbl) {
+  Orc& o = *(Orc*)h;
+  memcpy(hbls, o.hbls.data(), o.SXY * sizeof(double)); memcpy(hbbl, o.hbbl.data(), o.SXY * sizeof(double));
   return 0;
 }
 int orc_set_pot_tides(void* h, int on) { ((Orc*)h)->pot_tides = on != 0; return 0; }
