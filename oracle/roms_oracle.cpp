@@ -64,6 +64,8 @@ struct Orc {
   bool pipe_source = false;
   // LMD/KPP vertical mixing closure (lmd_vmix.F, lmd_kpp.F, lmd_swr_frac.F; cppdefs LMD_MIXING LMD_KPP LMD_BKPP LMD_RIMIX LMD_NONLOCAL)
   bool lmd_kpp = false;
+  bool lmd_convec = false;   // the LMD_CONVEC block of lmd_vmix.F: defined in the Rivers_ana cppdefs but dropped by `cpp -traditional`
+                             // (an apostrophe in the comment above it opens a character constant); orc_set_kpp(h, 2) switches it on
   vec bvf, swr_frac, ghat;   // (0:N): Brunt-Vaisala frequency^2 (rho_eos.F), solar penetration fraction, nonlocal transport
   vec hbls, hbbl;            // surface / bottom boundary layer thickness (mixing.F:143,151, start at 0)
   vec srflx;                 // shortwave flux (surf_flux.F), zero unless pushed
@@ -1842,6 +1844,10 @@ void lmd_vmix(Orc& o, int tind) {
         nu_sx = nu_sx * nu_sx * nu_sx;
         AW(Kv, i, j, k) = nuwm + nu0m * nu_sx;
         AW(Kt, i, j, k) = nuws + nu0s * nu_sx;
+        if (o.lmd_convec && AW(Rig, i, j, k) < 0.) {     // LMD_CONVEC (lmd_vmix.F:269-274), see lmd_convec
+          AW(Kv, i, j, k) = AW(Kv, i, j, k) + 0.1;
+          AW(Kt, i, j, k) = AW(Kt, i, j, k) + 0.1;
+        }
         AW(Ks, i, j, k) = AW(Kt, i, j, k);
       }
   }
@@ -2325,7 +2331,7 @@ int orc_set_pipe(void* h, int ipipe, const double* prf, const double* trc) {
   return 0;
 }
 // cppdefs LMD_MIXING/LMD_KPP/...: switch the vertical mixing closure on (call before init_step0: rho_eos then also fills bvf)
-int orc_set_kpp(void* h, int on) { ((Orc*)h)->lmd_kpp = on != 0; return 0; }
+int orc_set_kpp(void* h, int on) { ((Orc*)h)->lmd_kpp = on != 0; ((Orc*)h)->lmd_convec = on == 2; return 0; }
 int orc_get_hbl(void* h, double* hbls, double* hbbl) {
   Orc& o = *(Orc*)h;
   memcpy(hbls, o.hbls.data(), o.SXY * sizeof(double)); memcpy(hbbl, o.hbbl.data(), o.SXY * sizeof(double));
