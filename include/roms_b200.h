@@ -123,6 +123,10 @@ int  roms_step3d_t(roms_ctx* h, int tile);    /* step3d_t_ISO.F:20 */
 int  roms_visc3d(roms_ctx* h);                /* visc3d_S.F:4  (UV_VIS2: harmonic viscosity along S-surfaces)  */
 int  roms_t3dmix(roms_ctx* h);                /* t3dmix_S.F:4  (TS_DIF2: Laplacian tracer diffusion, all NT)   */
 int  roms_alfabeta(roms_ctx* h, double* alpha_host, double* beta_host); /* alfabeta.F:4 */
+int  roms_set_kpp(roms_ctx* h, int on);        /* cppdefs LMD_MIXING LMD_KPP LMD_BKPP LMD_RIMIX LMD_NONLOCAL: allocate the closure's arrays;
+                                                  roms_step then calls roms_lmd_vmix where main.F:408-410, 434-436 do; rho_eos also fills bvf */
+int  roms_lmd_vmix(roms_ctx* h, int tind);     /* lmd_vmix.F:4 lmd_vmix(tind): Akv, Akt, hbls, hbbl, ghat from u,v(tind), bvf, surface fluxes */
+int  roms_get_hbl(roms_ctx* h, double* hbls_host, double* hbbl_host); /* boundary layer thicknesses, (Lm+4)x(Mm+4) planes */
 int  roms_set_pot_tides(roms_ctx* h, int on);  /* tides.F pot_tides: prsgrd subtracts g*ptide (ROMS_PTIDE, pushed by the host each
                                                   step after its harmonic synthesis, tides.F:238-246) from the surface pressure, prsgrd.F:209-211 */
 int  roms_set_pipe(roms_ctx* h, int ipipe, const double* prf, const double* trc);

@@ -2331,6 +2331,7 @@ int orc_set_pipe(void* h, int ipipe, const double* prf, const double* trc) {
   return 0;
 }
 // cppdefs LMD_MIXING/LMD_KPP/...: switch the vertical mixing closure on (call before init_step0: rho_eos then also fills bvf)
+int orc_lmd_vmix(void* h, int tind) { lmd_vmix(*(Orc*)h, tind); return 0; }
 int orc_set_kpp(void* h, int on) { ((Orc*)h)->lmd_kpp = on != 0; ((Orc*)h)->lmd_convec = on == 2; return 0; }
 int orc_get_hbl(void* h, double* hbls, double* hbbl) {
   Orc& o = *(Orc*)h;

@@ -229,6 +229,36 @@ def test_rivers_ana_without_kpp_on_gpu():
     g.close(); o.close()
 
 
+def test_kpp_closure_on_gpu():
+    """LMD/KPP vertical mixing (lmd_vmix.F, lmd_kpp.F, lmd_swr_frac.F, bvf of rho_eos.F) on the reference's
+    Rivers_ana case: one call of lmd_vmix against the oracle field by field (Akv, Akt, hbls, hbbl), then 20 steps of the whole
+    model with the closure on, and the reference's own log (Courant columns to round-off, see test_rivers_ana_golden_with_kpp).
+    sin/log/exp of the closure come from the CUDA math library here and from libm in the oracle, hence 1e-13 instead of 0."""
+    G = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "rivers_ana_diag.json")))["diag"]
+    cfg, st = cases.rivers_ana(kpp=True)
+    g, o = Roms(cfg), Oracle(cfg)
+    cases.initialize(g, st); cases.initialize(o, st)
+    for m in (g, o):
+        m.set_idx(1, 1, 1, 1, 3, 1, 1)
+        m.call("lmd_vmix", 1)
+    for f, it in (("AKV", 1), ("AKT", 1), ("AKT", 2)):
+        a, b = parity_walk.view(g.pull(f, 1, it), cfg), parity_walk.view(o.pull(f, 1, it), cfg)
+        assert parity_walk.rel(a, b) <= 1e-13, (f, it, parity_walk.rel(a, b))
+    for a, b in zip(g.hbl(), o.hbl()):
+        assert parity_walk.rel(parity_walk.view(a, cfg), parity_walk.view(b, cfg)) <= 1e-13
+    g.close(); o.close()
+    g, o = Roms(cfg), Oracle(cfg)
+    cases.initialize(g, st); cases.initialize(o, st)
+    for n in range(1, 21):
+        g.call("step"); o.call("step")
+        d = g.diag()
+        if n <= 16:
+            assert abs(d[2] / G[n]["MAX_ADV_CFL"] - 1) <= 1e-11 and abs(d[3] / G[n]["MAX_VERT_CFL"] - 1) <= 1e-11, (n, d)
+    r = compare(g, o, cfg.NT, 1e-9, cfg)
+    print("Rivers_ana with KPP, 20 steps:", r)
+    g.close(); o.close()
+
+
 def test_pipe_source_budgets_and_100_steps():
     """Pipe outfalls (pipe_frc.F; hooks step2d_FB.F:155-159, omega.F:102-108, step3d_t_ISO.F:927-935): GPU-vs-oracle parity
     and closed budgets: per baroclinic step the domain gains sum(pipe_flx)*dt of water and sum(pipe_flx)*dt*pipe_trc of each tracer."""

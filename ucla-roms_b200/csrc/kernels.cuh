@@ -315,6 +315,7 @@ __global__ void k_rho_eos(const __grid_constant__ KP p, const double* __restrict
   }
   const double rmask = p.rmask[c];
   double rhoA = 0, rhoS = 0;
+  double zr_up = 0, r1_up = 0, q1_up = 0;   // level k+1 (bvf)
   for (int k = N; k >= 1; --k) {
     double r1, cff;
     const double Hz = R3(p.Hz, c, k);
@@ -325,8 +326,16 @@ __global__ void k_rho_eos(const __grid_constant__ KP p, const double* __restrict
       const double K0 = Tt * (K01 + Tt * (K02 + Tt * (K03 + Tt * K04))) + Ts * (K10 + Tt * (K11 + Tt * (K12 + Tt * K13)) + sqrtTs * (KS0 + Tt * (KS1 + Tt * KS2)));
       const double q1 = 0.1 * (rho0 + r1) * (K0_Duk - K0) / ((K00 + K0) * (K00 + K0_Duk)) * rmask;
       R3(p.qp1, c, k) = q1;
-      const double dpth = -R3(p.z_r, c, k);
+      const double zr = R3(p.z_r, c, k);
+      const double dpth = -zr;
       cff = Hz * (r1 + q1 * dpth * (1.0 - qp2 * dpth));
+      if (p.lmd_kpp) {      // rho_eos.F (LMD_KPP): Brunt-Vaisala frequency between levels k and k+1
+        if (k < N) {
+          const double dp2 = -0.5 * (zr_up + zr);
+          RW(p.bvf, c, k) = -(p.g / rho0) * (r1_up - r1 + (q1_up - q1) * dp2 * (1. - qp2 * dp2)) / (zr_up - zr) * rmask;
+        }
+        zr_up = zr; r1_up = r1; q1_up = q1;
+      }
     } else {
       r1 = cffl - p.Tcoef * R3(T, c, k);
       if (p.salinity) r1 = r1 + p.Scoef * R3(Sal, c, k);
@@ -337,6 +346,7 @@ __global__ void k_rho_eos(const __grid_constant__ KP p, const double* __restrict
     if (k == N) { rhoS = 0.5 * cff * Hz; rhoA = cff; }
     else { rhoS = rhoS + Hz * (rhoA + 0.5 * cff); rhoA = rhoA + cff; }
   }
+  if (NONLIN && p.lmd_kpp) { RW(p.bvf, c, N) = RW(p.bvf, c, N - 1); RW(p.bvf, c, 0) = RW(p.bvf, c, 1); }
   const double cff1 = 1.0 / rho0;
   const double cff = 1.0 / (RW(p.z_w, c, N) - RW(p.z_w, c, 0));
   p.rhoA[c] = cff * cff1 * rhoA;
@@ -1731,6 +1741,245 @@ __global__ void __launch_bounds__(64, 3) k_uv2_pass1_sm(const __grid_constant__ 
 }
 #undef SA
 #undef SB
+
+// ------------------------------------------------------------------------------------------------
+// LMD/KPP vertical mixing closure: lmd_swr_frac.F, lmd_vmix.F:31-433 (LMD_RIMIX), lmd_kpp.F (INT_AT_RHO_POINTS,
+// SMOOTH_HBL, LMD_BKPP, LMD_NONLOCAL).  Kernels follow the reference's phases; Kv,Kt,Ks live in Akv,Akt(:,:,:,1:2) themselves.
+__global__ void k_swr_frac(const __grid_constant__ KP p) {
+  THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
+  const double attn1 = -1. / 0.35, attn2 = -1. / 23.0;
+  double swdk1 = 0.58, swdk2 = 1. - swdk1;
+  RW(p.swr_frac, c, p.N) = 1.;
+  for (int k = p.N; k >= 1; --k) {
+    const double xi1 = attn1 * R3(p.Hz, c, k);
+    if (xi1 > -20.) swdk1 = swdk1 * exp(xi1); else swdk1 = 0.;
+    const double xi2 = attn2 * R3(p.Hz, c, k);
+    if (xi2 > -20.) swdk2 = swdk2 * exp(xi2); else swdk2 = 0.;
+    RW(p.swr_frac, c, k - 1) = swdk1 + swdk2;
+  }
+}
+// Richardson number (divided by its critical value) on levels 1..N-1 over [imin:imax]x[jmin:jmax] (blockIdx.z = k-1)
+__global__ void k_lmd_rig(const __grid_constant__ KP p, const double* __restrict__ u, const double* __restrict__ v, double* __restrict__ Rig, int imin, int imax,
+                          int jmin, int jmax) {
+  THREAD_IJ(imin, imax, jmin, jmax)
+  const int k = blockIdx.z + 1;
+  const double cff = 0.5 / (R3(p.z_r, c, k + 1) - R3(p.z_r, c, k));
+  const double dudz = cff * (R3(u, c, k + 1) - R3(u, c, k) + R3(u, c + 1, k + 1) - R3(u, c + 1, k));
+  const double dvdz = cff * (R3(v, c, k + 1) - R3(v, c, k) + R3(v, c + SX, k + 1) - R3(v, c + SX, k));
+  RW(Rig, c, k) = RW(p.bvf, c, k) / (0.7 * DMAX(dudz * dudz + dvdz * dvdz, 1.E-10));
+}
+// copies of the first/last computed line across a closed edge, incl. the corners (lmd_vmix.F:159-200, lmd_kpp_smooth_hbl.h)
+__global__ void k_lmd_edges(const __grid_constant__ KP p, double* __restrict__ a, int imin, int imax, int jmin, int jmax) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  double* pl = a + (ix_t)blockIdx.z * p.SXY;
+  const int side = blockIdx.y;     // 0 W, 1 E, 2 S, 3 N, 4 corners
+  if (side == 0 && p.wwall) { const int j = jmin + t; if (j <= jmax) pl[CIDX(p.istr - 1, j)] = pl[CIDX(p.istr, j)]; }
+  if (side == 1 && p.ewall) { const int j = jmin + t; if (j <= jmax) pl[CIDX(p.iend + 1, j)] = pl[CIDX(p.iend, j)]; }
+  if (side == 2 && p.swall) { const int i = imin + t; if (i <= imax) pl[CIDX(i, p.jstr - 1)] = pl[CIDX(i, p.jstr)]; }
+  if (side == 3 && p.nwall) { const int i = imin + t; if (i <= imax) pl[CIDX(i, p.jend + 1)] = pl[CIDX(i, p.jend)]; }
+  if (side == 4 && t == 0) {
+    if (p.wwall && p.swall) pl[CIDX(p.istr - 1, p.jstr - 1)] = pl[CIDX(p.istr, p.jstr)];
+    if (p.wwall && p.nwall) pl[CIDX(p.istr - 1, p.jend + 1)] = pl[CIDX(p.istr, p.jend)];
+    if (p.ewall && p.swall) pl[CIDX(p.iend + 1, p.jstr - 1)] = pl[CIDX(p.iend, p.jstr)];
+    if (p.ewall && p.nwall) pl[CIDX(p.iend + 1, p.jend + 1)] = pl[CIDX(p.iend, p.jend)];
+  }
+}
+// the masked isotropic smoothing (lmd_vmix.F:201-246): out-of-place, every intermediate of the reference (FX, FE1, FE) is
+// re-evaluated in registers from the 3x3 neighbourhood with the same expressions
+__global__ void k_lmd_smooth(const __grid_constant__ KP p, const double* __restrict__ a, double* __restrict__ out, int mask_result) {
+  THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
+  const double* __restrict__ q = a + (ix_t)blockIdx.z * p.SXY;
+  const double cff = 1. / 12., cff1 = 3. / 16.;
+  auto fx0 = [&](ix_t x) { return (q[x] - q[x - 1]) * p.umask[x]; };         // FX before the transversal terms
+  auto fe1 = [&](ix_t x) { return (q[x] - q[x - SX]) * p.vmask[x]; };
+  auto fe = [&](ix_t x) { return fe1(x) + cff * (fx0(x + 1) + fx0(x - SX) - fx0(x) - fx0(x + 1 - SX)); };
+  auto fx = [&](ix_t x) { return fx0(x) + cff * (fe1(x + SX) + fe1(x - 1) - fe1(x) - fe1(x - 1 + SX)); };
+  double r = q[c] + cff1 * (fx(c + 1) - fx(c) + fe(c + SX) - fe(c));
+  if (mask_result) r = r * p.rmask[c];
+  out[c + (ix_t)blockIdx.z * p.SXY] = r;
+}
+// interior mixing from the smoothed Rig, bottom taper, end values and the ascending in-place 1-2-1 filter (lmd_vmix.F:253-407)
+__global__ void k_lmd_vmix_col(const __grid_constant__ KP p, const double* __restrict__ Rig, double Akv_bak, double Akt_bak0, double Akt_bak1) {
+  THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
+  const int N = p.N;
+  const double nu0m = 1.e-2, nu0s = 1.e-2, nuwm = 1.0e-4, nuws = 0.1e-4, Lturb = 10., pi = 3.14159265358979323;
+  double* Kv = p.Akv; double* Kt = p.Akt[0]; double* Ks = p.Akt[1];
+  const double zw0 = RW(p.z_w, c, 0);
+  for (int k = 1; k <= N - 1; ++k) {
+    const double cff = DMIN(1., DMAX(0., RW(Rig, c, k)));
+    double nu_sx = 1. - cff * cff;
+    nu_sx = nu_sx * nu_sx * nu_sx;
+    double kv = nuwm + nu0m * nu_sx, kt = nuws + nu0s * nu_sx, ks = kt;
+    const double dist = RW(p.z_w, c, k) - zw0;
+    if (dist < Lturb) {
+      const double mult = sin(0.5 * pi * (RW(p.z_w, c, k) - zw0) / Lturb);
+      kv = kv * mult; kt = kt * mult; ks = ks * mult;
+    }
+    RW(Kv, c, k) = kv; RW(Kt, c, k) = kt; RW(Ks, c, k) = ks;
+  }
+  RW(Kv, c, N) = RW(Kv, c, N - 1) + Akv_bak; RW(Ks, c, N) = RW(Ks, c, N - 1) + Akt_bak1; RW(Kt, c, N) = RW(Kt, c, N - 1) + Akt_bak0;
+  RW(Kv, c, 0) = RW(Kv, c, 1) + Akv_bak; RW(Ks, c, 0) = RW(Ks, c, 1) + Akt_bak1; RW(Kt, c, 0) = RW(Kt, c, 1) + Akt_bak0;
+  for (int k = 1; k <= N - 1; ++k) {
+    RW(Kv, c, k) = 0.5 * RW(Kv, c, k) + 0.25 * RW(Kv, c, k - 1) + 0.25 * RW(Kv, c, k + 1) + Akv_bak;
+    RW(Kt, c, k) = 0.5 * RW(Kt, c, k) + 0.25 * RW(Kt, c, k - 1) + 0.25 * RW(Kt, c, k + 1) + Akt_bak0;
+    RW(Ks, c, k) = 0.5 * RW(Ks, c, k) + 0.25 * RW(Ks, c, k - 1) + 0.25 * RW(Ks, c, k + 1) + Akt_bak1;
+  }
+}
+// lmd_kpp.F first j-loop: surface forcing, the integral bulk-Richardson functional FC(0:N) (kept in FCs), hbl and bbl
+__global__ void k_lmd_kpp1(const __grid_constant__ KP p, const double* __restrict__ u, const double* __restrict__ v, const double* __restrict__ alpha,
+                           const double* __restrict__ beta, const double* __restrict__ stflxT, const double* __restrict__ stflxS, double* __restrict__ FCs,
+                           int imin, int imax, int jmin, int jmax) {
+  THREAD_IJ(imin, imax, jmin, jmax)
+  const int N = p.N;
+  const double Ricr = 0.15, Ri_inv = 1. / Ricr, epssfc = 0.1, betaT = -0.2, Cv = 1.8, C_Ek = 258., zeta_s = -1.0, a_s = -28.86, c_s = 98.96, r2 = 0.5, r3 = 1. / 3.,
+               vonKar = 0.41;
+  const double Vtc = Cv * sqrt(-betaT / (c_s * epssfc)) / (Ricr * (vonKar * vonKar));
+  const double g = p.g;
+  const double Bo = g * (alpha[c] * (stflxT[c] - p.srflx[c]) - beta[c] * (stflxS ? stflxS[c] : 0.0));
+  const double Bosol = g * alpha[c] * p.srflx[c];
+  const double sr = 0.5 * (p.sustr[c] + p.sustr[c + 1]), vr = 0.5 * (p.svstr[c] + p.svstr[c + SX]);
+  const double us = sqrt(sqrt(sr * sr + vr * vr));
+  p.k_Bo[c] = Bo; p.k_Bosol[c] = Bosol; p.k_ustar[c] = us;
+  const double hbl0 = p.hbls[c], bbl0 = p.hbbl[c];
+  const double zwN = RW(p.z_w, c, N), zw0 = RW(p.z_w, c, 0), ff = p.f[c];
+  const double eh = epssfc * hbl0, eb = epssfc * bbl0;
+  double FC = 0.;
+  RW(FCs, c, N) = 0.;
+  for (int k = N - 1; k >= 1; --k) {
+    const double du = zwN - RW(p.z_w, c, k), dd = RW(p.z_w, c, k) - zw0;
+    const double cff_up = du * du, cff_dn = dd * dd;
+    const double Kern = cff_up * cff_dn / ((cff_up + eh * eh) * (cff_dn + eb * eb));
+    const double su = R3(u, c, k + 1) + R3(u, c + 1, k + 1) - R3(u, c, k) - R3(u, c + 1, k);
+    const double sv = R3(v, c, k + 1) + R3(v, c + SX, k + 1) - R3(v, c, k) - R3(v, c + SX, k);
+    const double hh = R3(p.Hz, c, k) + R3(p.Hz, c, k + 1);
+    FC = FC + Kern * (0.5 * (su * su + sv * sv) / hh - 0.5 * hh * (Ri_inv * RW(p.bvf, c, k) + C_Ek * ff * ff));
+    RW(FCs, c, k) = FC;
+  }
+  {
+    const double z_bl = zw0 + 0.25 * R3(p.Hz, c, 1);
+    const double du = zwN - z_bl, dd = z_bl - zw0;
+    const double cff_up = du * du, cff_dn = dd * dd;
+    const double Kern = cff_up * cff_dn / ((cff_up + eh * eh) * (cff_dn + eb * eb));
+    const double su = R3(u, c, 1) + R3(u, c + 1, 1), sv = R3(v, c, 1) + R3(v, c + SX, 1);
+    FC = FC + Kern * (0.5 * (su * su + sv * sv) / R3(p.Hz, c, 1) - 0.5 * R3(p.Hz, c, 1) * (Ri_inv * RW(p.bvf, c, 1) + C_Ek * ff * ff));
+    RW(FCs, c, 0) = FC;
+  }
+  const double FC0 = FC, rm = p.rmask[c], ustar3 = us * us * us;
+  int kbls = 0;
+  double Cr_up = 0., Cr_hit = 0., Cr_hit_up = 0.;
+  for (int k = N; k >= 1; --k) {
+    const double w1 = sqrt(RW(p.swr_frac, c, k) * RW(p.swr_frac, c, k - 1));
+    double zscale = zwN - R3(p.z_r, c, k);
+    const double Bfsfc = Bo + Bosol * (1. - w1);
+    zscale = DMIN(zscale, hbl0 * epssfc);
+    zscale = zscale * rm;
+    const double zetahat = vonKar * zscale * Bfsfc;
+    double ws;
+    if (zetahat >= 0.) ws = vonKar * us * ustar3 / DMAX(ustar3 + 5. * zetahat, 1.E-20);
+    else if (zetahat > zeta_s * ustar3) ws = vonKar * pow((ustar3 - 16. * zetahat) / us, r2);
+    else ws = vonKar * pow(a_s * ustar3 - c_s * zetahat, r3);
+    const double Vtsq = 1.8 * Vtc * ws * sqrt(DMAX(1.e-5, RW(p.bvf, c, k - 1)));
+    const double Cr = RW(FCs, c, k) + Vtsq;
+    if (kbls == 0 && Cr < 0.) { kbls = k; Cr_hit = Cr; Cr_hit_up = Cr_up; }
+    Cr_up = Cr;
+  }
+  double hbl;
+  if (kbls > 0) {
+    if (kbls == N) hbl = zwN - R3(p.z_r, c, N);
+    else hbl = zwN - (R3(p.z_r, c, kbls) * Cr_hit_up - R3(p.z_r, c, kbls + 1) * Cr_hit) / (Cr_hit_up - Cr_hit);
+  } else hbl = zwN - zw0;
+  p.k_hbl[c] = hbl * rm;
+  int kbbl = 0;
+  double Cr_dn = 0., Cb = 0., Cb_dn = 0.;
+  for (int k = 1; k <= N; ++k) {
+    const double Cr = RW(FCs, c, k) - FC0;
+    if (kbbl == 0 && Cr > 0.) { kbbl = k; Cb = Cr; Cb_dn = Cr_dn; }
+    Cr_dn = Cr;
+  }
+  double bbl;
+  if (kbbl > 0) {
+    if (kbbl == 1) bbl = R3(p.z_r, c, 1) - zw0;
+    else bbl = (R3(p.z_r, c, kbbl - 1) * Cb - R3(p.z_r, c, kbbl) * Cb_dn) / (Cb - Cb_dn) - zw0;
+  } else bbl = zwN - zw0;
+  p.k_bbl[c] = bbl * rm;
+}
+// lmd_kpp.F second j-loop: time filter of hbl/bbl, KPP shape functions blended into Kv,Kt,Ks (= Akv,Akt), ghat, hbls/hbbl
+__global__ void k_lmd_kpp2(const __grid_constant__ KP p, const double* __restrict__ hbl_s, const double* __restrict__ bbl_s, const double* __restrict__ un,
+                           const double* __restrict__ vn, int first) {
+  THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
+  const int N = p.N;
+  const double epssfc = 0.1, Cstar = 10., zeta_m = -0.2, a_m = 1.257, c_m = 8.360, zeta_s = -1.0, a_s = -28.86, c_s = 98.96, r2 = 0.5, r3 = 1. / 3., r4 = 0.25,
+               EPS = 1.E-20, vonKar = 0.41;
+  const double Cg = Cstar * vonKar * pow(c_s * vonKar * epssfc, 1. / 3.);
+  double* Kv = p.Akv; double* Kt = p.Akt[0]; double* Ks = p.Akt[1];
+  double hbl = hbl_s[c], bbl = bbl_s[c];
+  if (!first) { hbl = 0.5 * (hbl + p.hbls[c]); bbl = 0.5 * (bbl + p.hbbl[c]); }
+  const double zwN = RW(p.z_w, c, N), zw0 = RW(p.z_w, c, 0), rm = p.rmask[c];
+  const double Bo = p.k_Bo[c], Bosol = p.k_Bosol[c], us = p.k_ustar[c], ustar3 = us * us * us;
+  int kbls = N;
+  for (int k = N - 1; k >= 1; --k)
+    if (RW(p.z_w, c, k) > zwN - hbl) kbls = k;
+  double Bfsfc;
+  {
+    const int k = kbls;
+    const double z_bl = zwN - hbl;
+    if (RW(p.swr_frac, c, k - 1) > 0.)
+      Bfsfc = Bo + Bosol * (1. - RW(p.swr_frac, c, k - 1) * RW(p.swr_frac, c, k) * (RW(p.z_w, c, k) - RW(p.z_w, c, k - 1)) /
+                                     (RW(p.swr_frac, c, k) * (RW(p.z_w, c, k) - z_bl) + RW(p.swr_frac, c, k - 1) * (z_bl - RW(p.z_w, c, k - 1))));
+    else Bfsfc = Bo + Bosol;
+  }
+  for (int k = N; k >= 0; --k) {
+    double zscale = zwN - RW(p.z_w, c, k);
+    zscale = DMIN(zscale, hbl * epssfc);
+    zscale = zscale * rm;
+    const double zetahat = vonKar * zscale * Bfsfc;
+    double wm, ws;
+    if (zetahat >= 0.) {
+      wm = vonKar * us * ustar3 / DMAX(ustar3 + 5. * zetahat, 1.E-20);
+      ws = wm;
+    } else {
+      if (zetahat > zeta_m * ustar3) wm = vonKar * pow(us * (ustar3 - 16. * zetahat), r4);
+      else wm = vonKar * pow(a_m * ustar3 - c_m * zetahat, r3);
+      if (zetahat > zeta_s * ustar3) ws = vonKar * pow((ustar3 - 16. * zetahat) / us, r2);
+      else ws = vonKar * pow(a_s * ustar3 - c_s * zetahat, r3);
+    }
+    const double ssgm = (zwN - RW(p.z_w, c, k)) / DMAX(hbl, EPS);
+    double gh = 0.;
+    if (ssgm < 1.) {
+      double cff;
+      if (ssgm < 0.07) cff = 0.5 * ((ssgm - 0.07) * (ssgm - 0.07)) / 0.07;
+      else cff = 0.;
+      cff = cff + ssgm * ((1. - ssgm) * (1. - ssgm));
+      const double amp = ssgm * ssgm;
+      const double akv = amp * RW(Kv, c, k), akt = amp * RW(Kt, c, k), aks = amp * RW(Ks, c, k);
+      const double bm = wm * hbl * cff, bs = ws * hbl * cff;
+      RW(Kv, c, k) = sqrt(akv * akv + bm * bm);
+      RW(Kt, c, k) = sqrt(akt * akt + bs * bs);
+      RW(Ks, c, k) = sqrt(aks * aks + bs * bs);
+      if (Bfsfc < 0.) gh = -Cg * ssgm * ((1. - ssgm) * (1. - ssgm));
+    }
+    RW(p.ghat, c, k) = gh;
+  }
+  {
+    const double u0 = R3(un, c, 1), u1 = R3(un, c + 1, 1), v0 = R3(vn, c, 1), v1 = R3(vn, c + SX, 1);
+    const double wmb = vonKar * vonKar * sqrt(0.333333333333 * (u0 * u0 + u1 * u1 + u0 * u1 + v0 * v0 + v1 * v1 + v0 * v1)) / log(1. + 0.5 * R3(p.Hz, c, 1) / p.Zob);
+    const double wsb = wmb;
+    for (int k = 0; k <= N; ++k) {
+      const double sgmb = (RW(p.z_w, c, k) - zw0 + p.Zob) / (bbl + p.Zob);
+      if (sgmb < 1.) {
+        const double cff1 = sgmb * ((1. - sgmb) * (1. - sgmb));
+        const double bm = wmb * bbl * cff1, bs = wsb * bbl * cff1;
+        RW(Kv, c, k) = sqrt(RW(Kv, c, k) * RW(Kv, c, k) + bm * bm);
+        RW(Kt, c, k) = sqrt(RW(Kt, c, k) * RW(Kt, c, k) + bs * bs);
+        RW(Ks, c, k) = sqrt(RW(Ks, c, k) * RW(Ks, c, k) + bs * bs);
+      }
+    }
+  }
+  if (!(rm > 0.5))
+    for (int k = 0; k <= N; ++k) { RW(Kv, c, k) = 0.; RW(Kt, c, k) = 0.; RW(Ks, c, k) = 0.; }
+  p.hbls[c] = hbl;
+  p.hbbl[c] = bbl;
+}
 
 // ------------------------------------------------------------------------------------------------
 // diag.F:50-658: per-column kinetic energy, barotropic KE, free-surface volume and max advective

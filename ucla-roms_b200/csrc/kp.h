@@ -56,6 +56,11 @@ struct KP {
   int pipes;
   double* ptide;     // tides.F:26 equilibrium tidal potential
   int pot_tides;
+  // LMD/KPP vertical mixing (lmd_vmix.F, lmd_kpp.F): allocated by roms_set_kpp
+  int lmd_kpp;
+  double *bvf, *swr_frac, *ghat;     // (0:N)
+  double *hbls, *hbbl, *srflx;       // 2-D
+  double *k_ustar, *k_Bo, *k_Bosol, *k_hbl, *k_bbl;   // 2-D work planes of lmd_kpp
 };
 
 // column base index of (i,j) and relative addressing

@@ -55,6 +55,8 @@ struct roms_ctx {
   std::vector<KTimer> ktimers;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   int col_bx = 32, col_by = 2, pl_bx = 32, pl_by = 8;   // plane tiles 32x8: fewest halo-row re-reads through L2 (profiles/r1_tuning_log.txt)
+  double* kpp_buf = nullptr;   // LMD/KPP arrays (roms_set_kpp)
+  double *kpp_Rig = nullptr, *kpp_RigS = nullptr, *kpp_FC = nullptr, *kpp_hblS = nullptr, *kpp_bblS = nullptr, *kpp_alpha = nullptr, *kpp_beta = nullptr;
   int fuse_rho = 1;       // a rho_eos call is deferred; if prsgrd follows (main.F:397-413, 430-445) both run as one fused column kernel
   int rho_pending = 0;    // time index of the deferred rho_eos (0: none)
   int uv2_sm = 1;     // k_uv2_pass1 with the column parked in shared memory (1.0 -> 0.78 ms on B200); off when the column is too tall
@@ -296,6 +298,7 @@ int roms_create(const roms_cfg* cfg, int device, roms_ctx** out) {
   p.pipe_tab = cur; cur += (size_t)MAXPIP * PIPROW(N);
   p.pipes = 0;
   p.pot_tides = 0;
+  p.lmd_kpp = 0;
 #define P1(name, id) p.name = h->f[id].ptr[0]
   P1(h, ROMS_H); P1(pm, ROMS_PM); P1(pn, ROMS_PN); P1(f, ROMS_F); P1(rmask, ROMS_RMASK); P1(umask, ROMS_UMASK); P1(vmask, ROMS_VMASK);
   P1(dm_u, ROMS_DM_U); P1(dn_u, ROMS_DN_U); P1(dm_v, ROMS_DM_V); P1(dn_v, ROMS_DN_V); P1(dm_r, ROMS_DM_R); P1(dn_r, ROMS_DN_R);
@@ -324,6 +327,7 @@ int roms_destroy(roms_ctx* h) {
   cudaStreamSynchronize(h->st);
   comm_destroy(&h->comm);
   cudaFree(h->arena);
+  cudaFree(h->kpp_buf);
   cudaStreamDestroy(h->st);
   delete h;
   return 0;
@@ -819,6 +823,70 @@ static double pairsum(const double* a, size_t n) {
   return pairsum(a, n / 2) + pairsum(a + n / 2, n - n / 2);
 }
 int roms_set_pot_tides(roms_ctx* h, int on) { h->kp.pot_tides = on ? 1 : 0; return 0; }
+// cppdefs LMD_MIXING + LMD_KPP + LMD_BKPP + LMD_RIMIX + LMD_NONLOCAL: allocates the closure's arrays and makes roms_step call
+// roms_lmd_vmix where main.F:408-410 and :434-436 do.  Call before roms_init_step0.
+int roms_set_kpp(roms_ctx* h, int on) {
+  CK(cudaSetDevice(h->device));
+  KP& p = h->kp;
+  if (!on) { p.lmd_kpp = 0; return 0; }
+  if (!h->c.nonlin_eos) { g_err = "roms_set_kpp: the Brunt-Vaisala frequency is implemented for the nonlinear split EOS only"; return -1; }
+  if (!h->kpp_buf) {
+    const size_t n2 = (size_t)p.SXY, nw = n2 * (p.N + 1), tot = 6 * nw + 13 * n2;
+    CK(cudaMalloc(&h->kpp_buf, tot * sizeof(double)));
+    CK(cudaMemset(h->kpp_buf, 0, tot * sizeof(double)));
+    double* cur = h->kpp_buf;
+    auto take = [&](size_t n) { double* r = cur; cur += n; return r; };
+    p.bvf = take(nw); p.swr_frac = take(nw); p.ghat = take(nw);
+    h->kpp_Rig = take(nw); h->kpp_RigS = take(nw); h->kpp_FC = take(nw);
+    p.hbls = take(n2); p.hbbl = take(n2); p.srflx = take(n2);
+    p.k_ustar = take(n2); p.k_Bo = take(n2); p.k_Bosol = take(n2); p.k_hbl = take(n2); p.k_bbl = take(n2);
+    h->kpp_hblS = take(n2); h->kpp_bblS = take(n2); h->kpp_alpha = take(n2); h->kpp_beta = take(n2);
+  }
+  p.lmd_kpp = 1;
+  h->fuse_rho = 0;     // the fused rho_eos + prsgrd kernel does not produce bvf
+  return 0;
+}
+int roms_get_hbl(roms_ctx* h, double* hbls, double* hbbl) {
+  CK(cudaSetDevice(h->device));
+  if (!h->kp.lmd_kpp) { g_err = "roms_get_hbl: KPP is off"; return -1; }
+  const KP& p = h->kp;
+  const size_t w = (size_t)(h->c.Lm + 4) * sizeof(double);
+  CK(cudaMemcpy2DAsync(hbls, w, p.hbls + (IOFF - 1), (size_t)p.SX * sizeof(double), w, h->c.Mm + 4, cudaMemcpyDeviceToHost, h->st));
+  CK(cudaMemcpy2DAsync(hbbl, w, p.hbbl + (IOFF - 1), (size_t)p.SX * sizeof(double), w, h->c.Mm + 4, cudaMemcpyDeviceToHost, h->st));
+  CK(cudaStreamSynchronize(h->st));
+  return 0;
+}
+// lmd_vmix(tind) (lmd_vmix.F:4-29): lmd_vmix_tile then lmd_kpp_tile; result in Akv, Akt(:,:,:,1:2), hbls, hbbl, ghat
+int roms_lmd_vmix(roms_ctx* h, int tind) {
+  FLUSH_RHO(h);
+  CK(cudaSetDevice(h->device));
+  const KP& p = h->kp;
+  if (!p.lmd_kpp) { g_err = "roms_lmd_vmix: call roms_set_kpp first"; return -1; }
+  const int N = p.N;
+  const int imin = p.wwall ? p.istr : p.istr - 1, imax = p.ewall ? p.iend : p.iend + 1, jmin = p.swall ? p.jstr : p.jstr - 1, jmax = p.nwall ? p.jend : p.jend + 1;
+  const int len = (p.Lm > p.Mm ? p.Lm : p.Mm) + 3;
+  const dim3 eb(128, 1, 1);
+  PLANE(k_lmd_rig, imax, jmin, jmax, N - 1, p, h->u(tind), h->v(tind), h->kpp_Rig, imin, imax, jmin, jmax);
+  k_lmd_edges<<<dim3((len + 127) / 128, 5, N - 1), eb, 0, h->st>>>(p, h->kpp_Rig + p.SXY, imin, imax, jmin, jmax);
+  h->launches++;
+  PLANE(k_lmd_smooth, p.iend, p.jstr, p.jend, N - 1, p, h->kpp_Rig + p.SXY, h->kpp_RigS + p.SXY, 0);
+  COLUMN(k_lmd_vmix_col, 0, p.iend, p.jstr, p.jend, p, h->kpp_RigS, 0.0, 0.0, 0.0);
+  COLUMN(k_alfabeta, 0, p.iend + 2, p.jstr - 2, p.jend + 2, p, h->t(h->nstp, 1), h->c.NT >= 2 ? h->t(h->nstp, 2) : nullptr, h->kpp_alpha, h->kpp_beta);
+  COLUMN(k_lmd_kpp1, 0, imax, jmin, jmax, p, h->u(tind), h->v(tind), h->kpp_alpha, h->kpp_beta, h->f[ROMS_STFLX].ptr[0],
+         h->c.NT >= 2 ? h->f[ROMS_STFLX].ptr[1] : (double*)nullptr, h->kpp_FC, imin, imax, jmin, jmax);
+  k_lmd_edges<<<dim3((len + 127) / 128, 5, 1), eb, 0, h->st>>>(p, p.k_hbl, imin, imax, jmin, jmax);
+  k_lmd_edges<<<dim3((len + 127) / 128, 5, 1), eb, 0, h->st>>>(p, p.k_bbl, imin, imax, jmin, jmax);
+  h->launches += 2;
+  PLANE(k_lmd_smooth, p.iend, p.jstr, p.jend, 1, p, p.k_hbl, h->kpp_hblS, 1);
+  PLANE(k_lmd_smooth, p.iend, p.jstr, p.jend, 1, p, p.k_bbl, h->kpp_bblS, 1);
+  COLUMN(k_lmd_kpp2, 0, p.iend, p.jstr, p.jend, p, h->kpp_hblS, h->kpp_bblS, h->u(h->nstp), h->v(h->nstp), h->iic == h->forw_start ? 1 : 0);
+  k_lmd_edges<<<dim3((len + 127) / 128, 5, 1), eb, 0, h->st>>>(p, p.hbls, p.istr, p.iend, p.jstr, p.jend);
+  k_lmd_edges<<<dim3((len + 127) / 128, 5, 1), eb, 0, h->st>>>(p, p.hbbl, p.istr, p.iend, p.jstr, p.jend);
+  h->launches += 2;
+  int rc = exchange(h, {{p.Akv, N + 1}, {p.hbls, 1}, {p.hbbl, 1}});
+  if (rc) return rc;
+  return exchange(h, {{p.Akt[0], N + 1}, {p.Akt[1], N + 1}});
+}
 // pipe_frc.F (init_arrays_pipes, set_pipe_frc): release profile and tracer values of one pipe
 int roms_set_pipe(roms_ctx* h, int ipipe, const double* prf, const double* trc) {
   CK(cudaSetDevice(h->device));
@@ -935,6 +1003,11 @@ int roms_init_step0(roms_ctx* h) {
   h->forw_start = h->ntstart;
   int rc;
   if ((rc = roms_set_depth(h, 0))) return rc;
+  if (h->kp.lmd_kpp) {       // main.F:219 swr_frac
+    const KP& p = h->kp;
+    COLUMN(k_swr_frac, 0, p.iend, p.jstr, p.jend, p);
+    if ((rc = exchange(h, {{p.swr_frac, p.N + 1}}))) return rc;
+  }
   if ((rc = roms_set_huv(h))) return rc;
   if ((rc = roms_omega(h))) return rc;
   if ((rc = roms_rho_eos(h, h->nrhs))) return rc;
@@ -949,12 +1022,14 @@ int roms_step(roms_ctx* h) {
   RUN(roms_rho_eos(h, h->nrhs));
   RUN(roms_set_huv(h));
   RUN(roms_omega(h));
+  if (h->kp.lmd_kpp) RUN(roms_lmd_vmix(h, h->nstp));      // main.F:408-410
   RUN(roms_prsgrd(h));
   RUN(roms_pre_step3d(h, 0));
   RUN(roms_set_huv1(h, 0));
   h->nrhs = 3; h->nnew = 3 - h->nstp;
   RUN(roms_omega(h));
   RUN(roms_rho_eos(h, h->nrhs));
+  if (h->kp.lmd_kpp) RUN(roms_lmd_vmix(h, h->nrhs));      // main.F:434-436
   RUN(roms_prsgrd(h));
   RUN(roms_step3d_uv1(h, 0));
   if (h->c.uv_vis2) RUN(roms_visc3d(h));

@@ -103,6 +103,12 @@ class CApi:
         self._check(self._f("grid_stats")(self.h, out), "grid_stats")
         return np.array(out[:])
 
+    def hbl(self):
+        """surface and bottom boundary layer thicknesses of the KPP closure (hbls, hbbl)"""
+        a = np.empty(self.shape2); b = np.empty(self.shape2)
+        self._check(self._f("get_hbl")(self.h, a.ctypes.data_as(C.POINTER(C.c_double)), b.ctypes.data_as(C.POINTER(C.c_double))), "get_hbl")
+        return a, b
+
     def set_river(self, iriver, vol, trc):
         """river_frc.F set_river_frc: volume flux [m3/s] and tracer values of river `iriver` (1-based)"""
         a = (C.c_double * len(trc))(*trc)

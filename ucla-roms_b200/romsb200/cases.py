@@ -300,7 +300,7 @@ def rivers_ana(akv=0.0, akt=0.0, kpp=False):
     """The reference's tests/Rivers_ana case without its KPP closure: grid and mask of `rivers_ana_grid`, ana_init.h (rest,
     T = 4 + 10 exp(z/50), S = 36), zero surface forcing (analytical.F:216-305), the analytic river of river_frc.F:125-137 /
     ana_frc_river.h (20 coast cells at the head of the channel share 500 m3/s of 24 degC, 1 PSU water).  Akv, Akt are uniform
-    stand-ins for what lmd_vmix/lmd_kpp would compute; kpp=True (oracle only) switches the closure itself on (state key "KPP") and
+    stand-ins for what lmd_vmix/lmd_kpp would compute; kpp=True switches the closure itself on (state key "KPP") and
     the UV_VIS2/TS_DIF2 switches of the case's cppdefs.opt (with its zero coefficients)."""
     cfg, st = rivers_ana_grid()
     if kpp:
@@ -334,7 +334,7 @@ def initialize(model, state):
     model.call("setup_grid")
     model.push_state({k: v for k, v in state.items() if k not in grid and k not in ("RIVERS", "PIPES", "KPP")})
     if state.get("KPP"):
-        model.call("set_kpp", 1)     # the mixing closure exists in the oracle only: raises for the CUDA library
+        model.call("set_kpp", 1)     # lmd_vmix/lmd_kpp
     for n, (vol, trc) in enumerate(state.get("RIVERS", []), 1):
         model.set_river(n, vol, trc)
     for n, (prf, trc) in enumerate(state.get("PIPES", []), 1):
