@@ -326,6 +326,26 @@ def rivers_ana(akv=0.0, akt=0.0, kpp=False):
     return cfg, st
 
 
+def take_block(cfg, state, sub):
+    """Cuts the block sub=(inode, jnode, np_xi, np_eta) (mpi_setup.F:61-70, extents as `block_extent`) out of a single-domain
+    cfg/state: every field keeps its 2-cell halo, which at an interior block edge holds the neighbour's values."""
+    import copy
+    inode, jnode, np_xi, np_eta = sub
+    (Lm, i0), (Mm, j0) = block_extent(cfg.Lm, np_xi, inode), block_extent(cfg.Mm, np_eta, jnode)
+    c = copy.copy(cfg)
+    c.Lm, c.Mm, c.np_xi, c.np_eta, c.inode, c.jnode = Lm, Mm, np_xi, np_eta, inode, jnode
+    cut = lambda a: np.ascontiguousarray(a[..., j0:j0 + Mm + 4, i0:i0 + Lm + 4])
+    st = {}
+    for k, v in state.items():
+        if isinstance(v, dict):
+            st[k] = {kk: cut(a) for kk, a in v.items()}
+        elif isinstance(v, np.ndarray):
+            st[k] = cut(v)
+        else:
+            st[k] = v
+    return c, st
+
+
 def initialize(model, state):
     """roms_init (main.F:86-321) for a host without Fortran: push the analytic fields, derive the
     grid metrics, then set_depth / set_HUV / omega / rho_eos."""
