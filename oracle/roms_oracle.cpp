@@ -64,8 +64,8 @@ struct Orc {
   bool pipe_source = false;
   // LMD/KPP vertical mixing closure (lmd_vmix.F, lmd_kpp.F, lmd_swr_frac.F; cppdefs LMD_MIXING LMD_KPP LMD_BKPP LMD_RIMIX LMD_NONLOCAL)
   bool lmd_kpp = false;
-  bool lmd_convec = false;   // the LMD_CONVEC block of lmd_vmix.F: defined in the Rivers_ana cppdefs but dropped by `cpp -traditional`
-                             // (an apostrophe in the comment above it opens a character constant); orc_set_kpp(h, 2) switches it on
+  bool lmd_convec = true;    // LMD_CONVEC (lmd_vmix.F:269-274): part of the reference's Rivers_ana / Pipes_ana builds -- the Pipes_ana log is
+                             // reproduced only with it; orc_set_kpp(h, 2) switches it off for experiments
   vec bvf, swr_frac, ghat;   // (0:N): Brunt-Vaisala frequency^2 (rho_eos.F), solar penetration fraction, nonlocal transport
   vec hbls, hbbl;            // surface / bottom boundary layer thickness (mixing.F:143,151, start at 0)
   vec srflx;                 // shortwave flux (surf_flux.F), zero unless pushed
@@ -1819,8 +1819,7 @@ static void lmd_smooth(Orc& o, double* a, int imin, int imax, int jmin, int jmax
     }
   }
 }
-// lmd_vmix.F:31-433 (LMD_RIMIX; no LMD_DDMIX; the LMD_CONVEC block is swallowed by the traditional cpp of the reference's build:
-// an apostrophe in the comment above it): interior mixing Kv,Kt,Ks(0:N), then lmd_kpp_tile below
+// lmd_vmix.F:31-433 (LMD_RIMIX, LMD_CONVEC; no LMD_DDMIX): interior mixing Kv,Kt,Ks(0:N), then lmd_kpp_tile below
 void lmd_kpp(Orc& o, int tind, vec& Kv, vec& Kt, vec& Ks);
 void lmd_vmix(Orc& o, int tind) {
   GEOM
@@ -2332,7 +2331,7 @@ int orc_set_pipe(void* h, int ipipe, const double* prf, const double* trc) {
 }
 // cppdefs LMD_MIXING/LMD_KPP/...: switch the vertical mixing closure on (call before init_step0: rho_eos then also fills bvf)
 int orc_lmd_vmix(void* h, int tind) { lmd_vmix(*(Orc*)h, tind); return 0; }
-int orc_set_kpp(void* h, int on) { ((Orc*)h)->lmd_kpp = on != 0; ((Orc*)h)->lmd_convec = on == 2; return 0; }
+int orc_set_kpp(void* h, int on) { ((Orc*)h)->lmd_kpp = on != 0; ((Orc*)h)->lmd_convec = on != 2; return 0; }
 int orc_get_hbl(void* h, double* hbls, double* hbbl) {
   Orc& o = *(Orc*)h;
   memcpy(hbls, o.hbls.data(), o.SXY * sizeof(double)); memcpy(hbbl, o.hbbl.data(), o.SXY * sizeof(double));

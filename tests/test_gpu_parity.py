@@ -259,6 +259,28 @@ def test_kpp_closure_on_gpu():
     g.close(); o.close()
 
 
+def test_pipes_ana_golden_on_gpu():
+    """The CUDA path against the reference's Pipes_ana log directly: 21 lines x 4 columns (walls, land mask, slope, nonlinear EOS,
+    Coriolis, KPP with convective adjustment, pipe source) to <= 1e-10 relative (the closure's sin/log come from the CUDA math
+    library), and against the oracle field by field after the 20 steps."""
+    G = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "pipes_ana_diag.json")))["diag"]
+    cfg, st = cases.pipes_ana()
+    g, o = Roms(cfg), Oracle(cfg)
+    cases.initialize(g, st); cases.initialize(o, st)
+    worst = 0.0
+    for n in range(0, 21):
+        if n:
+            g.call("step"); o.call("step")
+        d = g.diag()
+        ref = np.array([G[n]["KE"], G[n]["BAROTR_KE"], G[n]["MAX_ADV_CFL"], G[n]["MAX_VERT_CFL"]])
+        dev = np.where(ref != 0, np.abs(d - ref) / np.where(ref != 0, np.abs(ref), 1.0), np.abs(d))
+        worst = max(worst, dev.max())
+        assert dev.max() <= 1e-10, (n, d, ref)
+    r = compare(g, o, cfg.NT, 1e-9, cfg)
+    print("Pipes_ana golden on the GPU: worst deviation", worst, "; vs oracle after 20 steps:", r)
+    g.close(); o.close()
+
+
 def test_pipe_source_budgets_and_100_steps():
     """Pipe outfalls (pipe_frc.F; hooks step2d_FB.F:155-159, omega.F:102-108, step3d_t_ISO.F:927-935): GPU-vs-oracle parity
     and closed budgets: per baroclinic step the domain gains sum(pipe_flx)*dt of water and sum(pipe_flx)*dt*pipe_trc of each tracer."""

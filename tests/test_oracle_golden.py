@@ -245,3 +245,28 @@ def test_rivers_ana_golden_with_kpp():
         else:
             assert np.all(np.abs(dev[:2]) <= 2e-3), (n, dev)
     o.close()
+
+
+def test_pipes_ana_golden_20_steps():
+    """The reference's Pipes_ana log (tests/golden/pipes_ana_diag.json): all 21 lines x 4 columns to <= 1e-12 relative (observed
+    <= 1.5e-14).  This case runs every branch Filament does not: closed walls on all sides, a land mask, a sloping bottom,
+    the nonlinear split EOS with T and S, Coriolis with the KPP closure (lmd_vmix incl. the convective adjustment -- without
+    LMD_CONVEC step 2 is already off by 5e-4 --, lmd_kpp with both boundary layers, bvf) and a pipe source (omega, step2d,
+    step3d_t hooks)."""
+    import json
+    import os
+    G = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "pipes_ana_diag.json")))["diag"]
+    cfg, st = cases.pipes_ana()
+    o = Oracle(cfg)
+    cases.initialize(o, st)
+    worst = 0.0
+    for n in range(0, 21):
+        if n:
+            o.call("step")
+        d = o.diag()
+        g = np.array([G[n]["KE"], G[n]["BAROTR_KE"], G[n]["MAX_ADV_CFL"], G[n]["MAX_VERT_CFL"]])
+        dev = np.where(g != 0, np.abs(d - g) / np.where(g != 0, np.abs(g), 1.0), np.abs(d))
+        worst = max(worst, dev.max())
+        assert dev.max() <= 1e-12, (n, d, g)
+    print("Pipes_ana golden, worst relative deviation over 21 lines:", worst)
+    o.close()

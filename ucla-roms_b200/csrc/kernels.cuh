@@ -1809,7 +1809,9 @@ __global__ void k_lmd_vmix_col(const __grid_constant__ KP p, const double* __res
     const double cff = DMIN(1., DMAX(0., RW(Rig, c, k)));
     double nu_sx = 1. - cff * cff;
     nu_sx = nu_sx * nu_sx * nu_sx;
-    double kv = nuwm + nu0m * nu_sx, kt = nuws + nu0s * nu_sx, ks = kt;
+    double kv = nuwm + nu0m * nu_sx, kt = nuws + nu0s * nu_sx;
+    if (RW(Rig, c, k) < 0.) { kv = kv + 0.1; kt = kt + 0.1; }      // LMD_CONVEC (lmd_vmix.F:269-274): nu0c
+    double ks = kt;
     const double dist = RW(p.z_w, c, k) - zw0;
     if (dist < Lturb) {
       const double mult = sin(0.5 * pi * (RW(p.z_w, c, k) - zw0) / Lturb);

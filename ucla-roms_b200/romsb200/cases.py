@@ -346,6 +346,49 @@ def take_block(cfg, state, sub):
     return c, st
 
 
+def pipes_ana(kpp=True):
+    """The reference's tests/Pipes_ana case (ana_grid.h, ana_init.h, ana_pipe_frc.h, benchmark.in): 100x100x10, dx=dy=300 m,
+    f=1e-4, depth 10 m shelf then a slope to 100 m, the land strip of Rivers_ana, closed walls, dt=60 s, ndtfast=30; a 2x2-cell
+    pipe in the middle of the domain releases 500 m3/s of 24 degC, 1 PSU water over the two bottom levels."""
+    Lm = Mm = 100
+    N = 10
+    cfg = RomsCfg(Lm=Lm, Mm=Mm, N=N, NT=2, ew_periodic=0, ns_periodic=0, nonlin_eos=1, salinity=1, ndtfast=30,
+                  np_xi=1, np_eta=1, inode=0, jnode=0, dt=60.0, rho0=1027.5, g=9.81, Tcoef=0.0, T0=0.0, Scoef=0.0, S0=0.0,
+                  rdrg=0.0, rdrg2=1.0e-3, Zob=1.0e-2, gamma2=1.0, theta_s=6.0, theta_b=6.0, hc=25.0)
+    cfg.uv_vis2, cfg.ts_dif2 = 1, 1
+    sy, sx = Mm + 4, Lm + 4
+    SizeX = SizeY = 30.0e3
+    dx, dy = SizeX / Lm, SizeY / Mm
+    i = np.arange(-1, Lm + 3)[None, :] + np.zeros((sy, 1))
+    j = np.arange(-1, Mm + 3)[:, None] + np.zeros((1, sx))
+    xr, yr = dx * (i - 0.5), dy * (j - 0.5)
+    depth, max_depth = 10.0, 100.0
+    shelf = SizeY / 5
+    slope = (max_depth - depth) / (SizeY * 4 / 5)
+    h = np.where(yr < shelf, depth, depth + (yr - shelf) * slope)
+    land, coast, riv_west, riv_east = SizeY * 0.1, SizeY * 0.02, SizeX * 0.4, SizeX * 0.6
+    rmask = np.ones((sy, sx))
+    rmask[(yr < land) & ((xr < riv_west) | (xr > riv_east))] = 0.0
+    rmask[yr < coast] = 0.0
+    psz, px, py = SizeX * 0.02, SizeX * .5, SizeY * .5
+    pipe_cells = float(round(psz / dx)) ** 2
+    sel = (xr > px - 0.5 * psz) & (xr < px + 0.5 * psz) & (yr > py - 0.5 * psz) & (yr < py + 0.5 * psz)
+    pidx = np.where(sel, 1.0, 0.0)
+    pflx = np.where(sel, 1.0 / pipe_cells, 0.0) * 5.0e2
+    z_r, z_w = _depths(h, np.zeros_like(h), N, cfg.theta_s, cfg.theta_b, cfg.hc)
+    T = 4.0 + 10.0 * np.exp(z_r / 50.0)
+    S = np.full_like(T, 36.0)
+    zero2, zero3 = np.zeros((sy, sx)), np.zeros_like(T)
+    st = {"H": h, "PM": np.full((sy, sx), 1.0 / dx), "PN": np.full((sy, sx), 1.0 / dy), "F": np.full((sy, sx), 1.0e-4), "RMASK": rmask,
+          "ZETA": {(1, 1): zero2}, "UBAR": {(1, 1): zero2}, "VBAR": {(1, 1): zero2}, "U": {(1, 1): zero3, (2, 1): zero3},
+          "V": {(1, 1): zero3, (2, 1): zero3}, "T": {(1, 1): T, (2, 1): T, (1, 2): S, (2, 2): S},
+          "AKV": np.zeros((N + 1, sy, sx)), "AKT": {(1, 1): np.zeros((N + 1, sy, sx)), (1, 2): np.zeros((N + 1, sy, sx))},
+          "PIPE_IDX": pidx, "PIPE_FLX": pflx, "PIPES": [([0.5, 0.5] + [0.0] * (N - 2), [24.0, 1.0])]}
+    if kpp:
+        st["KPP"] = True
+    return cfg, st
+
+
 def initialize(model, state):
     """roms_init (main.F:86-321) for a host without Fortran: push the analytic fields, derive the
     grid metrics, then set_depth / set_HUV / omega / rho_eos."""
