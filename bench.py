@@ -168,6 +168,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--periodic", action="store_true", help="doubly periodic variant instead of the closed N/S walls of BASELINE configs[1]")
     ap.add_argument("--mixing", action="store_true", help="also run visc3d / t3dmix (UV_VIS2, TS_DIF2; SURVEY.md 8(f) row f1) inside every step")
+    ap.add_argument("--kpp", action="store_true", help="also run the LMD/KPP vertical mixing closure (lmd_vmix twice per step; SURVEY.md 8(f) row f2)")
     ap.add_argument("--kernel-table", default=None, help="write the per-kernel timing table to this file")
     a = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
@@ -180,7 +181,7 @@ def main():
         case_kw.update(visc2=100.0, tnu2=50.0)
     workload = f"analytic baroclinic channel {Lm}x{Mm}x{N} per GPU, T+S" + (f"+{NT - 2} passive" if NT > 2 else "") + \
                ", nonlinear split EOS, " + ("doubly periodic" if a.periodic else "E-W periodic, closed free-slip N/S walls") + ", ndtfast=60 (82 executed barotropic substeps per step)" + \
-               (", + harmonic lateral viscosity/diffusion (visc3d, t3dmix)" if a.mixing else "")
+               (", + harmonic lateral viscosity/diffusion (visc3d, t3dmix)" if a.mixing else "") + (", + KPP vertical mixing (lmd_vmix x2 per step)" if a.kpp else "")
     config = {"workload": workload, "grid_per_gpu": [Lm, Mm, N], "tracers": NT, "l2_policy": "inputs (15 GB of resident state per GPU) larger than L2; no flush",
               "timing": "CUDA events on the library stream, barrier+sync both sides, max over ranks"}
 
@@ -214,9 +215,13 @@ def main():
 
     np_xi, np_eta = cases.rank_grid(world)
     cfg, st = cases.channel(Lm * np_xi, Mm * np_eta, N, sub=(rank % np_xi, rank // np_xi, np_xi, np_eta), **case_kw)
+    if a.kpp:
+        cfg.Zob = 1.0e-2          # the bottom boundary layer of the closure needs a roughness length (log-layer drag then, too)
     g = Roms(cfg, local)
     if world > 1:
         g.attach_torch_comm(dist)
+    if a.kpp:
+        st["KPP"] = True
     cases.initialize(g, st)
     del st
     lib = g.lib
