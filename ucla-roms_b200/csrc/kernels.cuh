@@ -1845,31 +1845,12 @@ __global__ void k_lmd_kpp1(const __grid_constant__ KP p, const double* __restric
   const double hbl0 = p.hbls[c], bbl0 = p.hbbl[c];
   const double zwN = RW(p.z_w, c, N), zw0 = RW(p.z_w, c, 0), ff = p.f[c];
   const double eh = epssfc * hbl0, eb = epssfc * bbl0;
-  double FC = 0.;
-  RW(FCs, c, N) = 0.;
-  for (int k = N - 1; k >= 1; --k) {
-    const double du = zwN - RW(p.z_w, c, k), dd = RW(p.z_w, c, k) - zw0;
-    const double cff_up = du * du, cff_dn = dd * dd;
-    const double Kern = cff_up * cff_dn / ((cff_up + eh * eh) * (cff_dn + eb * eb));
-    const double su = R3(u, c, k + 1) + R3(u, c + 1, k + 1) - R3(u, c, k) - R3(u, c + 1, k);
-    const double sv = R3(v, c, k + 1) + R3(v, c + SX, k + 1) - R3(v, c, k) - R3(v, c + SX, k);
-    const double hh = R3(p.Hz, c, k) + R3(p.Hz, c, k + 1);
-    FC = FC + Kern * (0.5 * (su * su + sv * sv) / hh - 0.5 * hh * (Ri_inv * RW(p.bvf, c, k) + C_Ek * ff * ff));
-    RW(FCs, c, k) = FC;
-  }
-  {
-    const double z_bl = zw0 + 0.25 * R3(p.Hz, c, 1);
-    const double du = zwN - z_bl, dd = z_bl - zw0;
-    const double cff_up = du * du, cff_dn = dd * dd;
-    const double Kern = cff_up * cff_dn / ((cff_up + eh * eh) * (cff_dn + eb * eb));
-    const double su = R3(u, c, 1) + R3(u, c + 1, 1), sv = R3(v, c, 1) + R3(v, c + SX, 1);
-    FC = FC + Kern * (0.5 * (su * su + sv * sv) / R3(p.Hz, c, 1) - 0.5 * R3(p.Hz, c, 1) * (Ri_inv * RW(p.bvf, c, 1) + C_Ek * ff * ff));
-    RW(FCs, c, 0) = FC;
-  }
-  const double FC0 = FC, rm = p.rmask[c], ustar3 = us * us * us;
+  const double rm = p.rmask[c], ustar3 = us * us * us;
+  // Cr(k) = FC(k) + Vtsq(k) is formed in the same down-sweep that integrates FC (the reference's separate k=N..1 loop reads
+  // nothing that the sweep has not produced yet); kbls = first level from the top with Cr < 0
   int kbls = 0;
   double Cr_up = 0., Cr_hit = 0., Cr_hit_up = 0.;
-  for (int k = N; k >= 1; --k) {
+  auto crit = [&](int k, double FCk) {
     const double w1 = sqrt(RW(p.swr_frac, c, k) * RW(p.swr_frac, c, k - 1));
     double zscale = zwN - R3(p.z_r, c, k);
     const double Bfsfc = Bo + Bosol * (1. - w1);
@@ -1881,21 +1862,45 @@ __global__ void k_lmd_kpp1(const __grid_constant__ KP p, const double* __restric
     else if (zetahat > zeta_s * ustar3) ws = vonKar * pow((ustar3 - 16. * zetahat) / us, r2);
     else ws = vonKar * pow(a_s * ustar3 - c_s * zetahat, r3);
     const double Vtsq = 1.8 * Vtc * ws * sqrt(DMAX(1.e-5, RW(p.bvf, c, k - 1)));
-    const double Cr = RW(FCs, c, k) + Vtsq;
+    const double Cr = FCk + Vtsq;
     if (kbls == 0 && Cr < 0.) { kbls = k; Cr_hit = Cr; Cr_hit_up = Cr_up; }
     Cr_up = Cr;
+  };
+  double FC = 0.;
+  RW(FCs, c, N) = 0.;
+  crit(N, 0.);
+  for (int k = N - 1; k >= 1; --k) {
+    const double du = zwN - RW(p.z_w, c, k), dd = RW(p.z_w, c, k) - zw0;
+    const double cff_up = du * du, cff_dn = dd * dd;
+    const double Kern = cff_up * cff_dn / ((cff_up + eh * eh) * (cff_dn + eb * eb));
+    const double su = R3(u, c, k + 1) + R3(u, c + 1, k + 1) - R3(u, c, k) - R3(u, c + 1, k);
+    const double sv = R3(v, c, k + 1) + R3(v, c + SX, k + 1) - R3(v, c, k) - R3(v, c + SX, k);
+    const double hh = R3(p.Hz, c, k) + R3(p.Hz, c, k + 1);
+    FC = FC + Kern * (0.5 * (su * su + sv * sv) / hh - 0.5 * hh * (Ri_inv * RW(p.bvf, c, k) + C_Ek * ff * ff));
+    RW(FCs, c, k) = FC;
+    crit(k, FC);
   }
+  {
+    const double z_bl = zw0 + 0.25 * R3(p.Hz, c, 1);
+    const double du = zwN - z_bl, dd = z_bl - zw0;
+    const double cff_up = du * du, cff_dn = dd * dd;
+    const double Kern = cff_up * cff_dn / ((cff_up + eh * eh) * (cff_dn + eb * eb));
+    const double su = R3(u, c, 1) + R3(u, c + 1, 1), sv = R3(v, c, 1) + R3(v, c + SX, 1);
+    FC = FC + Kern * (0.5 * (su * su + sv * sv) / R3(p.Hz, c, 1) - 0.5 * R3(p.Hz, c, 1) * (Ri_inv * RW(p.bvf, c, 1) + C_Ek * ff * ff));
+  }
+  const double FC0 = FC;
   double hbl;
   if (kbls > 0) {
     if (kbls == N) hbl = zwN - R3(p.z_r, c, N);
     else hbl = zwN - (R3(p.z_r, c, kbls) * Cr_hit_up - R3(p.z_r, c, kbls + 1) * Cr_hit) / (Cr_hit_up - Cr_hit);
   } else hbl = zwN - zw0;
   p.k_hbl[c] = hbl * rm;
+  // bottom boundary layer: first level from the bottom with FC(k) - FC(0) > 0 (the search stops there)
   int kbbl = 0;
   double Cr_dn = 0., Cb = 0., Cb_dn = 0.;
-  for (int k = 1; k <= N; ++k) {
+  for (int k = 1; k <= N && kbbl == 0; ++k) {
     const double Cr = RW(FCs, c, k) - FC0;
-    if (kbbl == 0 && Cr > 0.) { kbbl = k; Cb = Cr; Cb_dn = Cr_dn; }
+    if (Cr > 0.) { kbbl = k; Cb = Cr; Cb_dn = Cr_dn; }
     Cr_dn = Cr;
   }
   double bbl;
