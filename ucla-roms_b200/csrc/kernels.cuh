@@ -440,6 +440,7 @@ __global__ void k_rho_prs_vert(const __grid_constant__ KP p, const double* __res
   }
   const double rmask = p.rmask[c];
   double rhoA = 0, rhoS = 0;
+  double zr_up = 0, r1_up = 0, q1_up = 0;   // level k+1 (bvf)
   // equation of state at level k (k_rho_eos body): stores rho1, qp1, advances the integrals, returns r1, q1, z_r
   auto eos = [&](int k, double& r1, double& q1, double& zr) {
     double cff;
@@ -454,6 +455,13 @@ __global__ void k_rho_prs_vert(const __grid_constant__ KP p, const double* __res
       R3(p.qp1, c, k) = q1;
       const double dpth = -zr;
       cff = Hz * (r1 + q1 * dpth * (1.0 - qp2 * dpth));
+      if (p.lmd_kpp) {      // rho_eos.F (LMD_KPP): Brunt-Vaisala frequency between levels k and k+1
+        if (k < N) {
+          const double dp2 = -0.5 * (zr_up + zr);
+          RW(p.bvf, c, k) = -(p.g / rho0) * (r1_up - r1 + (q1_up - q1) * dp2 * (1. - qp2 * dp2)) / (zr_up - zr) * rmask;
+        }
+        zr_up = zr; r1_up = r1; q1_up = q1;
+      }
     } else {
       r1 = cffl - p.Tcoef * R3(T, c, k);
       if (p.salinity) r1 = r1 + p.Scoef * R3(Sal, c, k);
@@ -515,6 +523,7 @@ __global__ void k_rho_prs_vert(const __grid_constant__ KP p, const double* __res
       else rawR_m = r1_c - r1_m;
     }
   }
+  if (NONLIN && p.lmd_kpp) { RW(p.bvf, c, N) = RW(p.bvf, c, N - 1); RW(p.bvf, c, 0) = RW(p.bvf, c, 1); }
   const double cff1 = 1.0 / rho0;
   const double cff = 1.0 / (RW(p.z_w, c, N) - RW(p.z_w, c, 0));
   p.rhoA[c] = cff * cff1 * rhoA;

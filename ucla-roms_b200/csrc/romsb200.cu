@@ -843,7 +843,6 @@ int roms_set_kpp(roms_ctx* h, int on) {
     h->kpp_hblS = take(n2); h->kpp_bblS = take(n2); h->kpp_alpha = take(n2); h->kpp_beta = take(n2);
   }
   p.lmd_kpp = 1;
-  h->fuse_rho = 0;     // the fused rho_eos + prsgrd kernel does not produce bvf
   return 0;
 }
 int roms_get_hbl(roms_ctx* h, double* hbls, double* hbbl) {
@@ -1022,15 +1021,17 @@ int roms_step(roms_ctx* h) {
   RUN(roms_rho_eos(h, h->nrhs));
   RUN(roms_set_huv(h));
   RUN(roms_omega(h));
-  if (h->kp.lmd_kpp) RUN(roms_lmd_vmix(h, h->nstp));      // main.F:408-410
   RUN(roms_prsgrd(h));
+  // main.F:408-410 calls lmd_vmix before prsgrd; the two share no data, and after prsgrd the deferred rho_eos (which also
+  // produces bvf) has run fused with the pressure integration
+  if (h->kp.lmd_kpp) RUN(roms_lmd_vmix(h, h->nstp));
   RUN(roms_pre_step3d(h, 0));
   RUN(roms_set_huv1(h, 0));
   h->nrhs = 3; h->nnew = 3 - h->nstp;
   RUN(roms_omega(h));
   RUN(roms_rho_eos(h, h->nrhs));
-  if (h->kp.lmd_kpp) RUN(roms_lmd_vmix(h, h->nrhs));      // main.F:434-436
   RUN(roms_prsgrd(h));
+  if (h->kp.lmd_kpp) RUN(roms_lmd_vmix(h, h->nrhs));      // main.F:434-436 (before prsgrd there; independent of it)
   RUN(roms_step3d_uv1(h, 0));
   if (h->c.uv_vis2) RUN(roms_visc3d(h));
   for (h->iif = 1; h->iif <= h->nfast; ++h->iif) {
