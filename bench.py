@@ -31,7 +31,8 @@ UNIT = "grid-point updates/s"
 KERNEL_WORDS = {
     "k_rho_eos": lambda t: (6 if t[0] == "true" else 4, 3), "k_set_huv": (5, 3), "k_omega": (6, 3),
     "k_prsgrd_vert": lambda t: (5 if t[0] == "true" else 3, 3),
-    "k_rho_prs_vert": lambda t: (8 if t[0] == "true" else 6, 3),   # rho_eos fused with the vertical part of prsgrd: T,S,Hz,z_r read; rho1,qp1,P,rho written "k_prsgrd_horiz": lambda t: (8 if t[0] == "true" else 6, 3),
+    "k_rho_prs_vert": lambda t: (8 if t[0] == "true" else 6, 3),   # rho_eos fused with the vertical part of prsgrd: T,S,Hz,z_r read; rho1,qp1,P,rho written
+    "k_prsgrd_horiz": lambda t: (8 if t[0] == "true" else 6, 3),
     "k_pre_flxdiv": (5, 3), "k_pre_t_horiz": (8, 3), "k_rhs_uv_horiz": (9, 3),
     "k_t_vert": lambda t: (8 if t[0] == "0" else 7, 3), "k_uv_vert": lambda t: (10 if t[0] == "0" else 9, 3),
     "k_set_huv1": (4, 3), "k_uv2_pass0": (3, 3), "k_uv2_pass1": (6, 3),

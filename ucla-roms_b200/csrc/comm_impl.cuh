@@ -27,21 +27,26 @@ struct SyncGeom { unsigned long long* to[8]; unsigned long long* from[8]; };
 // for another block of its own GPU, so the pair cannot deadlock whatever the block scheduling order.
 template <bool PACK>
 __global__ void k_halo_msg(const __grid_constant__ KP p, const __grid_constant__ HaloList hl, const __grid_constant__ MsgGeom g, int nplanes,
-                           const __grid_constant__ SyncGeom sg, unsigned long long epoch, unsigned* counter, int* fail) {
+                           const __grid_constant__ SyncGeom sg, unsigned long long epoch, unsigned* counter, int* fail, long long timeout_clk) {
   const int d = blockIdx.y;
   const bool act = g.active[d];
   if (!PACK) {
     if (!act) return;
     if (sg.from[d]) {
+      __shared__ int lost;
       if (threadIdx.x == 0) {
+        lost = 0;
         const long long t0 = clock64();
         unsigned long long v;
         do {
           asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(sg.from[d]) : "memory");
-          if (v < epoch && clock64() - t0 > 20000000000LL) { *fail = 1; break; }     // ~10 s: a neighbour died; do not hang the GPU
+          // the neighbour never raised its flag within the (configurable, ROMS_HALO_TIMEOUT_S) bound: report and do NOT
+          // unpack the stale buffer; the sticky flag is read by the host after the next stream synchronisation
+          if (v < epoch && clock64() - t0 > timeout_clk) { *fail = 1; lost = 1; break; }
         } while (v < epoch);
       }
       __syncthreads();
+      if (lost) return;
     }
   }
   if (act) {
@@ -92,6 +97,7 @@ struct NcclState {
   long long peer_off[8][2][8];           // that neighbour's offsets
   std::vector<std::pair<int, void*>> opened;   // rank -> mapped base (cudaIpcOpenMemHandle)
   int* d_fail = nullptr;                 // pinned host flag: a flag wait timed out
+  long long timeout_clk = 0;             // bound of one flag wait in SM clocks (ROMS_HALO_TIMEOUT_S seconds, default 600)
   unsigned* counter = nullptr;           // blocks of the current pack launch that have finished
 };
 struct P2PInfo { cudaIpcMemHandle_t handle; long long off[2][8]; };
@@ -138,6 +144,15 @@ static int p2p_setup(NcclState* ns, const KP& p) {
   CK(cudaMemset(ns->counter, 0, sizeof(unsigned)));
   CK(cudaHostAlloc(&ns->d_fail, sizeof(int), cudaHostAllocMapped));
   *ns->d_fail = 0;
+  {
+    // all ranks must stay within this bound of each other (host I/O between steps included); MPI would block for ever
+    double secs = 600.0;
+    if (const char* e = getenv("ROMS_HALO_TIMEOUT_S")) secs = atof(e);
+    int dev = 0, khz = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, dev);
+    ns->timeout_clk = (long long)(secs * 1e3 * (khz > 0 ? khz : 1965000));
+  }
   P2PInfo mine;
   memset(&mine, 0, sizeof(mine));
   int ok = cudaIpcGetMemHandle(&mine.handle, ns->shm) == cudaSuccess ? 1 : 0;
@@ -260,15 +275,14 @@ int comm_exchange(Comm* cm, const KP& p, cudaStream_t st, const XF* f, int nf, l
           sg.from[d] = (unsigned long long*)ns->shm + d;
         }
       }
-      k_halo_msg<true><<<g, b, 0, st>>>(p, hl, gs, nplanes, sg, ns->epoch, ns->counter, ns->d_fail);
-      k_halo_msg<false><<<g, b, 0, st>>>(p, hl, gr, nplanes, sg, ns->epoch, nullptr, ns->d_fail);
+      k_halo_msg<true><<<g, b, 0, st>>>(p, hl, gs, nplanes, sg, ns->epoch, ns->counter, ns->d_fail, ns->timeout_clk);
+      k_halo_msg<false><<<g, b, 0, st>>>(p, hl, gr, nplanes, sg, ns->epoch, nullptr, ns->d_fail, ns->timeout_clk);
       (*launches) += 2;
-      if (*ns->d_fail) { g_err = "halo exchange: a neighbour never raised its flag (rank lost?)"; return -2; }
       continue;
     }
     SyncGeom none;
     memset(&none, 0, sizeof(none));
-    k_halo_msg<true><<<g, b, 0, st>>>(p, hl, gs, nplanes, none, 0ull, nullptr, nullptr);
+    k_halo_msg<true><<<g, b, 0, st>>>(p, hl, gs, nplanes, none, 0ull, nullptr, nullptr, 0LL);
     (*launches)++;
     ncclGroupStart();
     for (int d = 0; d < 8; ++d) {
@@ -282,7 +296,7 @@ int comm_exchange(Comm* cm, const KP& p, cudaStream_t st, const XF* f, int nf, l
     }
     ncclResult_t r = ncclGroupEnd();
     if (r != ncclSuccess) { g_err = std::string("nccl send/recv: ") + ncclGetErrorString(r); return -1000 - (int)r; }
-    k_halo_msg<false><<<g, b, 0, st>>>(p, hl, gr, nplanes, none, 0ull, nullptr, nullptr);
+    k_halo_msg<false><<<g, b, 0, st>>>(p, hl, gr, nplanes, none, 0ull, nullptr, nullptr, 0LL);
     (*launches)++;
   }
   cudaError_t e = cudaGetLastError();
@@ -293,6 +307,12 @@ int comm_exchange(Comm* cm, const KP& p, cudaStream_t st, const XF* f, int nf, l
   g_err = "library built without NCCL";
   return -1;
 #endif
+}
+
+int comm_check_failed(Comm* cm) {
+  NcclState* ns = (NcclState*)cm->nccl;
+  if (ns && ns->d_fail && *(volatile int*)ns->d_fail) { g_err = "halo exchange: a neighbour never raised its flag within ROMS_HALO_TIMEOUT_S (rank lost?); halos were left untouched"; return -2; }
+  return 0;
 }
 
 // diag.F:434-504 (rank tree over 13 doubles) -> one ncclAllGather of 7 doubles, combined in rank order

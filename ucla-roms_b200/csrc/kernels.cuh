@@ -6,8 +6,8 @@
 //    of the reference's 2-D scratch planes (UFx,UFe,VFx,VFe,wrk1,wrk2,FX,FE,...) exist.
 //  * "column" kernels: one thread per (i,j) column, x along i; the k-recurrences (parabolic
 //    splines, Thomas solves, omega integration) run in registers with a sliding window, and the
-//    two per-level coefficients that a back-substitution needs live in shared memory laid out
-//    [k][thread] (conflict-free), falling back to global scratch only when N is too large.
+//    per-level coefficients that a back-substitution needs live in a full-size global scratch slab laid out
+//    [k][j][i] (coalesced); a shared-memory variant exists (ROMS_COL_SMEM=1) but loses on occupancy.
 // Operation order inside each expression follows the reference (file:line cited per kernel) so
 // that results agree with the CPU oracle to rounding of fp64 division/log only.
 #pragma once

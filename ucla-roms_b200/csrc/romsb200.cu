@@ -371,7 +371,7 @@ int roms_sync(roms_ctx* h) {
   CK(cudaSetDevice(h->device));
   CK(cudaStreamSynchronize(h->st));
   CK(cudaGetLastError());
-  return 0;
+  return comm_check_failed(&h->comm);
 }
 int roms_kernel_launches(roms_ctx* h, long* n) { *n = h->launches; return 0; }
 // device-side timing on the library's own stream (bench.py): events bracket whatever is enqueued between
