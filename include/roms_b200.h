@@ -82,6 +82,8 @@ enum roms_field {
   ROMS_RIV_UFLX, ROMS_RIV_VFLX,                  /* river_frc.F: river faces, 10*iriver + fraction of the river's volume flux */
   ROMS_PTIDE,                                    /* tides.F:26 equilibrium tidal potential [m] (pot_tides) */
   ROMS_PIPE_IDX, ROMS_PIPE_FLX,                  /* pipe_frc.F: pipe index of a cell (0: none) and its volume flux fraction*pipe_vol [m3/s] */
+  ROMS_SRFLX,                                    /* surf_flux.F srflx: shortwave radiation flux [degC m/s], part of stflx(itemp); with KPP on it
+                                                    penetrates by swr_frac (step3d_t_ISO.F:961-998, lmd_kpp.F:160-167); zero unless pushed */
   ROMS_NFIELDS
 };
 
@@ -125,6 +127,9 @@ int  roms_t3dmix(roms_ctx* h);                /* t3dmix_S.F:4  (TS_DIF2: Laplaci
 int  roms_alfabeta(roms_ctx* h, double* alpha_host, double* beta_host); /* alfabeta.F:4 */
 int  roms_set_kpp(roms_ctx* h, int on);        /* cppdefs LMD_MIXING LMD_KPP LMD_BKPP LMD_RIMIX LMD_NONLOCAL: allocate the closure's arrays;
                                                   roms_step then calls roms_lmd_vmix where main.F:408-410, 434-436 do; rho_eos also fills bvf */
+int  roms_set_kpp_opts(roms_ctx* h, int lmd_convec, double Akv_bak, double Akt_bak_T, double Akt_bak_S);
+                                               /* cppdefs LMD_CONVEC (lmd_vmix.F:269-274; default on, as in Rivers_ana/Pipes_ana) and the
+                                                  vertical_mixing keyword's background coefficients Akv_bak, Akt_bak(1:2) (default 0) */
 int  roms_lmd_vmix(roms_ctx* h, int tind);     /* lmd_vmix.F:4 lmd_vmix(tind): Akv, Akt, hbls, hbbl, ghat from u,v(tind), bvf, surface fluxes */
 int  roms_get_hbl(roms_ctx* h, double* hbls_host, double* hbbl_host); /* boundary layer thicknesses, (Lm+4)x(Mm+4) planes */
 int  roms_set_pot_tides(roms_ctx* h, int on);  /* tides.F pot_tides: prsgrd subtracts g*ptide (ROMS_PTIDE, pushed by the host each

@@ -1545,6 +1545,23 @@ void step3d_t(Orc& o) {
         if (itrc == 0)
           for (int i = istr; i <= iend; ++i) A3(tn, i, j, N) = A3(tn, i, j, N) + dt * A2(o.swflx, i, j) * A3(tn, i, j, N) / A3(o.Hz, i, j, N);
         for (int i = istr; i <= iend; ++i) A3(tn, i, j, N) = A3(tn, i, j, N) + dt * A2(o.stflx[itrc], i, j);
+        if (o.lmd_kpp) {   // step3d_t_ISO.F:961-998 (LMD_KPP, LMD_NONLOCAL, SALINITY): solar penetration and non-local transport
+          if (itrc == 0) {
+            for (int k = N - 1; k >= 1; --k)
+              for (int i = istr; i <= iend; ++i) {
+                const double cff = A2(o.srflx, i, j) * AW(o.swr_frac, i, j, k) - AW(o.ghat, i, j, k) * (A2(o.stflx[0], i, j) - A2(o.srflx, i, j));
+                A3(tn, i, j, k + 1) = A3(tn, i, j, k + 1) - dt * cff;
+                A3(tn, i, j, k) = A3(tn, i, j, k) + dt * cff;
+              }
+          } else if (itrc == 1) {
+            for (int k = N - 1; k >= 1; --k)
+              for (int i = istr; i <= iend; ++i) {
+                const double cff = -dt * AW(o.ghat, i, j, k) * A2(o.stflx[1], i, j);
+                A3(tn, i, j, k + 1) = A3(tn, i, j, k + 1) - cff;
+                A3(tn, i, j, k) = A3(tn, i, j, k) + cff;
+              }
+          }
+        }
         const vec& Akt = o.Akt[std::min(itrc, 1)];
         for (int i = istr; i <= iend; ++i) {
           SL(DC, i, 0) = dt * A2(o.pm, i, j) * A2(o.pn, i, j);
@@ -1899,9 +1916,9 @@ void lmd_kpp(Orc& o, int tind, vec& Kv, vec& Kt, vec& Ks) {
     for (int i = imin; i <= imax; ++i) {
       A2(Bo, i, j) = g * (A2(Bosol, i, j) * (A2(o.stflx[0], i, j) - A2(o.srflx, i, j)) - A2(Bo, i, j) * (o.NT >= 2 ? A2(o.stflx[1], i, j) : 0.0));
       A2(Bosol, i, j) = g * A2(Bosol, i, j) * A2(o.srflx, i, j);
-      // sustr_r, svstr_r: wind stress at rho points (surf_flux.F); here the mean of the two faces
-      const double sr = 0.5 * (A2(o.sustr, i, j) + A2(o.sustr, i + 1, j)), vr = 0.5 * (A2(o.svstr, i, j) + A2(o.svstr, i, j + 1));
-      A2(ustar, i, j) = sqrt(sqrt(sr * sr + vr * vr));
+      // lmd_kpp.F:176-180 (the branch without BULK_FRC)
+      A2(ustar, i, j) = sqrt(sqrt(0.333333333333 * (A2(o.sustr, i, j) * A2(o.sustr, i, j) + A2(o.sustr, i + 1, j) * A2(o.sustr, i + 1, j) + A2(o.sustr, i, j) * A2(o.sustr, i + 1, j) +
+                                                    A2(o.svstr, i, j) * A2(o.svstr, i, j) + A2(o.svstr, i, j + 1) * A2(o.svstr, i, j + 1) + A2(o.svstr, i, j) * A2(o.svstr, i, j + 1))));
       A2(hbl, i, j) = A2(o.hbls, i, j);
       A2(bbl, i, j) = A2(o.hbbl, i, j);
       I1(kbls, i) = 0;
@@ -2232,6 +2249,7 @@ vec* field_ptr(Orc& o, int field, int lvl, int itrc, long* count) {
     case ROMS_RIV_UFLX: p = &o.riv_uflx; break; case ROMS_RIV_VFLX: p = &o.riv_vflx; break;
     case ROMS_PIPE_IDX: p = &o.pipe_idx; break; case ROMS_PIPE_FLX: p = &o.pipe_flx; break;
     case ROMS_PTIDE: p = &o.ptide; break;
+    case ROMS_SRFLX: p = &o.srflx; break;
     default: break;
   }
   if (count) *count = n;
@@ -2332,6 +2350,12 @@ int orc_set_pipe(void* h, int ipipe, const double* prf, const double* trc) {
 // cppdefs LMD_MIXING/LMD_KPP/...: switch the vertical mixing closure on (call before init_step0: rho_eos then also fills bvf)
 int orc_lmd_vmix(void* h, int tind) { lmd_vmix(*(Orc*)h, tind); return 0; }
 int orc_set_kpp(void* h, int on) { ((Orc*)h)->lmd_kpp = on != 0; ((Orc*)h)->lmd_convec = on != 2; return 0; }
+// LMD_CONVEC switch and the background mixing coefficients of the vertical_mixing keyword (lmd_vmix.F: Akv_bak, Akt_bak)
+int orc_set_kpp_opts(void* h, int lmd_convec, double Akv_bak, double Akt_bak_T, double Akt_bak_S) {
+  Orc& o = *(Orc*)h;
+  o.lmd_convec = lmd_convec != 0; o.Akv_bak = Akv_bak; o.Akt_bak[0] = Akt_bak_T; o.Akt_bak[1] = Akt_bak_S;
+  return 0;
+}
 int orc_get_hbl(void* h, double* hbls, double* hbbl) {
   Orc& o = *(Orc*)h;
   memcpy(hbls, o.hbls.data(), o.SXY * sizeof(double)); memcpy(hbbl, o.hbbl.data(), o.SXY * sizeof(double));

@@ -786,23 +786,16 @@ __device__ __forceinline__ double tflux_fin(double t1, double t2, double Fa, dou
     return 0.5 * (t2 + t1 - 0.3333333333333333 * (wc - wm)) * fl;
   }
 }
-// rows next to a closed wall: first differences taken at the wall-clamped rows (offsets oA, oB, oC, see jclamp)
+// rows next to a closed wall: first differences taken at the wall-clamped rows (offsets oA, oB, oC, see jclamp); fl = Flx(c,k)
 template <bool UP>
-__device__ __forceinline__ double tflux_cl(const KP& p, const double* __restrict__ t, const double* __restrict__ Flx, const double* __restrict__ msk, ix_t c, ix_t d,
+__device__ __forceinline__ double tflux_cl(const KP& p, const double* __restrict__ t, double fl, const double* __restrict__ msk, ix_t c, ix_t d,
                                            int k, ix_t oA, ix_t oB, ix_t oC) {
   const double t1 = R3(t, c - d, k), t2 = R3(t, c, k);
   const ix_t XA = c - d + oA, XB = c + oB, XC = c + d + oC;
   const double Fa = (R3(t, XA, k) - R3(t, XA - d, k)) * msk[XA];
   const double Fb = (R3(t, XB, k) - R3(t, XB - d, k)) * msk[XB];
   const double Fc = (R3(t, XC, k) - R3(t, XC - d, k)) * msk[XC];
-  return tflux_fin<UP>(t1, t2, Fa, Fb, Fc, R3(Flx, c, k));
-}
-// interior: masks mA..mC = msk(c-d), msk(c), msk(c+d) are level-independent and come in registers
-template <bool UP>
-__device__ __forceinline__ double tflux(const double* __restrict__ t, const double* __restrict__ Flx, const KP& p, ix_t c, ix_t d, int k, double mA, double mB,
-                                        double mC) {
-  const double t0 = R3(t, c - 2 * d, k), t1 = R3(t, c - d, k), t2 = R3(t, c, k), t3 = R3(t, c + d, k);
-  return tflux_fin<UP>(t1, t2, (t1 - t0) * mA, (t2 - t1) * mB, (t3 - t2) * mC, R3(Flx, c, k));
+  return tflux_fin<UP>(t1, t2, Fa, Fb, Fc, fl);
 }
 
 // pre_step3d4S.F:138-147: FlxDiv such that Hz_bak = Hz + FlxDiv, Hz_fwd = Hz - FlxDiv
@@ -818,7 +811,8 @@ __global__ void k_pre_flxdiv(const __grid_constant__ KP p, double dtau) {
 // step3d_t_ISO.F:196-213: tracer corrector, horizontal part (UP3)
 // Horizontal flux divergence  FX(i+1)-FX(i)+FE(j+1)-FE(j)  at (i,j,k).  Between walls the first differences in j exist on
 // rows jstr..jend+1 only (compute_horiz_tracer_fluxes.h:118-160); NEAR rows take the clamped form.  The eight mask values
-// of the point are level-independent and are passed in registers.
+// of the point are level-independent and are passed in registers; the four volume fluxes of the cell's faces are loaded
+// ONCE per level and shared by every tracer of the batch (they, the masks and the metrics do not depend on the tracer).
 struct TMask { double u0, u1, u2, u3, v0, v1, v2, v3; };   // umask(c-1..c+2), vmask(c-SX..c+2SX)
 __device__ __forceinline__ TMask tmask_load(const KP& p, ix_t c) {
   const ix_t SX = p.SX;
@@ -827,31 +821,40 @@ __device__ __forceinline__ TMask tmask_load(const KP& p, ix_t c) {
   m.v0 = p.vmask[c - SX]; m.v1 = p.vmask[c]; m.v2 = p.vmask[c + SX]; m.v3 = p.vmask[c + 2 * SX];
   return m;
 }
+struct Flx4 { double u0, u1, v0, v1; };                     // FlxU(c), FlxU(c+1), FlxV(c), FlxV(c+SX) at one level
+__device__ __forceinline__ Flx4 flx4_load(const KP& p, ix_t c, int k) {
+  const double* __restrict__ gU = p.FlxU;
+  const double* __restrict__ gV = p.FlxV;
+  Flx4 f;
+  f.u0 = R3(gU, c, k); f.u1 = R3(gU, c + 1, k); f.v0 = R3(gV, c, k); f.v1 = R3(gV, c + p.SX, k);
+  return f;
+}
 template <bool UP, bool NEAR>
-__device__ __forceinline__ void tflux4(const KP& p, const double* __restrict__ t, ix_t c, int i, int j, int k, const TMask& m, double& FXi, double& FXip, double& FEj,
-                                       double& FEjp) {
+__device__ __forceinline__ void tflux4(const KP& p, const double* __restrict__ t, ix_t c, int i, int j, int k, const TMask& m, const Flx4& f, double& FXi,
+                                       double& FXip, double& FEj, double& FEjp) {
   const ix_t SX = p.SX;
   if (NEAR) {   // first differences in i exist on columns istr..iend+1 between walls (compute_horiz_tracer_fluxes.h:50-84)
-    FXi = tflux_cl<UP>(p, t, p.FlxU, p.umask, c, 1, k, iclamp(p, i - 1, p.istr, p.iend + 1), iclamp(p, i, p.istr, p.iend + 1), iclamp(p, i + 1, p.istr, p.iend + 1));
-    FXip = tflux_cl<UP>(p, t, p.FlxU, p.umask, c + 1, 1, k, iclamp(p, i, p.istr, p.iend + 1), iclamp(p, i + 1, p.istr, p.iend + 1),
+    FXi = tflux_cl<UP>(p, t, f.u0, p.umask, c, 1, k, iclamp(p, i - 1, p.istr, p.iend + 1), iclamp(p, i, p.istr, p.iend + 1), iclamp(p, i + 1, p.istr, p.iend + 1));
+    FXip = tflux_cl<UP>(p, t, f.u1, p.umask, c + 1, 1, k, iclamp(p, i, p.istr, p.iend + 1), iclamp(p, i + 1, p.istr, p.iend + 1),
                         iclamp(p, i + 2, p.istr, p.iend + 1));
-  } else {
-    FXi = tflux<UP>(t, p.FlxU, p, c, 1, k, m.u0, m.u1, m.u2);
-    FXip = tflux<UP>(t, p.FlxU, p, c + 1, 1, k, m.u1, m.u2, m.u3);
-  }
-  if (NEAR) {
-    FEj = tflux_cl<UP>(p, t, p.FlxV, p.vmask, c, SX, k, jclamp(p, j - 1, p.jstr, p.jend + 1), jclamp(p, j, p.jstr, p.jend + 1), jclamp(p, j + 1, p.jstr, p.jend + 1));
-    FEjp = tflux_cl<UP>(p, t, p.FlxV, p.vmask, c + SX, SX, k, jclamp(p, j, p.jstr, p.jend + 1), jclamp(p, j + 1, p.jstr, p.jend + 1),
+    FEj = tflux_cl<UP>(p, t, f.v0, p.vmask, c, SX, k, jclamp(p, j - 1, p.jstr, p.jend + 1), jclamp(p, j, p.jstr, p.jend + 1), jclamp(p, j + 1, p.jstr, p.jend + 1));
+    FEjp = tflux_cl<UP>(p, t, f.v1, p.vmask, c + SX, SX, k, jclamp(p, j, p.jstr, p.jend + 1), jclamp(p, j + 1, p.jstr, p.jend + 1),
                         jclamp(p, j + 2, p.jstr, p.jend + 1));
-  } else {
-    FEj = tflux<UP>(t, p.FlxV, p, c, SX, k, m.v0, m.v1, m.v2);
-    FEjp = tflux<UP>(t, p.FlxV, p, c + SX, SX, k, m.v1, m.v2, m.v3);
+  } else {      // interior: the five values along each axis are loaded once and serve both faces
+    const double a0 = R3(t, c - 2, k), a1 = R3(t, c - 1, k), t2 = R3(t, c, k), a3 = R3(t, c + 1, k), a4 = R3(t, c + 2, k);
+    const double dA = (a1 - a0) * m.u0, dB = (t2 - a1) * m.u1, dC = (a3 - t2) * m.u2, dD = (a4 - a3) * m.u3;
+    FXi = tflux_fin<UP>(a1, t2, dA, dB, dC, f.u0);
+    FXip = tflux_fin<UP>(t2, a3, dB, dC, dD, f.u1);
+    const double b0 = R3(t, c - 2 * SX, k), b1 = R3(t, c - SX, k), b3 = R3(t, c + SX, k), b4 = R3(t, c + 2 * SX, k);
+    const double eA = (b1 - b0) * m.v0, eB = (t2 - b1) * m.v1, eC = (b3 - t2) * m.v2, eD = (b4 - b3) * m.v3;
+    FEj = tflux_fin<UP>(b1, t2, eA, eB, eC, f.v0);
+    FEjp = tflux_fin<UP>(t2, b3, eB, eC, eD, f.v1);
   }
 }
 template <bool UP, bool NEAR>
-__device__ __forceinline__ double tdiv(const KP& p, const double* __restrict__ t, ix_t c, int i, int j, int k, const TMask& m) {
+__device__ __forceinline__ double tdiv(const KP& p, const double* __restrict__ t, ix_t c, int i, int j, int k, const TMask& m, const Flx4& f) {
   double FXi, FXip, FEj, FEjp;
-  tflux4<UP, NEAR>(p, t, c, i, j, k, m, FXi, FXip, FEj, FEjp);
+  tflux4<UP, NEAR>(p, t, c, i, j, k, m, f, FXi, FXip, FEj, FEjp);
   return FXip - FXi + FEjp - FEj;
 }
 // compute_horiz_tracer_fluxes.h:217-246: the flux through a river face is the river's tracer value times its volume flux,
@@ -875,21 +878,33 @@ __device__ __forceinline__ RivFaces riv_faces(const KP& p, ix_t c) {
   return r;
 }
 template <bool UP>
-__device__ __forceinline__ double tdiv_riv(const KP& p, const double* __restrict__ t, ix_t c, int i, int j, int k, const TMask& m, bool near, const RivFaces& r,
-                                           int itrc) {
+__device__ __forceinline__ double tdiv_riv(const KP& p, const double* __restrict__ t, ix_t c, int i, int j, int k, const TMask& m, const Flx4& f, bool near,
+                                           const RivFaces& r, int itrc) {
   double FXi, FXip, FEj, FEjp;
-  if (near) tflux4<UP, true>(p, t, c, i, j, k, m, FXi, FXip, FEj, FEjp);
-  else tflux4<UP, false>(p, t, c, i, j, k, m, FXi, FXip, FEj, FEjp);
+  if (near) tflux4<UP, true>(p, t, c, i, j, k, m, f, FXi, FXip, FEj, FEjp);
+  else tflux4<UP, false>(p, t, c, i, j, k, m, f, FXi, FXip, FEj, FEjp);
   if (riv_on(r.u0)) FXi = riv_tflux(p, r.u0, c, 1, k, itrc);
   if (riv_on(r.u1)) FXip = riv_tflux(p, r.u1, c + 1, 1, k, itrc);
   if (riv_on(r.v0)) FEj = riv_tflux(p, r.v0, c, p.SX, k, itrc);
   if (riv_on(r.v1)) FEjp = riv_tflux(p, r.v1, c + p.SX, p.SX, k, itrc);
   return FXip - FXi + FEjp - FEj;
 }
-template <bool WALL, int KB, bool RIV>
-__global__ void __launch_bounds__(256, LB_TP) k_pre_t_horiz(const __grid_constant__ KP p, const double* __restrict__ t_rhs, double* __restrict__ t_new,
-                                                            const double* __restrict__ t_stp, double* __restrict__ t_indx, double dtau, double cf_stp, double cf_bak,
-                                                            int itrc) {
+// A batch of TB tracers handled by one launch (the reference loops "do itrc=1,nt" around the same code, pre_step3d4S.F:152,
+// step3d_t_ISO.F:179): everything that does not depend on the tracer -- FlxU, FlxV, Hz, FlxDiv, We, Wi, the masks, the
+// Hz-only spline elimination, the Thomas coefficients of tracers that share a diffusivity -- is read / computed once per batch.
+template <int TB>
+struct TrcBatch {
+  const double* rhs[TB];    // t(:,:,:,nrhs,itrc)
+  double* tnew[TB];         // t(:,:,:,nnew,itrc)
+  const double* stp[TB];    // t(:,:,:,nstp,itrc)   (predictor)
+  double* indx[TB];         // t(:,:,:,indx,itrc)   (predictor)
+  const double* akt[TB];    // Akt(:,:,:,itrc<=2 ? itrc : isalt)
+  const double* stflx[TB];  // stflx(:,:,itrc)      (corrector)
+  int itrc[TB];             // 1-based tracer index: itemp = 1, isalt = 2
+};
+template <bool WALL, int KB, bool RIV, int TB>
+__global__ void __launch_bounds__(256, LB_TP) k_pre_t_horiz(const __grid_constant__ KP p, const __grid_constant__ TrcBatch<TB> tb, double dtau, double cf_stp,
+                                                            double cf_bak) {
   THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
   const int k0 = blockIdx.z * KB + 1;
   const TMask m = tmask_load(p, c);
@@ -898,21 +913,28 @@ __global__ void __launch_bounds__(256, LB_TP) k_pre_t_horiz(const __grid_constan
   RivFaces rf;
   rf.any = false;
   if (RIV) rf = riv_faces(p, c);
+  const double* __restrict__ gHz = p.Hz;
+  const double* __restrict__ gFd = p.FlxDiv;
 #pragma unroll
   for (int q = 0; q < KB; ++q) {
     const int k = k0 + q;
     if (k <= p.N) {
-      const double dv = (RIV && rf.any) ? tdiv_riv<false>(p, t_rhs, c, i, j, k, m, near, rf, itrc)
-                                        : (near ? tdiv<false, true>(p, t_rhs, c, i, j, k, m) : tdiv<false, false>(p, t_rhs, c, i, j, k, m));
-      const double Hz = R3(p.Hz, c, k), Hz_bak = Hz + R3(p.FlxDiv, c, k);
-      const double ts = R3(t_stp, c, k);
-      R3(t_new, c, k) = Hz_bak * (cf_stp * ts + cf_bak * R3(t_indx, c, k)) - cdt * (dv);
-      R3(t_indx, c, k) = Hz * ts;
+      const Flx4 f = flx4_load(p, c, k);
+      const double Hz = R3(gHz, c, k), Hz_bak = Hz + R3(gFd, c, k);
+#pragma unroll
+      for (int t = 0; t < TB; ++t) {
+        const double* __restrict__ t_rhs = tb.rhs[t];
+        const double dv = (RIV && rf.any) ? tdiv_riv<false>(p, t_rhs, c, i, j, k, m, f, near, rf, tb.itrc[t])
+                                          : (near ? tdiv<false, true>(p, t_rhs, c, i, j, k, m, f) : tdiv<false, false>(p, t_rhs, c, i, j, k, m, f));
+        const double ts = R3(tb.stp[t], c, k);
+        R3(tb.tnew[t], c, k) = Hz_bak * (cf_stp * ts + cf_bak * R3(tb.indx[t], c, k)) - cdt * (dv);
+        R3(tb.indx[t], c, k) = Hz * ts;
+      }
     }
   }
 }
-template <bool WALL, int KB, bool RIV>
-__global__ void __launch_bounds__(256, LB_TC) k_t_horiz(const __grid_constant__ KP p, const double* __restrict__ t_rhs, double* __restrict__ t_new, int itrc) {
+template <bool WALL, int KB, bool RIV, int TB>
+__global__ void __launch_bounds__(256, LB_TC) k_t_horiz(const __grid_constant__ KP p, const __grid_constant__ TrcBatch<TB> tb) {
   THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
   const int k0 = blockIdx.z * KB + 1;
   const TMask m = tmask_load(p, c);
@@ -925,9 +947,14 @@ __global__ void __launch_bounds__(256, LB_TC) k_t_horiz(const __grid_constant__ 
   for (int q = 0; q < KB; ++q) {
     const int k = k0 + q;
     if (k <= p.N) {
-      const double dv = (RIV && rf.any) ? tdiv_riv<true>(p, t_rhs, c, i, j, k, m, near, rf, itrc)
-                                        : (near ? tdiv<true, true>(p, t_rhs, c, i, j, k, m) : tdiv<true, false>(p, t_rhs, c, i, j, k, m));
-      R3(t_new, c, k) = R3(t_new, c, k) - cdt * (dv);
+      const Flx4 f = flx4_load(p, c, k);
+#pragma unroll
+      for (int t = 0; t < TB; ++t) {
+        const double* __restrict__ t_rhs = tb.rhs[t];
+        const double dv = (RIV && rf.any) ? tdiv_riv<true>(p, t_rhs, c, i, j, k, m, f, near, rf, tb.itrc[t])
+                                          : (near ? tdiv<true, true>(p, t_rhs, c, i, j, k, m, f) : tdiv<true, false>(p, t_rhs, c, i, j, k, m, f));
+        R3(tb.tnew[t], c, k) = R3(tb.tnew[t], c, k) - cdt * (dv);
+      }
     }
   }
 }
@@ -1808,7 +1835,7 @@ __global__ void k_lmd_smooth(const __grid_constant__ KP p, const double* __restr
   out[c + (ix_t)blockIdx.z * p.SXY] = r;
 }
 // interior mixing from the smoothed Rig, bottom taper, end values and the ascending in-place 1-2-1 filter (lmd_vmix.F:253-407)
-__global__ void k_lmd_vmix_col(const __grid_constant__ KP p, const double* __restrict__ Rig, double Akv_bak, double Akt_bak0, double Akt_bak1) {
+__global__ void k_lmd_vmix_col(const __grid_constant__ KP p, const double* __restrict__ Rig, double Akv_bak, double Akt_bak0, double Akt_bak1, int convec) {
   THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
   const int N = p.N;
   const double nu0m = 1.e-2, nu0s = 1.e-2, nuwm = 1.0e-4, nuws = 0.1e-4, Lturb = 10., pi = 3.14159265358979323;
@@ -1819,7 +1846,7 @@ __global__ void k_lmd_vmix_col(const __grid_constant__ KP p, const double* __res
     double nu_sx = 1. - cff * cff;
     nu_sx = nu_sx * nu_sx * nu_sx;
     double kv = nuwm + nu0m * nu_sx, kt = nuws + nu0s * nu_sx;
-    if (RW(Rig, c, k) < 0.) { kv = kv + 0.1; kt = kt + 0.1; }      // LMD_CONVEC (lmd_vmix.F:269-274): nu0c
+    if (convec && RW(Rig, c, k) < 0.) { kv = kv + 0.1; kt = kt + 0.1; }      // LMD_CONVEC (lmd_vmix.F:269-274): nu0c
     double ks = kt;
     const double dist = RW(p.z_w, c, k) - zw0;
     if (dist < Lturb) {
@@ -1848,8 +1875,8 @@ __global__ void k_lmd_kpp1(const __grid_constant__ KP p, const double* __restric
   const double g = p.g;
   const double Bo = g * (alpha[c] * (stflxT[c] - p.srflx[c]) - beta[c] * (stflxS ? stflxS[c] : 0.0));
   const double Bosol = g * alpha[c] * p.srflx[c];
-  const double sr = 0.5 * (p.sustr[c] + p.sustr[c + 1]), vr = 0.5 * (p.svstr[c] + p.svstr[c + SX]);
-  const double us = sqrt(sqrt(sr * sr + vr * vr));
+  const double su0 = p.sustr[c], su1 = p.sustr[c + 1], sv0 = p.svstr[c], sv1 = p.svstr[c + SX];
+  const double us = sqrt(sqrt(0.333333333333 * (su0 * su0 + su1 * su1 + su0 * su1 + sv0 * sv0 + sv1 * sv1 + sv0 * sv1)));   // lmd_kpp.F:176-180 (no BULK_FRC)
   p.k_Bo[c] = Bo; p.k_Bosol[c] = Bosol; p.k_ustar[c] = us;
   const double hbl0 = p.hbls[c], bbl0 = p.hbbl[c];
   const double zwN = RW(p.z_w, c, N), zw0 = RW(p.z_w, c, 0), ff = p.f[c];

@@ -57,6 +57,8 @@ struct roms_ctx {
   int col_bx = 32, col_by = 2, pl_bx = 32, pl_by = 8;   // plane tiles 32x8: fewest halo-row re-reads through L2 (profiles/r1_tuning_log.txt)
   double* kpp_buf = nullptr;   // LMD/KPP arrays (roms_set_kpp)
   double *kpp_Rig = nullptr, *kpp_RigS = nullptr, *kpp_FC = nullptr, *kpp_hblS = nullptr, *kpp_bblS = nullptr, *kpp_alpha = nullptr, *kpp_beta = nullptr;
+  int kpp_convec = 1;     // cppdefs LMD_CONVEC
+  double kpp_Akv_bak = 0.0, kpp_Akt_bak[2] = {0.0, 0.0};   // vertical_mixing keyword
   int fuse_rho = 1;       // a rho_eos call is deferred; if prsgrd follows (main.F:397-413, 430-445) both run as one fused column kernel
   int rho_pending = 0;    // time index of the deferred rho_eos (0: none)
   int uv2_sm = 1;     // k_uv2_pass1 with the column parked in shared memory (1.0 -> 0.78 ms on B200); off when the column is too tall
@@ -309,7 +311,7 @@ int roms_create(const roms_cfg* cfg, int device, roms_ctx** out) {
   P1(Wi, ROMS_WI); P1(rho1, ROMS_RHO1); P1(qp1, ROMS_QP1); P1(Akv, ROMS_AKV); P1(ru, ROMS_RU); P1(rv, ROMS_RV);
   P1(pmask, ROMS_PMASK); P1(dm_p, ROMS_DM_P); P1(dn_p, ROMS_DN_P); P1(pmon_u, ROMS_PMON_U); P1(pnom_v, ROMS_PNOM_V);
   P1(visc2_r, ROMS_VISC2_R); P1(visc2_p, ROMS_VISC2_P);
-  P1(riv_uflx, ROMS_RIV_UFLX); P1(riv_vflx, ROMS_RIV_VFLX); P1(pipe_idx, ROMS_PIPE_IDX); P1(pipe_flx, ROMS_PIPE_FLX); P1(ptide, ROMS_PTIDE);
+  P1(riv_uflx, ROMS_RIV_UFLX); P1(riv_vflx, ROMS_RIV_VFLX); P1(pipe_idx, ROMS_PIPE_IDX); P1(pipe_flx, ROMS_PIPE_FLX); P1(ptide, ROMS_PTIDE); P1(srflx, ROMS_SRFLX);
 #undef P1
   p.Akt[0] = h->f[ROMS_AKT].ptr[0]; p.Akt[1] = h->f[ROMS_AKT].ptr[1];
   host_scoord(h);
@@ -838,11 +840,15 @@ int roms_set_kpp(roms_ctx* h, int on) {
     auto take = [&](size_t n) { double* r = cur; cur += n; return r; };
     p.bvf = take(nw); p.swr_frac = take(nw); p.ghat = take(nw);
     h->kpp_Rig = take(nw); h->kpp_RigS = take(nw); h->kpp_FC = take(nw);
-    p.hbls = take(n2); p.hbbl = take(n2); p.srflx = take(n2);
+    p.hbls = take(n2); p.hbbl = take(n2); take(n2);   /* (srflx is a field of the arena: ROMS_SRFLX) */
     p.k_ustar = take(n2); p.k_Bo = take(n2); p.k_Bosol = take(n2); p.k_hbl = take(n2); p.k_bbl = take(n2);
     h->kpp_hblS = take(n2); h->kpp_bblS = take(n2); h->kpp_alpha = take(n2); h->kpp_beta = take(n2);
   }
   p.lmd_kpp = 1;
+  return 0;
+}
+int roms_set_kpp_opts(roms_ctx* h, int lmd_convec, double Akv_bak, double Akt_bak_T, double Akt_bak_S) {
+  h->kpp_convec = lmd_convec ? 1 : 0; h->kpp_Akv_bak = Akv_bak; h->kpp_Akt_bak[0] = Akt_bak_T; h->kpp_Akt_bak[1] = Akt_bak_S;
   return 0;
 }
 int roms_get_hbl(roms_ctx* h, double* hbls, double* hbbl) {
@@ -869,7 +875,7 @@ int roms_lmd_vmix(roms_ctx* h, int tind) {
   k_lmd_edges<<<dim3((len + 127) / 128, 5, N - 1), eb, 0, h->st>>>(p, h->kpp_Rig + p.SXY, imin, imax, jmin, jmax);
   h->launches++;
   PLANE(k_lmd_smooth, p.iend, p.jstr, p.jend, N - 1, p, h->kpp_Rig + p.SXY, h->kpp_RigS + p.SXY, 0);
-  COLUMN(k_lmd_vmix_col, 0, p.iend, p.jstr, p.jend, p, h->kpp_RigS, 0.0, 0.0, 0.0);
+  COLUMN(k_lmd_vmix_col, 0, p.iend, p.jstr, p.jend, p, h->kpp_RigS, h->kpp_Akv_bak, h->kpp_Akt_bak[0], h->kpp_Akt_bak[1], h->kpp_convec);
   COLUMN(k_alfabeta, 0, p.iend + 2, p.jstr - 2, p.jend + 2, p, h->t(h->nstp, 1), h->c.NT >= 2 ? h->t(h->nstp, 2) : nullptr, h->kpp_alpha, h->kpp_beta);
   COLUMN(k_lmd_kpp1, 0, imax, jmin, jmax, p, h->u(tind), h->v(tind), h->kpp_alpha, h->kpp_beta, h->f[ROMS_STFLX].ptr[0],
          h->c.NT >= 2 ? h->f[ROMS_STFLX].ptr[1] : (double*)nullptr, h->kpp_FC, imin, imax, jmin, jmax);

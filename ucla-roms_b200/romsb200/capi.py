@@ -24,7 +24,7 @@ FIELDS = ["H", "PM", "PN", "F", "RMASK", "UMASK", "VMASK", "DM_U", "DN_U", "DM_V
           "DV_AVG1", "DU_AVG2", "DV_AVG2", "DU_AVG_BAK", "DV_AVG_BAK", "R_D", "SUSTR", "SVSTR", "SWFLX",
           "STFLX", "U", "V", "T", "HZ", "Z_R", "Z_W", "FLXU", "FLXV", "WE", "WI", "RHO1", "QP1", "AKV", "AKT",
           "RU", "RV", "PMASK", "DM_P", "DN_P", "PMON_U", "PNOM_V", "VISC2_R", "VISC2_P", "DIFF2", "RIV_UFLX", "RIV_VFLX",
-          "PTIDE", "PIPE_IDX", "PIPE_FLX"]
+          "PTIDE", "PIPE_IDX", "PIPE_FLX", "SRFLX"]
 FID = {n: i for i, n in enumerate(FIELDS)}
 
 
