@@ -81,7 +81,8 @@ def test_rivers_ana_startup_on_gpu():
 @pytest.mark.parametrize("case", ["channel", "filament", "channel_linear_odd", "channel_walls", "channel_walls_linear_odd",
                                   "seamount_island_walls", "seamount_island_periodic", "closed_basin", "closed_basin_seamount_odd",
                                   "ew_walls_ns_periodic", "channel_mixing", "closed_basin_seamount_mixing", "filament_mixing_switches",
-                                  "closed_basin_river", "walled_channel_river_mixing", "walled_channel_pipe", "closed_basin_river_pipe", "closed_basin_tide", "rivers_ana_without_kpp"])
+                                  "closed_basin_river", "walled_channel_river_mixing", "walled_channel_pipe", "closed_basin_river_pipe", "closed_basin_tide", "rivers_ana_without_kpp",
+                                  "channel_nt8", "closed_basin_nt7_river", "channel_walls_n64", "closed_basin_seamount_n100", "periodic_nt5_mixing"])
 def test_routine_by_routine(case):
     if case == "channel":
         cfg, st = cases.channel(48, 40, 12)
@@ -118,6 +119,16 @@ def test_routine_by_routine(case):
         cfg, st = cases.channel(40, 36, 8, ns_walls=True, ew_walls=True, seamount=True, tide=True)
     elif case == "rivers_ana_without_kpp":                              # the reference's tests/Rivers_ana, uniform Akv/Akt instead of KPP
         cfg, st = cases.rivers_ana(1.0e-4, 1.0e-5)
+    elif case == "channel_nt8":                                         # tracer batches (T,S) + 4 + 2 (TrcBatch in kernels.cuh)
+        cfg, st = cases.channel(40, 33, 10, NT=8, ns_walls=True)
+    elif case == "closed_basin_nt7_river":                              # batches 2 + 4 + 1, river tracer values per tracer, land mask
+        cfg, st = cases.channel(37, 31, 9, NT=7, ns_walls=True, ew_walls=True, river=True, pipe=True, dt=60.0)
+    elif case == "periodic_nt5_mixing":                                 # batches 2 + 2 + 1, doubly periodic, per-tracer diffusivities
+        cfg, st = cases.channel(33, 30, 8, NT=5, visc2=60.0, tnu2=30.0, sponge=True)
+    elif case == "channel_walls_n64":                                   # the bench column height (configs[1]: N=64): KB_T=8 blocks, KC=4 chunks
+        cfg, st = cases.channel(70, 44, 64, ns_walls=True)
+    elif case == "closed_basin_seamount_n100":                          # configs[2] column height (N=100 is not a multiple of 8)
+        cfg, st = cases.channel(44, 36, 100, ns_walls=True, ew_walls=True, seamount=True)
     elif case == "filament":
         cfg, st = cases.filament(64, 64, 32)
     else:
@@ -257,6 +268,44 @@ def test_kpp_closure_on_gpu():
     r = compare(g, o, cfg.NT, 1e-9, cfg)
     print("Rivers_ana with KPP, 20 steps:", r)
     g.close(); o.close()
+
+
+def kpp_flux_case(Lm=40, Mm=36, N=12):
+    """closed basin 200 m deep with the KPP closure on and NON-ZERO surface forcing: net cooling with shortwave heating
+    (Bfsfc < 0 under the surface -> ghat != 0: the LMD_NONLOCAL terms of step3d_t_ISO.F:961-998), a salt flux and a
+    non-uniform wind stress (ustar of lmd_kpp.F:176-180)."""
+    cfg, st = cases.channel(Lm, Mm, N, ns_walls=True, ew_walls=True, seamount=True, depth=200.0, dt=60.0)
+    cfg.Zob = 1.0e-2
+    st["KPP"] = True
+    sy, sx = Mm + 4, Lm + 4
+    x = (np.arange(sx)[None, :] - 1.5) / Lm + np.zeros((sy, 1)); y = (np.arange(sy)[:, None] - 1.5) / Mm + np.zeros((1, sx))
+    srflx = 3.7e-5 * (1.0 + 0.3 * np.cos(2 * np.pi * x))
+    st["SRFLX"] = srflx
+    st["STFLX"] = {(1, 1): srflx - 4.9e-5 * (1.0 + 0.5 * np.sin(2 * np.pi * y)), (1, 2): 2.0e-6 * (1.0 + 0.5 * np.cos(2 * np.pi * (x + y)))}
+    st["SUSTR"] = 1.0e-4 * (1.0 + 0.8 * np.sin(2 * np.pi * y) * np.cos(np.pi * x))
+    st["SVSTR"] = 0.6e-4 * np.cos(2 * np.pi * x) * (1.0 + 0.5 * y)
+    return cfg, st
+
+
+def test_kpp_surface_fluxes_on_gpu():
+    """the consumer half of the closure (VERDICT f2): srflx*swr_frac and ghat in the tracer corrector, ustar from a
+    non-uniform wind stress, LMD_CONVEC off and non-zero background coefficients (roms_set_kpp_opts)."""
+    for opts in (None, (0, 1.0e-4, 1.0e-5, 2.0e-5)):
+        cfg, st = kpp_flux_case()
+        g, o = Roms(cfg), Oracle(cfg)
+        for m in (g, o):
+            cases.initialize(m, st)
+            if opts:
+                m.call("set_kpp_opts", opts[0], *[__import__("ctypes").c_double(v) for v in opts[1:]])
+        g.call("step"); o.call("step")
+        r1 = compare(g, o, cfg.NT, 1e-11, cfg)
+        g.call("run", 19); o.call("run", 19)
+        r20 = compare(g, o, cfg.NT, 1e-9, cfg)
+        for f, it in (("AKV", 1), ("AKT", 1), ("AKT", 2)):
+            a, b = parity_walk.view(g.pull(f, 1, it), cfg), parity_walk.view(o.pull(f, 1, it), cfg)
+            assert parity_walk.rel(a, b) <= 1e-9, (f, it, parity_walk.rel(a, b))
+        print("KPP with surface fluxes", opts, r1, r20)
+        g.close(); o.close()
 
 
 def test_pipes_ana_golden_on_gpu():

@@ -903,7 +903,7 @@ struct TrcBatch {
   int itrc[TB];             // 1-based tracer index: itemp = 1, isalt = 2
 };
 template <bool WALL, int KB, bool RIV, int TB>
-__global__ void __launch_bounds__(256, LB_TP) k_pre_t_horiz(const __grid_constant__ KP p, const __grid_constant__ TrcBatch<TB> tb, double dtau, double cf_stp,
+__global__ void __launch_bounds__(256, (TB == 1 ? LB_TP : (TB == 2 ? 4 : 3))) k_pre_t_horiz(const __grid_constant__ KP p, const __grid_constant__ TrcBatch<TB> tb, double dtau, double cf_stp,
                                                             double cf_bak) {
   THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
   const int k0 = blockIdx.z * KB + 1;
@@ -934,7 +934,7 @@ __global__ void __launch_bounds__(256, LB_TP) k_pre_t_horiz(const __grid_constan
   }
 }
 template <bool WALL, int KB, bool RIV, int TB>
-__global__ void __launch_bounds__(256, LB_TC) k_t_horiz(const __grid_constant__ KP p, const __grid_constant__ TrcBatch<TB> tb) {
+__global__ void __launch_bounds__(256, (TB == 1 ? LB_TC : (TB == 2 ? 3 : 2))) k_t_horiz(const __grid_constant__ KP p, const __grid_constant__ TrcBatch<TB> tb) {
   THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
   const int k0 = blockIdx.z * KB + 1;
   const TMask m = tmask_load(p, c);
@@ -995,77 +995,135 @@ __global__ void k_rd_bott_drag(const __grid_constant__ KP p, const double* __res
 
 // ------------------------------------------------------------------------------------------------
 // Tracer column kernel: compute_vert_tracer_fluxes.h:1-140 (SPLINE_TS) + flux divergence + implicit
-// vertical diffusion/advection Thomas solve.  MODE 0: predictor (pre_step3d4S.F:201-263, dtau, Hz_fwd);
-// MODE 1: corrector (step3d_t_ISO.F:907-1100: dt, Hz, swflx/stflx at the surface, rmask).
-// Four sweeps (up, down, up, down) with two shared-memory arrays per thread:
-//   A: spline CF(2:N)            -> Thomas CF(1:N-1)
-//   B: spline FC(0:N-1) -> rhs(1:N) -> Thomas DC(1:N-1)
+// vertical diffusion/advection Thomas solve, for a batch of TB tracers per thread.
+// MODE 0: predictor (pre_step3d4S.F:201-263, dtau, Hz_fwd);
+// MODE 1: corrector (step3d_t_ISO.F:907-1100: dt, Hz, swflx/stflx at the surface, the LMD_KPP solar-penetration and
+//         non-local transport terms :961-998, pipes :927-935, rmask).
+// Four sweeps (up, down, up, down).  Scratch (global slab, [k][j][i]): array 0 = spline CF(2:N), shared by the batch (it
+// depends on Hz only); array 1+t = spline FC(0:N-1) of tracer t.  The right-hand side and the Thomas DC of every tracer are
+// parked IN t(nnew) itself (each level is read before it is overwritten), and the Thomas CF re-uses the dead spline slots:
+// array 0 when the batch shares one diffusivity (SHARE), else array 1+t.
 #define KC 4   // levels per register chunk: all global/scratch loads of a chunk are issued before its arithmetic
-template <int MODE>
-__global__ void __launch_bounds__(64, 12)
-k_t_vert(const __grid_constant__ KP p, const double* __restrict__ t_rhs, double* __restrict__ t_new, const double* __restrict__ Akt,
-         const double* __restrict__ stflx, double dtau, int is_temp, int itrc) {
+#ifndef LB_TV1
+#define LB_TV1 12
+#endif
+#ifndef LB_TV2
+#define LB_TV2 8
+#endif
+#ifndef LB_TV4
+#define LB_TV4 5
+#endif
+template <int MODE, int TB, bool SHARE>
+__global__ void __launch_bounds__(64, (TB == 1 ? LB_TV1 : (TB == 2 ? LB_TV2 : LB_TV4)))
+k_t_vert(const __grid_constant__ KP p, const __grid_constant__ TrcBatch<TB> tb, double dtau) {
   extern __shared__ double smem[];
   THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
   ColScr sc = col_scratch(p, c, smem);
+  constexpr int TA = SHARE ? 1 : TB;     // distinct diffusivities in the batch
   const int N = p.N;
   const double* __restrict__ gHz = p.Hz;
   const double* __restrict__ gWe = p.We;
   const double* __restrict__ gWi = p.Wi;
   const double* __restrict__ gFd = p.FlxDiv;
   // ---- sweep 1 (up): spline forward elimination
-  double Hzk = R3(gHz, c, 1), tk = R3(t_rhs, c, 1);
-  double CFk = 1.0, FCkm = 2.0 * tk;
-  S(1, 0) = FCkm;
+  double Hzk = R3(gHz, c, 1), CFk = 1.0;
+  double tk[TB], FCkm[TB];
+#pragma unroll
+  for (int t = 0; t < TB; ++t) {
+    tk[t] = R3(tb.rhs[t], c, 1);
+    FCkm[t] = 2.0 * tk[t];
+    S(1 + t, 0) = FCkm[t];
+  }
   for (int k0 = 1; k0 <= N - 1; k0 += KC) {
-    double hz[KC], tt[KC];
+    double hz[KC], tt[TB][KC];
 #pragma unroll
     for (int q = 0; q < KC; ++q)
-      if (k0 + q <= N - 1) { hz[q] = R3(gHz, c, k0 + q + 1); tt[q] = R3(t_rhs, c, k0 + q + 1); }
+      if (k0 + q <= N - 1) {
+        hz[q] = R3(gHz, c, k0 + q + 1);
+#pragma unroll
+        for (int t = 0; t < TB; ++t) { const double* __restrict__ r = tb.rhs[t]; tt[t][q] = R3(r, c, k0 + q + 1); }
+      }
 #pragma unroll
     for (int q = 0; q < KC; ++q) {
       const int k = k0 + q;
       if (k <= N - 1) {
-        const double Hzp = hz[q], tp = tt[q];
+        const double Hzp = hz[q];
         const double cff = 1.0 / (2.0 * Hzk + Hzp * (2.0 - CFk));
         CFk = cff * Hzk;                                            // CF(k+1)
-        FCkm = cff * (3.0 * (Hzk * tp + Hzp * tk) - Hzp * FCkm);   // FC(k)
         S(0, k + 1) = CFk;
-        S(1, k) = FCkm;
-        Hzk = Hzp; tk = tp;
+#pragma unroll
+        for (int t = 0; t < TB; ++t) {
+          const double tp = tt[t][q];
+          FCkm[t] = cff * (3.0 * (Hzk * tp + Hzp * tk[t]) - Hzp * FCkm[t]);   // FC(k)
+          S(1 + t, k) = FCkm[t];
+          tk[t] = tp;
+        }
+        Hzk = Hzp;
       }
     }
   }
-  // ---- sweep 2 (down): back-substitution, vertical flux and its divergence -> rhs(k) in B
+  // ---- sweep 2 (down): back-substitution, vertical flux and its divergence -> rhs(k) parked in t(nnew)
   const double cdt = dtau * p.pm[c] * p.pn[c];
   const int pidx = (MODE == 1 && p.pipes) ? (int)p.pipe_idx[c] : 0;
-  const double pflx = pidx > 0 ? p.pipe_flx[c] : 0.0, ptrc = pidx > 0 ? p.pipe_tab[(pidx - 1) * PIPROW(N) + N + itrc - 1] : 0.0;
-  double FCs_p = (2.0 * tk - FCkm) / (1.0 - CFk);   // FC(N) spline value
-  double flux_p = 0.0;                               // FC(N)=0 after the sweep
+  const double pflx = pidx > 0 ? p.pipe_flx[c] : 0.0;
+  const bool kpp = MODE == 1 && p.lmd_kpp;
+  const double srflx = kpp ? p.srflx[c] : 0.0;
+  double FCs_p[TB], flux_p[TB], ptrc[TB], sfl[TB], kcf_up[TB];
+#pragma unroll
+  for (int t = 0; t < TB; ++t) {
+    FCs_p[t] = (2.0 * tk[t] - FCkm[t]) / (1.0 - CFk);   // FC(N) spline value
+    flux_p[t] = 0.0;                                     // FC(N)=0 after the sweep
+    ptrc[t] = pidx > 0 ? p.pipe_tab[(pidx - 1) * PIPROW(N) + N + tb.itrc[t] - 1] : 0.0;
+    sfl[t] = MODE == 1 ? tb.stflx[t][c] : 0.0;
+    kcf_up[t] = 0.0;
+  }
   for (int k0 = N - 1; k0 >= 0; k0 -= KC) {
-    double b1[KC], a0[KC], we[KC], tn[KC];
+    double a0[KC], we[KC], b1[TB][KC], tn[TB][KC];
 #pragma unroll
     for (int q = 0; q < KC; ++q) {
       const int k = k0 - q;
       if (k >= 0) {
-        tn[q] = R3(t_new, c, k + 1);
-        if (k >= 1) { b1[q] = S(1, k); a0[q] = S(0, k + 1); we[q] = RW(gWe, c, k); }
+        if (k >= 1) { a0[q] = S(0, k + 1); we[q] = RW(gWe, c, k); }
+#pragma unroll
+        for (int t = 0; t < TB; ++t) {
+          tn[t][q] = R3(tb.tnew[t], c, k + 1);
+          if (k >= 1) b1[t][q] = S(1 + t, k);
+        }
       }
     }
 #pragma unroll
     for (int q = 0; q < KC; ++q) {
       const int k = k0 - q;
       if (k >= 0) {
-        double FCs = 0.0, flux = 0.0;                        // FC(0) of the spline is never used (flux(0)=0)
-        if (k >= 1) { FCs = b1[q] - a0[q] * FCs_p; flux = FCs * we[q]; }
-        double r = tn[q] - cdt * (flux_p - flux);            // rhs(k+1) = t_new(k+1) - cdt*(flux(k+1)-flux(k))
-        if (MODE == 1 && pidx > 0) r = r + cdt * pflx * p.pipe_tab[(pidx - 1) * PIPROW(N) + k] * ptrc;   // step3d_t_ISO.F:927-935 (level k+1)
-        if (MODE == 1 && k + 1 == N) {
-          if (is_temp) r = r + p.dt * p.swflx[c] * r / R3(gHz, c, N);
-          r = r + p.dt * stflx[c];
+        double gh = 0.0, sw = 0.0;
+        if (kpp && k >= 1) { gh = RW(p.ghat, c, k); sw = RW(p.swr_frac, c, k); }
+#pragma unroll
+        for (int t = 0; t < TB; ++t) {
+          double FCs = 0.0, flux = 0.0;                        // FC(0) of the spline is never used (flux(0)=0)
+          if (k >= 1) { FCs = b1[t][q] - a0[q] * FCs_p[t]; flux = FCs * we[q]; }
+          double r = tn[t][q] - cdt * (flux_p[t] - flux);      // rhs(k+1) = t_new(k+1) - cdt*(flux(k+1)-flux(k))
+          if (MODE == 1 && pidx > 0) r = r + cdt * pflx * p.pipe_tab[(pidx - 1) * PIPROW(N) + k] * ptrc[t];   // step3d_t_ISO.F:927-935 (level k+1)
+          if (MODE == 1 && k + 1 == N) {
+            if (tb.itrc[t] == 1) r = r + p.dt * p.swflx[c] * r / R3(gHz, c, N);
+            r = r + p.dt * sfl[t];
+          }
+          if (kpp && tb.itrc[t] <= 2) {   // step3d_t_ISO.F:961-998, reference order k=N-1..1: level k+1 first loses dt*cff(k+1)... see below
+            // the reference's loop visits interface k+1 (adds +dt*cff(k+1) to level k+1) BEFORE interface k (subtracts dt*cff(k))
+            if (tb.itrc[t] == 1) {
+              if (k + 1 <= N - 1) r = r + p.dt * kcf_up[t];
+              double cf = 0.0;
+              if (k >= 1) { cf = srflx * sw - gh * (sfl[t] - srflx); r = r - p.dt * cf; }
+              kcf_up[t] = cf;
+            } else {
+              if (k + 1 <= N - 1) r = r + kcf_up[t];
+              double cf = 0.0;
+              if (k >= 1) { cf = -p.dt * gh * sfl[t]; r = r - cf; }
+              kcf_up[t] = cf;
+            }
+          }
+          R3(tb.tnew[t], c, k + 1) = r;
+          FCs_p[t] = FCs; flux_p[t] = flux;
         }
-        S(1, k + 1) = r;
-        FCs_p = FCs; flux_p = flux;
       }
     }
   }
@@ -1073,22 +1131,37 @@ k_t_vert(const __grid_constant__ KP p, const double* __restrict__ t_rhs, double*
   const double DC0 = cdt;
   double Hzf1 = R3(gHz, c, 1), Hzf2 = R3(gHz, c, 2);
   if (MODE == 0) { Hzf1 -= R3(gFd, c, 1); Hzf2 -= R3(gFd, c, 2); }
-  double FCt = 2.0 * dtau * RW(Akt, c, 1) / (MODE == 0 ? (Hzf2 + Hzf1) : (Hzf1 + Hzf2));
   double WC = DC0 * RW(gWi, c, 1);
-  double cff = 1.0 / (Hzf1 + FCt + DMAX(WC, 0.0));
-  double CFt = cff * (FCt - DMIN(WC, 0.0));
-  double DCt = cff * S(1, 1);
-  S(0, 1) = CFt; S(1, 1) = DCt;
+  double FCt[TA], CFt[TA], DCt[TB];
+  {
+    double cffa[TA];
+#pragma unroll
+    for (int a = 0; a < TA; ++a) {
+      FCt[a] = 2.0 * dtau * RW(tb.akt[a], c, 1) / (MODE == 0 ? (Hzf2 + Hzf1) : (Hzf1 + Hzf2));
+      cffa[a] = 1.0 / (Hzf1 + FCt[a] + DMAX(WC, 0.0));
+      CFt[a] = cffa[a] * (FCt[a] - DMIN(WC, 0.0));
+      S(SHARE ? 0 : 1 + a, 1) = CFt[a];
+    }
+#pragma unroll
+    for (int t = 0; t < TB; ++t) {
+      DCt[t] = cffa[SHARE ? 0 : t] * R3(tb.tnew[t], c, 1);
+      R3(tb.tnew[t], c, 1) = DCt[t];
+    }
+  }
   double Hzfk = Hzf2;
   for (int k0 = 2; k0 <= N - 1; k0 += KC) {
-    double hz[KC], ak[KC], wi[KC], rh[KC];
+    double hz[KC], wi[KC], ak[TA][KC], rh[TB][KC];
 #pragma unroll
     for (int q = 0; q < KC; ++q) {
       const int k = k0 + q;
       if (k <= N - 1) {
         hz[q] = R3(gHz, c, k + 1);
         if (MODE == 0) hz[q] -= R3(gFd, c, k + 1);
-        ak[q] = RW(Akt, c, k); wi[q] = RW(gWi, c, k); rh[q] = S(1, k);
+        wi[q] = RW(gWi, c, k);
+#pragma unroll
+        for (int a = 0; a < TA; ++a) { const double* __restrict__ A = tb.akt[a]; ak[a][q] = RW(A, c, k); }
+#pragma unroll
+        for (int t = 0; t < TB; ++t) rh[t][q] = R3(tb.tnew[t], c, k);
       }
     }
 #pragma unroll
@@ -1096,33 +1169,59 @@ k_t_vert(const __grid_constant__ KP p, const double* __restrict__ t_rhs, double*
       const int k = k0 + q;
       if (k <= N - 1) {
         const double Hzfp = hz[q];
-        const double FCtk = 2.0 * dtau * ak[q] / (MODE == 0 ? (Hzfp + Hzfk) : (Hzfk + Hzfp));
         const double WCk = DC0 * wi[q];
-        cff = 1.0 / (Hzfk + FCtk + DMAX(WCk, 0.0) + FCt - DMIN(WC, 0.0) - CFt * (FCt + DMAX(WC, 0.0)));
-        const double CFtk = cff * (FCtk - DMIN(WCk, 0.0));
-        DCt = cff * (rh[q] + DCt * (FCt + DMAX(WC, 0.0)));
-        S(0, k) = CFtk; S(1, k) = DCt;
-        CFt = CFtk; FCt = FCtk; WC = WCk; Hzfk = Hzfp;
+        double cffa[TA], FCtk[TA];
+#pragma unroll
+        for (int a = 0; a < TA; ++a) {
+          FCtk[a] = 2.0 * dtau * ak[a][q] / (MODE == 0 ? (Hzfp + Hzfk) : (Hzfk + Hzfp));
+          cffa[a] = 1.0 / (Hzfk + FCtk[a] + DMAX(WCk, 0.0) + FCt[a] - DMIN(WC, 0.0) - CFt[a] * (FCt[a] + DMAX(WC, 0.0)));
+        }
+#pragma unroll
+        for (int t = 0; t < TB; ++t) {
+          const int a = SHARE ? 0 : t;
+          DCt[t] = cffa[a] * (rh[t][q] + DCt[t] * (FCt[a] + DMAX(WC, 0.0)));
+          R3(tb.tnew[t], c, k) = DCt[t];
+        }
+#pragma unroll
+        for (int a = 0; a < TA; ++a) {
+          CFt[a] = cffa[a] * (FCtk[a] - DMIN(WCk, 0.0));
+          S(SHARE ? 0 : 1 + a, k) = CFt[a];
+          FCt[a] = FCtk[a];
+        }
+        WC = WCk; Hzfk = Hzfp;
       }
     }
   }
   // ---- sweep 4 (down): back-substitution
   const double rm = MODE == 1 ? p.rmask[c] : 1.0;
-  double tkp = (S(1, N) + DCt * (FCt + DMAX(WC, 0.0))) / (Hzfk + FCt - DMIN(WC, 0.0) - CFt * (FCt + DMAX(WC, 0.0)));
-  if (MODE == 1) tkp = tkp * rm;
-  R3(t_new, c, N) = tkp;
+  double tkp[TB];
+#pragma unroll
+  for (int t = 0; t < TB; ++t) {
+    const int a = SHARE ? 0 : t;
+    tkp[t] = (R3(tb.tnew[t], c, N) + DCt[t] * (FCt[a] + DMAX(WC, 0.0))) / (Hzfk + FCt[a] - DMIN(WC, 0.0) - CFt[a] * (FCt[a] + DMAX(WC, 0.0)));
+    if (MODE == 1) tkp[t] = tkp[t] * rm;
+    R3(tb.tnew[t], c, N) = tkp[t];
+  }
   for (int k0 = N - 1; k0 >= 1; k0 -= KC) {
-    double dc[KC], cf[KC];
+    double dc[TB][KC], cf[TA][KC];
 #pragma unroll
     for (int q = 0; q < KC; ++q)
-      if (k0 - q >= 1) { dc[q] = S(1, k0 - q); cf[q] = S(0, k0 - q); }
+      if (k0 - q >= 1) {
+#pragma unroll
+        for (int a = 0; a < TA; ++a) cf[a][q] = S(SHARE ? 0 : 1 + a, k0 - q);
+#pragma unroll
+        for (int t = 0; t < TB; ++t) dc[t][q] = R3(tb.tnew[t], c, k0 - q);
+      }
 #pragma unroll
     for (int q = 0; q < KC; ++q) {
       const int k = k0 - q;
       if (k >= 1) {
-        tkp = dc[q] + cf[q] * tkp;
-        if (MODE == 1) tkp = tkp * rm;
-        R3(t_new, c, k) = tkp;
+#pragma unroll
+        for (int t = 0; t < TB; ++t) {
+          tkp[t] = dc[t][q] + cf[SHARE ? 0 : t][q] * tkp[t];
+          if (MODE == 1) tkp[t] = tkp[t] * rm;
+          R3(tb.tnew[t], c, k) = tkp[t];
+        }
       }
     }
   }

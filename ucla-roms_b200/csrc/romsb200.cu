@@ -62,6 +62,7 @@ struct roms_ctx {
   int fuse_rho = 1;       // a rho_eos call is deferred; if prsgrd follows (main.F:397-413, 430-445) both run as one fused column kernel
   int rho_pending = 0;    // time index of the deferred rho_eos (0: none)
   int uv2_sm = 1;     // k_uv2_pass1 with the column parked in shared memory (1.0 -> 0.78 ms on B200); off when the column is too tall
+  int tb_max = 4;     // most tracers per launch of the tracer kernels (ROMS_TB = 1, 2 or 4)
   int use_smem = 0;   // measured on B200 (profiles/r1_scratch_policy.txt): occupancy beats shared-memory scratch
   Comm comm;
   double* u(int l) { return f[ROMS_U].ptr[l - 1]; }
@@ -259,6 +260,7 @@ int roms_create(const roms_cfg* cfg, int device, roms_ctx** out) {
   p.wrap_y = (single && cfg->ns_periodic) ? 1 : 0;
   if (const char* e = getenv("ROMS_COL_SMEM")) h->use_smem = atoi(e);
   if (const char* e = getenv("ROMS_UV2_SM")) h->uv2_sm = atoi(e);
+  if (const char* e = getenv("ROMS_TB")) h->tb_max = atoi(e);
   if (const char* e = getenv("ROMS_FUSE_RHO")) h->fuse_rho = atoi(e);
   if ((size_t)2 * (N + 1) * 32 * sizeof(double) > 64 * 1024) h->uv2_sm = 0;   // fewer than 3 warps per SM would fit: global re-read version
   if ((size_t)2 * (N + 1) * h->col_bx * h->col_by * sizeof(double) > 200 * 1024) { h->col_by = 1; }
@@ -277,8 +279,12 @@ int roms_create(const roms_cfg* cfg, int device, roms_ctx** out) {
   // one arena: all fields + device-owned scratch
   size_t planes = 0;
   for (int id = 0; id < ROMS_NFIELDS; ++id) planes += (size_t)h->f[id].nlvl * h->f[id].ntrc * h->f[id].nk;
+  if (h->use_smem) h->tb_max = 1;
+  if (h->tb_max != 1 && h->tb_max != 2 && h->tb_max != 4) { g_err = "ROMS_TB must be 1, 2 or 4"; return -1; }
+  // column scratch slab: spline CF + one array per tracer of the largest batch (k_t_vert), 2 arrays for k_uv_vert / k_omega
+  const int scr_arrays = (NT - 2 >= 4 && h->tb_max >= 4) ? 5 : ((NT >= 2 && h->tb_max >= 2) ? 3 : 2);
   const size_t scratch_planes = (size_t)3 * N            /* FlxDiv, P, rho */
-                                + (h->use_smem ? 0 : (size_t)2 * (N + 1)) /* column scratch fallback */
+                                + (h->use_smem ? 0 : (size_t)scr_arrays * (N + 1)) /* column scratch slab */
                                 + 1 /* zeta_new */ + 2 /* ub, vb */ + 5 /* diag planes */;
   const size_t small = 2 * (size_t)(N + 1) + 64 + (size_t)MAXRIV * RIVROW + (size_t)MAXPIP * PIPROW(N);
   h->arena_doubles = (planes + scratch_planes) * (size_t)p.SXY + small;
@@ -289,7 +295,7 @@ int roms_create(const roms_cfg* cfg, int device, roms_ctx** out) {
   for (int id = 0; id < ROMS_NFIELDS; ++id)
     for (size_t s = 0; s < h->f[id].ptr.size(); ++s) h->f[id].ptr[s] = take(h->f[id].nk);
   p.FlxDiv = take(N); p.P = take(N); p.rho = take(N);
-  p.scr = h->use_smem ? nullptr : take(2 * (N + 1));
+  p.scr = h->use_smem ? nullptr : take((size_t)scr_arrays * (N + 1));
   p.zeta_new = take(1);
   h->d_ub = take(1); h->d_vb = take(1);
   for (int q = 0; q < 5; ++q) h->d_o[q] = take(1);
@@ -614,6 +620,64 @@ static int flush_rho(roms_ctx* h) {
   h->rho_pending = 0;
   return rho_eos_launch(h, tidx, false);
 }
+// ---- tracer batches: tracers handled together by one launch of the tracer kernels (see TrcBatch in kernels.cuh) ----
+struct TPlan { int n; int it[4]; bool share; };
+static std::vector<TPlan> plan_batches(const roms_ctx* h) {
+  std::vector<TPlan> v;
+  const int NT = h->c.NT, tmax = h->tb_max;
+  int it = 1;
+  if (NT >= 2 && tmax >= 2) { v.push_back({2, {1, 2, 0, 0}, false}); it = 3; }      // T and S: different diffusivities (Akt slots 1, 2)
+  else { v.push_back({1, {1, 0, 0, 0}, true}); it = 2; }
+  while (it <= NT) {                                                                // the rest share Akt(:,:,:,isalt)
+    const int left = NT - it + 1;
+    const int n = (left >= 4 && tmax >= 4) ? 4 : ((left >= 2 && tmax >= 2) ? 2 : 1);
+    TPlan b = {n, {0, 0, 0, 0}, true};
+    for (int q = 0; q < n; ++q) b.it[q] = it + q;
+    v.push_back(b);
+    it += n;
+  }
+  return v;
+}
+template <int TB>
+static TrcBatch<TB> make_batch(roms_ctx* h, const TPlan& pl, int nrhs, int nnew, int nstp, int indx) {
+  TrcBatch<TB> b;
+  for (int q = 0; q < TB; ++q) {
+    const int it = pl.it[q];
+    b.rhs[q] = h->t(nrhs, it); b.tnew[q] = h->t(nnew, it); b.stp[q] = h->t(nstp, it); b.indx[q] = h->t(indx, it);
+    b.akt[q] = h->kp.Akt[it >= 2 ? 1 : 0]; b.stflx[q] = h->f[ROMS_STFLX].ptr[it - 1]; b.itrc[q] = it;
+  }
+  return b;
+}
+// the three build variants of the horizontal tracer kernels: rivers (implies walls), walls, open periodic
+#define T_HORIZ_LAUNCH(kern, TBn, ...)                                                                                          \
+  do {                                                                                                                          \
+    if (p.rivers) PLANE((kern<true, KB_T, true, TBn>), p.iend, p.jstr, p.jend, (p.N + KB_T - 1) / KB_T, p, __VA_ARGS__);       \
+    else if (WALLED(h)) PLANE((kern<true, KB_T, false, TBn>), p.iend, p.jstr, p.jend, (p.N + KB_T - 1) / KB_T, p, __VA_ARGS__); \
+    else PLANE((kern<false, KB_T, false, TBn>), p.iend, p.jstr, p.jend, (p.N + KB_T - 1) / KB_T, p, __VA_ARGS__);               \
+  } while (0)
+static int tracer_pre_horiz(roms_ctx* h, const TPlan& pl, int nrhs, int nnew, int nstp, int indx, double dtau, double cf_stp, double cf_bak) {
+  const KP& p = h->kp;
+  if (pl.n == 4) T_HORIZ_LAUNCH(k_pre_t_horiz, 4, make_batch<4>(h, pl, nrhs, nnew, nstp, indx), dtau, cf_stp, cf_bak);
+  else if (pl.n == 2) T_HORIZ_LAUNCH(k_pre_t_horiz, 2, make_batch<2>(h, pl, nrhs, nnew, nstp, indx), dtau, cf_stp, cf_bak);
+  else T_HORIZ_LAUNCH(k_pre_t_horiz, 1, make_batch<1>(h, pl, nrhs, nnew, nstp, indx), dtau, cf_stp, cf_bak);
+  return 0;
+}
+static int tracer_cor_horiz(roms_ctx* h, const TPlan& pl, int nrhs, int nnew) {
+  const KP& p = h->kp;
+  if (pl.n == 4) T_HORIZ_LAUNCH(k_t_horiz, 4, make_batch<4>(h, pl, nrhs, nnew, nrhs, nnew));
+  else if (pl.n == 2) T_HORIZ_LAUNCH(k_t_horiz, 2, make_batch<2>(h, pl, nrhs, nnew, nrhs, nnew));
+  else T_HORIZ_LAUNCH(k_t_horiz, 1, make_batch<1>(h, pl, nrhs, nnew, nrhs, nnew));
+  return 0;
+}
+template <int MODE>
+static int tracer_vert(roms_ctx* h, const TPlan& pl, int nrhs, int nnew, double dtau) {
+  const KP& p = h->kp;
+  if (pl.n == 4) COLUMN((k_t_vert<MODE, 4, true>), 5, p.iend, p.jstr, p.jend, p, make_batch<4>(h, pl, nrhs, nnew, nrhs, nnew), dtau);
+  else if (pl.n == 2 && pl.share) COLUMN((k_t_vert<MODE, 2, true>), 3, p.iend, p.jstr, p.jend, p, make_batch<2>(h, pl, nrhs, nnew, nrhs, nnew), dtau);
+  else if (pl.n == 2) COLUMN((k_t_vert<MODE, 2, false>), 3, p.iend, p.jstr, p.jend, p, make_batch<2>(h, pl, nrhs, nnew, nrhs, nnew), dtau);
+  else COLUMN((k_t_vert<MODE, 1, true>), 2, p.iend, p.jstr, p.jend, p, make_batch<1>(h, pl, nrhs, nnew, nrhs, nnew), dtau);
+  return 0;
+}
 extern "C" {
 int roms_rho_eos(roms_ctx* h, int tidx) {
   CK(cudaSetDevice(h->device));
@@ -655,16 +719,12 @@ int roms_pre_step3d(roms_ctx* h, int tile) {
   else { dtau = dt * (1.0 - AM3_crv); cf_stp = 0.5 + AM3_crv; cf_bak = 0.5 - AM3_crv; }
   const bool wl = WALLED(h);
   PLANE(k_pre_flxdiv, p.iend, p.jstrV - 1, p.jend, p.N, p, dtau);
-  for (int it = 1; it <= h->c.NT; ++it) {
-    if (p.rivers) PLANE((k_pre_t_horiz<true, KB_T, true>), p.iend, p.jstr, p.jend, (p.N + KB_T - 1) / KB_T, p, h->t(nrhs, it), h->t(nnew, it), h->t(nstp, it), h->t(indx, it), dtau, cf_stp, cf_bak, it);
-    else if (wl) PLANE((k_pre_t_horiz<true, KB_T, false>), p.iend, p.jstr, p.jend, (p.N + KB_T - 1) / KB_T, p, h->t(nrhs, it), h->t(nnew, it), h->t(nstp, it), h->t(indx, it), dtau, cf_stp, cf_bak, it);
-    else PLANE((k_pre_t_horiz<false, KB_T, false>), p.iend, p.jstr, p.jend, (p.N + KB_T - 1) / KB_T, p, h->t(nrhs, it), h->t(nnew, it), h->t(nstp, it), h->t(indx, it), dtau, cf_stp, cf_bak, it);
-  }
+  const std::vector<TPlan> plan = plan_batches(h);
+  for (const TPlan& pl : plan) { int rc = tracer_pre_horiz(h, pl, nrhs, nnew, nstp, indx, dtau, cf_stp, cf_bak); if (rc) return rc; }
   if (wl) PLANE_JB((k_rhs_uv_horiz<false, true, 4>), 4, p.iend, p.jstr, p.jend, p.N, p, h->u(nrhs), h->v(nrhs));
   else PLANE_JB((k_rhs_uv_horiz<false, false, 4>), 4, p.iend, p.jstr, p.jend, p.N, p, h->u(nrhs), h->v(nrhs));
   PLANE(k_rd_bott_drag, p.iend, p.jstrV - 1, p.jend, 1, p, h->u(nstp), h->v(nstp));
-  for (int it = 1; it <= h->c.NT; ++it)
-    COLUMN(k_t_vert<0>, 2, p.iend, p.jstr, p.jend, p, h->t(nrhs, it), h->t(nnew, it), p.Akt[it >= 2 ? 1 : 0], (const double*)nullptr, dtau, 0, it);
+  for (const TPlan& pl : plan) { int rc = tracer_vert<0>(h, pl, nrhs, nnew, dtau); if (rc) return rc; }
   COLUMN((k_uv_vert<0, 0>), 2, p.iend, p.jstr, p.jend, p, h->u(nrhs), h->u(nnew), h->u(nstp), h->u(indx), dtau, cf_stp, cf_bak);
   COLUMN((k_uv_vert<0, 1>), 2, p.iend, p.jstrV, p.jend, p, h->v(nrhs), h->v(nnew), h->v(nstp), h->v(indx), dtau, cf_stp, cf_bak);
   if (p.rivers) PLANE(k_river_uv, p.iend, p.jstr, p.jend, 1, p, h->u(nnew), h->v(nnew), p.istrU, p.jstrV);   // pre_step3d4S.F:493-522
@@ -766,12 +826,10 @@ int roms_step3d_t(roms_ctx* h, int tile) {
   CK(cudaSetDevice(h->device));
   const KP& p = h->kp;
   const int nrhs = h->nrhs, nnew = h->nnew, NT = h->c.NT;
-  for (int it = 1; it <= NT; ++it) {
-    if (p.rivers) PLANE((k_t_horiz<true, KB_T, true>), p.iend, p.jstr, p.jend, (p.N + KB_T - 1) / KB_T, p, h->t(nrhs, it), h->t(nnew, it), it);
-    else if (WALLED(h)) PLANE((k_t_horiz<true, KB_T, false>), p.iend, p.jstr, p.jend, (p.N + KB_T - 1) / KB_T, p, h->t(nrhs, it), h->t(nnew, it), it);
-    else PLANE((k_t_horiz<false, KB_T, false>), p.iend, p.jstr, p.jend, (p.N + KB_T - 1) / KB_T, p, h->t(nrhs, it), h->t(nnew, it), it);
-    COLUMN(k_t_vert<1>, 2, p.iend, p.jstr, p.jend, p, h->t(nrhs, it), h->t(nnew, it), p.Akt[it >= 2 ? 1 : 0], h->f[ROMS_STFLX].ptr[it - 1], h->c.dt,
-           it == 1 ? 1 : 0, it);
+  for (const TPlan& pl : plan_batches(h)) {
+    int rc = tracer_cor_horiz(h, pl, nrhs, nnew);
+    if (!rc) rc = tracer_vert<1>(h, pl, nrhs, nnew, h->c.dt);
+    if (rc) return rc;
   }
   for (int it = 1; it <= NT; ++it) bc3d(h, h->t(nnew, it), p.N, BC_T);   // t3dbc_tile (step3d_t_ISO.F:1157-1159)
   for (int it = 1; it + 1 <= NT; it += 2) {
