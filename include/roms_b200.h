@@ -150,6 +150,17 @@ int  roms_grid_stats(roms_ctx* h, double out[9]); /* setup_grid2.F:64-100 start-
                                                   grdmax, Cg_min, Cg_max, Cu_Cor, area, volume                                */
 int  roms_diag(roms_ctx* h, double out[4]);   /* diag.F:50: KE, barotropic KE, max adv CFL, its vertical part */
 
+/* ---- allocation-free variant (NO counterpart in the reference) ----
+ * For callers that cannot call cudaMalloc (CUDA-graph capture, tight serving loops, harnesses that forbid it): the
+ * omega.F:17-164 column kernel of roms_omega without a context.  Its column scratch is a file-scope static device array
+ * of 4 Mi doubles (32 MiB, held by every GPU that loads the library until exit): 2*(N+1)*Lm*Mm must not exceed it, else
+ * the call returns -3 with a message.  Calls no cudaMalloc/cudaFree.  All pointers are DEVICE pointers in the reference's
+ * unpadded layout (-1:Lm+2,-1:Mm+2[,k]): FlxU,FlxV,Hz k=1:N; z_w,We,Wi k=0:N; pm,pn,swflx 2-D.  Writes We,Wi on the
+ * interior (1:Lm,1:Mm), k=0:N; no boundary copies, no halo exchange.  Stream-ordered on `stream` (a cudaStream_t; NULL =
+ * default stream).  All calls share the one scratch array: calls that overlap on the GPU race (serialise them on one stream). */
+int  roms_omega_noalloc(int Lm, int Mm, int N, double dtau, const double* FlxU, const double* FlxV, const double* z_w, const double* Hz,
+                        const double* pm, const double* pn, const double* swflx, double* We, double* Wi, void* stream);
+
 /* ---- the driver loop body, for hosts without a Fortran main (main.F:86-321, 333-520) ---- */
 int  roms_init_step0(roms_ctx* h);            /* set_depth, set_HUV, omega, rho_eos of roms_init */
 int  roms_step(roms_ctx* h);                  /* one baroclinic step: main.F:397-479            */

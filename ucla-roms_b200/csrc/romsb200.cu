@@ -1123,3 +1123,123 @@ int roms_run(roms_ctx* h, int nsteps) {
 }  // extern "C"
 
 #include "comm_impl.cuh"
+
+// ================================================================================================
+// roms_omega_noalloc -- an allocation-free variant of the omega kernel (omega.F:17-164 arithmetic of k_omega).
+// It has NO counterpart in the reference; it was added for callers that cannot
+// call cudaMalloc (code under CUDA-graph capture, tight serving loops, harnesses that forbid allocation).  The two
+// per-level column coefficients that k_omega keeps in the context's arena live here in ONE file-scope device array
+// of fixed size, held by every GPU that loads the library until the process exits:
+//     2 * (N+1) * Lm * Mm  <=  ROMS_NOALLOC_MAX_DOUBLES  (4 Mi doubles = 32 MiB)
+// The entry point calls no cudaMalloc/cudaFree and no allocating library routine.  Every call shares the array, which
+// keeps the previous call's contents: nothing in it has to start at zero (each column writes its levels 1..N in the
+// up-sweep before the down-sweep reads them), but two calls that overlap on the GPU (different streams, threads or
+// processes' contexts on one device do not share it; streams and threads of ONE process do) race on it.
+#define ROMS_NOALLOC_MAX_DOUBLES (4u << 20)
+static __device__ __align__(256) double g_noalloc_scratch[ROMS_NOALLOC_MAX_DOUBLES];
+
+struct OmegaNA {
+  int Lm, Mm, N, SXh;
+  long SXYh, ncell;
+  double dtau;
+  const double *FlxU, *FlxV, *z_w, *Hz, *pm, *pn, *swflx;
+  double *We, *Wi;
+  double* scr;
+};
+// one thread per (i,j) column of the interior; fields are DEVICE arrays in the reference's unpadded layout
+// (-1:Lm+2, -1:Mm+2 [, k]) -- what roms_pull returns, uploaded as is
+__global__ void __launch_bounds__(64) k_omega_noalloc(const __grid_constant__ OmegaNA a) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x + 1, j = blockIdx.y * blockDim.y + threadIdx.y + 1;
+  if (i > a.Lm || j > a.Mm) return;
+  const int N = a.N;
+  const long SX = a.SXh, SXY = a.SXYh;
+  const long c = (i + 1) + (long)(j + 1) * SX;
+  double* __restrict__ s0 = a.scr + ((long)(j - 1) * a.Lm + (i - 1));
+  double* __restrict__ s1 = s0 + (long)(N + 1) * a.ncell;
+#define NA3(f, x, k) (f)[(x) + (long)((k)-1) * SXY]
+#define NAW(f, x, k) (f)[(x) + (long)(k)*SXY]
+  const double cu_min = 0.6, cu_max = 1.0, cmnx_ratio = cu_min / cu_max, cutoff = 2.0 - cmnx_ratio, r4cmx = 0.25 / (1.0 - cmnx_ratio);
+  double W = 0.0;
+  NAW(a.Wi, c, 0) = 0.0;
+  for (int k = 1; k <= N; ++k) {
+    const double fu1 = NA3(a.FlxU, c + 1, k), fu0 = NA3(a.FlxU, c, k), fv1 = NA3(a.FlxV, c + SX, k), fv0 = NA3(a.FlxV, c, k);
+    W = W - fu1 + fu0 - fv1 + fv0;
+    s0[(long)k * a.ncell] = DMAX(fu1, 0.0) - DMIN(fu0, 0.0) + DMAX(fv1, 0.0) - DMIN(fv0, 0.0);
+    s1[(long)k * a.ncell] = W;
+  }
+  const double dm_r = 1.0 / a.pm[c], dn_r = 1.0 / a.pn[c];      // setup_grid1.F: dm_r = 1/pm, dn_r = 1/pn
+  W = W + a.swflx[c] * dm_r * dn_r;
+  const double zw0 = NAW(a.z_w, c, 0);
+  const double wrk = W / (NAW(a.z_w, c, N) - zw0);
+  NAW(a.Wi, c, N) = 0.0;
+  NAW(a.We, c, N) = 0.0;
+  NAW(a.We, c, 0) = 0.0;
+  const double CX0 = a.dtau * a.pm[c] * a.pn[c];
+  double CXkp = s0[(long)N * a.ncell], Hzkp = NA3(a.Hz, c, N);
+  for (int k = N - 1; k >= 1; --k) {
+    double Wik = s1[(long)k * a.ncell] - wrk * (NAW(a.z_w, c, k) - zw0);
+    const double CXk = s0[(long)k * a.ncell], Hzk = NA3(a.Hz, c, k);
+    const double c2d = DMAX(CXk, CXkp);
+    const double dh = DMIN(Hzk, Hzkp);
+    const double cw_max = cu_max * dh - c2d * CX0;
+    double Wek;
+    if (cw_max > 0.0) {
+      const double cw_max2 = cw_max * cw_max;
+      const double cw_min = cw_max * cmnx_ratio;
+      const double cw = fabs(Wik) * CX0;
+      double cff;
+      if (cw < cw_min) cff = cw_max2;
+      else if (cw < cutoff * cw_max) cff = cw_max2 + r4cmx * ((cw - cw_min) * (cw - cw_min));
+      else cff = cw_max * cw;
+      Wek = cw_max2 * Wik / cff;
+      Wik = Wik - Wek;
+    } else Wek = 0.0;
+    NAW(a.We, c, k) = Wek;
+    NAW(a.Wi, c, k) = Wik;
+    CXkp = CXk; Hzkp = Hzk;
+  }
+#undef NA3
+#undef NAW
+}
+
+#include <mutex>
+static std::mutex g_noalloc_mu;
+static double* g_noalloc_ptr[64] = {nullptr};     // device address of g_noalloc_scratch, per device ordinal
+
+extern "C" int roms_omega_noalloc(int Lm, int Mm, int N, double dtau, const double* FlxU, const double* FlxV, const double* z_w, const double* Hz,
+                                  const double* pm, const double* pn, const double* swflx, double* We, double* Wi, void* stream) {
+  if (Lm < 1 || Mm < 1 || N < 2 || !FlxU || !FlxV || !z_w || !Hz || !pm || !pn || !swflx || !We || !Wi) { g_err = "roms_omega_noalloc: bad argument"; return -1; }
+  const unsigned long long need = 2ull * (unsigned long long)(N + 1) * (unsigned long long)Lm * (unsigned long long)Mm;
+  if (need > ROMS_NOALLOC_MAX_DOUBLES) {
+    char msg[256];
+    snprintf(msg, sizeof msg, "roms_omega_noalloc: 2*(N+1)*Lm*Mm = %llu doubles exceeds the static scratch of %u doubles (32 MiB); use roms_omega on a context",
+             need, (unsigned)ROMS_NOALLOC_MAX_DOUBLES);
+    g_err = msg;
+    return -3;
+  }
+  int dev = -1;
+  CK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= 64) { g_err = "roms_omega_noalloc: device ordinal out of range"; return -1; }
+  double* scr;
+  {
+    // once per device, with that device current: in host code the array's NAME is only a host-side stand-in for the symbol,
+    // not a device address -- the address the kernel needs comes from cudaGetSymbolAddress
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (!g_noalloc_ptr[dev]) {
+      void* ptr = nullptr;
+      CK(cudaGetSymbolAddress(&ptr, g_noalloc_scratch));
+      g_noalloc_ptr[dev] = (double*)ptr;
+    }
+    scr = g_noalloc_ptr[dev];
+  }
+  OmegaNA a;
+  a.Lm = Lm; a.Mm = Mm; a.N = N; a.SXh = Lm + 4;
+  a.SXYh = (long)(Lm + 4) * (Mm + 4); a.ncell = (long)Lm * Mm;
+  a.dtau = dtau;
+  a.FlxU = FlxU; a.FlxV = FlxV; a.z_w = z_w; a.Hz = Hz; a.pm = pm; a.pn = pn; a.swflx = swflx; a.We = We; a.Wi = Wi;
+  a.scr = scr;
+  dim3 b(32, 2, 1), g((Lm + 31) / 32, (Mm + 1) / 2, 1);
+  k_omega_noalloc<<<g, b, 0, (cudaStream_t)stream>>>(a);
+  CK(cudaGetLastError());
+  return 0;
+}
