@@ -33,10 +33,16 @@ KERNEL_WORDS = {
     "k_prsgrd_vert": lambda t: (5 if t[0] == "true" else 3, 3),
     "k_rho_prs_vert": lambda t: (8 if t[0] == "true" else 6, 3),   # rho_eos fused with the vertical part of prsgrd: T,S,Hz,z_r read; rho1,qp1,P,rho written
     "k_prsgrd_horiz": lambda t: (8 if t[0] == "true" else 6, 3),
-    "k_pre_flxdiv": (5, 3), "k_pre_t_horiz": (8, 3), "k_rhs_uv_horiz": (9, 3),
-    "k_t_vert": lambda t: (8 if t[0] == "0" else 7, 3), "k_uv_vert": lambda t: (10 if t[0] == "0" else 9, 3),
-    "k_set_huv1": (4, 3), "k_uv2_pass0": (3, 3), "k_uv2_pass1": (6, 3),
-    "k_t_horiz": (5, 3), "k_set_depth": (3, 3), "k_step2d_zeta": (24, 2), "k_step2d_uv": (23, 2), "k_rd_bott_drag": (3, 2),
+    "k_pre_flxdiv": (5, 3), "k_rhs_uv_horiz": (9, 3),
+    # tracer kernels, TB tracers per launch: operands shared by the batch count once
+    "k_pre_t_horiz": lambda t: (3 + 5 * int(t[3]), 3),    # FlxU,FlxV,FlxDiv + per tracer t(nrhs),t(nstp),t(indx) R, t(nnew),t(indx) W
+    "k_t_horiz": lambda t: (2 + 3 * int(t[3]), 3),        # FlxU,FlxV + per tracer t(nrhs) R, t(nnew) RW
+    "k_t_vert": lambda t: ((4 if t[0] == "0" else 3) + (1 if t[2] == "true" else int(t[1])) + 3 * int(t[1]), 3),   # Hz,We,Wi[,FlxDiv] + Akt slots + per tracer t(nrhs) R, t(nnew) RW
+    "k_uv_vert": lambda t: (10 if t[0] == "0" else 9, 3),
+    "k_set_huv1": (4, 3), "k_uv2_pass0": (3, 3), "k_uv2_pass1": (6, 3), "k_uv2_pass1_sm": (6, 3),
+    # KPP closure (row f2): 3-D operands read once, results written once
+    "k_lmd_rig": (5, 3), "k_lmd_smooth": (2, 3), "k_lmd_vmix_col": (5, 3), "k_lmd_kpp1": (8, 3), "k_lmd_kpp2": (9, 3),
+    "k_set_depth": (3, 3), "k_step2d_zeta": (24, 2), "k_step2d_uv": (23, 2), "k_rd_bott_drag": (3, 2),
     "k_visc3d": (7, 3),      # row f1: u,v(nstp),Hz read; u,v(3-nstp) read+written
     "k_t3dmix": (4, 3),      # row f1: t(nrhs),Hz read; t(nnew) read+written
     "k_step2d": (34, 2),     # 9 state R + 3 W + 12 static R + 10 averages RW per 2-D point and substep
@@ -115,6 +121,81 @@ class ClockSampler:
                 "reasons": sorted(reasons), "samples": len(sm)}
 
 
+# Workloads = BASELINE.json configs[1..4] as per-GPU blocks (weak scaling: the block is fixed, the domain grows with the rank grid
+# 1x1, 2x1, 2x2, 4x2).  `total_at` = the rank count at which the assembled domain is the configuration BASELINE.json names.
+WORKLOADS = {
+    "channel": dict(size=(1024, 1024, 64), nt=2, kw=dict(ns_walls=True), cpu_sample=(256, 256, 64), total_at=1,
+                    what="analytic baroclinic channel, T+S, nonlinear split EOS, E-W periodic, closed free-slip N/S walls"),
+    "seamount": dict(size=(1024, 2048, 100), nt=2, kw=dict(ns_walls=True, ew_walls=True, seamount=True), cpu_sample=(128, 256, 100), total_at=8,
+                     what="analytic seamount h=4500(1-0.5exp(-r^2/(L/5)^2)) in a closed basin, T+S, nonlinear split EOS (4096x4096x100 on 8 GPUs)"),
+    "tracers": dict(size=(1024, 2048, 64), nt=32, kw=dict(ns_walls=True, ew_walls=True, river=True, dt=60.0), cpu_sample=(96, 128, 64), total_at=2,
+                    what="Rivers_ana geometry (land strip, river channel and river source) in a closed basin, T+S+30 passive tracers (2048x2048x64 on 2 GPUs)"),
+    "weak": dict(size=(2304, 2304, 100), nt=2, kw=dict(ns_walls=True, ew_walls=True, seamount=True), cpu_sample=(128, 256, 100), total_at=8,
+                 what="largest block that fits 180 GB: analytic seamount in a closed basin, T+S (9216x4608x100 on 8 GPUs; 8192x8192x100 needs 1.8 TB)"),
+}
+
+
+def rel_l2(a, b):
+    import numpy as np
+    n = float(np.linalg.norm(b.ravel()))
+    d = float(np.linalg.norm((a - b).ravel()))
+    return d / n if n > 0 else d
+
+
+def parity_check(case_kw, NT, N, rank, world, local, dist):
+    """Run before the timed region, so that every bench line carries its own parity evidence:
+    (a) rank 0: two baroclinic steps of a 96x64xN block of THIS workload's physics (same N, same NT up to 8) through the CUDA
+        library against the CPU oracle, worst relative L2 over zeta, ubar, vbar, u, v, every tracer and rho;
+    (b) N > 1 ranks: a small domain cut into the rank grid, stepped with the halo swaps, against the single-domain oracle."""
+    import numpy as np
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from orclib import Oracle
+    from romsb200 import Roms, cases
+    os.environ["OMP_NUM_THREADS"] = str(os.cpu_count() or 1)
+    out = {"tolerance": "relative L2 <= 1e-12 after one step (north_star)"}
+    nt = min(NT, 8)
+    kw = dict(case_kw, NT=nt)
+
+    def fields(m):
+        idx = m.get_idx()
+        nnew, knew = idx[4], idx[6]
+        return [("zeta", m.pull("ZETA", knew)), ("ubar", m.pull("UBAR", knew)), ("vbar", m.pull("VBAR", knew)), ("u", m.pull("U", nnew)),
+                ("v", m.pull("V", nnew)), ("rho", m.pull("RHO1"))] + [(f"t{it}", m.pull("T", nnew, it)) for it in range(1, nt + 1)]
+
+    def trim(a, cfg, r=None):
+        ns = slice(1 if (not cfg.ns_periodic and cfg.jnode == 0) else 0, -1 if (not cfg.ns_periodic and cfg.jnode == cfg.np_eta - 1) else None)
+        ew = slice(1 if (not cfg.ew_periodic and cfg.inode == 0) else 0, -1 if (not cfg.ew_periodic and cfg.inode == cfg.np_xi - 1) else None)
+        return a[..., ns, ew]
+    if rank == 0:
+        cfg, st = cases.channel(96, 64, N, **kw)
+        g, o = Roms(cfg, local), Oracle(cfg)
+        cases.initialize(g, st); cases.initialize(o, st)
+        g.call("run", 2); o.call("run", 2)
+        out["single_domain"] = {"sample": f"96x64x{N}, {nt} tracers, 2 steps", "worst_rel_l2": max(rel_l2(trim(a, cfg), trim(b, cfg)) for (_, a), (_, b) in zip(fields(g), fields(o)))}
+        g.close(); o.close()
+    if world > 1:
+        npx, npe = cases.rank_grid(world)
+        LG, MG, Ns = 32 * npx, 28 * npe, min(N, 16)
+        sub = (rank % npx, rank // npx, npx, npe)
+        cfg, st = cases.channel(LG, MG, Ns, sub=sub, **kw)
+        g = Roms(cfg, local)
+        g.attach_torch_comm(dist)
+        cases.initialize(g, st)
+        g.call("run", 2)
+        cfgG, stG = cases.channel(LG, MG, Ns, **kw)
+        o = Oracle(cfgG)
+        cases.initialize(o, stG)
+        o.call("run", 2)
+        i0, j0 = cases.block_extent(LG, npx, sub[0])[1], cases.block_extent(MG, npe, sub[1])[1]
+        w = max(rel_l2(trim(a, cfg), trim(b[..., j0:j0 + cfg.Mm + 4, i0:i0 + cfg.Lm + 4], cfg)) for (_, a), (_, b) in zip(fields(g), fields(o)))
+        g.close(); o.close()
+        import torch
+        t = torch.tensor([w], device="cuda", dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        out["decomposed_vs_single_domain"] = {"sample": f"{LG}x{MG}x{Ns} over {npx}x{npe} ranks, 2 steps", "worst_rel_l2": float(t.item())}
+    return out
+
+
 def cpu_oracle_rate(cfg_kw, steps, warmup, sample):
     """Times the CPU restatement of the path (oracle/, OpenMP over the reference's independent j/k loops)
     on all host cores for a bounded sample of the workload; returns (updates/s, cores, seconds, sample str)."""
@@ -134,7 +215,7 @@ def cpu_oracle_rate(cfg_kw, steps, warmup, sample):
         o.call("step")
     dt = time.perf_counter() - t0
     o.close()
-    return Lm * Mm * N * steps / dt, cores, dt, f"{Lm}x{Mm}x{N} block of the same analytic channel, {steps} baroclinic steps after {warmup} warm-up"
+    return Lm * Mm * N * steps / dt, cores, dt, f"{Lm}x{Mm}x{N} block of the same workload ({cfg.NT} tracers), {steps} baroclinic steps after {warmup} warm-up, {cores} OpenMP threads"
 
 
 _STDOUT_FD = None
@@ -163,10 +244,12 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--size", type=int, nargs=3, default=[1024, 1024, 64], metavar=("Lm", "Mm", "N"))
-    ap.add_argument("--nt", type=int, default=2)
-    ap.add_argument("--cpu-sample", type=int, nargs=3, default=[256, 256, 64])
+    ap.add_argument("--workload", default="channel", choices=sorted(WORKLOADS), help="BASELINE.json configs[1..4] as per-GPU blocks; the default is the configuration the metric is quoted on")
+    ap.add_argument("--size", type=int, nargs=3, default=None, metavar=("Lm", "Mm", "N"), help="per-GPU block (default: the workload's)")
+    ap.add_argument("--nt", type=int, default=None)
+    ap.add_argument("--cpu-sample", type=int, nargs=3, default=None)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-parity", action="store_true", help="skip the GPU-vs-oracle check that precedes the timed region")
     ap.add_argument("--periodic", action="store_true", help="doubly periodic variant instead of the closed N/S walls of BASELINE configs[1]")
     ap.add_argument("--mixing", action="store_true", help="also run visc3d / t3dmix (UV_VIS2, TS_DIF2; SURVEY.md 8(f) row f1) inside every step")
     ap.add_argument("--kpp", action="store_true", help="also run the LMD/KPP vertical mixing closure (lmd_vmix twice per step; SURVEY.md 8(f) row f2)")
@@ -175,15 +258,20 @@ def main():
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
-    Lm, Mm, N = a.size
-    NT = a.nt
-    case_kw = dict(NT=NT, ns_walls=not a.periodic, nonlin_eos=True)
+    wl = WORKLOADS[a.workload]
+    Lm, Mm, N = a.size or wl["size"]
+    NT = a.nt or wl["nt"]
+    cpu_sample = tuple(a.cpu_sample or wl["cpu_sample"])
+    case_kw = dict(wl["kw"], NT=NT, nonlin_eos=True)
+    if a.periodic:
+        case_kw.update(ns_walls=False, ew_walls=False)
     if a.mixing:
         case_kw.update(visc2=100.0, tnu2=50.0)
-    workload = f"analytic baroclinic channel {Lm}x{Mm}x{N} per GPU, T+S" + (f"+{NT - 2} passive" if NT > 2 else "") + \
-               ", nonlinear split EOS, " + ("doubly periodic" if a.periodic else "E-W periodic, closed free-slip N/S walls") + ", ndtfast=60 (82 executed barotropic substeps per step)" + \
+    workload = f"{wl['what']}; {Lm}x{Mm}x{N} per GPU, {NT} tracers" + (", doubly periodic variant" if a.periodic else "") + \
+               ", ndtfast=60 (82 executed barotropic substeps per step)" + \
                (", + harmonic lateral viscosity/diffusion (visc3d, t3dmix)" if a.mixing else "") + (", + KPP vertical mixing (lmd_vmix x2 per step)" if a.kpp else "")
-    config = {"workload": workload, "grid_per_gpu": [Lm, Mm, N], "tracers": NT, "l2_policy": "inputs (15 GB of resident state per GPU) larger than L2; no flush",
+    config = {"workload": workload, "name": a.workload, "grid_per_gpu": [Lm, Mm, N], "tracers": NT,
+              "l2_policy": "inputs (the resident state, see resident_gb_per_gpu) far larger than the 126 MB L2; no flush",
               "timing": "CUDA events on the library stream, barrier+sync both sides, max over ranks"}
 
     if a.impl == "reference":
@@ -192,7 +280,8 @@ def main():
         if rank != 0:
             return 0
         steps = max(1, min(a.steps, 3))
-        rate, cores, secs, sample = cpu_oracle_rate(case_kw, steps, min(a.warmup, 1), tuple(a.cpu_sample))
+        rate, cores, secs, sample = cpu_oracle_rate(case_kw, steps, min(a.warmup, 1), cpu_sample)
+        config["cpu_sample"] = sample
         line = {"impl": "reference", "metric": METRIC, "value": rate, "unit": UNIT, "n_gpus": a.gpus, "steps": steps, "warmup": min(a.warmup, 1),
                 "ms_per_step": 1e3 * secs / steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
                 "data": "synthetic", "config": config,
@@ -214,8 +303,11 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
+    parity = None if a.no_parity else parity_check(case_kw, NT, N, rank, world, local, dist)
     np_xi, np_eta = cases.rank_grid(world)
-    cfg, st = cases.channel(Lm * np_xi, Mm * np_eta, N, sub=(rank % np_xi, rank // np_xi, np_xi, np_eta), **case_kw)
+    cfg, st = cases.channel_strips(Lm * np_xi, Mm * np_eta, N, strips=(8 if Lm * Mm * N > (1 << 26) else 1), sub=(rank % np_xi, rank // np_xi, np_xi, np_eta), **case_kw)
+    config["domain"] = [Lm * np_xi, Mm * np_eta, N]
+    config["rank_grid"] = [np_xi, np_eta]
     if a.kpp:
         cfg.Zob = 1.0e-2          # the bottom boundary layer of the closure needs a roughness length (log-layer drag then, too)
     g = Roms(cfg, local)
@@ -226,6 +318,7 @@ def main():
     cases.initialize(g, st)
     del st
     lib = g.lib
+    config["resident_gb_per_gpu"] = round(g.resident_bytes() / 1e9, 2)
     nfast = g.nfast()
 
     def timed_steps(k):
@@ -330,13 +423,13 @@ def main():
 
     cpu = None
     if rank == 0 and world == 1 and not a.no_cpu_baseline:
-        rate, cores, secs, sample = cpu_oracle_rate(case_kw, 2, 1, tuple(a.cpu_sample))
+        rate, cores, secs, sample = cpu_oracle_rate(case_kw, 2, 1, cpu_sample)
         cpu = {"value": rate, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}
     g.close()
     if rank == 0:
         line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": a.warmup, "ms_per_step": ms / a.steps,
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": config,
-                "roofline": roof, "step_roofline": step_roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
+                "roofline": roof, "step_roofline": step_roof, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks, "parity": parity,
                 "diag": {"KE": d[0], "BAROTR_KE": d[1], "MAX_ADV_CFL": d[2], "MAX_VERT_CFL": d[3]}}
         _emit(line)
     if world > 1:

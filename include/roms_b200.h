@@ -166,6 +166,7 @@ int  roms_init_step0(roms_ctx* h);            /* set_depth, set_HUV, omega, rho_
 int  roms_step(roms_ctx* h);                  /* one baroclinic step: main.F:397-479            */
 int  roms_run(roms_ctx* h, int nsteps);       /* nsteps x roms_step                             */
 int  roms_kernel_launches(roms_ctx* h, long* n); /* kernels launched so far by this context    */
+int  roms_resident_bytes(roms_ctx* h, long long* n); /* HBM bytes this context keeps resident */
 
 /* ---- multi-GPU: 2-D subdomain split, one process per GPU (replaces mpi_setup.F / mpi_exchanges.F) ---- */
 int  roms_comm_unique_id(char* out, int len);  /* rank 0: NCCL unique id (>=128 bytes) to broadcast   */

@@ -382,6 +382,12 @@ int roms_sync(roms_ctx* h) {
   return comm_check_failed(&h->comm);
 }
 int roms_kernel_launches(roms_ctx* h, long* n) { *n = h->launches; return 0; }
+// bytes of HBM this context keeps resident (state arena + KPP arrays; halo buffers are not counted)
+int roms_resident_bytes(roms_ctx* h, long long* n) {
+  const size_t kpp = h->kpp_buf ? ((size_t)6 * h->kp.SXY * (h->kp.N + 1) + (size_t)13 * h->kp.SXY) * sizeof(double) : 0;
+  *n = (long long)(h->arena_doubles * sizeof(double) + kpp);
+  return 0;
+}
 // device-side timing on the library's own stream (bench.py): events bracket whatever is enqueued between
 int roms_timer_start(roms_ctx* h) {
   FLUSH_RHO(h);
@@ -669,18 +675,26 @@ static int tracer_cor_horiz(roms_ctx* h, const TPlan& pl, int nrhs, int nnew) {
   else T_HORIZ_LAUNCH(k_t_horiz, 1, make_batch<1>(h, pl, nrhs, nnew, nrhs, nnew));
   return 0;
 }
-template <int MODE>
-static int tracer_vert(roms_ctx* h, const TPlan& pl, int nrhs, int nnew, double dtau) {
+#define T_VERT_LAUNCH(MODEn)                                                                                                                            \
+  do {                                                                                                                                                  \
+    if (pl.n == 4) COLUMN((k_t_vert<MODEn, 4, true>), 5, p.iend, p.jstr, p.jend, p, make_batch<4>(h, pl, nrhs, nnew, nrhs, nnew), dtau);                 \
+    else if (pl.n == 2 && pl.share) COLUMN((k_t_vert<MODEn, 2, true>), 3, p.iend, p.jstr, p.jend, p, make_batch<2>(h, pl, nrhs, nnew, nrhs, nnew), dtau); \
+    else if (pl.n == 2) COLUMN((k_t_vert<MODEn, 2, false>), 3, p.iend, p.jstr, p.jend, p, make_batch<2>(h, pl, nrhs, nnew, nrhs, nnew), dtau);            \
+    else COLUMN((k_t_vert<MODEn, 1, true>), 2, p.iend, p.jstr, p.jend, p, make_batch<1>(h, pl, nrhs, nnew, nrhs, nnew), dtau);                           \
+  } while (0)
+static int tracer_vert(roms_ctx* h, int mode, const TPlan& pl, int nrhs, int nnew, double dtau) {
   const KP& p = h->kp;
-  if (pl.n == 4) COLUMN((k_t_vert<MODE, 4, true>), 5, p.iend, p.jstr, p.jend, p, make_batch<4>(h, pl, nrhs, nnew, nrhs, nnew), dtau);
-  else if (pl.n == 2 && pl.share) COLUMN((k_t_vert<MODE, 2, true>), 3, p.iend, p.jstr, p.jend, p, make_batch<2>(h, pl, nrhs, nnew, nrhs, nnew), dtau);
-  else if (pl.n == 2) COLUMN((k_t_vert<MODE, 2, false>), 3, p.iend, p.jstr, p.jend, p, make_batch<2>(h, pl, nrhs, nnew, nrhs, nnew), dtau);
-  else COLUMN((k_t_vert<MODE, 1, true>), 2, p.iend, p.jstr, p.jend, p, make_batch<1>(h, pl, nrhs, nnew, nrhs, nnew), dtau);
+  if (mode == 0) T_VERT_LAUNCH(0);
+  else T_VERT_LAUNCH(1);
   return 0;
 }
 extern "C" {
 int roms_rho_eos(roms_ctx* h, int tidx) {
   CK(cudaSetDevice(h->device));
+  // A deferred call for the SAME time level is still pending and nothing has touched the state since (every other export
+  // flushes first): this call would recompute bit-identical values from identical inputs -- rho_eos(nnew) at the end of a
+  // step (main.F:477) followed by rho_eos(nrhs) at the start of the next (main.F:397, nrhs = the previous nnew).  Keep one.
+  if (h->fuse_rho && h->rho_pending == tidx) return 0;
   FLUSH_RHO(h);
   if (h->fuse_rho) { h->rho_pending = tidx; return 0; }
   return rho_eos_launch(h, tidx, false);
@@ -724,7 +738,7 @@ int roms_pre_step3d(roms_ctx* h, int tile) {
   if (wl) PLANE_JB((k_rhs_uv_horiz<false, true, 4>), 4, p.iend, p.jstr, p.jend, p.N, p, h->u(nrhs), h->v(nrhs));
   else PLANE_JB((k_rhs_uv_horiz<false, false, 4>), 4, p.iend, p.jstr, p.jend, p.N, p, h->u(nrhs), h->v(nrhs));
   PLANE(k_rd_bott_drag, p.iend, p.jstrV - 1, p.jend, 1, p, h->u(nstp), h->v(nstp));
-  for (const TPlan& pl : plan) { int rc = tracer_vert<0>(h, pl, nrhs, nnew, dtau); if (rc) return rc; }
+  for (const TPlan& pl : plan) { int rc = tracer_vert(h, 0, pl, nrhs, nnew, dtau); if (rc) return rc; }
   COLUMN((k_uv_vert<0, 0>), 2, p.iend, p.jstr, p.jend, p, h->u(nrhs), h->u(nnew), h->u(nstp), h->u(indx), dtau, cf_stp, cf_bak);
   COLUMN((k_uv_vert<0, 1>), 2, p.iend, p.jstrV, p.jend, p, h->v(nrhs), h->v(nnew), h->v(nstp), h->v(indx), dtau, cf_stp, cf_bak);
   if (p.rivers) PLANE(k_river_uv, p.iend, p.jstr, p.jend, 1, p, h->u(nnew), h->v(nnew), p.istrU, p.jstrV);   // pre_step3d4S.F:493-522
@@ -828,7 +842,7 @@ int roms_step3d_t(roms_ctx* h, int tile) {
   const int nrhs = h->nrhs, nnew = h->nnew, NT = h->c.NT;
   for (const TPlan& pl : plan_batches(h)) {
     int rc = tracer_cor_horiz(h, pl, nrhs, nnew);
-    if (!rc) rc = tracer_vert<1>(h, pl, nrhs, nnew, h->c.dt);
+    if (!rc) rc = tracer_vert(h, 1, pl, nrhs, nnew, h->c.dt);
     if (rc) return rc;
   }
   for (int it = 1; it <= NT; ++it) bc3d(h, h->t(nnew, it), p.N, BC_T);   // t3dbc_tile (step3d_t_ISO.F:1157-1159)

@@ -172,6 +172,11 @@ class Roms(CApi):
         self.lib.roms_kernel_launches(self.h, C.byref(n))
         return n.value
 
+    def resident_bytes(self):
+        n = C.c_longlong()
+        self.lib.roms_resident_bytes(self.h, C.byref(n))
+        return n.value
+
     def exchange(self, field, lvl=1, itrc=1):
         f = (C.c_int * 1)(FID[field]); l = (C.c_int * 1)(lvl); t = (C.c_int * 1)(itrc)
         self._check(self.lib.roms_exchange(self.h, 1, f, l, t), "exchange")

@@ -225,6 +225,49 @@ def channel(Lm=64, Mm=64, N=16, NT=2, ns_walls=False, nonlin_eos=True, dt=120.0,
     return cfg, st
 
 
+def channel_strips(Lm, Mm, N, strips=8, sub=(0, 0, 1, 1), **kw):
+    """`channel(...)` for a large block without its dozen full-size temporaries: the rank's block is assembled from `strips`
+    horizontal strips, each produced by `channel` itself as the block of a finer process grid (every formula is a function of the
+    GLOBAL indices, so the values are those of the direct call, bit for bit).  Needs Mm divisible by np_eta*strips."""
+    inode, jnode, np_xi, np_eta = sub
+    if strips <= 1 or Mm % (np_eta * strips) != 0 or (Mm // (np_eta * strips)) < 4:
+        return channel(Lm, Mm, N, sub=sub, **kw)
+    cfg = st = None
+    rows = Mm // (np_eta * strips)
+    for s_ in range(strips):
+        c, part = channel(Lm, Mm, N, sub=(inode, jnode * strips + s_, np_xi, np_eta * strips), **kw)
+        if st is None:
+            cfg = c
+            cfg.Mm, cfg.np_eta, cfg.jnode = rows * strips, np_eta, jnode
+            st = {}
+        # rows of this strip that land in the assembled block: its interior, plus the 2 halo rows at the block's own ends
+        lo = 0 if s_ == 0 else 2
+        hi = rows + 4 if s_ == strips - 1 else rows + 2
+        dst = slice(s_ * rows + lo, s_ * rows + hi)
+
+        def put(key, sel, a):
+            tgt = st.setdefault(key, {}) if sel is not None else st
+            k = sel if sel is not None else key
+            if k not in tgt:
+                tgt[k] = np.empty(a.shape[:-2] + (rows * strips + 4, a.shape[-1]), dtype=a.dtype)
+            tgt[k][..., dst, :] = a[..., lo:hi, :]
+        for key, v in part.items():
+            if isinstance(v, dict):
+                seen = {}
+                for sel, a in v.items():
+                    if id(a) in seen:                      # (1,it) and (2,it) share one array in `channel`: keep them shared
+                        st[key][sel] = st[key][seen[id(a)]]
+                        continue
+                    seen[id(a)] = sel
+                    put(key, sel, a)
+            elif isinstance(v, np.ndarray):
+                put(key, None, v)
+            else:
+                st[key] = v
+        del part
+    return cfg, st
+
+
 def filament(Lm=64, Mm=64, N=32):
     """tests/Filament analytical case (ana_grid.h, ana_init.h) evaluated with numpy."""
     cfg = RomsCfg(Lm=Lm, Mm=Mm, N=N, NT=1, ew_periodic=1, ns_periodic=1, nonlin_eos=0, salinity=0, ndtfast=60,
