@@ -62,6 +62,12 @@ struct roms_ctx {
   int fuse_rho = 1;       // a rho_eos call is deferred; if prsgrd follows (main.F:397-413, 430-445) both run as one fused column kernel
   int rho_pending = 0;    // time index of the deferred rho_eos (0: none)
   int uv2_sm = 1;     // k_uv2_pass1 with the column parked in shared memory (1.0 -> 0.78 ms on B200); off when the column is too tall
+  int s2d_hw = 0;     // k_step2d with two dedicated halo warps per block
+  int huv1_sm = 0;
+  int uv2_fused = 1;  // step3d_uv2 passes 0 and 1 in one shared-memory column kernel (k_uv2_sm)
+  int omega2 = 0;     // scratch-free two-pass omega kernel (k_omega2); 0: the slab version k_omega
+  int flxdiv_valid = 0;     // k_omega2 has already produced FlxDiv of the interior columns with the factor flxdiv_cff
+  double flxdiv_cff = 0.0;
   int tb_max = 4;     // most tracers per launch of the tracer kernels (ROMS_TB = 1, 2 or 4)
   int use_smem = 0;   // measured on B200 (profiles/r1_scratch_policy.txt): occupancy beats shared-memory scratch
   Comm comm;
@@ -261,6 +267,10 @@ int roms_create(const roms_cfg* cfg, int device, roms_ctx** out) {
   if (const char* e = getenv("ROMS_COL_SMEM")) h->use_smem = atoi(e);
   if (const char* e = getenv("ROMS_UV2_SM")) h->uv2_sm = atoi(e);
   if (const char* e = getenv("ROMS_TB")) h->tb_max = atoi(e);
+  if (const char* e = getenv("ROMS_OMEGA2")) h->omega2 = atoi(e);
+  if (const char* e = getenv("ROMS_UV2_FUSED")) h->uv2_fused = atoi(e);
+  if (const char* e = getenv("ROMS_S2D_HW")) h->s2d_hw = atoi(e);
+  if (const char* e = getenv("ROMS_HUV1_SM")) h->huv1_sm = atoi(e);
   if (const char* e = getenv("ROMS_FUSE_RHO")) h->fuse_rho = atoi(e);
   if ((size_t)2 * (N + 1) * 32 * sizeof(double) > 64 * 1024) h->uv2_sm = 0;   // fewer than 3 warps per SM would fit: global re-read version
   if ((size_t)2 * (N + 1) * h->col_bx * h->col_by * sizeof(double) > 200 * 1024) { h->col_by = 1; }
@@ -356,6 +366,7 @@ long roms_field_count(roms_ctx* h, int field) {
 }
 int roms_push(roms_ctx* h, int field, int lvl, int itrc, const double* host) {
   FLUSH_RHO(h);
+  h->flxdiv_valid = 0;
   double* d; int nk;
   if (find_slot(h, field, lvl, itrc, &d, &nk)) return -1;
   CK(cudaSetDevice(h->device));
@@ -577,6 +588,7 @@ int roms_set_depth(roms_ctx* h, int tile) {
 }
 int roms_set_huv(roms_ctx* h) {
   CK(cudaSetDevice(h->device));
+  h->flxdiv_valid = 0;
   const KP& p = h->kp;
   PLANE(k_set_huv, p.iendR, p.jstrR, p.jendR, p.N, p, h->u(h->nrhs), h->v(h->nrhs));
   return exchange(h, {{p.FlxU, p.N}, {p.FlxV, p.N}});
@@ -587,8 +599,14 @@ int roms_set_huv1(roms_ctx* h, int tile) {
   CK(cudaSetDevice(h->device));
   const KP& p = h->kp;
   const int first = (h->iic == h->forw_start);
-  COLUMN(k_set_huv1<0>, 0, p.iendR, p.jstrR, p.jendR, p, h->u(h->nnew), first);
-  COLUMN(k_set_huv1<1>, 0, p.iendR, p.jstr, p.jendR, p, h->v(h->nnew), first);
+  h->flxdiv_valid = 0;
+  if (h->uv2_sm && h->huv1_sm) {
+    COLUMN_SM(k_set_huv1_sm<0>, p.iendR, p.jstrR, p.jendR, p, h->u(h->nnew), first);
+    COLUMN_SM(k_set_huv1_sm<1>, p.iendR, p.jstr, p.jendR, p, h->v(h->nnew), first);
+  } else {
+    COLUMN(k_set_huv1<0>, 0, p.iendR, p.jstrR, p.jendR, p, h->u(h->nnew), first);
+    COLUMN(k_set_huv1<1>, 0, p.iendR, p.jstr, p.jendR, p, h->v(h->nnew), first);
+  }
   return exchange(h, {{p.FlxU, p.N}, {p.FlxV, p.N}, {h->u(h->nnew), p.N}, {h->v(h->nnew), p.N}});
 }
 int roms_omega(roms_ctx* h) {
@@ -598,7 +616,17 @@ int roms_omega(roms_ctx* h) {
   if (h->nrhs == 3) dtau = h->c.dt;
   else if (h->iic == h->forw_start) dtau = 0.5 * h->c.dt;
   else dtau = 0.6 * h->c.dt;
-  COLUMN(k_omega, 2, p.iend, p.jstr, p.jend, p, dtau);
+  h->flxdiv_valid = 0;
+  if (h->omega2) {
+    // the predictor-stage call (main.F:402) is followed by pre_step3d, whose first act is FlxDiv = 0.5*dtau_pre*pm*pn*div(Flx,W)
+    // (pre_step3d4S.F:138-147): the kernel has every operand of it in registers and stores it for its own columns
+    double fd_cff = 0.0;
+    if (h->nrhs != 3) fd_cff = 0.5 * ((h->iic == h->forw_start) ? 0.5 * h->c.dt : h->c.dt * (1.0 - 1.0 / 6.0));
+    COLUMN(k_omega2, 0, p.iend, p.jstr, p.jend, p, dtau, fd_cff);
+    if (fd_cff != 0.0) { h->flxdiv_valid = 1; h->flxdiv_cff = fd_cff; }
+  } else {
+    COLUMN(k_omega, 2, p.iend, p.jstr, p.jend, p, dtau);
+  }
   bc3d(h, p.We, p.N + 1, BC_W);      // omega.F:171-231 edge copies
   bc3d(h, p.Wi, p.N + 1, BC_W);
   return exchange(h, {{p.We, p.N + 1}, {p.Wi, p.N + 1}});
@@ -722,6 +750,8 @@ int roms_prsgrd(roms_ctx* h) {
   return 0;
 }
 int roms_pre_step3d(roms_ctx* h, int tile) {
+  const int flxdiv_done = h->flxdiv_valid;
+  h->flxdiv_valid = 0;
   FLUSH_RHO(h);
   (void)tile;
   CK(cudaSetDevice(h->device));
@@ -732,7 +762,13 @@ int roms_pre_step3d(roms_ctx* h, int tile) {
   if (h->iic == h->forw_start) { dtau = 0.5 * dt; cf_stp = 1.0; cf_bak = 0.0; }
   else { dtau = dt * (1.0 - AM3_crv); cf_stp = 0.5 + AM3_crv; cf_bak = 0.5 - AM3_crv; }
   const bool wl = WALLED(h);
-  PLANE(k_pre_flxdiv, p.iend, p.jstrV - 1, p.jend, p.N, p, dtau);
+  if (flxdiv_done && h->flxdiv_cff == 0.5 * dtau) {
+    // interior columns came out of k_omega2; what is left is the halo ring on periodic / inter-subdomain sides (needs the exchanged We, Wi)
+    if (!p.wwall) PLANE(k_pre_flxdiv, 0, p.jstrV - 1, p.jend, p.N, p, dtau, 0, 0, p.jstrV - 1, p.jend);
+    if (!p.swall) PLANE(k_pre_flxdiv, p.iend, 0, 0, p.N, p, dtau, p.istrU - 1, p.iend, 0, 0);
+  } else {
+    PLANE(k_pre_flxdiv, p.iend, p.jstrV - 1, p.jend, p.N, p, dtau, p.istrU - 1, p.iend, p.jstrV - 1, p.jend);
+  }
   const std::vector<TPlan> plan = plan_batches(h);
   for (const TPlan& pl : plan) { int rc = tracer_pre_horiz(h, pl, nrhs, nnew, nstp, indx, dtau, cf_stp, cf_bak); if (rc) return rc; }
   if (wl) PLANE_JB((k_rhs_uv_horiz<false, true, 4>), 4, p.iend, p.jstr, p.jend, p.N, p, h->u(nrhs), h->v(nrhs));
@@ -792,9 +828,10 @@ int roms_step2d(roms_ctx* h) {
   s.w1 = h->w1[iif]; s.w2 = h->w2[iif];
   s.iif = iif; s.nfast = h->nfast;
   {
-    dim3 b_(S2_TX, S2_TY, 1), g_((p.iend + IOFF + 1 + S2_TX - 1) / S2_TX, (p.jend - p.jstr + 1 + S2_TY - 1) / S2_TY, 1);
+    dim3 b_(S2_TX, S2_TY + (h->s2d_hw ? 2 : 0), 1), g_((p.iend + IOFF + 1 + S2_TX - 1) / S2_TX, (p.jend - p.jstr + 1 + S2_TY - 1) / S2_TY, 1);
     if (h->ktiming) kt_begin(h, "k_step2d");
-    k_step2d<<<g_, b_, 0, h->st>>>(p, s);
+    if (h->s2d_hw) k_step2d<1><<<g_, b_, 0, h->st>>>(p, s);
+    else k_step2d<0><<<g_, b_, 0, h->st>>>(p, s);
     if (h->ktiming) kt_end(h);
     h->launches++;
   }
@@ -814,10 +851,31 @@ int roms_step2d(roms_ctx* h) {
 }
 int roms_step3d_uv2(roms_ctx* h, int tile) {
   FLUSH_RHO(h);
+  h->flxdiv_valid = 0;
   (void)tile;
   CK(cudaSetDevice(h->device));
   const KP& p = h->kp;
   const int nnew = h->nnew, nstp = h->nstp, knew = h->knew;
+  if (h->uv2_sm && h->uv2_fused) {
+    // both passes in one kernel per direction; the wall rows / columns (u3dbc, v3dbc between the passes) first, from the original u(nnew)
+    const double g2 = h->c.gamma2;
+#define UV2_EDGE(DIRn, arr, sarr, barr, a0, a1, b0, b1) COLUMN_SM((k_uv2_sm<DIRn, true>), a1, b0, b1, p, arr, sarr, barr, g2, a0, a1, b0, b1)
+    if (p.swall) UV2_EDGE(0, h->u(nnew), h->u(nstp), h->ubar(knew), p.istr, p.iendR, p.jstr - 1, p.jstr - 1);
+    if (p.nwall) UV2_EDGE(0, h->u(nnew), h->u(nstp), h->ubar(knew), p.istr, p.iendR, p.jend + 1, p.jend + 1);
+    if (p.wwall) UV2_EDGE(0, h->u(nnew), h->u(nstp), h->ubar(knew), p.istr, p.istr, p.jstr, p.jend);
+    if (p.ewall) UV2_EDGE(0, h->u(nnew), h->u(nstp), h->ubar(knew), p.iend + 1, p.iend + 1, p.jstr, p.jend);
+    if (p.wwall) UV2_EDGE(1, h->v(nnew), h->v(nstp), h->vbar(knew), p.istr - 1, p.istr - 1, p.jstr, p.jendR);
+    if (p.ewall) UV2_EDGE(1, h->v(nnew), h->v(nstp), h->vbar(knew), p.iend + 1, p.iend + 1, p.jstr, p.jendR);
+    if (p.swall) UV2_EDGE(1, h->v(nnew), h->v(nstp), h->vbar(knew), p.istr, p.iend, p.jstr, p.jstr);
+    if (p.nwall) UV2_EDGE(1, h->v(nnew), h->v(nstp), h->vbar(knew), p.istr, p.iend, p.jend + 1, p.jend + 1);
+#undef UV2_EDGE
+    COLUMN_SM((k_uv2_sm<0, false>), p.iend, p.jstr, p.jend, p, h->u(nnew), h->u(nstp), h->ubar(knew), g2, p.istrU, p.iend, p.jstr, p.jend);
+    COLUMN_SM((k_uv2_sm<1, false>), p.iend, p.jstrV, p.jend, p, h->v(nnew), h->v(nstp), h->vbar(knew), g2, p.istr, p.iend, p.jstrV, p.jend);
+    if (p.rivers) PLANE(k_river_uv, p.iend, p.jstr, p.jend, 1, p, h->u(nnew), h->v(nnew), p.istr, p.jstr);   // step3d_uv2.F:689-717
+    int rc = exchange(h, {{p.FlxU, p.N}, {h->u(nnew), p.N}, {h->ubar(knew), 1}});
+    if (rc) return rc;
+    return exchange(h, {{p.FlxV, p.N}, {h->v(nnew), p.N}, {h->vbar(knew), 1}});
+  }
   COLUMN(k_uv2_pass0<0>, 0, p.iend, p.jstr, p.jend, p, h->u(nnew));
   COLUMN(k_uv2_pass0<1>, 0, p.iend, p.jstrV, p.jend, p, h->v(nnew));
   bc3d(h, h->u(nnew), p.N, BC_U);     // u3dbc_tile / v3dbc_tile (step3d_uv2.F:471-472)
