@@ -47,6 +47,7 @@ KERNEL_WORDS = {
     "k_set_depth": (3, 3), "k_step2d_zeta": (24, 2), "k_step2d_uv": (23, 2), "k_rd_bott_drag": (3, 2),
     "k_visc3d": (7, 3),      # row f1: u,v(nstp),Hz read; u,v(3-nstp) read+written
     "k_t3dmix": (4, 3),      # row f1: t(nrhs),Hz read; t(nnew) read+written
+    "k_step2d_tma": (34, 2), "k_step2d_march": (34, 2),
     "k_step2d": (34, 2),     # 9 state R + 3 W + 12 static R + 10 averages RW per 2-D point and substep
 }
 

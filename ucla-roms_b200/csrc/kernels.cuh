@@ -1706,6 +1706,9 @@ __global__ void __launch_bounds__(S2_TX * (S2_TY + 2 * HW), (HW ? 3 : LB_S2D)) k
     }
   }
 }
+#include "step2d_tma.cuh"
+#include "step2d_march.cuh"
+
 // zeta_new at any point of the rho-range incl. wall rows, wall columns and basin corners (zetabc.F:39-81)
 __device__ __forceinline__ double s2d_zn_full(const KP& p, const S2D& s, int i, int j) {
   const int ii = (p.wwall && i < p.istr) ? p.istr : ((p.ewall && i > p.iend) ? p.iend : i);

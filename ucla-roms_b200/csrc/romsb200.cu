@@ -62,6 +62,8 @@ struct roms_ctx {
   int fuse_rho = 1;       // a rho_eos call is deferred; if prsgrd follows (main.F:397-413, 430-445) both run as one fused column kernel
   int rho_pending = 0;    // time index of the deferred rho_eos (0: none)
   int uv2_sm = 1;     // k_uv2_pass1 with the column parked in shared memory (1.0 -> 0.78 ms on B200); off when the column is too tall
+  int s2d_tma = 1;    // barotropic substep as the TMA-fed marching kernel k_step2d_tma; 0: the tile kernel k_step2d
+  int s2d_rows = 16;  // rows per block of the marching kernels (measured best on B200: profiles/r2_step2d_variants.txt)
   int s2d_hw = 0;     // k_step2d with two dedicated halo warps per block
   int huv1_sm = 0;
   int uv2_fused = 1;  // step3d_uv2 passes 0 and 1 in one shared-memory column kernel (k_uv2_sm)
@@ -270,6 +272,8 @@ int roms_create(const roms_cfg* cfg, int device, roms_ctx** out) {
   if (const char* e = getenv("ROMS_OMEGA2")) h->omega2 = atoi(e);
   if (const char* e = getenv("ROMS_UV2_FUSED")) h->uv2_fused = atoi(e);
   if (const char* e = getenv("ROMS_S2D_HW")) h->s2d_hw = atoi(e);
+  if (const char* e = getenv("ROMS_S2D_TMA")) h->s2d_tma = atoi(e);
+  if (const char* e = getenv("ROMS_S2D_ROWS")) h->s2d_rows = atoi(e) > 0 ? atoi(e) : 32;
   if (const char* e = getenv("ROMS_HUV1_SM")) h->huv1_sm = atoi(e);
   if (const char* e = getenv("ROMS_FUSE_RHO")) h->fuse_rho = atoi(e);
   if ((size_t)2 * (N + 1) * 32 * sizeof(double) > 64 * 1024) h->uv2_sm = 0;   // fewer than 3 warps per SM would fit: global re-read version
@@ -827,7 +831,52 @@ int roms_step2d(roms_ctx* h) {
   s.zn = h->zeta(knew); s.un = h->ubar(knew); s.vn = h->vbar(knew);
   s.w1 = h->w1[iif]; s.w2 = h->w2[iif];
   s.iif = iif; s.nfast = h->nfast;
-  {
+  if (h->s2d_tma >= 6) {
+    // register-marching kernel (step2d_march.cuh): strips of TX-1 columns x s2d_rows rows per block
+    const int rows = h->s2d_rows;
+#define S2R_LAUNCH(TXn, MB)                                                                                                   \
+  do {                                                                                                                      \
+    dim3 b_(TXn, 1, 1), g_((p.iend - p.istr + 1 + TXn - 2) / (TXn - 1), (p.jend - p.jstr + 1 + rows - 1) / rows, 1);         \
+    if (h->ktiming) kt_begin(h, "k_step2d_march");                                                                          \
+    k_step2d_march<TXn, MB><<<g_, b_, 0, h->st>>>(p, s, rows);                                                                \
+    if (h->ktiming) kt_end(h);                                                                                              \
+    h->launches++;                                                                                                          \
+  } while (0)
+    if (h->s2d_tma == 7) S2R_LAUNCH(128, 1);
+    else if (h->s2d_tma == 8) S2R_LAUNCH(32, 1);
+    else if (h->s2d_tma == 9) S2R_LAUNCH(64, 8);
+    else if (h->s2d_tma == 10) S2R_LAUNCH(128, 4);
+    else if (h->s2d_tma == 11) S2R_LAUNCH(64, 6);
+    else S2R_LAUNCH(64, 1);
+#undef S2R_LAUNCH
+  } else if (h->s2d_tma) {
+    // TMA-fed marching kernel (step2d_tma.cuh): strips of S2M_TX-1 columns x s2d_rows rows per block
+    S2Planes ap;
+    ap.a[A_H] = p.h; ap.a[A_ZS] = s.zs; ap.a[A_ZB] = s.zb; ap.a[A_ZO] = s.zo; ap.a[A_VS] = s.vs; ap.a[A_VB] = s.vb; ap.a[A_VO] = s.vo; ap.a[A_DMV] = p.dm_v;
+    ap.a[A_US] = s.us; ap.a[A_UB] = s.ub; ap.a[A_UO] = s.uo; ap.a[A_DNU] = p.dn_u; ap.a[A_PM] = p.pm; ap.a[A_PN] = p.pn; ap.a[A_RM] = p.rmask;
+    ap.a[A_SWF] = p.swflx; ap.a[A_RHOA] = p.rhoA; ap.a[A_RHOS] = p.rhoS; ap.a[A_UM] = p.umask; ap.a[A_VM] = p.vmask; ap.a[A_RUF] = p.rufrc;
+    ap.a[A_RVF] = p.rvfrc; ap.a[A_ZT] = p.Zt_avg1; ap.a[A_DU1] = p.DU_avg1; ap.a[A_DV1] = p.DV_avg1; ap.a[A_DU2] = p.DU_avg2; ap.a[A_DV2] = p.DV_avg2;
+    const int rows = h->s2d_rows;
+#define S2M_LAUNCH(TXn, Sn)                                                                                                                        \
+  do {                                                                                                                                             \
+    const size_t sm_ = ((size_t)Sn * S2M_NA * (TXn + 4) + 2 * TXn) * sizeof(double) + Sn * sizeof(unsigned long long);                              \
+    static bool attr_ = false;                                                                                                                     \
+    if (!attr_) { CK(cudaFuncSetAttribute((k_step2d_tma<TXn, Sn>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_)); attr_ = true; }        \
+    dim3 b_(TXn + 32, 1, 1), g_((p.iend - p.istr + 1 + TXn - 2) / (TXn - 1), (p.jend - p.jstr + 1 + rows - 1) / rows, 1);                           \
+    if (h->ktiming) kt_begin(h, "k_step2d_tma");                                                                                                   \
+    k_step2d_tma<TXn, Sn><<<g_, b_, sm_, h->st>>>(p, s, ap, rows);                                                                                 \
+    if (h->ktiming) kt_end(h);                                                                                                                     \
+    h->launches++;                                                                                                                                 \
+  } while (0)
+    switch (h->s2d_tma) {
+      case 2: S2M_LAUNCH(128, 3); break;
+      case 3: S2M_LAUNCH(128, 4); break;
+      case 4: S2M_LAUNCH(256, 3); break;
+      case 5: S2M_LAUNCH(64, 6); break;
+      default: S2M_LAUNCH(64, 4); break;
+    }
+#undef S2M_LAUNCH
+  } else {
     dim3 b_(S2_TX, S2_TY + (h->s2d_hw ? 2 : 0), 1), g_((p.iend + IOFF + 1 + S2_TX - 1) / S2_TX, (p.jend - p.jstr + 1 + S2_TY - 1) / S2_TY, 1);
     if (h->ktiming) kt_begin(h, "k_step2d");
     if (h->s2d_hw) k_step2d<1><<<g_, b_, 0, h->st>>>(p, s);
