@@ -2404,8 +2404,7 @@ __global__ void k_diag_bar(const __grid_constant__ KP p, const double* __restric
   ub[c] = (a + (R3(p.Hz, c, 1) + R3(p.Hz, c - 1, 1)) * R3(u, c, 1)) / (RW(p.z_w, c, N) + RW(p.z_w, c - 1, N) - RW(p.z_w, c, 0) - RW(p.z_w, c - 1, 0));
   vb[c] = (b + (R3(p.Hz, c, 1) + R3(p.Hz, c - SX, 1)) * R3(v, c, 1)) / (RW(p.z_w, c, N) + RW(p.z_w, c - SX, N) - RW(p.z_w, c, 0) - RW(p.z_w, c - SX, 0));
 }
-// one thread per column writes its 5 values; the (deterministic) reduction is done on the host side
-// of the C ABI over the pulled planes -- diag runs every ninfo steps, outside the timed hot path.
+// one thread per column writes its 5 values; k_diag_rows / k_diag_final reduce them on the device in a fixed order
 __global__ void k_diag_col(const __grid_constant__ KP p, const double* __restrict__ u, const double* __restrict__ v, const double* __restrict__ ub,
                            const double* __restrict__ vb, double* __restrict__ o_ke, double* __restrict__ o_ke2b, double* __restrict__ o_vol,
                            double* __restrict__ o_cx, double* __restrict__ o_cw) {
@@ -2430,6 +2429,46 @@ __global__ void k_diag_col(const __grid_constant__ KP p, const double* __restric
   o_ke2b[c] = dA * ke2b;
   o_cx[c] = cxm;
   o_cw[c] = cwm;
+}
+
+// diag.F:256-325: the global sums, on the device.  The summation tree is fixed -- halving down to runs of at most 8 terms, the
+// same tree whatever the launch geometry -- so the diagnostics do not depend on the number of threads: one thread per row j
+// sums its row of the three per-column planes with that tree, accumulates the row's area and volume left to right and finds the
+// row's first maximum of the advective Courant number; k_diag_final then combines the rows with the same tree.  Only the 7
+// results (56 bytes) travel to the host.
+__device__ double d_pairsum(const double* __restrict__ a, int n) {
+  if (n <= 8) { double s = 0; for (int i = 0; i < n; ++i) s += a[i]; return s; }
+  return d_pairsum(a, n / 2) + d_pairsum(a + n / 2, n - n / 2);
+}
+// rows: [7][Mm] = ke, ke2b, vol(zeta part), area, volume(h part), max cx, its cw
+__global__ void k_diag_rows(const __grid_constant__ KP p, const double* __restrict__ o_ke, const double* __restrict__ o_ke2b, const double* __restrict__ o_vol,
+                            const double* __restrict__ o_cx, const double* __restrict__ o_cw, double* __restrict__ rows) {
+  const int j = p.jstr + blockIdx.x * blockDim.x + threadIdx.x;
+  if (j > p.jend) return;
+  const int Lm = p.Lm, Mm = p.Mm;
+  const ix_t c0 = CIDX(1, j);
+  rows[0 * Mm + j - 1] = d_pairsum(o_ke + c0, Lm);
+  rows[1 * Mm + j - 1] = d_pairsum(o_ke2b + c0, Lm);
+  rows[2 * Mm + j - 1] = d_pairsum(o_vol + c0, Lm);
+  double ar = 0, vr = 0, cx = 0.0, cw = 0.0;
+  for (int i = 0; i < Lm; ++i) {
+    const ix_t c = c0 + i;
+    const double dA = p.rmask[c] / (p.pm[c] * p.pn[c]);
+    ar += dA; vr += dA * p.h[c];
+    if (o_cx[c] > cx) { cx = o_cx[c]; cw = o_cw[c]; }
+  }
+  rows[3 * Mm + j - 1] = ar; rows[4 * Mm + j - 1] = vr;
+  rows[5 * Mm + j - 1] = cx; rows[6 * Mm + j - 1] = cw;
+}
+__global__ void k_diag_final(const double* __restrict__ rows, int Mm, double* __restrict__ red) {
+  const int q = threadIdx.x;
+  if (q < 5) red[q] = d_pairsum(rows + q * Mm, Mm);
+  if (q == 5) {
+    double cx = 0.0, cw = 0.0;
+    for (int j = 0; j < Mm; ++j)
+      if (rows[5 * Mm + j] > cx) { cx = rows[5 * Mm + j]; cw = rows[6 * Mm + j]; }
+    red[5] = cx; red[6] = cw;
+  }
 }
 
 // alfabeta.F:4-79

@@ -45,6 +45,7 @@ struct roms_ctx {
   size_t arena_doubles = 0;
   // scratch planes for diag
   double *d_ub, *d_vb, *d_o[5];
+  double* d_rows = nullptr;   // [7][Mm] row partials of diag + 8 results
   // scalars.F
   int iic = 0, iif = 1, nstp = 1, nrhs = 1, nnew = 1, kstp = 1, knew = 1, ntstart = 1, forw_start = 1;
   int nfast = 0;
@@ -300,7 +301,7 @@ int roms_create(const roms_cfg* cfg, int device, roms_ctx** out) {
   const size_t scratch_planes = (size_t)3 * N            /* FlxDiv, P, rho */
                                 + (h->use_smem ? 0 : (size_t)scr_arrays * (N + 1)) /* column scratch slab */
                                 + 1 /* zeta_new */ + 2 /* ub, vb */ + 5 /* diag planes */;
-  const size_t small = 2 * (size_t)(N + 1) + 64 + (size_t)MAXRIV * RIVROW + (size_t)MAXPIP * PIPROW(N);
+  const size_t small = 2 * (size_t)(N + 1) + 64 + 7 * (size_t)cfg->Mm + 8 + (size_t)MAXRIV * RIVROW + (size_t)MAXPIP * PIPROW(N);
   h->arena_doubles = (planes + scratch_planes) * (size_t)p.SXY + small;
   CK(cudaMalloc(&h->arena, h->arena_doubles * sizeof(double)));
   CK(cudaMemset(h->arena, 0, h->arena_doubles * sizeof(double)));   // init=0 (init_scalars.F:31)
@@ -318,6 +319,7 @@ int roms_create(const roms_cfg* cfg, int device, roms_ctx** out) {
   p.riv_tab = cur; cur += (size_t)MAXRIV * RIVROW;
   p.rivers = 0;
   p.pipe_tab = cur; cur += (size_t)MAXPIP * PIPROW(N);
+  h->d_rows = cur; cur += 7 * (size_t)cfg->Mm + 8;
   p.pipes = 0;
   p.pot_tides = 0;
   p.lmd_kpp = 0;
@@ -1135,39 +1137,20 @@ int roms_diag(roms_ctx* h, double out[4]) {
   FLUSH_RHO(h);
   CK(cudaSetDevice(h->device));
   const KP& p = h->kp;
-  const int Lm = h->c.Lm, Mm = h->c.Mm, SXh = Lm + 4;
+  const int Mm = h->c.Mm;
   COLUMN(k_diag_bar, 0, p.iend + 1, p.jstr, p.jend + 1, p, h->u(h->nstp), h->v(h->nstp), h->d_ub, h->d_vb);
   COLUMN(k_diag_col, 0, p.iend, p.jstr, p.jend, p, h->u(h->nstp), h->v(h->nstp), h->d_ub, h->d_vb, h->d_o[0], h->d_o[1], h->d_o[2], h->d_o[3], h->d_o[4]);
-  const size_t n2 = (size_t)SXh * (Mm + 4), w = (size_t)SXh * sizeof(double);
-  std::vector<double> pl[5];
-  std::vector<double> pmv(n2), pnv(n2), hv(n2), rmv(n2);
-  for (int q = 0; q < 5; ++q) {
-    pl[q].resize(n2);
-    CK(cudaMemcpy2DAsync(pl[q].data(), w, h->d_o[q] + (IOFF - 1), (size_t)p.SX * sizeof(double), w, Mm + 4, cudaMemcpyDeviceToHost, h->st));
+  {
+    dim3 b_(128, 1, 1), g_((Mm + 127) / 128, 1, 1);
+    if (h->ktiming) kt_begin(h, "k_diag_rows");
+    k_diag_rows<<<g_, b_, 0, h->st>>>(p, h->d_o[0], h->d_o[1], h->d_o[2], h->d_o[3], h->d_o[4], h->d_rows);
+    if (h->ktiming) kt_end(h);
+    k_diag_final<<<1, 32, 0, h->st>>>(h->d_rows, Mm, h->d_rows + (size_t)7 * Mm);
+    h->launches += 2;
   }
-  if (roms_pull(h, ROMS_PM, 1, 1, pmv.data()) || roms_pull(h, ROMS_PN, 1, 1, pnv.data()) || roms_pull(h, ROMS_H, 1, 1, hv.data()) ||
-      roms_pull(h, ROMS_RMASK, 1, 1, rmv.data()))
-    return -1;
+  double red[7];
+  CK(cudaMemcpyAsync(red, h->d_rows + (size_t)7 * Mm, 7 * sizeof(double), cudaMemcpyDeviceToHost, h->st));
   CK(cudaStreamSynchronize(h->st));
-  std::vector<double> rows[5];
-  for (int q = 0; q < 5; ++q) rows[q].resize(Mm);
-  double cx = 0.0, cw = 0.0;
-  for (int j = 1; j <= Mm; ++j) {
-    const size_t o = (size_t)(j + 1) * SXh + 2;
-    rows[0][j - 1] = pairsum(&pl[0][o], Lm);
-    rows[1][j - 1] = pairsum(&pl[1][o], Lm);
-    rows[2][j - 1] = pairsum(&pl[2][o], Lm);
-    double ar = 0, vr = 0;
-    for (int i = 0; i < Lm; ++i) {
-      const double dA = rmv[o + i] / (pmv[o + i] * pnv[o + i]);
-      ar += dA; vr += dA * hv[o + i];
-      if (pl[3][o + i] > cx) { cx = pl[3][o + i]; cw = pl[4][o + i]; }
-    }
-    rows[3][j - 1] = ar; rows[4][j - 1] = vr;
-  }
-  double sums[5];
-  for (int q = 0; q < 5; ++q) sums[q] = pairsum(rows[q].data(), Mm);
-  double red[7] = {sums[0], sums[1], sums[2], sums[3], sums[4], cx, cw};
   int rc = comm_diag_reduce(&h->comm, red);
   if (rc) return rc;
   const double avke = red[0], avke2b = red[1], avzeta = red[2], volume = red[4];
