@@ -1502,7 +1502,10 @@ struct S2D {
   double *zn, *un, *vn;                                       // knew
   double fwd, fwd1, fwd2, bkw_new, bkw, bkw1, bkw2, w1, w2;
   int iif, nfast;
+  int region;     // 0: every interior point; 1: all but the ring of width 2 along the subdomain's edges; 2: that ring only (halo-swap overlap)
 };
+// the ring of width 2 whose results travel in the halo messages (and whose inputs come from them)
+__device__ __forceinline__ bool s2d_in_ring(const KP& p, int i, int j) { return i < p.istr + 2 || i > p.iend - 2 || j < p.jstr + 2 || j > p.jend - 2; }
 __device__ __forceinline__ double s2d_Drhs(const KP& p, const S2D& s, ix2_t c) { return p.h[c] + s.fwd * s.zs[c] + s.fwd1 * s.zb[c] + s.fwd2 * s.zo[c]; }
 __device__ __forceinline__ double s2d_DUon(const KP& p, const S2D& s, ix2_t c) {
   const double urhs = s.fwd * s.us[c] + s.fwd1 * s.ub[c] + s.fwd2 * s.uo[c];
@@ -1600,6 +1603,8 @@ __global__ void __launch_bounds__(S2_TX * (S2_TY + 2 * HW), (HW ? 3 : LB_S2D)) k
   const int i0 = blockIdx.x * S2_TX - IOFF, j0 = p.jstr + blockIdx.y * S2_TY;
   const int i = i0 + tx, j = j0 + ty;
   const ix2_t SX = p.SX;
+  // ring-only launch: tiles that hold no ring point leave at once
+  if (s.region == 2 && !(i0 <= p.istr + 1 || i0 + S2_TX - 1 >= p.iend - 1 || j0 <= p.jstr + 1 || j0 + S2_TY - 1 >= p.jend - 1)) return;
   // ---- phase 1: zeta_new (step2d_FB.F:151-216) on the tile, the row below it and the column to its left
   if ((HW == 0 || ty < S2_TY) && i >= p.istrU - 1 && i <= p.iend && j <= p.jend) zt[ty + 1][tx + 1] = s2d_zeta_new(p, s, CIDX(i, j));
   if (HW == 0 || ty >= S2_TY) {
@@ -1615,6 +1620,7 @@ __global__ void __launch_bounds__(S2_TX * (S2_TY + 2 * HW), (HW ? 3 : LB_S2D)) k
   __syncthreads();
   if (HW && ty >= S2_TY) return;
   if (i < p.istr || i > p.iend || j > p.jend) return;
+  if (s.region && (s2d_in_ring(p, i, j) != (s.region == 2))) return;
   // ---- phase 2: own point
   const ix2_t c = CIDX(i, j);
   const double zn = zt[ty + 1][tx + 1], znw = zt[ty + 1][tx], zns = zt[ty][tx + 1];

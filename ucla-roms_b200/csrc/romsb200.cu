@@ -40,6 +40,9 @@ struct roms_ctx {
   int device;
   KP kp;
   cudaStream_t st;
+  cudaStream_t st2 = nullptr;                      // high-priority stream of the ring kernels and halo swaps of the barotropic loop
+  cudaEvent_t ev_int[2] = {nullptr, nullptr}, ev_edge[2] = {nullptr, nullptr}, ev_join = nullptr;
+  int overlap = 1;    // multi-rank: barotropic halo swaps overlapped with the interior launch of the next substep (ROMS_OVERLAP=0: serial)
   FieldSlot f[ROMS_NFIELDS];
   double* arena = nullptr;
   size_t arena_doubles = 0;
@@ -87,8 +90,8 @@ struct roms_ctx {
 static dim3 grid_plane(const roms_ctx* h, int i1, int j0, int j1, int nk, dim3 b) {
   return dim3((i1 + IOFF + 1 + b.x - 1) / b.x, (j1 - j0 + 1 + b.y - 1) / b.y, nk);
 }
-static void kt_begin(roms_ctx* h, const char* name);
-static void kt_end(roms_ctx* h);
+static void kt_begin(roms_ctx* h, const char* name, cudaStream_t st = nullptr);
+static void kt_end(roms_ctx* h, cudaStream_t st = nullptr);
 static int flush_rho(roms_ctx* h);
 #define FLUSH_RHO(h) do { int rc_ = flush_rho(h); if (rc_) return rc_; } while (0)
 // plane kernel whose threads each compute JB consecutive rows
@@ -135,15 +138,15 @@ static size_t col_smem(const roms_ctx* h, int narr) {
     h->launches++;                                                                            \
   } while (0)
 
-static void kt_begin(roms_ctx* h, const char* name) {
+static void kt_begin(roms_ctx* h, const char* name, cudaStream_t st) {
   KTimer t;
   t.name = name;
   cudaEventCreate(&t.a);
   cudaEventCreate(&t.b);
-  cudaEventRecord(t.a, h->st);
+  cudaEventRecord(t.a, st ? st : h->st);
   h->ktimers.push_back(t);
 }
-static void kt_end(roms_ctx* h) { cudaEventRecord(h->ktimers.back().b, h->st); }
+static void kt_end(roms_ctx* h, cudaStream_t st) { cudaEventRecord(h->ktimers.back().b, st ? st : h->st); }
 
 // ------------------------------------------------------------------------------------------------
 // set_scoord.F:4-66 and set_weights.F:7-246, evaluated on the host in the reference's operation order
@@ -238,6 +241,13 @@ int roms_create(const roms_cfg* cfg, int device, roms_ctx** out) {
   h->c = *cfg;
   h->device = device;
   CK(cudaStreamCreateWithFlags(&h->st, cudaStreamNonBlocking));
+  {
+    int lo = 0, hi = 0;
+    CK(cudaDeviceGetStreamPriorityRange(&lo, &hi));
+    CK(cudaStreamCreateWithPriority(&h->st2, cudaStreamNonBlocking, hi));
+    for (int q = 0; q < 2; ++q) { CK(cudaEventCreateWithFlags(&h->ev_int[q], cudaEventDisableTiming)); CK(cudaEventCreateWithFlags(&h->ev_edge[q], cudaEventDisableTiming)); }
+    CK(cudaEventCreateWithFlags(&h->ev_join, cudaEventDisableTiming));
+  }
   const int N = cfg->N, NT = cfg->NT;
   KP& p = h->kp;
   memset(&p, 0, sizeof(p));
@@ -273,6 +283,7 @@ int roms_create(const roms_cfg* cfg, int device, roms_ctx** out) {
   if (const char* e = getenv("ROMS_OMEGA2")) h->omega2 = atoi(e);
   if (const char* e = getenv("ROMS_UV2_FUSED")) h->uv2_fused = atoi(e);
   if (const char* e = getenv("ROMS_S2D_HW")) h->s2d_hw = atoi(e);
+  if (const char* e = getenv("ROMS_OVERLAP")) h->overlap = atoi(e);
   if (const char* e = getenv("ROMS_S2D_TMA")) h->s2d_tma = atoi(e);
   if (const char* e = getenv("ROMS_S2D_ROWS")) h->s2d_rows = atoi(e) > 0 ? atoi(e) : 32;
   if (const char* e = getenv("ROMS_HUV1_SM")) h->huv1_sm = atoi(e);
@@ -352,11 +363,21 @@ int roms_destroy(roms_ctx* h) {
   comm_destroy(&h->comm);
   cudaFree(h->arena);
   cudaFree(h->kpp_buf);
+  for (int q = 0; q < 2; ++q) { if (h->ev_int[q]) cudaEventDestroy(h->ev_int[q]); if (h->ev_edge[q]) cudaEventDestroy(h->ev_edge[q]); }
+  if (h->ev_join) cudaEventDestroy(h->ev_join);
+  if (h->st2) cudaStreamDestroy(h->st2);
   cudaStreamDestroy(h->st);
   delete h;
   return 0;
 }
 
+// work enqueued on the second stream (ring kernels and halo swaps of an unfinished barotropic loop) becomes visible to the main stream
+static int join_st2(roms_ctx* h) {
+  if (!h->st2) return 0;
+  CK(cudaEventRecord(h->ev_join, h->st2));
+  CK(cudaStreamWaitEvent(h->st, h->ev_join, 0));
+  return 0;
+}
 static int find_slot(roms_ctx* h, int field, int lvl, int itrc, double** ptr, int* nk) {
   if (field < 0 || field >= ROMS_NFIELDS) { g_err = "bad field id"; return -1; }
   FieldSlot& s = h->f[field];
@@ -372,6 +393,7 @@ long roms_field_count(roms_ctx* h, int field) {
 }
 int roms_push(roms_ctx* h, int field, int lvl, int itrc, const double* host) {
   FLUSH_RHO(h);
+  if (join_st2(h)) return -1;
   h->flxdiv_valid = 0;
   double* d; int nk;
   if (find_slot(h, field, lvl, itrc, &d, &nk)) return -1;
@@ -383,6 +405,7 @@ int roms_push(roms_ctx* h, int field, int lvl, int itrc, const double* host) {
 }
 int roms_pull(roms_ctx* h, int field, int lvl, int itrc, double* host) {
   FLUSH_RHO(h);
+  if (join_st2(h)) return -1;
   double* d; int nk;
   if (find_slot(h, field, lvl, itrc, &d, &nk)) return -1;
   CK(cudaSetDevice(h->device));
@@ -394,6 +417,7 @@ int roms_pull(roms_ctx* h, int field, int lvl, int itrc, double* host) {
 int roms_sync(roms_ctx* h) {
   FLUSH_RHO(h);
   CK(cudaSetDevice(h->device));
+  if (join_st2(h)) return -1;
   CK(cudaStreamSynchronize(h->st));
   CK(cudaGetLastError());
   return comm_check_failed(&h->comm);
@@ -416,6 +440,7 @@ int roms_timer_start(roms_ctx* h) {
 }
 int roms_timer_stop(roms_ctx* h, double* ms) {
   FLUSH_RHO(h);
+  if (join_st2(h)) return -1;
   CK(cudaEventRecord(h->ev1, h->st));
   CK(cudaEventSynchronize(h->ev1));
   float f = 0;
@@ -480,10 +505,10 @@ int roms_compute_tile_bounds(roms_ctx* h, int tile, int* istr, int* iend, int* j
 }
 
 // ---- exchange_xxx -------------------------------------------------------------------------------
-static int exchange(roms_ctx* h, std::initializer_list<XF> fl) {
-  if (h->ktiming) kt_begin(h, "exchange_xxx");
-  int rc = comm_exchange(&h->comm, h->kp, h->st, fl.begin(), (int)fl.size(), &h->launches);
-  if (h->ktiming) kt_end(h);
+static int exchange(roms_ctx* h, std::initializer_list<XF> fl, cudaStream_t st = nullptr) {
+  if (h->ktiming) kt_begin(h, "exchange_xxx", st);
+  int rc = comm_exchange(&h->comm, h->kp, st ? st : h->st, fl.begin(), (int)fl.size(), &h->launches);
+  if (h->ktiming) kt_end(h, st);
   return rc;
 }
 int roms_exchange(roms_ctx* h, int nfields, const int* fields, const int* lvls, const int* itrcs) {
@@ -704,8 +729,13 @@ static int tracer_pre_horiz(roms_ctx* h, const TPlan& pl, int nrhs, int nnew, in
 }
 static int tracer_cor_horiz(roms_ctx* h, const TPlan& pl, int nrhs, int nnew) {
   const KP& p = h->kp;
-  if (pl.n == 4) T_HORIZ_LAUNCH(k_t_horiz, 4, make_batch<4>(h, pl, nrhs, nnew, nrhs, nnew));
-  else if (pl.n == 2) T_HORIZ_LAUNCH(k_t_horiz, 2, make_batch<2>(h, pl, nrhs, nnew, nrhs, nnew));
+  if (pl.n == 4) {
+    // measured on B200 (profiles/r2_kernels_tracers_v0.txt): the UP3 corrector is faster per tracer in batches of 2 (1.87 vs 2.54 ms)
+    for (int half = 0; half < 2; ++half) {
+      TPlan q = {2, {pl.it[2 * half], pl.it[2 * half + 1], 0, 0}, pl.share};
+      T_HORIZ_LAUNCH(k_t_horiz, 2, make_batch<2>(h, q, nrhs, nnew, nrhs, nnew));
+    }
+  } else if (pl.n == 2) T_HORIZ_LAUNCH(k_t_horiz, 2, make_batch<2>(h, pl, nrhs, nnew, nrhs, nnew));
   else T_HORIZ_LAUNCH(k_t_horiz, 1, make_batch<1>(h, pl, nrhs, nnew, nrhs, nnew));
   return 0;
 }
@@ -806,6 +836,15 @@ int roms_step3d_uv1(roms_ctx* h, int tile) {
   COLUMN((k_uv_vert<1, 1>), 2, p.iend, p.jstrV, p.jend, p, h->v(nrhs), h->v(nnew), (const double*)nullptr, (double*)nullptr, h->c.dt, 0.0, 0.0);
   return 0;
 }
+}  // extern "C"
+// operand planes of the TMA marching kernel, in the order of step2d_tma.cuh
+static void s2d_planes(const KP& p, const S2D& s, S2Planes& ap) {
+  ap.a[A_H] = p.h; ap.a[A_ZS] = s.zs; ap.a[A_ZB] = s.zb; ap.a[A_ZO] = s.zo; ap.a[A_VS] = s.vs; ap.a[A_VB] = s.vb; ap.a[A_VO] = s.vo; ap.a[A_DMV] = p.dm_v;
+  ap.a[A_US] = s.us; ap.a[A_UB] = s.ub; ap.a[A_UO] = s.uo; ap.a[A_DNU] = p.dn_u; ap.a[A_PM] = p.pm; ap.a[A_PN] = p.pn; ap.a[A_RM] = p.rmask;
+  ap.a[A_SWF] = p.swflx; ap.a[A_RHOA] = p.rhoA; ap.a[A_RHOS] = p.rhoS; ap.a[A_UM] = p.umask; ap.a[A_VM] = p.vmask; ap.a[A_RUF] = p.rufrc;
+  ap.a[A_RVF] = p.rvfrc; ap.a[A_ZT] = p.Zt_avg1; ap.a[A_DU1] = p.DU_avg1; ap.a[A_DV1] = p.DV_avg1; ap.a[A_DU2] = p.DU_avg2; ap.a[A_DV2] = p.DV_avg2;
+}
+extern "C" {
 int roms_step2d(roms_ctx* h) {
   FLUSH_RHO(h);
   CK(cudaSetDevice(h->device));
@@ -833,6 +872,57 @@ int roms_step2d(roms_ctx* h) {
   s.zn = h->zeta(knew); s.un = h->ubar(knew); s.vn = h->vbar(knew);
   s.w1 = h->w1[iif]; s.w2 = h->w2[iif];
   s.iif = iif; s.nfast = h->nfast;
+  s.region = 0;
+  const bool multi = h->c.np_xi * h->c.np_eta > 1;
+  if (multi && h->overlap && p.Lm >= 8 && p.Mm >= 8) {
+    // ---- halo swaps of the barotropic loop hidden behind compute (north_star; the reference blocks in exchange_xxx, mpi_exchanges.F:672-800).
+    // Substep n is launched as INTERIOR (all points at least two cells from the subdomain's edges: they read no halo) on the main
+    // stream and RING (the two outermost cells, which read the halos of substeps n-1..n-3 and fill the messages of n) followed by
+    // the pack/flag/unpack pair on a second, high-priority stream.  interior(n) waits for ring(n-1), ring(n) waits for
+    // interior(n-1) and (stream order) for unpack(n-1): the swap of substep n runs while interior(n) and interior(n+1) compute.
+    const int e = iif & 1, o = e ^ 1;
+    dim3 b_(S2_TX, S2_TY, 1), g_((p.iend + IOFF + 1 + S2_TX - 1) / S2_TX, (p.jend - p.jstr + 1 + S2_TY - 1) / S2_TY, 1);
+    if (iif == 1) { CK(cudaEventRecord(h->ev_join, h->st)); CK(cudaStreamWaitEvent(h->st2, h->ev_join, 0)); }
+    else CK(cudaStreamWaitEvent(h->st, h->ev_edge[o], 0));
+    S2D si = s, sr = s;
+    si.region = 1; sr.region = 2;
+    if (h->s2d_tma >= 1 && h->s2d_tma <= 5) {     // interior by the TMA marching kernel (its emit mask skips the ring)
+      S2Planes ap;
+      s2d_planes(p, s, ap);
+      const int rows = h->s2d_rows;
+      const size_t sm_ = ((size_t)4 * S2M_NA * (64 + 4) + 2 * 64) * sizeof(double) + 4 * sizeof(unsigned long long);
+      static bool attr_ = false;
+      if (!attr_) { CK(cudaFuncSetAttribute((k_step2d_tma<64, 4>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_)); attr_ = true; }
+      dim3 bt_(64 + 32, 1, 1), gt_((p.iend - p.istr + 1 + 64 - 2) / (64 - 1), (p.jend - p.jstr + 1 + rows - 1) / rows, 1);
+      if (h->ktiming) kt_begin(h, "k_step2d_tma(interior)");
+      k_step2d_tma<64, 4><<<gt_, bt_, sm_, h->st>>>(p, si, ap, rows);
+      if (h->ktiming) kt_end(h);
+    } else {
+      if (h->ktiming) kt_begin(h, "k_step2d(interior)");
+      k_step2d<0><<<g_, b_, 0, h->st>>>(p, si);
+      if (h->ktiming) kt_end(h);
+    }
+    CK(cudaEventRecord(h->ev_int[e], h->st));
+    if (iif > 1) CK(cudaStreamWaitEvent(h->st2, h->ev_int[o], 0));
+    if (h->ktiming) kt_begin(h, "k_step2d(ring)", h->st2);
+    k_step2d<0><<<g_, b_, 0, h->st2>>>(p, sr);
+    if (h->ktiming) kt_end(h, h->st2);
+    h->launches += 2;
+    if (p.wwall || p.ewall) {
+      dim3 bw_(128, 1, 1), gw_((p.jendR - p.jstrR + 1 + 127) / 128, 2, 1);
+      k_step2d_ew<<<gw_, bw_, 0, h->st2>>>(p, s);
+      h->launches++;
+    }
+    CK(cudaEventRecord(h->ev_edge[e], h->st2));
+    int rc = exchange(h, {{s.zn, 1}, {s.un, 1}, {s.vn, 1}}, h->st2);
+    if (rc) return rc;
+    if (iif == h->nfast) {       // the 3-D part that follows needs the whole level and its halos
+      CK(cudaEventRecord(h->ev_join, h->st2));
+      CK(cudaStreamWaitEvent(h->st, h->ev_join, 0));
+      return roms_set_depth(h, 0);
+    }
+    return 0;
+  }
   if (h->s2d_tma >= 6) {
     // register-marching kernel (step2d_march.cuh): strips of TX-1 columns x s2d_rows rows per block
     const int rows = h->s2d_rows;
@@ -854,10 +944,7 @@ int roms_step2d(roms_ctx* h) {
   } else if (h->s2d_tma) {
     // TMA-fed marching kernel (step2d_tma.cuh): strips of S2M_TX-1 columns x s2d_rows rows per block
     S2Planes ap;
-    ap.a[A_H] = p.h; ap.a[A_ZS] = s.zs; ap.a[A_ZB] = s.zb; ap.a[A_ZO] = s.zo; ap.a[A_VS] = s.vs; ap.a[A_VB] = s.vb; ap.a[A_VO] = s.vo; ap.a[A_DMV] = p.dm_v;
-    ap.a[A_US] = s.us; ap.a[A_UB] = s.ub; ap.a[A_UO] = s.uo; ap.a[A_DNU] = p.dn_u; ap.a[A_PM] = p.pm; ap.a[A_PN] = p.pn; ap.a[A_RM] = p.rmask;
-    ap.a[A_SWF] = p.swflx; ap.a[A_RHOA] = p.rhoA; ap.a[A_RHOS] = p.rhoS; ap.a[A_UM] = p.umask; ap.a[A_VM] = p.vmask; ap.a[A_RUF] = p.rufrc;
-    ap.a[A_RVF] = p.rvfrc; ap.a[A_ZT] = p.Zt_avg1; ap.a[A_DU1] = p.DU_avg1; ap.a[A_DV1] = p.DV_avg1; ap.a[A_DU2] = p.DU_avg2; ap.a[A_DV2] = p.DV_avg2;
+    s2d_planes(p, s, ap);
     const int rows = h->s2d_rows;
 #define S2M_LAUNCH(TXn, Sn)                                                                                                                        \
   do {                                                                                                                                             \

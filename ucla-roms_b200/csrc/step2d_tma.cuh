@@ -103,7 +103,19 @@ __global__ void __launch_bounds__(S2M_TX + 32) k_step2d_tma(const __grid_constan
   const double cffg = 0.5 * p.g;
   const double cff = 0.5 * p.dtfast, cff1 = 0.5 * s.w1;
   const bool dou = (i >= p.istrU);            // u(istr) sits on a closed western wall: u2dbc, not the momentum update
+  // single periodic subdomain: results are stored to their halo images too (s2d_store); the offsets are fixed per thread / per row
+  const ix2_t ox = !p.wrap_x ? 0 : (i <= 2 ? (ix2_t)p.Lm : (i >= p.Lm - 1 ? -(ix2_t)p.Lm : 0));
+#define S2ST_(a, cc, v, oyy)                                  \
+  do {                                                        \
+    (a)[cc] = (v);                                            \
+    if (ox | (oyy)) {                                         \
+      if (ox) (a)[(cc) + ox] = (v);                           \
+      if (oyy) (a)[(cc) + (oyy)] = (v);                       \
+      if (ox && (oyy)) (a)[(cc) + ox + (oyy)] = (v);          \
+    }                                                         \
+  } while (0)
   for (int j = ja - 1; j <= jb; ++j) {
+    const ix2_t oy = !p.wrap_y ? 0 : (j <= 2 ? (ix2_t)p.Mm * SX : (j >= p.Mm - 1 ? -(ix2_t)p.Mm * SX : 0));
     const int C = (j - r0) % S2M_S, Nn = (j + 1 - r0) % S2M_S;
     s2m_wait(&full[Nn], (uint32_t)(((j + 1 - r0) / S2M_S) & 1));
     // ---- zeta_new(i,j) (step2d_FB.F:151-216)
@@ -136,14 +148,14 @@ __global__ void __launch_bounds__(S2M_TX + 32) k_step2d_tma(const __grid_constan
       b0.VFe = b0.UFe * (zn + zs);
       b0.VFx = b0.UFx * (rhoS0 - rhoA0);
     }
-    if (j >= ja && tx >= 1 && i <= p.iend) {
+    if (j >= ja && tx >= 1 && i <= p.iend && !(s.region == 1 && s2d_in_ring(p, i, j))) {
       // ---- own point (k_step2d phase 2)
       const double znw = znx[(j & 1) * S2M_TX + tx - 1];
       const bool swr = p.swall && j == p.jstr, nwr = p.nwall && j == p.jend;
       double zns = zn_s;
       if (swr) zns = zn * p.rmask[c - SX];       // zetabc.F: gradient condition on the row below the southern wall (s2d_zn_at)
       double DU1, DV1, Zt;
-      s2d_store(p, s.zn, i, j, c, zn);
+      S2ST_(s.zn, c, zn, oy);
       if (s.iif == 1) {
         p.DU_avg_bak[c] = SM_(C, A_DU1, 0) - 0.1024390243902439 * SM_(C, A_DU2, 0);
         p.DV_avg_bak[c] = SM_(C, A_DV1, 0) - 0.1024390243902439 * SM_(C, A_DV2, 0);
@@ -214,7 +226,7 @@ __global__ void __launch_bounds__(S2M_TX + 32) k_step2d_tma(const __grid_constan
         }
         p.DU_avg1[c] = DUa;
       } else if (s.iif == 1) p.DU_avg1[c] = DU1;
-      s2d_store(p, s.un, i, j, c, un);
+      S2ST_(s.un, c, un, oy);
       if (dov) {
         const double DVnew = ((D0 + Ds) * SM_(C, A_VS, 0) + cff * (pm0 + pm_s) * (pn0 + pn_s) * (rvbar + rvfrc)) * SM_(C, A_VM, 0);
         double vn = DVnew / (Dn0 + Dns);
@@ -228,14 +240,14 @@ __global__ void __launch_bounds__(S2M_TX + 32) k_step2d_tma(const __grid_constan
             DVa = river_flux;
           }
         }
-        s2d_store(p, s.vn, i, j, c, vn);
+        S2ST_(s.vn, c, vn, oy);
         p.DV_avg1[c] = DVa;
       } else {   // row jstr on a southern wall: v2dbc (no normal flow) and its DV_avg1 term (step2d_FB.F:449-529)
         const double vn = 0.0;
-        s2d_store(p, s.vn, i, j, c, vn);
+        S2ST_(s.vn, c, vn, oy);
         p.DV_avg1[c] = DV1 + cff1 * (Dn0 + Dns) * (vn)*dmv;
       }
-      if (s.iif == s.nfast) s2d_store(p, s.zn, i, j, c, Zt);
+      if (s.iif == s.nfast) S2ST_(s.zn, c, Zt, oy);
       // ---- wall point beside this one (k_step2d, same expressions; operands straight from global memory: two rows per domain)
       if (swr | nwr) {
 #pragma unroll 1
@@ -248,15 +260,15 @@ __global__ void __launch_bounds__(S2M_TX + 32) k_step2d_tma(const __grid_constan
           double DU1w, DV1w, Ztw;
           s2d_avg_out(p, s, i, jw, w, znb, s2d_DUon(p, s, w), side == 0 ? 0.0 : s2d_DVom(p, s, w), DU1w, DV1w, Ztw);
           const double unw = p.gamma2 * un * p.umask[w];          // u2dbc_im.F:150-152
-          s2d_store(p, s.un, i, jw, w, unw);
+          S2ST_(s.un, w, unw, (ix2_t)0);
           if (dou) p.DU_avg1[w] = DU1w + cff1 * ((p.h[w] + znb) + (p.h[w - 1] + znbw)) * (unw)*p.dn_u[w];
           else if (s.iif == 1) p.DU_avg1[w] = DU1w;
           if (side == 1) {
             const double vnw = 0.0;
-            s2d_store(p, s.vn, i, jw, w, vnw);
+            S2ST_(s.vn, w, vnw, (ix2_t)0);
             p.DV_avg1[w] = DV1w + cff1 * ((znb + p.h[w]) + (zn + p.h[c])) * (vnw)*p.dm_v[w];
           } else if (s.iif == 1) p.DV_avg1[w] = DV1w;
-          if (s.iif == s.nfast) s2d_store(p, s.zn, i, jw, w, Ztw);
+          if (s.iif == s.nfast) S2ST_(s.zn, w, Ztw, (ix2_t)0);
         }
       }
     }
@@ -266,5 +278,6 @@ __global__ void __launch_bounds__(S2M_TX + 32) k_step2d_tma(const __grid_constan
     Drhs_c = Drhs_n; DVom_c = DVom_n;
   }
 #undef SM_
+#undef S2ST_
 #undef DRHS_
 }
