@@ -39,9 +39,8 @@ KERNEL_WORDS = {
     "k_t_horiz": lambda t: (2 + 3 * int(t[3]), 3),        # FlxU,FlxV + per tracer t(nrhs) R, t(nnew) RW
     "k_t_vert": lambda t: ((4 if t[0] == "0" else 3) + (1 if t[2] == "true" else int(t[1])) + 3 * int(t[1]), 3),   # Hz,We,Wi[,FlxDiv] + Akt slots + per tracer t(nrhs) R, t(nnew) RW
     "k_uv_vert": lambda t: (10 if t[0] == "0" else 9, 3),
-    "k_set_huv1": (4, 3), "k_set_huv1_sm": (4, 3), "k_uv2_pass0": (3, 3), "k_uv2_pass1": (6, 3), "k_uv2_pass1_sm": (6, 3),
+    "k_set_huv1": (4, 3), "k_uv2_pass0": (3, 3), "k_uv2_pass1": (6, 3), "k_uv2_pass1_sm": (6, 3),
     "k_uv2_sm": (6, 3),      # step3d_uv2 passes 0+1 fused: Hz, u(nnew), u(nstp), Flx read; u(nnew), Flx written
-    "k_omega2": (6, 3),
     # KPP closure (row f2): 3-D operands read once, results written once
     "k_lmd_rig": (5, 3), "k_lmd_smooth": (2, 3), "k_lmd_vmix_col": (5, 3), "k_lmd_kpp1": (8, 3), "k_lmd_kpp2": (9, 3),
     "k_set_depth": (3, 3), "k_step2d_zeta": (24, 2), "k_step2d_uv": (23, 2), "k_rd_bott_drag": (3, 2),

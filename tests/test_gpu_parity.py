@@ -154,6 +154,23 @@ def test_one_step_and_100_steps_channel(walls, topo, ew, mix):
     g.close(); o.close()
 
 
+@pytest.mark.parametrize("env", [{"ROMS_S2D_TMA": "0"}, {"ROMS_S2D_TMA": "2", "ROMS_S2D_ROWS": "5"}, {"ROMS_S2D_TMA": "6", "ROMS_S2D_ROWS": "7"},
+                                 {"ROMS_UV2_FUSED": "0"}])
+@pytest.mark.parametrize("closed", [False, True])
+def test_kernel_variants_are_bit_identical(env, closed, monkeypatch):
+    """The shipped alternatives of the barotropic substep (tile kernel, TMA ring of another shape, register marching; ragged row
+    blocks on purpose) and the unfused step3d_uv2 passes: every variant must reproduce the oracle exactly like the defaults do."""
+    for k, v in env.items():
+        monkeypatch.setenv(k, v)
+    cfg, st = cases.channel(70, 45, 12, ns_walls=True, seamount=closed, island=closed, ew_walls=closed)
+    g, o = Roms(cfg), Oracle(cfg)
+    cases.initialize(g, st); cases.initialize(o, st)
+    g.call("run", 3); o.call("run", 3)
+    r = compare(g, o, cfg.NT, TOL1, cfg)
+    assert max(r.values()) == 0.0, r
+    g.close(); o.close()
+
+
 def test_filament_golden_on_gpu():
     """The CUDA path itself against the reference's golden log (tests/Filament/benchmark.result_github_gnu:146-167)."""
     cfg, _ = cases.filament()

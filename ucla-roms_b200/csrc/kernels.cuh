@@ -293,100 +293,6 @@ __global__ void k_omega(const __grid_constant__ KP p, double dtau) {
   }
 }
 
-// omega_tile WITHOUT column scratch (the shipped variant).  In the reference's second loop every level is independent once
-// the surface value W(N) of the continuity integral is known (omega.F:118-160: Wi(k), We(k) need W(k), CX(k), CX(k+1), Hz(k),
-// Hz(k+1) only).  So: pass A integrates continuity to the surface (the four fluxes of a level, nothing stored), pass B repeats
-// the identical running sum -- same operands, same order, hence the same roundings -- and finishes level k-1 as soon as
-// CX(k) is known.  Per point: FlxU, FlxV twice (the second time mostly from L2), z_w, Hz once, We, Wi written: no 2*(N+1)-plane
-// slab, 8 instead of 10 words of traffic.  With fd_cff != 0 the kernel also produces FlxDiv of pre_step3d4S.F:138-147 for its
-// own column (We, Wi of the column are final; the halo ring of FlxDiv is left to k_pre_flxdiv).
-__global__ void __launch_bounds__(64, 12) k_omega2(const __grid_constant__ KP p, double dtau, double fd_cff) {
-  THREAD_IJ(p.istr, p.iend, p.jstr, p.jend)
-  const int N = p.N;
-  const double cu_min = 0.6, cu_max = 1.0, cmnx_ratio = cu_min / cu_max, cutoff = 2.0 - cmnx_ratio, r4cmx = 0.25 / (1.0 - cmnx_ratio);
-  const int pidx = p.pipes ? (int)p.pipe_idx[c] : 0;
-  const double pflx = pidx > 0 ? p.pipe_flx[c] : 0.0;
-  const double* __restrict__ gFu = p.FlxU;
-  const double* __restrict__ gFv = p.FlxV;
-  const double* __restrict__ gzw = p.z_w;
-  const double* __restrict__ gHz = p.Hz;
-  double W = 0.0;
-  for (int k0 = 1; k0 <= N; k0 += KCO) {
-    double a1[KCO], a0[KCO], b1[KCO], b0[KCO];
-#pragma unroll
-    for (int q = 0; q < KCO; ++q)
-      if (k0 + q <= N) { a1[q] = R3(gFu, c + 1, k0 + q); a0[q] = R3(gFu, c, k0 + q); b1[q] = R3(gFv, c + SX, k0 + q); b0[q] = R3(gFv, c, k0 + q); }
-#pragma unroll
-    for (int q = 0; q < KCO; ++q) {
-      const int k = k0 + q;
-      if (k <= N) {
-        W = W - a1[q] + a0[q] - b1[q] + b0[q];
-        if (pidx > 0) W = W + pflx * p.pipe_tab[(pidx - 1) * PIPROW(N) + k - 1];   // omega.F:102-108
-      }
-    }
-  }
-  W = W + p.swflx[c] * p.dm_r[c] * p.dn_r[c];
-  const double zw0 = RW(gzw, c, 0);
-  const double wrk = W / (RW(gzw, c, N) - zw0);
-  RW(p.Wi, c, 0) = 0.0;
-  RW(p.We, c, 0) = 0.0;
-  const double CX0 = dtau * p.pm[c] * p.pn[c];
-  const double fdc = fd_cff * p.pm[c] * p.pn[c];
-  // pass B: level k arrives, level k-1 is finished
-  double Wk = 0.0, Wm = 0.0, CXm = 0.0, Hzm = 0.0, zwm = 0.0, divm = 0.0;   // "m" = level k-1
-  double We_mm = 0.0, Wi_mm = 0.0;                                           // We, Wi at level k-2 (zero at the bottom)
-  for (int k0 = 1; k0 <= N; k0 += KCO) {
-    double a1[KCO], a0[KCO], b1[KCO], b0[KCO], hz[KCO], zw[KCO];
-#pragma unroll
-    for (int q = 0; q < KCO; ++q)
-      if (k0 + q <= N) {
-        a1[q] = R3(gFu, c + 1, k0 + q); a0[q] = R3(gFu, c, k0 + q); b1[q] = R3(gFv, c + SX, k0 + q); b0[q] = R3(gFv, c, k0 + q);
-        hz[q] = R3(gHz, c, k0 + q); zw[q] = RW(gzw, c, k0 + q);
-      }
-#pragma unroll
-    for (int q = 0; q < KCO; ++q) {
-      const int k = k0 + q;
-      if (k <= N) {
-        const double fu1 = a1[q], fu0 = a0[q], fv1 = b1[q], fv0 = b0[q];
-        Wk = Wk - fu1 + fu0 - fv1 + fv0;
-        if (pidx > 0) Wk = Wk + pflx * p.pipe_tab[(pidx - 1) * PIPROW(N) + k - 1];
-        const double CXk = DMAX(fu1, 0.0) - DMIN(fu0, 0.0) + DMAX(fv1, 0.0) - DMIN(fv0, 0.0);
-        const double Hzk = hz[q];
-        const double divk = fu1 - fu0 + fv1 - fv0;      // FlxU(i+1)-FlxU(i)+FlxV(j+1)-FlxV(j)
-        if (k >= 2) {                                   // finish level k-1 (omega.F:118-160)
-          double Wik = Wm - wrk * (zwm - zw0);
-          const double c2d = DMAX(CXm, CXk);
-          const double dh = DMIN(Hzm, Hzk);
-          const double cw_max = cu_max * dh - c2d * CX0;
-          double Wek;
-          if (cw_max > 0.0) {
-            const double cw_max2 = cw_max * cw_max;
-            const double cw_min = cw_max * cmnx_ratio;
-            const double cw = fabs(Wik) * CX0;
-            double cff;
-            if (cw < cw_min) cff = cw_max2;
-            else if (cw < cutoff * cw_max) cff = cw_max2 + r4cmx * ((cw - cw_min) * (cw - cw_min));
-            else cff = cw_max * cw;
-            Wek = cw_max2 * Wik / cff;
-            Wik = Wik - Wek;
-          } else Wek = 0.0;
-          RW(p.We, c, k - 1) = Wek;
-          RW(p.Wi, c, k - 1) = Wik;
-          if (fd_cff != 0.0) {
-            // pre_step3d4S.F:138-147 at level k-1: ... + We(k-1) + Wi(k-1) - We(k-2) - Wi(k-2), summed in the reference's order
-            R3(p.FlxDiv, c, k - 1) = fdc * (divm + Wek + Wik - We_mm - Wi_mm);
-            We_mm = Wek; Wi_mm = Wik;
-          }
-        }
-        Wm = Wk; CXm = CXk; Hzm = Hzk; zwm = zw[q]; divm = divk;
-      }
-    }
-  }
-  RW(p.Wi, c, N) = 0.0;
-  RW(p.We, c, N) = 0.0;
-  if (fd_cff != 0.0) R3(p.FlxDiv, c, N) = fdc * (divm + 0.0 + 0.0 - We_mm - Wi_mm);   // We(N) = Wi(N) = 0
-}
-
 // rho_eos.F:26-409 rho_eos_tile over the extended range (whole padded subdomain), one down-sweep:
 // rho1,qp1 per level and the vertical integrals rhoA, rhoS (rho_eos.F:364-395).
 template <bool NONLIN>
@@ -893,8 +799,8 @@ __device__ __forceinline__ double tflux_cl(const KP& p, const double* __restrict
 }
 
 // pre_step3d4S.F:138-147: FlxDiv such that Hz_bak = Hz + FlxDiv, Hz_fwd = Hz - FlxDiv
-__global__ void k_pre_flxdiv(const __grid_constant__ KP p, double dtau, int i0, int i1, int j0, int j1) {
-  THREAD_IJ(i0, i1, j0, j1)
+__global__ void k_pre_flxdiv(const __grid_constant__ KP p, double dtau) {
+  THREAD_IJ(p.istrU - 1, p.iend, p.jstrV - 1, p.jend)
   const int k = blockIdx.z + 1;
   const double cff = 0.5 * dtau;
   R3(p.FlxDiv, c, k) = cff * p.pm[c] * p.pn[c] *
@@ -1594,10 +1500,7 @@ __device__ __forceinline__ void s2d_avg_out(const KP& p, const S2D& s, int i, in
   }
   p.Zt_avg1[c] = Zt;
 }
-// HW = 1: two extra warps per block (ty = S2_TY, S2_TY+1) evaluate the 41 halo values of zeta_new while the eight tile warps
-// evaluate their own, instead of two tile warps doing it in a second serial pass: the latency of phase 1 halves.
-template <int HW>
-__global__ void __launch_bounds__(S2_TX * (S2_TY + 2 * HW), (HW ? 3 : LB_S2D)) k_step2d(const __grid_constant__ KP p, const __grid_constant__ S2D s) {
+__global__ void __launch_bounds__(S2_TX * S2_TY, LB_S2D) k_step2d(const __grid_constant__ KP p, const __grid_constant__ S2D s) {
   __shared__ double zt[S2_TY + 1][S2_TX + 1];
   const int tx = threadIdx.x, ty = threadIdx.y;
   const int i0 = blockIdx.x * S2_TX - IOFF, j0 = p.jstr + blockIdx.y * S2_TY;
@@ -1606,9 +1509,9 @@ __global__ void __launch_bounds__(S2_TX * (S2_TY + 2 * HW), (HW ? 3 : LB_S2D)) k
   // ring-only launch: tiles that hold no ring point leave at once
   if (s.region == 2 && !(i0 <= p.istr + 1 || i0 + S2_TX - 1 >= p.iend - 1 || j0 <= p.jstr + 1 || j0 + S2_TY - 1 >= p.jend - 1)) return;
   // ---- phase 1: zeta_new (step2d_FB.F:151-216) on the tile, the row below it and the column to its left
-  if ((HW == 0 || ty < S2_TY) && i >= p.istrU - 1 && i <= p.iend && j <= p.jend) zt[ty + 1][tx + 1] = s2d_zeta_new(p, s, CIDX(i, j));
-  if (HW == 0 || ty >= S2_TY) {
-    const int t = (HW ? ty - S2_TY : ty) * S2_TX + tx;
+  if (i >= p.istrU - 1 && i <= p.iend && j <= p.jend) zt[ty + 1][tx + 1] = s2d_zeta_new(p, s, CIDX(i, j));
+  {
+    const int t = ty * S2_TX + tx;
     if (t < S2_TX + 1) {
       const int ii = i0 - 1 + t, jj = j0 - 1;
       if (ii >= p.istrU - 1 && ii <= p.iend) zt[0][t] = s2d_zn_at(p, s, CIDX(ii, jj), jj);
@@ -1618,7 +1521,6 @@ __global__ void __launch_bounds__(S2_TX * (S2_TY + 2 * HW), (HW ? 3 : LB_S2D)) k
     }
   }
   __syncthreads();
-  if (HW && ty >= S2_TY) return;
   if (i < p.istr || i > p.iend || j > p.jend) return;
   if (s.region && (s2d_in_ring(p, i, j) != (s.region == 2))) return;
   // ---- phase 2: own point
@@ -1714,6 +1616,7 @@ __global__ void __launch_bounds__(S2_TX * (S2_TY + 2 * HW), (HW ? 3 : LB_S2D)) k
 }
 #include "step2d_tma.cuh"
 #include "step2d_march.cuh"
+#include "tracer_tma.cuh"
 
 // zeta_new at any point of the rho-range incl. wall rows, wall columns and basin corners (zetabc.F:39-81)
 __device__ __forceinline__ double s2d_zn_full(const KP& p, const S2D& s, int i, int j) {
@@ -2121,31 +2024,6 @@ __global__ void __launch_bounds__(64, 3) k_uv2_sm(const __grid_constant__ KP p, 
   for (int k = 1; k <= N; ++k) R3(Flx, c, k) = SB(k) - SA(k) * CF0;
 }
 
-// set_HUV1_tile (set_depth.F:252-422) with the column parked in shared memory between its two loops: Hz and u cross HBM once
-// (4 words per point instead of ~6.5).  Expression for expression k_set_huv1.
-template <int DIR>
-__global__ void __launch_bounds__(64, 3) k_set_huv1_sm(const __grid_constant__ KP p, double* __restrict__ u, int first) {
-  extern __shared__ double smem[];
-  THREAD_IJT(ixc_t, (DIR == 0 ? p.istr : p.istrR), p.iendR, (DIR == 0 ? p.jstrR : p.jstr), p.jendR)
-  COLSM_PROLOGUE
-  const ixc_t d = DIR == 0 ? 1 : SX;
-  const int N = p.N;
-  const double dn = DIR == 0 ? p.dn_u[c] : p.dm_v[c];
-  const double msk = DIR == 0 ? p.umask[c] : p.vmask[c];
-  double* __restrict__ Flx = DIR == 0 ? p.FlxU : p.FlxV;
-  double DC0 = 0.0, FC0 = 0.0;
-  colsm_sum_sweep<DIR>(p, c, d, dn, u, sA, sB, nth, DC0, FC0);
-  const double* a1 = DIR == 0 ? p.DU_avg1 : p.DV_avg1;
-  const double* a2 = DIR == 0 ? p.DU_avg2 : p.DV_avg2;
-  const double* ab = DIR == 0 ? p.DU_avg_bak : p.DV_avg_bak;
-  if (first) FC0 = (FC0 - a1[c]) / DC0;
-  else FC0 = (FC0 - 3.63 * a1[c] + 4.47 * a2[c] - 2.05 * ab[c]) / DC0;
-  for (int k = 1; k <= N; ++k) {
-    const double un = (SB(k) - FC0) * msk;
-    R3(u, c, k) = un;
-    R3(Flx, c, k) = SA(k) * (un);
-  }
-}
 #undef SA
 #undef SB
 

@@ -42,6 +42,9 @@ struct roms_ctx {
   cudaStream_t st;
   cudaStream_t st2 = nullptr;                      // high-priority stream of the ring kernels and halo swaps of the barotropic loop
   cudaEvent_t ev_int[2] = {nullptr, nullptr}, ev_edge[2] = {nullptr, nullptr}, ev_join = nullptr;
+  int t_tma = 1;      // horizontal tracer kernels with TMA-staged tiles (tracer_tma.cuh); 0: the scalar-load kernels
+  TmaMaps tmaps;      // three tensor maps over the whole arena (one per box shape)
+  int tmaps_ok = 0;
   int overlap = 1;    // multi-rank: barotropic halo swaps overlapped with the interior launch of the next substep (ROMS_OVERLAP=0: serial)
   FieldSlot f[ROMS_NFIELDS];
   double* arena = nullptr;
@@ -68,12 +71,7 @@ struct roms_ctx {
   int uv2_sm = 1;     // k_uv2_pass1 with the column parked in shared memory (1.0 -> 0.78 ms on B200); off when the column is too tall
   int s2d_tma = 1;    // barotropic substep as the TMA-fed marching kernel k_step2d_tma; 0: the tile kernel k_step2d
   int s2d_rows = 16;  // rows per block of the marching kernels (measured best on B200: profiles/r2_step2d_variants.txt)
-  int s2d_hw = 0;     // k_step2d with two dedicated halo warps per block
-  int huv1_sm = 0;
   int uv2_fused = 1;  // step3d_uv2 passes 0 and 1 in one shared-memory column kernel (k_uv2_sm)
-  int omega2 = 0;     // scratch-free two-pass omega kernel (k_omega2); 0: the slab version k_omega
-  int flxdiv_valid = 0;     // k_omega2 has already produced FlxDiv of the interior columns with the factor flxdiv_cff
-  double flxdiv_cff = 0.0;
   int tb_max = 4;     // most tracers per launch of the tracer kernels (ROMS_TB = 1, 2 or 4)
   int use_smem = 0;   // measured on B200 (profiles/r1_scratch_policy.txt): occupancy beats shared-memory scratch
   Comm comm;
@@ -280,13 +278,11 @@ int roms_create(const roms_cfg* cfg, int device, roms_ctx** out) {
   if (const char* e = getenv("ROMS_COL_SMEM")) h->use_smem = atoi(e);
   if (const char* e = getenv("ROMS_UV2_SM")) h->uv2_sm = atoi(e);
   if (const char* e = getenv("ROMS_TB")) h->tb_max = atoi(e);
-  if (const char* e = getenv("ROMS_OMEGA2")) h->omega2 = atoi(e);
   if (const char* e = getenv("ROMS_UV2_FUSED")) h->uv2_fused = atoi(e);
-  if (const char* e = getenv("ROMS_S2D_HW")) h->s2d_hw = atoi(e);
   if (const char* e = getenv("ROMS_OVERLAP")) h->overlap = atoi(e);
+  if (const char* e = getenv("ROMS_T_TMA")) h->t_tma = atoi(e);
   if (const char* e = getenv("ROMS_S2D_TMA")) h->s2d_tma = atoi(e);
   if (const char* e = getenv("ROMS_S2D_ROWS")) h->s2d_rows = atoi(e) > 0 ? atoi(e) : 32;
-  if (const char* e = getenv("ROMS_HUV1_SM")) h->huv1_sm = atoi(e);
   if (const char* e = getenv("ROMS_FUSE_RHO")) h->fuse_rho = atoi(e);
   if ((size_t)2 * (N + 1) * 32 * sizeof(double) > 64 * 1024) h->uv2_sm = 0;   // fewer than 3 warps per SM would fit: global re-read version
   if ((size_t)2 * (N + 1) * h->col_bx * h->col_by * sizeof(double) > 200 * 1024) { h->col_by = 1; }
@@ -347,6 +343,28 @@ int roms_create(const roms_cfg* cfg, int device, roms_ctx** out) {
   P1(riv_uflx, ROMS_RIV_UFLX); P1(riv_vflx, ROMS_RIV_VFLX); P1(pipe_idx, ROMS_PIPE_IDX); P1(pipe_flx, ROMS_PIPE_FLX); P1(ptide, ROMS_PTIDE); P1(srflx, ROMS_SRFLX);
 #undef P1
   p.Akt[0] = h->f[ROMS_AKT].ptr[0]; p.Akt[1] = h->f[ROMS_AKT].ptr[1];
+  if (h->t_tma) {
+    // the arena as ONE 2-D tensor: SX columns x every row of every plane (all fields share the pitch and the plane height)
+    typedef CUresult (*encode_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                  CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    void* fp = nullptr;
+    cudaDriverEntryPointQueryResult qr;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fp, cudaEnableDefault, &qr) == cudaSuccess && fp && qr == cudaDriverEntryPointSuccess) {
+      encode_fn enc = (encode_fn)fp;
+      const cuuint64_t gdim[2] = {(cuuint64_t)p.SX, (cuuint64_t)(h->arena_doubles / (size_t)p.SX)};
+      const cuuint64_t gstr[1] = {(cuuint64_t)p.SX * sizeof(double)};
+      const cuuint32_t estr[2] = {1, 1};
+      struct { CUtensorMap* m; cuuint32_t bx, by; } mk[3] = {{&h->tmaps.t36x12, TT_W, TT_H}, {&h->tmaps.f34x9, TF_W, TF_H}, {&h->tmaps.o32x8, 32, 8}};
+      int ok = 1;
+      for (auto& q : mk) {
+        const cuuint32_t box[2] = {q.bx, q.by};
+        if (enc(q.m, CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, h->arena, gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                CU_TENSOR_MAP_L2_PROMOTION_L2_128B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) != CUDA_SUCCESS) ok = 0;
+      }
+      h->tmaps_ok = ok;
+    } else cudaGetLastError();
+    if (!h->tmaps_ok) { g_err = "roms_create: cuTensorMapEncodeTiled failed (the TMA tracer kernels need it); set ROMS_T_TMA=0 to use the scalar-load kernels"; return -1; }
+  }
   host_scoord(h);
   host_weights(h);
   CK(cudaMemcpy(p.Cs_w, h->Cs_w.data(), (N + 1) * sizeof(double), cudaMemcpyHostToDevice));
@@ -394,7 +412,6 @@ long roms_field_count(roms_ctx* h, int field) {
 int roms_push(roms_ctx* h, int field, int lvl, int itrc, const double* host) {
   FLUSH_RHO(h);
   if (join_st2(h)) return -1;
-  h->flxdiv_valid = 0;
   double* d; int nk;
   if (find_slot(h, field, lvl, itrc, &d, &nk)) return -1;
   CK(cudaSetDevice(h->device));
@@ -619,7 +636,6 @@ int roms_set_depth(roms_ctx* h, int tile) {
 }
 int roms_set_huv(roms_ctx* h) {
   CK(cudaSetDevice(h->device));
-  h->flxdiv_valid = 0;
   const KP& p = h->kp;
   PLANE(k_set_huv, p.iendR, p.jstrR, p.jendR, p.N, p, h->u(h->nrhs), h->v(h->nrhs));
   return exchange(h, {{p.FlxU, p.N}, {p.FlxV, p.N}});
@@ -630,14 +646,8 @@ int roms_set_huv1(roms_ctx* h, int tile) {
   CK(cudaSetDevice(h->device));
   const KP& p = h->kp;
   const int first = (h->iic == h->forw_start);
-  h->flxdiv_valid = 0;
-  if (h->uv2_sm && h->huv1_sm) {
-    COLUMN_SM(k_set_huv1_sm<0>, p.iendR, p.jstrR, p.jendR, p, h->u(h->nnew), first);
-    COLUMN_SM(k_set_huv1_sm<1>, p.iendR, p.jstr, p.jendR, p, h->v(h->nnew), first);
-  } else {
-    COLUMN(k_set_huv1<0>, 0, p.iendR, p.jstrR, p.jendR, p, h->u(h->nnew), first);
-    COLUMN(k_set_huv1<1>, 0, p.iendR, p.jstr, p.jendR, p, h->v(h->nnew), first);
-  }
+  COLUMN(k_set_huv1<0>, 0, p.iendR, p.jstrR, p.jendR, p, h->u(h->nnew), first);
+  COLUMN(k_set_huv1<1>, 0, p.iendR, p.jstr, p.jendR, p, h->v(h->nnew), first);
   return exchange(h, {{p.FlxU, p.N}, {p.FlxV, p.N}, {h->u(h->nnew), p.N}, {h->v(h->nnew), p.N}});
 }
 int roms_omega(roms_ctx* h) {
@@ -647,17 +657,7 @@ int roms_omega(roms_ctx* h) {
   if (h->nrhs == 3) dtau = h->c.dt;
   else if (h->iic == h->forw_start) dtau = 0.5 * h->c.dt;
   else dtau = 0.6 * h->c.dt;
-  h->flxdiv_valid = 0;
-  if (h->omega2) {
-    // the predictor-stage call (main.F:402) is followed by pre_step3d, whose first act is FlxDiv = 0.5*dtau_pre*pm*pn*div(Flx,W)
-    // (pre_step3d4S.F:138-147): the kernel has every operand of it in registers and stores it for its own columns
-    double fd_cff = 0.0;
-    if (h->nrhs != 3) fd_cff = 0.5 * ((h->iic == h->forw_start) ? 0.5 * h->c.dt : h->c.dt * (1.0 - 1.0 / 6.0));
-    COLUMN(k_omega2, 0, p.iend, p.jstr, p.jend, p, dtau, fd_cff);
-    if (fd_cff != 0.0) { h->flxdiv_valid = 1; h->flxdiv_cff = fd_cff; }
-  } else {
-    COLUMN(k_omega, 2, p.iend, p.jstr, p.jend, p, dtau);
-  }
+  COLUMN(k_omega, 2, p.iend, p.jstr, p.jend, p, dtau);
   bc3d(h, p.We, p.N + 1, BC_W);      // omega.F:171-231 edge copies
   bc3d(h, p.Wi, p.N + 1, BC_W);
   return exchange(h, {{p.We, p.N + 1}, {p.Wi, p.N + 1}});
@@ -720,8 +720,52 @@ static TrcBatch<TB> make_batch(roms_ctx* h, const TPlan& pl, int nrhs, int nnew,
     else if (WALLED(h)) PLANE((kern<true, KB_T, false, TBn>), p.iend, p.jstr, p.jend, (p.N + KB_T - 1) / KB_T, p, __VA_ARGS__); \
     else PLANE((kern<false, KB_T, false, TBn>), p.iend, p.jstr, p.jend, (p.N + KB_T - 1) / KB_T, p, __VA_ARGS__);               \
   } while (0)
+// ---- TMA-staged horizontal tracer kernels (tracer_tma.cuh)
+template <int TB>
+static TrcRows<TB> make_rows(roms_ctx* h, const TrcBatch<TB>& b) {
+  const KP& p = h->kp;
+  const int R = h->c.Mm + 4;
+  auto row = [&](const double* a) { return (int)(((size_t)(a - h->arena) / (size_t)p.SXY) * (size_t)R); };
+  TrcRows<TB> r;
+  r.flxu = row(p.FlxU); r.flxv = row(p.FlxV); r.hz = row(p.Hz); r.fd = row(p.FlxDiv);
+  for (int q = 0; q < TB; ++q) { r.rhs[q] = row(b.rhs[q]); r.tnew[q] = row(b.tnew[q]); r.stp[q] = row(b.stp[q]); r.indx[q] = row(b.indx[q]); }
+  return r;
+}
+#define TTMA_KB 8
+template <bool PRE, bool WALL, bool RIV, int TB, int NS>
+static int t_tma_launch(roms_ctx* h, const TrcBatch<TB>& b, double dtau, double cf_stp, double cf_bak) {
+  const KP& p = h->kp;
+  typedef TtmaLayout<PRE, TB> L;
+  const size_t sm_ = (size_t)NS * L::stage * sizeof(double) + NS * sizeof(unsigned long long);
+  static bool attr_ = false;
+  if (!attr_) { CK(cudaFuncSetAttribute((k_t_horiz_tma<PRE, WALL, RIV, TB, TTMA_KB, NS>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_)); attr_ = true; }
+  dim3 b_(288, 1, 1), g_((p.iend + IOFF + 1 + 31) / 32, (p.jend - p.jstr + 1 + 7) / 8, (p.N + TTMA_KB - 1) / TTMA_KB);
+  if (h->ktiming) kt_begin(h, PRE ? "k_pre_t_horiz_tma" : "k_t_horiz_tma");
+  k_t_horiz_tma<PRE, WALL, RIV, TB, TTMA_KB, NS><<<g_, b_, sm_, h->st>>>(p, b, h->tmaps, make_rows<TB>(h, b), dtau, cf_stp, cf_bak);
+  if (h->ktiming) kt_end(h);
+  h->launches++;
+  return 0;
+}
+template <bool PRE, int TB, int NS>
+static int t_tma_variant(roms_ctx* h, const TrcBatch<TB>& b, double dtau, double cf_stp, double cf_bak) {
+  if (h->kp.rivers) return t_tma_launch<PRE, true, true, TB, NS>(h, b, dtau, cf_stp, cf_bak);
+  if (WALLED(h)) return t_tma_launch<PRE, true, false, TB, NS>(h, b, dtau, cf_stp, cf_bak);
+  return t_tma_launch<PRE, false, false, TB, NS>(h, b, dtau, cf_stp, cf_bak);
+}
 static int tracer_pre_horiz(roms_ctx* h, const TPlan& pl, int nrhs, int nnew, int nstp, int indx, double dtau, double cf_stp, double cf_bak) {
   const KP& p = h->kp;
+  if (h->t_tma) {
+    if (pl.n == 4) {      // two half-batches: a stage of four predictor tracers would leave one block per SM
+      for (int half = 0; half < 2; ++half) {
+        TPlan q = {2, {pl.it[2 * half], pl.it[2 * half + 1], 0, 0}, pl.share};
+        int rc = t_tma_variant<true, 2, 3>(h, make_batch<2>(h, q, nrhs, nnew, nstp, indx), dtau, cf_stp, cf_bak);
+        if (rc) return rc;
+      }
+      return 0;
+    }
+    if (pl.n == 2) return t_tma_variant<true, 2, 3>(h, make_batch<2>(h, pl, nrhs, nnew, nstp, indx), dtau, cf_stp, cf_bak);
+    return t_tma_variant<true, 1, 3>(h, make_batch<1>(h, pl, nrhs, nnew, nstp, indx), dtau, cf_stp, cf_bak);
+  }
   if (pl.n == 4) T_HORIZ_LAUNCH(k_pre_t_horiz, 4, make_batch<4>(h, pl, nrhs, nnew, nstp, indx), dtau, cf_stp, cf_bak);
   else if (pl.n == 2) T_HORIZ_LAUNCH(k_pre_t_horiz, 2, make_batch<2>(h, pl, nrhs, nnew, nstp, indx), dtau, cf_stp, cf_bak);
   else T_HORIZ_LAUNCH(k_pre_t_horiz, 1, make_batch<1>(h, pl, nrhs, nnew, nstp, indx), dtau, cf_stp, cf_bak);
@@ -729,6 +773,18 @@ static int tracer_pre_horiz(roms_ctx* h, const TPlan& pl, int nrhs, int nnew, in
 }
 static int tracer_cor_horiz(roms_ctx* h, const TPlan& pl, int nrhs, int nnew) {
   const KP& p = h->kp;
+  if (h->t_tma) {
+    if (pl.n == 4) {
+      for (int half = 0; half < 2; ++half) {
+        TPlan q = {2, {pl.it[2 * half], pl.it[2 * half + 1], 0, 0}, pl.share};
+        int rc = t_tma_variant<false, 2, 3>(h, make_batch<2>(h, q, nrhs, nnew, nrhs, nnew), 0.0, 0.0, 0.0);
+        if (rc) return rc;
+      }
+      return 0;
+    }
+    if (pl.n == 2) return t_tma_variant<false, 2, 3>(h, make_batch<2>(h, pl, nrhs, nnew, nrhs, nnew), 0.0, 0.0, 0.0);
+    return t_tma_variant<false, 1, 3>(h, make_batch<1>(h, pl, nrhs, nnew, nrhs, nnew), 0.0, 0.0, 0.0);
+  }
   if (pl.n == 4) {
     // measured on B200 (profiles/r2_kernels_tracers_v0.txt): the UP3 corrector is faster per tracer in batches of 2 (1.87 vs 2.54 ms)
     for (int half = 0; half < 2; ++half) {
@@ -786,8 +842,6 @@ int roms_prsgrd(roms_ctx* h) {
   return 0;
 }
 int roms_pre_step3d(roms_ctx* h, int tile) {
-  const int flxdiv_done = h->flxdiv_valid;
-  h->flxdiv_valid = 0;
   FLUSH_RHO(h);
   (void)tile;
   CK(cudaSetDevice(h->device));
@@ -798,13 +852,7 @@ int roms_pre_step3d(roms_ctx* h, int tile) {
   if (h->iic == h->forw_start) { dtau = 0.5 * dt; cf_stp = 1.0; cf_bak = 0.0; }
   else { dtau = dt * (1.0 - AM3_crv); cf_stp = 0.5 + AM3_crv; cf_bak = 0.5 - AM3_crv; }
   const bool wl = WALLED(h);
-  if (flxdiv_done && h->flxdiv_cff == 0.5 * dtau) {
-    // interior columns came out of k_omega2; what is left is the halo ring on periodic / inter-subdomain sides (needs the exchanged We, Wi)
-    if (!p.wwall) PLANE(k_pre_flxdiv, 0, p.jstrV - 1, p.jend, p.N, p, dtau, 0, 0, p.jstrV - 1, p.jend);
-    if (!p.swall) PLANE(k_pre_flxdiv, p.iend, 0, 0, p.N, p, dtau, p.istrU - 1, p.iend, 0, 0);
-  } else {
-    PLANE(k_pre_flxdiv, p.iend, p.jstrV - 1, p.jend, p.N, p, dtau, p.istrU - 1, p.iend, p.jstrV - 1, p.jend);
-  }
+  PLANE(k_pre_flxdiv, p.iend, p.jstrV - 1, p.jend, p.N, p, dtau);
   const std::vector<TPlan> plan = plan_batches(h);
   for (const TPlan& pl : plan) { int rc = tracer_pre_horiz(h, pl, nrhs, nnew, nstp, indx, dtau, cf_stp, cf_bak); if (rc) return rc; }
   if (wl) PLANE_JB((k_rhs_uv_horiz<false, true, 4>), 4, p.iend, p.jstr, p.jend, p.N, p, h->u(nrhs), h->v(nrhs));
@@ -899,13 +947,13 @@ int roms_step2d(roms_ctx* h) {
       if (h->ktiming) kt_end(h);
     } else {
       if (h->ktiming) kt_begin(h, "k_step2d(interior)");
-      k_step2d<0><<<g_, b_, 0, h->st>>>(p, si);
+      k_step2d<<<g_, b_, 0, h->st>>>(p, si);
       if (h->ktiming) kt_end(h);
     }
     CK(cudaEventRecord(h->ev_int[e], h->st));
     if (iif > 1) CK(cudaStreamWaitEvent(h->st2, h->ev_int[o], 0));
     if (h->ktiming) kt_begin(h, "k_step2d(ring)", h->st2);
-    k_step2d<0><<<g_, b_, 0, h->st2>>>(p, sr);
+    k_step2d<<<g_, b_, 0, h->st2>>>(p, sr);
     if (h->ktiming) kt_end(h, h->st2);
     h->launches += 2;
     if (p.wwall || p.ewall) {
@@ -966,10 +1014,9 @@ int roms_step2d(roms_ctx* h) {
     }
 #undef S2M_LAUNCH
   } else {
-    dim3 b_(S2_TX, S2_TY + (h->s2d_hw ? 2 : 0), 1), g_((p.iend + IOFF + 1 + S2_TX - 1) / S2_TX, (p.jend - p.jstr + 1 + S2_TY - 1) / S2_TY, 1);
+    dim3 b_(S2_TX, S2_TY, 1), g_((p.iend + IOFF + 1 + S2_TX - 1) / S2_TX, (p.jend - p.jstr + 1 + S2_TY - 1) / S2_TY, 1);
     if (h->ktiming) kt_begin(h, "k_step2d");
-    if (h->s2d_hw) k_step2d<1><<<g_, b_, 0, h->st>>>(p, s);
-    else k_step2d<0><<<g_, b_, 0, h->st>>>(p, s);
+    k_step2d<<<g_, b_, 0, h->st>>>(p, s);
     if (h->ktiming) kt_end(h);
     h->launches++;
   }
@@ -989,7 +1036,6 @@ int roms_step2d(roms_ctx* h) {
 }
 int roms_step3d_uv2(roms_ctx* h, int tile) {
   FLUSH_RHO(h);
-  h->flxdiv_valid = 0;
   (void)tile;
   CK(cudaSetDevice(h->device));
   const KP& p = h->kp;

@@ -1,0 +1,166 @@
+// tracer_tma.cuh -- horizontal tracer advection (pre_step3d4S.F:152-168 predictor C4, step3d_t_ISO.F:196-213 corrector UP3;
+// compute_horiz_tracer_fluxes.h:1-246) with every operand staged by the TMA unit (sm_100a).
+//
+// k_pre_t_horiz / k_t_horiz (kernels.cuh) fetch the nine tracer values, four volume fluxes and the own-point operands of a
+// point with ~25 scalar loads per level; ncu shows them waiting on those loads (long-scoreboard stall 13-24 cycles per issued
+// instruction, IPC 1.1-1.3, 33-45 % of the HBM peak).  Here a block owns a 32x8 tile and marches over KB levels.  A producer
+// warp issues, per level, cp.async.bulk.tensor copies of
+//     FlxU, FlxV                 (34x9 box: the faces c, c+1 / c, c+SX of every cell)
+//     [Hz, FlxDiv]               (32x8, predictor)
+//     per tracer  t(nrhs)        (36x12: the tile and its 2-cell halo)
+//                 t(nnew)  or, predictor, t(nstp), t(indx)   (32x8)
+// into a ring of NS shared-memory stages, each completing on an mbarrier, NS-1 levels ahead of the arithmetic; the 256 compute
+// threads only read shared memory and store results.  ONE tensor map per box shape describes the whole arena as a 2-D tensor
+// (SX columns x all rows of all planes: every field is a stack of (Mm+4)-row planes with the same pitch), so an operand is
+// addressed by (column, plane_row0 + row): three CUtensorMap objects serve every field, tracer and time level.
+// Points within two cells of a closed wall and river cells take the global-memory path of the original kernels (same
+// device functions).  Arithmetic: expression for expression that of k_pre_t_horiz / k_t_horiz.
+#pragma once
+#include <cuda.h>
+#include <cstdint>
+
+struct TmaMaps {
+  CUtensorMap t36x12, f34x9, o32x8;
+};
+template <int TB>
+struct TrcRows {      // first arena row (plane index x (Mm+4)) of level k=1 of every operand
+  int flxu, flxv, hz, fd;
+  int rhs[TB], tnew[TB], stp[TB], indx[TB];
+};
+#define TT_W 36
+#define TT_H 12
+#define TF_W 34
+#define TF_H 9
+#define TT_N (TT_W * TT_H)       // 432 doubles = 3456 B (multiple of 128)
+#define TF_N 320                 // 34*9 = 306 doubles, padded to 2560 B
+#define TO_N 256                 // 32*8
+template <bool PRE, int TB>
+struct TtmaLayout {
+  static constexpr int flxu = 0, flxv = TF_N, hz = 2 * TF_N, fd = 2 * TF_N + TO_N;
+  static constexpr int trc0 = PRE ? 2 * TF_N + 2 * TO_N : 2 * TF_N;
+  static constexpr int per_trc = PRE ? TT_N + 2 * TO_N : TT_N + TO_N;      // predictor: t(nrhs) tile, t(nstp), t(indx); corrector: t(nrhs) tile, t(nnew)
+  static constexpr int stage = trc0 + TB * per_trc;                          // doubles per stage
+  static constexpr unsigned bytes = (2 * TF_W * TF_H + (PRE ? 2 * TO_N : 0) + TB * (TT_N + (PRE ? 2 : 1) * TO_N)) * 8;   // bytes that arrive per stage
+};
+__device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, int x, int y, uint64_t* bar) {
+  asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%2, %3}], [%4];" ::"r"(s2m_u32(dst)), "l"(map), "r"(x),
+               "r"(y), "r"(s2m_u32(bar))
+               : "memory");
+}
+
+template <bool PRE, bool WALL, bool RIV, int TB, int KB, int NS>
+__global__ void __launch_bounds__(288, (PRE ? 2 : 3))
+k_t_horiz_tma(const __grid_constant__ KP p, const __grid_constant__ TrcBatch<TB> tb, const __grid_constant__ TmaMaps tm, const __grid_constant__ TrcRows<TB> tr,
+              double dtau, double cf_stp, double cf_bak) {
+  typedef TtmaLayout<PRE, TB> L;
+  extern __shared__ __align__(128) unsigned char ttma_raw[];
+  double* st = (double*)ttma_raw;                              // [NS][L::stage]
+  uint64_t* full = (uint64_t*)(st + NS * L::stage);            // [NS]
+  const int tid = threadIdx.x;
+  const int bx = blockIdx.x, by = blockIdx.y;
+  const int j0 = p.jstr + by * 8;
+  const int k0 = blockIdx.z * KB + 1;
+  const int nlev = min(KB, p.N - k0 + 1);
+  const int R = p.Mm + 4;
+  if (tid == 0) {
+    for (int q = 0; q < NS; ++q) s2m_mbar_init(&full[q], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  if (tid >= 256) {
+    // ---- producer warp: lane 0 arms the barrier of the stage, then the copies of one level
+    auto issue = [&](int q) {
+      if (q >= nlev || tid != 256) return;
+      double* sg = st + (q % NS) * L::stage;
+      uint64_t* bar = &full[q % NS];
+      const int krow = (k0 + q - 1) * R;
+      s2m_expect_tx(bar, L::bytes);
+      const int xo = bx * 32, yo = krow + j0 + 1;              // own column / row of the tile's first point
+      tma_load_2d(sg + L::flxu, &tm.f34x9, xo, tr.flxu + yo, bar);
+      tma_load_2d(sg + L::flxv, &tm.f34x9, xo, tr.flxv + yo, bar);
+      if (PRE) {
+        tma_load_2d(sg + L::hz, &tm.o32x8, xo, tr.hz + yo, bar);
+        tma_load_2d(sg + L::fd, &tm.o32x8, xo, tr.fd + yo, bar);
+      }
+#pragma unroll
+      for (int t = 0; t < TB; ++t) {
+        double* s0 = sg + L::trc0 + t * L::per_trc;
+        tma_load_2d(s0, &tm.t36x12, xo - 2, tr.rhs[t] + yo - 2, bar);
+        if (PRE) {
+          tma_load_2d(s0 + TT_N, &tm.o32x8, xo, tr.stp[t] + yo, bar);
+          tma_load_2d(s0 + TT_N + TO_N, &tm.o32x8, xo, tr.indx[t] + yo, bar);
+        } else {
+          tma_load_2d(s0 + TT_N, &tm.o32x8, xo, tr.tnew[t] + yo, bar);
+        }
+      }
+    };
+    for (int q = 0; q < NS; ++q) issue(q);
+    for (int q = 0; q < nlev; ++q) {
+      __syncthreads();                                         // every compute thread is done with level q: its stage is free
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      issue(q + NS);
+    }
+    return;
+  }
+  // ---- compute threads
+  const int tx = tid & 31, ty = tid >> 5;
+  const int i = bx * 32 + tx - IOFF, j = j0 + ty;
+  const bool active = i >= p.istr && i <= p.iend && j <= p.jend;
+  const ix_t c = CIDX(active ? i : p.istr, active ? j : p.jstr);
+  const ix_t SX = p.SX;
+  (void)SX;
+  TMask m;
+  m.u0 = m.u1 = m.u2 = m.u3 = m.v0 = m.v1 = m.v2 = m.v3 = 0.0;
+  double cdt = 0.0;
+  bool near = false;
+  RivFaces rf;
+  rf.any = false;
+  if (active) {
+    m = tmask_load(p, c);
+    cdt = (PRE ? dtau : p.dt) * p.pm[c] * p.pn[c];
+    near = WALL && near_wall(p, i, j);
+    if (RIV) rf = riv_faces(p, c);
+  }
+  for (int q = 0; q < nlev; ++q) {
+    const int k = k0 + q;
+    const double* sg = st + (q % NS) * L::stage;
+    s2m_wait(&full[q % NS], (uint32_t)((q / NS) & 1));
+    if (active) {
+      Flx4 f;
+      f.u0 = sg[L::flxu + ty * TF_W + tx]; f.u1 = sg[L::flxu + ty * TF_W + tx + 1];
+      f.v0 = sg[L::flxv + ty * TF_W + tx]; f.v1 = sg[L::flxv + (ty + 1) * TF_W + tx];
+      double Hz = 0.0, Hz_bak = 0.0;
+      if (PRE) { Hz = sg[L::hz + ty * 32 + tx]; Hz_bak = Hz + sg[L::fd + ty * 32 + tx]; }
+#pragma unroll
+      for (int t = 0; t < TB; ++t) {
+        const double* s0 = sg + L::trc0 + t * L::per_trc;
+        double dv;
+        if ((RIV && rf.any) || near) {
+          const double* __restrict__ t_rhs = tb.rhs[t];
+          if (RIV && rf.any) dv = tdiv_riv<!PRE>(p, t_rhs, c, i, j, k, m, f, near, rf, tb.itrc[t]);
+          else dv = tdiv<!PRE, true>(p, t_rhs, c, i, j, k, m, f);
+        } else {
+          // tflux4<UP, false> with the five values along each axis read from the staged tile
+          const double* sc = s0 + (ty + 2) * TT_W + tx + 2;
+          const double a0 = sc[-2], a1 = sc[-1], t2 = sc[0], a3 = sc[1], a4 = sc[2];
+          const double dA = (a1 - a0) * m.u0, dB = (t2 - a1) * m.u1, dC = (a3 - t2) * m.u2, dD = (a4 - a3) * m.u3;
+          const double FXi = tflux_fin<!PRE>(a1, t2, dA, dB, dC, f.u0);
+          const double FXip = tflux_fin<!PRE>(t2, a3, dB, dC, dD, f.u1);
+          const double b0 = sc[-2 * TT_W], b1 = sc[-TT_W], b3 = sc[TT_W], b4 = sc[2 * TT_W];
+          const double eA = (b1 - b0) * m.v0, eB = (t2 - b1) * m.v1, eC = (b3 - t2) * m.v2, eD = (b4 - b3) * m.v3;
+          const double FEj = tflux_fin<!PRE>(b1, t2, eA, eB, eC, f.v0);
+          const double FEjp = tflux_fin<!PRE>(t2, b3, eB, eC, eD, f.v1);
+          dv = FXip - FXi + FEjp - FEj;
+        }
+        if (PRE) {
+          const double ts = s0[TT_N + ty * 32 + tx];
+          R3(tb.tnew[t], c, k) = Hz_bak * (cf_stp * ts + cf_bak * s0[TT_N + TO_N + ty * 32 + tx]) - cdt * (dv);
+          R3(tb.indx[t], c, k) = Hz * ts;
+        } else {
+          R3(tb.tnew[t], c, k) = s0[TT_N + ty * 32 + tx] - cdt * (dv);
+        }
+      }
+    }
+    __syncthreads();
+  }
+}
