@@ -720,6 +720,7 @@ static TrcBatch<TB> make_batch(roms_ctx* h, const TPlan& pl, int nrhs, int nnew,
     else if (WALLED(h)) PLANE((kern<true, KB_T, false, TBn>), p.iend, p.jstr, p.jend, (p.N + KB_T - 1) / KB_T, p, __VA_ARGS__); \
     else PLANE((kern<false, KB_T, false, TBn>), p.iend, p.jstr, p.jend, (p.N + KB_T - 1) / KB_T, p, __VA_ARGS__);               \
   } while (0)
+#define TTMA_KB 8
 // ---- TMA-staged horizontal tracer kernels (tracer_tma.cuh)
 template <int TB>
 static TrcRows<TB> make_rows(roms_ctx* h, const TrcBatch<TB>& b) {
@@ -731,7 +732,6 @@ static TrcRows<TB> make_rows(roms_ctx* h, const TrcBatch<TB>& b) {
   for (int q = 0; q < TB; ++q) { r.rhs[q] = row(b.rhs[q]); r.tnew[q] = row(b.tnew[q]); r.stp[q] = row(b.stp[q]); r.indx[q] = row(b.indx[q]); }
   return r;
 }
-#define TTMA_KB 8
 template <bool PRE, bool WALL, bool RIV, int TB, int NS>
 static int t_tma_launch(roms_ctx* h, const TrcBatch<TB>& b, double dtau, double cf_stp, double cf_bak) {
   const KP& p = h->kp;
@@ -751,6 +751,25 @@ static int t_tma_variant(roms_ctx* h, const TrcBatch<TB>& b, double dtau, double
   if (h->kp.rivers) return t_tma_launch<PRE, true, true, TB, NS>(h, b, dtau, cf_stp, cf_bak);
   if (WALLED(h)) return t_tma_launch<PRE, true, false, TB, NS>(h, b, dtau, cf_stp, cf_bak);
   return t_tma_launch<PRE, false, false, TB, NS>(h, b, dtau, cf_stp, cf_bak);
+}
+// TMA-staged horizontal momentum RHS (k_rhs_uv_tma)
+template <bool UP, bool WALL>
+static int rhs_uv_tma_launch(roms_ctx* h, const double* u, const double* v) {
+  const KP& p = h->kp;
+  constexpr int NS = 3;
+  const int R = h->c.Mm + 4;
+  auto row = [&](const double* a) { return (int)(((size_t)(a - h->arena) / (size_t)p.SXY) * (size_t)R); };
+  RhsRows r;
+  r.u = row(u); r.v = row(v); r.flxu = row(p.FlxU); r.flxv = row(p.FlxV); r.hz = row(p.Hz); r.ru = row(p.ru); r.rv = row(p.rv);
+  const size_t sm_ = (size_t)NS * RhsLayout::stage * sizeof(double) + NS * sizeof(unsigned long long);
+  static bool attr_ = false;
+  if (!attr_) { CK(cudaFuncSetAttribute((k_rhs_uv_tma<UP, WALL, TTMA_KB, NS>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_)); attr_ = true; }
+  dim3 b_(288, 1, 1), g_((p.iend + IOFF + 1 + 31) / 32, (p.jend - p.jstr + 1 + 7) / 8, (p.N + TTMA_KB - 1) / TTMA_KB);
+  if (h->ktiming) kt_begin(h, UP ? "k_rhs_uv_tma<UP3>" : "k_rhs_uv_tma<C4>");
+  k_rhs_uv_tma<UP, WALL, TTMA_KB, NS><<<g_, b_, sm_, h->st>>>(p, h->tmaps, r, u, v);
+  if (h->ktiming) kt_end(h);
+  h->launches++;
+  return 0;
 }
 static int tracer_pre_horiz(roms_ctx* h, const TPlan& pl, int nrhs, int nnew, int nstp, int indx, double dtau, double cf_stp, double cf_bak) {
   const KP& p = h->kp;
@@ -855,7 +874,8 @@ int roms_pre_step3d(roms_ctx* h, int tile) {
   PLANE(k_pre_flxdiv, p.iend, p.jstrV - 1, p.jend, p.N, p, dtau);
   const std::vector<TPlan> plan = plan_batches(h);
   for (const TPlan& pl : plan) { int rc = tracer_pre_horiz(h, pl, nrhs, nnew, nstp, indx, dtau, cf_stp, cf_bak); if (rc) return rc; }
-  if (wl) PLANE_JB((k_rhs_uv_horiz<false, true, 4>), 4, p.iend, p.jstr, p.jend, p.N, p, h->u(nrhs), h->v(nrhs));
+  if (h->t_tma) { int rc = wl ? rhs_uv_tma_launch<false, true>(h, h->u(nrhs), h->v(nrhs)) : rhs_uv_tma_launch<false, false>(h, h->u(nrhs), h->v(nrhs)); if (rc) return rc; }
+  else if (wl) PLANE_JB((k_rhs_uv_horiz<false, true, 4>), 4, p.iend, p.jstr, p.jend, p.N, p, h->u(nrhs), h->v(nrhs));
   else PLANE_JB((k_rhs_uv_horiz<false, false, 4>), 4, p.iend, p.jstr, p.jend, p.N, p, h->u(nrhs), h->v(nrhs));
   PLANE(k_rd_bott_drag, p.iend, p.jstrV - 1, p.jend, 1, p, h->u(nstp), h->v(nstp));
   for (const TPlan& pl : plan) { int rc = tracer_vert(h, 0, pl, nrhs, nnew, dtau); if (rc) return rc; }
@@ -878,7 +898,8 @@ int roms_step3d_uv1(roms_ctx* h, int tile) {
   CK(cudaSetDevice(h->device));
   const KP& p = h->kp;
   const int nrhs = h->nrhs, nnew = h->nnew;
-  if (WALLED(h)) PLANE_JB((k_rhs_uv_horiz<true, true, 1>), 1, p.iend, p.jstr, p.jend, p.N, p, h->u(nrhs), h->v(nrhs));
+  if (h->t_tma) { int rc = WALLED(h) ? rhs_uv_tma_launch<true, true>(h, h->u(nrhs), h->v(nrhs)) : rhs_uv_tma_launch<true, false>(h, h->u(nrhs), h->v(nrhs)); if (rc) return rc; }
+  else if (WALLED(h)) PLANE_JB((k_rhs_uv_horiz<true, true, 1>), 1, p.iend, p.jstr, p.jend, p.N, p, h->u(nrhs), h->v(nrhs));
   else PLANE_JB((k_rhs_uv_horiz<true, false, 1>), 1, p.iend, p.jstr, p.jend, p.N, p, h->u(nrhs), h->v(nrhs));
   COLUMN((k_uv_vert<1, 0>), 2, p.iend, p.jstr, p.jend, p, h->u(nrhs), h->u(nnew), (const double*)nullptr, (double*)nullptr, h->c.dt, 0.0, 0.0);
   COLUMN((k_uv_vert<1, 1>), 2, p.iend, p.jstrV, p.jend, p, h->v(nrhs), h->v(nnew), (const double*)nullptr, (double*)nullptr, h->c.dt, 0.0, 0.0);

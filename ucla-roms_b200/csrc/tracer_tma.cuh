@@ -164,3 +164,108 @@ k_t_horiz_tma(const __grid_constant__ KP p, const __grid_constant__ TrcBatch<TB>
     __syncthreads();
   }
 }
+
+// ------------------------------------------------------------------------------------------------
+// Horizontal momentum right-hand side (compute_horiz_rhs_uv_terms.h:1-291: Coriolis + UP3 / C4 advection of u and v) with the
+// same TMA staging: per level the 36x12 boxes of u, v, FlxU, FlxV, Hz and the
+// 32x8 boxes of ru, rv (the pressure-gradient term left there by prsgrd).  Replaces k_rhs_uv_horiz (~110 scalar loads per
+// point through L1).  Points within two cells of a closed wall take rhs_uv_point<UP, true> on global memory.
+struct RhsRows { int u, v, flxu, flxv, hz, ru, rv; };
+struct RhsLayout {
+  static constexpr int u = 0, v = TT_N, fu = 2 * TT_N, fv = 3 * TT_N, hz = 4 * TT_N, ru = 5 * TT_N, rv = 5 * TT_N + TO_N;
+  static constexpr int stage = 5 * TT_N + 2 * TO_N;                        // 2672 doubles = 21376 B (multiple of 128)
+  static constexpr unsigned bytes = (5 * TT_N + 2 * TO_N) * 8;
+};
+template <bool UP, bool WALL, int KB, int NS>
+__global__ void __launch_bounds__(288, 3)
+k_rhs_uv_tma(const __grid_constant__ KP p, const __grid_constant__ TmaMaps tm, const __grid_constant__ RhsRows tr, const double* __restrict__ u, const double* __restrict__ v) {
+  typedef RhsLayout L;
+  extern __shared__ __align__(128) unsigned char ttma_raw[];
+  double* st = (double*)ttma_raw;
+  uint64_t* full = (uint64_t*)(st + NS * L::stage);
+  const int tid = threadIdx.x;
+  const int bx = blockIdx.x, by = blockIdx.y;
+  const int j0 = p.jstr + by * 8;
+  const int k0 = blockIdx.z * KB + 1;
+  const int nlev = min(KB, p.N - k0 + 1);
+  const int R = p.Mm + 4;
+  if (tid == 0) {
+    for (int q = 0; q < NS; ++q) s2m_mbar_init(&full[q], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  if (tid >= 256) {
+    auto issue = [&](int q) {
+      if (q >= nlev || tid != 256) return;
+      double* sg = st + (q % NS) * L::stage;
+      uint64_t* bar = &full[q % NS];
+      const int xo = bx * 32, yo = (k0 + q - 1) * R + j0 + 1;
+      s2m_expect_tx(bar, L::bytes);
+      tma_load_2d(sg + L::u, &tm.t36x12, xo - 2, tr.u + yo - 2, bar);
+      tma_load_2d(sg + L::v, &tm.t36x12, xo - 2, tr.v + yo - 2, bar);
+      tma_load_2d(sg + L::fu, &tm.t36x12, xo - 2, tr.flxu + yo - 2, bar);
+      tma_load_2d(sg + L::fv, &tm.t36x12, xo - 2, tr.flxv + yo - 2, bar);
+      tma_load_2d(sg + L::hz, &tm.t36x12, xo - 2, tr.hz + yo - 2, bar);     // (a box must start on a 16-byte boundary: even column)
+      tma_load_2d(sg + L::ru, &tm.o32x8, xo, tr.ru + yo, bar);
+      tma_load_2d(sg + L::rv, &tm.o32x8, xo, tr.rv + yo, bar);
+    };
+    for (int q = 0; q < NS; ++q) issue(q);
+    for (int q = 0; q < nlev; ++q) {
+      __syncthreads();
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      issue(q + NS);
+    }
+    return;
+  }
+  const int tx = tid & 31, ty = tid >> 5;
+  const int i = bx * 32 + tx - IOFF, j = j0 + ty;
+  const bool active = i >= p.istr && i <= p.iend && j <= p.jend;
+  const ixr_t c = CIDX(active ? i : p.istr, active ? j : p.jstr);
+  const bool near = active && WALL && near_wall(p, i, j);
+  double fomn_c = 0.0, fomn_w = 0.0, fomn_s = 0.0;
+  if (active) { fomn_c = p.fomn[c]; fomn_w = p.fomn[c - 1]; fomn_s = p.fomn[c - p.SX]; }
+  const int cl = (ty + 2) * TT_W + tx + 2;          // this thread's point inside a 36x12 box
+  for (int q = 0; q < nlev; ++q) {
+    const int k = k0 + q;
+    const double* sg = st + (q % NS) * L::stage;
+    s2m_wait(&full[q % NS], (uint32_t)((q / NS) & 1));
+    if (active) {
+      double ru, rv;
+      bool dou = true, dov = true;
+      if (near) {
+        dov = j >= p.jstrV; dou = i >= p.istrU;
+        rhs_uv_point<UP, true>(p, u, v, c, i, j, k, dov, ru, rv);
+      } else {
+        // rhs_uv_point<UP, false> on the staged boxes (row pitch TT_W instead of SX, level offset 0)
+        const double* U = sg + L::u;
+        const double* V = sg + L::v;
+        const double* FU = sg + L::fu;
+        const double* FV = sg + L::fv;
+        const double* sh = sg + L::hz + cl;
+        const double cf0 = 0.5 * sh[0] * (fomn_c);
+        const double cfw = 0.5 * sh[-1] * (fomn_w);
+        const double v00 = V[cl], u00 = U[cl];
+        const double UFx_c = cf0 * (v00 + V[cl + TT_W]);
+        const double UFx_w = cfw * (V[cl - 1] + V[cl - 1 + TT_W]);
+        ru = sg[L::ru + ty * 32 + tx] + 0.5 * (UFx_c + UFx_w);
+        const double UFx_i = flux_along<UP, false>(p, U, FU, cl, 1, 1);
+        const double UFx_im = flux_along<UP, false>(p, U, FU, cl - 1, 1, 1);
+        const double UFe_jp = flux_cross<UP, false>(p, U, FV, cl + TT_W, TT_W, 1, 1);
+        const double UFe_j = flux_cross<UP, false>(p, U, FV, cl, TT_W, 1, 1);
+        ru = ru - UFx_i + UFx_im - UFe_jp + UFe_j;
+        const double cfs = 0.5 * sh[-TT_W] * (fomn_s);
+        const double VFe_c = cf0 * (u00 + U[cl + 1]);
+        const double VFe_s = cfs * (U[cl - TT_W] + U[cl - TT_W + 1]);
+        rv = sg[L::rv + ty * 32 + tx] - 0.5 * (VFe_c + VFe_s);
+        const double VFx_ip = flux_cross<UP, false>(p, V, FU, cl + 1, 1, TT_W, 1);
+        const double VFx_i = flux_cross<UP, false>(p, V, FU, cl, 1, TT_W, 1);
+        const double VFe_j = flux_along<UP, false>(p, V, FV, cl, TT_W, 1);
+        const double VFe_jm = flux_along<UP, false>(p, V, FV, cl - TT_W, TT_W, 1);
+        rv = rv - VFx_ip + VFx_i - VFe_j + VFe_jm;
+      }
+      if (dou) R3(p.ru, c, k) = ru;
+      if (dov) R3(p.rv, c, k) = rv;
+    }
+    __syncthreads();
+  }
+}
