@@ -32,7 +32,7 @@ KERNEL_WORDS = {
     "k_rho_eos": lambda t: (6 if t[0] == "true" else 4, 3), "k_set_huv": (5, 3), "k_omega": (6, 3),
     "k_prsgrd_vert": lambda t: (5 if t[0] == "true" else 3, 3),
     "k_rho_prs_vert": lambda t: (8 if t[0] == "true" else 6, 3),   # rho_eos fused with the vertical part of prsgrd: T,S,Hz,z_r read; rho1,qp1,P,rho written
-    "k_prsgrd_horiz": lambda t: (8 if t[0] == "true" else 6, 3),
+    "k_prsgrd_horiz": lambda t: (8 if t[0] == "true" else 6, 3), "k_prsgrd_tma": (8, 3),
     "k_pre_flxdiv": (5, 3), "k_rhs_uv_horiz": (9, 3), "k_rhs_uv_tma": (9, 3),
     "k_pre_t_horiz_tma": lambda t: (13, 3), "k_t_horiz_tma": lambda t: (8, 3),     # TB = 2 in every launch of the TMA kernels (3+5*2, 2+3*2); TB = 1 launches over-count
     # tracer kernels, TB tracers per launch: operands shared by the batch count once

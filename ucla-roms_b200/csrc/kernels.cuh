@@ -544,9 +544,10 @@ __device__ __forceinline__ void prs_fc_rx(const KP& p, ix_t X, ix_t d, int k, co
   } else rx = (R3(rho, X, k) - R3(rho, X - d, k)) * m;
 }
 // second half of prsgrd.F:330-421 for one direction: harmonic means of the three first differences -> ru / rv
+// prs_tail_core: the arithmetic, operands in registers (shared by the global-memory and the TMA-staged kernels)
 template <bool NONLIN>
-__device__ __forceinline__ double prs_tail(const KP& p, ix_t c, ix_t d, int k, double dn, const double* __restrict__ rho, double FCa, double FCb, double FCc,
-                                           double rxa, double rxb, double rxc, double q1, double q2v, double z1, double z2) {
+__device__ __forceinline__ double prs_tail_core(const KP& p, double dn, double FCa, double FCb, double FCc, double rxa, double rxb, double rxc, double q1, double q2v,
+                                                double z1, double z2, double rho_c, double rho_m, double Hz_c, double Hz_m, double P_m, double P_c) {
   const double qp2 = 0.0000172, OneFifth = 0.2, OneTwelfth = 1.0 / 12.0, epsil = 0.0;
   const double HalfGRho = 0.5 * (p.g / p.rho0);
   // dZx, dRx at c-d ("m") and c ("c"): harmonic means (prsgrd.F:330-345).  The quotient is formed unconditionally and
@@ -563,11 +564,16 @@ __device__ __forceinline__ double prs_tail(const KP& p, ix_t c, ix_t d, int k, d
     dRx_m = dRx_m - q1 * dZx_m * (1.0 + 2.0 * qp2 * z1);
     dRx_c = dRx_c - q2v * dZx_c * (1.0 + 2.0 * qp2 * z2);
   }
-  const double rho_c = R3(rho, c, k), rho_m = R3(rho, c - d, k);
-  return 0.5 * (R3(p.Hz, c, k) + R3(p.Hz, c - d, k)) * dn *
-         (R3(p.P, c - d, k) - R3(p.P, c, k) -
+  return 0.5 * (Hz_c + Hz_m) * dn *
+         (P_m - P_c -
           HalfGRho * ((rho_c + rho_m) * (z2 - z1) -
                       OneFifth * ((dRx_c - dRx_m) * (z2 - z1 - OneTwelfth * (dZx_c + dZx_m)) - (dZx_c - dZx_m) * (rho_c - rho_m - OneTwelfth * (dRx_c + dRx_m)))));
+}
+template <bool NONLIN>
+__device__ __forceinline__ double prs_tail(const KP& p, ix_t c, ix_t d, int k, double dn, const double* __restrict__ rho, double FCa, double FCb, double FCc,
+                                           double rxa, double rxb, double rxc, double q1, double q2v, double z1, double z2) {
+  return prs_tail_core<NONLIN>(p, dn, FCa, FCb, FCc, rxa, rxb, rxc, q1, q2v, z1, z2, R3(rho, c, k), R3(rho, c - d, k), R3(p.Hz, c, k), R3(p.Hz, c - d, k),
+                               R3(p.P, c - d, k), R3(p.P, c, k));
 }
 // rows next to a closed wall: the three difference positions (c-d, c, c+d) are displaced by oA, oB, oC (see jclamp)
 template <bool NONLIN>

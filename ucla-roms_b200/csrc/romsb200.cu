@@ -771,6 +771,25 @@ static int rhs_uv_tma_launch(roms_ctx* h, const double* u, const double* v) {
   h->launches++;
   return 0;
 }
+// TMA-staged horizontal pressure gradient (k_prsgrd_tma, nonlinear split EOS)
+template <bool WALL>
+static int prsgrd_tma_launch(roms_ctx* h) {
+  const KP& p = h->kp;
+  constexpr int NS = 3;
+  const int R = h->c.Mm + 4;
+  auto row = [&](const double* a) { return (int)(((size_t)(a - h->arena) / (size_t)p.SXY) * (size_t)R); };
+  PrsRows r;
+  r.zr = row(p.z_r); r.r1 = row(p.rho1); r.q1 = row(p.qp1); r.P = row(p.P); r.rho = row(p.rho); r.hz = row(p.Hz);
+  const size_t sm_ = (size_t)NS * PrsLayout::stage * sizeof(double) + NS * sizeof(unsigned long long);
+  static bool attr_ = false;
+  if (!attr_) { CK(cudaFuncSetAttribute((k_prsgrd_tma<WALL, TTMA_KB, NS>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_)); attr_ = true; }
+  dim3 b_(288, 1, 1), g_((p.iend + IOFF + 1 + 31) / 32, (p.jend - p.jstr + 1 + 7) / 8, (p.N + TTMA_KB - 1) / TTMA_KB);
+  if (h->ktiming) kt_begin(h, "k_prsgrd_tma");
+  k_prsgrd_tma<WALL, TTMA_KB, NS><<<g_, b_, sm_, h->st>>>(p, h->tmaps, r);
+  if (h->ktiming) kt_end(h);
+  h->launches++;
+  return 0;
+}
 static int tracer_pre_horiz(roms_ctx* h, const TPlan& pl, int nrhs, int nnew, int nstp, int indx, double dtau, double cf_stp, double cf_bak) {
   const KP& p = h->kp;
   if (h->t_tma) {
@@ -851,6 +870,7 @@ int roms_prsgrd(roms_ctx* h) {
   }
   if (h->c.nonlin_eos) {
     if (!fused) COLUMN(k_prsgrd_vert<true>, 0, p.Lm, 0, p.Mm, p);
+    if (h->t_tma) return WALLED(h) ? prsgrd_tma_launch<true>(h) : prsgrd_tma_launch<false>(h);
     if (WALLED(h)) PLANE((k_prsgrd_horiz<true, true, KB_PRS>), p.iend, p.jstr, p.jend, (p.N + KB_PRS - 1) / KB_PRS, p);
     else PLANE((k_prsgrd_horiz<true, false, KB_PRS>), p.iend, p.jstr, p.jend, (p.N + KB_PRS - 1) / KB_PRS, p);
   } else {

@@ -269,3 +269,106 @@ k_rhs_uv_tma(const __grid_constant__ KP p, const __grid_constant__ TmaMaps tm, c
     __syncthreads();
   }
 }
+
+// ------------------------------------------------------------------------------------------------
+// prsgrd.F:231-421, horizontal part (nonlinear split EOS), with TMA staging: per level the 36x12 boxes of z_r, rho1, qp1
+// (the four points c-2d..c+d of both directions) and the 34x9 boxes of P, rho, Hz (origin (i0-2, j0-1): the points c-d, c).
+// Replaces k_prsgrd_horiz<true, *, *>.  Points within two cells of a closed wall take prs_dir_cl on global memory.
+struct PrsRows { int zr, r1, q1, P, rho, hz; };
+struct PrsLayout {
+  static constexpr int zr = 0, r1 = TT_N, q1 = 2 * TT_N, P = 3 * TT_N, rho = 3 * TT_N + TF_N, hz = 3 * TT_N + 2 * TF_N;
+  static constexpr int stage = 3 * TT_N + 3 * TF_N;                        // 2256 doubles = 18048 B (multiple of 128)
+  static constexpr unsigned bytes = (3 * TT_N + 3 * TF_W * TF_H) * 8;
+};
+// prs_dir<true> on staged boxes: zr, r1, q1 share the 36-wide layout (centre cl, stride d), P, rho, Hz the 34-wide one (centre ch, stride dh)
+__device__ __forceinline__ double prs_dir_s(const KP& p, const double* __restrict__ zr, const double* __restrict__ r1, const double* __restrict__ q1v, int cl, int d,
+                                            const double* __restrict__ sP, const double* __restrict__ srho, const double* __restrict__ sHz, int ch, int dh, double m1,
+                                            double m2, double m3, double dn) {
+  const double qp2 = 0.0000172;
+  const double z0 = zr[cl - 2 * d], z1 = zr[cl - d], z2 = zr[cl], z3 = zr[cl + d];
+  const double FCa = (z1 - z0) * m1, FCb = (z2 - z1) * m2, FCc = (z3 - z2) * m3;   // FC(i-1), FC(i), FC(i+1)
+  const double a0 = r1[cl - 2 * d], a1 = r1[cl - d], a2 = r1[cl], a3 = r1[cl + d];
+  const double b0 = q1v[cl - 2 * d], b1 = q1v[cl - d], b2 = q1v[cl], b3 = q1v[cl + d];
+  double dpth = -0.5 * (z1 + z0);
+  const double rxa = (a1 - a0 + (b1 - b0) * dpth * (1.0 - qp2 * dpth)) * m1;
+  dpth = -0.5 * (z2 + z1);
+  const double rxb = (a2 - a1 + (b2 - b1) * dpth * (1.0 - qp2 * dpth)) * m2;
+  dpth = -0.5 * (z3 + z2);
+  const double rxc = (a3 - a2 + (b3 - b2) * dpth * (1.0 - qp2 * dpth)) * m3;
+  return prs_tail_core<true>(p, dn, FCa, FCb, FCc, rxa, rxb, rxc, b1, b2, z1, z2, srho[ch], srho[ch - dh], sHz[ch], sHz[ch - dh], sP[ch - dh], sP[ch]);
+}
+template <bool WALL, int KB, int NS>
+__global__ void __launch_bounds__(288, 3) k_prsgrd_tma(const __grid_constant__ KP p, const __grid_constant__ TmaMaps tm, const __grid_constant__ PrsRows tr) {
+  typedef PrsLayout L;
+  extern __shared__ __align__(128) unsigned char ttma_raw[];
+  double* st = (double*)ttma_raw;
+  uint64_t* full = (uint64_t*)(st + NS * L::stage);
+  const int tid = threadIdx.x;
+  const int bx = blockIdx.x, by = blockIdx.y;
+  const int j0 = p.jstr + by * 8;
+  const int k0 = blockIdx.z * KB + 1;
+  const int nlev = min(KB, p.N - k0 + 1);
+  const int R = p.Mm + 4;
+  if (tid == 0) {
+    for (int q = 0; q < NS; ++q) s2m_mbar_init(&full[q], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  if (tid >= 256) {
+    auto issue = [&](int q) {
+      if (q >= nlev || tid != 256) return;
+      double* sg = st + (q % NS) * L::stage;
+      uint64_t* bar = &full[q % NS];
+      const int xo = bx * 32, yo = (k0 + q - 1) * R + j0 + 1;
+      s2m_expect_tx(bar, L::bytes);
+      tma_load_2d(sg + L::zr, &tm.t36x12, xo - 2, tr.zr + yo - 2, bar);
+      tma_load_2d(sg + L::r1, &tm.t36x12, xo - 2, tr.r1 + yo - 2, bar);
+      tma_load_2d(sg + L::q1, &tm.t36x12, xo - 2, tr.q1 + yo - 2, bar);
+      tma_load_2d(sg + L::P, &tm.f34x9, xo - 2, tr.P + yo - 1, bar);
+      tma_load_2d(sg + L::rho, &tm.f34x9, xo - 2, tr.rho + yo - 1, bar);
+      tma_load_2d(sg + L::hz, &tm.f34x9, xo - 2, tr.hz + yo - 1, bar);
+    };
+    for (int q = 0; q < NS; ++q) issue(q);
+    for (int q = 0; q < nlev; ++q) {
+      __syncthreads();
+      asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+      issue(q + NS);
+    }
+    return;
+  }
+  const int tx = tid & 31, ty = tid >> 5;
+  const int i = bx * 32 + tx - IOFF, j = j0 + ty;
+  const bool active = i >= p.istr && i <= p.iend && j <= p.jend;
+  const ix_t c = CIDX(active ? i : p.istr, active ? j : p.jstr);
+  const ix_t SX = p.SX;
+  const bool near = active && WALL && near_wall(p, i, j);
+  double dnu = 0, dmv = 0, mu1 = 0, mu2 = 0, mu3 = 0, mv1 = 0, mv2 = 0, mv3 = 0;
+  ix_t oA = 0, oB = 0, oC = 0, iA = 0, iB = 0, iC = 0;
+  if (active) {
+    dnu = p.dn_u[c]; dmv = p.dm_v[c];
+    mu1 = p.umask[c - 1]; mu2 = p.umask[c]; mu3 = p.umask[c + 1];
+    mv1 = p.vmask[c - SX]; mv2 = p.vmask[c]; mv3 = p.vmask[c + SX];
+    if (near) {
+      oA = jclamp(p, j - 1, p.jstrV, p.jend); oB = jclamp(p, j, p.jstrV, p.jend); oC = jclamp(p, j + 1, p.jstrV, p.jend);
+      iA = iclamp(p, i - 1, p.istrU, p.iend); iB = iclamp(p, i, p.istrU, p.iend); iC = iclamp(p, i + 1, p.istrU, p.iend);
+    }
+  }
+  const int cl = (ty + 2) * TT_W + tx + 2, ch = (ty + 1) * TF_W + tx + 2;
+  for (int q = 0; q < nlev; ++q) {
+    const int k = k0 + q;
+    const double* sg = st + (q % NS) * L::stage;
+    s2m_wait(&full[q % NS], (uint32_t)((q / NS) & 1));
+    if (active) {
+      if (near) {     // prsgrd.F:288-310: FC,rx exist on rows jstrV..jend / columns istrU..iend between walls, copied outward
+        if (i >= p.istrU) R3(p.ru, c, k) = prs_dir_cl<true>(p, c, 1, k, p.umask, dnu, p.rho, iA, iB, iC);
+        if (j >= p.jstrV) R3(p.rv, c, k) = prs_dir_cl<true>(p, c, SX, k, p.vmask, dmv, p.rho, oA, oB, oC);
+      } else {
+        const double ru = prs_dir_s(p, sg + L::zr, sg + L::r1, sg + L::q1, cl, 1, sg + L::P, sg + L::rho, sg + L::hz, ch, 1, mu1, mu2, mu3, dnu);
+        const double rv = prs_dir_s(p, sg + L::zr, sg + L::r1, sg + L::q1, cl, TT_W, sg + L::P, sg + L::rho, sg + L::hz, ch, TF_W, mv1, mv2, mv3, dmv);
+        R3(p.ru, c, k) = ru;
+        R3(p.rv, c, k) = rv;
+      }
+    }
+    __syncthreads();
+  }
+}
