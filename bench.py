@@ -47,7 +47,7 @@ KERNEL_WORDS = {
     "k_set_depth": (3, 3), "k_step2d_zeta": (24, 2), "k_step2d_uv": (23, 2), "k_rd_bott_drag": (3, 2),
     "k_visc3d": (7, 3),      # row f1: u,v(nstp),Hz read; u,v(3-nstp) read+written
     "k_t3dmix": (4, 3),      # row f1: t(nrhs),Hz read; t(nnew) read+written
-    "k_step2d_tma": (34, 2), "k_step2d_march": (34, 2),
+    "k_step2d_tma": (34, 2), "k_step2d_march": (34, 2), "k_step2d_hyb": (34, 2),
     "k_step2d": (34, 2),     # 9 state R + 3 W + 12 static R + 10 averages RW per 2-D point and substep
 }
 
@@ -75,15 +75,15 @@ def peaks():
 
 
 def ncu_traffic(kernel):
-    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel` from the committed `ncu --set full` capture of this
-    workload (profiles/r1_ncu_traffic_v3.json, made from gpurun_out/prof3/full_v3.ncu-rep and the v2 captures); None if the kernel is not in it."""
-    p = os.path.join(ROOT, "profiles", "r1_ncu_traffic_v3.json")
+    """dram__bytes_read.sum + dram__bytes_write.sum per launch of `kernel` from the committed `ncu --set full` capture of the channel
+    workload (profiles/r2_ncu_traffic.json, made by tools/ncu_summary.py from the raw pages of that capture); None if the kernel is not in it."""
+    p = os.path.join(ROOT, "profiles", "r2_ncu_traffic.json")
     if not os.path.exists(p):
         return None
     norm = lambda n: n.replace("(", "").replace(")", "").replace(" ", "").replace("true", "1").replace("false", "0")
     want = norm(kernel)
     for k, v in json.load(open(p)).items():
-        if norm(k) == want or norm(k).split("<")[0] == want:
+        if norm(k) == want or norm(k).split("<")[0] == want.split("<")[0]:
             return v["dram_bytes"]
     return None
 
@@ -413,7 +413,7 @@ def main():
                     "traffic": ncu_traffic(top[0]) if (Lm, Mm, N) == (1024, 1024, 64) else None,
                     "peak_source": peak_src, "algorithmic_bytes_per_launch": words * 8.0 * npts, "avg_launch_ms": avg_ms,
                     "launches_per_step": top[1] / a.steps, "share_of_step": top[2] / tot,
-                    "traffic_source": "profiles/r1_ncu_traffic_v3.json (ncu --set full, dram read+write bytes per launch, this workload)"}
+                    "traffic_source": "profiles/r2_ncu_traffic.json (ncu --set full, dram read+write bytes per launch, this workload)"}
         if a.kernel_table:
             with open(a.kernel_table, "w") as f:
                 f.write(f"# per-kernel CUDA-event times, {a.steps} steps, {workload}\n# kernel launches total_ms avg_ms share algorithmic_GB/s\n")

@@ -154,12 +154,13 @@ def test_one_step_and_100_steps_channel(walls, topo, ew, mix):
     g.close(); o.close()
 
 
-@pytest.mark.parametrize("env", [{"ROMS_S2D_TMA": "0"}, {"ROMS_S2D_TMA": "2", "ROMS_S2D_ROWS": "5"}, {"ROMS_S2D_TMA": "6", "ROMS_S2D_ROWS": "7"},
-                                 {"ROMS_UV2_FUSED": "0"}])
+@pytest.mark.parametrize("env", [{"ROMS_S2D_TMA": "0"}, {"ROMS_S2D_TMA": "1"}, {"ROMS_S2D_TMA": "2", "ROMS_S2D_ROWS": "5"}, {"ROMS_S2D_TMA": "6", "ROMS_S2D_ROWS": "7"},
+                                 {"ROMS_S2D_TMA": "12", "ROMS_S2D_ROWS": "9"}, {"ROMS_UV2_FUSED": "0"}, {"ROMS_T_TMA": "0"}])
 @pytest.mark.parametrize("closed", [False, True])
 def test_kernel_variants_are_bit_identical(env, closed, monkeypatch):
-    """The shipped alternatives of the barotropic substep (tile kernel, TMA ring of another shape, register marching; ragged row
-    blocks on purpose) and the unfused step3d_uv2 passes: every variant must reproduce the oracle exactly like the defaults do."""
+    """The shipped alternatives of the barotropic substep (tile kernel, full TMA ring, another ring shape, register marching, the
+    default hybrid with ragged row blocks), the unfused step3d_uv2 passes and the scalar-load plane kernels: every variant must
+    reproduce the oracle exactly like the defaults do."""
     for k, v in env.items():
         monkeypatch.setenv(k, v)
     cfg, st = cases.channel(70, 45, 12, ns_walls=True, seamount=closed, island=closed, ew_walls=closed)

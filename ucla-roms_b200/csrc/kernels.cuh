@@ -1622,6 +1622,7 @@ __global__ void __launch_bounds__(S2_TX * S2_TY, LB_S2D) k_step2d(const __grid_c
 }
 #include "step2d_tma.cuh"
 #include "step2d_march.cuh"
+#include "step2d_hyb.cuh"
 #include "tracer_tma.cuh"
 
 // zeta_new at any point of the rho-range incl. wall rows, wall columns and basin corners (zetabc.F:39-81)

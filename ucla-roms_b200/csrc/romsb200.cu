@@ -69,8 +69,9 @@ struct roms_ctx {
   int fuse_rho = 1;       // a rho_eos call is deferred; if prsgrd follows (main.F:397-413, 430-445) both run as one fused column kernel
   int rho_pending = 0;    // time index of the deferred rho_eos (0: none)
   int uv2_sm = 1;     // k_uv2_pass1 with the column parked in shared memory (1.0 -> 0.78 ms on B200); off when the column is too tall
-  int s2d_tma = 1;    // barotropic substep as the TMA-fed marching kernel k_step2d_tma; 0: the tile kernel k_step2d
-  int s2d_rows = 16;  // rows per block of the marching kernels (measured best on B200: profiles/r2_step2d_variants.txt)
+  int s2d_tma = 12;   // barotropic kernel: 12 k_step2d_hyb<64,4> (shipped), 0 tile kernel k_step2d, 1-5 k_step2d_tma shapes, 6-11 k_step2d_march, 13-15 other hyb shapes
+  int s2d_rows = 0;   // rows per block of the marching kernels; 0: one-wave rule for k_step2d_hyb, 16 for the others
+  int n_sm = 148;
   int uv2_fused = 1;  // step3d_uv2 passes 0 and 1 in one shared-memory column kernel (k_uv2_sm)
   int tb_max = 4;     // most tracers per launch of the tracer kernels (ROMS_TB = 1, 2 or 4)
   int use_smem = 0;   // measured on B200 (profiles/r1_scratch_policy.txt): occupancy beats shared-memory scratch
@@ -282,7 +283,8 @@ int roms_create(const roms_cfg* cfg, int device, roms_ctx** out) {
   if (const char* e = getenv("ROMS_OVERLAP")) h->overlap = atoi(e);
   if (const char* e = getenv("ROMS_T_TMA")) h->t_tma = atoi(e);
   if (const char* e = getenv("ROMS_S2D_TMA")) h->s2d_tma = atoi(e);
-  if (const char* e = getenv("ROMS_S2D_ROWS")) h->s2d_rows = atoi(e) > 0 ? atoi(e) : 32;
+  if (const char* e = getenv("ROMS_S2D_ROWS")) h->s2d_rows = atoi(e) > 0 ? atoi(e) : 0;
+  CK(cudaDeviceGetAttribute(&h->n_sm, cudaDevAttrMultiProcessorCount, device));
   if (const char* e = getenv("ROMS_FUSE_RHO")) h->fuse_rho = atoi(e);
   if ((size_t)2 * (N + 1) * 32 * sizeof(double) > 64 * 1024) h->uv2_sm = 0;   // fewer than 3 warps per SM would fit: global re-read version
   if ((size_t)2 * (N + 1) * h->col_bx * h->col_by * sizeof(double) > 200 * 1024) { h->col_by = 1; }
@@ -926,6 +928,36 @@ int roms_step3d_uv1(roms_ctx* h, int tile) {
   return 0;
 }
 }  // extern "C"
+// k_step2d_hyb<64,4> (step2d_hyb.cuh): the shipped barotropic kernel.  rows per block: as few as keep the whole grid resident in ONE wave
+// (occupancy x SMs block slots) -- a block's run time is (rows+1) row iterations of ~2 us each, so a second wave doubles it
+// (measured, profiles/r2_step2d_variants.txt: 1024x1024 on 148 SMs -> 17 strips x 52 row blocks of 20 rows, 58 us)
+static int s2d_hyb_launch(roms_ctx* h, const S2D& s, const char* name) {
+  const KP& p = h->kp;
+  S2PlanesH ap;
+  ap.a[HA_H] = p.h; ap.a[HA_ZS] = s.zs; ap.a[HA_ZB] = s.zb; ap.a[HA_ZO] = s.zo; ap.a[HA_US] = s.us; ap.a[HA_UB] = s.ub; ap.a[HA_UO] = s.uo;
+  ap.a[HA_DNU] = p.dn_u; ap.a[HA_PM] = p.pm; ap.a[HA_PN] = p.pn; ap.a[HA_RHOA] = p.rhoA; ap.a[HA_RHOS] = p.rhoS;
+  constexpr int TXn = 64, Sn = 4, MINBn = 5;     // bound 5, not 6: ptxas keeps 168 registers (6 blocks fit) but must not spill -- a 64-byte spill costs 45 %
+  const int strips = (p.iend - p.istr + 1 + TXn - 2) / (TXn - 1), Mrows = p.jend - p.jstr + 1;
+  const size_t sm_ = ((size_t)Sn * HA_N * (TXn + 4) + 2 * TXn) * sizeof(double) + Sn * sizeof(unsigned long long);
+  static int occ_ = 0;
+  if (!occ_) {
+    CK(cudaFuncSetAttribute((k_step2d_hyb<TXn, Sn, MINBn>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_));
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_, (k_step2d_hyb<TXn, Sn, MINBn>), TXn, sm_));
+    if (occ_ < 1) occ_ = 1;
+  }
+  int rows = h->s2d_rows;
+  if (rows <= 0) {
+    const int slots = h->n_sm * occ_, by = slots / strips > 0 ? slots / strips : 1;
+    rows = (Mrows + by - 1) / by;
+    if (rows < 8) rows = 8;
+  }
+  dim3 b_(TXn, 1, 1), g_(strips, (Mrows + rows - 1) / rows, 1);
+  if (h->ktiming) kt_begin(h, name);
+  k_step2d_hyb<TXn, Sn, MINBn><<<g_, b_, sm_, h->st>>>(p, s, ap, rows);
+  if (h->ktiming) kt_end(h);
+  h->launches++;
+  return 0;
+}
 // operand planes of the TMA marching kernel, in the order of step2d_tma.cuh
 static void s2d_planes(const KP& p, const S2D& s, S2Planes& ap) {
   ap.a[A_H] = p.h; ap.a[A_ZS] = s.zs; ap.a[A_ZB] = s.zb; ap.a[A_ZO] = s.zo; ap.a[A_VS] = s.vs; ap.a[A_VB] = s.vb; ap.a[A_VO] = s.vo; ap.a[A_DMV] = p.dm_v;
@@ -975,10 +1007,14 @@ int roms_step2d(roms_ctx* h) {
     else CK(cudaStreamWaitEvent(h->st, h->ev_edge[o], 0));
     S2D si = s, sr = s;
     si.region = 1; sr.region = 2;
-    if (h->s2d_tma >= 1 && h->s2d_tma <= 5) {     // interior by the TMA marching kernel (its emit mask skips the ring)
+    if (h->s2d_tma == 12) {     // interior by the shipped marching kernel (its emit mask skips the ring)
+      int rc = s2d_hyb_launch(h, si, "k_step2d_hyb(interior)");
+      if (rc) return rc;
+      h->launches--;
+    } else if (h->s2d_tma >= 1 && h->s2d_tma <= 5) {
       S2Planes ap;
       s2d_planes(p, s, ap);
-      const int rows = h->s2d_rows;
+      const int rows = h->s2d_rows > 0 ? h->s2d_rows : 16;
       const size_t sm_ = ((size_t)4 * S2M_NA * (64 + 4) + 2 * 64) * sizeof(double) + 4 * sizeof(unsigned long long);
       static bool attr_ = false;
       if (!attr_) { CK(cudaFuncSetAttribute((k_step2d_tma<64, 4>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_)); attr_ = true; }
@@ -1012,9 +1048,34 @@ int roms_step2d(roms_ctx* h) {
     }
     return 0;
   }
-  if (h->s2d_tma >= 6) {
+  if (h->s2d_tma == 12) {
+    int rc = s2d_hyb_launch(h, s, "k_step2d_hyb");
+    if (rc) return rc;
+  } else if (h->s2d_tma > 12) {
+    // other shapes of k_step2d_hyb (tuning)
+    S2PlanesH ap;
+    ap.a[HA_H] = p.h; ap.a[HA_ZS] = s.zs; ap.a[HA_ZB] = s.zb; ap.a[HA_ZO] = s.zo; ap.a[HA_US] = s.us; ap.a[HA_UB] = s.ub; ap.a[HA_UO] = s.uo;
+    ap.a[HA_DNU] = p.dn_u; ap.a[HA_PM] = p.pm; ap.a[HA_PN] = p.pn; ap.a[HA_RHOA] = p.rhoA; ap.a[HA_RHOS] = p.rhoS;
+    const int rows = h->s2d_rows > 0 ? h->s2d_rows : 20;
+#define S2H_LAUNCH(TXn, Sn, MINBn)                                                                                                                      \
+  do {                                                                                                                                             \
+    const size_t sm_ = ((size_t)Sn * HA_N * (TXn + 4) + 2 * TXn) * sizeof(double) + Sn * sizeof(unsigned long long);                                \
+    static bool attr_ = false;                                                                                                                     \
+    if (!attr_) { CK(cudaFuncSetAttribute((k_step2d_hyb<TXn, Sn, MINBn>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_)); attr_ = true; }        \
+    dim3 b_(TXn, 1, 1), g_((p.iend - p.istr + 1 + TXn - 2) / (TXn - 1), (p.jend - p.jstr + 1 + rows - 1) / rows, 1);                                \
+    if (h->ktiming) kt_begin(h, "k_step2d_hyb");                                                                                                   \
+    k_step2d_hyb<TXn, Sn, MINBn><<<g_, b_, sm_, h->st>>>(p, s, ap, rows);                                                                                 \
+    if (h->ktiming) kt_end(h);                                                                                                                     \
+    h->launches++;                                                                                                                                 \
+  } while (0)
+    if (h->s2d_tma == 13) S2H_LAUNCH(64, 4, 5);
+    else if (h->s2d_tma == 14) S2H_LAUNCH(64, 4, 4);
+    else if (h->s2d_tma == 15) S2H_LAUNCH(32, 4, 8);
+    else S2H_LAUNCH(32, 4, 10);
+#undef S2H_LAUNCH
+  } else if (h->s2d_tma >= 6) {
     // register-marching kernel (step2d_march.cuh): strips of TX-1 columns x s2d_rows rows per block
-    const int rows = h->s2d_rows;
+    const int rows = h->s2d_rows > 0 ? h->s2d_rows : 16;
 #define S2R_LAUNCH(TXn, MB)                                                                                                   \
   do {                                                                                                                      \
     dim3 b_(TXn, 1, 1), g_((p.iend - p.istr + 1 + TXn - 2) / (TXn - 1), (p.jend - p.jstr + 1 + rows - 1) / rows, 1);         \
@@ -1034,7 +1095,7 @@ int roms_step2d(roms_ctx* h) {
     // TMA-fed marching kernel (step2d_tma.cuh): strips of S2M_TX-1 columns x s2d_rows rows per block
     S2Planes ap;
     s2d_planes(p, s, ap);
-    const int rows = h->s2d_rows;
+    const int rows = h->s2d_rows > 0 ? h->s2d_rows : 16;
 #define S2M_LAUNCH(TXn, Sn)                                                                                                                        \
   do {                                                                                                                                             \
     const size_t sm_ = ((size_t)Sn * S2M_NA * (TXn + 4) + 2 * TXn) * sizeof(double) + Sn * sizeof(unsigned long long);                              \
@@ -1050,7 +1111,7 @@ int roms_step2d(roms_ctx* h) {
       case 2: S2M_LAUNCH(128, 3); break;
       case 3: S2M_LAUNCH(128, 4); break;
       case 4: S2M_LAUNCH(256, 3); break;
-      case 5: S2M_LAUNCH(64, 6); break;
+      case 5: S2M_LAUNCH(64, 3); break;
       default: S2M_LAUNCH(64, 4); break;
     }
 #undef S2M_LAUNCH
