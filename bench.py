@@ -360,11 +360,12 @@ def main():
 
     def e2e_step():
         for t_, (f, l, it) in zip(pin_in, in_fields):
-            lib.roms_push(g.h, FID[f], l, it, C.cast(t_.data_ptr(), dptr))
+            lib.roms_push_async(g.h, FID[f], l, it, C.cast(t_.data_ptr(), dptr))
         g.call("step")
         knew = g.get_idx()[6]
         for t_, f in zip(pin_out, ("ZETA", "UBAR", "VBAR")):
-            lib.roms_pull(g.h, FID[f], knew, 1, C.cast(t_.data_ptr(), dptr))
+            lib.roms_pull_async(g.h, FID[f], knew, 1, C.cast(t_.data_ptr(), dptr))
+        g.sync()      # one synchronisation per step: the forcing buffers are free again, the output planes are valid
     e2e_step()
     barrier()
     t0 = time.perf_counter()
@@ -381,7 +382,7 @@ def main():
     e2e_ms = float(te.max().item())
     plane = sy * sx * 8
     e2e = {"value": updates / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": len(pin_in) * plane, "d2h_bytes_per_step": len(pin_out) * plane,
-           "what": "per step: H2D of sustr,svstr,swflx,stflx(1:NT) from pinned host, roms_step, D2H of zeta,ubar,vbar(knew)"}
+           "what": "per step: H2D of sustr,svstr,swflx,stflx(1:NT) from pinned host (roms_push_async), roms_step, D2H of zeta,ubar,vbar(knew) (roms_pull_async), one roms_sync"}
 
     # ---- roofline of the dominant kernel: a second pass of the same K steps with every launch bracketed by its own events
     peak, peak_src = peaks()

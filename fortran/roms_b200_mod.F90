@@ -80,6 +80,12 @@ module roms_b200_mod
     integer(c_int) function roms_pull(h, field, lvl, itrc, host) bind(C, name='roms_pull')
       import; type(c_ptr), value :: h, host; integer(c_int), value :: field, lvl, itrc
     end function
+    integer(c_int) function roms_push_async(h, field, lvl, itrc, host) bind(C, name='roms_push_async')
+      import; type(c_ptr), value :: h, host; integer(c_int), value :: field, lvl, itrc
+    end function
+    integer(c_int) function roms_pull_async(h, field, lvl, itrc, host) bind(C, name='roms_pull_async')
+      import; type(c_ptr), value :: h, host; integer(c_int), value :: field, lvl, itrc
+    end function
     integer(c_int) function roms_sync(h) bind(C, name='roms_sync')
       import; type(c_ptr), value :: h
     end function

@@ -92,6 +92,11 @@ int  roms_create(const roms_cfg* cfg, int device, roms_ctx** out);
 int  roms_destroy(roms_ctx* h);
 int  roms_push(roms_ctx* h, int field, int lvl, int itrc, const double* host);   /* H2D */
 int  roms_pull(roms_ctx* h, int field, int lvl, int itrc, double* host);         /* D2H, blocking */
+/* The same transfers enqueued on the library's stream without waiting (pinned host memory makes them truly asynchronous): the host
+ * buffer of a push must stay untouched, and that of a pull is valid, only after the next roms_sync.  For a driver that exchanges
+ * forcing and output planes every step (set_forces / wrt_his, main.F:386, :324): one roms_sync per step instead of one per plane. */
+int  roms_push_async(roms_ctx* h, int field, int lvl, int itrc, const double* host);
+int  roms_pull_async(roms_ctx* h, int field, int lvl, int itrc, double* host);
 long roms_field_count(roms_ctx* h, int field);  /* doubles per (lvl,itrc) slab */
 int  roms_sync(roms_ctx* h);
 const char* roms_last_error(void);

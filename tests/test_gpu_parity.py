@@ -45,6 +45,25 @@ def test_push_pull_roundtrip():
     g.close()
 
 
+def test_async_push_pull_roundtrip():
+    """roms_push_async / roms_pull_async: same planes as the blocking calls once roms_sync has returned."""
+    import ctypes as C
+    from romsb200 import FID
+    cfg, st = cases.channel(20, 12, 6)
+    g = Roms(cfg)
+    rng = np.random.default_rng(2)
+    dptr = C.POINTER(C.c_double)
+    for f, lvl, it in [("ZETA", 2, 1), ("V", 1, 1), ("T", 2, 2)]:
+        a = np.ascontiguousarray(rng.standard_normal(g.shape(f)))
+        b = np.empty_like(a)
+        assert g.lib.roms_push_async(g.h, FID[f], lvl, it, a.ctypes.data_as(dptr)) == 0
+        assert g.lib.roms_pull_async(g.h, FID[f], lvl, it, b.ctypes.data_as(dptr)) == 0
+        g.sync()
+        assert np.array_equal(a, b)
+        assert np.array_equal(g.pull(f, lvl, it), a)
+    g.close()
+
+
 def test_constants_match_oracle():
     cfg, _ = cases.filament()
     g, o = Roms(cfg), Oracle(cfg)

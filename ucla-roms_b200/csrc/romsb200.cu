@@ -433,6 +433,26 @@ int roms_pull(roms_ctx* h, int field, int lvl, int itrc, double* host) {
   CK(cudaStreamSynchronize(h->st));
   return 0;
 }
+int roms_push_async(roms_ctx* h, int field, int lvl, int itrc, const double* host) {
+  FLUSH_RHO(h);
+  if (join_st2(h)) return -1;
+  double* d; int nk;
+  if (find_slot(h, field, lvl, itrc, &d, &nk)) return -1;
+  CK(cudaSetDevice(h->device));
+  const size_t w = (size_t)(h->c.Lm + 4) * sizeof(double);
+  CK(cudaMemcpy2DAsync(d + (IOFF - 1), (size_t)h->kp.SX * sizeof(double), host, w, w, (size_t)(h->c.Mm + 4) * nk, cudaMemcpyHostToDevice, h->st));
+  return 0;
+}
+int roms_pull_async(roms_ctx* h, int field, int lvl, int itrc, double* host) {
+  FLUSH_RHO(h);
+  if (join_st2(h)) return -1;
+  double* d; int nk;
+  if (find_slot(h, field, lvl, itrc, &d, &nk)) return -1;
+  CK(cudaSetDevice(h->device));
+  const size_t w = (size_t)(h->c.Lm + 4) * sizeof(double);
+  CK(cudaMemcpy2DAsync(host, w, d + (IOFF - 1), (size_t)h->kp.SX * sizeof(double), w, (size_t)(h->c.Mm + 4) * nk, cudaMemcpyDeviceToHost, h->st));
+  return 0;
+}
 int roms_sync(roms_ctx* h) {
   FLUSH_RHO(h);
   CK(cudaSetDevice(h->device));

@@ -36,16 +36,20 @@ __global__ void __launch_bounds__(TX, MINB) k_step2d_hyb(const __grid_constant__
   __syncthreads();
   // lane a of warp 0 owns plane a; rows ja-2 and jb+1 only need h and the three zeta levels
   const double* src0 = ap.a[tx < HA_N ? tx : 0] + e0;
-  auto issue = [&](int r) {
-    if (r > rlast) return;
-    const int sl = (r - r0) % NS;
-    const int na = (r == r0 || r == rlast) ? 4 : HA_N;
-    if (tx == 0) s2m_expect_tx(&full[sl], (uint32_t)(na * nW * 8));
-    __syncwarp();
-    if (tx < na) s2m_bulk_g2s(st + (sl * HA_N + tx) * W, src0 + (ix2_t)(r + 1) * SX, (uint32_t)(nW * 8), &full[sl]);
-  };
+  // (a macro, not a lambda: when the by-reference lambda was not inlined its captures lived on the stack -- 64 B, -45 %)
+#define S2H_ISSUE(r_)                                                                                                          \
+  do {                                                                                                                         \
+    const int rr_ = (r_);                                                                                                      \
+    if (rr_ <= rlast) {                                                                                                        \
+      const int sl_ = (rr_ - r0) % NS;                                                                                         \
+      const int na_ = (rr_ == r0 || rr_ == rlast) ? 4 : HA_N;                                                                  \
+      if (tx == 0) s2m_expect_tx(&full[sl_], (uint32_t)(na_ * nW * 8));                                                        \
+      __syncwarp();                                                                                                            \
+      if (tx < na_) s2m_bulk_g2s(st + (sl_ * HA_N + tx) * W, src0 + (ix2_t)(rr_ + 1) * SX, (uint32_t)(nW * 8), &full[sl_]);    \
+    }                                                                                                                          \
+  } while (0)
   if (tx < 32)
-    for (int q = 0; q < NS; ++q) issue(r0 + q);
+    for (int q = 0; q < NS; ++q) S2H_ISSUE(r0 + q);
 #define SMH_(sl, A, dx) st[((sl)*HA_N + (A)) * W + x + (dx)]
 #define DRHS_(sl, dx) (SMH_(sl, HA_H, dx) + s.fwd * SMH_(sl, HA_ZS, dx) + s.fwd1 * SMH_(sl, HA_ZB, dx) + s.fwd2 * SMH_(sl, HA_ZO, dx))
   // own-column operands kept in registers: row ja-1 (c*), the v-type ones of row ja (n*)
@@ -85,7 +89,11 @@ __global__ void __launch_bounds__(TX, MINB) k_step2d_hyb(const __grid_constant__
     const int C = (j - r0) % NS, Nn = (j + 1 - r0) % NS;
     const ix2_t c = CIDX(il, j);
     // requests for the next iteration: own-column operands of row j+1, v-type operands of row j+2
-    const double pRM = p.rmask[c + SX]; const double pSWF = p.swflx[c + SX]; const double pUM = p.umask[c + SX]; const double pVM = p.vmask[c + SX]; const double pRUF = p.rufrc[c + SX]; const double pRVF = p.rvfrc[c + SX]; const double pZT = p.Zt_avg1[c + SX]; const double pDU1 = p.DU_avg1[c + SX]; const double pDV1 = p.DV_avg1[c + SX]; const double pDU2 = p.DU_avg2[c + SX]; const double pDV2 = p.DV_avg2[c + SX];
+    const double pRM = p.rmask[c + SX]; const double pSWF = p.swflx[c + SX];
+    // the nine planes that only the second half of the row needs (masks, forcing, fast-time averages): asked into L2 one row ahead
+    // (no register cost), loaded here, used after the row barrier -- their registers do not live across the loop back-edge
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(p.umask + c + SX)); asm volatile("prefetch.global.L2 [%0];" ::"l"(p.vmask + c + SX)); asm volatile("prefetch.global.L2 [%0];" ::"l"(p.rufrc + c + SX)); asm volatile("prefetch.global.L2 [%0];" ::"l"(p.rvfrc + c + SX)); asm volatile("prefetch.global.L2 [%0];" ::"l"(p.Zt_avg1 + c + SX)); asm volatile("prefetch.global.L2 [%0];" ::"l"(p.DU_avg1 + c + SX)); asm volatile("prefetch.global.L2 [%0];" ::"l"(p.DV_avg1 + c + SX)); asm volatile("prefetch.global.L2 [%0];" ::"l"(p.DU_avg2 + c + SX)); asm volatile("prefetch.global.L2 [%0];" ::"l"(p.DV_avg2 + c + SX));
+    cUM = p.umask[c]; cVM = p.vmask[c]; cRUF = p.rufrc[c]; cRVF = p.rvfrc[c]; cZT = p.Zt_avg1[c]; cDU1 = p.DU_avg1[c]; cDV1 = p.DV_avg1[c]; cDU2 = p.DU_avg2[c]; cDV2 = p.DV_avg2[c];
     const double qVS = s.vs[c + 2 * SX]; const double qVB = s.vb[c + 2 * SX]; const double qVO = s.vo[c + 2 * SX]; const double qDMV = p.dm_v[c + 2 * SX];
     s2m_wait(&full[Nn], (uint32_t)(((j + 1 - r0) / NS) & 1));
     // ---- zeta_new(i,j) (step2d_FB.F:151-216)
@@ -105,7 +113,7 @@ __global__ void __launch_bounds__(TX, MINB) k_step2d_hyb(const __grid_constant__
     __syncthreads();     // every thread is past row j-1: its slot is free
     if (tx < 32) {
       asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-      issue(j - 1 + NS);
+      S2H_ISSUE(j - 1 + NS);
     }
     const double rhoA0 = SMH_(C, HA_RHOA, 0), rhoS0 = SMH_(C, HA_RHOS, 0);
     const double zb0 = SMH_(C, HA_ZB, 0), zo0 = SMH_(C, HA_ZO, 0);
@@ -156,7 +164,8 @@ __global__ void __launch_bounds__(TX, MINB) k_step2d_hyb(const __grid_constant__
         aw.VFx = aw.UFx * (rhoS_w - rhoA_w);
         aw.VFe = aw.UFe * aw.UFx;
       }
-      const S2Pt asv = sv ? as : zero;
+      S2Pt asv;      // component-wise selects: a struct select may be lowered through local memory (64 B of stack, -45 %)
+      asv.UFx = sv ? as.UFx : 0.0; asv.UFe = sv ? as.UFe : 0.0; asv.VFx = sv ? as.VFx : 0.0; asv.VFe = sv ? as.VFe : 0.0;
       const double dnu = SMH_(C, HA_DNU, 0), dmv = cDMV;
       // s2d_pgf(cffg, dn, c, d, a, b): a at c-d, b at c
       double rubar = cffg * dnu *
@@ -175,7 +184,8 @@ __global__ void __launch_bounds__(TX, MINB) k_step2d_hyb(const __grid_constant__
           bw.VFe = bw.UFe * (znw + zs_w);
           bw.VFx = bw.UFx * (rhoS_w - rhoA_w);
         }
-        const S2Pt bsv = sv ? bs : zero;
+        S2Pt bsv;
+        bsv.UFx = sv ? bs.UFx : 0.0; bsv.UFe = sv ? bs.UFe : 0.0; bsv.VFx = sv ? bs.VFx : 0.0; bsv.VFe = sv ? bs.VFe : 0.0;
         rubar = rubar + cffg * dnu *
                             ((h_w + h0) * (bw.UFe - b0.UFe) + bw.VFe - b0.VFe + (h_w - h0) * (bw.VFx + b0.VFx + 0.333333333333 * (rhoA_w - rhoA0) * (bw.UFx - b0.UFx)));
         rvbar = rvbar + cffg * dmv *
@@ -250,10 +260,11 @@ __global__ void __launch_bounds__(TX, MINB) k_step2d_hyb(const __grid_constant__
     as = a0; bs = b0;
     Drhs_c = Drhs_n; DVom_c = DVom_n;
     cVS = nVS; cDMV = nDMV;
-    cRM = pRM; cSWF = pSWF; cUM = pUM; cVM = pVM; cRUF = pRUF; cRVF = pRVF; cZT = pZT; cDU1 = pDU1; cDV1 = pDV1; cDU2 = pDU2; cDV2 = pDV2;
+    cRM = pRM; cSWF = pSWF;
     nVS = qVS; nVB = qVB; nVO = qVO; nDMV = qDMV;
   }
 #undef SMH_
+#undef S2H_ISSUE
 #undef DRHS_
 #undef S2ST_
 }

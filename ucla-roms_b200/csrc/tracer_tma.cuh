@@ -20,7 +20,7 @@
 #include <cstdint>
 
 struct TmaMaps {
-  CUtensorMap t36x12, f34x9, o32x8;
+  CUtensorMap t36x12, f34x9, o32x8;      // 2-D boxes over the arena seen as SX x (all rows)
 };
 template <int TB>
 struct TrcRows {      // first arena row (plane index x (Mm+4)) of level k=1 of every operand
