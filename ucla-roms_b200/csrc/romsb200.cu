@@ -794,7 +794,7 @@ static int rhs_uv_tma_launch(roms_ctx* h, const double* u, const double* v) {
   return 0;
 }
 // TMA-staged horizontal pressure gradient (k_prsgrd_tma, nonlinear split EOS)
-template <bool WALL>
+template <bool WALL, int MINB>
 static int prsgrd_tma_launch(roms_ctx* h) {
   const KP& p = h->kp;
   constexpr int NS = 3;
@@ -804,10 +804,10 @@ static int prsgrd_tma_launch(roms_ctx* h) {
   r.zr = row(p.z_r); r.r1 = row(p.rho1); r.q1 = row(p.qp1); r.P = row(p.P); r.rho = row(p.rho); r.hz = row(p.Hz);
   const size_t sm_ = (size_t)NS * PrsLayout::stage * sizeof(double) + NS * sizeof(unsigned long long);
   static bool attr_ = false;
-  if (!attr_) { CK(cudaFuncSetAttribute((k_prsgrd_tma<WALL, TTMA_KB, NS>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_)); attr_ = true; }
+  if (!attr_) { CK(cudaFuncSetAttribute((k_prsgrd_tma<WALL, TTMA_KB, NS, MINB>), cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm_)); attr_ = true; }
   dim3 b_(288, 1, 1), g_((p.iend + IOFF + 1 + 31) / 32, (p.jend - p.jstr + 1 + 7) / 8, (p.N + TTMA_KB - 1) / TTMA_KB);
   if (h->ktiming) kt_begin(h, "k_prsgrd_tma");
-  k_prsgrd_tma<WALL, TTMA_KB, NS><<<g_, b_, sm_, h->st>>>(p, h->tmaps, r);
+  k_prsgrd_tma<WALL, TTMA_KB, NS, MINB><<<g_, b_, sm_, h->st>>>(p, h->tmaps, r);
   if (h->ktiming) kt_end(h);
   h->launches++;
   return 0;
@@ -892,7 +892,7 @@ int roms_prsgrd(roms_ctx* h) {
   }
   if (h->c.nonlin_eos) {
     if (!fused) COLUMN(k_prsgrd_vert<true>, 0, p.Lm, 0, p.Mm, p);
-    if (h->t_tma) return WALLED(h) ? prsgrd_tma_launch<true>(h) : prsgrd_tma_launch<false>(h);
+    if (h->t_tma) return WALLED(h) ? prsgrd_tma_launch<true, 3>(h) : prsgrd_tma_launch<false, 3>(h);   // bound 3 (72 registers): 1.42 ms; bound 2 (96, no spill): 1.57 ms
     if (WALLED(h)) PLANE((k_prsgrd_horiz<true, true, KB_PRS>), p.iend, p.jstr, p.jend, (p.N + KB_PRS - 1) / KB_PRS, p);
     else PLANE((k_prsgrd_horiz<true, false, KB_PRS>), p.iend, p.jstr, p.jend, (p.N + KB_PRS - 1) / KB_PRS, p);
   } else {

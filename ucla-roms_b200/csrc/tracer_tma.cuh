@@ -48,6 +48,15 @@ __device__ __forceinline__ void tma_load_2d(void* dst, const CUtensorMap* map, i
                : "memory");
 }
 
+// The wall path of k_rhs_uv_tma is OUT OF LINE: inlined it costs the hot path its registers (144-176 B of spills at the 72-register
+// bound; UP3 1.61 -> 1.39 ms, C4 1.38 -> 1.14 ms on the same box); only the threads next to a wall pay for the call.  (The same move
+// made k_t_horiz_tma slower, 1.20 -> 1.29 ms, and left k_prsgrd_tma unchanged: those keep their wall paths inline.)
+template <bool UP>
+__device__ __noinline__ void rhs_uv_point_near_ool(const KP& p, const double* __restrict__ u, const double* __restrict__ v, ixr_t c, int i, int j, int k, bool dov,
+                                                   double& ru, double& rv) {
+  rhs_uv_point<UP, true>(p, u, v, c, i, j, k, dov, ru, rv);
+}
+
 template <bool PRE, bool WALL, bool RIV, int TB, int KB, int NS>
 __global__ void __launch_bounds__(288, (PRE ? 2 : 3))
 k_t_horiz_tma(const __grid_constant__ KP p, const __grid_constant__ TrcBatch<TB> tb, const __grid_constant__ TmaMaps tm, const __grid_constant__ TrcRows<TB> tr,
@@ -234,7 +243,7 @@ k_rhs_uv_tma(const __grid_constant__ KP p, const __grid_constant__ TmaMaps tm, c
       bool dou = true, dov = true;
       if (near) {
         dov = j >= p.jstrV; dou = i >= p.istrU;
-        rhs_uv_point<UP, true>(p, u, v, c, i, j, k, dov, ru, rv);
+        rhs_uv_point_near_ool<UP>(p, u, v, c, i, j, k, dov, ru, rv);
       } else {
         // rhs_uv_point<UP, false> on the staged boxes (row pitch TT_W instead of SX, level offset 0)
         const double* U = sg + L::u;
@@ -297,8 +306,8 @@ __device__ __forceinline__ double prs_dir_s(const KP& p, const double* __restric
   const double rxc = (a3 - a2 + (b3 - b2) * dpth * (1.0 - qp2 * dpth)) * m3;
   return prs_tail_core<true>(p, dn, FCa, FCb, FCc, rxa, rxb, rxc, b1, b2, z1, z2, srho[ch], srho[ch - dh], sHz[ch], sHz[ch - dh], sP[ch - dh], sP[ch]);
 }
-template <bool WALL, int KB, int NS>
-__global__ void __launch_bounds__(288, 3) k_prsgrd_tma(const __grid_constant__ KP p, const __grid_constant__ TmaMaps tm, const __grid_constant__ PrsRows tr) {
+template <bool WALL, int KB, int NS, int MINB>
+__global__ void __launch_bounds__(288, MINB) k_prsgrd_tma(const __grid_constant__ KP p, const __grid_constant__ TmaMaps tm, const __grid_constant__ PrsRows tr) {
   typedef PrsLayout L;
   extern __shared__ __align__(128) unsigned char ttma_raw[];
   double* st = (double*)ttma_raw;
