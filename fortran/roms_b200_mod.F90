@@ -33,6 +33,8 @@ module roms_b200_mod
     integer(c_int) :: ts_dif2
     real(c_double) :: visc2
     real(c_double) :: tnu2(ROMS_MAXNT)
+    integer(c_int) :: obc_west, obc_east, obc_south, obc_north
+    real(c_double) :: ubind
   end type roms_cfg
 
   ! enum roms_field (0-based, order of include/roms_b200.h)
@@ -63,6 +65,12 @@ module roms_b200_mod
     enumerator :: ROMS_PTIDE
     enumerator :: ROMS_PIPE_IDX, ROMS_PIPE_FLX
     enumerator :: ROMS_SRFLX
+    enumerator :: ROMS_ZETA_WEST, ROMS_ZETA_EAST, ROMS_ZETA_SOUTH, ROMS_ZETA_NORTH
+    enumerator :: ROMS_UBAR_WEST, ROMS_UBAR_EAST, ROMS_UBAR_SOUTH, ROMS_UBAR_NORTH
+    enumerator :: ROMS_VBAR_WEST, ROMS_VBAR_EAST, ROMS_VBAR_SOUTH, ROMS_VBAR_NORTH
+    enumerator :: ROMS_U_WEST, ROMS_U_EAST, ROMS_U_SOUTH, ROMS_U_NORTH
+    enumerator :: ROMS_V_WEST, ROMS_V_EAST, ROMS_V_SOUTH, ROMS_V_NORTH
+    enumerator :: ROMS_T_WEST, ROMS_T_EAST, ROMS_T_SOUTH, ROMS_T_NORTH
     enumerator :: ROMS_NFIELDS
   end enum
 

@@ -43,6 +43,13 @@ typedef struct roms_cfg {
   int ts_dif2;                /* cppdefs TS_DIF2: roms_step calls roms_t3dmix after step3d_t (main.F:471-473)   */
   double visc2;               /* lateral_visc keyword [m2/s] -> visc2_r, visc2_p (mixing.F:156-157)           */
   double tnu2[ROMS_MAXNT];    /* tracer_diff2 keyword [m2/s] -> diff2(:,:,itrc)  (mixing.F:161-163)           */
+  /* open boundaries; zero-initialised = every non-periodic edge is a closed wall.  An open edge runs the
+     combination every open-boundary case of the reference is built with (cppdefs.opt:185-225, tests/{Flux_frc,Pipes_real,CDR_*}):
+     OBC_M2FLATHER (zetabc.F:28-36, u2dbc_im.F:28-56: characteristic condition on the normal barotropic velocity, upstream advection +
+     binding to the boundary data on the tangential one), OBC_M3ORLANSKI (u3dbc_im.F:47-119, v3dbc_im.F), OBC_TORLANSKI (t3dbc_im.F:36-83),
+     with Z_FRC_BRY, M2_FRC_BRY, M3_FRC_BRY, T_FRC_BRY boundary data (boundary.F:109-222) pushed as ROMS_*_WEST ... ROMS_*_NORTH. */
+  int obc_west, obc_east, obc_south, obc_north;   /* cppdefs OBC_WEST / OBC_EAST / OBC_SOUTH / OBC_NORTH (ignored on a periodic edge) */
+  double ubind;               /* ubind keyword [m/s]: binding velocity towards the boundary data on inflow (u3dbc_im.F:83-90)      */
 } roms_cfg;
 
 /* Field identifiers for roms_push / roms_pull.  `lvl` selects the time level (1-based, as in
@@ -84,6 +91,16 @@ enum roms_field {
   ROMS_PIPE_IDX, ROMS_PIPE_FLX,                  /* pipe_frc.F: pipe index of a cell (0: none) and its volume flux fraction*pipe_vol [m3/s] */
   ROMS_SRFLX,                                    /* surf_flux.F srflx: shortwave radiation flux [degC m/s], part of stflx(itemp); with KPP on it
                                                     penetrates by swr_frac (step3d_t_ISO.F:961-998, lmd_kpp.F:160-167); zero unless pushed */
+  /* boundary data of the open edges (boundary.F:21-60 zeta_west(j), ubar_west(j), vbar_west(j), u_west(j,k), v_west(j,k),
+     t_west(j,k,itrc) and their east/south/north counterparts): lines along the edge with the same 2-cell margin as the planes --
+     Mm+4 values (west, east) or Lm+4 values (south, north), times N levels for the 3-D ones (level-major).  Id = base + side,
+     side 0 west, 1 east, 2 south, 3 north.  Zero unless pushed. */
+  ROMS_ZETA_WEST, ROMS_ZETA_EAST, ROMS_ZETA_SOUTH, ROMS_ZETA_NORTH,
+  ROMS_UBAR_WEST, ROMS_UBAR_EAST, ROMS_UBAR_SOUTH, ROMS_UBAR_NORTH,
+  ROMS_VBAR_WEST, ROMS_VBAR_EAST, ROMS_VBAR_SOUTH, ROMS_VBAR_NORTH,
+  ROMS_U_WEST, ROMS_U_EAST, ROMS_U_SOUTH, ROMS_U_NORTH,             /* k=1:N */
+  ROMS_V_WEST, ROMS_V_EAST, ROMS_V_SOUTH, ROMS_V_NORTH,             /* k=1:N */
+  ROMS_T_WEST, ROMS_T_EAST, ROMS_T_SOUTH, ROMS_T_NORTH,             /* itrc 1..NT, k=1:N */
   ROMS_NFIELDS
 };
 

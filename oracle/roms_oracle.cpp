@@ -74,12 +74,18 @@ struct Orc {
   bool pot_tides = false;
   vec xr;  // only for the Filament analytic initial condition
   std::vector<vec> s2d;
+  // boundary.F:21-60: data of the open edges, side 0 west, 1 east (index j), 2 south, 3 north (index i); lines with the planes' margin
+  vec zeta_bry[4], ubar_bry[4], vbar_bry[4], u_bry[4], v_bry[4];
+  std::vector<vec> t_bry[4];
+  int bryL(int side) const { return side < 2 ? SY : SX; }
 };
 
 #define A2(a, i, j) (a)[(size_t)((i) + 1) + (size_t)((j) + 1) * SX]
 #define A3(a, i, j, k) (a)[(size_t)((i) + 1) + (size_t)((j) + 1) * SX + (size_t)((k)-1) * SXY]
 #define AW(a, i, j, k) (a)[(size_t)((i) + 1) + (size_t)((j) + 1) * SX + (size_t)(k) * SXY]
 #define SL(a, i, k) (a)[(size_t)((i) + 1) + (size_t)(k) * SX]   // (i,k) slab scratch, k=0:N
+#define B1(a, q) (a)[(size_t)((q) + 1)]                                   // boundary line: zeta_west(j), ubar_south(i) ...
+#define B2(a, q, k, L) (a)[(size_t)((q) + 1) + (size_t)((k)-1) * (L)]     // u_west(j,k), t_south(i,k) ...
 static inline bool riv_on(double code) { return std::fabs(code) > 1e-3; }
 static inline int riv_id(double code) { return (int)std::lround(code / 10); }   // nint(riv_uflx/10)
 
@@ -939,59 +945,343 @@ void vert_tracer_flux(Orc& o, int j, const vec& t, vec& FC, vec& CF) {
   }
 }
 
-// Lateral boundary conditions on closed (wall) edges, incl. the corner rules of a fully closed basin.
+// Lateral boundary conditions on non-periodic edges.  Closed (wall) edges, incl. the corner rules of a fully closed basin:
 // zetabc.F:3 (gradient), u2dbc_im.F:150-152,359,442 / u3dbc_im.F:293-295 (gamma2 slip), v2dbc_im.F / v3dbc_im.F
-// (no normal flow), t3dbc_im.F:86-96 (gradient).  Nothing happens on periodic edges.
+// (no normal flow), t3dbc_im.F:86-96 (gradient).  Open edges (cfg.obc_*): the OBC_M2FLATHER / OBC_M3ORLANSKI / OBC_TORLANSKI
+// branches with Z/M2/M3/T_FRC_BRY boundary data, every edge restated as the reference writes it (the edges are not mirror images of
+// each other: t3dbc takes the interior neighbour at nstp on the west and south but at nnew on the east and north).
+// Nothing happens on periodic edges.
+#define OBCW (WWALL && o.c.obc_west)
+#define OBCE (EWALL && o.c.obc_east)
+#define OBCS (SWALL && o.c.obc_south)
+#define OBCN (NWALL && o.c.obc_north)
 void zetabc(Orc& o, vec& zeta_new) {
   GEOM
-  if (WWALL) for (int j = jstrV - 1; j <= jend; ++j) A2(zeta_new, istr - 1, j) = A2(zeta_new, istr, j) * A2(o.rmask, istr - 1, j);
-  if (EWALL) for (int j = jstrV - 1; j <= jend; ++j) A2(zeta_new, iend + 1, j) = A2(zeta_new, iend, j) * A2(o.rmask, iend + 1, j);
-  if (SWALL) for (int i = istrU - 1; i <= iend; ++i) A2(zeta_new, i, jstr - 1) = A2(zeta_new, i, jstr) * A2(o.rmask, i, jstr - 1);
-  if (NWALL) for (int i = istrU - 1; i <= iend; ++i) A2(zeta_new, i, jend + 1) = A2(zeta_new, i, jend) * A2(o.rmask, i, jend + 1);
+  const vec& zs = o.zeta[o.kstp - 1];
+  const double dtfast = o.dtfast, g = o.c.g;
+  if (OBCW) {   // zetabc.F:28-36
+    for (int j = jstrV - 1; j <= jend; ++j) {
+      const double cx = dtfast * A2(o.pm, istr, j) * sqrt(g * A2(o.h, istr, j));
+      A2(zeta_new, istr - 1, j) = ((1. - cx) * A2(zs, istr - 1, j) + cx * A2(zs, istr, j)) * A2(o.rmask, istr - 1, j);
+    }
+  } else if (WWALL) for (int j = jstrV - 1; j <= jend; ++j) A2(zeta_new, istr - 1, j) = A2(zeta_new, istr, j) * A2(o.rmask, istr - 1, j);
+  if (OBCE) {   // zetabc.F:66-75
+    for (int j = jstrV - 1; j <= jend; ++j) {
+      const double cx = dtfast * A2(o.pm, iend, j) * sqrt(g * A2(o.h, iend, j));
+      A2(zeta_new, iend + 1, j) = ((1. - cx) * A2(zs, iend + 1, j) + cx * A2(zs, iend, j)) * A2(o.rmask, iend + 1, j);
+    }
+  } else if (EWALL) for (int j = jstrV - 1; j <= jend; ++j) A2(zeta_new, iend + 1, j) = A2(zeta_new, iend, j) * A2(o.rmask, iend + 1, j);
+  if (OBCS) {   // zetabc.F:125-134
+    for (int i = istrU - 1; i <= iend; ++i) {
+      const double cx = dtfast * A2(o.pn, i, jstr) * sqrt(g * A2(o.h, i, jstr));
+      A2(zeta_new, i, jstr - 1) = ((1. - cx) * A2(zs, i, jstr - 1) + cx * A2(zs, i, jstr)) * A2(o.rmask, i, jstr - 1);
+    }
+  } else if (SWALL) for (int i = istrU - 1; i <= iend; ++i) A2(zeta_new, i, jstr - 1) = A2(zeta_new, i, jstr) * A2(o.rmask, i, jstr - 1);
+  if (OBCN) {   // zetabc.F:165-174
+    for (int i = istrU - 1; i <= iend; ++i) {
+      const double cx = dtfast * A2(o.pn, i, jend) * sqrt(g * A2(o.h, i, jend));
+      A2(zeta_new, i, jend + 1) = ((1. - cx) * A2(zs, i, jend + 1) + cx * A2(zs, i, jend)) * A2(o.rmask, i, jend + 1);
+    }
+  } else if (NWALL) for (int i = istrU - 1; i <= iend; ++i) A2(zeta_new, i, jend + 1) = A2(zeta_new, i, jend) * A2(o.rmask, i, jend + 1);
   if (SWALL && WWALL) A2(zeta_new, istr - 1, jstr - 1) = 0.5 * (A2(zeta_new, istr, jstr - 1) + A2(zeta_new, istr - 1, jstr));
   if (SWALL && EWALL) A2(zeta_new, iend + 1, jstr - 1) = 0.5 * (A2(zeta_new, iend, jstr - 1) + A2(zeta_new, iend + 1, jstr));
   if (NWALL && WWALL) A2(zeta_new, istr - 1, jend + 1) = 0.5 * (A2(zeta_new, istr, jend + 1) + A2(zeta_new, istr - 1, jend));
   if (NWALL && EWALL) A2(zeta_new, iend + 1, jend + 1) = 0.5 * (A2(zeta_new, iend, jend + 1) + A2(zeta_new, iend + 1, jend));
 }
+// the characteristic (Flather-type) value of the velocity normal to an open edge, u2dbc_im.F:29-56 / v2dbc_im.F:
+// zin, zout = zeta(kstp) on the interior / exterior side of the face, zin_new = zeta(knew) on the interior side, vb = the face's own
+// velocity and vin that of the next face inwards (kstp), sgn = -1 on the west/south, +1 on the east/north
+static inline double flather(double dtfast, double g, double hout, double hin, double pout, double pin, double zin, double zout, double zin_new, double vb, double vin,
+                             double vbry, double zbry, double sgn, bool lowfirst) {
+  // lowfirst: the western/southern edges add h and pm/pn as (exterior + interior), the eastern/northern ones as (interior + exterior)
+  const double cff = lowfirst ? 0.5 * (hout + hin) : 0.5 * (hin + hout);
+  const double hx = sqrt(g / cff);
+  const double cx = dtfast * cff * hx * 0.5 * (lowfirst ? (pout + pin) : (pin + pout));
+  double zx = (0.5 + cx) * zin + (0.5 - cx) * zout;
+  if (cx > 0.292893218813452) {
+    const double q = 1. - 0.292893218813452 / cx;
+    zx = zx + (zin_new + cx * zout - (1. + cx) * zin) * (q * q);
+  }
+  return sgn < 0 ? 0.5 * ((1. - cx) * vb + cx * vin + vbry - hx * (zx - zbry)) : 0.5 * ((1. - cx) * vb + cx * vin + vbry + hx * (zx - zbry));
+}
 void u2dbc(Orc& o, vec& ubar) {
   GEOM
-  if (WWALL) for (int j = jstr; j <= jend; ++j) A2(ubar, istr, j) = 0.0;
-  if (EWALL) for (int j = jstr; j <= jend; ++j) A2(ubar, iend + 1, j) = 0.0;
-  if (SWALL) for (int i = istr; i <= iendR; ++i) A2(ubar, i, jstr - 1) = o.c.gamma2 * A2(ubar, i, jstr) * A2(o.umask, i, jstr - 1);
-  if (NWALL) for (int i = istr; i <= iendR; ++i) A2(ubar, i, jend + 1) = o.c.gamma2 * A2(ubar, i, jend) * A2(o.umask, i, jend + 1);
+  const vec &zs = o.zeta[o.kstp - 1], &zn = o.zeta[o.knew - 1], &us = o.ubar[o.kstp - 1], &vs = o.vbar[o.kstp - 1];
+  const double dtfast = o.dtfast, g = o.c.g;
+  if (OBCW) {
+    for (int j = jstr; j <= jend; ++j)
+      A2(ubar, istr, j) = flather(dtfast, g, A2(o.h, istr - 1, j), A2(o.h, istr, j), A2(o.pm, istr - 1, j), A2(o.pm, istr, j), A2(zs, istr, j), A2(zs, istr - 1, j),
+                                  A2(zn, istr, j), A2(us, istr, j), A2(us, istr + 1, j), B1(o.ubar_bry[0], j), B1(o.zeta_bry[0], j), -1., true) * A2(o.umask, istr, j);
+  } else if (WWALL) for (int j = jstr; j <= jend; ++j) A2(ubar, istr, j) = 0.0;
+  if (OBCE) {
+    for (int j = jstr; j <= jend; ++j)
+      A2(ubar, iend + 1, j) = flather(dtfast, g, A2(o.h, iend + 1, j), A2(o.h, iend, j), A2(o.pm, iend + 1, j), A2(o.pm, iend, j), A2(zs, iend, j), A2(zs, iend + 1, j),
+                                      A2(zn, iend, j), A2(us, iend + 1, j), A2(us, iend, j), B1(o.ubar_bry[1], j), B1(o.zeta_bry[1], j), +1., false) * A2(o.umask, iend + 1, j);
+  } else if (EWALL) for (int j = jstr; j <= jend; ++j) A2(ubar, iend + 1, j) = 0.0;
+  // tangential component on an open southern/northern edge (u2dbc_im.F:278-330,398-450 under OBC_M2FLATHER -> OBC_M2ORLANSKI rename, :276-279):
+  // upstream advection by the kstp velocities and binding to the boundary data where the flow enters
+  auto tang = [&](int jb, int ja, double sgn, const vec& bry) {    // jb boundary row, ja the interior row beside it
+    auto grad = [&](int i, int j) { return A2(us, i + 1, j) - A2(us, i, j); };
+    const int jv = sgn < 0 ? jstr : jend + 1;                        // the v-row on the edge
+    for (int i = istrU; i <= iend; ++i) {
+      double cx, cy;
+      if (sgn < 0) {
+        cx = -0.125 * dtfast * (A2(vs, i, jv) + A2(vs, i - 1, jv)) * (A2(o.pn, i, jb) + A2(o.pn, i - 1, jb) + A2(o.pn, i, ja) + A2(o.pn, i - 1, ja));
+        cy = 0.125 * dtfast * (A2(us, i, jb) + A2(us, i, ja)) * (A2(o.pm, i, jb) + A2(o.pm, i - 1, jb) + A2(o.pm, i, ja) + A2(o.pm, i - 1, ja));
+      } else {
+        cx = 0.125 * dtfast * (A2(vs, i, jv) + A2(vs, i - 1, jv)) * (A2(o.pn, i, ja) + A2(o.pn, i - 1, ja) + A2(o.pn, i, jb) + A2(o.pn, i - 1, jb));
+        cy = 0.125 * dtfast * (A2(us, i, ja) + A2(us, i, jb)) * (A2(o.pm, i, ja) + A2(o.pm, i - 1, ja) + A2(o.pm, i, jb) + A2(o.pm, i - 1, jb));
+      }
+      double cext;
+      if (cx > 0.) cext = 0.; else { cext = -cx; cx = 0.; }
+      double r = (1. - cx) * (A2(us, i, jb) - std::max(cy, 0.) * grad(i - 1, jb) - std::min(cy, 0.) * grad(i, jb)) +
+                 cx * (A2(us, i, ja) - std::max(cy, 0.) * grad(i - 1, ja) - std::min(cy, 0.) * grad(i, ja));
+      r = (1. - cext) * r + cext * B1(bry, i);
+      A2(ubar, i, jb) = r * A2(o.umask, i, jb);
+    }
+  };
+  if (OBCS) tang(jstr - 1, jstr, -1., o.ubar_bry[2]);
+  else if (SWALL) for (int i = istr; i <= iendR; ++i) A2(ubar, i, jstr - 1) = o.c.gamma2 * A2(ubar, i, jstr) * A2(o.umask, i, jstr - 1);
+  if (OBCN) tang(jend + 1, jend, +1., o.ubar_bry[3]);
+  else if (NWALL) for (int i = istr; i <= iendR; ++i) A2(ubar, i, jend + 1) = o.c.gamma2 * A2(ubar, i, jend) * A2(o.umask, i, jend + 1);
+  // corners between adjacent open edges (u2dbc_im.F:453-476)
+  if (OBCS && OBCW) A2(ubar, istr, jstr - 1) = 0.5 * (A2(ubar, istr + 1, jstr - 1) + A2(ubar, istr, jstr));
+  if (OBCS && OBCE) A2(ubar, iend + 1, jstr - 1) = 0.5 * (A2(ubar, iend, jstr - 1) + A2(ubar, iend + 1, jstr));
+  if (OBCN && OBCW) A2(ubar, istr, jend + 1) = 0.5 * (A2(ubar, istr + 1, jend + 1) + A2(ubar, istr, jend));
+  if (OBCN && OBCE) A2(ubar, iend + 1, jend + 1) = 0.5 * (A2(ubar, iend, jend + 1) + A2(ubar, iend + 1, jend));
 }
 void v2dbc(Orc& o, vec& vbar) {
   GEOM
-  if (SWALL) for (int i = istr; i <= iend; ++i) A2(vbar, i, jstr) = 0.0;
-  if (NWALL) for (int i = istr; i <= iend; ++i) A2(vbar, i, jend + 1) = 0.0;
-  if (WWALL) for (int j = jstr; j <= jendR; ++j) A2(vbar, istr - 1, j) = o.c.gamma2 * A2(vbar, istr, j) * A2(o.vmask, istr - 1, j);
-  if (EWALL) for (int j = jstr; j <= jendR; ++j) A2(vbar, iend + 1, j) = o.c.gamma2 * A2(vbar, iend, j) * A2(o.vmask, iend + 1, j);
+  const vec &zs = o.zeta[o.kstp - 1], &zn = o.zeta[o.knew - 1], &us = o.ubar[o.kstp - 1], &vs = o.vbar[o.kstp - 1];
+  const double dtfast = o.dtfast, g = o.c.g;
+  if (OBCS) {
+    for (int i = istr; i <= iend; ++i)
+      A2(vbar, i, jstr) = flather(dtfast, g, A2(o.h, i, jstr - 1), A2(o.h, i, jstr), A2(o.pn, i, jstr - 1), A2(o.pn, i, jstr), A2(zs, i, jstr), A2(zs, i, jstr - 1),
+                                  A2(zn, i, jstr), A2(vs, i, jstr), A2(vs, i, jstr + 1), B1(o.vbar_bry[2], i), B1(o.zeta_bry[2], i), -1., true) * A2(o.vmask, i, jstr);
+  } else if (SWALL) for (int i = istr; i <= iend; ++i) A2(vbar, i, jstr) = 0.0;
+  if (OBCN) {
+    for (int i = istr; i <= iend; ++i)
+      A2(vbar, i, jend + 1) = flather(dtfast, g, A2(o.h, i, jend + 1), A2(o.h, i, jend), A2(o.pn, i, jend + 1), A2(o.pn, i, jend), A2(zs, i, jend), A2(zs, i, jend + 1),
+                                      A2(zn, i, jend), A2(vs, i, jend + 1), A2(vs, i, jend), B1(o.vbar_bry[3], i), B1(o.zeta_bry[3], i), +1., false) * A2(o.vmask, i, jend + 1);
+  } else if (NWALL) for (int i = istr; i <= iend; ++i) A2(vbar, i, jend + 1) = 0.0;
+  auto tang = [&](int ib, int ia, double sgn, const vec& bry) {    // ib boundary column, ia the interior column beside it
+    auto grad = [&](int i, int j) { return A2(vs, i, j + 1) - A2(vs, i, j); };
+    const int iu = sgn < 0 ? istr : iend + 1;                        // the u-column on the edge
+    for (int j = jstrV; j <= jend; ++j) {
+      double cx, cy;
+      if (sgn < 0) {
+        cx = -0.125 * dtfast * (A2(us, iu, j) + A2(us, iu, j - 1)) * (A2(o.pm, ib, j) + A2(o.pm, ib, j - 1) + A2(o.pm, ia, j) + A2(o.pm, ia, j - 1));
+        cy = 0.125 * dtfast * (A2(vs, ib, j) + A2(vs, ia, j)) * (A2(o.pn, ib, j) + A2(o.pn, ib, j - 1) + A2(o.pn, ia, j) + A2(o.pn, ia, j - 1));
+      } else {
+        cx = 0.125 * dtfast * (A2(us, iu, j) + A2(us, iu, j - 1)) * (A2(o.pm, ia, j) + A2(o.pm, ia, j - 1) + A2(o.pm, ib, j) + A2(o.pm, ib, j - 1));
+        cy = 0.125 * dtfast * (A2(vs, ia, j) + A2(vs, ib, j)) * (A2(o.pn, ia, j) + A2(o.pn, ia, j - 1) + A2(o.pn, ib, j) + A2(o.pn, ib, j - 1));
+      }
+      double cext;
+      if (cx > 0.) cext = 0.; else { cext = -cx; cx = 0.; }
+      double r = (1. - cx) * (A2(vs, ib, j) - std::max(cy, 0.) * grad(ib, j - 1) - std::min(cy, 0.) * grad(ib, j)) +
+                 cx * (A2(vs, ia, j) - std::max(cy, 0.) * grad(ia, j - 1) - std::min(cy, 0.) * grad(ia, j));
+      r = (1. - cext) * r + cext * B1(bry, j);
+      A2(vbar, ib, j) = r * A2(o.vmask, ib, j);
+    }
+  };
+  if (OBCW) tang(istr - 1, istr, -1., o.vbar_bry[0]);
+  else if (WWALL) for (int j = jstr; j <= jendR; ++j) A2(vbar, istr - 1, j) = o.c.gamma2 * A2(vbar, istr, j) * A2(o.vmask, istr - 1, j);
+  if (OBCE) tang(iend + 1, iend, +1., o.vbar_bry[1]);
+  else if (EWALL) for (int j = jstr; j <= jendR; ++j) A2(vbar, iend + 1, j) = o.c.gamma2 * A2(vbar, iend, j) * A2(o.vmask, iend + 1, j);
+  if (OBCW && OBCS) A2(vbar, istr - 1, jstr) = 0.5 * (A2(vbar, istr - 1, jstr + 1) + A2(vbar, istr, jstr));
+  if (OBCE && OBCS) A2(vbar, iend + 1, jstr) = 0.5 * (A2(vbar, iend + 1, jstr + 1) + A2(vbar, iend, jstr));
+  if (OBCW && OBCN) A2(vbar, istr - 1, jend + 1) = 0.5 * (A2(vbar, istr - 1, jend) + A2(vbar, istr, jend + 1));
+  if (OBCE && OBCN) A2(vbar, iend + 1, jend + 1) = 0.5 * (A2(vbar, iend + 1, jend) + A2(vbar, iend, jend + 1));
+}
+// Orlanski-type radiation of the velocity normal to an open edge with binding to the boundary data on inflow (u3dbc_im.F:47-119 west,
+// :124-196 east; v3dbc_im.F south/north).  qb_s = boundary value at nstp, q1_s/q1_n = first interior value at nstp/nnew, q2_n = second interior
+// value at nnew, g1a/g1b = tangential differences of the first interior line (nstp) either side of the point, gba/gbb = those of the boundary line
+static inline double orlanski(double qb_s, double q1_s, double q1_n, double q2_n, double g1a, double g1b, double gba, double gbb, double bry, bool bry_inward,
+                              double ubind, double dtfwd, double pscale) {
+  const double eps = 1.E-33;
+  const double dft = q1_s - q1_n, dfx = q1_n - q2_n;
+  const double dfy = (dft * (g1a + g1b) > 0.) ? g1a : g1b;
+  const double cff = std::max(dfx * dfx + dfy * dfy, eps);
+  double cy = std::min(cff, std::max(dft * dfy, -cff));
+  double cx = dft * dfx, cext;
+  if (cx < 0.) {
+    cx = 0.; cy = 0.;
+    cext = bry_inward ? fabs(bry) : ubind;     // u_west > 0: cext=u_west; u_east < 0: cext=-u_east
+    cext = cext * dtfwd * pscale;
+  } else cext = 0.;
+  double r = (cff * qb_s + cx * q1_n - std::max(cy, 0.) * gba - std::min(cy, 0.) * gbb) / (cff + cx);
+  r = (1. - cext) * r + cext * bry;
+  return r;
 }
 void u3dbc(Orc& o, vec& u) {
   GEOM
+  const vec &us = o.u[o.nstp - 1], &ur = o.u[o.nrhs - 1], &vr = o.v[o.nrhs - 1];
+  const double dtfwd = (o.nnew == 3) ? 0.5 * o.c.dt : o.c.dt, ubind = o.c.ubind;
+  const int LW = o.bryL(0), LS = o.bryL(2);
   for (int k = 1; k <= N; ++k) {
-    if (WWALL) for (int j = jstr; j <= jend; ++j) A3(u, istr, j, k) = 0.0;
-    if (EWALL) for (int j = jstr; j <= jend; ++j) A3(u, iend + 1, j, k) = 0.0;
-    if (SWALL) for (int i = istr; i <= iendR; ++i) A3(u, i, jstr - 1, k) = o.c.gamma2 * A3(u, i, jstr, k) * A2(o.umask, i, jstr - 1);
-    if (NWALL) for (int i = istr; i <= iendR; ++i) A3(u, i, jend + 1, k) = o.c.gamma2 * A3(u, i, jend, k) * A2(o.umask, i, jend + 1);
+    if (OBCW) {
+      auto grad = [&](int i, int j) { return (A3(us, i, j, k) - A3(us, i, j - 1, k)) * A2(o.pmask, i, j); };
+      for (int j = jstr; j <= jend; ++j) {
+        const double b = B2(o.u_bry[0], j, k, LW);
+        A3(u, istr, j, k) = orlanski(A3(us, istr, j, k), A3(us, istr + 1, j, k), A3(u, istr + 1, j, k), A3(u, istr + 2, j, k), grad(istr + 1, j), grad(istr + 1, j + 1),
+                                     grad(istr, j), grad(istr, j + 1), b, b > 0., ubind, dtfwd, 0.5 * (A2(o.pm, istr - 1, j) + A2(o.pm, istr, j))) * A2(o.umask, istr, j);
+      }
+    } else if (WWALL) for (int j = jstr; j <= jend; ++j) A3(u, istr, j, k) = 0.0;
+    if (OBCE) {
+      auto grad = [&](int i, int j) { return (A3(us, i, j, k) - A3(us, i, j - 1, k)) * A2(o.pmask, i, j); };
+      for (int j = jstr; j <= jend; ++j) {
+        const double b = B2(o.u_bry[1], j, k, LW);
+        A3(u, iend + 1, j, k) = orlanski(A3(us, iend + 1, j, k), A3(us, iend, j, k), A3(u, iend, j, k), A3(u, iend - 1, j, k), grad(iend, j), grad(iend, j + 1),
+                                         grad(iend + 1, j), grad(iend + 1, j + 1), b, b < 0., ubind, dtfwd, 0.5 * (A2(o.pm, iend, j) + A2(o.pm, iend + 1, j))) * A2(o.umask, iend + 1, j);
+      }
+    } else if (EWALL) for (int j = jstr; j <= jend; ++j) A3(u, iend + 1, j, k) = 0.0;
+    // tangential component on open southern/northern edges: upstream advection by the nrhs velocities (u3dbc_im.F:203-243,:250-290)
+    auto tang = [&](int jb, int ja, double sgn, const vec& bry) {
+      auto grad = [&](int i, int j) { return A3(us, i + 1, j, k) - A3(us, i, j, k); };
+      const int jv = sgn < 0 ? jstr : jend + 1;
+      for (int i = istrU; i <= iend; ++i) {
+        double cx, cy;
+        if (sgn < 0) {
+          cx = -0.125 * dtfwd * (A3(vr, i, jv, k) + A3(vr, i - 1, jv, k)) * (A2(o.pn, i, jb) + A2(o.pn, i - 1, jb) + A2(o.pn, i, ja) + A2(o.pn, i - 1, ja));
+          cy = 0.125 * dtfwd * (A3(ur, i, jb, k) + A3(ur, i, ja, k)) * (A2(o.pm, i, jb) + A2(o.pm, i - 1, jb) + A2(o.pm, i, ja) + A2(o.pm, i - 1, ja));
+        } else {
+          cx = 0.125 * dtfwd * (A3(vr, i, jv, k) + A3(vr, i - 1, jv, k)) * (A2(o.pn, i, jb) + A2(o.pn, i - 1, jb) + A2(o.pn, i, ja) + A2(o.pn, i - 1, ja));
+          cy = 0.125 * dtfwd * (A3(ur, i, ja, k) + A3(ur, i, jb, k)) * (A2(o.pm, i, jb) + A2(o.pm, i - 1, jb) + A2(o.pm, i, ja) + A2(o.pm, i - 1, ja));
+        }
+        double cext;
+        if (cx > 0.) cext = 0.; else { cext = -cx; cx = 0.; }
+        double r = (1. - cx) * (A3(us, i, jb, k) - std::max(cy, 0.) * grad(i - 1, jb) - std::min(cy, 0.) * grad(i, jb)) +
+                   cx * (A3(us, i, ja, k) - std::max(cy, 0.) * grad(i - 1, ja) - std::min(cy, 0.) * grad(i, ja));
+        r = (1. - cext) * r + cext * B2(bry, i, k, LS);
+        A3(u, i, jb, k) = r * A2(o.umask, i, jb);
+      }
+    };
+    if (OBCS) tang(jstr - 1, jstr, -1., o.u_bry[2]);
+    else if (SWALL) for (int i = istr; i <= iendR; ++i) A3(u, i, jstr - 1, k) = o.c.gamma2 * A3(u, i, jstr, k) * A2(o.umask, i, jstr - 1);
+    if (OBCN) tang(jend + 1, jend, +1., o.u_bry[3]);
+    else if (NWALL) for (int i = istr; i <= iendR; ++i) A3(u, i, jend + 1, k) = o.c.gamma2 * A3(u, i, jend, k) * A2(o.umask, i, jend + 1);
+  }
+  for (int k = 1; k <= N; ++k) {   // corners between adjacent open edges (u3dbc_im.F:397-421)
+    if (OBCW && OBCS) A3(u, istr, jstr - 1, k) = 0.5 * (A3(u, istr + 1, jstr - 1, k) + A3(u, istr, jstr, k));
+    if (OBCE && OBCS) A3(u, iend + 1, jstr - 1, k) = 0.5 * (A3(u, iend, jstr - 1, k) + A3(u, iend + 1, jstr, k));
+    if (OBCW && OBCN) A3(u, istr, jend + 1, k) = 0.5 * (A3(u, istr + 1, jend + 1, k) + A3(u, istr, jend, k));
+    if (OBCE && OBCN) A3(u, iend + 1, jend + 1, k) = 0.5 * (A3(u, iend, jend + 1, k) + A3(u, iend + 1, jend, k));
   }
 }
 void v3dbc(Orc& o, vec& v) {
   GEOM
+  const vec &vs = o.v[o.nstp - 1], &ur = o.u[o.nrhs - 1], &vr = o.v[o.nrhs - 1];
+  const double dtfwd = (o.nnew == 3) ? 0.5 * o.c.dt : o.c.dt, ubind = o.c.ubind;
+  const int LW = o.bryL(0), LS = o.bryL(2);
   for (int k = 1; k <= N; ++k) {
-    if (SWALL) for (int i = istr; i <= iend; ++i) A3(v, i, jstr, k) = 0.0;
-    if (NWALL) for (int i = istr; i <= iend; ++i) A3(v, i, jend + 1, k) = 0.0;
-    if (WWALL) for (int j = jstr; j <= jendR; ++j) A3(v, istr - 1, j, k) = o.c.gamma2 * A3(v, istr, j, k) * A2(o.vmask, istr - 1, j);
-    if (EWALL) for (int j = jstr; j <= jendR; ++j) A3(v, iend + 1, j, k) = o.c.gamma2 * A3(v, iend, j, k) * A2(o.vmask, iend + 1, j);
+    if (OBCS) {   // v3dbc_im.F:44-111
+      auto grad = [&](int i, int j) { return (A3(vs, i, j, k) - A3(vs, i - 1, j, k)) * A2(o.pmask, i, j); };
+      for (int i = istr; i <= iend; ++i) {
+        const double b = B2(o.v_bry[2], i, k, LS);
+        A3(v, i, jstr, k) = orlanski(A3(vs, i, jstr, k), A3(vs, i, jstr + 1, k), A3(v, i, jstr + 1, k), A3(v, i, jstr + 2, k), grad(i, jstr + 1), grad(i + 1, jstr + 1),
+                                     grad(i, jstr), grad(i + 1, jstr), b, b > 0., ubind, dtfwd, 0.5 * (A2(o.pn, i, jstr - 1) + A2(o.pn, i, jstr))) * A2(o.vmask, i, jstr);
+      }
+    } else if (SWALL) for (int i = istr; i <= iend; ++i) A3(v, i, jstr, k) = 0.0;
+    if (OBCN) {
+      auto grad = [&](int i, int j) { return (A3(vs, i, j, k) - A3(vs, i - 1, j, k)) * A2(o.pmask, i, j); };
+      for (int i = istr; i <= iend; ++i) {
+        const double b = B2(o.v_bry[3], i, k, LS);
+        A3(v, i, jend + 1, k) = orlanski(A3(vs, i, jend + 1, k), A3(vs, i, jend, k), A3(v, i, jend, k), A3(v, i, jend - 1, k), grad(i, jend), grad(i + 1, jend),
+                                         grad(i, jend + 1), grad(i + 1, jend + 1), b, b < 0., ubind, dtfwd, 0.5 * (A2(o.pn, i, jend) + A2(o.pn, i, jend + 1))) * A2(o.vmask, i, jend + 1);
+      }
+    } else if (NWALL) for (int i = istr; i <= iend; ++i) A3(v, i, jend + 1, k) = 0.0;
+    auto tang = [&](int ib, int ia, double sgn, const vec& bry) {
+      auto grad = [&](int i, int j) { return A3(vs, i, j + 1, k) - A3(vs, i, j, k); };
+      const int iu = sgn < 0 ? istr : iend + 1;
+      for (int j = jstrV; j <= jend; ++j) {
+        double cx, cy;
+        if (sgn < 0) {
+          cx = -0.125 * dtfwd * (A3(ur, iu, j, k) + A3(ur, iu, j - 1, k)) * (A2(o.pm, ib, j) + A2(o.pm, ib, j - 1) + A2(o.pm, ia, j) + A2(o.pm, ia, j - 1));
+          cy = 0.125 * dtfwd * (A3(vr, ib, j, k) + A3(vr, ia, j, k)) * (A2(o.pn, ib, j) + A2(o.pn, ib, j - 1) + A2(o.pn, ia, j) + A2(o.pn, ia, j - 1));
+        } else {
+          cx = 0.125 * dtfwd * (A3(ur, iu, j, k) + A3(ur, iu, j - 1, k)) * (A2(o.pm, ib, j) + A2(o.pm, ib, j - 1) + A2(o.pm, ia, j) + A2(o.pm, ia, j - 1));
+          cy = 0.125 * dtfwd * (A3(vr, ia, j, k) + A3(vr, ib, j, k)) * (A2(o.pn, ib, j) + A2(o.pn, ib, j - 1) + A2(o.pn, ia, j) + A2(o.pn, ia, j - 1));
+        }
+        double cext;
+        if (cx > 0.) cext = 0.; else { cext = -cx; cx = 0.; }
+        double r = (1. - cx) * (A3(vs, ib, j, k) - std::max(cy, 0.) * grad(ib, j - 1) - std::min(cy, 0.) * grad(ib, j)) +
+                   cx * (A3(vs, ia, j, k) - std::max(cy, 0.) * grad(ia, j - 1) - std::min(cy, 0.) * grad(ia, j));
+        r = (1. - cext) * r + cext * B2(bry, j, k, LW);
+        A3(v, ib, j, k) = r * A2(o.vmask, ib, j);
+      }
+    };
+    if (OBCW) tang(istr - 1, istr, -1., o.v_bry[0]);
+    else if (WWALL) for (int j = jstr; j <= jendR; ++j) A3(v, istr - 1, j, k) = o.c.gamma2 * A3(v, istr, j, k) * A2(o.vmask, istr - 1, j);
+    if (OBCE) tang(iend + 1, iend, +1., o.v_bry[1]);
+    else if (EWALL) for (int j = jstr; j <= jendR; ++j) A3(v, iend + 1, j, k) = o.c.gamma2 * A3(v, iend, j, k) * A2(o.vmask, iend + 1, j);
+  }
+  for (int k = 1; k <= N; ++k) {   // v3dbc_im.F:406-430
+    if (OBCW && OBCS) A3(v, istr - 1, jstr, k) = 0.5 * (A3(v, istr - 1, jstr + 1, k) + A3(v, istr, jstr, k));
+    if (OBCE && OBCS) A3(v, iend + 1, jstr, k) = 0.5 * (A3(v, iend + 1, jstr + 1, k) + A3(v, iend, jstr, k));
+    if (OBCW && OBCN) A3(v, istr - 1, jend + 1, k) = 0.5 * (A3(v, istr - 1, jend, k) + A3(v, istr, jend + 1, k));
+    if (OBCE && OBCN) A3(v, iend + 1, jend + 1, k) = 0.5 * (A3(v, iend + 1, jend, k) + A3(v, iend, jend + 1, k));
   }
 }
-void t3dbc(Orc& o, vec& t) {
+void t3dbc(Orc& o, vec& t, int itrc) {
   GEOM
+  const vec &ts = o.t[o.nstp - 1][itrc], &ur = o.u[o.nrhs - 1], &vr = o.v[o.nrhs - 1];
+  const double dtfwd = (o.nnew == 3) ? 0.5 * o.c.dt : o.c.dt;
+  const int LW = o.bryL(0), LS = o.bryL(2);
   for (int k = 1; k <= N; ++k) {
-    if (WWALL) for (int j = jstr; j <= jend; ++j) A3(t, istr - 1, j, k) = A3(t, istr, j, k) * A2(o.rmask, istr - 1, j);
-    if (EWALL) for (int j = jstr; j <= jend; ++j) A3(t, iend + 1, j, k) = A3(t, iend, j, k) * A2(o.rmask, iend + 1, j);
-    if (SWALL) for (int i = istr; i <= iend; ++i) A3(t, i, jstr - 1, k) = A3(t, i, jstr, k) * A2(o.rmask, i, jstr - 1);
-    if (NWALL) for (int i = istr; i <= iend; ++i) A3(t, i, jend + 1, k) = A3(t, i, jend, k) * A2(o.rmask, i, jend + 1);
+    // open edges (t3dbc_im.F:36-83 west, :100-148 east, :165-212 south, :229-277 north): upstream advection by the nrhs velocities, binding
+    // to the boundary data on inflow.  The interior neighbour enters at nstp on the west and south and at nnew on the east and north.
+    if (OBCW) {
+      auto grad = [&](int i, int j) { return (A3(ts, i, j, k) - A3(ts, i, j - 1, k)) * A2(o.vmask, i, j); };
+      for (int j = jstr; j <= jend; ++j) {
+        double cx = -dtfwd * A3(ur, istr, j, k) * A2(o.pm, istr - 1, j);
+        const double cy = 0.5 * dtfwd * (A3(vr, istr - 1, j, k) + A3(vr, istr - 1, j + 1, k)) * A2(o.pn, istr - 1, j);
+        double cext;
+        if (cx > 0.) cext = 0.; else { cext = -cx; cx = 0.; }
+        double r = (1. - cx) * (A3(ts, istr - 1, j, k) - std::max(cy, 0.) * grad(istr - 1, j) - std::min(cy, 0.) * grad(istr - 1, j + 1)) +
+                   cx * (A3(ts, istr, j, k) - std::max(cy, 0.) * grad(istr, j) - std::min(cy, 0.) * grad(istr, j + 1));
+        r = (1. - cext) * r + cext * B2(o.t_bry[0][itrc], j, k, LW);
+        A3(t, istr - 1, j, k) = r * A2(o.rmask, istr - 1, j);
+      }
+    } else if (WWALL) for (int j = jstr; j <= jend; ++j) A3(t, istr - 1, j, k) = A3(t, istr, j, k) * A2(o.rmask, istr - 1, j);
+    if (OBCE) {
+      auto grad = [&](int i, int j) { return (A3(ts, i, j, k) - A3(ts, i, j - 1, k)) * A2(o.vmask, i, j); };
+      for (int j = jstr; j <= jend; ++j) {
+        double cx = dtfwd * A3(ur, iend + 1, j, k) * A2(o.pm, iend + 1, j);
+        const double cy = 0.5 * dtfwd * (A3(vr, iend + 1, j, k) + A3(vr, iend + 1, j + 1, k)) * A2(o.pn, iend + 1, j);
+        double cext;
+        if (cx > 0.) cext = 0.; else { cext = -cx; cx = 0.; }
+        double r = (1. - cx) * (A3(ts, iend + 1, j, k) - std::max(cy, 0.) * grad(iend + 1, j) - std::min(cy, 0.) * grad(iend + 1, j + 1)) +
+                   cx * (A3(t, iend, j, k) - std::max(cy, 0.) * grad(iend, j) - std::min(cy, 0.) * grad(iend, j + 1));
+        r = (1. - cext) * r + cext * B2(o.t_bry[1][itrc], j, k, LW);
+        A3(t, iend + 1, j, k) = r * A2(o.rmask, iend + 1, j);
+      }
+    } else if (EWALL) for (int j = jstr; j <= jend; ++j) A3(t, iend + 1, j, k) = A3(t, iend, j, k) * A2(o.rmask, iend + 1, j);
+    if (OBCS) {
+      auto grad = [&](int i, int j) { return (A3(ts, i, j, k) - A3(ts, i - 1, j, k)) * A2(o.umask, i, j); };
+      for (int i = istr; i <= iend; ++i) {
+        double cx = -dtfwd * A3(vr, i, jstr, k) * A2(o.pn, i, jstr - 1);
+        const double cy = 0.5 * dtfwd * (A3(ur, i, jstr - 1, k) + A3(ur, i + 1, jstr - 1, k)) * A2(o.pm, i, jstr - 1);
+        double cext;
+        if (cx > 0.) cext = 0.; else { cext = -cx; cx = 0.; }
+        double r = (1. - cx) * (A3(ts, i, jstr - 1, k) - std::max(cy, 0.) * grad(i, jstr - 1) - std::min(cy, 0.) * grad(i + 1, jstr - 1)) +
+                   cx * (A3(ts, i, jstr, k) - std::max(cy, 0.) * grad(i, jstr) - std::min(cy, 0.) * grad(i + 1, jstr));
+        r = (1. - cext) * r + cext * B2(o.t_bry[2][itrc], i, k, LS);
+        A3(t, i, jstr - 1, k) = r * A2(o.rmask, i, jstr - 1);
+      }
+    } else if (SWALL) for (int i = istr; i <= iend; ++i) A3(t, i, jstr - 1, k) = A3(t, i, jstr, k) * A2(o.rmask, i, jstr - 1);
+    if (OBCN) {
+      auto grad = [&](int i, int j) { return (A3(ts, i, j, k) - A3(ts, i - 1, j, k)) * A2(o.umask, i, j); };
+      for (int i = istr; i <= iend; ++i) {
+        double cx = dtfwd * A3(vr, i, jend + 1, k) * A2(o.pn, i, jend + 1);
+        const double cy = 0.5 * dtfwd * (A3(ur, i, jend + 1, k) + A3(ur, i + 1, jend + 1, k)) * A2(o.pm, i, jend + 1);
+        double cext;
+        if (cx > 0.) cext = 0.; else { cext = -cx; cx = 0.; }
+        double r = (1. - cx) * (A3(ts, i, jend + 1, k) - std::max(cy, 0.) * grad(i, jend + 1) - std::min(cy, 0.) * grad(i + 1, jend + 1)) +
+                   cx * (A3(t, i, jend, k) - std::max(cy, 0.) * grad(i, jend) - std::min(cy, 0.) * grad(i + 1, jend));
+        r = (1. - cext) * r + cext * B2(o.t_bry[3][itrc], i, k, LS);
+        A3(t, i, jend + 1, k) = r * A2(o.rmask, i, jend + 1);
+      }
+    } else if (NWALL) for (int i = istr; i <= iend; ++i) A3(t, i, jend + 1, k) = A3(t, i, jend, k) * A2(o.rmask, i, jend + 1);
   }
   // corners: mask-weighted mean of the two neighbouring edge values (t3dbc_im.F:81-144)
   auto corner = [&](int ic, int jc, int ia, int ja, int ib, int jb) {   // (ic,jc) from (ia,ja) and (ib,jb)
@@ -1162,7 +1452,7 @@ void pre_step3d(Orc& o) {
   u3dbc(o, o.u[nnew - 1]);
   v3dbc(o, o.v[nnew - 1]);
   for (int itrc = 0; itrc < NT; ++itrc) {
-    t3dbc(o, o.t[nnew - 1][itrc]);
+    t3dbc(o, o.t[nnew - 1][itrc], itrc);
     ex3(o, o.t[nnew - 1][itrc]);
   }
 }
@@ -1589,7 +1879,7 @@ void step3d_t(Orc& o) {
       }
     }
   }
-  for (int itrc = 0; itrc < NT; ++itrc) t3dbc(o, o.t[nnew - 1][itrc]);
+  for (int itrc = 0; itrc < NT; ++itrc) t3dbc(o, o.t[nnew - 1][itrc], itrc);
   for (int itrc = 0; itrc < NT; ++itrc) ex3(o, o.t[nnew - 1][itrc]);
 }
 
@@ -2250,7 +2540,13 @@ vec* field_ptr(Orc& o, int field, int lvl, int itrc, long* count) {
     case ROMS_PIPE_IDX: p = &o.pipe_idx; break; case ROMS_PIPE_FLX: p = &o.pipe_flx; break;
     case ROMS_PTIDE: p = &o.ptide; break;
     case ROMS_SRFLX: p = &o.srflx; break;
-    default: break;
+    default:
+      if (field >= ROMS_ZETA_WEST && field <= ROMS_T_NORTH) {
+        const int var = (field - ROMS_ZETA_WEST) / 4, side = (field - ROMS_ZETA_WEST) % 4;
+        n = o.bryL(side) * (var < 3 ? 1 : o.N);
+        p = var == 0 ? &o.zeta_bry[side] : var == 1 ? &o.ubar_bry[side] : var == 2 ? &o.vbar_bry[side] : var == 3 ? &o.u_bry[side] : var == 4 ? &o.v_bry[side] : &o.t_bry[side][itrc - 1];
+      }
+      break;
   }
   if (count) *count = n;
   return p;
@@ -2286,6 +2582,12 @@ int orc_create(const roms_cfg* cfg, void** out) {
   }
   for (vec* a : {&o->Hz, &o->z_r, &o->FlxU, &o->FlxV, &o->rho1, &o->qp1, &o->ru, &o->rv, &o->Hz_bak, &o->Hz_fwd, &o->Pp, &o->rho}) a->assign(n3, 0.0);
   for (vec* a : {&o->z_w, &o->We, &o->Wi, &o->Akv, &o->Akt[0], &o->Akt[1]}) a->assign(nw, 0.0);
+  for (int side = 0; side < 4; ++side) {
+    const size_t L = o->bryL(side);
+    o->zeta_bry[side].assign(L, 0.0); o->ubar_bry[side].assign(L, 0.0); o->vbar_bry[side].assign(L, 0.0);
+    o->u_bry[side].assign(L * o->N, 0.0); o->v_bry[side].assign(L * o->N, 0.0);
+    o->t_bry[side].assign(o->NT, vec(L * o->N, 0.0));
+  }
   o->iic = 0; o->iif = 1; o->nstp = 1; o->nrhs = 1; o->nnew = 1; o->kstp = 1; o->knew = 1; o->ntstart = 1; o->forw_start = 1;
   o->dtfast = cfg->dt / double(cfg->ndtfast);   // read_inp_mod.F:416-446
   set_scoord(*o);

@@ -15,7 +15,8 @@ class RomsCfg(C.Structure):
                 ("Tcoef", C.c_double), ("T0", C.c_double), ("Scoef", C.c_double), ("S0", C.c_double),
                 ("rdrg", C.c_double), ("rdrg2", C.c_double), ("Zob", C.c_double), ("gamma2", C.c_double),
                 ("theta_s", C.c_double), ("theta_b", C.c_double), ("hc", C.c_double),
-                ("uv_vis2", C.c_int), ("ts_dif2", C.c_int), ("visc2", C.c_double), ("tnu2", C.c_double * 40)]
+                ("uv_vis2", C.c_int), ("ts_dif2", C.c_int), ("visc2", C.c_double), ("tnu2", C.c_double * 40),
+                ("obc_west", C.c_int), ("obc_east", C.c_int), ("obc_south", C.c_int), ("obc_north", C.c_int), ("ubind", C.c_double)]
 
 
 # enum roms_field, in the order of include/roms_b200.h
@@ -24,7 +25,8 @@ FIELDS = ["H", "PM", "PN", "F", "RMASK", "UMASK", "VMASK", "DM_U", "DN_U", "DM_V
           "DV_AVG1", "DU_AVG2", "DV_AVG2", "DU_AVG_BAK", "DV_AVG_BAK", "R_D", "SUSTR", "SVSTR", "SWFLX",
           "STFLX", "U", "V", "T", "HZ", "Z_R", "Z_W", "FLXU", "FLXV", "WE", "WI", "RHO1", "QP1", "AKV", "AKT",
           "RU", "RV", "PMASK", "DM_P", "DN_P", "PMON_U", "PNOM_V", "VISC2_R", "VISC2_P", "DIFF2", "RIV_UFLX", "RIV_VFLX",
-          "PTIDE", "PIPE_IDX", "PIPE_FLX", "SRFLX"]
+          "PTIDE", "PIPE_IDX", "PIPE_FLX", "SRFLX"] + \
+         [v + "_" + s for v in ("ZETA", "UBAR", "VBAR", "U", "V", "T") for s in ("WEST", "EAST", "SOUTH", "NORTH")]
 FID = {n: i for i, n in enumerate(FIELDS)}
 
 
@@ -58,6 +60,11 @@ class CApi:
         return fn(self.h, FID[field])
 
     def shape(self, field):
+        side = field.rsplit("_", 1)[-1]
+        if side in ("WEST", "EAST", "SOUTH", "NORTH"):       # boundary data: a line along the edge (times N levels)
+            L = self.shape2[0] if side in ("WEST", "EAST") else self.shape2[1]
+            n = self.count(field) // L
+            return (L,) if n == 1 else (n, L)
         n = self.count(field) // (self.shape2[0] * self.shape2[1])
         return self.shape2 if n == 1 else (n,) + self.shape2
 

@@ -92,7 +92,7 @@ def _noise(ig, jg, k, salt):
 
 def channel(Lm=64, Mm=64, N=16, NT=2, ns_walls=False, nonlin_eos=True, dt=120.0, ndtfast=60, dx=1.0e3, dy=1.0e3,
             depth=4000.0, seed=20260101, perturb=1e-6, amp=None, sub=(0, 0, 1, 1), seamount=False, island=False, ew_walls=False,
-            visc2=None, tnu2=None, sponge=False, ishift=0, river=False, pipe=False, tide=False):
+            visc2=None, tnu2=None, sponge=False, ishift=0, river=False, pipe=False, tide=False, open_edges=""):
     """Lm, Mm are the GLOBAL interior sizes; sub=(inode, jnode, np_xi, np_eta) selects this rank's block
     (mpi_setup.F:61-70; uneven splits as mpi_setup.F:117-160, see block_extent).  Returns the cfg and state of that block.
     seamount: Gaussian seamount h = depth*(1 - 0.5*exp(-r^2/(L/5)^2)) (SURVEY.md 8(d) input (3), form of
@@ -110,6 +110,9 @@ def channel(Lm=64, Mm=64, N=16, NT=2, ns_walls=False, nonlin_eos=True, dt=120.0,
     released over the two bottom levels (the profile of pipe_frc.F:232-234) with its own tracer values (state key "PIPES").
     tide: an equilibrium tidal potential ptide (tides.F) of 0.3 m amplitude, one wave across the domain (state key "PTIDE";
     `initialize` switches pot_tides on).
+    open_edges: letters out of "WESN" -- those (non-periodic) edges are open boundaries (cfg.obc_*, ubind = 0.1 m/s) instead of walls; the
+    boundary data (boundary.F: zeta_west ... t_north) are the initial fields on the boundary points, i.e. the exterior is clamped to
+    the initial state (state keys "ZETA_WEST" ... "T_NORTH"), and the initial flow through an open edge is kept.
     ishift: translate the whole E-W periodic problem by this many cells in xi (the state is the roll of the unshifted one, so
     the solution must be the roll of the unshifted solution, bit for bit -- a size-independent parity property)."""
     inode, jnode, np_xi, np_eta = sub
@@ -163,12 +166,23 @@ def channel(Lm=64, Mm=64, N=16, NT=2, ns_walls=False, nonlin_eos=True, dt=120.0,
     v = 0.01 * (np.sin(2 * np.pi * x / Lx) * np.cos(2 * np.pi * y / Ly))[None] * np.exp(z_r / 500.0)
     T = T * (1 + perturb * nz(1)); S = S * (1 + perturb * nz(2))
     u = u + perturb * 0.1 * nz(3); v = v + perturb * 0.1 * nz(4)
+    if open_edges:
+        assert np_xi == 1 and np_eta == 1, "open-boundary cases are single-domain"
+        assert all(e in "WESN" for e in open_edges) and (ew_walls or not set(open_edges) & set("WE")) and (ns_walls or not set(open_edges) & set("SN"))
+        cfg.obc_west, cfg.obc_east, cfg.obc_south, cfg.obc_north = ("W" in open_edges), ("E" in open_edges), ("S" in open_edges), ("N" in open_edges)
+        cfg.ubind = 0.1
     if ns_walls:
         jl = (np.arange(-2, Mm + 4) + j0)
-        v[:, (jl <= 1) | (jl >= MmG + 1), :] = 0.0     # closed south (j=1) and north (j=Mm+1) walls
+        if "S" not in open_edges:
+            v[:, jl <= 1, :] = 0.0                     # closed south wall (j=1)
+        if "N" not in open_edges:
+            v[:, jl >= MmG + 1, :] = 0.0               # closed north wall (j=Mm+1)
     if ew_walls:
         il = (np.arange(-2, Lm + 4) + i0)
-        u[:, :, (il <= 1) | (il >= LmG + 1)] = 0.0     # closed west (i=1) and east (i=Lm+1) walls
+        if "W" not in open_edges:
+            u[:, :, il <= 1] = 0.0                     # closed west wall (i=1)
+        if "E" not in open_edges:
+            u[:, :, il >= LmG + 1] = 0.0               # closed east wall (i=Lm+1)
     if island or river:
         um = np.ones_like(rmask); vm = np.ones_like(rmask)
         um[:, 1:] = rmask[:, 1:] * rmask[:, :-1]; vm[1:, :] = rmask[1:, :] * rmask[:-1, :]
@@ -196,6 +210,17 @@ def channel(Lm=64, Mm=64, N=16, NT=2, ns_walls=False, nonlin_eos=True, dt=120.0,
     akv = np.full((N + 1, Mm + 4, Lm + 4), 1.0e-4)
     st["AKV"] = akv
     st["AKT"] = {(1, 1): akv, (1, 2): akv}
+    if open_edges:
+        # python index = Fortran index + 1: rho/v columns istr-1 -> 1, iend+1 -> Lm+2; the u-face ON the western edge is istr -> 2
+        line = {"W": lambda a, face: a[..., 2 if face else 1], "E": lambda a, face: a[..., Lm + 2],
+                "S": lambda a, face: a[..., 2 if face else 1, :], "N": lambda a, face: a[..., Mm + 2, :]}
+        name = {"W": "WEST", "E": "EAST", "S": "SOUTH", "N": "NORTH"}
+        for e in open_edges:
+            cut = lambda a, face=False: np.ascontiguousarray(line[e](a, face))
+            st["ZETA_" + name[e]] = cut(zeta)
+            st["UBAR_" + name[e]] = cut(ubar, e == "W"); st["VBAR_" + name[e]] = cut(vbar, e == "S")
+            st["U_" + name[e]] = cut(u, e == "W"); st["V_" + name[e]] = cut(v, e == "S")
+            st["T_" + name[e]] = {(1, it): cut(tr[(1, it)]) for it in range(1, NT + 1)}
     if river:
         ridx = np.zeros_like(rmask); rfrc = np.zeros_like(rmask)
         head = np.zeros_like(rmask, dtype=bool)
@@ -222,6 +247,32 @@ def channel(Lm=64, Mm=64, N=16, NT=2, ns_walls=False, nonlin_eos=True, dt=120.0,
             st["VISC2_R"] = t2(visc2 * (1.0 + wr)); st["VISC2_P"] = t2(visc2 * (1.0 + wp))
         if tnu2 is not None:
             st["DIFF2"] = {(1, it + 1): t2(cfg.tnu2[it] * (1.0 + wr)) for it in range(NT)}
+    return cfg, st
+
+
+def pulse_box(Lm=64, Mm=64, N=4, open_edges="WESN", dx=1.0e3, depth=100.0, dt=60.0, ndtfast=30):
+    """Radiation test of the open boundaries: a homogeneous box at rest (f = 0, no drag, no mixing) with a Gaussian free-surface
+    bump in its centre.  The gravity-wave ring it sheds has to leave through the open edges (boundary data: zero = a resting
+    exterior); behind closed walls the same energy stays in the box.  Returns cfg, state."""
+    cfg = RomsCfg(Lm=Lm, Mm=Mm, N=N, NT=2, ew_periodic=0, ns_periodic=0, nonlin_eos=0, salinity=1, ndtfast=ndtfast, np_xi=1, np_eta=1, inode=0, jnode=0,
+                  dt=dt, rho0=1027.0, g=9.81, Tcoef=0.0, T0=10.0, Scoef=0.0, S0=35.0, rdrg=0.0, rdrg2=0.0, Zob=0.0, gamma2=1.0,
+                  theta_s=3.0, theta_b=0.0, hc=25.0)
+    cfg.obc_west, cfg.obc_east, cfg.obc_south, cfg.obc_north = ("W" in open_edges), ("E" in open_edges), ("S" in open_edges), ("N" in open_edges)
+    cfg.ubind = 0.1
+    sy, sx = Mm + 4, Lm + 4
+    x = dx * (np.arange(-1, Lm + 3)[None, :] - 0.5) + np.zeros((sy, 1))
+    y = dx * (np.arange(-1, Mm + 3)[:, None] - 0.5) + np.zeros((1, sx))
+    zeta = 0.1 * np.exp(-((x - 0.5 * dx * Lm) ** 2 + (y - 0.5 * dx * Mm) ** 2) / (5.0 * dx) ** 2)
+    zero2, zero3 = np.zeros((sy, sx)), np.zeros((N, sy, sx))
+    st = {"H": np.full((sy, sx), depth), "PM": np.full((sy, sx), 1.0 / dx), "PN": np.full((sy, sx), 1.0 / dx), "F": zero2.copy(), "RMASK": np.ones((sy, sx)),
+          "ZETA": {(1, 1): zeta, (2, 1): zeta}, "UBAR": {(1, 1): zero2, (2, 1): zero2}, "VBAR": {(1, 1): zero2, (2, 1): zero2},
+          "U": {(1, 1): zero3, (2, 1): zero3}, "V": {(1, 1): zero3, (2, 1): zero3},
+          "T": {(1, 1): zero3 + 10.0, (2, 1): zero3 + 10.0, (1, 2): zero3 + 35.0, (2, 2): zero3 + 35.0},
+          "AKV": np.zeros((N + 1, sy, sx)), "AKT": {(1, 1): np.zeros((N + 1, sy, sx)), (1, 2): np.zeros((N + 1, sy, sx))}}
+    for e, nm in (("W", "WEST"), ("E", "EAST"), ("S", "SOUTH"), ("N", "NORTH")):
+        if e in open_edges:
+            L = sy if e in "WE" else sx
+            st["T_" + nm] = {(1, 1): np.full((N, L), 10.0), (1, 2): np.full((N, L), 35.0)}     # the other boundary data stay zero
     return cfg, st
 
 
