@@ -1570,8 +1570,8 @@ __global__ void __launch_bounds__(S2_TX * S2_TY, LB_S2D) k_step2d(const __grid_c
       }
     }
     p.DU_avg1[c] = DUa;
-  } else if (s.iif == 1) p.DU_avg1[c] = DU1;
-  s2d_store(p, s.un, i, j, c, un);
+  } else if (s.iif == 1 && !p.bry2d) p.DU_avg1[c] = DU1;
+  if (dou || !p.bry2d) s2d_store(p, s.un, i, j, c, un);
   if (dov) {
     const double DVnew = ((D0 + Ds) * s.vs[c] + cff * (p.pm[c] + p.pm[c - SX]) * (p.pn[c] + p.pn[c - SX]) * (rvbar + rvfrc)) * p.vmask[c];
     double vn = DVnew / (Dn0 + Dns);
@@ -1587,14 +1587,14 @@ __global__ void __launch_bounds__(S2_TX * S2_TY, LB_S2D) k_step2d(const __grid_c
     }
     s2d_store(p, s.vn, i, j, c, vn);
     p.DV_avg1[c] = DVa;
-  } else {   // row jstr on a southern wall: v2dbc (no normal flow) and its DV_avg1 term (step2d_FB.F:449-529)
+  } else if (!p.bry2d) {   // row jstr on a southern wall: v2dbc (no normal flow) and its DV_avg1 term (step2d_FB.F:449-529)
     const double vn = 0.0;
     s2d_store(p, s.vn, i, j, c, vn);
     p.DV_avg1[c] = DV1 + cff1 * (Dn0 + Dns) * (vn) * p.dm_v[c];
   }
   if (s.iif == s.nfast) s2d_store(p, s.zn, i, j, c, Zt);
-  // ---- wall point beside this one
-  const bool sw = p.swall && j == p.jstr, nw = p.nwall && j == p.jend;
+  // ---- wall point beside this one (bry2d: every boundary point belongs to k_step2d_bry, obc.cuh)
+  const bool sw = p.swall && j == p.jstr && !p.bry2d, nw = p.nwall && j == p.jend && !p.bry2d;
   if (sw | nw) {
 #pragma unroll 1
     for (int side = 0; side < 2; ++side) {
@@ -1734,6 +1734,8 @@ __global__ void k_bc3d(const __grid_constant__ KP p, double* __restrict__ a, dou
 }
 
 // ------------------------------------------------------------------------------------------------
+#include "obc.cuh"
+
 // step3d_uv2.F:18-786.  PASS 0 (:244-268): u <- (u/Hz_u - vertical-mean mismatch vs DU_avg1)*umask.
 // PASS 1 (:521-577): ubar(knew)=DU_avg1/D, re-correct u, FlxU <- DELTA*FlxU+EPSIL*DC*(u(nstp)+u(nnew))
 // minus its mismatch with DU_avg2.  Column kernels without scratch (re-read through L1/L2).

@@ -61,7 +61,17 @@ struct KP {
   double *bvf, *swr_frac, *ghat;     // (0:N)
   double *hbls, *hbbl, *srflx;       // 2-D
   double *k_ustar, *k_Bo, *k_Bosol, *k_hbl, *k_bbl;   // 2-D work planes of lmd_kpp
+  // open boundaries (obc.cuh): bit 0 west, 1 east, 2 south, 3 north edge is open (only looked at where the matching *wall flag says
+  // that this subdomain touches that non-periodic physical edge).  bry2d / bry3d: the boundary points of ALL non-periodic edges are
+  // set by the general boundary kernels of obc.cuh instead of the closed-wall code inside the interior kernels (always on when an
+  // edge is open; ROMS_BRY=1 forces it for closed basins, which validates those kernels against the in-kernel wall code).
+  int obc, bry2d, bry3d;
+  double ubind;
+  // boundary.F:21-60 boundary data, side 0 west, 1 east (lines over j), 2 south, 3 north (lines over i), index q+1 for q=-1..; the 3-D
+  // ones level-major [k-1][q+1]; bry_t: [itrc][k-1][q+1]
+  double *bry_zeta[4], *bry_ubar[4], *bry_vbar[4], *bry_u[4], *bry_v[4], *bry_t[4];
 };
+#define BRYL(p, side) ((side) < 2 ? (p).Mm + 4 : (p).Lm + 4)
 
 // column base index of (i,j) and relative addressing
 #define CIDX(i, j) ((ix_t)((i) + IOFF) + (ix_t)((j) + 1) * p.SX)

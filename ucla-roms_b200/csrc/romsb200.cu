@@ -62,6 +62,8 @@ struct roms_ctx {
   std::vector<KTimer> ktimers;
   cudaEvent_t ev0 = nullptr, ev1 = nullptr;
   int col_bx = 32, col_by = 2, pl_bx = 32, pl_by = 8;   // plane tiles 32x8: fewest halo-row re-reads through L2 (profiles/r1_tuning_log.txt)
+  double* bry_buf = nullptr;   // boundary data of the open edges (ROMS_ZETA_WEST ... ROMS_T_NORTH), allocated when an edge is open
+  size_t bry_doubles = 0;
   double* kpp_buf = nullptr;   // LMD/KPP arrays (roms_set_kpp)
   double *kpp_Rig = nullptr, *kpp_RigS = nullptr, *kpp_FC = nullptr, *kpp_hblS = nullptr, *kpp_bblS = nullptr, *kpp_alpha = nullptr, *kpp_beta = nullptr;
   int kpp_convec = 1;     // cppdefs LMD_CONVEC
@@ -293,6 +295,7 @@ int roms_create(const roms_cfg* cfg, int device, roms_ctx** out) {
 
   // field table
   for (int id = 0; id < ROMS_NFIELDS; ++id) slot(h, id, 1, 1, 1);
+  for (int id = ROMS_ZETA_WEST; id <= ROMS_T_NORTH; ++id) slot(h, id, 0, 0, 0);     // boundary lines live in bry_buf, not in the plane arena
   slot(h, ROMS_ZETA, 4, 1, 1); slot(h, ROMS_UBAR, 4, 1, 1); slot(h, ROMS_VBAR, 4, 1, 1);
   slot(h, ROMS_STFLX, 1, NT, 1);
   slot(h, ROMS_DIFF2, 1, NT, 1);
@@ -371,6 +374,28 @@ int roms_create(const roms_cfg* cfg, int device, roms_ctx** out) {
   host_weights(h);
   CK(cudaMemcpy(p.Cs_w, h->Cs_w.data(), (N + 1) * sizeof(double), cudaMemcpyHostToDevice));
   CK(cudaMemcpy(p.Cs_r, h->Cs_r.data(), (N + 1) * sizeof(double), cudaMemcpyHostToDevice));
+  // open boundaries (obc.cuh)
+  p.obc = (cfg->obc_west ? 1 : 0) | (cfg->obc_east ? 2 : 0) | (cfg->obc_south ? 4 : 0) | (cfg->obc_north ? 8 : 0);
+  if (cfg->ew_periodic) p.obc &= ~3;
+  if (cfg->ns_periodic) p.obc &= ~12;
+  p.ubind = cfg->ubind;
+  int bry = p.obc != 0;
+  if (const char* e = getenv("ROMS_BRY")) bry = bry || (atoi(e) != 0 && (!cfg->ew_periodic || !cfg->ns_periodic));
+  p.bry2d = p.bry3d = bry;
+  for (int sd = 0; sd < 4; ++sd) { p.bry_zeta[sd] = p.bry_ubar[sd] = p.bry_vbar[sd] = p.bry_u[sd] = p.bry_v[sd] = p.bry_t[sd] = nullptr; }
+  if (bry) {
+    size_t n = 0;
+    for (int sd = 0; sd < 4; ++sd) n += (size_t)BRYL(p, sd) * (3 + (size_t)(2 + NT) * N);
+    h->bry_doubles = n;
+    CK(cudaMalloc(&h->bry_buf, n * sizeof(double)));
+    CK(cudaMemset(h->bry_buf, 0, n * sizeof(double)));
+    double* cb = h->bry_buf;
+    for (int sd = 0; sd < 4; ++sd) {
+      const size_t L = BRYL(p, sd);
+      p.bry_zeta[sd] = cb; cb += L; p.bry_ubar[sd] = cb; cb += L; p.bry_vbar[sd] = cb; cb += L;
+      p.bry_u[sd] = cb; cb += L * N; p.bry_v[sd] = cb; cb += L * N; p.bry_t[sd] = cb; cb += L * N * NT;
+    }
+  }
   comm_init(&h->comm, cfg);
   *out = h;
   return 0;
@@ -382,6 +407,7 @@ int roms_destroy(roms_ctx* h) {
   cudaStreamSynchronize(h->st);
   comm_destroy(&h->comm);
   cudaFree(h->arena);
+  cudaFree(h->bry_buf);
   cudaFree(h->kpp_buf);
   for (int q = 0; q < 2; ++q) { if (h->ev_int[q]) cudaEventDestroy(h->ev_int[q]); if (h->ev_edge[q]) cudaEventDestroy(h->ev_edge[q]); }
   if (h->ev_join) cudaEventDestroy(h->ev_join);
@@ -407,13 +433,42 @@ static int find_slot(roms_ctx* h, int field, int lvl, int itrc, double** ptr, in
   *nk = s.nk;
   return 0;
 }
+// boundary data of the open edges: device line and its length for a ROMS_*_WEST ... ROMS_*_NORTH id (nullptr when no edge is open: the
+// data would never be read, pushes are accepted and dropped)
+static bool bry_field(roms_ctx* h, int field, int itrc, double** d, size_t* n) {
+  if (field < ROMS_ZETA_WEST || field > ROMS_T_NORTH) return false;
+  const KP& p = h->kp;
+  const int var = (field - ROMS_ZETA_WEST) / 4, sd = (field - ROMS_ZETA_WEST) % 4;
+  const size_t L = BRYL(p, sd);
+  *n = L * (var < 3 ? 1 : (size_t)p.N);
+  double* base = var == 0 ? p.bry_zeta[sd] : var == 1 ? p.bry_ubar[sd] : var == 2 ? p.bry_vbar[sd] : var == 3 ? p.bry_u[sd] : var == 4 ? p.bry_v[sd] : p.bry_t[sd];
+  if (var == 5 && base) {
+    const int t = (itrc >= 1 && itrc <= h->c.NT) ? itrc : 1;
+    base += (size_t)(t - 1) * L * p.N;
+  }
+  *d = base;
+  return true;
+}
+static int bry_xfer(roms_ctx* h, int field, int itrc, double* host, bool push, bool wait) {
+  double* d; size_t n;
+  bry_field(h, field, itrc, &d, &n);
+  if (!d) { if (!push) memset(host, 0, n * sizeof(double)); return 0; }
+  CK(cudaSetDevice(h->device));
+  if (push) CK(cudaMemcpyAsync(d, host, n * sizeof(double), cudaMemcpyHostToDevice, h->st));
+  else CK(cudaMemcpyAsync(host, d, n * sizeof(double), cudaMemcpyDeviceToHost, h->st));
+  if (wait) CK(cudaStreamSynchronize(h->st));
+  return 0;
+}
+#define IS_BRY(field) ((field) >= ROMS_ZETA_WEST && (field) <= ROMS_T_NORTH)
 long roms_field_count(roms_ctx* h, int field) {
   if (field < 0 || field >= ROMS_NFIELDS) return 0;
+  if (IS_BRY(field)) { double* d; size_t n; bry_field(h, field, 1, &d, &n); return (long)n; }
   return (long)(h->c.Lm + 4) * (h->c.Mm + 4) * h->f[field].nk;
 }
 int roms_push(roms_ctx* h, int field, int lvl, int itrc, const double* host) {
   FLUSH_RHO(h);
   if (join_st2(h)) return -1;
+  if (IS_BRY(field)) return bry_xfer(h, field, itrc, const_cast<double*>(host), true, true);
   double* d; int nk;
   if (find_slot(h, field, lvl, itrc, &d, &nk)) return -1;
   CK(cudaSetDevice(h->device));
@@ -425,6 +480,7 @@ int roms_push(roms_ctx* h, int field, int lvl, int itrc, const double* host) {
 int roms_pull(roms_ctx* h, int field, int lvl, int itrc, double* host) {
   FLUSH_RHO(h);
   if (join_st2(h)) return -1;
+  if (IS_BRY(field)) return bry_xfer(h, field, itrc, host, false, true);
   double* d; int nk;
   if (find_slot(h, field, lvl, itrc, &d, &nk)) return -1;
   CK(cudaSetDevice(h->device));
@@ -436,6 +492,7 @@ int roms_pull(roms_ctx* h, int field, int lvl, int itrc, double* host) {
 int roms_push_async(roms_ctx* h, int field, int lvl, int itrc, const double* host) {
   FLUSH_RHO(h);
   if (join_st2(h)) return -1;
+  if (IS_BRY(field)) return bry_xfer(h, field, itrc, const_cast<double*>(host), true, false);
   double* d; int nk;
   if (find_slot(h, field, lvl, itrc, &d, &nk)) return -1;
   CK(cudaSetDevice(h->device));
@@ -446,6 +503,7 @@ int roms_push_async(roms_ctx* h, int field, int lvl, int itrc, const double* hos
 int roms_pull_async(roms_ctx* h, int field, int lvl, int itrc, double* host) {
   FLUSH_RHO(h);
   if (join_st2(h)) return -1;
+  if (IS_BRY(field)) return bry_xfer(h, field, itrc, host, false, false);
   double* d; int nk;
   if (find_slot(h, field, lvl, itrc, &d, &nk)) return -1;
   CK(cudaSetDevice(h->device));
@@ -562,12 +620,27 @@ int roms_exchange(roms_ctx* h, int nfields, const int* fields, const int* lvls, 
   return comm_exchange(&h->comm, h->kp, h->st, v.data(), (int)v.size(), &h->launches);
 }
 
-// closed-wall boundary rows (u3dbc/v3dbc/t3dbc/omega copies): no-ops unless this subdomain touches a wall
-static int bc3d(roms_ctx* h, double* a, int nk, int kind) {
+// boundary rows of the 3-D fields (u3dbc/v3dbc/t3dbc/omega copies): no-ops unless this subdomain touches a non-periodic edge.
+// itrc: tracer (1-based) of a BC_T pass -- the open-edge rule needs t(nstp,itrc) and the tracer's boundary data.
+static int bc3d(roms_ctx* h, double* a, int nk, int kind, int itrc = 1) {
   const KP& p = h->kp;
   if (!p.swall && !p.nwall && !p.wwall && !p.ewall) return 0;
   const int len = (p.Lm > p.Mm ? p.Lm : p.Mm) + 3;
   dim3 b(128, 1, 1), g((len + 127) / 128, 4, nk);
+  if (p.bry3d && kind != BC_W) {      // at least one open edge: the general boundary kernels (obc.cuh) take every non-periodic edge
+    OB3 o;
+    o.a = a; o.ur = h->u(h->nrhs); o.vr = h->v(h->nrhs);
+    o.as = kind == BC_U ? h->u(h->nstp) : (kind == BC_V ? h->v(h->nstp) : h->t(h->nstp, itrc));
+    o.dtfwd = (h->nnew == 3) ? 0.5 * h->c.dt : h->c.dt;
+    o.itrc = itrc - 1;
+    if (h->ktiming) kt_begin(h, "k_bry3d");
+    if (kind == BC_U) k_bry3d<BC_U><<<g, b, 0, h->st>>>(p, o);
+    else if (kind == BC_V) k_bry3d<BC_V><<<g, b, 0, h->st>>>(p, o);
+    else k_bry3d<BC_T><<<g, b, 0, h->st>>>(p, o);
+    if (h->ktiming) kt_end(h);
+    h->launches++;
+    return 0;
+  }
   if (h->ktiming) kt_begin(h, "k_bc3d");
   const double g2 = h->c.gamma2;
   if (kind == BC_U) k_bc3d<BC_U><<<g, b, 0, h->st>>>(p, a, g2);
@@ -928,7 +1001,7 @@ int roms_pre_step3d(roms_ctx* h, int tile) {
   bc3d(h, h->u(nnew), p.N, BC_U);
   bc3d(h, h->v(nnew), p.N, BC_V);
   for (int it = 1; it <= h->c.NT; ++it) {
-    bc3d(h, h->t(nnew, it), p.N, BC_T);
+    bc3d(h, h->t(nnew, it), p.N, BC_T, it);
     int rc = exchange(h, {{h->t(nnew, it), p.N}});
     if (rc) return rc;
   }
@@ -1027,11 +1100,12 @@ int roms_step2d(roms_ctx* h) {
     else CK(cudaStreamWaitEvent(h->st, h->ev_edge[o], 0));
     S2D si = s, sr = s;
     si.region = 1; sr.region = 2;
-    if (h->s2d_tma == 12) {     // interior by the shipped marching kernel (its emit mask skips the ring)
+    const int s2mode_ = p.bry2d ? 0 : h->s2d_tma;   // the marching kernels carry the closed-wall code: open edges take the tile kernel
+    if (s2mode_ == 12) {     // interior by the shipped marching kernel (its emit mask skips the ring)
       int rc = s2d_hyb_launch(h, si, "k_step2d_hyb(interior)");
       if (rc) return rc;
       h->launches--;
-    } else if (h->s2d_tma >= 1 && h->s2d_tma <= 5) {
+    } else if (s2mode_ >= 1 && s2mode_ <= 5) {
       S2Planes ap;
       s2d_planes(p, s, ap);
       const int rows = h->s2d_rows > 0 ? h->s2d_rows : 16;
@@ -1053,7 +1127,12 @@ int roms_step2d(roms_ctx* h) {
     k_step2d<<<g_, b_, 0, h->st2>>>(p, sr);
     if (h->ktiming) kt_end(h, h->st2);
     h->launches += 2;
-    if (p.wwall || p.ewall) {
+    if (p.bry2d) {
+      const int len_ = (p.Lm > p.Mm ? p.Lm : p.Mm) + 3;
+      dim3 bw_(128, 1, 1), gw_((len_ + 127) / 128, 6, 1);
+      k_step2d_bry<<<gw_, bw_, 0, h->st2>>>(p, s);
+      h->launches++;
+    } else if (p.wwall || p.ewall) {
       dim3 bw_(128, 1, 1), gw_((p.jendR - p.jstrR + 1 + 127) / 128, 2, 1);
       k_step2d_ew<<<gw_, bw_, 0, h->st2>>>(p, s);
       h->launches++;
@@ -1068,7 +1147,19 @@ int roms_step2d(roms_ctx* h) {
     }
     return 0;
   }
-  if (h->s2d_tma == 12) {
+  if (p.bry2d) {
+    // open edges: interior by the tile kernel (it leaves every boundary point alone in this mode), then one thread per boundary point
+    dim3 b_(S2_TX, S2_TY, 1), g_((p.iend + IOFF + 1 + S2_TX - 1) / S2_TX, (p.jend - p.jstr + 1 + S2_TY - 1) / S2_TY, 1);
+    if (h->ktiming) kt_begin(h, "k_step2d");
+    k_step2d<<<g_, b_, 0, h->st>>>(p, s);
+    if (h->ktiming) kt_end(h);
+    const int len_ = (p.Lm > p.Mm ? p.Lm : p.Mm) + 3;
+    dim3 bw_(128, 1, 1), gw_((len_ + 127) / 128, 6, 1);
+    if (h->ktiming) kt_begin(h, "k_step2d_bry");
+    k_step2d_bry<<<gw_, bw_, 0, h->st>>>(p, s);
+    if (h->ktiming) kt_end(h);
+    h->launches += 2;
+  } else if (h->s2d_tma == 12) {
     int rc = s2d_hyb_launch(h, s, "k_step2d_hyb");
     if (rc) return rc;
   } else if (h->s2d_tma > 12) {
@@ -1142,7 +1233,7 @@ int roms_step2d(roms_ctx* h) {
     if (h->ktiming) kt_end(h);
     h->launches++;
   }
-  if (p.wwall || p.ewall) {
+  if (!p.bry2d && (p.wwall || p.ewall)) {
     dim3 b_(128, 1, 1), g_((p.jendR - p.jstrR + 1 + 127) / 128, 2, 1);
     if (h->ktiming) kt_begin(h, "k_step2d_ew");
     k_step2d_ew<<<g_, b_, 0, h->st>>>(p, s);
@@ -1162,7 +1253,7 @@ int roms_step3d_uv2(roms_ctx* h, int tile) {
   CK(cudaSetDevice(h->device));
   const KP& p = h->kp;
   const int nnew = h->nnew, nstp = h->nstp, knew = h->knew;
-  if (h->uv2_sm && h->uv2_fused) {
+  if (h->uv2_sm && h->uv2_fused && !p.bry3d) {
     // both passes in one kernel per direction; the wall rows / columns (u3dbc, v3dbc between the passes) first, from the original u(nnew)
     const double g2 = h->c.gamma2;
 #define UV2_EDGE(DIRn, arr, sarr, barr, a0, a1, b0, b1) COLUMN_SM((k_uv2_sm<DIRn, true>), a1, b0, b1, p, arr, sarr, barr, g2, a0, a1, b0, b1)
@@ -1209,7 +1300,7 @@ int roms_step3d_t(roms_ctx* h, int tile) {
     if (!rc) rc = tracer_vert(h, 1, pl, nrhs, nnew, h->c.dt);
     if (rc) return rc;
   }
-  for (int it = 1; it <= NT; ++it) bc3d(h, h->t(nnew, it), p.N, BC_T);   // t3dbc_tile (step3d_t_ISO.F:1157-1159)
+  for (int it = 1; it <= NT; ++it) bc3d(h, h->t(nnew, it), p.N, BC_T, it);   // t3dbc_tile (step3d_t_ISO.F:1157-1159)
   for (int it = 1; it + 1 <= NT; it += 2) {
     int rc = exchange(h, {{h->t(nnew, it), p.N}, {h->t(nnew, it + 1), p.N}});
     if (rc) return rc;
