@@ -28,6 +28,8 @@ def main():
     npx, npe = cases.rank_grid(world)
     if mode == "kpp":        # the reference's Rivers_ana case with the KPP closure on, cut into blocks
         return main_kpp(nsteps, rank, world, local, npx, npe)
+    if mode == "obc":        # four open edges (Flather / Orlanski, exterior clamped to the initial state), cut into blocks
+        return main_obc(nsteps, rank, world, local, npx, npe)
     LG, MG, N = 24 * npx, 20 * npe, 10
     if mode.startswith("uneven"):       # blocks of unequal size (mpi_setup.F:117-160): 3 points short in xi, 1 in eta
         LG, MG = LG - (3 if npx > 1 else 0), MG - (1 if npe > 1 else 0)
@@ -89,6 +91,39 @@ def main_kpp(nsteps, rank, world, local, npx, npe):
         worst = max(worst, np.linalg.norm((a - b).ravel()) / max(np.linalg.norm(b.ravel()), 1e-300))
     ok = worst <= 1e-11 and np.allclose(dg, do, rtol=1e-10, atol=1e-18)
     print(f"rank {rank}/{world}: KPP case, worst relative L2 vs single-domain oracle after {nsteps} steps = {worst:.2e}; diag gpu {dg} oracle {do}", flush=True)
+    t = torch.tensor([0 if ok else 1], device="cuda")
+    dist.all_reduce(t)
+    g.close()
+    dist.destroy_process_group()
+    sys.exit(int(t.item() != 0))
+
+
+def main_obc(nsteps, rank, world, local, npx, npe):
+    cfgG, stG = cases.channel(28 * npx, 22 * npe, 10, ns_walls=True, ew_walls=True, seamount=True, island=True, open_edges="WESN", dt=60.0, ndtfast=30, depth=500.0)
+    cfg, st = cases.take_block(cfgG, stG, (rank % npx, rank // npx, npx, npe))
+    g = Roms(cfg, local)
+    g.attach_torch_comm(dist)
+    cases.initialize(g, st)
+    g.call("run", nsteps)
+    dg = g.diag()
+    o = Oracle(cfgG)
+    cases.initialize(o, stG)
+    o.call("run", nsteps)
+    do = o.diag()
+    iic, iif, nstp, nrhs, nnew, kstp, knew = g.get_idx()
+    Lm, Mm = cfg.Lm, cfg.Mm
+    i0, j0 = cases.block_extent(cfgG.Lm, npx, rank % npx)[1], cases.block_extent(cfgG.Mm, npe, rank // npx)[1]
+    worst = 0.0
+    for f, l, it in [("ZETA", knew, 1), ("UBAR", knew, 1), ("VBAR", knew, 1), ("U", nnew, 1), ("V", nnew, 1), ("T", nnew, 1), ("T", nnew, 2), ("DU_AVG1", 1, 1), ("DV_AVG2", 1, 1),
+                     ("FLXU", 1, 1)]:
+        # the block's interior plus the boundary points of the open edges it touches (halo values of the averages are not exchanged)
+        ia, ib = (1 if rank % npx == 0 else 2), (Lm + 3 if rank % npx == npx - 1 else Lm + 2)
+        ja, jb = (1 if rank // npx == 0 else 2), (Mm + 3 if rank // npx == npe - 1 else Mm + 2)
+        a = g.pull(f, l, it)[..., ja:jb, ia:ib]
+        b = o.pull(f, l, it)[..., j0 + ja:j0 + jb, i0 + ia:i0 + ib]
+        worst = max(worst, np.linalg.norm((a - b).ravel()) / max(np.linalg.norm(b.ravel()), 1e-300))
+    ok = worst <= 1e-12 and np.allclose(dg, do, rtol=1e-11, atol=1e-18)
+    print(f"rank {rank}/{world}: open-boundary case, worst relative L2 vs single-domain oracle after {nsteps} steps = {worst:.2e}; diag gpu {dg} oracle {do}", flush=True)
     t = torch.tensor([0 if ok else 1], device="cuda")
     dist.all_reduce(t)
     g.close()

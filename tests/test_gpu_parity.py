@@ -459,7 +459,7 @@ def test_two_gpu_halo_exchange_parity():
     r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
                         "--master-port", "29735", script, "3", "closedmix"], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
-    for port, mode in ((29736, "uneven"), (29737, "unevenclosed"), (29738, "river"), (29739, "kpp")):      # blocks of unequal size (mpi_setup.F:117-160); river source
+    for port, mode in ((29736, "uneven"), (29737, "unevenclosed"), (29738, "river"), (29739, "kpp"), (29740, "obc")):      # blocks of unequal size (mpi_setup.F:117-160); river source; KPP; open edges
         r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
                             "--master-port", str(port), script, "3", mode], capture_output=True, text=True, timeout=600)
         assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]

@@ -429,12 +429,16 @@ def take_block(cfg, state, sub):
     c = copy.copy(cfg)
     c.Lm, c.Mm, c.np_xi, c.np_eta, c.inode, c.jnode = Lm, Mm, np_xi, np_eta, inode, jnode
     cut = lambda a: np.ascontiguousarray(a[..., j0:j0 + Mm + 4, i0:i0 + Lm + 4])
+    cut_j = lambda a: np.ascontiguousarray(a[..., j0:j0 + Mm + 4])      # boundary data of the western / eastern edge: lines over j
+    cut_i = lambda a: np.ascontiguousarray(a[..., i0:i0 + Lm + 4])      # southern / northern edge: lines over i
     st = {}
     for k, v in state.items():
+        side = k.rsplit("_", 1)[-1]
+        f = cut_j if side in ("WEST", "EAST") else cut_i if side in ("SOUTH", "NORTH") else cut
         if isinstance(v, dict):
-            st[k] = {kk: cut(a) for kk, a in v.items()}
+            st[k] = {kk: f(a) for kk, a in v.items()}
         elif isinstance(v, np.ndarray):
-            st[k] = cut(v)
+            st[k] = f(v)
         else:
             st[k] = v
     return c, st
