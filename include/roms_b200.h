@@ -92,8 +92,9 @@ enum roms_field {
   ROMS_SRFLX,                                    /* surf_flux.F srflx: shortwave radiation flux [degC m/s], part of stflx(itemp); with KPP on it
                                                     penetrates by swr_frac (step3d_t_ISO.F:961-998, lmd_kpp.F:160-167); zero unless pushed */
   /* boundary data of the open edges (boundary.F:21-60 zeta_west(j), ubar_west(j), vbar_west(j), u_west(j,k), v_west(j,k),
-     t_west(j,k,itrc) and their east/south/north counterparts): lines along the edge with the same 2-cell margin as the planes --
-     Mm+4 values (west, east) or Lm+4 values (south, north), times N levels for the 3-D ones (level-major).  Id = base + side,
+     t_west(j,k,itrc) and their east/south/north counterparts): lines along the edge with the reference's own extents
+     (boundary.F:111-131: zeta_west(0:Mm+1), u_west(0:Mm+1,N), t_south(0:Lm+1,N,NT) ...) -- Mm+2 values (west, east) or Lm+2 values
+     (south, north), times N levels for the 3-D ones (level-major, i.e. the Fortran (j,k) order).  Id = base + side,
      side 0 west, 1 east, 2 south, 3 north.  Zero unless pushed. */
   ROMS_ZETA_WEST, ROMS_ZETA_EAST, ROMS_ZETA_SOUTH, ROMS_ZETA_NORTH,
   ROMS_UBAR_WEST, ROMS_UBAR_EAST, ROMS_UBAR_SOUTH, ROMS_UBAR_NORTH,

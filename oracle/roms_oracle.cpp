@@ -6,6 +6,9 @@
 // Parity pin: the restatement reproduces the reference's golden regression log
 // tests/Filament/benchmark.result_github_gnu:146-167 (KINETIC_ENRG, BAROTR_KE, MAX_ADV_CFL,
 // MAX_VERT_CFL for steps 0..20); see tests/test_oracle_golden.py.
+// PARITY UNPINNED for the open-boundary branches (cfg.obc_*: zetabc, u2dbc, v2dbc, u3dbc, v3dbc, t3dbc under OBC_M2FLATHER /
+// OBC_M3ORLANSKI / OBC_TORLANSKI): every reference case with an open edge needs netCDF input that is not in the reference tree, so no
+// golden log covers them; tests/test_open_boundaries.py holds the physical properties that stand in (radiation, transparency).
 //
 // Each function follows the switch-resolved Fortran that the reference's own pre-processing
 // (cpp -traditional | Tools-Roms/mpc_python/mpc.py) emits for the Filament configuration
@@ -74,18 +77,18 @@ struct Orc {
   bool pot_tides = false;
   vec xr;  // only for the Filament analytic initial condition
   std::vector<vec> s2d;
-  // boundary.F:21-60: data of the open edges, side 0 west, 1 east (index j), 2 south, 3 north (index i); lines with the planes' margin
+  // boundary.F:21-60: data of the open edges, side 0 west, 1 east (index j = 0:Mm+1), 2 south, 3 north (index i = 0:Lm+1), the reference's own extents
   vec zeta_bry[4], ubar_bry[4], vbar_bry[4], u_bry[4], v_bry[4];
   std::vector<vec> t_bry[4];
-  int bryL(int side) const { return side < 2 ? SY : SX; }
+  int bryL(int side) const { return side < 2 ? Mm + 2 : Lm + 2; }      // boundary.F:111-131: zeta_west(0:Mm+1), u_south(0:Lm+1,N) ...
 };
 
 #define A2(a, i, j) (a)[(size_t)((i) + 1) + (size_t)((j) + 1) * SX]
 #define A3(a, i, j, k) (a)[(size_t)((i) + 1) + (size_t)((j) + 1) * SX + (size_t)((k)-1) * SXY]
 #define AW(a, i, j, k) (a)[(size_t)((i) + 1) + (size_t)((j) + 1) * SX + (size_t)(k) * SXY]
 #define SL(a, i, k) (a)[(size_t)((i) + 1) + (size_t)(k) * SX]   // (i,k) slab scratch, k=0:N
-#define B1(a, q) (a)[(size_t)((q) + 1)]                                   // boundary line: zeta_west(j), ubar_south(i) ...
-#define B2(a, q, k, L) (a)[(size_t)((q) + 1) + (size_t)((k)-1) * (L)]     // u_west(j,k), t_south(i,k) ...
+#define B1(a, q) (a)[(size_t)(q)]                                         // boundary line (0:Mm+1) or (0:Lm+1): zeta_west(j), ubar_south(i) ...
+#define B2(a, q, k, L) (a)[(size_t)(q) + (size_t)((k)-1) * (L)]           // u_west(j,k), t_south(i,k) ...
 static inline bool riv_on(double code) { return std::fabs(code) > 1e-3; }
 static inline int riv_id(double code) { return (int)std::lround(code / 10); }   // nint(riv_uflx/10)
 

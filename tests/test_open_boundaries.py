@@ -50,7 +50,7 @@ def test_uniform_throughflow_is_transparent(U0, V0):
     for nm, val in (("U", U0), ("V", V0)):
         st[nm + "BAR"] = {(1, 1): np.full((sy, sx), val), (2, 1): np.full((sy, sx), val)}
         st[nm] = {(1, 1): np.full((N, sy, sx), val), (2, 1): np.full((N, sy, sx), val)}
-        for side, L in (("WEST", sy), ("EAST", sy), ("SOUTH", sx), ("NORTH", sx)):
+        for side, L in (("WEST", sy - 2), ("EAST", sy - 2), ("SOUTH", sx - 2), ("NORTH", sx - 2)):
             st[nm + "BAR_" + side] = np.full(L, val)
             st[nm + "_" + side] = np.full((N, L), val)
     o = Oracle(cfg)
@@ -73,8 +73,8 @@ def test_closed_flags_off_is_the_old_path():
     for push_bry in (False, True):
         cfg, st = cases.channel(Lm=24, Mm=20, N=6, ns_walls=True, ew_walls=True, seamount=True)
         if push_bry:
-            st["ZETA_WEST"] = np.full(cfg.Mm + 4, 0.3)
-            st["U_EAST"] = np.full((cfg.N, cfg.Mm + 4), 0.2)
+            st["ZETA_WEST"] = np.full(cfg.Mm + 2, 0.3)
+            st["U_EAST"] = np.full((cfg.N, cfg.Mm + 2), 0.2)
         o = Oracle(cfg)
         cases.initialize(o, st)
         for n in range(5):

@@ -67,11 +67,11 @@ struct KP {
   // edge is open; ROMS_BRY=1 forces it for closed basins, which validates those kernels against the in-kernel wall code).
   int obc, bry2d, bry3d;
   double ubind;
-  // boundary.F:21-60 boundary data, side 0 west, 1 east (lines over j), 2 south, 3 north (lines over i), index q+1 for q=-1..; the 3-D
-  // ones level-major [k-1][q+1]; bry_t: [itrc][k-1][q+1]
+  // boundary.F:21-60 boundary data, side 0 west, 1 east (lines over j = 0:Mm+1), 2 south, 3 north (lines over i = 0:Lm+1), the reference's
+  // extents (boundary.F:111-131); the 3-D ones level-major [k-1][q]; bry_t: [itrc][k-1][q]
   double *bry_zeta[4], *bry_ubar[4], *bry_vbar[4], *bry_u[4], *bry_v[4], *bry_t[4];
 };
-#define BRYL(p, side) ((side) < 2 ? (p).Mm + 4 : (p).Lm + 4)
+#define BRYL(p, side) ((side) < 2 ? (p).Mm + 2 : (p).Lm + 2)
 
 // column base index of (i,j) and relative addressing
 #define CIDX(i, j) ((ix_t)((i) + IOFF) + (ix_t)((j) + 1) * p.SX)

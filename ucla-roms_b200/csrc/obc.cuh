@@ -13,8 +13,8 @@
 // west/south and at nnew on the east/north).
 #pragma once
 
-#define OB_B1(a, q) (a)[(q) + 1]
-#define OB_B2(a, q, k, L) (a)[(q) + 1 + ((k)-1) * (L)]
+#define OB_B1(a, q) (a)[(q)]
+#define OB_B2(a, q, k, L) (a)[(q) + ((k)-1) * (L)]
 __device__ __forceinline__ bool ob_open(const KP& p, int side) { return (p.obc >> side) & 1; }
 __device__ __forceinline__ double ob_max0(double a) { return (a < 0.) ? 0. : a; }     // max(a,0.) / min(a,0.) with the value returned for a = -0.
 __device__ __forceinline__ double ob_min0(double a) { return (0. < a) ? 0. : a; }     // spelled out, so that both sides of the parity test agree

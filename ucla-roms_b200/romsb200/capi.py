@@ -62,7 +62,7 @@ class CApi:
     def shape(self, field):
         side = field.rsplit("_", 1)[-1]
         if side in ("WEST", "EAST", "SOUTH", "NORTH"):       # boundary data: a line along the edge (times N levels)
-            L = self.shape2[0] if side in ("WEST", "EAST") else self.shape2[1]
+            L = (self.shape2[0] if side in ("WEST", "EAST") else self.shape2[1]) - 2     # zeta_west(0:Mm+1), ubar_south(0:Lm+1)
             n = self.count(field) // L
             return (L,) if n == 1 else (n, L)
         n = self.count(field) // (self.shape2[0] * self.shape2[1])

@@ -216,7 +216,7 @@ def channel(Lm=64, Mm=64, N=16, NT=2, ns_walls=False, nonlin_eos=True, dt=120.0,
                 "S": lambda a, face: a[..., 2 if face else 1, :], "N": lambda a, face: a[..., Mm + 2, :]}
         name = {"W": "WEST", "E": "EAST", "S": "SOUTH", "N": "NORTH"}
         for e in open_edges:
-            cut = lambda a, face=False: np.ascontiguousarray(line[e](a, face))
+            cut = lambda a, face=False: np.ascontiguousarray(line[e](a, face)[..., 1:-1])      # (0:Mm+1) / (0:Lm+1)
             st["ZETA_" + name[e]] = cut(zeta)
             st["UBAR_" + name[e]] = cut(ubar, e == "W"); st["VBAR_" + name[e]] = cut(vbar, e == "S")
             st["U_" + name[e]] = cut(u, e == "W"); st["V_" + name[e]] = cut(v, e == "S")
@@ -271,7 +271,7 @@ def pulse_box(Lm=64, Mm=64, N=4, open_edges="WESN", dx=1.0e3, depth=100.0, dt=60
           "AKV": np.zeros((N + 1, sy, sx)), "AKT": {(1, 1): np.zeros((N + 1, sy, sx)), (1, 2): np.zeros((N + 1, sy, sx))}}
     for e, nm in (("W", "WEST"), ("E", "EAST"), ("S", "SOUTH"), ("N", "NORTH")):
         if e in open_edges:
-            L = sy if e in "WE" else sx
+            L = (sy if e in "WE" else sx) - 2
             st["T_" + nm] = {(1, 1): np.full((N, L), 10.0), (1, 2): np.full((N, L), 35.0)}     # the other boundary data stay zero
     return cfg, st
 
@@ -429,8 +429,8 @@ def take_block(cfg, state, sub):
     c = copy.copy(cfg)
     c.Lm, c.Mm, c.np_xi, c.np_eta, c.inode, c.jnode = Lm, Mm, np_xi, np_eta, inode, jnode
     cut = lambda a: np.ascontiguousarray(a[..., j0:j0 + Mm + 4, i0:i0 + Lm + 4])
-    cut_j = lambda a: np.ascontiguousarray(a[..., j0:j0 + Mm + 4])      # boundary data of the western / eastern edge: lines over j
-    cut_i = lambda a: np.ascontiguousarray(a[..., i0:i0 + Lm + 4])      # southern / northern edge: lines over i
+    cut_j = lambda a: np.ascontiguousarray(a[..., j0:j0 + Mm + 2])      # boundary data of the western / eastern edge: lines over j = 0:Mm+1
+    cut_i = lambda a: np.ascontiguousarray(a[..., i0:i0 + Lm + 2])      # southern / northern edge: lines over i = 0:Lm+1
     st = {}
     for k, v in state.items():
         side = k.rsplit("_", 1)[-1]
