@@ -80,7 +80,10 @@ struct Orc {
   // boundary.F:21-60: data of the open edges, side 0 west, 1 east (index j = 0:Mm+1), 2 south, 3 north (index i = 0:Lm+1), the reference's own extents
   vec zeta_bry[4], ubar_bry[4], vbar_bry[4], u_bry[4], v_bry[4];
   std::vector<vec> t_bry[4];
-  int bryL(int side) const { return side < 2 ? Mm + 2 : Lm + 2; }      // boundary.F:111-131: zeta_west(0:Mm+1), u_south(0:Lm+1,N) ...
+  int bryL(int side) const { return side < 2 ? Mm + 2 : Lm + 2; }
+  // Emulation of a set-up artifact of the reference's OWN Rivers_ana run (see step2d): first owned column / row of every MPI block
+  // that has a western / southern neighbour in that run (3x2 blocks of 100x100: columns 34, 68, row 51).  Empty = off.
+  std::vector<int> hbug_i, hbug_j;      // boundary.F:111-131: zeta_west(0:Mm+1), u_south(0:Lm+1,N) ...
 };
 
 #define A2(a, i, j) (a)[(size_t)((i) + 1) + (size_t)((j) + 1) * SX]
@@ -1584,6 +1587,56 @@ void step2d(Orc& o) {
       A2(VFe, i, j) = A2(UFe, i, j) * A2(UFx, i, j);
     }
   zetabc(o, zeta_new);
+  // ---- the reference's Rivers_ana log was produced on 3x2 MPI blocks by a set-up that leaves h = 0 (init_scalars.F:31) in the SECOND
+  // halo line of every block: tests/Rivers_ana/ana_grid.h fills 0:nx+1, 0:ny+1 only (tests/Pipes_ana/ana_grid.h fills -1:nx+2) and an
+  // analytic grid is never exchanged (grid.F:444-446, unlike the netCDF branch :580-613).  The one place that reads h there is
+  // Drhs(istrU-2,j), Drhs(i,jstrV-2) above (step2d_FB.F:96-101): a block with a western (southern) neighbour forms DUon(istr-1,j)
+  // (DVom(i,jstr-1)) with half the depth, so its PRIVATE zeta_new on its first halo line is off, and with it rubar/Dnew at its first
+  // u-column (rvbar at its first v-row).  Its neighbour computes the same point correctly for itself, so the artifact exists only in
+  // the decomposed run.  hbug_i / hbug_j switch on an emulation: shadow values of zeta_new at (i0-1,j) and (i,j0-1) as that block sees them.
+  const int nbi = (int)o.hbug_i.size(), nbj = (int)o.hbug_j.size();
+  std::vector<vec> znW(nbi, vec(o.SY, 0.0)), znS(nbj, vec(o.SX, 0.0));
+  for (int b = 0; b < nbi; ++b) {
+    const int i0 = o.hbug_i[b];
+    for (int j = jstrV - 1; j <= jend; ++j) {
+      const double Drhs_far = fwd * A2(zs, i0 - 2, j) + fwd1 * A2(zb, i0 - 2, j) + fwd2 * A2(zo, i0 - 2, j);      // h(i0-2,j) = 0 in that block
+      const double DUon_b = 0.5 * (A2(Drhs, i0 - 1, j) + Drhs_far) * A2(o.dn_u, i0 - 1, j) * (A2(urhs, i0 - 1, j));
+      double z = A2(zs, i0 - 1, j) + dtfast * A2(o.pm, i0 - 1, j) * A2(o.pn, i0 - 1, j) * (DUon_b - A2(DUon, i0, j) + A2(DVom, i0 - 1, j) - A2(DVom, i0 - 1, j + 1)) +
+                 dtfast * A2(o.swflx, i0 - 1, j);
+      if (o.pipe_source && A2(o.pipe_idx, i0 - 1, j) > 0.) z = z + dtfast * A2(o.pm, i0 - 1, j) * A2(o.pn, i0 - 1, j) * A2(o.pipe_flx, i0 - 1, j);
+      znW[b][j + 1] = z * A2(o.rmask, i0 - 1, j);
+    }
+  }
+  for (int b = 0; b < nbj; ++b) {
+    const int j0 = o.hbug_j[b];
+    for (int i = istrU - 1; i <= iend; ++i) {
+      const double Drhs_far = fwd * A2(zs, i, j0 - 2) + fwd1 * A2(zb, i, j0 - 2) + fwd2 * A2(zo, i, j0 - 2);
+      const double DVom_b = 0.5 * (A2(Drhs, i, j0 - 1) + Drhs_far) * A2(o.dm_v, i, j0 - 1) * (A2(vrhs, i, j0 - 1));
+      double z = A2(zs, i, j0 - 1) + dtfast * A2(o.pm, i, j0 - 1) * A2(o.pn, i, j0 - 1) * (A2(DUon, i, j0 - 1) - A2(DUon, i + 1, j0 - 1) + DVom_b - A2(DVom, i, j0)) +
+                 dtfast * A2(o.swflx, i, j0 - 1);
+      if (o.pipe_source && A2(o.pipe_idx, i, j0 - 1) > 0.) z = z + dtfast * A2(o.pm, i, j0 - 1) * A2(o.pn, i, j0 - 1) * A2(o.pipe_flx, i, j0 - 1);
+      znS[b][i + 1] = z * A2(o.rmask, i, j0 - 1);
+    }
+  }
+  auto bug_i = [&](int i) { for (int b = 0; b < nbi; ++b) if (o.hbug_i[b] == i) return b; return -1; };
+  auto bug_j = [&](int j) { for (int b = 0; b < nbj; ++b) if (o.hbug_j[b] == j) return b; return -1; };
+  // the four pressure-gradient ingredients of a rho-point from a given zeta_new (main set; corr: the first-substep correction set)
+  struct Pt4 { double UFx, UFe, VFx, VFe; };
+  auto pt4 = [&](double zn_, int i, int j, bool corr) {
+    Pt4 r;
+    if (!corr) {
+      r.UFx = bkw_new * zn_ + bkw * A2(zs, i, j) + bkw1 * A2(zb, i, j) + bkw2 * A2(zo, i, j);
+      r.UFe = (1.0 + A2(o.rhoS, i, j)) * r.UFx;
+      r.VFx = r.UFx * (A2(o.rhoS, i, j) - A2(o.rhoA, i, j));
+      r.VFe = r.UFe * r.UFx;
+    } else {
+      r.UFx = zn_ - A2(zs, i, j);
+      r.UFe = (1.0 + A2(o.rhoS, i, j)) * r.UFx;
+      r.VFe = r.UFe * (zn_ + A2(zs, i, j));
+      r.VFx = r.UFx * (A2(o.rhoS, i, j) - A2(o.rhoA, i, j));
+    }
+    return r;
+  };
   for (int j = jstrR; j <= jendR; ++j)
     for (int i = istrR; i <= iendR; ++i) A2(zn, i, j) = A2(zeta_new, i, j);
   double cff1 = o.weight1[iif], cff2 = o.weight2[iif];
@@ -1617,6 +1670,23 @@ void step2d(Orc& o) {
                         ((A2(o.h, i, j - 1) + A2(o.h, i, j)) * (A2(UFe, i, j - 1) - A2(UFe, i, j)) + A2(VFe, i, j - 1) - A2(VFe, i, j) +
                          (A2(o.h, i, j - 1) - A2(o.h, i, j)) * (A2(VFx, i, j - 1) + A2(VFx, i, j) + 0.333333333333 * (A2(o.rhoA, i, j - 1) - A2(o.rhoA, i, j)) * (A2(UFx, i, j - 1) - A2(UFx, i, j))));
     }
+  auto pgf_u = [&](const Pt4& a, int i, int j) {     // rubar(i,j) with the western neighbour's ingredients a
+    return cff * A2(o.dn_u, i, j) *
+           ((A2(o.h, i - 1, j) + A2(o.h, i, j)) * (a.UFe - A2(UFe, i, j)) + a.VFe - A2(VFe, i, j) +
+            (A2(o.h, i - 1, j) - A2(o.h, i, j)) * (a.VFx + A2(VFx, i, j) + 0.333333333333 * (A2(o.rhoA, i - 1, j) - A2(o.rhoA, i, j)) * (a.UFx - A2(UFx, i, j))));
+  };
+  auto pgf_v = [&](const Pt4& a, int i, int j) {     // rvbar(i,j) with the southern neighbour's ingredients a
+    return cff * A2(o.dm_v, i, j) *
+           ((A2(o.h, i, j - 1) + A2(o.h, i, j)) * (a.UFe - A2(UFe, i, j)) + a.VFe - A2(VFe, i, j) +
+            (A2(o.h, i, j - 1) - A2(o.h, i, j)) * (a.VFx + A2(VFx, i, j) + 0.333333333333 * (A2(o.rhoA, i, j - 1) - A2(o.rhoA, i, j)) * (a.UFx - A2(UFx, i, j))));
+  };
+  for (int b = 0; b < nbi; ++b)
+    for (int j = jstr; j <= jend; ++j) A2(rubar, o.hbug_i[b], j) = pgf_u(pt4(znW[b][j + 1], o.hbug_i[b] - 1, j, false), o.hbug_i[b], j);
+  for (int b = 0; b < nbj; ++b)
+    for (int i = istr; i <= iend; ++i) A2(rvbar, i, o.hbug_j[b]) = pgf_v(pt4(znS[b][i + 1], i, o.hbug_j[b] - 1, false), i, o.hbug_j[b]);
+  std::vector<vec> rub_main(nbi, vec(o.SY, 0.0)), rvb_main(nbj, vec(o.SX, 0.0));
+  for (int b = 0; b < nbi; ++b) for (int j = jstr; j <= jend; ++j) rub_main[b][j + 1] = A2(rubar, o.hbug_i[b], j);
+  for (int b = 0; b < nbj; ++b) for (int i = istr; i <= iend; ++i) rvb_main[b][i + 1] = A2(rvbar, i, o.hbug_j[b]);
   if (iif == 1) {
     for (int j = jstr; j <= jend; ++j)
       for (int i = istr; i <= iend; ++i) {
@@ -1643,6 +1713,12 @@ void step2d(Orc& o) {
                                (A2(o.h, i, j - 1) - A2(o.h, i, j)) * (A2(VFx, i, j - 1) + A2(VFx, i, j) + 0.333333333333 * (A2(o.rhoA, i, j - 1) - A2(o.rhoA, i, j)) * (A2(UFx, i, j - 1) - A2(UFx, i, j))));
       }
   }
+  if (iif == 1) {      // the first-substep correction of the artifact columns / rows, again with the block's own halo zeta_new
+    for (int b = 0; b < nbi; ++b)
+      for (int j = jstr; j <= jend; ++j) A2(rubar, o.hbug_i[b], j) = rub_main[b][j + 1] + pgf_u(pt4(znW[b][j + 1], o.hbug_i[b] - 1, j, true), o.hbug_i[b], j);
+    for (int b = 0; b < nbj; ++b)
+      for (int i = istr; i <= iend; ++i) A2(rvbar, i, o.hbug_j[b]) = rvb_main[b][i + 1] + pgf_v(pt4(znS[b][i + 1], i, o.hbug_j[b] - 1, true), i, o.hbug_j[b]);
+  }
   for (int j = jstrV - 1; j <= jend; ++j)
     for (int i = istrU - 1; i <= iend; ++i) A2(DUon, i, j) = A2(zs, i, j) + A2(o.h, i, j);
   cff = 0.5 * dtfast;
@@ -1653,7 +1729,9 @@ void step2d(Orc& o) {
       double DUnew = ((A2(DUon, i, j) + A2(DUon, i - 1, j)) * A2(us, i, j) +
                       cff * (A2(o.pm, i, j) + A2(o.pm, i - 1, j)) * (A2(o.pn, i, j) + A2(o.pn, i - 1, j)) * (A2(rubar, i, j) + A2(o.rufrc, i, j))) *
                      A2(o.umask, i, j);
-      A2(un, i, j) = DUnew / (A2(Dnew, i, j) + A2(Dnew, i - 1, j));
+      double Dnew_w = A2(Dnew, i - 1, j);
+      if (nbi) { const int b = bug_i(i); if (b >= 0) Dnew_w = znW[b][j + 1] + A2(o.h, i - 1, j); }
+      A2(un, i, j) = DUnew / (A2(Dnew, i, j) + Dnew_w);
       A2(o.DU_avg1, i, j) = A2(o.DU_avg1, i, j) + cff1 * A2(o.dn_u, i, j) * (DUnew);
     }
     if (j >= jstrV)
@@ -1661,7 +1739,9 @@ void step2d(Orc& o) {
       double DVnew = ((A2(DUon, i, j) + A2(DUon, i, j - 1)) * A2(vs, i, j) +
                       cff * (A2(o.pm, i, j) + A2(o.pm, i, j - 1)) * (A2(o.pn, i, j) + A2(o.pn, i, j - 1)) * (A2(rvbar, i, j) + A2(o.rvfrc, i, j))) *
                      A2(o.vmask, i, j);
-      A2(vn, i, j) = DVnew / (A2(Dnew, i, j) + A2(Dnew, i, j - 1));
+      double Dnew_s = A2(Dnew, i, j - 1);
+      if (nbj) { const int b = bug_j(j); if (b >= 0) Dnew_s = znS[b][i + 1] + A2(o.h, i, j - 1); }
+      A2(vn, i, j) = DVnew / (A2(Dnew, i, j) + Dnew_s);
       A2(o.DV_avg1, i, j) = A2(o.DV_avg1, i, j) + cff1 * A2(o.dm_v, i, j) * (DVnew);
     }
   }
@@ -2659,6 +2739,12 @@ int orc_set_kpp(void* h, int on) { ((Orc*)h)->lmd_kpp = on != 0; ((Orc*)h)->lmd_
 int orc_set_kpp_opts(void* h, int lmd_convec, double Akv_bak, double Akt_bak_T, double Akt_bak_S) {
   Orc& o = *(Orc*)h;
   o.lmd_convec = lmd_convec != 0; o.Akv_bak = Akv_bak; o.Akt_bak[0] = Akt_bak_T; o.Akt_bak[1] = Akt_bak_S;
+  return 0;
+}
+// Emulate the halo artifact of the reference's own decomposed Rivers_ana run (see step2d): ni first-owned columns, nj first-owned rows
+int orc_set_block_halo_artifact(void* h, int ni, const int* bi, int nj, const int* bj) {
+  Orc& o = *(Orc*)h;
+  o.hbug_i.assign(bi, bi + ni); o.hbug_j.assign(bj, bj + nj);
   return 0;
 }
 int orc_get_hbl(void* h, double* hbls, double* hbbl) {

@@ -36,5 +36,15 @@ class Oracle(CApi):
             self.lib.orc_destroy(self.h)
             self.h = None
 
+    def set_block_halo_artifact(self, np_xi, np_eta):
+        """Emulate the set-up artifact of the reference's OWN decomposed Rivers_ana run (oracle step2d): that run leaves
+        h = 0 in the second halo line of each of its np_xi x np_eta MPI blocks, which halves Drhs(istr-2,j) / Drhs(i,jstr-2) of every block
+        with a western / southern neighbour.  Columns and rows are the first owned ones of those blocks (mpi_setup.F:117-160)."""
+        bi = [cases.block_extent(self.cfg.Lm, np_xi, n)[1] + 1 for n in range(1, np_xi)]
+        bj = [cases.block_extent(self.cfg.Mm, np_eta, n)[1] + 1 for n in range(1, np_eta)]
+        self._check(self.lib.orc_set_block_halo_artifact(self.h, len(bi), (C.c_int * max(len(bi), 1))(*bi), len(bj), (C.c_int * max(len(bj), 1))(*bj)),
+                    "set_block_halo_artifact")
+        return bi, bj
+
     def exchange(self, field, lvl=1, itrc=1):
         self.call("exchange", FID[field], lvl, itrc)
