@@ -28,6 +28,8 @@ def main():
     npx, npe = cases.rank_grid(world)
     if mode == "kpp":        # the reference's Rivers_ana case with the KPP closure on, cut into blocks
         return main_kpp(nsteps, rank, world, local, npx, npe)
+    if mode == "reflog":     # the reference's own Rivers_ana run: 3x2 blocks, h = 0 in the second halo line of every block
+        return main_reflog(nsteps, rank, world, local)
     if mode == "obc":        # four open edges (Flather / Orlanski, exterior clamped to the initial state), cut into blocks
         return main_obc(nsteps, rank, world, local, npx, npe)
     LG, MG, N = 24 * npx, 20 * npe, 10
@@ -91,6 +93,45 @@ def main_kpp(nsteps, rank, world, local, npx, npe):
         worst = max(worst, np.linalg.norm((a - b).ravel()) / max(np.linalg.norm(b.ravel()), 1e-300))
     ok = worst <= 1e-11 and np.allclose(dg, do, rtol=1e-10, atol=1e-18)
     print(f"rank {rank}/{world}: KPP case, worst relative L2 vs single-domain oracle after {nsteps} steps = {worst:.2e}; diag gpu {dg} oracle {do}", flush=True)
+    t = torch.tensor([0 if ok else 1], device="cuda")
+    dist.all_reduce(t)
+    g.close()
+    dist.destroy_process_group()
+    sys.exit(int(t.item() != 0))
+
+
+def main_reflog(nsteps, rank, world, local):
+    """Six ranks decomposed exactly like the run that wrote tests/Rivers_ana/benchmark.result_github_gnu (NP_XI=3, NP_ETA=2,
+    tests/Rivers_ana/param.opt), each block given the bathymetry the way that run had it: tests/Rivers_ana/ana_grid.h fills 0:nx+1 x
+    0:ny+1, the second halo line keeps init = 0 and an analytic grid is never exchanged (grid.F:444-446).  With that input the CUDA
+    path must reproduce the reference's log itself -- all 21 lines x 4 columns -- not just the oracle."""
+    import json
+    assert world == 6, "the reference's Rivers_ana log was written by 6 ranks"
+    npx, npe = 3, 2
+    cfgG, stG = cases.rivers_ana(kpp=True)
+    cfg, st = cases.take_block(cfgG, stG, (rank % npx, rank // npx, npx, npe))
+    h = st["H"].copy()
+    h[0, :] = 0.0; h[-1, :] = 0.0; h[:, 0] = 0.0; h[:, -1] = 0.0
+    st["H"] = h
+    g = Roms(cfg, local)
+    g.attach_torch_comm(dist)
+    cases.initialize(g, st)
+    G = json.load(open(os.path.join(HERE, "golden", "rivers_ana_diag.json")))["diag"]
+    worst = np.zeros(4)
+    rows = []
+    for n in range(0, min(nsteps, 20) + 1):
+        if n:
+            g.call("step")
+        d = g.diag()
+        ref = np.array([G[n]["KE"], G[n]["BAROTR_KE"], G[n]["MAX_ADV_CFL"], G[n]["MAX_VERT_CFL"]])
+        dev = np.where(ref != 0, np.abs(d - ref) / np.where(ref != 0, np.abs(ref), 1.0), np.abs(d))
+        worst = np.maximum(worst, dev)
+        rows.append((n, d.tolist(), dev.tolist()))
+    ok = worst.max() <= 1e-11
+    if rank == 0:
+        for n, d, dev in rows:
+            print(f"line {n:2d}: " + " ".join(f"{x:.16e}" for x in d) + "   rel.dev " + " ".join(f"{x:.1e}" for x in dev), flush=True)
+        print(f"Rivers_ana log on 3x2 GPU blocks with the reference's halo of h: worst relative deviation per column {worst}  -> {'OK' if ok else 'MISMATCH'}", flush=True)
     t = torch.tensor([0 if ok else 1], device="cuda")
     dist.all_reduce(t)
     g.close()

@@ -463,3 +463,19 @@ def test_two_gpu_halo_exchange_parity():
         r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2", "--master-addr", "127.0.0.1",
                             "--master-port", str(port), script, "3", mode], capture_output=True, text=True, timeout=600)
         assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+
+
+def test_six_gpu_run_reproduces_the_rivers_ana_log():
+    """The CUDA path decomposed like the run that wrote the reference's Rivers_ana log (3x2 blocks) and given the bathymetry as that run
+    had it (h = 0 in the second halo line of every block: tests/Rivers_ana/ana_grid.h fills 0:nx+1 only, analytic grids are never
+    exchanged) reproduces the log itself on all 21 lines x 4 columns (observed <= 4.3e-16 on the energies, <= 4.3e-13 on the Courant
+    numbers: profiles/r2_rivers_ana_reflog_6gpu.txt).  Needs 6 GPUs; skipped on smaller boxes."""
+    import subprocess
+    import sys
+    import torch
+    if torch.cuda.device_count() < 6:
+        pytest.skip("needs 6 GPUs")
+    script = os.path.join(os.path.dirname(__file__), "mgpu_parity.py")
+    r = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=6", "--master-addr", "127.0.0.1",
+                        "--master-port", "29750", script, "20", "reflog"], capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
