@@ -5,7 +5,9 @@
 //
 // Parity pin: the restatement reproduces the reference's golden regression log
 // tests/Filament/benchmark.result_github_gnu:146-167 (KINETIC_ENRG, BAROTR_KE, MAX_ADV_CFL,
-// MAX_VERT_CFL for steps 0..20); see tests/test_oracle_golden.py.
+// MAX_VERT_CFL for steps 0..20), tests/Pipes_ana/benchmark.result_github_gnu (21 lines x 4 columns, <= 1.5e-14) and
+// tests/Rivers_ana/benchmark.result_github_gnu (21 lines x 4 columns, <= 4.3e-13, with the halo artifact of that run emulated:
+// orc_set_block_halo_artifact); see tests/test_oracle_golden.py.
 // PARITY UNPINNED for the open-boundary branches (cfg.obc_*: zetabc, u2dbc, v2dbc, u3dbc, v3dbc, t3dbc under OBC_M2FLATHER /
 // OBC_M3ORLANSKI / OBC_TORLANSKI): every reference case with an open edge needs netCDF input that is not in the reference tree, so no
 // golden log covers them; tests/test_open_boundaries.py holds the physical properties that stand in (radiation, transparency).

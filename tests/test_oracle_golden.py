@@ -216,8 +216,9 @@ def test_pipe_source_budgets_oracle():
 
 def test_rivers_ana_golden_without_kpp():
     """The reference's Rivers_ana log (tests/golden/rivers_ana_diag.json) exercises what Filament does not: closed walls, a land
-    mask, a sloping bottom, the nonlinear split EOS, T+S and a river source -- but also the KPP closure (lmd_vmix/lmd_kpp,
-    SURVEY.md 8f-2), which this path does not have, so the log cannot be reproduced to round-off.  What CAN be checked: with
+    mask, a sloping bottom, the nonlinear split EOS, T+S and a river source -- and the KPP closure (lmd_vmix/lmd_kpp,
+    SURVEY.md 8f-2).  With the closure the log is met to round-off (test_rivers_ana_golden_with_kpp); this older test keeps the closure
+    OFF and checks the sensitivity bracket that was the only statement possible before the closure existed: with
     uniform Akv/Akt standing in for KPP the oracle stays within the mixing sensitivity of the log -- kinetic and barotropic
     kinetic energy of step 2 (the first non-zero ones, driven by the river through step2d and the predictor) agree to 5e-9
     relative for both Akv = 0 and Akv = 1e-4 m2/s, all four columns of steps 1-6 agree to 2e-3, and the two stand-ins BRACKET
