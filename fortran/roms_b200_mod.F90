@@ -35,6 +35,7 @@ module roms_b200_mod
     real(c_double) :: tnu2(ROMS_MAXNT)
     integer(c_int) :: obc_west, obc_east, obc_south, obc_north
     real(c_double) :: ubind
+    integer(c_int) :: obc_m2, obc_m3, obc_t
   end type roms_cfg
 
   ! enum roms_field (0-based, order of include/roms_b200.h)

@@ -50,6 +50,11 @@ typedef struct roms_cfg {
      with Z_FRC_BRY, M2_FRC_BRY, M3_FRC_BRY, T_FRC_BRY boundary data (boundary.F:109-222) pushed as ROMS_*_WEST ... ROMS_*_NORTH. */
   int obc_west, obc_east, obc_south, obc_north;   /* cppdefs OBC_WEST / OBC_EAST / OBC_SOUTH / OBC_NORTH (ignored on a periodic edge) */
   double ubind;               /* ubind keyword [m/s]: binding velocity towards the boundary data on inflow (u3dbc_im.F:83-90)      */
+  /* the reference's alternative open conditions, one choice per variable family for all open edges (they are compile-time switches there):
+     0 = the default above; 1 = OBC_M2SPECIFIED / OBC_M3SPECIFIED / OBC_TSPECIFIED (boundary value = boundary data, u2dbc_im.F:130-140,
+     u3dbc_im.F:121-131, t3dbc_im.F:85-96); 2 = none of the switches (zero-gradient, the "#else" branches).  With obc_m2 != 0 the free
+     surface takes the gradient condition (zetabc.F:54-61). */
+  int obc_m2, obc_m3, obc_t;
 } roms_cfg;
 
 /* Field identifiers for roms_push / roms_pull.  `lvl` selects the time level (1-based, as in

@@ -967,25 +967,26 @@ void zetabc(Orc& o, vec& zeta_new) {
   GEOM
   const vec& zs = o.zeta[o.kstp - 1];
   const double dtfast = o.dtfast, g = o.c.g;
-  if (OBCW) {   // zetabc.F:28-36
+  const bool zf = o.c.obc_m2 == 0;     // the Flather companion condition; with OBC_M2SPECIFIED or no switch: gradient (zetabc.F:54-61)
+  if (OBCW && zf) {   // zetabc.F:28-36
     for (int j = jstrV - 1; j <= jend; ++j) {
       const double cx = dtfast * A2(o.pm, istr, j) * sqrt(g * A2(o.h, istr, j));
       A2(zeta_new, istr - 1, j) = ((1. - cx) * A2(zs, istr - 1, j) + cx * A2(zs, istr, j)) * A2(o.rmask, istr - 1, j);
     }
   } else if (WWALL) for (int j = jstrV - 1; j <= jend; ++j) A2(zeta_new, istr - 1, j) = A2(zeta_new, istr, j) * A2(o.rmask, istr - 1, j);
-  if (OBCE) {   // zetabc.F:66-75
+  if (OBCE && zf) {   // zetabc.F:66-75
     for (int j = jstrV - 1; j <= jend; ++j) {
       const double cx = dtfast * A2(o.pm, iend, j) * sqrt(g * A2(o.h, iend, j));
       A2(zeta_new, iend + 1, j) = ((1. - cx) * A2(zs, iend + 1, j) + cx * A2(zs, iend, j)) * A2(o.rmask, iend + 1, j);
     }
   } else if (EWALL) for (int j = jstrV - 1; j <= jend; ++j) A2(zeta_new, iend + 1, j) = A2(zeta_new, iend, j) * A2(o.rmask, iend + 1, j);
-  if (OBCS) {   // zetabc.F:125-134
+  if (OBCS && zf) {   // zetabc.F:125-134
     for (int i = istrU - 1; i <= iend; ++i) {
       const double cx = dtfast * A2(o.pn, i, jstr) * sqrt(g * A2(o.h, i, jstr));
       A2(zeta_new, i, jstr - 1) = ((1. - cx) * A2(zs, i, jstr - 1) + cx * A2(zs, i, jstr)) * A2(o.rmask, i, jstr - 1);
     }
   } else if (SWALL) for (int i = istrU - 1; i <= iend; ++i) A2(zeta_new, i, jstr - 1) = A2(zeta_new, i, jstr) * A2(o.rmask, i, jstr - 1);
-  if (OBCN) {   // zetabc.F:165-174
+  if (OBCN && zf) {   // zetabc.F:165-174
     for (int i = istrU - 1; i <= iend; ++i) {
       const double cx = dtfast * A2(o.pn, i, jend) * sqrt(g * A2(o.h, i, jend));
       A2(zeta_new, i, jend + 1) = ((1. - cx) * A2(zs, i, jend + 1) + cx * A2(zs, i, jend)) * A2(o.rmask, i, jend + 1);
@@ -1016,12 +1017,17 @@ void u2dbc(Orc& o, vec& ubar) {
   GEOM
   const vec &zs = o.zeta[o.kstp - 1], &zn = o.zeta[o.knew - 1], &us = o.ubar[o.kstp - 1], &vs = o.vbar[o.kstp - 1];
   const double dtfast = o.dtfast, g = o.c.g;
-  if (OBCW) {
+  const int m2 = o.c.obc_m2;     // 0 Flather, 1 OBC_M2SPECIFIED (u2dbc_im.F:130-140), 2 gradient (:141-148)
+  if (OBCW && m2 == 1) for (int j = jstr; j <= jend; ++j) A2(ubar, istr, j) = B1(o.ubar_bry[0], j) * A2(o.umask, istr, j);
+  else if (OBCW && m2 == 2) for (int j = jstr; j <= jend; ++j) A2(ubar, istr, j) = A2(ubar, istr + 1, j) * A2(o.umask, istr, j);
+  else if (OBCW) {
     for (int j = jstr; j <= jend; ++j)
       A2(ubar, istr, j) = flather(dtfast, g, A2(o.h, istr - 1, j), A2(o.h, istr, j), A2(o.pm, istr - 1, j), A2(o.pm, istr, j), A2(zs, istr, j), A2(zs, istr - 1, j),
                                   A2(zn, istr, j), A2(us, istr, j), A2(us, istr + 1, j), B1(o.ubar_bry[0], j), B1(o.zeta_bry[0], j), -1., true) * A2(o.umask, istr, j);
   } else if (WWALL) for (int j = jstr; j <= jend; ++j) A2(ubar, istr, j) = 0.0;
-  if (OBCE) {
+  if (OBCE && m2 == 1) for (int j = jstr; j <= jend; ++j) A2(ubar, iend + 1, j) = B1(o.ubar_bry[1], j) * A2(o.umask, iend + 1, j);
+  else if (OBCE && m2 == 2) for (int j = jstr; j <= jend; ++j) A2(ubar, iend + 1, j) = A2(ubar, iend, j) * A2(o.umask, iend + 1, j);
+  else if (OBCE) {
     for (int j = jstr; j <= jend; ++j)
       A2(ubar, iend + 1, j) = flather(dtfast, g, A2(o.h, iend + 1, j), A2(o.h, iend, j), A2(o.pm, iend + 1, j), A2(o.pm, iend, j), A2(zs, iend, j), A2(zs, iend + 1, j),
                                       A2(zn, iend, j), A2(us, iend + 1, j), A2(us, iend, j), B1(o.ubar_bry[1], j), B1(o.zeta_bry[1], j), +1., false) * A2(o.umask, iend + 1, j);
@@ -1048,9 +1054,15 @@ void u2dbc(Orc& o, vec& ubar) {
       A2(ubar, i, jb) = r * A2(o.umask, i, jb);
     }
   };
-  if (OBCS) tang(jstr - 1, jstr, -1., o.ubar_bry[2]);
+  // tangential component under OBC_M2SPECIFIED / no switch (u2dbc_im.F:337-349): the data / the interior neighbour, i = istrU:iend
+  auto tang_alt = [&](int jb, int ja, const vec& bry) {
+    for (int i = istrU; i <= iend; ++i) A2(ubar, i, jb) = (m2 == 1 ? B1(bry, i) : A2(ubar, i, ja)) * A2(o.umask, i, jb);
+  };
+  if (OBCS && m2) tang_alt(jstr - 1, jstr, o.ubar_bry[2]);
+  else if (OBCS) tang(jstr - 1, jstr, -1., o.ubar_bry[2]);
   else if (SWALL) for (int i = istr; i <= iendR; ++i) A2(ubar, i, jstr - 1) = o.c.gamma2 * A2(ubar, i, jstr) * A2(o.umask, i, jstr - 1);
-  if (OBCN) tang(jend + 1, jend, +1., o.ubar_bry[3]);
+  if (OBCN && m2) tang_alt(jend + 1, jend, o.ubar_bry[3]);
+  else if (OBCN) tang(jend + 1, jend, +1., o.ubar_bry[3]);
   else if (NWALL) for (int i = istr; i <= iendR; ++i) A2(ubar, i, jend + 1) = o.c.gamma2 * A2(ubar, i, jend) * A2(o.umask, i, jend + 1);
   // corners between adjacent open edges (u2dbc_im.F:453-476)
   if (OBCS && OBCW) A2(ubar, istr, jstr - 1) = 0.5 * (A2(ubar, istr + 1, jstr - 1) + A2(ubar, istr, jstr));
@@ -1062,12 +1074,17 @@ void v2dbc(Orc& o, vec& vbar) {
   GEOM
   const vec &zs = o.zeta[o.kstp - 1], &zn = o.zeta[o.knew - 1], &us = o.ubar[o.kstp - 1], &vs = o.vbar[o.kstp - 1];
   const double dtfast = o.dtfast, g = o.c.g;
-  if (OBCS) {
+  const int m2 = o.c.obc_m2;
+  if (OBCS && m2 == 1) for (int i = istr; i <= iend; ++i) A2(vbar, i, jstr) = B1(o.vbar_bry[2], i) * A2(o.vmask, i, jstr);
+  else if (OBCS && m2 == 2) for (int i = istr; i <= iend; ++i) A2(vbar, i, jstr) = A2(vbar, i, jstr + 1) * A2(o.vmask, i, jstr);
+  else if (OBCS) {
     for (int i = istr; i <= iend; ++i)
       A2(vbar, i, jstr) = flather(dtfast, g, A2(o.h, i, jstr - 1), A2(o.h, i, jstr), A2(o.pn, i, jstr - 1), A2(o.pn, i, jstr), A2(zs, i, jstr), A2(zs, i, jstr - 1),
                                   A2(zn, i, jstr), A2(vs, i, jstr), A2(vs, i, jstr + 1), B1(o.vbar_bry[2], i), B1(o.zeta_bry[2], i), -1., true) * A2(o.vmask, i, jstr);
   } else if (SWALL) for (int i = istr; i <= iend; ++i) A2(vbar, i, jstr) = 0.0;
-  if (OBCN) {
+  if (OBCN && m2 == 1) for (int i = istr; i <= iend; ++i) A2(vbar, i, jend + 1) = B1(o.vbar_bry[3], i) * A2(o.vmask, i, jend + 1);
+  else if (OBCN && m2 == 2) for (int i = istr; i <= iend; ++i) A2(vbar, i, jend + 1) = A2(vbar, i, jend) * A2(o.vmask, i, jend + 1);
+  else if (OBCN) {
     for (int i = istr; i <= iend; ++i)
       A2(vbar, i, jend + 1) = flather(dtfast, g, A2(o.h, i, jend + 1), A2(o.h, i, jend), A2(o.pn, i, jend + 1), A2(o.pn, i, jend), A2(zs, i, jend), A2(zs, i, jend + 1),
                                       A2(zn, i, jend), A2(vs, i, jend + 1), A2(vs, i, jend), B1(o.vbar_bry[3], i), B1(o.zeta_bry[3], i), +1., false) * A2(o.vmask, i, jend + 1);
@@ -1092,9 +1109,14 @@ void v2dbc(Orc& o, vec& vbar) {
       A2(vbar, ib, j) = r * A2(o.vmask, ib, j);
     }
   };
-  if (OBCW) tang(istr - 1, istr, -1., o.vbar_bry[0]);
+  auto tang_alt = [&](int ib, int ia, const vec& bry) {
+    for (int j = jstrV; j <= jend; ++j) A2(vbar, ib, j) = (m2 == 1 ? B1(bry, j) : A2(vbar, ia, j)) * A2(o.vmask, ib, j);
+  };
+  if (OBCW && m2) tang_alt(istr - 1, istr, o.vbar_bry[0]);
+  else if (OBCW) tang(istr - 1, istr, -1., o.vbar_bry[0]);
   else if (WWALL) for (int j = jstr; j <= jendR; ++j) A2(vbar, istr - 1, j) = o.c.gamma2 * A2(vbar, istr, j) * A2(o.vmask, istr - 1, j);
-  if (OBCE) tang(iend + 1, iend, +1., o.vbar_bry[1]);
+  if (OBCE && m2) tang_alt(iend + 1, iend, o.vbar_bry[1]);
+  else if (OBCE) tang(iend + 1, iend, +1., o.vbar_bry[1]);
   else if (EWALL) for (int j = jstr; j <= jendR; ++j) A2(vbar, iend + 1, j) = o.c.gamma2 * A2(vbar, iend, j) * A2(o.vmask, iend + 1, j);
   if (OBCW && OBCS) A2(vbar, istr - 1, jstr) = 0.5 * (A2(vbar, istr - 1, jstr + 1) + A2(vbar, istr, jstr));
   if (OBCE && OBCS) A2(vbar, iend + 1, jstr) = 0.5 * (A2(vbar, iend + 1, jstr + 1) + A2(vbar, iend, jstr));
@@ -1125,9 +1147,11 @@ void u3dbc(Orc& o, vec& u) {
   GEOM
   const vec &us = o.u[o.nstp - 1], &ur = o.u[o.nrhs - 1], &vr = o.v[o.nrhs - 1];
   const double dtfwd = (o.nnew == 3) ? 0.5 * o.c.dt : o.c.dt, ubind = o.c.ubind;
-  const int LW = o.bryL(0), LS = o.bryL(2);
+  const int LW = o.bryL(0), LS = o.bryL(2), m3 = o.c.obc_m3;
   for (int k = 1; k <= N; ++k) {
-    if (OBCW) {
+    if (OBCW && m3 == 1) for (int j = jstr; j <= jend; ++j) A3(u, istr, j, k) = B2(o.u_bry[0], j, k, LW) * A2(o.umask, istr, j);        // u3dbc_im.F:121-131
+    else if (OBCW && m3 == 2) for (int j = jstr; j <= jend; ++j) A3(u, istr, j, k) = A3(u, istr + 1, j, k) * A2(o.umask, istr, j);
+    else if (OBCW) {
       auto grad = [&](int i, int j) { return (A3(us, i, j, k) - A3(us, i, j - 1, k)) * A2(o.pmask, i, j); };
       for (int j = jstr; j <= jend; ++j) {
         const double b = B2(o.u_bry[0], j, k, LW);
@@ -1135,7 +1159,9 @@ void u3dbc(Orc& o, vec& u) {
                                      grad(istr, j), grad(istr, j + 1), b, b > 0., ubind, dtfwd, 0.5 * (A2(o.pm, istr - 1, j) + A2(o.pm, istr, j))) * A2(o.umask, istr, j);
       }
     } else if (WWALL) for (int j = jstr; j <= jend; ++j) A3(u, istr, j, k) = 0.0;
-    if (OBCE) {
+    if (OBCE && m3 == 1) for (int j = jstr; j <= jend; ++j) A3(u, iend + 1, j, k) = B2(o.u_bry[1], j, k, LW) * A2(o.umask, iend + 1, j);
+    else if (OBCE && m3 == 2) for (int j = jstr; j <= jend; ++j) A3(u, iend + 1, j, k) = A3(u, iend, j, k) * A2(o.umask, iend + 1, j);
+    else if (OBCE) {
       auto grad = [&](int i, int j) { return (A3(us, i, j, k) - A3(us, i, j - 1, k)) * A2(o.pmask, i, j); };
       for (int j = jstr; j <= jend; ++j) {
         const double b = B2(o.u_bry[1], j, k, LW);
@@ -1164,9 +1190,14 @@ void u3dbc(Orc& o, vec& u) {
         A3(u, i, jb, k) = r * A2(o.umask, i, jb);
       }
     };
-    if (OBCS) tang(jstr - 1, jstr, -1., o.u_bry[2]);
+    auto tang_alt = [&](int jb, int ja, const vec& bry) {
+      for (int i = istrU; i <= iend; ++i) A3(u, i, jb, k) = (m3 == 1 ? B2(bry, i, k, LS) : A3(u, i, ja, k)) * A2(o.umask, i, jb);
+    };
+    if (OBCS && m3) tang_alt(jstr - 1, jstr, o.u_bry[2]);
+    else if (OBCS) tang(jstr - 1, jstr, -1., o.u_bry[2]);
     else if (SWALL) for (int i = istr; i <= iendR; ++i) A3(u, i, jstr - 1, k) = o.c.gamma2 * A3(u, i, jstr, k) * A2(o.umask, i, jstr - 1);
-    if (OBCN) tang(jend + 1, jend, +1., o.u_bry[3]);
+    if (OBCN && m3) tang_alt(jend + 1, jend, o.u_bry[3]);
+    else if (OBCN) tang(jend + 1, jend, +1., o.u_bry[3]);
     else if (NWALL) for (int i = istr; i <= iendR; ++i) A3(u, i, jend + 1, k) = o.c.gamma2 * A3(u, i, jend, k) * A2(o.umask, i, jend + 1);
   }
   for (int k = 1; k <= N; ++k) {   // corners between adjacent open edges (u3dbc_im.F:397-421)
@@ -1180,9 +1211,11 @@ void v3dbc(Orc& o, vec& v) {
   GEOM
   const vec &vs = o.v[o.nstp - 1], &ur = o.u[o.nrhs - 1], &vr = o.v[o.nrhs - 1];
   const double dtfwd = (o.nnew == 3) ? 0.5 * o.c.dt : o.c.dt, ubind = o.c.ubind;
-  const int LW = o.bryL(0), LS = o.bryL(2);
+  const int LW = o.bryL(0), LS = o.bryL(2), m3 = o.c.obc_m3;
   for (int k = 1; k <= N; ++k) {
-    if (OBCS) {   // v3dbc_im.F:44-111
+    if (OBCS && m3 == 1) for (int i = istr; i <= iend; ++i) A3(v, i, jstr, k) = B2(o.v_bry[2], i, k, LS) * A2(o.vmask, i, jstr);
+    else if (OBCS && m3 == 2) for (int i = istr; i <= iend; ++i) A3(v, i, jstr, k) = A3(v, i, jstr + 1, k) * A2(o.vmask, i, jstr);
+    else if (OBCS) {   // v3dbc_im.F:44-111
       auto grad = [&](int i, int j) { return (A3(vs, i, j, k) - A3(vs, i - 1, j, k)) * A2(o.pmask, i, j); };
       for (int i = istr; i <= iend; ++i) {
         const double b = B2(o.v_bry[2], i, k, LS);
@@ -1190,7 +1223,9 @@ void v3dbc(Orc& o, vec& v) {
                                      grad(i, jstr), grad(i + 1, jstr), b, b > 0., ubind, dtfwd, 0.5 * (A2(o.pn, i, jstr - 1) + A2(o.pn, i, jstr))) * A2(o.vmask, i, jstr);
       }
     } else if (SWALL) for (int i = istr; i <= iend; ++i) A3(v, i, jstr, k) = 0.0;
-    if (OBCN) {
+    if (OBCN && m3 == 1) for (int i = istr; i <= iend; ++i) A3(v, i, jend + 1, k) = B2(o.v_bry[3], i, k, LS) * A2(o.vmask, i, jend + 1);
+    else if (OBCN && m3 == 2) for (int i = istr; i <= iend; ++i) A3(v, i, jend + 1, k) = A3(v, i, jend, k) * A2(o.vmask, i, jend + 1);
+    else if (OBCN) {
       auto grad = [&](int i, int j) { return (A3(vs, i, j, k) - A3(vs, i - 1, j, k)) * A2(o.pmask, i, j); };
       for (int i = istr; i <= iend; ++i) {
         const double b = B2(o.v_bry[3], i, k, LS);
@@ -1218,9 +1253,14 @@ void v3dbc(Orc& o, vec& v) {
         A3(v, ib, j, k) = r * A2(o.vmask, ib, j);
       }
     };
-    if (OBCW) tang(istr - 1, istr, -1., o.v_bry[0]);
+    auto tang_alt = [&](int ib, int ia, const vec& bry) {
+      for (int j = jstrV; j <= jend; ++j) A3(v, ib, j, k) = (m3 == 1 ? B2(bry, j, k, LW) : A3(v, ia, j, k)) * A2(o.vmask, ib, j);
+    };
+    if (OBCW && m3) tang_alt(istr - 1, istr, o.v_bry[0]);
+    else if (OBCW) tang(istr - 1, istr, -1., o.v_bry[0]);
     else if (WWALL) for (int j = jstr; j <= jendR; ++j) A3(v, istr - 1, j, k) = o.c.gamma2 * A3(v, istr, j, k) * A2(o.vmask, istr - 1, j);
-    if (OBCE) tang(iend + 1, iend, +1., o.v_bry[1]);
+    if (OBCE && m3) tang_alt(iend + 1, iend, o.v_bry[1]);
+    else if (OBCE) tang(iend + 1, iend, +1., o.v_bry[1]);
     else if (EWALL) for (int j = jstr; j <= jendR; ++j) A3(v, iend + 1, j, k) = o.c.gamma2 * A3(v, iend, j, k) * A2(o.vmask, iend + 1, j);
   }
   for (int k = 1; k <= N; ++k) {   // v3dbc_im.F:406-430
@@ -1234,11 +1274,12 @@ void t3dbc(Orc& o, vec& t, int itrc) {
   GEOM
   const vec &ts = o.t[o.nstp - 1][itrc], &ur = o.u[o.nrhs - 1], &vr = o.v[o.nrhs - 1];
   const double dtfwd = (o.nnew == 3) ? 0.5 * o.c.dt : o.c.dt;
-  const int LW = o.bryL(0), LS = o.bryL(2);
+  const int LW = o.bryL(0), LS = o.bryL(2), mt = o.c.obc_t;    // 0 OBC_TORLANSKI, 1 OBC_TSPECIFIED (t3dbc_im.F:85-96), 2 gradient = the wall rule
   for (int k = 1; k <= N; ++k) {
     // open edges (t3dbc_im.F:36-83 west, :100-148 east, :165-212 south, :229-277 north): upstream advection by the nrhs velocities, binding
     // to the boundary data on inflow.  The interior neighbour enters at nstp on the west and south and at nnew on the east and north.
-    if (OBCW) {
+    if (OBCW && mt == 1) for (int j = jstr; j <= jend; ++j) A3(t, istr - 1, j, k) = B2(o.t_bry[0][itrc], j, k, LW) * A2(o.rmask, istr - 1, j);
+    else if (OBCW && mt == 0) {
       auto grad = [&](int i, int j) { return (A3(ts, i, j, k) - A3(ts, i, j - 1, k)) * A2(o.vmask, i, j); };
       for (int j = jstr; j <= jend; ++j) {
         double cx = -dtfwd * A3(ur, istr, j, k) * A2(o.pm, istr - 1, j);
@@ -1251,7 +1292,8 @@ void t3dbc(Orc& o, vec& t, int itrc) {
         A3(t, istr - 1, j, k) = r * A2(o.rmask, istr - 1, j);
       }
     } else if (WWALL) for (int j = jstr; j <= jend; ++j) A3(t, istr - 1, j, k) = A3(t, istr, j, k) * A2(o.rmask, istr - 1, j);
-    if (OBCE) {
+    if (OBCE && mt == 1) for (int j = jstr; j <= jend; ++j) A3(t, iend + 1, j, k) = B2(o.t_bry[1][itrc], j, k, LW) * A2(o.rmask, iend + 1, j);
+    else if (OBCE && mt == 0) {
       auto grad = [&](int i, int j) { return (A3(ts, i, j, k) - A3(ts, i, j - 1, k)) * A2(o.vmask, i, j); };
       for (int j = jstr; j <= jend; ++j) {
         double cx = dtfwd * A3(ur, iend + 1, j, k) * A2(o.pm, iend + 1, j);
@@ -1264,7 +1306,8 @@ void t3dbc(Orc& o, vec& t, int itrc) {
         A3(t, iend + 1, j, k) = r * A2(o.rmask, iend + 1, j);
       }
     } else if (EWALL) for (int j = jstr; j <= jend; ++j) A3(t, iend + 1, j, k) = A3(t, iend, j, k) * A2(o.rmask, iend + 1, j);
-    if (OBCS) {
+    if (OBCS && mt == 1) for (int i = istr; i <= iend; ++i) A3(t, i, jstr - 1, k) = B2(o.t_bry[2][itrc], i, k, LS) * A2(o.rmask, i, jstr - 1);
+    else if (OBCS && mt == 0) {
       auto grad = [&](int i, int j) { return (A3(ts, i, j, k) - A3(ts, i - 1, j, k)) * A2(o.umask, i, j); };
       for (int i = istr; i <= iend; ++i) {
         double cx = -dtfwd * A3(vr, i, jstr, k) * A2(o.pn, i, jstr - 1);
@@ -1277,7 +1320,8 @@ void t3dbc(Orc& o, vec& t, int itrc) {
         A3(t, i, jstr - 1, k) = r * A2(o.rmask, i, jstr - 1);
       }
     } else if (SWALL) for (int i = istr; i <= iend; ++i) A3(t, i, jstr - 1, k) = A3(t, i, jstr, k) * A2(o.rmask, i, jstr - 1);
-    if (OBCN) {
+    if (OBCN && mt == 1) for (int i = istr; i <= iend; ++i) A3(t, i, jend + 1, k) = B2(o.t_bry[3][itrc], i, k, LS) * A2(o.rmask, i, jend + 1);
+    else if (OBCN && mt == 0) {
       auto grad = [&](int i, int j) { return (A3(ts, i, j, k) - A3(ts, i - 1, j, k)) * A2(o.umask, i, j); };
       for (int i = istr; i <= iend; ++i) {
         double cx = dtfwd * A3(vr, i, jend + 1, k) * A2(o.pn, i, jend + 1);

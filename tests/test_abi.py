@@ -30,8 +30,8 @@ def test_field_enum_matches_python_mirror():
 
 
 def test_cfg_struct_layout():
-    # 13 ints (padded to 56) + 14 doubles + 2 ints + visc2 + tnu2[ROMS_MAXNT=40] + 4 ints (obc_*) + ubind, natural alignment
-    assert C.sizeof(RomsCfg) == 56 + 14 * 8 + 8 + 8 + 40 * 8 + 16 + 8
+    # 13 ints (padded to 56) + 14 doubles + 2 ints + visc2 + tnu2[ROMS_MAXNT=40] + 4 ints (obc_*) + ubind + 3 ints, natural alignment
+    assert C.sizeof(RomsCfg) == 56 + 14 * 8 + 8 + 8 + 40 * 8 + 16 + 8 + 16          # + obc_m2, obc_m3, obc_t (+4 padding)
     assert RomsCfg.obc_west.offset == 56 + 14 * 8 + 8 + 8 + 40 * 8 and RomsCfg.ubind.offset == RomsCfg.obc_west.offset + 16
     assert RomsCfg.uv_vis2.offset == 56 + 14 * 8 and RomsCfg.visc2.offset == 56 + 14 * 8 + 8
 

@@ -39,12 +39,15 @@ def test_gravity_wave_pulse_leaves_through_open_edges():
     assert left["WESN"][1] < left["E"][1] < left[""][1], left
 
 
+@pytest.mark.parametrize("kind", [0, 1, 2])
 @pytest.mark.parametrize("U0,V0", [(0.05, 0.0), (0.0, -0.03), (0.04, 0.02)])
-def test_uniform_throughflow_is_transparent(U0, V0):
+def test_uniform_throughflow_is_transparent(U0, V0, kind):
     """A uniform current over a flat bottom (f = 0, no drag) with the same current as boundary data is a steady state of the
     equations; the open edges -- characteristic condition, upstream advection of the tangential component, 3-D radiation,
-    tracer advection, corner means -- must leave it untouched (observed: exactly)."""
+    tracer advection, corner means -- must leave it untouched (observed: exactly).  kind 1 / 2: the reference's alternative conditions
+    (OBC_M2SPECIFIED + OBC_M3SPECIFIED + OBC_TSPECIFIED; no switch = zero gradient) for all three variable families."""
     cfg, st = cases.pulse_box(Lm=32, Mm=24, N=4, open_edges="WESN")
+    cfg.obc_m2 = cfg.obc_m3 = cfg.obc_t = kind
     sy, sx, N = cfg.Mm + 4, cfg.Lm + 4, cfg.N
     st["ZETA"] = {(1, 1): np.zeros((sy, sx)), (2, 1): np.zeros((sy, sx))}
     for nm, val in (("U", U0), ("V", V0)):
@@ -150,6 +153,25 @@ def test_open_edges_gpu_equals_oracle(edges, ns, ew):
         done += n
         _same(g, o, cfg, done)
     g.close(); o.close()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("m2,m3,mt", [(1, 1, 1), (2, 2, 2), (0, 1, 2), (1, 0, 0)])
+def test_alternative_open_conditions_gpu_equals_oracle(m2, m3, mt):
+    """OBC_M2SPECIFIED / OBC_M3SPECIFIED / OBC_TSPECIFIED and the zero-gradient defaults, mixed per variable family, on four open edges and
+    on a west+south pair beside closed edges: GPU == oracle exactly."""
+    from romsb200 import Roms
+    for edges in ("WESN", "WS"):
+        cfg, st = cases.channel(48, 40, 8, ns_walls=True, ew_walls=True, seamount=True, island=True, open_edges=edges, dt=60.0, ndtfast=30, depth=500.0)
+        cfg.obc_m2, cfg.obc_m3, cfg.obc_t = m2, m3, mt
+        g, o = Roms(cfg), Oracle(cfg)
+        cases.initialize(g, st); cases.initialize(o, st)
+        done = 0
+        for n in (1, 9):
+            g.call("run", n); o.call("run", n)
+            done += n
+            _same(g, o, cfg, done)
+        g.close(); o.close()
 
 
 @pytest.mark.gpu

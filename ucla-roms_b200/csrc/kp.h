@@ -66,6 +66,7 @@ struct KP {
   // set by the general boundary kernels of obc.cuh instead of the closed-wall code inside the interior kernels (always on when an
   // edge is open; ROMS_BRY=1 forces it for closed basins, which validates those kernels against the in-kernel wall code).
   int obc, bry2d, bry3d;
+  int obc_m2, obc_m3, obc_t;   // 0 Flather / Orlanski / upstream (default), 1 specified, 2 zero-gradient (roms_cfg)
   double ubind;
   // boundary.F:21-60 boundary data, side 0 west, 1 east (lines over j = 0:Mm+1), 2 south, 3 north (lines over i = 0:Lm+1), the reference's
   // extents (boundary.F:111-131); the 3-D ones level-major [k-1][q]; bry_t: [itrc][k-1][q]

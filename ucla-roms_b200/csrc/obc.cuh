@@ -26,7 +26,7 @@ __device__ __noinline__ double ob_zn_edge(const KP& p, const S2D& s, int i, int 
   const int ia = w ? p.istr : (e ? p.iend : i), ja = so ? p.jstr : (n ? p.jend : j);
   const ix2_t c = CIDX(i, j), ca = CIDX(ia, ja);
   const int side = w ? 0 : (e ? 1 : (so ? 2 : 3));
-  if (ob_open(p, side)) {
+  if (ob_open(p, side) && p.obc_m2 == 0) {      // the Flather companion; OBC_M2SPECIFIED / no switch: gradient, like a wall (zetabc.F:54-61)
     const double cx = p.dtfast * (side < 2 ? p.pm[ca] : p.pn[ca]) * sqrt(p.g * p.h[ca]);
     return ((1. - cx) * s.zs[c] + cx * s.zs[ca]) * p.rmask[c];
   }
@@ -79,6 +79,7 @@ __device__ __noinline__ double ob_un(const KP& p, const S2D& s, int i, int j) {
       return p.gamma2 * ob_un(p, s, i, ja) * p.umask[c];         // closed row: its loop runs over istr:iendR after the W/E edges are set
     }
     if (!ob_open(p, side)) return p.gamma2 * s.un[CIDX(i, ja)] * p.umask[c];
+    if (p.obc_m2) return (p.obc_m2 == 1 ? OB_B1(p.bry_ubar[side], i) : s.un[CIDX(i, ja)]) * p.umask[c];   // specified / gradient (u2dbc_im.F:337-349)
     const ix2_t ca = CIDX(i, ja), cv = srow ? ca : c;            // the v-row on the edge: jstr (south), jend+1 (north)
     const double psn = srow ? (p.pn[c] + p.pn[c - 1] + p.pn[ca] + p.pn[ca - 1]) : (p.pn[ca] + p.pn[ca - 1] + p.pn[c] + p.pn[c - 1]);
     const double psm = srow ? (p.pm[c] + p.pm[c - 1] + p.pm[ca] + p.pm[ca - 1]) : (p.pm[ca] + p.pm[ca - 1] + p.pm[c] + p.pm[c - 1]);
@@ -90,11 +91,13 @@ __device__ __noinline__ double ob_un(const KP& p, const S2D& s, int i, int j) {
   }
   if (wface) {
     if (!ob_open(p, 0)) return 0.0;
+    if (p.obc_m2) return (p.obc_m2 == 1 ? OB_B1(p.bry_ubar[0], j) : s.un[c + 1]) * p.umask[c];            // u2dbc_im.F:130-148
     return ob_flather(p.dtfast, p.g, p.h[c - 1], p.h[c], p.pm[c - 1], p.pm[c], s.zs[c], s.zs[c - 1], s2d_zeta_new(p, s, c), s.us[c], s.us[c + 1],
                       OB_B1(p.bry_ubar[0], j), OB_B1(p.bry_zeta[0], j), true) * p.umask[c];
   }
   if (eface) {
     if (!ob_open(p, 1)) return 0.0;
+    if (p.obc_m2) return (p.obc_m2 == 1 ? OB_B1(p.bry_ubar[1], j) : s.un[c - 1]) * p.umask[c];
     return ob_flather(p.dtfast, p.g, p.h[c], p.h[c - 1], p.pm[c], p.pm[c - 1], s.zs[c - 1], s.zs[c], s2d_zeta_new(p, s, c - 1), s.us[c], s.us[c - 1],
                       OB_B1(p.bry_ubar[1], j), OB_B1(p.bry_zeta[1], j), false) * p.umask[c];
   }
@@ -116,6 +119,7 @@ __device__ __noinline__ double ob_vn(const KP& p, const S2D& s, int i, int j) {
       return p.gamma2 * ob_vn(p, s, ia, j) * p.vmask[c];
     }
     if (!ob_open(p, side)) return p.gamma2 * s.vn[CIDX(ia, j)] * p.vmask[c];
+    if (p.obc_m2) return (p.obc_m2 == 1 ? OB_B1(p.bry_vbar[side], j) : s.vn[CIDX(ia, j)]) * p.vmask[c];
     const ix2_t ca = CIDX(ia, j), cu = wcol ? ca : c;            // the u-column on the edge: istr (west), iend+1 (east)
     const double psm = wcol ? (p.pm[c] + p.pm[c - SX] + p.pm[ca] + p.pm[ca - SX]) : (p.pm[ca] + p.pm[ca - SX] + p.pm[c] + p.pm[c - SX]);
     const double psn = wcol ? (p.pn[c] + p.pn[c - SX] + p.pn[ca] + p.pn[ca - SX]) : (p.pn[ca] + p.pn[ca - SX] + p.pn[c] + p.pn[c - SX]);
@@ -127,11 +131,13 @@ __device__ __noinline__ double ob_vn(const KP& p, const S2D& s, int i, int j) {
   }
   if (sface) {
     if (!ob_open(p, 2)) return 0.0;
+    if (p.obc_m2) return (p.obc_m2 == 1 ? OB_B1(p.bry_vbar[2], i) : s.vn[c + SX]) * p.vmask[c];
     return ob_flather(p.dtfast, p.g, p.h[c - SX], p.h[c], p.pn[c - SX], p.pn[c], s.zs[c], s.zs[c - SX], s2d_zeta_new(p, s, c), s.vs[c], s.vs[c + SX],
                       OB_B1(p.bry_vbar[2], i), OB_B1(p.bry_zeta[2], i), true) * p.vmask[c];
   }
   if (nface) {
     if (!ob_open(p, 3)) return 0.0;
+    if (p.obc_m2) return (p.obc_m2 == 1 ? OB_B1(p.bry_vbar[3], i) : s.vn[c - SX]) * p.vmask[c];
     return ob_flather(p.dtfast, p.g, p.h[c], p.h[c - SX], p.pn[c], p.pn[c - SX], s.zs[c - SX], s.zs[c], s2d_zeta_new(p, s, c - SX), s.vs[c], s.vs[c - SX],
                       OB_B1(p.bry_vbar[3], i), OB_B1(p.bry_zeta[3], i), false) * p.vmask[c];
   }
@@ -246,6 +252,7 @@ __device__ __noinline__ double ob3_u(const KP& p, const OB3& o, int i, int j, in
       return p.gamma2 * ob3_u(p, o, i, ja, k) * p.umask[c];
     }
     if (!ob_open(p, side)) return p.gamma2 * R3(o.a, CIDX(i, ja), k) * p.umask[c];
+    if (p.obc_m3) return (p.obc_m3 == 1 ? OB_B2(p.bry_u[side], i, k, BRYL(p, side)) : R3(o.a, CIDX(i, ja), k)) * p.umask[c];   // specified / gradient
     const ix_t ca = CIDX(i, ja), cv = srow ? ca : c;
     const double psn = p.pn[c] + p.pn[c - 1] + p.pn[ca] + p.pn[ca - 1];                        // u3dbc_im.F:212-213,259-260: boundary row first on both edges
     const double psm = p.pm[c] + p.pm[c - 1] + p.pm[ca] + p.pm[ca - 1];
@@ -257,6 +264,7 @@ __device__ __noinline__ double ob3_u(const KP& p, const OB3& o, int i, int j, in
   }
   if (wface | eface) {
     if (!ob_open(p, wface ? 0 : 1)) return 0.0;
+    if (p.obc_m3) return (p.obc_m3 == 1 ? OB_B2(p.bry_u[wface ? 0 : 1], j, k, BRYL(p, 0)) : R3(o.a, c + (wface ? 1 : -1), k)) * p.umask[c];   // u3dbc_im.F:121-131
     const int d = wface ? 1 : -1;                // towards the interior
     const ix_t c1 = c + d, c2 = c + 2 * d;
     // along-edge differences at nstp, masked at the psi-points (u3dbc_im.F:50-57): grad(i,j) = (u(i,j)-u(i,j-1))*pmask(i,j)
@@ -283,6 +291,7 @@ __device__ __noinline__ double ob3_v(const KP& p, const OB3& o, int i, int j, in
       return p.gamma2 * ob3_v(p, o, ia, j, k) * p.vmask[c];
     }
     if (!ob_open(p, side)) return p.gamma2 * R3(o.a, CIDX(ia, j), k) * p.vmask[c];
+    if (p.obc_m3) return (p.obc_m3 == 1 ? OB_B2(p.bry_v[side], j, k, BRYL(p, side)) : R3(o.a, CIDX(ia, j), k)) * p.vmask[c];
     const ix_t ca = CIDX(ia, j), cu = wcol ? ca : c;
     const double psm = p.pm[c] + p.pm[c - SX] + p.pm[ca] + p.pm[ca - SX];                      // v3dbc_im.F: boundary column first on both edges
     const double psn = p.pn[c] + p.pn[c - SX] + p.pn[ca] + p.pn[ca - SX];
@@ -294,6 +303,7 @@ __device__ __noinline__ double ob3_v(const KP& p, const OB3& o, int i, int j, in
   }
   if (sface | nface) {
     if (!ob_open(p, sface ? 2 : 3)) return 0.0;
+    if (p.obc_m3) return (p.obc_m3 == 1 ? OB_B2(p.bry_v[sface ? 2 : 3], i, k, BRYL(p, 2)) : R3(o.a, c + (sface ? SX : -SX), k)) * p.vmask[c];
     const ix_t d = sface ? SX : -SX;
     const ix_t c1 = c + d, c2 = c + 2 * d;
     // grad(i,j) = (v(i,j)-v(i-1,j))*pmask(i,j) (v3dbc_im.F:46-51)
@@ -313,8 +323,9 @@ __device__ __noinline__ double ob3_t_edge(const KP& p, const OB3& o, int i, int 
   if (!(w | e | so | n)) return R3(o.a, c, k);
   const int side = w ? 0 : (e ? 1 : (so ? 2 : 3));
   const ix_t ca = w ? c + 1 : (e ? c - 1 : (so ? c + SX : c - SX));
-  if (!ob_open(p, side)) return R3(o.a, ca, k) * p.rmask[c];
+  if (!ob_open(p, side) || p.obc_t == 2) return R3(o.a, ca, k) * p.rmask[c];     // wall, or an open edge without a switch: gradient
   const double b = OB_B2(p.bry_t[side] + (size_t)o.itrc * p.N * BRYL(p, side), side < 2 ? j : i, k, BRYL(p, side));
+  if (p.obc_t == 1) return b * p.rmask[c];                                         // OBC_TSPECIFIED (t3dbc_im.F:85-96)
   double cx, cy, gb0, gb1, ga0, ga1;
   if (side < 2) {
     const ix_t cu = w ? ca : c;            // the u-face on the edge: istr (west), iend+1 (east)

@@ -379,6 +379,7 @@ int roms_create(const roms_cfg* cfg, int device, roms_ctx** out) {
   if (cfg->ew_periodic) p.obc &= ~3;
   if (cfg->ns_periodic) p.obc &= ~12;
   p.ubind = cfg->ubind;
+  p.obc_m2 = cfg->obc_m2; p.obc_m3 = cfg->obc_m3; p.obc_t = cfg->obc_t;
   int bry = p.obc != 0;
   if (const char* e = getenv("ROMS_BRY")) bry = bry || (atoi(e) != 0 && (!cfg->ew_periodic || !cfg->ns_periodic));
   p.bry2d = p.bry3d = bry;

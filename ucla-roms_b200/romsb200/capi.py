@@ -16,7 +16,8 @@ class RomsCfg(C.Structure):
                 ("rdrg", C.c_double), ("rdrg2", C.c_double), ("Zob", C.c_double), ("gamma2", C.c_double),
                 ("theta_s", C.c_double), ("theta_b", C.c_double), ("hc", C.c_double),
                 ("uv_vis2", C.c_int), ("ts_dif2", C.c_int), ("visc2", C.c_double), ("tnu2", C.c_double * 40),
-                ("obc_west", C.c_int), ("obc_east", C.c_int), ("obc_south", C.c_int), ("obc_north", C.c_int), ("ubind", C.c_double)]
+                ("obc_west", C.c_int), ("obc_east", C.c_int), ("obc_south", C.c_int), ("obc_north", C.c_int), ("ubind", C.c_double),
+                ("obc_m2", C.c_int), ("obc_m3", C.c_int), ("obc_t", C.c_int)]
 
 
 # enum roms_field, in the order of include/roms_b200.h
