@@ -133,6 +133,9 @@ WORKLOADS = {
                      what="analytic seamount h=4500(1-0.5exp(-r^2/(L/5)^2)) in a closed basin, T+S, nonlinear split EOS (4096x4096x100 on 8 GPUs)"),
     "tracers": dict(size=(1024, 2048, 64), nt=32, kw=dict(ns_walls=True, ew_walls=True, river=True, dt=60.0), cpu_sample=(96, 128, 64), total_at=2,
                     what="Rivers_ana geometry (land strip, river channel and river source) in a closed basin, T+S+30 passive tracers (2048x2048x64 on 2 GPUs)"),
+    "regional": dict(size=(1024, 1024, 64), nt=2, kw=dict(ns_walls=True, ew_walls=True, seamount=True, open_edges="WESN"), cpu_sample=(256, 256, 64), total_at=1,
+                     what="regional box with four OPEN edges (Flather / Orlanski radiation, exterior clamped to the initial state) over the analytic seamount, T+S, nonlinear split EOS; "
+                          "not a BASELINE.json config -- the cost of SURVEY.md 8(f) row f3 (single GPU)"),
     "weak": dict(size=(2304, 2304, 100), nt=2, kw=dict(ns_walls=True, ew_walls=True, seamount=True), cpu_sample=(128, 256, 100), total_at=8,
                  what="largest block that fits 180 GB: analytic seamount in a closed basin, T+S (9216x4608x100 on 8 GPUs; 8192x8192x100 needs 1.8 TB)"),
 }

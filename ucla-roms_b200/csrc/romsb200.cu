@@ -1101,7 +1101,7 @@ int roms_step2d(roms_ctx* h) {
     else CK(cudaStreamWaitEvent(h->st, h->ev_edge[o], 0));
     S2D si = s, sr = s;
     si.region = 1; sr.region = 2;
-    const int s2mode_ = p.bry2d ? 0 : h->s2d_tma;   // the marching kernels carry the closed-wall code: open edges take the tile kernel
+    const int s2mode_ = (p.bry2d && h->s2d_tma != 12) ? 0 : h->s2d_tma;   // the marching kernels carry the closed-wall code; as INTERIOR kernel (no boundary point in its mask) the shipped one is fine
     if (s2mode_ == 12) {     // interior by the shipped marching kernel (its emit mask skips the ring)
       int rc = s2d_hyb_launch(h, si, "k_step2d_hyb(interior)");
       if (rc) return rc;
@@ -1151,9 +1151,20 @@ int roms_step2d(roms_ctx* h) {
   if (p.bry2d) {
     // open edges: interior by the tile kernel (it leaves every boundary point alone in this mode), then one thread per boundary point
     dim3 b_(S2_TX, S2_TY, 1), g_((p.iend + IOFF + 1 + S2_TX - 1) / S2_TX, (p.jend - p.jstr + 1 + S2_TY - 1) / S2_TY, 1);
-    if (h->ktiming) kt_begin(h, "k_step2d");
-    k_step2d<<<g_, b_, 0, h->st>>>(p, s);
-    if (h->ktiming) kt_end(h);
+    if (h->s2d_tma == 12 && p.Lm >= 8 && p.Mm >= 8) {
+      // the marching kernel for everything but the ring of width 2 (its wall code never runs there), the tile kernel for the ring
+      S2D si = s, sr = s;
+      si.region = 1; sr.region = 2;
+      int rc = s2d_hyb_launch(h, si, "k_step2d_hyb(interior)");
+      if (rc) return rc;
+      if (h->ktiming) kt_begin(h, "k_step2d(ring)");
+      k_step2d<<<g_, b_, 0, h->st>>>(p, sr);
+      if (h->ktiming) kt_end(h);
+    } else {
+      if (h->ktiming) kt_begin(h, "k_step2d");
+      k_step2d<<<g_, b_, 0, h->st>>>(p, s);
+      if (h->ktiming) kt_end(h);
+    }
     const int len_ = (p.Lm > p.Mm ? p.Lm : p.Mm) + 3;
     dim3 bw_(128, 1, 1), gw_((len_ + 127) / 128, 6, 1);
     if (h->ktiming) kt_begin(h, "k_step2d_bry");
