@@ -265,6 +265,8 @@ def main():
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local = int(os.environ.get("LOCAL_RANK", "0"))
     wl = WORKLOADS[a.workload]
+    if a.workload == "regional" and world > 1:
+        raise SystemExit("bench.py: the 'regional' (open-boundary) workload is built single-domain; decomposed open boundaries are covered by tests/mgpu_parity.py obc")
     Lm, Mm, N = a.size or wl["size"]
     NT = a.nt or wl["nt"]
     cpu_sample = tuple(a.cpu_sample or wl["cpu_sample"])
