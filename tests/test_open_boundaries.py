@@ -186,3 +186,23 @@ def test_gravity_wave_pulse_leaves_on_gpu():
     assert _energy(g, 100.0) / e0 < 1e-2
     _same(g, o, cfg, 30)
     g.close(); o.close()
+
+
+def test_boundary_lines_are_cut_like_the_planes():
+    """take_block hands every rank the slice of the boundary data that belongs to its block: index q of a local line is the same point
+    as index q + offset of the global one (lines run 0:Mm+1 / 0:Lm+1 like the reference's zeta_west(0:Mm+1), boundary.F:111-131)."""
+    cfgG, stG = cases.channel(46, 37, 5, ns_walls=True, ew_walls=True, open_edges="WESN")
+    for npx, npe in ((2, 1), (3, 2)):
+        for rank in range(npx * npe):
+            inode, jnode = rank % npx, rank // npx
+            cfg, st = cases.take_block(cfgG, stG, (inode, jnode, npx, npe))
+            (Lm, i0), (Mm, j0) = cases.block_extent(46, npx, inode), cases.block_extent(37, npe, jnode)
+            assert (cfg.Lm, cfg.Mm, cfg.obc_west, cfg.obc_north, cfg.ubind) == (Lm, Mm, 1, 1, 0.1)
+            assert np.array_equal(st["ZETA_WEST"], stG["ZETA_WEST"][j0:j0 + Mm + 2]) and st["ZETA_WEST"].shape == (Mm + 2,)
+            assert np.array_equal(st["U_SOUTH"], stG["U_SOUTH"][:, i0:i0 + Lm + 2]) and st["U_SOUTH"].shape == (5, Lm + 2)
+            assert np.array_equal(st["T_EAST"][(1, 2)], stG["T_EAST"][(1, 2)][:, j0:j0 + Mm + 2])
+            # the line value at local q is the plane value at the boundary point of the same local index
+            if inode == 0:
+                assert np.array_equal(st["ZETA_WEST"], st["ZETA"][(1, 1)][1:-1, 1])
+            if jnode == npe - 1:
+                assert np.array_equal(st["V_NORTH"], st["V"][(1, 1)][:, Mm + 2, 1:-1])
