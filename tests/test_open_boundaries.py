@@ -39,6 +39,40 @@ def test_gravity_wave_pulse_leaves_through_open_edges():
     assert left["WESN"][1] < left["E"][1] < left[""][1], left
 
 
+def _drive_wave(m, cfg, nsteps, a=0.01, period=1800.0, depth=100.0):
+    """push the incoming wave as western boundary data before every step (what set_bry_all does on the host); returns zeta(x) of row 2 per step"""
+    cg = np.sqrt(cfg.g / depth)
+    ser = []
+    for n in range(1, nsteps + 1):
+        zw = a * np.sin(2 * np.pi / period * (n - 0.5) * cfg.dt)
+        m.push("ZETA_WEST", np.full(cfg.Mm + 2, zw))
+        m.push("UBAR_WEST", np.full(cfg.Mm + 2, cg * zw))
+        m.push("U_WEST", np.full((cfg.N, cfg.Mm + 2), cg * zw))
+        m.call("step")
+        ser.append(m.pull("ZETA", m.get_idx()[6])[4, 2:-2].copy())
+    return np.array(ser)
+
+
+def test_incoming_wave_enters_through_the_boundary_data():
+    """The forcing side of the Flather condition: a gravity wave prescribed as western boundary data (zeta_west = a sin(wt) with the
+    matching ubar_west, period 1800 s, c = 31 m/s) must travel down the channel as a sin(w(t - x/c)) -- amplitude within 2 %, correlation
+    > 0.998 at x = 10, 40 and 70 km once it has filled the 80 km -- and leave through the open eastern edge without building up."""
+    cfg, st = cases.wave_channel()
+    o = Oracle(cfg)
+    cases.initialize(o, st)
+    ser = _drive_wave(o, cfg, 120)
+    o.close()
+    a, period, c = 0.01, 1800.0, np.sqrt(9.81 * 100.0)
+    x = 1.0e3 * (np.arange(1, cfg.Lm + 1) - 0.5)
+    t = np.arange(1, 121) * cfg.dt
+    late = t > 4000.0
+    for i in (10, 40, 70):
+        ref = a * np.sin(2 * np.pi / period * (t - x[i] / c))
+        assert abs(ser[late, i].std() / ref[late].std() - 1.0) < 0.02
+        assert np.corrcoef(ser[late, i], ref[late])[0, 1] > 0.998
+    assert np.abs(ser[-30:]).max() < 1.02 * a
+
+
 @pytest.mark.parametrize("kind", [0, 1, 2])
 @pytest.mark.parametrize("U0,V0", [(0.05, 0.0), (0.0, -0.03), (0.04, 0.02)])
 def test_uniform_throughflow_is_transparent(U0, V0, kind):
@@ -172,6 +206,19 @@ def test_alternative_open_conditions_gpu_equals_oracle(m2, m3, mt):
             done += n
             _same(g, o, cfg, done)
         g.close(); o.close()
+
+
+@pytest.mark.gpu
+def test_incoming_wave_on_gpu():
+    """The boundary data pushed step by step (roms_push of the lines between steps) drive the CUDA path exactly like the oracle."""
+    from romsb200 import Roms
+    cfg, st = cases.wave_channel()
+    g, o = Roms(cfg), Oracle(cfg)
+    cases.initialize(g, st); cases.initialize(o, st)
+    sg, so = _drive_wave(g, cfg, 40), _drive_wave(o, cfg, 40)
+    assert np.array_equal(sg, so)
+    _same(g, o, cfg, 40)
+    g.close(); o.close()
 
 
 @pytest.mark.gpu

@@ -276,6 +276,27 @@ def pulse_box(Lm=64, Mm=64, N=4, open_edges="WESN", dx=1.0e3, depth=100.0, dt=60
     return cfg, st
 
 
+def wave_channel(Lm=80, Mm=8, N=3, dx=1.0e3, depth=100.0, dt=60.0, ndtfast=30):
+    """Forcing test of the open boundaries: a homogeneous flat channel at rest, periodic in eta, open to the west and east.  The caller
+    pushes an incoming gravity wave as western boundary data step by step (zeta_west = a sin(wt), ubar_west = u_west = sqrt(g/h) zeta_west:
+    the incoming characteristic); the eastern data stay zero.  Returns cfg, state."""
+    cfg = RomsCfg(Lm=Lm, Mm=Mm, N=N, NT=2, ew_periodic=0, ns_periodic=1, nonlin_eos=0, salinity=1, ndtfast=ndtfast, np_xi=1, np_eta=1, inode=0, jnode=0,
+                  dt=dt, rho0=1027.0, g=9.81, Tcoef=0.0, T0=10.0, Scoef=0.0, S0=35.0, rdrg=0.0, rdrg2=0.0, Zob=0.0, gamma2=1.0,
+                  theta_s=3.0, theta_b=0.0, hc=25.0)
+    cfg.obc_west = cfg.obc_east = 1
+    cfg.ubind = 0.1
+    sy, sx = Mm + 4, Lm + 4
+    z2, z3 = np.zeros((sy, sx)), np.zeros((N, sy, sx))
+    st = {"H": np.full((sy, sx), depth), "PM": np.full((sy, sx), 1.0 / dx), "PN": np.full((sy, sx), 1.0 / dx), "F": z2.copy(), "RMASK": np.ones((sy, sx)),
+          "ZETA": {(1, 1): z2, (2, 1): z2}, "UBAR": {(1, 1): z2, (2, 1): z2}, "VBAR": {(1, 1): z2, (2, 1): z2},
+          "U": {(1, 1): z3, (2, 1): z3}, "V": {(1, 1): z3, (2, 1): z3},
+          "T": {(1, 1): z3 + 10.0, (2, 1): z3 + 10.0, (1, 2): z3 + 35.0, (2, 2): z3 + 35.0},
+          "AKV": np.zeros((N + 1, sy, sx)), "AKT": {(1, 1): np.zeros((N + 1, sy, sx)), (1, 2): np.zeros((N + 1, sy, sx))}}
+    for nm in ("WEST", "EAST"):
+        st["T_" + nm] = {(1, 1): np.full((N, Mm + 2), 10.0), (1, 2): np.full((N, Mm + 2), 35.0)}
+    return cfg, st
+
+
 def channel_strips(Lm, Mm, N, strips=8, sub=(0, 0, 1, 1), **kw):
     """`channel(...)` for a large block without its dozen full-size temporaries: the rank's block is assembled from `strips`
     horizontal strips, each produced by `channel` itself as the block of a finer process grid (every formula is a function of the
