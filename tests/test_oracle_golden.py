@@ -214,6 +214,27 @@ def test_pipe_source_budgets_oracle():
     o.close()
 
 
+def test_pipes_real_startup_golden():
+    """Third pin of the start-up arithmetic, at the level count of the reference's realistic cases: the 51-row Cs_w table for
+    N = 50, theta_s = theta_b = 6 of tests/Pipes_real/benchmark.result_github_gnu:105-155 (8 printed digits) and its mode-splitting line
+    (:61, nfast = 41).  The time stepping of that case needs netCDF input that is not in the reference tree."""
+    import json
+    import os
+    G = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "pipes_real_startup.json")))
+    assert len(G["Cs_w"]) == 51
+    cfg, _ = cases.rivers_ana_grid()
+    cfg.N, cfg.Lm, cfg.Mm = 50, 8, 8
+    cfg.theta_s, cfg.theta_b, cfg.hc, cfg.ndtfast = G["theta_s"], G["theta_b"], G["hc"], G["ndtfast"]
+    o = Oracle(cfg)
+    assert o.nfast() == G["nfast"]
+    cw, _ = o.scoord()
+    for k, sc, cs in G["Cs_w"]:
+        tol = 0.51e-7 * 10.0 ** np.floor(np.log10(abs(cs))) if cs != 0 else 0.0
+        assert abs(cw[k] - cs) <= tol, (k, cw[k], cs)
+        assert abs(sc - (k - 50) / 50.0) < 1e-4 * max(1.0, abs(sc))      # the printed S-coordinate column (E11.4)
+    o.close()
+
+
 def test_rivers_ana_golden_without_kpp():
     """The reference's Rivers_ana log (tests/golden/rivers_ana_diag.json) exercises what Filament does not: closed walls, a land
     mask, a sloping bottom, the nonlinear split EOS, T+S and a river source -- and the KPP closure (lmd_vmix/lmd_kpp,
