@@ -521,10 +521,10 @@ int roms_sync(roms_ctx* h) {
   return comm_check_failed(&h->comm);
 }
 int roms_kernel_launches(roms_ctx* h, long* n) { *n = h->launches; return 0; }
-// bytes of HBM this context keeps resident (state arena + KPP arrays; halo buffers are not counted)
+// bytes of HBM this context keeps resident (state arena + KPP arrays + boundary data of open edges; halo buffers are not counted)
 int roms_resident_bytes(roms_ctx* h, long long* n) {
   const size_t kpp = h->kpp_buf ? ((size_t)6 * h->kp.SXY * (h->kp.N + 1) + (size_t)13 * h->kp.SXY) * sizeof(double) : 0;
-  *n = (long long)(h->arena_doubles * sizeof(double) + kpp);
+  *n = (long long)(h->arena_doubles * sizeof(double) + kpp + h->bry_doubles * sizeof(double));
   return 0;
 }
 // device-side timing on the library's own stream (bench.py): events bracket whatever is enqueued between
