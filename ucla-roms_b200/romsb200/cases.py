@@ -276,6 +276,31 @@ def pulse_box(Lm=64, Mm=64, N=4, open_edges="WESN", dx=1.0e3, depth=100.0, dt=60
     return cfg, st
 
 
+def strat_box(open_edges="WESN", Lm=32, Mm=32, N=8, dx=500.0, depth=100.0):
+    """Baroclinic radiation test of the open boundaries: `pulse_box` with a linear stratification (10 K over the depth, linear EOS) and a
+    mode-1 Gaussian displacement of the isotherms (5 m) in the centre instead of the free-surface bump; the internal-wave ring it sheds
+    (c1 = 0.44 m/s) has to leave through the 3-D conditions (u3dbc/v3dbc radiation, t3dbc upstream advection towards the resting profile).
+    Returns cfg, state and the background profile Tb(k,j,i)."""
+    cfg, st = pulse_box(Lm=Lm, Mm=Mm, N=N, open_edges=open_edges, dx=dx, depth=depth, dt=60.0, ndtfast=30)
+    cfg.Tcoef = 0.2
+    sy, sx = Mm + 4, Lm + 4
+    z_r, _ = _depths(st["H"], np.zeros((sy, sx)), N, cfg.theta_s, cfg.theta_b, cfg.hc)
+    x = dx * (np.arange(-1, Lm + 3)[None, :] - 0.5) + np.zeros((sy, 1))
+    y = dx * (np.arange(-1, Mm + 3)[:, None] - 0.5) + np.zeros((1, sx))
+    r2 = (x - 0.5 * dx * Lm) ** 2 + (y - 0.5 * dx * Mm) ** 2
+    Tb = 10.0 + 10.0 * (z_r + depth) / depth
+    disp = 5.0 * np.exp(-r2 / (3.0 * dx) ** 2)[None] * np.sin(np.pi * (z_r + depth) / depth)
+    T = Tb - (10.0 / depth) * disp
+    S = st["T"][(1, 2)]
+    st["ZETA"] = {(1, 1): np.zeros((sy, sx)), (2, 1): np.zeros((sy, sx))}
+    st["T"] = {(1, 1): T, (2, 1): T, (1, 2): S, (2, 2): S}
+    for e, nm in (("W", "WEST"), ("E", "EAST"), ("S", "SOUTH"), ("N", "NORTH")):
+        if e in open_edges:
+            L = (sy if e in "WE" else sx) - 2
+            st["T_" + nm] = {(1, 1): np.repeat(Tb[:, 2, 2][:, None], L, 1), (1, 2): np.full((N, L), 35.0)}
+    return cfg, st, Tb
+
+
 def wave_channel(Lm=80, Mm=8, N=3, dx=1.0e3, depth=100.0, dt=60.0, ndtfast=30):
     """Forcing test of the open boundaries: a homogeneous flat channel at rest, periodic in eta, open to the west and east.  The caller
     pushes an incoming gravity wave as western boundary data step by step (zeta_west = a sin(wt), ubar_west = u_west = sqrt(g/h) zeta_west:
