@@ -37,3 +37,18 @@ def test_every_driver_call_has_a_shim():
     used = set(re.findall(r"\b(roms_\w+_c)\b", SHIMS))
     declared = set(re.findall(r"function\s+(roms_\w+_c)\b", MOD))
     assert used <= declared, used - declared
+
+
+def test_boundary_data_shim_pushes_every_line():
+    """roms_b200_push_bry hands all 4 x 6 boundary arrays of boundary.F to the library under the same OBC_* switches, with the field ids
+    of the header and the reference's own lower bound 0."""
+    body = SHIMS[SHIMS.index("subroutine roms_b200_push_bry"):SHIMS.index("end subroutine roms_b200_push_bry")]
+    for side in ("WEST", "EAST", "SOUTH", "NORTH"):
+        blk = body[body.index("#ifdef OBC_" + side):]
+        blk = blk[:blk.index("#endif")]
+        for var in ("ZETA", "UBAR", "VBAR", "U", "V", "T"):
+            fid = f"ROMS_{var}_{side}"
+            assert fid[5:] in FIELDS and fid in blk, fid
+            assert f"{var.lower()}_{side.lower()}(0" in blk
+    assert "roms_push_async" in MOD
+
